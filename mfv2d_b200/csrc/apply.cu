@@ -1,0 +1,502 @@
+// Matrix-free evaluation of bytecode programs applied to element DoF vectors
+// (compute_element_vector, src/evaluation/element_system.c:245-411) - the "apply_recompute" path of
+// y_e = sum_c block(r, c) x_c from the 8 corner doubles and the shared basis tables,
+// without ever forming an element matrix.  Mass and interior-product factors are applied by sum
+// factorisation (interpolate to the q x q points, scale by the metric weight, project back),
+// incidences as signed gathers; only an inverse mass needs a dense matrix, which is built and
+// inverted in shared memory.
+//
+// The same evaluator, fed with unit vectors, is the generic (non-fused) fallback of the matrix path for
+// programs whose blocks are not of the form  coef * [E] * D * [E].
+#include "dense_device.cuh"
+
+#define APPLY_THREADS 128
+
+// flattened program: [n_terms] then per term: row_form, col_form, coef_index, n_factors, 4 ints per factor
+// factor: (type, a, b, c)  type 0: incidence (a = kind) | 1: mass (a = DK_MASS*, b = inverse) |
+//                          2: interior product (a = DK_IPROD*, b = field, c = transpose)
+static void flatten(const mfv2d_plan *plan, const std::vector<BlockProgram> &blocks, std::vector<int32_t> &prog,
+                    std::vector<double> &coef, bool *needs_dense)
+{
+    const int nf = plan->n_forms;
+    prog.clear();
+    coef.clear();
+    prog.push_back(0);
+    int n_terms = 0;
+    for (int r = 0; r < nf; ++r)
+        for (int c = 0; c < nf; ++c)
+        {
+            const BlockProgram &bp = blocks[r * nf + c];
+            if (!bp.present)
+                continue;
+            if (bp.identity)
+            {
+                prog.insert(prog.end(), {r, c, (int32_t)coef.size(), 0});
+                coef.push_back(bp.identity_coef);
+                ++n_terms;
+                continue;
+            }
+            for (const Term &t : bp.terms)
+            {
+                prog.insert(prog.end(), {r, c, (int32_t)coef.size(), (int32_t)t.f.size()});
+                coef.push_back(t.coef);
+                for (const Factor &f : t.f)
+                {
+                    if (!f.is_dense)
+                        prog.insert(prog.end(), {0, f.inc_kind, 0, 0});
+                    else if (f.dk <= DK_MASS2)
+                    {
+                        prog.insert(prog.end(), {1, f.dk, f.inverse, 0});
+                        if (f.inverse)
+                            *needs_dense = true;
+                    }
+                    else
+                        prog.insert(prog.end(), {2, f.dk, f.field, f.transpose});
+                }
+                ++n_terms;
+            }
+        }
+    prog[0] = n_terms;
+}
+
+int plan_lower_vector(mfv2d_plan *plan)
+{
+    std::vector<int32_t> vprog, mprog;
+    std::vector<double> vcoef, mcoef;
+    bool nd = false;
+    flatten(plan, plan->vec_blocks, vprog, vcoef, &nd);
+    flatten(plan, plan->mat_blocks, mprog, mcoef, &nd);
+    plan->vector_needs_dense = nd;
+    // device layout: [vprog | mprog], [vcoef | mcoef]
+    plan->vprog = vprog;
+    plan->vcoef = vcoef;
+    plan->mprog_off = (int)vprog.size();
+    plan->mcoef_off = (int)vcoef.size();
+    plan->vprog.insert(plan->vprog.end(), mprog.begin(), mprog.end());
+    plan->vcoef.insert(plan->vcoef.end(), mcoef.begin(), mcoef.end());
+    if (plan->vcoef.empty())
+        plan->vcoef.push_back(0.0);
+    MFV2D_TRY(mfv2d_cuda_malloc(plan->ctx, plan->vprog.size() * sizeof(int32_t), (void **)&plan->d_vprog));
+    MFV2D_TRY(mfv2d_cuda_malloc(plan->ctx, plan->vcoef.size() * sizeof(double), (void **)&plan->d_vcoef));
+    MFV2D_TRY(mfv2d_cuda_upload(plan->ctx, plan->d_vprog, plan->vprog.data(), plan->vprog.size() * sizeof(int32_t)));
+    MFV2D_TRY(mfv2d_cuda_upload(plan->ctx, plan->d_vcoef, plan->vcoef.data(), plan->vcoef.size() * sizeof(double)));
+    return MFV2D_SUCCESS;
+}
+
+struct ApplyArgs
+{
+    const double *tab;
+    const int32_t *inc;
+    const double *corners;
+    const int32_t *prog;
+    const double *coef;
+    const double *fields[16];
+    const double *x; // [n_elem][N]  (unused in column mode)
+    double *y;       // [n_elem][N]  or  [n_elem][N][N] in column mode
+    unsigned long long n_elem;
+    int tab_len, p, q;
+    int inc_off[4];
+    int n_forms;
+    int form_offsets[17];
+    int n_total;
+    int column_mode; // evaluate the programs on unit vectors and write the columns of the element matrix
+    int needs_dense;
+    int vmax; // length of the ping-pong vectors
+};
+
+struct ApplyView
+{
+    const double *node, *edge, *pnts, *wgts;
+    double *geo;    // 5 q^2
+    double *u0, *u1; // q^2 each: values at the quadrature points
+    double *tmp;    // 2 (p+1) q: intermediate of the two-stage contractions
+    double *v0, *v1; // ping-pong coefficient vectors
+    double *xs, *ys; // element input / output vectors (N each)
+};
+
+// u[a][b] (+)= sum_i A[i][a] sum_j c[i*nB + j] B[j][b]
+__device__ __forceinline__ void interp(const ApplyView &s, int q, const double *__restrict__ c, const double *__restrict__ A,
+                                       int nA, const double *__restrict__ B, int nB, double *__restrict__ u)
+{
+    for (int idx = threadIdx.x; idx < nA * q; idx += blockDim.x)
+    {
+        const int i = idx / q, b = idx - i * q;
+        double r = 0.0;
+        for (int j = 0; j < nB; ++j)
+            r = fma(c[i * nB + j], B[j * q + b], r);
+        s.tmp[idx] = r;
+    }
+    __syncthreads();
+    for (int idx = threadIdx.x; idx < q * q; idx += blockDim.x)
+    {
+        const int a = idx / q, b = idx - a * q;
+        double r = 0.0;
+        for (int i = 0; i < nA; ++i)
+            r = fma(A[i * q + a], s.tmp[i * q + b], r);
+        u[idx] = r;
+    }
+    __syncthreads();
+}
+
+// out[i*nB + j] = sum_a A[i][a] sum_b B[j][b] g[a][b]
+__device__ __forceinline__ void project(const ApplyView &s, int q, const double *__restrict__ g, const double *__restrict__ A,
+                                        int nA, const double *__restrict__ B, int nB, double *__restrict__ out)
+{
+    for (int idx = threadIdx.x; idx < nA * q; idx += blockDim.x)
+    {
+        const int i = idx / q, b = idx - i * q;
+        double r = 0.0;
+        for (int a = 0; a < q; ++a)
+            r = fma(A[i * q + a], g[a * q + b], r);
+        s.tmp[idx] = r;
+    }
+    __syncthreads();
+    for (int idx = threadIdx.x; idx < nA * nB; idx += blockDim.x)
+    {
+        const int i = idx / nB, j = idx - i * nB;
+        double r = 0.0;
+        for (int b = 0; b < q; ++b)
+            r = fma(B[j * q + b], s.tmp[i * q + b], r);
+        out[idx] = r;
+    }
+    __syncthreads();
+}
+
+// pointwise metric scaling between interpolation and projection.  mode selects the weights:
+//  0: u0 *= det W                     (M0)          1: u0 *= W / det                 (M2)
+//  2: (u0,u1) <- (khh u0 + khv u1, khv u0 + kvv u1) W / det            (M1; u0 = h part, u1 = v part)
+//  3: u0 <- kh u0 + kv u1  (P1: 1-form in)         4: (u0,u1) <- (kh u0, kv u0)     (P1^T: 0-form in)
+//  5: (u0,u1) <- (kh u0, kv u0)  (P2: 2-form in)   6: u0 <- kh u0 + kv u1           (P2^T: 1-form in)
+__device__ __forceinline__ void scale_points(const ApplyView &s, int q, int mode, const double *__restrict__ fld)
+{
+    const int q2 = q * q;
+    for (int idx = threadIdx.x; idx < q2; idx += blockDim.x)
+    {
+        const int a = idx / q, b = idx - a * q;
+        const double w = s.wgts[a] * s.wgts[b];
+        const double j00 = s.geo[idx], j01 = s.geo[q2 + idx], j10 = s.geo[2 * q2 + idx], j11 = s.geo[3 * q2 + idx],
+                     det = s.geo[4 * q2 + idx];
+        const double a0 = s.u0[idx];
+        switch (mode)
+        {
+        case 0:
+            s.u0[idx] = a0 * det * w;
+            break;
+        case 1:
+            s.u0[idx] = a0 * w / det;
+            break;
+        case 2: {
+            const double a1 = s.u1[idx];
+            const double khh = (j11 * j11 + j10 * j10) / det * w, kvv = (j00 * j00 + j01 * j01) / det * w,
+                         khv = (j01 * j11 + j00 * j10) / det * w;
+            s.u0[idx] = khh * a0 + khv * a1;
+            s.u1[idx] = khv * a0 + kvv * a1;
+            break;
+        }
+        case 3:
+        case 4: {
+            const double fx = fld[2 * idx], fy = fld[2 * idx + 1];
+            const double kh = (fx * j11 - fy * j10) * w, kv = -(fy * j00 - fx * j01) * w;
+            if (mode == 3)
+                s.u0[idx] = kh * a0 + kv * s.u1[idx];
+            else
+            {
+                s.u0[idx] = kh * a0;
+                s.u1[idx] = kv * a0;
+            }
+            break;
+        }
+        default: {
+            const double fx = fld[2 * idx], fy = fld[2 * idx + 1];
+            const double kh = -(fx * j10 + fy * j11) / det * w, kv = -(fx * j00 + fy * j01) / det * w;
+            if (mode == 6)
+                s.u0[idx] = kh * a0 + kv * s.u1[idx];
+            else
+            {
+                s.u0[idx] = kh * a0;
+                s.u1[idx] = kv * a0;
+            }
+            break;
+        }
+        }
+    }
+    __syncthreads();
+}
+
+__global__ void __launch_bounds__(APPLY_THREADS) element_vector_kernel(const ApplyArgs args)
+{
+    MFV2D_DYN_SMEM(double, smem);
+    const int p = args.p, q = args.q, q2 = q * q, np1 = p + 1, nh = p * (p + 1);
+    const int N = args.n_total;
+    ApplyView s;
+    s.node = smem;
+    s.edge = s.node + np1 * q;
+    s.pnts = s.edge + p * q;
+    s.wgts = s.pnts + q;
+    double *w = smem + ((args.tab_len + 1) & ~1);
+    s.geo = w;
+    w += 5 * q2;
+    s.u0 = w;
+    w += q2;
+    s.u1 = w;
+    w += q2;
+    s.tmp = w;
+    w += 2 * np1 * q;
+    s.v0 = w;
+    w += args.vmax;
+    s.v1 = w;
+    w += args.vmax;
+    s.xs = w;
+    w += N;
+    s.ys = w;
+    w += N;
+    // dense part (only when an inverse mass appears): the assembly kernel's scratch + one matrix
+    SmemView dv;
+    dv.tab = smem;
+    dv.node = smem;
+    dv.edge = smem + np1 * q;
+    dv.pnts = dv.edge + p * q;
+    dv.wgts = dv.pnts + q;
+    dv.geo = s.geo;
+    w = smem + (((int)(w - smem) + 1) & ~1);
+    dv.G = w;
+    w += (q2 + 1) & ~1;
+    dv.ldT = (np1 * np1 + 3) & ~3;
+    dv.T = w;
+    w += q * dv.ldT + 4;
+    dv.arena = w;
+    __shared__ double cs[8];
+
+    for (int i = threadIdx.x; i < args.tab_len; i += blockDim.x)
+        smem[i] = args.tab[i];
+
+    const int n_terms = args.prog[0];
+    const int n_cols = args.column_mode ? N : 1;
+
+    for (unsigned long long elem = blockIdx.x; elem < args.n_elem; elem += gridDim.x)
+    {
+        __syncthreads();
+        for (int i = threadIdx.x; i < 8; i += blockDim.x)
+            cs[i] = args.corners[elem * 8 + i];
+        __syncthreads();
+        fill_geometry(s.geo, cs, s.pnts, q);
+        for (int col = 0; col < n_cols; ++col)
+        {
+            __syncthreads();
+            for (int i = threadIdx.x; i < N; i += blockDim.x)
+            {
+                s.xs[i] = args.column_mode ? (i == col ? 1.0 : 0.0) : args.x[elem * N + i];
+                s.ys[i] = 0.0;
+            }
+            __syncthreads();
+            int pc = 1;
+            for (int t = 0; t < n_terms; ++t)
+            {
+                const int rf = args.prog[pc], cf = args.prog[pc + 1], ci = args.prog[pc + 2], nfac = args.prog[pc + 3];
+                pc += 4;
+                const int c0 = args.form_offsets[cf], nc = args.form_offsets[cf + 1] - c0;
+                const int r0 = args.form_offsets[rf];
+                double *cur = s.v0, *nxt = s.v1;
+                int n_cur = nc;
+                for (int i = threadIdx.x; i < nc; i += blockDim.x)
+                    cur[i] = s.xs[c0 + i];
+                __syncthreads();
+                for (int f = 0; f < nfac; ++f, pc += 4)
+                {
+                    const int type = args.prog[pc], fa = args.prog[pc + 1], fb = args.prog[pc + 2], fc = args.prog[pc + 3];
+                    int n_out;
+                    if (type == 0)
+                    {
+                        // incidence: signed gather through the row map of E
+                        const int rows = (fa == MFV2D_INC_10 || fa == MFV2D_INC_21_T) ? 2 * nh : (fa == MFV2D_INC_21 ? p * p : np1 * np1);
+                        const int4 *map = reinterpret_cast<const int4 *>(args.inc) + args.inc_off[fa];
+                        for (int r = threadIdx.x; r < rows; r += blockDim.x)
+                        {
+                            const int4 e = ld_ro(map + r);
+                            const int ev[4] = {e.x, e.y, e.z, e.w};
+                            double acc = 0.0;
+#pragma unroll
+                            for (int k = 0; k < 4; ++k)
+                            {
+                                if (ev[k] == 0)
+                                    break;
+                                const double v = cur[abs(ev[k]) - 1];
+                                acc += ev[k] < 0 ? -v : v;
+                            }
+                            nxt[r] = acc;
+                        }
+                        __syncthreads();
+                        n_out = rows;
+                    }
+                    else if (type == 1 && fb)
+                    {
+                        // inverse mass: dense matrix in shared memory, inverted in place, then a mat-vec
+                        DevDense dd{fa, 1, -1, 0, 0, 0, 0};
+                        dd.rows = dd.cols = fa == DK_MASS0 ? np1 * np1 : (fa == DK_MASS1 ? 2 * nh : p * p);
+                        int bad = 0;
+                        __syncthreads();
+                        compute_dense(dv, dd, p, q, args.fields, elem, &bad);
+                        __syncthreads();
+                        const int n = dd.rows;
+                        for (int r = threadIdx.x; r < n; r += blockDim.x)
+                        {
+                            double acc = 0.0;
+                            for (int k = 0; k < n; ++k)
+                                acc = fma(dv.arena[r * n + k], cur[k], acc);
+                            nxt[r] = acc;
+                        }
+                        __syncthreads();
+                        n_out = n;
+                    }
+                    else if (type == 1)
+                    {
+                        if (fa == DK_MASS0)
+                        {
+                            interp(s, q, cur, s.node, np1, s.node, np1, s.u0);
+                            scale_points(s, q, 0, nullptr);
+                            project(s, q, s.u0, s.node, np1, s.node, np1, nxt);
+                            n_out = np1 * np1;
+                        }
+                        else if (fa == DK_MASS2)
+                        {
+                            interp(s, q, cur, s.edge, p, s.edge, p, s.u0);
+                            scale_points(s, q, 1, nullptr);
+                            project(s, q, s.u0, s.edge, p, s.edge, p, nxt);
+                            n_out = p * p;
+                        }
+                        else
+                        {
+                            interp(s, q, cur, s.node, np1, s.edge, p, s.u0);      // h part
+                            interp(s, q, cur + nh, s.edge, p, s.node, np1, s.u1); // v part
+                            scale_points(s, q, 2, nullptr);
+                            project(s, q, s.u0, s.node, np1, s.edge, p, nxt);
+                            project(s, q, s.u1, s.edge, p, s.node, np1, nxt + nh);
+                            n_out = 2 * nh;
+                        }
+                    }
+                    else
+                    {
+                        const double *fld = args.fields[fb] + elem * (unsigned long long)(2 * q2);
+                        if (fa == DK_IPROD1 && !fc)
+                        { // (n0 x n1): 1-form in, 0-form out
+                            interp(s, q, cur, s.node, np1, s.edge, p, s.u0);
+                            interp(s, q, cur + nh, s.edge, p, s.node, np1, s.u1);
+                            scale_points(s, q, 3, fld);
+                            project(s, q, s.u0, s.node, np1, s.node, np1, nxt);
+                            n_out = np1 * np1;
+                        }
+                        else if (fa == DK_IPROD1)
+                        { // transposed: 0-form in, 1-form out
+                            interp(s, q, cur, s.node, np1, s.node, np1, s.u0);
+                            scale_points(s, q, 4, fld);
+                            project(s, q, s.u0, s.node, np1, s.edge, p, nxt);
+                            project(s, q, s.u1, s.edge, p, s.node, np1, nxt + nh);
+                            n_out = 2 * nh;
+                        }
+                        else if (!fc)
+                        { // (n1 x n2): 2-form in, 1-form out
+                            interp(s, q, cur, s.edge, p, s.edge, p, s.u0);
+                            scale_points(s, q, 5, fld);
+                            project(s, q, s.u0, s.node, np1, s.edge, p, nxt);
+                            project(s, q, s.u1, s.edge, p, s.node, np1, nxt + nh);
+                            n_out = 2 * nh;
+                        }
+                        else
+                        { // transposed: 1-form in, 2-form out
+                            interp(s, q, cur, s.node, np1, s.edge, p, s.u0);
+                            interp(s, q, cur + nh, s.edge, p, s.node, np1, s.u1);
+                            scale_points(s, q, 6, fld);
+                            project(s, q, s.u0, s.edge, p, s.edge, p, nxt);
+                            n_out = p * p;
+                        }
+                    }
+                    double *sw = cur;
+                    cur = nxt;
+                    nxt = sw;
+                    n_cur = n_out;
+                }
+                const double cf_ = args.coef[ci];
+                for (int i = threadIdx.x; i < n_cur; i += blockDim.x)
+                    s.ys[r0 + i] = fma(cf_, cur[i], s.ys[r0 + i]);
+                __syncthreads();
+            }
+            if (args.column_mode)
+            {
+                double *o = args.y + elem * (unsigned long long)N * N;
+                for (int i = threadIdx.x; i < N; i += blockDim.x)
+                    o[(unsigned long long)i * N + col] = s.ys[i];
+            }
+            else
+            {
+                for (int i = threadIdx.x; i < N; i += blockDim.x)
+                    args.y[elem * N + i] = s.ys[i];
+            }
+        }
+    }
+}
+
+static int launch_apply(const mfv2d_plan *plan, const mfv2d_elements *e, const double *const *fields, const double *d_x,
+                        double *d_y, int column_mode)
+{
+    mfv2d_ctx *ctx = plan->ctx;
+    ApplyArgs a{};
+    a.tab = plan->basis->d_tab;
+    a.inc = plan->basis->d_inc;
+    a.corners = e->d_corners;
+    a.prog = plan->d_vprog + (column_mode ? plan->mprog_off : 0);
+    a.coef = plan->d_vcoef + (column_mode ? plan->mcoef_off : 0);
+    for (int i = 0; i < 16; ++i)
+        a.fields[i] = (fields && i < plan->n_fields) ? fields[i] : nullptr;
+    a.x = d_x;
+    a.y = d_y;
+    a.n_elem = e->n;
+    a.tab_len = plan->basis->tab_len;
+    a.p = plan->p;
+    a.q = plan->q;
+    for (int i = 0; i < 4; ++i)
+        a.inc_off[i] = plan->basis->inc_off[i];
+    a.n_forms = plan->n_forms;
+    for (int i = 0; i <= plan->n_forms; ++i)
+        a.form_offsets[i] = plan->form_offsets[i];
+    a.n_total = plan->n_total;
+    a.column_mode = column_mode;
+    a.needs_dense = plan->vector_needs_dense ? 1 : 0;
+    const int p = plan->p, q = plan->q, q2 = q * q, np1 = p + 1;
+    a.vmax = (2 * p * np1 > np1 * np1 ? 2 * p * np1 : np1 * np1) + 2;
+    a.vmax = (a.vmax + 1) & ~1;
+    size_t doubles = ((a.tab_len + 1) & ~1) + 5 * q2 + 2 * q2 + 2 * np1 * q + 2 * a.vmax + 2 * (size_t)a.n_total + 2;
+    if (plan->vector_needs_dense)
+    {
+        const int ldT = (np1 * np1 + 3) & ~3;
+        const int nmax = 2 * p * np1;
+        doubles += ((q2 + 1) & ~1) + q * ldT + 4 + (size_t)nmax * nmax + 8;
+    }
+    const size_t smem = doubles * sizeof(double);
+    if (smem > ctx->smem_optin)
+        return mfv2d_fail(ctx, MFV2D_CUDA_UNSUPPORTED, "element vectors of order %d need %zu bytes of shared memory", p, smem);
+    MFV2D_CUDA_CHECK(ctx, cudaFuncSetAttribute(element_vector_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int per_sm = 1;
+    MFV2D_CUDA_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, element_vector_kernel, APPLY_THREADS, smem));
+    if (per_sm < 1)
+        per_sm = 1;
+    unsigned long long grid = (unsigned long long)ctx->sm_count * per_sm;
+    if (grid > e->n)
+        grid = e->n;
+    if (grid == 0)
+        return MFV2D_SUCCESS;
+    MFV2D_LAUNCH(element_vector_kernel, (unsigned)grid, APPLY_THREADS, smem, ctx->stream, a);
+    ctx->launches++;
+    MFV2D_CUDA_CHECK(ctx, cudaGetLastError());
+    return MFV2D_SUCCESS;
+}
+
+int launch_element_vector(const mfv2d_plan *plan, const mfv2d_elements *e, const double *const *fields, const double *d_x,
+                          double *d_y)
+{
+    return launch_apply(plan, e, fields, d_x, d_y, 0);
+}
+
+int launch_matrix_by_columns(const mfv2d_plan *plan, const mfv2d_elements *e, const double *const *fields, double *d_out)
+{
+    return launch_apply(plan, e, fields, nullptr, d_out, 1);
+}

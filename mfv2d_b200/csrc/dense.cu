@@ -1,0 +1,348 @@
+// Batched dense algebra on small matrices: inverse and linear solve with partial pivoting
+// (replaces decompose_pivoted_lu / solve_lu / matrix_full_invert, src/algebra/matrix.c:361-534, and the
+// Python-facing _compute_matrix_inverse / _solve_linear_system, :546-660).
+//
+// One CTA per matrix (persistent over the batch).  The working copy lives in shared memory when
+// n*(n+nrhs) doubles fit (n <= ~165 for an inverse), otherwise in the output buffer in global memory
+// (L2 resident).  The reference picks a static row order from the ORIGINAL column magnitudes and fails
+// with MFV2D_PIVOT_FAILED when a column has no unused entry above 1e-12 (matrix.c:424-466); here true
+// partial pivoting is used (same result to rounding for regular matrices) and the same code is reported
+// when the best available pivot is below 1e-12.
+#include "internal.cuh"
+
+#define DENSE_THREADS 256
+#define PIVOT_TOL 1e-12
+
+// CTA-wide argmax of |col[r]| for r in [k, n): returns the row index to every thread.
+__device__ __forceinline__ int block_argmax(const double *__restrict__ M, int ld, int k, int n, double *red_v, int *red_i)
+{
+    double best = -1.0;
+    int bi = k;
+    for (int r = k + threadIdx.x; r < n; r += blockDim.x)
+    {
+        const double v = fabs(M[(size_t)r * ld + k]);
+        if (v > best)
+        {
+            best = v;
+            bi = r;
+        }
+    }
+#ifndef MFV2D_EMU
+    for (int o = 16; o > 0; o >>= 1)
+    {
+        const double ov = __shfl_xor_sync(0xffffffffu, best, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+        if (ov > best || (ov == best && oi < bi))
+        {
+            best = ov;
+            bi = oi;
+        }
+    }
+#endif
+    const int warp = threadIdx.x >> 5, nwarps = MFV2D_NWARPS;
+    if ((threadIdx.x & 31) == 0)
+    {
+        red_v[warp] = best;
+        red_i[warp] = bi;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0)
+    {
+        double b = red_v[0];
+        int i = red_i[0];
+        for (int w = 1; w < nwarps; ++w)
+            if (red_v[w] > b || (red_v[w] == b && red_i[w] < i))
+            {
+                b = red_v[w];
+                i = red_i[w];
+            }
+        red_v[0] = b;
+        red_i[0] = i;
+    }
+    __syncthreads();
+    const int res = red_i[0];
+    return res;
+}
+
+// In-place Gauss-Jordan inverse with partial pivoting of the n x n matrix M (leading dimension n).
+// scratch: 2n doubles (column and row of the pivot), piv: n ints.  Returns non-zero on pivot failure.
+__device__ int gauss_jordan_inverse(double *M, int n, double *scratch, int *piv, double *red_v, int *red_i)
+{
+    double *colk = scratch, *rowk = scratch + n;
+    int bad = 0;
+    for (int k = 0; k < n; ++k)
+    {
+        __syncthreads();
+        const int r = block_argmax(M, n, k, n, red_v, red_i);
+        if (!(red_v[0] >= PIVOT_TOL))
+            bad = 1;
+        if (threadIdx.x == 0)
+            piv[k] = r;
+        if (r != k)
+            for (int j = threadIdx.x; j < n; j += blockDim.x)
+            {
+                const double t = M[(size_t)k * n + j];
+                M[(size_t)k * n + j] = M[(size_t)r * n + j];
+                M[(size_t)r * n + j] = t;
+            }
+        __syncthreads();
+        for (int i = threadIdx.x; i < n; i += blockDim.x)
+        {
+            colk[i] = M[(size_t)i * n + k];
+            rowk[i] = M[(size_t)k * n + i];
+        }
+        __syncthreads();
+        const double ip = 1.0 / colk[k];
+        for (int idx = threadIdx.x; idx < n * n; idx += blockDim.x)
+        {
+            const int i = idx / n, j = idx - i * n;
+            double v;
+            if (i == k)
+                v = (j == k) ? ip : rowk[j] * ip;
+            else if (j == k)
+                v = -colk[i] * ip;
+            else
+                v = fma(-colk[i] * ip, rowk[j], M[idx]);
+            M[idx] = v;
+        }
+    }
+    __syncthreads();
+    // (P A)^-1 = A^-1 P^-1  ->  undo the row swaps as column swaps in reverse order
+    for (int k = n - 1; k >= 0; --k)
+    {
+        const int r = piv[k];
+        if (r != k)
+        {
+            for (int i = threadIdx.x; i < n; i += blockDim.x)
+            {
+                const double t = M[(size_t)i * n + k];
+                M[(size_t)i * n + k] = M[(size_t)i * n + r];
+                M[(size_t)i * n + r] = t;
+            }
+            __syncthreads();
+        }
+    }
+    return bad;
+}
+
+__global__ void __launch_bounds__(DENSE_THREADS) inverse_kernel(int n, unsigned long long batch, const double *__restrict__ in,
+                                                               double *__restrict__ out, int32_t *__restrict__ status,
+                                                               int use_smem)
+{
+    MFV2D_DYN_SMEM(double, smem);
+    __shared__ double red_v[32];
+    __shared__ int red_i[32];
+    const size_t nn = (size_t)n * n;
+    double *scratch = smem;                                   // 2n
+    int *piv = reinterpret_cast<int *>(smem + 2 * n);         // n ints
+    double *work_s = smem + 2 * n + ((n + 1) / 2) + 1;        // n*n when use_smem
+    work_s = smem + (((int)(work_s - smem) + 1) & ~1);
+    for (unsigned long long b = blockIdx.x; b < batch; b += gridDim.x)
+    {
+        __syncthreads();
+        double *M = use_smem ? work_s : out + b * nn;
+        const double *src = in + b * nn;
+        if (use_smem || src != M)
+            for (size_t i = threadIdx.x; i < nn; i += blockDim.x)
+                M[i] = src[i];
+        __syncthreads();
+        const int bad = gauss_jordan_inverse(M, n, scratch, piv, red_v, red_i);
+        __syncthreads();
+        if (use_smem)
+            for (size_t i = threadIdx.x; i < nn; i += blockDim.x)
+                out[b * nn + i] = M[i];
+        if (status && threadIdx.x == 0)
+            status[b] = bad ? MFV2D_PIVOT_FAILED : MFV2D_SUCCESS;
+    }
+}
+
+// Gaussian elimination with partial pivoting on the augmented system [A | B] (n x (n + nrhs)), then
+// back substitution; the working copy W has leading dimension ld = n + nrhs.
+__global__ void __launch_bounds__(DENSE_THREADS) solve_kernel(int n, int nrhs, unsigned long long batch,
+                                                             const double *__restrict__ a, const double *__restrict__ bmat,
+                                                             double *__restrict__ x, double *__restrict__ work_g,
+                                                             int32_t *__restrict__ status, int use_smem)
+{
+    MFV2D_DYN_SMEM(double, smem);
+    __shared__ double red_v[32];
+    __shared__ int red_i[32];
+    const int ld = n + nrhs;
+    const size_t per = (size_t)n * ld;
+    for (unsigned long long b = blockIdx.x; b < batch; b += gridDim.x)
+    {
+        __syncthreads();
+        double *W = use_smem ? smem : work_g + (size_t)blockIdx.x * per;
+        for (size_t idx = threadIdx.x; idx < per; idx += blockDim.x)
+        {
+            const int i = (int)(idx / ld), j = (int)(idx - (size_t)i * ld);
+            W[idx] = j < n ? a[b * (size_t)n * n + (size_t)i * n + j] : bmat[b * (size_t)n * nrhs + (size_t)i * nrhs + (j - n)];
+        }
+        __syncthreads();
+        int bad = 0;
+        for (int k = 0; k < n; ++k)
+        {
+            const int r = block_argmax(W, ld, k, n, red_v, red_i);
+            if (!(red_v[0] >= PIVOT_TOL))
+                bad = 1;
+            if (r != k)
+                for (int j = threadIdx.x; j < ld; j += blockDim.x)
+                {
+                    const double t = W[(size_t)k * ld + j];
+                    W[(size_t)k * ld + j] = W[(size_t)r * ld + j];
+                    W[(size_t)r * ld + j] = t;
+                }
+            __syncthreads();
+            const double ip = 1.0 / W[(size_t)k * ld + k];
+            // eliminate below: rows i > k, columns j > k
+            const int nr = n - k - 1, ncw = ld - k - 1;
+            for (int idx = threadIdx.x; idx < nr * ncw; idx += blockDim.x)
+            {
+                const int i = k + 1 + idx / ncw, j = k + 1 + idx % ncw;
+                const double f = W[(size_t)i * ld + k] * ip;
+                W[(size_t)i * ld + j] = fma(-f, W[(size_t)k * ld + j], W[(size_t)i * ld + j]);
+            }
+            __syncthreads();
+        }
+        // back substitution, one right-hand side per thread
+        for (int c = threadIdx.x; c < nrhs; c += blockDim.x)
+        {
+            for (int i = n - 1; i >= 0; --i)
+            {
+                double s = W[(size_t)i * ld + n + c];
+                for (int j = i + 1; j < n; ++j)
+                    s = fma(-W[(size_t)i * ld + j], W[(size_t)j * ld + n + c], s);
+                W[(size_t)i * ld + n + c] = s / W[(size_t)i * ld + i];
+            }
+        }
+        __syncthreads();
+        for (int idx = threadIdx.x; idx < n * nrhs; idx += blockDim.x)
+        {
+            const int i = idx / nrhs, c = idx - i * nrhs;
+            x[b * (size_t)n * nrhs + idx] = W[(size_t)i * ld + n + c];
+        }
+        if (status && threadIdx.x == 0)
+            status[b] = bad ? MFV2D_PIVOT_FAILED : MFV2D_SUCCESS;
+    }
+}
+
+// device-pointer entry used by system.cu as well
+int launch_inverse_batch(mfv2d_ctx *ctx, int n, size_t batch, const double *d_in, double *d_out, int32_t *d_status)
+{
+    if (batch == 0 || n == 0)
+        return MFV2D_SUCCESS;
+    const size_t head = (size_t)2 * n + (n + 1) / 2 + 4;
+    const size_t smem_full = (head + (size_t)n * n) * sizeof(double);
+    const int use_smem = smem_full <= ctx->smem_optin;
+    const size_t smem = use_smem ? smem_full : head * sizeof(double);
+    MFV2D_CUDA_CHECK(ctx, cudaFuncSetAttribute(inverse_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int per_sm = 1;
+    MFV2D_CUDA_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, inverse_kernel, DENSE_THREADS, smem));
+    if (per_sm < 1)
+        per_sm = 1;
+    size_t grid = (size_t)ctx->sm_count * per_sm;
+    if (grid > batch)
+        grid = batch;
+    MFV2D_LAUNCH(inverse_kernel, (unsigned)grid, DENSE_THREADS, smem, ctx->stream, n, (unsigned long long)batch, d_in, d_out,
+                 d_status, use_smem);
+    ctx->launches++;
+    MFV2D_CUDA_CHECK(ctx, cudaGetLastError());
+    return MFV2D_SUCCESS;
+}
+
+extern "C" {
+
+int mfv2d_cuda_inverse_batch(mfv2d_ctx *ctx, int n, size_t batch, const double *in, double *out, int32_t *status,
+                             int space)
+{
+    if (n < 1)
+        return mfv2d_fail(ctx, MFV2D_BAD_ARGUMENT, "inverse_batch: n must be positive");
+    if (batch == 0)
+        return MFV2D_SUCCESS;
+    const size_t bytes = batch * (size_t)n * n * sizeof(double);
+    Staged i, o, st;
+    int r = stage_in(ctx, in, bytes, space, &i);
+    if (!r)
+        r = stage_out_alloc(ctx, out, bytes, space, &o);
+    if (!r)
+        r = stage_out_alloc(ctx, status, status ? batch * sizeof(int32_t) : 0, space, &st);
+    if (!r)
+        r = launch_inverse_batch(ctx, n, batch, (const double *)i.dev, (double *)o.dev, (int32_t *)st.dev);
+    if (!r)
+    {
+        r = stage_finish(&o);
+        const int r2 = stage_finish(&st);
+        if (!r)
+            r = r2;
+    }
+    else
+    {
+        stage_abort(&o);
+        stage_abort(&st);
+    }
+    stage_abort(&i);
+    return r;
+}
+
+int mfv2d_cuda_solve_batch(mfv2d_ctx *ctx, int n, int nrhs, size_t batch, const double *a, const double *b, double *x,
+                           int32_t *status, int space)
+{
+    if (n < 1 || nrhs < 1)
+        return mfv2d_fail(ctx, MFV2D_BAD_ARGUMENT, "solve_batch: n and nrhs must be positive");
+    if (batch == 0)
+        return MFV2D_SUCCESS;
+    const size_t per = (size_t)n * (n + nrhs);
+    const size_t smem_full = per * sizeof(double);
+    const int use_smem = smem_full <= ctx->smem_optin;
+    const size_t smem = use_smem ? smem_full : 0;
+    Staged sa, sb, sx, st;
+    void *work = nullptr;
+    int r = stage_in(ctx, a, batch * (size_t)n * n * sizeof(double), space, &sa);
+    if (!r)
+        r = stage_in(ctx, b, batch * (size_t)n * nrhs * sizeof(double), space, &sb);
+    if (!r)
+        r = stage_out_alloc(ctx, x, batch * (size_t)n * nrhs * sizeof(double), space, &sx);
+    if (!r)
+        r = stage_out_alloc(ctx, status, status ? batch * sizeof(int32_t) : 0, space, &st);
+    size_t grid = 0;
+    if (!r)
+    {
+        cudaFuncSetAttribute(solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        int per_sm = 1;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, solve_kernel, DENSE_THREADS, smem);
+        if (per_sm < 1)
+            per_sm = 1;
+        grid = (size_t)ctx->sm_count * per_sm;
+        if (grid > batch)
+            grid = batch;
+        if (!use_smem)
+            r = mfv2d_cuda_malloc(ctx, grid * per * sizeof(double), &work);
+    }
+    if (!r)
+    {
+        MFV2D_LAUNCH(solve_kernel, (unsigned)grid, DENSE_THREADS, smem, ctx->stream, n, nrhs, (unsigned long long)batch,
+                     (const double *)sa.dev, (const double *)sb.dev, (double *)sx.dev, (double *)work, (int32_t *)st.dev,
+                     use_smem);
+        ctx->launches++;
+        if (cudaGetLastError() != cudaSuccess)
+            r = mfv2d_fail(ctx, MFV2D_CUDA_ERROR, "solve kernel launch failed");
+    }
+    if (!r)
+    {
+        r = stage_finish(&sx);
+        const int r2 = stage_finish(&st);
+        if (!r)
+            r = r2;
+    }
+    else
+    {
+        stage_abort(&sx);
+        stage_abort(&st);
+    }
+    stage_abort(&sa);
+    stage_abort(&sb);
+    if (work)
+        mfv2d_cuda_free(ctx, work);
+    return r;
+}
+
+} // extern "C"

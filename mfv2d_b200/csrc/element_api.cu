@@ -1,0 +1,469 @@
+// C-ABI entry points for the per-element batches: masses, interior products, field reconstruction,
+// incidence application and bytecode-driven element matrices.
+#include "plan.cuh"
+
+int launch_element_matrix(const mfv2d_plan *plan, const mfv2d_elements *e, const double *const *fields, double *d_out,
+                          int32_t *d_status);
+int launch_element_vector(const mfv2d_plan *plan, const mfv2d_elements *e, const double *const *fields,
+                          const double *d_x, double *d_y);
+int launch_matrix_by_columns(const mfv2d_plan *plan, const mfv2d_elements *e, const double *const *fields, double *d_out);
+
+// ---- field reconstruction (integrating_fields.c:238-352) -------------------------------------
+// one thread per (element, quadrature point)
+__global__ void reconstruct_kernel(const double *__restrict__ tab, int p, int q, const double *__restrict__ corners,
+                                   unsigned long long n_elem, int form, const double *__restrict__ dofs, long long dof_stride,
+                                   double *__restrict__ out)
+{
+    const int q2 = q * q;
+    const double *node = tab, *edge = tab + (p + 1) * q, *pnts = edge + p * q;
+    const unsigned long long total = n_elem * q2;
+    for (unsigned long long g = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; g < total;
+         g += (unsigned long long)gridDim.x * blockDim.x)
+    {
+        const unsigned long long e = g / q2;
+        const int idx = (int)(g - e * q2);
+        const int a = idx / q, b = idx - a * q;
+        const double *c = corners + e * 8;
+        const double eta = pnts[a], xi = pnts[b];
+        const double x0 = c[0], y0 = c[1], x1 = c[2], y1 = c[3], x2 = c[4], y2 = c[5], x3 = c[6], y3 = c[7];
+        const double j00 = 0.25 * ((x1 - x0) * (1 - eta) + (x2 - x3) * (1 + eta));
+        const double j01 = 0.25 * ((y1 - y0) * (1 - eta) + (y2 - y3) * (1 + eta));
+        const double j10 = 0.25 * ((x3 - x0) * (1 - xi) + (x2 - x1) * (1 + xi));
+        const double j11 = 0.25 * ((y3 - y0) * (1 - xi) + (y2 - y1) * (1 + xi));
+        const double det = j00 * j11 - j10 * j01;
+        const double *d = dofs + e * dof_stride;
+        if (form == MFV2D_FORM_ORDER_0)
+        {
+            double s = 0.0;
+            for (int i = 0; i <= p; ++i)
+            {
+                double r = 0.0;
+                for (int j = 0; j <= p; ++j)
+                    r = fma(d[i * (p + 1) + j], node[j * q + b], r);
+                s = fma(r, node[i * q + a], s);
+            }
+            out[g] = s * det;
+        }
+        else if (form == MFV2D_FORM_ORDER_2)
+        {
+            double s = 0.0;
+            for (int i = 0; i < p; ++i)
+            {
+                double r = 0.0;
+                for (int j = 0; j < p; ++j)
+                    r = fma(d[i * p + j], edge[j * q + b], r);
+                s = fma(r, edge[i * q + a], s);
+            }
+            out[g] = s / det;
+        }
+        else
+        {
+            double v_eta = 0.0, v_xi = 0.0; // h part -> eta component, v part -> xi component
+            for (int i = 0; i <= p; ++i)
+            {
+                double r = 0.0;
+                for (int j = 0; j < p; ++j)
+                    r = fma(d[i * p + j], edge[j * q + b], r);
+                v_eta = fma(r, node[i * q + a], v_eta);
+            }
+            const double *dv = d + p * (p + 1);
+            for (int i = 0; i < p; ++i)
+            {
+                double r = 0.0;
+                for (int j = 0; j <= p; ++j)
+                    r = fma(dv[i * (p + 1) + j], node[j * q + b], r);
+                v_xi = fma(r, edge[i * q + a], v_xi);
+            }
+            out[2 * g] = (j00 * v_xi + j10 * v_eta) / det;
+            out[2 * g + 1] = (j01 * v_xi + j11 * v_eta) / det;
+        }
+    }
+}
+
+static int launch_reconstruct(const mfv2d_elements *e, int form, const double *d_dofs, long long dof_stride, double *d_out)
+{
+    mfv2d_ctx *ctx = e->ctx;
+    const int q = e->basis->q;
+    size_t blocks = (e->n * q * q + 127) / 128;
+    if (blocks > (size_t)ctx->sm_count * 32)
+        blocks = (size_t)ctx->sm_count * 32;
+    if (blocks == 0)
+        return MFV2D_SUCCESS;
+    MFV2D_LAUNCH(reconstruct_kernel, (unsigned)blocks, 128, 0, ctx->stream, e->basis->d_tab, e->basis->p, q, e->d_corners,
+                 (unsigned long long)e->n, form, d_dofs, dof_stride, d_out);
+    ctx->launches++;
+    MFV2D_CUDA_CHECK(ctx, cudaGetLastError());
+    return MFV2D_SUCCESS;
+}
+
+// ---- incidence application (incidence.c:16-443) -----------------------------------------------
+// left:  out[b][r][c] = sum_k E[r][k] in[b][k][c]      in (cols(E) x n), out (rows(E) x n)
+// right: out[b][r][c] = sum_k in[b][r][k] E[k][c]      in (n x rows(E)), out (n x cols(E))
+__global__ void incidence_kernel(const int32_t *__restrict__ map, int map_rows, int in_dim, int right, int n,
+                                 unsigned long long batch, const double *__restrict__ in, double *__restrict__ out)
+{
+    // map = row map of E (left) or of E^T (right); map_rows = rows of that map
+    const unsigned long long per_out = (unsigned long long)map_rows * n;
+    const unsigned long long total = batch * per_out;
+    for (unsigned long long g = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; g < total;
+         g += (unsigned long long)gridDim.x * blockDim.x)
+    {
+        const unsigned long long b = g / per_out;
+        const unsigned long long rem = g - b * per_out;
+        int r, c, m;
+        if (!right)
+        {
+            r = (int)(rem / n);
+            c = (int)(rem - (unsigned long long)r * n);
+            m = r;
+        }
+        else
+        {
+            r = (int)(rem / map_rows);
+            c = (int)(rem - (unsigned long long)r * map_rows);
+            m = c;
+        }
+        const int4 e = ld_ro(reinterpret_cast<const int4 *>(map) + m);
+        const int ev[4] = {e.x, e.y, e.z, e.w};
+        const double *src = in + b * (unsigned long long)in_dim * n;
+        double s = 0.0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+        {
+            if (ev[k] == 0)
+                break;
+            const int j = abs(ev[k]) - 1;
+            const double v = right ? src[(unsigned long long)r * in_dim + j] : src[(unsigned long long)j * n + c];
+            s += ev[k] < 0 ? -v : v;
+        }
+        out[g] = s;
+    }
+}
+
+// a plan with one block holding one dense matrix (coef 1, no incidences)
+static int make_dense_plan(mfv2d_ctx *ctx, const mfv2d_basis *basis, int dk, int inverse, int transpose, int n_fields,
+                           mfv2d_plan **out)
+{
+    mfv2d_plan *plan = new mfv2d_plan();
+    plan->ctx = ctx;
+    plan->basis = basis;
+    plan->p = basis->p;
+    plan->q = basis->q;
+    const int p = basis->p;
+    Factor d{};
+    d.is_dense = 1;
+    d.dk = dk;
+    d.inverse = inverse;
+    d.field = n_fields ? 0 : -1;
+    d.transpose = transpose;
+    const int n0 = form_size(1, p), n1 = form_size(2, p), n2 = form_size(3, p);
+    switch (dk)
+    {
+    case DK_MASS0:
+        d.rows = d.cols = n0;
+        break;
+    case DK_MASS1:
+        d.rows = d.cols = n1;
+        break;
+    case DK_MASS2:
+        d.rows = d.cols = n2;
+        break;
+    case DK_IPROD1:
+        d.rows = n0;
+        d.cols = n1;
+        break;
+    default:
+        d.rows = n1;
+        d.cols = n2;
+        break;
+    }
+    if (transpose)
+    {
+        const int t = d.rows;
+        d.rows = d.cols;
+        d.cols = t;
+    }
+    // a non-square "system": rows and cols are described through a 1x1 block with explicit dims
+    plan->n_forms = 1;
+    plan->form_orders = {0};
+    plan->form_offsets = {0, d.rows};
+    plan->n_total = d.rows;
+    plan->n_fields = n_fields;
+    plan->field_form.assign(n_fields, -1);
+    plan->mat_blocks.resize(1);
+    plan->vec_blocks.resize(1);
+    // hand-lowered (plan_lower_matrix assumes square systems)
+    plan->matrix_fused = true;
+    DevDense dd{dk, inverse, d.field, transpose, d.rows, d.cols, 0};
+    plan->dense.push_back(dd);
+    plan->terms.push_back(DevTerm{1.0, 0, -1, -1});
+    plan->blocks.push_back(DevBlock{0, 0, d.rows, d.cols, 0, 1, 0});
+    for (int c0 = 0; c0 < d.cols; c0 += 32)
+        for (int r0 = 0; r0 < d.rows; r0 += 8)
+            plan->units.push_back(DevUnit{0, (short)c0, (short)r0, (short)((d.rows - r0) < 8 ? (d.rows - r0) : 8)});
+    plan->stages.push_back(DevStage{0, 1, 0, 1, 0, (int)plan->units.size()});
+    std::vector<char> blob;
+    auto append = [&](const void *ptr, size_t bytes) {
+        size_t off = (blob.size() + 15) & ~size_t(15);
+        blob.resize(off + bytes);
+        memcpy(blob.data() + off, ptr, bytes);
+        return (int)off;
+    };
+    append(plan->stages.data(), plan->stages.size() * sizeof(DevStage));
+    plan->off_dense = append(plan->dense.data(), plan->dense.size() * sizeof(DevDense));
+    plan->off_terms = append(plan->terms.data(), plan->terms.size() * sizeof(DevTerm));
+    plan->off_blocks = append(plan->blocks.data(), plan->blocks.size() * sizeof(DevBlock));
+    plan->off_units = append(plan->units.data(), plan->units.size() * sizeof(DevUnit));
+    plan->blob_bytes = blob.size();
+    int r = mfv2d_cuda_malloc(ctx, blob.size(), &plan->d_blob);
+    if (!r)
+        r = mfv2d_cuda_upload(ctx, plan->d_blob, blob.data(), blob.size());
+    if (r)
+    {
+        mfv2d_cuda_plan_destroy(plan);
+        return r;
+    }
+    *out = plan;
+    return MFV2D_SUCCESS;
+}
+
+extern "C" {
+
+int mfv2d_cuda_reconstruct_batch(const mfv2d_elements *e, int form, const double *dofs, double *out, int space)
+{
+    mfv2d_ctx *ctx = e->ctx;
+    const int p = e->basis->p, q = e->basis->q;
+    const int nk = form_size(form, p);
+    if (nk < 0)
+        return mfv2d_fail(ctx, MFV2D_BAD_ENUM, "reconstruct_batch: invalid form order %d", form);
+    if (e->n == 0)
+        return MFV2D_SUCCESS;
+    const size_t per = (size_t)q * q * (form == MFV2D_FORM_ORDER_1 ? 2 : 1);
+    Staged in, o;
+    MFV2D_TRY(stage_in(ctx, dofs, e->n * nk * sizeof(double), space, &in));
+    int r = stage_out_alloc(ctx, out, e->n * per * sizeof(double), space, &o);
+    if (!r)
+        r = launch_reconstruct(e, form, (const double *)in.dev, nk, (double *)o.dev);
+    if (!r)
+        r = stage_finish(&o);
+    else
+        stage_abort(&o);
+    stage_abort(&in);
+    return r;
+}
+
+int mfv2d_cuda_incidence_apply(mfv2d_ctx *ctx, int p, int kind, int right, size_t batch, int n, const double *in,
+                               double *out, int space)
+{
+    if (kind < 0 || kind > 3 || p < 1)
+        return mfv2d_fail(ctx, MFV2D_BAD_ENUM, "incidence_apply: invalid kind %d / order %d", kind, p);
+    if (batch == 0 || n == 0)
+        return MFV2D_SUCCESS;
+    // left application walks the rows of E, right application the rows of E^T (= columns of E)
+    const int map_kind = right ? (kind ^ 2) : kind;
+    std::vector<int32_t> map;
+    host_incidence_rowmap(p, map_kind, map);
+    const int map_rows = (int)(map.size() / 4);
+    const int in_dim = right ? incidence_rows(p, kind) : incidence_cols(p, kind);
+    int32_t *d_map = nullptr;
+    MFV2D_TRY(mfv2d_cuda_malloc(ctx, map.size() * sizeof(int32_t), (void **)&d_map));
+    int r = mfv2d_cuda_upload(ctx, d_map, map.data(), map.size() * sizeof(int32_t));
+    Staged i, o;
+    if (!r)
+        r = stage_in(ctx, in, batch * (size_t)in_dim * n * sizeof(double), space, &i);
+    if (!r)
+        r = stage_out_alloc(ctx, out, batch * (size_t)map_rows * n * sizeof(double), space, &o);
+    if (!r)
+    {
+        size_t blocks = (batch * (size_t)map_rows * n + 255) / 256;
+        if (blocks > (size_t)ctx->sm_count * 16)
+            blocks = (size_t)ctx->sm_count * 16;
+        MFV2D_LAUNCH(incidence_kernel, (unsigned)blocks, 256, 0, ctx->stream, d_map, map_rows, in_dim, right, n,
+                     (unsigned long long)batch, (const double *)i.dev, (double *)o.dev);
+        ctx->launches++;
+        if (cudaGetLastError() != cudaSuccess)
+            r = mfv2d_fail(ctx, MFV2D_CUDA_ERROR, "incidence kernel launch failed");
+    }
+    if (!r)
+        r = stage_finish(&o);
+    else
+        stage_abort(&o);
+    stage_abort(&i);
+    mfv2d_cuda_free(ctx, d_map);
+    return r;
+}
+
+static int dense_batch(const mfv2d_elements *e, int dk, int inverse, int transpose, const double *field, double *out,
+                       int32_t *status, int space)
+{
+    mfv2d_ctx *ctx = e->ctx;
+    if (e->n == 0)
+        return MFV2D_SUCCESS;
+    mfv2d_plan *plan = nullptr;
+    MFV2D_TRY(make_dense_plan(ctx, e->basis, dk, inverse, transpose, field ? 1 : 0, &plan));
+    const DevDense &dd = plan->dense[0];
+    const int q = e->basis->q;
+    Staged f, o, st;
+    int r = stage_in(ctx, field, field ? e->n * (size_t)q * q * 2 * sizeof(double) : 0, space, &f);
+    if (!r)
+        r = stage_out_alloc(ctx, out, e->n * (size_t)dd.rows * dd.cols * sizeof(double), space, &o);
+    if (!r)
+        r = stage_out_alloc(ctx, status, status ? e->n * sizeof(int32_t) : 0, space, &st);
+    if (!r)
+    {
+        const double *fields[1] = {(const double *)f.dev};
+        // the kernel writes N x N blocks with N = n_total; for a rectangular matrix emit with the
+        // column count as the leading dimension
+        plan->out_ld = dd.cols;
+        plan->out_stride = (unsigned long long)dd.rows * dd.cols;
+        r = launch_element_matrix(plan, e, fields, (double *)o.dev, (int32_t *)st.dev);
+    }
+    if (!r)
+    {
+        r = stage_finish(&o);
+        int r2 = stage_finish(&st);
+        if (!r)
+            r = r2;
+    }
+    else
+    {
+        stage_abort(&o);
+        stage_abort(&st);
+    }
+    stage_abort(&f);
+    mfv2d_cuda_plan_destroy(plan);
+    return r;
+}
+
+int mfv2d_cuda_mass_batch(const mfv2d_elements *e, int form, int inverse, double *out, int32_t *status, int space)
+{
+    if (form < MFV2D_FORM_ORDER_0 || form > MFV2D_FORM_ORDER_2)
+        return mfv2d_fail(e->ctx, MFV2D_BAD_ENUM, "mass_batch: invalid form order %d", form);
+    return dense_batch(e, DK_MASS0 + (form - 1), inverse ? 1 : 0, 0, nullptr, out, status, space);
+}
+
+int mfv2d_cuda_interprod_batch(const mfv2d_elements *e, int start_form, int transpose, const double *field, double *out,
+                               int space)
+{
+    if (start_form != MFV2D_FORM_ORDER_1 && start_form != MFV2D_FORM_ORDER_2)
+        return mfv2d_fail(e->ctx, MFV2D_BAD_ENUM, "interprod_batch: starting form must be a 1- or 2-form");
+    if (!field)
+        return mfv2d_fail(e->ctx, MFV2D_BAD_ARGUMENT, "interprod_batch: field values are required");
+    return dense_batch(e, start_form == MFV2D_FORM_ORDER_1 ? DK_IPROD1 : DK_IPROD2, 0, transpose ? 1 : 0, field, out,
+                       nullptr, space);
+}
+
+// resolve the plan's fields: supplied values are used in place (or staged from the host), fields of
+// unknowns are reconstructed from the element DoFs into temporaries.
+struct FieldSet
+{
+    std::vector<Staged> staged;
+    std::vector<void *> temps;
+    const double *ptr[16];
+};
+
+static int resolve_fields(const mfv2d_plan *plan, const mfv2d_elements *e, const double *d_dofs, const double *field_values,
+                          int space, FieldSet *fs)
+{
+    mfv2d_ctx *ctx = plan->ctx;
+    const size_t per = e->n * (size_t)plan->q * plan->q * 2;
+    for (int i = 0; i < 16; ++i)
+        fs->ptr[i] = nullptr;
+    for (int i = 0; i < plan->n_fields; ++i)
+    {
+        if (plan->field_form[i] < 0)
+        {
+            if (!field_values)
+                return mfv2d_fail(ctx, MFV2D_BAD_ARGUMENT, "field %d needs caller-supplied values", i);
+            Staged s;
+            MFV2D_TRY(stage_in(ctx, field_values + (size_t)i * per, per * sizeof(double), space, &s));
+            fs->ptr[i] = (const double *)s.dev;
+            fs->staged.push_back(s);
+        }
+        else
+        {
+            if (!d_dofs)
+                return mfv2d_fail(ctx, MFV2D_BAD_ARGUMENT, "field %d is reconstructed from an unknown: degrees of freedom are required", i);
+            void *tmp = nullptr;
+            MFV2D_TRY(mfv2d_cuda_malloc(ctx, per * sizeof(double), &tmp));
+            fs->temps.push_back(tmp);
+            fs->ptr[i] = (const double *)tmp;
+            const int f = plan->field_form[i];
+            MFV2D_TRY(launch_reconstruct(e, plan->form_orders[f], d_dofs + plan->form_offsets[f], plan->n_total, (double *)tmp));
+        }
+    }
+    return MFV2D_SUCCESS;
+}
+
+static void release_fields(mfv2d_ctx *ctx, FieldSet *fs)
+{
+    for (Staged &s : fs->staged)
+        stage_abort(&s);
+    for (void *t : fs->temps)
+        mfv2d_cuda_free(ctx, t);
+    fs->staged.clear();
+    fs->temps.clear();
+}
+
+int mfv2d_cuda_element_matrix_batch(const mfv2d_plan *plan, const mfv2d_elements *e, const double *dofs,
+                                    const double *field_values, double *out, int space)
+{
+    mfv2d_ctx *ctx = plan->ctx;
+    if (e->basis != plan->basis)
+        return mfv2d_fail(ctx, MFV2D_ORDER_MISMATCH, "element batch and plan use different bases");
+    if (e->n == 0)
+        return MFV2D_SUCCESS;
+    const size_t N = plan->n_total;
+    Staged d, o;
+    FieldSet fs;
+    int r = stage_in(ctx, plan->needs_dofs ? dofs : nullptr, e->n * N * sizeof(double), space, &d);
+    if (!r)
+        r = resolve_fields(plan, e, (const double *)d.dev, field_values, space, &fs);
+    if (!r)
+        r = stage_out_alloc(ctx, out, e->n * N * N * sizeof(double), space, &o);
+    if (!r)
+    {
+        if (plan->matrix_fused)
+            r = launch_element_matrix(plan, e, fs.ptr, (double *)o.dev, nullptr);
+        else
+            r = launch_matrix_by_columns(plan, e, fs.ptr, (double *)o.dev);
+    }
+    if (!r)
+        r = stage_finish(&o);
+    else
+        stage_abort(&o);
+    release_fields(ctx, &fs);
+    stage_abort(&d);
+    return r;
+}
+
+int mfv2d_cuda_element_vector_batch(const mfv2d_plan *plan, const mfv2d_elements *e, const double *dofs,
+                                    const double *field_values, double *out, int space)
+{
+    mfv2d_ctx *ctx = plan->ctx;
+    if (e->basis != plan->basis)
+        return mfv2d_fail(ctx, MFV2D_ORDER_MISMATCH, "element batch and plan use different bases");
+    if (!dofs)
+        return mfv2d_fail(ctx, MFV2D_BAD_ARGUMENT, "element_vector_batch: degrees of freedom are required");
+    if (e->n == 0)
+        return MFV2D_SUCCESS;
+    const size_t N = plan->n_total;
+    Staged d, o;
+    FieldSet fs;
+    int r = stage_in(ctx, dofs, e->n * N * sizeof(double), space, &d);
+    if (!r)
+        r = resolve_fields(plan, e, (const double *)d.dev, field_values, space, &fs);
+    if (!r)
+        r = stage_out_alloc(ctx, out, e->n * N * sizeof(double), space, &o);
+    if (!r)
+        r = launch_element_vector(plan, e, fs.ptr, (const double *)d.dev, (double *)o.dev);
+    if (!r)
+        r = stage_finish(&o);
+    else
+        stage_abort(&o);
+    release_fields(ctx, &fs);
+    stage_abort(&d);
+    return r;
+}
+
+} // extern "C"
