@@ -1,0 +1,213 @@
+"""Element-block linear system and Krylov solvers on the device.
+
+Mirror of the reference's ``LinearSystem`` / ``DenseVector`` / ``TraceVector`` (src/algebra/
+system_objects.c, sparse_system.c) and of python/mfv2d/solving.py (``solve_schur_iterative``,
+``solve_pcg_iterative``, ``ConvergenceSettings``).  The reference crosses Python -> C once per vector
+operation; here a whole solve is one call into libmfv2d_cuda.so and the vectors never leave the GPU.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from collections.abc import Sequence
+from dataclasses import dataclass
+
+import numpy as np
+
+from ._capi import DEVICE, HOST, check, lib
+from .runtime import Context, DeviceArray, addr, get_context, space_of
+
+
+@dataclass(frozen=True)
+class ConvergenceSettings:
+    """python/mfv2d/solving.py:157-171."""
+
+    maximum_iterations: int = 100
+    absolute_tolerance: float = 1e-6
+    relative_tolerance: float = 1e-5
+
+
+@dataclass(frozen=True)
+class ElementConstraint:
+    """python/mfv2d/mimetic2d.py:804-821."""
+
+    i_e: int
+    dofs: np.ndarray
+    coeffs: np.ndarray
+
+
+@dataclass(frozen=True, init=False)
+class Constraint:
+    """python/mfv2d/mimetic2d.py:853-873."""
+
+    rhs: float
+    element_constraints: tuple
+
+    def __init__(self, rhs: float, *element_constraints: ElementConstraint) -> None:
+        object.__setattr__(self, "rhs", float(rhs))
+        object.__setattr__(self, "element_constraints", element_constraints)
+
+
+def constraints_to_coo(constraints: Sequence[Constraint], offsets: np.ndarray):
+    """Flatten Constraint objects into the global COO (row, column, value) of N, sorted by (row, col)."""
+    rows, cols, vals = [], [], []
+    for ic, con in enumerate(constraints):
+        for ec in con.element_constraints:
+            d = np.asarray(ec.dofs, np.int64)
+            rows.append(np.full(d.size, ic, np.int64))
+            cols.append(d + int(offsets[ec.i_e]))
+            vals.append(np.asarray(ec.coeffs, np.float64))
+    if not rows:
+        return np.zeros(0, np.int64), np.zeros(0, np.int64), np.zeros(0)
+    row, col, val = np.concatenate(rows), np.concatenate(cols), np.concatenate(vals)
+    order = np.lexsort((col, row))
+    return row[order], col[order], val[order]
+
+
+class LinearSystem:
+    """``[[A, N^T], [N, 0]]`` with block-diagonal ``A`` (one dense block per element) and the
+    constraint matrix ``N`` (system_new / system_fill_out, src/algebra/system_objects.c:73-199).
+
+    ``element_matrices``: sequence of ``(N_e, N_e)`` arrays, a ``(n, N_e, N_e)`` array, or a DeviceArray of
+    that shape (e.g. straight out of ``compute_element_matrices(..., out=DeviceArray)``).
+    ``constraints``: sequence of :class:`Constraint`, or a COO triple ``(row, col, val)`` over global
+    dense columns together with ``n_trace``."""
+
+    def __init__(self, element_matrices, constraints, n_trace: int | None = None, ctx: Context | None = None):
+        self.ctx = ctx or get_context()
+        if isinstance(element_matrices, DeviceArray):
+            n, ne, ne2 = element_matrices.shape
+            assert ne == ne2
+            sizes = np.full(n, ne, np.int64)
+            blocks, space = element_matrices, DEVICE
+        else:
+            mats = [np.ascontiguousarray(m, np.float64) for m in element_matrices]
+            for m in mats:
+                if m.ndim != 2 or m.shape[0] != m.shape[1]:
+                    raise ValueError("element matrices must be square")
+            sizes = np.array([m.shape[0] for m in mats], np.int64)
+            blocks = np.concatenate([m.ravel() for m in mats]) if mats else np.zeros(0)
+            space = HOST
+        self._blocks = blocks  # keep a borrowed device buffer alive
+        self.offsets = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int64)
+        self.n_elem = int(sizes.size)
+        if isinstance(constraints, tuple) and len(constraints) == 3 and isinstance(constraints[0], np.ndarray):
+            row, col, val = (np.ascontiguousarray(constraints[0], np.int64), np.ascontiguousarray(constraints[1], np.int64),
+                             np.ascontiguousarray(constraints[2], np.float64))
+            if n_trace is None:
+                n_trace = int(row.max()) + 1 if row.size else 0
+            self.constraint_rhs = None
+        else:
+            row, col, val = constraints_to_coo(constraints, self.offsets)
+            n_trace = len(constraints)
+            self.constraint_rhs = np.array([c.rhs for c in constraints], np.float64)
+        self.con = (row, col, val)
+        self.n_trace = int(n_trace)
+        self.n_dense = int(self.offsets[-1])
+        h = C.c_void_p()
+        check(
+            lib().mfv2d_cuda_system_create(self.ctx.handle, self.n_elem, self.offsets.ctypes.data, addr(blocks), space, self.n_trace,
+                                           row.size, row.ctypes.data, col.ctypes.data, val.ctypes.data, C.byref(h)),
+            self.ctx.handle,
+        )
+        self.handle = h
+
+    def __del__(self):
+        try:
+            if self.handle and self.ctx.handle:
+                lib().mfv2d_cuda_system_destroy(self.handle)
+        except Exception:
+            pass
+        self.handle = None
+
+    # ---- operators (sparse_system.c:3-207); numpy in -> numpy out, DeviceArray in -> DeviceArray out ----
+    def _apply(self, fn, x, n_in: int, n_out: int, out=None):
+        if isinstance(x, DeviceArray):
+            out = out if out is not None else self.ctx.empty(n_out)
+        else:
+            x = np.ascontiguousarray(x, np.float64)
+            out = out if out is not None else np.empty(n_out)
+        if x.size != n_in or out.size != n_out:
+            raise ValueError("vector does not belong to this system (MFV2D_BAD_VECTOR_PARENT)")
+        check(fn(self.handle, addr(x), addr(out), space_of(x, out)), self.ctx.handle)
+        return out
+
+    def apply_diagonal(self, x, out=None):
+        return self._apply(lib().mfv2d_cuda_system_apply_diagonal, x, self.n_dense, self.n_dense, out)
+
+    def apply_diagonal_inverse(self, x, out=None):
+        return self._apply(lib().mfv2d_cuda_system_apply_diagonal_inverse, x, self.n_dense, self.n_dense, out)
+
+    def apply_trace(self, x, out=None):
+        return self._apply(lib().mfv2d_cuda_system_apply_trace, x, self.n_dense, self.n_trace, out)
+
+    def apply_trace_transpose(self, t, out=None):
+        return self._apply(lib().mfv2d_cuda_system_apply_trace_transpose, t, self.n_trace, self.n_dense, out)
+
+    def apply_full_trace_system(self, t, out=None):
+        """``N A^-1 N^T t`` (solving.py:99-123) through the condensed per-element blocks."""
+        return self._apply(lib().mfv2d_cuda_system_apply_schur, t, self.n_trace, self.n_trace, out)
+
+    def set_interface(self, shared_index: np.ndarray, slot: np.ndarray, n_slots: int, owned: np.ndarray) -> None:
+        """Multi-GPU: declare the multipliers shared with other ranks (see include/mfv2d_cuda.h)."""
+        si = np.ascontiguousarray(shared_index, np.int64)
+        sl = np.ascontiguousarray(slot, np.int64)
+        ow = np.ascontiguousarray(owned, np.uint8)
+        assert ow.size == self.n_trace
+        check(lib().mfv2d_cuda_system_set_interface(self.handle, si.size, si.ctypes.data, sl.ctypes.data, int(n_slots), ow.ctypes.data),
+              self.ctx.handle)
+
+
+def solve_schur_iterative(system: LinearSystem, rhs, constraints, convergence: ConvergenceSettings, precondition: bool = False):
+    """python/mfv2d/solving.py:439-500: CG on ``N A^-1 N^T`` for the multipliers, then back substitution.
+    Returns ``(x, lambda, residual, iterations)`` like the reference."""
+    dev = isinstance(rhs, DeviceArray)
+    if dev:
+        x, lam = system.ctx.empty(system.n_dense), system.ctx.empty(system.n_trace)
+    else:
+        rhs = np.ascontiguousarray(rhs, np.float64)
+        constraints = np.ascontiguousarray(constraints, np.float64)
+        x, lam = np.empty(system.n_dense), np.empty(system.n_trace)
+    res, it = C.c_double(), C.c_int()
+    check(
+        lib().mfv2d_cuda_solve_schur_cg(system.handle, addr(rhs), addr(constraints), int(convergence.maximum_iterations),
+                                        float(convergence.absolute_tolerance), float(convergence.relative_tolerance),
+                                        int(bool(precondition)), addr(x), addr(lam), C.byref(res), C.byref(it),
+                                        space_of(rhs, constraints, x, lam)),
+        system.ctx.handle,
+    )
+    return x, lam, res.value, it.value
+
+
+def solve_pcg_iterative(system: LinearSystem, rhs, constraints, convergence: ConvergenceSettings):
+    """python/mfv2d/solving.py:634-684: PCG on the saddle system with the block-Jacobi ``A^-1 (+) I``."""
+    dev = isinstance(rhs, DeviceArray)
+    if dev:
+        x, lam = system.ctx.empty(system.n_dense), system.ctx.empty(system.n_trace)
+    else:
+        rhs = np.ascontiguousarray(rhs, np.float64)
+        constraints = np.ascontiguousarray(constraints, np.float64)
+        x, lam = np.empty(system.n_dense), np.empty(system.n_trace)
+    res, it = C.c_double(), C.c_int()
+    check(
+        lib().mfv2d_cuda_solve_pcg(system.handle, addr(rhs), addr(constraints), int(convergence.maximum_iterations),
+                                   float(convergence.absolute_tolerance), float(convergence.relative_tolerance), addr(x), addr(lam),
+                                   C.byref(res), C.byref(it), space_of(rhs, constraints, x, lam)),
+        system.ctx.handle,
+    )
+    return x, lam, res.value, it.value
+
+
+def vec_axpby(a: float, x, b: float, y, out=None, ctx: Context | None = None):
+    """``out = a x + b y`` (DenseVector/TraceVector add, subtract, scale; system_objects.c:945-1300)."""
+    ctx = ctx or get_context()
+    if out is None:
+        out = ctx.empty(x.size) if isinstance(x, DeviceArray) else np.empty(x.size)
+    check(lib().mfv2d_cuda_vec_axpby(ctx.handle, x.size, float(a), addr(x), float(b), addr(y), addr(out), space_of(x, y, out)), ctx.handle)
+    return out
+
+
+def vec_dot(x, y, ctx: Context | None = None) -> float:
+    ctx = ctx or get_context()
+    r = C.c_double()
+    check(lib().mfv2d_cuda_vec_dot(ctx.handle, x.size, addr(x), addr(y), C.byref(r), space_of(x, y)), ctx.handle)
+    return r.value

@@ -1,0 +1,96 @@
+"""Array-based structured quad meshes and their continuity constraints.
+
+The reference builds meshes through Python objects (``mfv2d.examples.unit_square_mesh``,
+python/mfv2d/examples.py:11-73) and its constraints through a recursive per-edge Python walk
+(``connect_elements``, python/mfv2d/continuity.py:610-759).  For the synthetic structured configs of
+BASELINE.json (up to 10^6 elements) those are generated here directly as flat arrays, reproducing the
+reference's leaf order, row order, DoF order and coefficients exactly (pinned against reference output
+in tests/golden/solve_*.npz and constraints_*.npz).
+"""
+from __future__ import annotations
+
+from collections.abc import Callable
+
+import numpy as np
+
+FORM_ORDER_0, FORM_ORDER_1, FORM_ORDER_2 = 1, 2, 3
+
+
+def unit_square_corners(nh: int, nv: int, deformation: Callable | None = None) -> np.ndarray:
+    """Corner coordinates ``(nh*nv, 4, 2)`` of ``unit_square_mesh(nh, nv, ...)``: element ``i + nh*j``,
+    corners counter-clockwise from bottom-left, nodes on the uniform grid of [-1, 1]^2 passed through
+    ``deformation(xi, eta) -> (x, y)`` (examples.py:40-47, 55-66)."""
+    xi, eta = np.meshgrid(np.linspace(-1, +1, nh + 1), np.linspace(-1, +1, nv + 1))
+    if deformation is not None:
+        px, py = deformation(xi, eta)
+        xi = np.array(px, np.float64)
+        eta = np.array(py, np.float64)
+    pts = np.stack((xi, eta), axis=-1)  # (nv+1, nh+1, 2)
+    c = np.empty((nv, nh, 4, 2))
+    c[:, :, 0] = pts[:-1, :-1]
+    c[:, :, 1] = pts[:-1, 1:]
+    c[:, :, 2] = pts[1:, 1:]
+    c[:, :, 3] = pts[1:, :-1]
+    return np.ascontiguousarray(c.reshape(nh * nv, 4, 2))
+
+
+def form_sizes(form_orders, p: int) -> np.ndarray:
+    size = {FORM_ORDER_0: (p + 1) ** 2, FORM_ORDER_1: 2 * p * (p + 1), FORM_ORDER_2: p * p}
+    return np.array([size[int(o)] for o in form_orders], np.int64)
+
+
+def continuity_constraints_1form(nh: int, nv: int, p: int, form_orders) -> tuple[np.ndarray, np.ndarray, np.ndarray, int]:
+    """Continuity rows of the 1-form unknowns on the conforming ``nh x nv`` mesh of uniform order p, in
+    the reference's order (continuity.py:650-683, 498-508): for each 1-form of the system, first the
+    interior horizontal lines (line index ``nh*j + i``, j = 1..nv-1), then the interior vertical lines
+    (``j*(nh+1) + i``, i = 1..nh-1); ``p`` rows per line.
+
+    Returns COO arrays (row, global dense column, value) sorted by (row, column) and the row count."""
+    sizes = form_sizes(form_orders, p)
+    offs = np.concatenate([[0], np.cumsum(sizes)])
+    ne = int(offs[-1])
+    nh_edges = p * (p + 1)
+    rows, cols, vals = [], [], []
+    row0 = 0
+    k = np.arange(p)[::-1]  # DoFs along a side are traversed in reverse
+    for f, order in enumerate(form_orders):
+        if int(order) != FORM_ORDER_1:
+            continue
+        o1 = int(offs[f])
+        # horizontal interior lines: element below (top side, +1) and element above (bottom side, -1)
+        jj, ii = np.meshgrid(np.arange(1, nv), np.arange(nh), indexing="ij")
+        e_below = (ii + nh * (jj - 1)).ravel()
+        e_above = (ii + nh * jj).ravel()
+        n_l = e_below.size
+        r = row0 + (np.arange(n_l)[:, None] * p + np.arange(p)[None, :])
+        top = o1 + p * p + k  # h(p, c)
+        bot = o1 + k  # h(0, c)
+        rows += [r.ravel(), r.ravel()]
+        cols += [(e_below[:, None] * ne + top[None, :]).ravel(), (e_above[:, None] * ne + bot[None, :]).ravel()]
+        vals += [np.full(n_l * p, 1.0), np.full(n_l * p, -1.0)]
+        row0 += n_l * p
+        # vertical interior lines: element on the right (left side, +1) and on the left (right side, -1)
+        jj, ii = np.meshgrid(np.arange(nv), np.arange(1, nh), indexing="ij")
+        e_right = (ii + nh * jj).ravel()
+        e_left = (ii - 1 + nh * jj).ravel()
+        n_l = e_right.size
+        r = row0 + (np.arange(n_l)[:, None] * p + np.arange(p)[None, :])
+        left = o1 + nh_edges + (p + 1) * k  # v(r, 0)
+        right = o1 + nh_edges + (p + 1) * k + p  # v(r, p)
+        rows += [r.ravel(), r.ravel()]
+        cols += [(e_right[:, None] * ne + left[None, :]).ravel(), (e_left[:, None] * ne + right[None, :]).ravel()]
+        vals += [np.full(n_l * p, 1.0), np.full(n_l * p, -1.0)]
+        row0 += n_l * p
+    if not rows:
+        return np.zeros(0, np.int64), np.zeros(0, np.int64), np.zeros(0), 0
+    row = np.concatenate(rows).astype(np.int64)
+    col = np.concatenate(cols).astype(np.int64)
+    val = np.concatenate(vals)
+    order = np.lexsort((col, row))
+    return row[order], col[order], val[order], row0
+
+
+def strip_partition(nh: int, nv: int, n_ranks: int) -> list[tuple[int, int]]:
+    """Contiguous ranges of leaf indices (horizontal strips of whole element rows)."""
+    rows = [nv * r // n_ranks for r in range(n_ranks + 1)]
+    return [(rows[r] * nh, rows[r + 1] * nh) for r in range(n_ranks)]

@@ -1,0 +1,292 @@
+"""Parity checks of the mfv2d_b200 API against the oracle (numpy restatement pinned to the reference) and
+against the golden fixtures produced by the reference itself.  The same functions run
+
+* under ``-m gpu`` on the B200 through libmfv2d_cuda.so (tests/test_gpu_parity.py) - the parity tests proper;
+* under ``-m "not gpu"`` through the host emulation of the same sources (tests/test_emu_kernels.py), which
+  checks the planner / layouts / index arithmetic in the GPU-less container.
+
+Tolerances: fp64 element matrices 1e-12 relative (north_star), inverses 1e-10, solutions 1e-8 against the
+reference's own iterative solution (both stop at a residual tolerance), indices bit-exact.
+"""
+from __future__ import annotations
+
+import numpy as np
+from conftest import golden, load_systems, relerr
+
+import fields as F
+from oracle import mfv2d_oracle as O
+
+SYSTEMS = load_systems()
+TOL_MAT = 1e-12
+TOL_INV = 1e-10
+
+
+def make_basis(M, p, k):
+    b1 = M.Basis1D(p, M.IntegrationRule1D(p + k))
+    return M.Basis2D(b1, b1)
+
+
+def specs_of(M, s):
+    return M._ElementFormSpecification(*zip(s["form_names"], s["form_orders"]))
+
+
+def check_tables(M, cases=((1, 2), (3, 3), (4, 2), (5, 0))):
+    g = golden("element_stokes.npz")
+    for p, k in cases:
+        tag = f"p{p}k{k}q4"
+        rule = M.IntegrationRule1D(p + k)
+        b1 = M.Basis1D(p, rule)
+        assert np.array_equal(rule.nodes, g[tag + "_pnts"])  # GLL iteration is reproduced bit for bit
+        assert np.array_equal(rule.weights, g[tag + "_wgts"])
+        assert relerr(b1.node, g[tag + "_node"]) < 1e-14
+        assert relerr(b1.edge, g[tag + "_edge"]) < 1e-13
+    for n in range(0, 13):
+        x, w = M.compute_gll(n)
+        xo, wo = O.compute_gll(n)
+        assert np.array_equal(x, xo) and np.array_equal(w, wo)
+        assert abs(w.sum() - 2.0) < 1e-14
+    rng = np.random.default_rng(3)
+    roots = np.sort(rng.uniform(-1, 1, 7))
+    pos = rng.uniform(-1, 1, (5, 4))
+    assert relerr(M.lagrange1d(roots, pos), O.lagrange1d(roots, pos)) < 1e-12
+    assert relerr(M.dlagrange1d(roots, pos), O.dlagrange1d(roots, pos)) < 1e-11
+    assert relerr(M.compute_legendre(9, pos), O.legendre(9, pos)) < 1e-14
+    assert relerr(M.compute_legendre_device(9, pos), O.legendre(9, pos)) < 1e-14
+
+
+def check_masses_golden(M, cases=((1, 2), (3, 3), (4, 2), (5, 0))):
+    """Mass matrices and inverses against the reference's own output on the skewed quad."""
+    g = golden("element_stokes.npz")
+    for p, k in cases:
+        tag = f"p{p}k{k}q4"
+        batch = M.ElementBatch(make_basis(M, p, k), np.ascontiguousarray(F.QUADS[4:5]))
+        for fo in (1, 2, 3):
+            assert relerr(batch.mass(fo)[0], g[tag + f"_m{fo - 1}"]) < TOL_MAT
+            assert relerr(batch.mass(fo, True)[0], g[tag + f"_m{fo - 1}i"]) < TOL_INV
+        jac = batch.jacobian()[0]
+        ob = O.basis(p, p + k + 1)
+        for a, b in zip(jac, O.jacobian(F.QUADS[4], ob.pnts)):
+            assert relerr(a, b) < 1e-15
+
+
+def check_masses_oracle(M, cases, n_random=64, seed=0):
+    """Masses on the test quads + randomly perturbed unit quads (tests/test_basis.py:83-87 distribution)."""
+    rng = np.random.default_rng(seed)
+    unit = np.array([(-1, -1), (1, -1), (1, 1), (-1, 1)], float)
+    corners = np.concatenate([F.QUADS, unit + rng.uniform(-0.1, 0.1, (n_random, 4, 2))])
+    for p, k in cases:
+        ob = O.basis(p, p + k + 1)
+        batch = M.ElementBatch(make_basis(M, p, k), np.ascontiguousarray(corners))
+        for fo in (1, 2, 3):
+            m = batch.mass(fo)
+            ref = O.mass(ob, corners, fo)
+            assert relerr(m, ref) < TOL_MAT, (p, k, fo)
+            mi = batch.mass(fo, True)
+            eye = np.einsum("eij,ejk->eik", m, mi)
+            assert np.max(np.abs(eye - np.eye(m.shape[1]))) < 1e-9, (p, k, fo)  # tests/test_basis.py:80-100
+
+
+def check_system_golden(M, name, cases=((1, 2), (3, 3), (4, 2), (5, 0))):
+    """Element matrices and vectors of one example system against the reference's outputs."""
+    s = SYSTEMS[name]
+    g = golden(f"element_{name}.npz")
+    specs = specs_of(M, s)
+    for p, k in cases:
+        batch = M.ElementBatch(make_basis(M, p, k), np.ascontiguousarray(F.QUADS))
+        n = specs.total_size(p, p)
+        dofs = np.stack([g[f"p{p}k{k}q{iq}_dofs"] for iq in range(len(F.QUADS))])
+        assert dofs.shape == (len(F.QUADS), n)
+        mats = M.compute_element_matrices(specs, s["lhs"], batch, dofs)
+        vecs = M.compute_element_vectors(specs, s["lhs"], batch, dofs)
+        for iq in range(len(F.QUADS)):
+            tag = f"p{p}k{k}q{iq}"
+            assert relerr(mats[iq], g[tag + "_lhs"]) < TOL_MAT, (name, tag)
+            assert relerr(vecs[iq], g[tag + "_lhs_vec"]) < TOL_MAT, (name, tag)
+        if s["rhs"] is not None:
+            vecs = M.compute_element_vectors(specs, s["rhs"], batch, dofs)
+            for iq in range(len(F.QUADS)):
+                assert relerr(vecs[iq], g[f"p{p}k{k}q{iq}_rhs_vec"]) < TOL_MAT, (name, iq)
+        if s["nonlin"] is not None:
+            mats = M.compute_element_matrices(specs, s["nonlin"], batch, dofs)
+            for iq in range(len(F.QUADS)):
+                assert relerr(mats[iq], g[f"p{p}k{k}q{iq}_nonlin"]) < TOL_MAT, (name, iq)
+        # per-element entry points (batch of one), as the reference's Python loops call them
+        sp = M.ElementFemSpace2D(make_basis(M, p, k), np.ascontiguousarray(F.QUADS[4]))
+        tag = f"p{p}k{k}q4"
+        assert relerr(M.compute_element_matrix(specs, s["lhs"], sp, dofs[4]), g[tag + "_lhs"]) < TOL_MAT
+        assert relerr(M.compute_element_vector(specs, s["lhs"], sp, dofs[4]), g[tag + "_lhs_vec"]) < TOL_MAT
+
+
+def check_matrix_vector_consistency(M, name, p, k, n=16, seed=5):
+    """tests/test_explicit.py: ``compute_element_matrix @ x == compute_element_vector(x)`` for linear systems."""
+    s = SYSTEMS[name]
+    specs = specs_of(M, s)
+    rng = np.random.default_rng(seed)
+    unit = np.array([(-1, -1), (1, -1), (1, 1), (-1, 1)], float)
+    corners = np.ascontiguousarray(unit + rng.uniform(-0.2, 0.2, (n, 4, 2)))
+    batch = M.ElementBatch(make_basis(M, p, k), corners)
+    ne = specs.total_size(p, p)
+    x = rng.standard_normal((n, ne))
+    mats = M.compute_element_matrices(specs, s["lhs"], batch, x)
+    vecs = M.compute_element_vectors(specs, s["lhs"], batch, x)
+    assert relerr(np.einsum("eij,ej->ei", mats, x), vecs) < 1e-12
+
+
+def check_incidence(M, orders=(1, 2, 3, 5)):
+    """tests/test_apply_incidence-c.py: all 8 incidence kernels against explicit matrices."""
+    rng = np.random.default_rng(11)
+    for p in orders:
+        for t in range(4):
+            e = O.incidence(t, p)
+            m = rng.standard_normal((e.shape[1], 5))
+            assert np.array_equal(M.check_incidence(m, p, t % 2, t >= 2, False), e @ m) or relerr(
+                M.check_incidence(m, p, t % 2, t >= 2, False), e @ m) < 1e-15
+            mr = rng.standard_normal((6, e.shape[0]))
+            assert relerr(M.check_incidence(mr, p, t % 2, t >= 2, True), mr @ e) < 1e-15
+    # structure must be bit-exact: apply to identity and compare the integer matrices
+    for p in orders:
+        for t in range(4):
+            e = O.incidence(t, p)
+            got = M.check_incidence(np.eye(e.shape[1]), p, t % 2, t >= 2, False)
+            assert np.array_equal(got, e)
+
+
+def check_dense(M):
+    """tests/test_linalg_inverse.py: inverse and solve against numpy.linalg up to 100 x 100."""
+    rng = np.random.default_rng(2)
+    for n in (1, 2, 7, 30, 100):
+        a = rng.standard_normal((n, n)) + 0.1 * n * np.eye(n)
+        assert relerr(M._compute_matrix_inverse(a), np.linalg.inv(a)) < 1e-10
+        b = rng.standard_normal((n, 3))
+        assert relerr(M._solve_linear_system(a, b), np.linalg.solve(a, b)) < 1e-10
+        v = rng.standard_normal(n)
+        assert relerr(M._solve_linear_system(a, v), np.linalg.solve(a, v)) < 1e-10
+    # a matrix that needs pivoting, and a singular one
+    a = np.array([[0.0, 2.0], [3.0, 1.0]])
+    assert relerr(M._compute_matrix_inverse(a), np.linalg.inv(a)) < 1e-14
+    try:
+        M._compute_matrix_inverse(np.zeros((3, 3)))
+    except RuntimeError as e:
+        assert "MFV2D_PIVOT_FAILED" in str(e)
+    else:
+        raise AssertionError("singular matrix must raise MFV2D_PIVOT_FAILED")
+
+
+def check_fields(M, p=3, k=3):
+    """tests/test_compute_fields.py: callable and DoF-based fields at the quadrature points."""
+    rng = np.random.default_rng(4)
+    ob = O.basis(p, p + k + 1)
+    specs = M._ElementFormSpecification(("a", 1), ("b", 2), ("c", 3))
+    quad = np.ascontiguousarray(F.QUADS[4])
+    sp = M.ElementFemSpace2D(make_basis(M, p, k), quad)
+    dofs = rng.standard_normal(specs.total_size(p, p))
+    offs = specs.form_offsets(p, p)
+    out = M.compute_integrating_fields(sp, specs, (1, 2, 3, 2), (0, 1, 2, F.adv_field), dofs)
+    for i, fo in enumerate((1, 2, 3)):
+        ref = O.reconstruct_field(ob, quad, fo, dofs[offs[i] : offs[i + 1]])
+        assert relerr(out[i], ref) < 1e-13
+    x, y = O.physical_coordinates(quad, ob.pnts)
+    assert relerr(out[3], F.adv_field(x, y)) < 1e-14
+
+
+def check_interior_products(M, p=4, k=2):
+    rng = np.random.default_rng(8)
+    ob = O.basis(p, p + k + 1)
+    corners = np.ascontiguousarray(F.QUADS)
+    batch = M.ElementBatch(make_basis(M, p, k), corners)
+    fld = rng.standard_normal((len(corners), ob.q, ob.q, 2))
+    for tr in (False, True):
+        ref = np.stack([O.interprod_node_edge(ob, c, f, tr) for c, f in zip(corners, fld)])
+        assert relerr(batch.interior_product(2, fld, tr), ref) < TOL_MAT
+        ref = np.stack([O.interprod_edge_surf(ob, c, f, tr) for c, f in zip(corners, fld)])
+        assert relerr(batch.interior_product(3, fld, tr), ref) < TOL_MAT
+
+
+def check_bytecode_errors(M):
+    """Programs the reference rejects must be rejected with the same error code."""
+    specs = M._ElementFormSpecification(("u", 1), ("q", 2))
+    sp = M.ElementFemSpace2D(make_basis(M, 2, 1), np.ascontiguousarray(F.QUADS[0]))
+
+    def run(block):
+        return M.compute_element_matrix(specs, ((block, None), (None, None)), sp)
+
+    for block, code in (
+        (((3, 1, False), (3, 2, False)), "MFV2D_FAILED_ALLOC"),  # incidence o incidence (Q1)
+        (((3, 1, True),), "MFV2D_FAILED_ALLOC"),  # bare incidence (Q1)
+        (((2, 2, False),), "MFV2D_DIMS_MISMATCH"),  # 1-form mass in a 0-form block
+        (((6, 1),), "MFV2D_STACK_UNDERFLOW"),
+        (((2, 7, False),), "MFV2D_BAD_ENUM"),
+        (((2, 1, False), (4,), (1,), (6, 1)), "MFV2D_FAILED_ALLOC"),  # dense + identity (Q3 / Q1)
+    ):
+        try:
+            run(block)
+        except RuntimeError as e:
+            assert code in str(e), (block, str(e))
+        else:
+            raise AssertionError(f"{block} must fail with {code}")
+    # Q2: a scalar in front of a dense*dense product is dropped in matrix mode
+    m = run(((2, 1, False), (5, 3.0), (2, 1, True)))
+    n0 = 9
+    assert relerr(m[:n0, :n0], np.eye(n0)) < 1e-10
+    # identity block and scaled identity
+    m = run(((1,), (5, -2.5)))
+    assert np.array_equal(m[:n0, :n0], -2.5 * np.eye(n0))
+    # check_bytecode round trip (tests/test_bytecode.py)
+    prog = ((2, 1, False), (5, 0.5), (4,), (7, 2, "q", True), (6, 1))
+    assert M.check_bytecode(specs, prog) == prog
+
+
+def check_generic_chain(M, p=3, k=2):
+    """A block that is not of the fused form (two dense factors): M1^-1 * (E10 M0 ...) style chains go
+    through the column-by-column evaluator and must agree with the oracle's stack machine."""
+    rng = np.random.default_rng(9)
+    specs = M._ElementFormSpecification(("u", 1), ("q", 2))
+    names, orders = ["u", "q"], [1, 2]
+    prog = ((3, 1, False), (2, 2, False), (5, 0.5), (2, 2, True), (3, 1, True), (2, 1, True))
+    exprs = ((prog, None), (((3, 1, False), (2, 2, True)), ((2, 2, False), (5, 2.0), (4,), (2, 2, True), (6, 1))))
+    corners = np.ascontiguousarray(F.QUADS[3:6])
+    batch = M.ElementBatch(make_basis(M, p, k), corners)
+    n = specs.total_size(p, p)
+    x = rng.standard_normal((3, n))
+    mats = M.compute_element_matrices(specs, exprs, batch)
+    vecs = M.compute_element_vectors(specs, exprs, batch, x)
+    ob = O.basis(p, p + k + 1)
+    blocks, fs = O.decode_expressions(exprs, names)
+    for i in range(3):
+        assert relerr(mats[i], O.element_matrix(ob, corners[i], orders, blocks, fs)) < 1e-10
+        assert relerr(vecs[i], O.element_vector(ob, corners[i], orders, blocks, x[i], fs)) < 1e-10
+
+
+def check_linear_system(M, SV, ST, fix, nh, nv):
+    """tests/test_solving.py: operators against the reference's outputs, Schur solve against its solution."""
+    g = golden(fix + ".npz")
+    s = SYSTEMS["mixed_poisson_sorted"]
+    p, k = int(g["order"]), int(g["k"])
+    specs = specs_of(M, s)
+    batch = M.ElementBatch(make_basis(M, p, k), np.ascontiguousarray(g["corners"]))
+    mats = M.compute_element_matrices(specs, s["lhs"], batch)
+    assert relerr(mats[0], g["mat0"]) < TOL_MAT
+    ne = mats.shape[1]
+    row, col, val, nt = ST.continuity_constraints_1form(nh, nv, p, s["form_orders"])
+    sysm = SV.LinearSystem(mats, (row, col, val), nt)
+    assert relerr(sysm.apply_diagonal(g["x"]), g["apply_diagonal"]) < 1e-12
+    assert relerr(sysm.apply_diagonal_inverse(g["x"]), g["apply_diagonal_inverse"]) < 1e-9
+    assert relerr(sysm.apply_trace(g["x"]), g["apply_trace"]) < 1e-12
+    assert relerr(sysm.apply_trace_transpose(g["trace_in"]), g["apply_trace_transpose"]) < 1e-12
+    t = g["trace_in"]
+    composed = sysm.apply_trace(sysm.apply_diagonal_inverse(sysm.apply_trace_transpose(t)))
+    assert relerr(sysm.apply_full_trace_system(t), composed) < 1e-12
+    x, lam, res, it = SV.solve_schur_iterative(sysm, g["rhs"], g["con_rhs"], SV.ConvergenceSettings(2000, 1e-30, 1e-12))
+    assert relerr(x, g["sol_dense"]) < 1e-8
+    assert relerr(lam, g["sol_trace"]) < 1e-8
+    assert abs(it - int(g["iters"])) <= 12
+    # residual of the REFERENCE-assembled saddle system (north_star: 1e-10 relative)
+    n_dense = x.size
+    r1 = g["rhs"] - sysm.apply_diagonal(x) - sysm.apply_trace_transpose(lam)
+    r2 = g["con_rhs"] - sysm.apply_trace(x)
+    rel = np.sqrt(r1 @ r1 + r2 @ r2) / np.sqrt(g["rhs"] @ g["rhs"] + g["con_rhs"] @ g["con_rhs"])
+    assert rel < 1e-10, rel
+    # BLAS-1
+    a, b = g["x"], g["rhs"]
+    assert relerr(SV.vec_axpby(2.0, a, -0.5, b), 2.0 * a - 0.5 * b) < 1e-15
+    assert abs(SV.vec_dot(a, b) - a @ b) < 1e-10 * abs(a @ b) + 1e-12

@@ -1,0 +1,118 @@
+"""`-m gpu`: parity of the CUDA path (libmfv2d_cuda.so on cuda:0, called through the C-ABI by the host
+mirror) against the oracle and the reference's golden outputs, plus size-independent properties at the
+BASELINE.json sizes.  Nothing here reads /root/reference."""
+import numpy as np
+import pytest
+
+import parity_cases as P
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def gpu():
+    import mfv2d_b200._capi as capi
+
+    capi._use_library_for_testing(capi.LIB_PATH)
+    from mfv2d_b200 import _mfv2d as M
+    from mfv2d_b200 import solving as SV
+    from mfv2d_b200 import structured as ST
+    from mfv2d_b200.runtime import get_context
+
+    ctx = get_context()  # raises loudly without a B200 / without the built library
+    assert ctx.handle
+    return M, SV, ST
+
+
+def test_tables(gpu):
+    P.check_tables(gpu[0])
+
+
+def test_masses_golden(gpu):
+    P.check_masses_golden(gpu[0])
+
+
+@pytest.mark.parametrize("k", [0, 2, 3])
+def test_masses_oracle(gpu, k):
+    P.check_masses_oracle(gpu[0], cases=[(p, k) for p in range(1, 9)], n_random=256)
+
+
+@pytest.mark.parametrize("name", sorted(P.SYSTEMS))
+def test_system_golden(gpu, name):
+    P.check_system_golden(gpu[0], name)
+
+
+@pytest.mark.parametrize("name,p,k", [("stokes", 4, 3), ("mixed_poisson", 6, 3), ("adv_dif", 5, 3), ("direct_poisson", 8, 3),
+                                      ("navier_stokes", 3, 3), ("heat_mixed", 7, 2), ("stokes", 8, 3)])
+def test_matrix_vector_consistency(gpu, name, p, k):
+    P.check_matrix_vector_consistency(gpu[0], name, p, k, n=300)
+
+
+def test_incidence(gpu):
+    P.check_incidence(gpu[0], orders=(1, 2, 3, 4, 5, 8))
+
+
+def test_dense(gpu):
+    P.check_dense(gpu[0])
+
+
+def test_fields(gpu):
+    P.check_fields(gpu[0])
+
+
+def test_interior_products(gpu):
+    P.check_interior_products(gpu[0], p=4, k=2)
+    P.check_interior_products(gpu[0], p=6, k=3)
+
+
+def test_bytecode_errors(gpu):
+    P.check_bytecode_errors(gpu[0])
+
+
+def test_generic_chain(gpu):
+    P.check_generic_chain(gpu[0], p=3, k=2)
+
+
+@pytest.mark.parametrize("fix,nh,nv", [("solve_10x10_p3", 10, 10), ("solve_3x4_p4", 3, 4), ("solve_5x2_p5_def", 5, 2),
+                                       ("solve_6x6_p3_def", 6, 6)])
+def test_linear_system(gpu, fix, nh, nv):
+    P.check_linear_system(*gpu, fix, nh, nv)
+
+
+def test_empty_batches(gpu):
+    M = gpu[0]
+    b = P.make_basis(M, 3, 3)
+    batch = M.ElementBatch(b, np.zeros((0, 4, 2)))
+    assert batch.mass(2).shape == (0, 24, 24)
+    s = P.SYSTEMS["mixed_poisson"]
+    assert M.compute_element_matrices(P.specs_of(M, s), s["lhs"], batch).shape == (0, 33, 33)
+
+
+def test_full_size_properties(gpu):
+    """Config 2 (Stokes 256 x 256, p = 4) at full size, device resident: symmetry of the assembled blocks,
+    matrix @ x == matrix-free vector, and agreement of a strided sample with the oracle."""
+    import fields as F
+    from oracle import mfv2d_oracle as O
+
+    M, SV, ST = gpu
+    from mfv2d_b200.runtime import get_context
+
+    ctx = get_context()
+    p, k, n_side = 4, 3, 256
+    s = P.SYSTEMS["stokes"]
+    specs = P.specs_of(M, s)
+    corners = ST.unit_square_corners(n_side, n_side, F.deform)
+    batch = M.ElementBatch(P.make_basis(M, p, k), corners)
+    ne = specs.total_size(p, p)
+    out = ctx.empty((batch.n, ne, ne))
+    M.compute_element_matrices(specs, s["lhs"], batch, out=out)
+    mats = out.get()
+    assert np.array_equal(mats, np.swapaxes(mats, 1, 2)) or P.relerr(mats, np.swapaxes(mats, 1, 2)) < 1e-13
+    rng = np.random.default_rng(0)
+    x = rng.standard_normal((batch.n, ne))
+    y = M.compute_element_vectors(specs, s["lhs"], batch, x)
+    assert P.relerr(np.einsum("eij,ej->ei", mats, x), y) < 1e-12
+    ob = O.basis(p, p + k + 1)
+    blocks, fs = O.decode_expressions(s["lhs"], s["form_names"])
+    for e in range(0, batch.n, 4099):
+        assert P.relerr(mats[e], O.element_matrix(ob, corners[e], s["form_orders"], blocks, fs)) < 1e-12
