@@ -287,7 +287,7 @@ def run_ours(args):
     ctx.synchronize()
     barrier(dist)
     launches = ctx.launch_count - l0
-    clocks = sampler.stop() if rank == 0 else None
+    clocks = None
     ms = max_over_ranks(dist, ms)
     total_elems = sum_over_ranks(dist, float(n))
     ms_per_step = ms / args.steps
@@ -316,10 +316,13 @@ def run_ours(args):
         hbatch.set_corners(h_corners)
         M.compute_element_matrices(specs, lhs, hbatch, out=h_out)
 
-    step_host()
+    if args.skip_e2e:
+        e2e_steps = 0
+    else:
+        step_host()
+        e2e_steps = max(1, min(args.steps, 3))
     ctx.synchronize()
     barrier(dist)
-    e2e_steps = max(1, min(args.steps, 3))
     t0 = time.perf_counter()
     ctx.timer_start()
     for _ in range(e2e_steps):
@@ -328,13 +331,15 @@ def run_ours(args):
     ctx.synchronize()
     e2e_wall = (time.perf_counter() - t0) * 1e3
     e2e_ms = max_over_ranks(dist, max(e2e_ms, e2e_wall))
-    e2e_value = total_elems / (e2e_ms / e2e_steps * 1e-3)
-    check_sum = float(h_out[0].sum())
+    e2e_value = total_elems / (e2e_ms / e2e_steps * 1e-3) if e2e_steps else None
+    check_sum = float(h_out[0].sum()) if e2e_steps else None
+    if rank == 0:
+        clocks = sampler.stop()
     del h_out, hbatch
 
     # ---- extra metrics on rank-local data: matrix-free apply and the Schur-CG solve ----
     extra = {}
-    if rank == 0 or True:
+    if not args.skip_extra:
         rng = np.random.default_rng(rank)
         x = ctx.to_device(rng.standard_normal((n, ne)))
         y = ctx.empty((n, ne))
@@ -372,7 +377,7 @@ def run_ours(args):
         rhs = ctx.to_device(rng.standard_normal(n * s_ne))
         phi = ctx.to_device(np.zeros(nt))
         t0 = time.perf_counter()
-        xs, lam, res, it = SV.solve_schur_iterative(system, rhs, phi, SV.ConvergenceSettings(20000, 1e-300, 1e-10))
+        xs, lam, res, it = SV.solve_schur_iterative(system, rhs, phi, SV.ConvergenceSettings(20000, 1e300, 1e-10))
         ctx.synchronize()
         extra["solve"] = {"system": f"mixed Poisson (Darcy) {nh}x{n // nh} p{p} strip of this rank, random rhs, rtol 1e-10",
                           "s": time.perf_counter() - t0, "iterations": it, "residual": res, "multipliers": nt,
@@ -403,6 +408,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--skip-extra", action="store_true", help="skip the apply / solve extras (profiling runs)")
+    ap.add_argument("--skip-e2e", action="store_true", help="skip the host-buffer leg (profiling runs)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":
