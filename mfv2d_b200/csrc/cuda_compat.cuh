@@ -26,6 +26,7 @@ __device__ __forceinline__ double warp_sum(double v)
 __device__ __forceinline__ double ld_ro(const double *p) { return __ldg(p); }
 __device__ __forceinline__ int4 ld_ro(const int4 *p) { return __ldg(p); }
 __device__ __forceinline__ int ld_ro(const int *p) { return __ldg(p); }
+__device__ __forceinline__ float4 ld_ro(const float4 *p) { return __ldg(p); }
 
 #else // ---------------------------------------------------------------------------------------
 #include "../../tests/emu/emu_cuda.h"

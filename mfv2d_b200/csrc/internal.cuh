@@ -96,6 +96,10 @@ struct mfv2d_basis
     int32_t *d_inc = nullptr;
     int inc_off[5] = {0, 0, 0, 0, 0};
     std::vector<int32_t> h_inc;
+    // the same maps in branch-free form: [rows][4] column indices (0 when unused) and [rows][4] signs
+    // (+1, -1, or 0 when unused), used by the assembly kernel's emission
+    int32_t *d_inc_idx = nullptr;
+    float *d_inc_sgn = nullptr;
 };
 
 struct mfv2d_elements

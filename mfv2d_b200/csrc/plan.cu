@@ -407,9 +407,8 @@ int plan_lower_matrix(mfv2d_plan *plan)
     }
 
     // fixed shared memory: tables, geometry (5 q^2), weight field G (q^2), T scratch (q * (p+1)^2, padded)
-    const AsmLayout lay = asm_layout(p, q, plan->basis->tab_len);
-    const int fixed = lay.arena;
-    const int capacity = (int)(plan->ctx->smem_optin / sizeof(double)) - fixed - 32;
+    const int fixed = asm_fixed_doubles(p, plan->basis->tab_len, 1) + slot_layout(p, q).arena;
+    const int capacity = (int)(plan->ctx->smem_optin / sizeof(double)) - fixed - 64;
 
     auto find_dense = [&](std::vector<DevDense> &list, int begin, const Factor &d) {
         for (int i = begin; i < (int)list.size(); ++i)
@@ -433,7 +432,7 @@ int plan_lower_matrix(mfv2d_plan *plan)
         for (int bi = stage.block_begin; bi < stage.block_end; ++bi)
         {
             const DevBlock &db = plan->blocks[bi];
-            const int RG = 8;
+            const int RG = 16; // rows per emission strip (ASM_ROWS_PER_UNIT)
             for (int c0 = 0; c0 < db.ncols; c0 += 32)
                 for (int r0 = 0; r0 < db.nrows; r0 += RG)
                 {

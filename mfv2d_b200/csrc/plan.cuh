@@ -113,21 +113,28 @@ struct mfv2d_plan
     int mprog_off = 0, mcoef_off = 0; // matrix-mode programs (column-by-column fallback) follow the vector ones
 };
 
-// shared-memory layout of the assembly kernel (in doubles); used by the planner and the kernel
-struct AsmLayout
+// shared-memory layout of the assembly kernel (in doubles); used by the planner and the kernel.
+// One slot per element of a pass: geo 5 q^2 | G | T | arena
+struct SlotLayout
 {
-    int geo, G, T, ldT, arena;
+    int G, T, ldT, arena;
 };
-static inline __host__ __device__ AsmLayout asm_layout(int p, int q, int tab_len)
+static inline __host__ __device__ SlotLayout slot_layout(int p, int q)
 {
-    AsmLayout l;
+    SlotLayout l;
     const int q2 = q * q;
-    l.geo = (tab_len + 1) & ~1;
-    l.G = l.geo + 5 * q2;
-    l.T = (l.G + q2 + 1) & ~1;
+    l.G = 5 * q2;
+    l.T = (l.G + q2 + 3) & ~3;
     l.ldT = ((p + 1) * (p + 1) + 3) & ~3;
     l.arena = l.T + q * l.ldT + 4;
     return l;
+}
+// fixed part: tables | pair LUTs (two ints per double) | corners of the slots
+static inline __host__ __device__ int asm_fixed_doubles(int p, int tab_len, int epb)
+{
+    const int n_pairs = (p + 1) * (p + 2) / 2 + p * (p + 1) / 2;
+    int n = ((tab_len + 1) & ~1) + ((n_pairs + 1) >> 1) + 8 * epb;
+    return (n + 15) & ~15;
 }
 
 int plan_lower_matrix(mfv2d_plan *plan);

@@ -358,6 +358,22 @@ int mfv2d_cuda_basis_create(mfv2d_ctx *ctx, int p, int q, mfv2d_basis **out)
         r = mfv2d_cuda_upload(ctx, b->d_tab, tab.data(), tab.size() * sizeof(double));
     if (!r)
         r = mfv2d_cuda_upload(ctx, b->d_inc, b->h_inc.data(), b->h_inc.size() * sizeof(int32_t));
+    std::vector<int32_t> idx(b->h_inc.size());
+    std::vector<float> sgn(b->h_inc.size());
+    for (size_t i = 0; i < b->h_inc.size(); ++i)
+    {
+        const int32_t v = b->h_inc[i];
+        idx[i] = v == 0 ? 0 : (v < 0 ? -v : v) - 1;
+        sgn[i] = v == 0 ? 0.f : (v < 0 ? -1.f : 1.f);
+    }
+    if (!r)
+        r = mfv2d_cuda_malloc(ctx, idx.size() * sizeof(int32_t), (void **)&b->d_inc_idx);
+    if (!r)
+        r = mfv2d_cuda_malloc(ctx, sgn.size() * sizeof(float), (void **)&b->d_inc_sgn);
+    if (!r)
+        r = mfv2d_cuda_upload(ctx, b->d_inc_idx, idx.data(), idx.size() * sizeof(int32_t));
+    if (!r)
+        r = mfv2d_cuda_upload(ctx, b->d_inc_sgn, sgn.data(), sgn.size() * sizeof(float));
     if (r)
     {
         mfv2d_cuda_basis_destroy(b);
@@ -375,6 +391,10 @@ void mfv2d_cuda_basis_destroy(mfv2d_basis *b)
         mfv2d_cuda_free(b->ctx, b->d_tab);
     if (b->d_inc)
         mfv2d_cuda_free(b->ctx, b->d_inc);
+    if (b->d_inc_idx)
+        mfv2d_cuda_free(b->ctx, b->d_inc_idx);
+    if (b->d_inc_sgn)
+        mfv2d_cuda_free(b->ctx, b->d_inc_sgn);
     delete b;
 }
 

@@ -19,6 +19,7 @@
 #define __device__
 #define __host__
 #define __forceinline__ inline
+#define __noinline__
 #define __restrict__
 #define __shared__ static
 #define __launch_bounds__(...)
@@ -43,6 +44,11 @@ struct int2
 {
     int x, y;
 };
+struct float4
+{
+    float x, y, z, w;
+};
+static inline float4 make_float4(float a, float b, float c, float d) { return float4{a, b, c, d}; }
 static inline int4 make_int4(int a, int b, int c, int d) { return int4{a, b, c, d}; }
 static inline double2 make_double2(double a, double b) { return double2{a, b}; }
 
