@@ -1,5 +1,5 @@
-// Batched element-matrix assembly: Jacobian, sum-factorised mass / interior-product matrices in
-// shared memory, incidence application as signed gathers and coalesced row-major stores of the
+// Batched element-matrix assembly: Jacobian and weight fields, sum-factorised mass / interior-product
+// matrices in shared memory, incidence application as signed gathers and row-major stores of the
 // N_e x N_e element matrices.
 //
 // Replaces, per element: fem_space_2d_create (src/fem_space/fem_space.c:16-57),
@@ -8,288 +8,319 @@
 // (src/evaluation/incidence.c:16-479) and the block loop of compute_element_matrix
 // (src/evaluation/element_system.c:135-181).
 //
-// Organisation: a persistent CTA works on EPB elements at a time ("slots").  Every phase is a
-// thread-strided loop over (item, slot) pairs with the slot index fastest, so that the basis tables
-// are read as broadcasts and per-slot data sits in distinct banks (slot stride = 4 mod 16 doubles):
-//   geometry -> [weight field -> T = sum_b B B' G -> M = sum_a A A' T] per tensor block -> emission.
-// Symmetric blocks (M0, M2, the hh / vv blocks of M1) are computed for i <= k only and mirrored.
-// The emission applies the incidence maps branch-free from (index, sign) tables: NL x NR gathers per
-// output entry, with NL, NR in {1, 2, 4} compiled in.
+// Organisation.  A persistent CTA keeps the plan's descriptor blob (stages, tensor blocks, emission
+// units, incidence rows, the basis tables and their pairwise products) in shared memory and works on
+// `epb` elements at a time ("slots").  Per pass and plan stage:
+//   W   every thread takes quadrature points (e, a, b): Jacobian in registers, all weight fields of the
+//       stage written to the slot                                                      (1 barrier)
+//   S1  T[(j,l)][a] = sum_b (B_j B2_l)(b) W[a][b]: a thread holds one row W[a][:] in registers and walks a
+//       chunk of the (j,l) pair list, reading the product table rows as 16-byte broadcasts (1 barrier)
+//   S2  D[(i,j),(k,l)] = sum_a (A_i A2_k)(a) T[(j,l)][a]: a thread holds two columns T[(j,l)][:] in
+//       registers and walks a chunk of the (i,k) pair list; i <-> k and transposed images are stored
+//       from the same accumulator                                                      (1 barrier)
+//   E   emission: a warp takes a tile of one block, lanes = columns (x rows for narrow blocks); the
+//       right incidence row is fetched once per lane, the left one once per row; coalesced stores.
+// S1 and S2 are templated on the number of quadrature points so that the register tiles are real
+// registers.  Symmetric index pairs are computed once.
 //
 // Roofline: bound by the HBM WRITE of the element matrices, 64 + 8 N_e^2 algorithmic bytes per element
 // (SURVEY.md 8d); the sum-factorised contraction needs O(p^4 q) flops per element.
-#include "dense_device.cuh"
+#include "plan.cuh"
 
 #define ASM_THREADS 256
-#define ASM_ROWS_PER_UNIT 16
 
 struct AsmArgs
 {
-    const double *tab;
-    const int32_t *inc_idx; // [rows][4]
-    const float *inc_sgn;   // [rows][4]
-    const double *corners;
     const char *blob;
+    const double *corners;
     const double *fields[16]; // per field: [n_elem][q*q][2]
     double *out;
     int32_t *status;
     unsigned long long n_elem;
-    int tab_len, p, q;
-    int inc_off[4];
-    int n_stages, off_dense, off_terms, off_blocks, off_units;
+    int p, q;
     int n_total;                   // leading dimension of the output rows
     unsigned long long out_stride; // doubles between consecutive elements of the output
-    int epb_shift;                 // log2(elements per CTA pass)
-    int slot_stride;               // doubles between slots
-    int slot_off;                  // offset of slot 0 inside shared memory (doubles)
+    AsmLayout lay;
 };
 
 // x / n for 0 <= x < 2^20 and 1 <= n < 2^11 without an integer division
 __device__ __forceinline__ int fast_div(int x, float inv_n) { return (int)(((float)x + 0.5f) * inv_n); }
 
-struct AsmShared
+template <int Q> __device__ __forceinline__ void load_row(double (&r)[Q], const double *__restrict__ src)
 {
-    const double *node, *edge, *pnts, *wgts;
-    const int *pairs_n, *pairs_e; // (i << 8) | k for i <= k, for n = p + 1 and n = p
-    double *cs;                   // [epb][8]
-    double *slot0;
-    int slot_stride, epb, epb_shift, n_valid;
-    SlotLayout sl;
-    int p, q;
-};
-
-__device__ __forceinline__ double *slot_base(const AsmShared &s, int e) { return s.slot0 + (size_t)e * s.slot_stride; }
-
-__device__ __forceinline__ void phase_geometry(const AsmShared &s)
-{
-    const int q = s.q, q2 = q * q;
-    const float inv_q = 1.0f / (float)q;
-    for (int idx = threadIdx.x; idx < (q2 << s.epb_shift); idx += blockDim.x)
+#pragma unroll
+    for (int b = 0; b + 1 < Q; b += 2)
     {
-        const int e = idx & (s.epb - 1), pt = idx >> s.epb_shift;
-        if (e >= s.n_valid)
-            continue;
-        const int a = fast_div(pt, inv_q), b = pt - a * q;
-        const double *cs = s.cs + 8 * e;
-        double *geo = slot_base(s, e);
-        const double eta = s.pnts[a], xi = s.pnts[b];
+        const double2 v = *reinterpret_cast<const double2 *>(src + b);
+        r[b] = v.x;
+        r[b + 1] = v.y;
+    }
+    if (Q & 1)
+        r[Q - 1] = src[Q - 1];
+}
+
+template <int Q> __device__ __forceinline__ void dot_row2(const double *__restrict__ row, const double (&t0)[Q],
+                                                          const double (&t1)[Q], double &r0, double &r1)
+{
+    double a0 = 0.0, a1 = 0.0;
+#pragma unroll
+    for (int b = 0; b + 1 < Q; b += 2)
+    {
+        const double2 v = *reinterpret_cast<const double2 *>(row + b);
+        a0 = fma(v.x, t0[b], a0);
+        a1 = fma(v.x, t1[b], a1);
+        a0 = fma(v.y, t0[b + 1], a0);
+        a1 = fma(v.y, t1[b + 1], a1);
+    }
+    if (Q & 1)
+    {
+        const double v = row[Q - 1];
+        a0 = fma(v, t0[Q - 1], a0);
+        a1 = fma(v, t1[Q - 1], a1);
+    }
+    r0 = a0;
+    r1 = a1;
+}
+
+template <int Q> __device__ __forceinline__ double dot_row(const double *__restrict__ row, const double (&g)[Q])
+{
+    double a0 = 0.0, a1 = 0.0;
+#pragma unroll
+    for (int b = 0; b + 1 < Q; b += 2)
+    {
+        const double2 v = *reinterpret_cast<const double2 *>(row + b);
+        a0 = fma(v.x, g[b], a0);
+        a1 = fma(v.y, g[b + 1], a1);
+    }
+    if (Q & 1)
+        a0 = fma(row[Q - 1], g[Q - 1], a0);
+    return a0 + a1;
+}
+
+// ---- W: Jacobian (src/fem_space/fem_space.c:39-53) and the weight fields of a stage -------------------
+template <int Q>
+__device__ __forceinline__ void phase_weights(const AsmArgs &args, double *smem, const DevStage &sg, const DevW *ws,
+                                              const double *pnts, const double *wgts, unsigned long long elem0, int n_valid)
+{
+    const AsmLayout &L = args.lay;
+    constexpr int q2 = Q * Q;
+    const int ldq = L.ldq;
+    for (int idx = threadIdx.x; idx < n_valid * q2; idx += blockDim.x)
+    {
+        const int e = idx / q2, pt = idx - e * q2;
+        const int a = pt / Q, b = pt - a * Q;
+        const double *cs = smem + L.off_cs + 8 * e;
+        const double eta = pnts[a], xi = pnts[b];
         const double x0 = cs[0], y0 = cs[1], x1 = cs[2], y1 = cs[3], x2 = cs[4], y2 = cs[5], x3 = cs[6], y3 = cs[7];
         const double j00 = 0.25 * ((x1 - x0) * (1 - eta) + (x2 - x3) * (1 + eta));
         const double j01 = 0.25 * ((y1 - y0) * (1 - eta) + (y2 - y3) * (1 + eta));
         const double j10 = 0.25 * ((x3 - x0) * (1 - xi) + (x2 - x1) * (1 + xi));
         const double j11 = 0.25 * ((y3 - y0) * (1 - xi) + (y2 - y1) * (1 + xi));
-        geo[pt] = j00;
-        geo[q2 + pt] = j01;
-        geo[2 * q2 + pt] = j10;
-        geo[3 * q2 + pt] = j11;
-        geo[4 * q2 + pt] = j00 * j11 - j10 * j01;
-    }
-}
-
-__device__ __forceinline__ void phase_weight(const AsmShared &s, int kind, const double *field, unsigned long long elem0)
-{
-    const int q = s.q, q2 = q * q;
-    const float inv_q = 1.0f / (float)q;
-    for (int idx = threadIdx.x; idx < (q2 << s.epb_shift); idx += blockDim.x)
-    {
-        const int e = idx & (s.epb - 1), pt = idx >> s.epb_shift;
-        if (e >= s.n_valid)
-            continue;
-        const int a = fast_div(pt, inv_q), b = pt - a * q;
-        double *geo = slot_base(s, e);
-        const double w = s.wgts[a] * s.wgts[b];
-        const double det = geo[4 * q2 + pt];
-        double v;
-        switch (kind)
+        const double det = j00 * j11 - j10 * j01;
+        const double w = wgts[a] * wgts[b];
+        double *W = smem + L.off_slots + (size_t)e * L.slot_stride + L.slot_w + a * ldq + b;
+        for (int wi = sg.w_begin; wi < sg.w_end; ++wi, W += Q * ldq)
         {
-        case W_M0:
-            v = det * w;
-            break;
-        case W_M2:
-            v = w / det;
-            break;
-        case W_HH: {
-            const double j10 = geo[2 * q2 + pt], j11 = geo[3 * q2 + pt];
-            v = (j11 * j11 + j10 * j10) / det * w;
-            break;
-        }
-        case W_VV: {
-            const double j00 = geo[pt], j01 = geo[q2 + pt];
-            v = (j00 * j00 + j01 * j01) / det * w;
-            break;
-        }
-        case W_HV: {
-            const double j00 = geo[pt], j01 = geo[q2 + pt], j10 = geo[2 * q2 + pt], j11 = geo[3 * q2 + pt];
-            v = (j01 * j11 + j00 * j10) / det * w;
-            break;
-        }
-        default: {
-            const double j00 = geo[pt], j01 = geo[q2 + pt], j10 = geo[2 * q2 + pt], j11 = geo[3 * q2 + pt];
-            const double *fld = field + (elem0 + e) * (unsigned long long)(2 * q2);
-            const double fx = fld[2 * pt], fy = fld[2 * pt + 1];
-            if (kind == W_P1H)
-                v = (fx * j11 - fy * j10) * w;
-            else if (kind == W_P1V)
-                v = -(fy * j00 - fx * j01) * w;
-            else if (kind == W_P2H)
-                v = -(fx * j10 + fy * j11) / det * w;
-            else
-                v = -(fx * j00 + fy * j01) / det * w;
-            break;
-        }
-        }
-        geo[s.sl.G + pt] = v;
-    }
-}
-
-// T[a][j * nB2 + l] = sum_b B[j][b] B2[l][b] G[a][b]      (sym: B == B2, j <= l computed and mirrored)
-__device__ __forceinline__ void phase_stage1(const AsmShared &s, const double *__restrict__ B, int nB,
-                                             const double *__restrict__ B2, int nB2, bool sym, const int *pairs)
-{
-    const int q = s.q, ldT = s.sl.ldT;
-    const int per_a = sym ? nB * (nB + 1) / 2 : nB * nB2;
-    const float inv_per_a = 1.0f / (float)per_a, inv_nb2 = 1.0f / (float)nB2;
-    for (int idx = threadIdx.x; idx < ((q * per_a) << s.epb_shift); idx += blockDim.x)
-    {
-        const int e = idx & (s.epb - 1), item = idx >> s.epb_shift;
-        if (e >= s.n_valid)
-            continue;
-        const int a = fast_div(item, inv_per_a), rem = item - a * per_a;
-        int j, l;
-        if (sym)
-        {
-            const int pr = pairs[rem];
-            j = pr >> 8;
-            l = pr & 255;
-        }
-        else
-        {
-            j = fast_div(rem, inv_nb2);
-            l = rem - j * nB2;
-        }
-        double *base = slot_base(s, e);
-        const double *g = base + s.sl.G + a * q;
-        const double *bj = B + j * q, *bl = B2 + l * q;
-        double acc = 0.0;
-        for (int b = 0; b < q; ++b)
-            acc = fma(bj[b] * bl[b], g[b], acc);
-        double *T = base + s.sl.T + a * ldT;
-        T[j * nB2 + l] = acc;
-        if (sym)
-            T[l * nB2 + j] = acc;
-    }
-}
-
-// dst[(r0 + i nB + j), (c0 + k nB2 + l)] = sum_a A[i][a] A2[k][a] T[a][j nB2 + l]
-//   sym:    A == A2, r0 == c0: only i <= k, mirrored into the lower triangle
-//   mirror: the block is also written transposed (symmetric off-diagonal block of M1)
-//   trans:  the block is written transposed only (transposed interior products)
-__device__ __forceinline__ void phase_stage2(const AsmShared &s, int dst_off, int ld, int r0, int c0, bool trans, bool mirror,
-                                             bool sym, const double *__restrict__ A, int nA, const double *__restrict__ A2,
-                                             int nA2, int nB, int nB2, const int *pairs)
-{
-    const int q = s.q, ldT = s.sl.ldT;
-    const int nJL = nB * nB2;
-    const int ntile = (nJL + 3) >> 2;
-    const int n_ik = sym ? nA * (nA + 1) / 2 : nA * nA2;
-    const float inv_ntile = 1.0f / (float)ntile, inv_na2 = 1.0f / (float)nA2, inv_nb2 = 1.0f / (float)nB2;
-    for (int idx = threadIdx.x; idx < ((n_ik * ntile) << s.epb_shift); idx += blockDim.x)
-    {
-        const int e = idx & (s.epb - 1), item = idx >> s.epb_shift;
-        if (e >= s.n_valid)
-            continue;
-        const int ik = fast_div(item, inv_ntile);
-        const int jl0 = (item - ik * ntile) << 2;
-        int i, k;
-        if (sym)
-        {
-            const int pr = pairs[ik];
-            i = pr >> 8;
-            k = pr & 255;
-        }
-        else
-        {
-            i = fast_div(ik, inv_na2);
-            k = ik - i * nA2;
-        }
-        double *base = slot_base(s, e);
-        const double *T = base + s.sl.T + jl0;
-        const double *ai = A + i * q, *ak = A2 + k * q;
-        double acc0 = 0.0, acc1 = 0.0, acc2 = 0.0, acc3 = 0.0;
-        for (int a = 0; a < q; ++a)
-        {
-            const double pa = ai[a] * ak[a];
-            const double2 t01 = *reinterpret_cast<const double2 *>(T + a * ldT);
-            const double2 t23 = *reinterpret_cast<const double2 *>(T + a * ldT + 2);
-            acc0 = fma(pa, t01.x, acc0);
-            acc1 = fma(pa, t01.y, acc1);
-            acc2 = fma(pa, t23.x, acc2);
-            acc3 = fma(pa, t23.y, acc3);
-        }
-        double *dst = base + s.sl.arena + dst_off;
-        const double acc[4] = {acc0, acc1, acc2, acc3};
-        int j = fast_div(jl0, inv_nb2), l = jl0 - j * nB2;
-#pragma unroll
-        for (int t = 0; t < 4; ++t)
-        {
-            if (jl0 + t < nJL)
+            const DevW dw = ws[wi];
+            double v;
+            switch (dw.kind)
             {
-                const int row = r0 + i * nB + j, col = c0 + k * nB2 + l;
-                if (!trans)
-                    dst[row * ld + col] = acc[t];
-                if (trans || mirror || (sym && i != k))
-                    dst[col * ld + row] = acc[t];
+            case W_M0:
+                v = det * w;
+                break;
+            case W_M2:
+                v = w / det;
+                break;
+            case W_HH:
+                v = (j11 * j11 + j10 * j10) / det * w;
+                break;
+            case W_VV:
+                v = (j00 * j00 + j01 * j01) / det * w;
+                break;
+            case W_HV:
+                v = (j01 * j11 + j00 * j10) / det * w;
+                break;
+            default: {
+                const double *fld = args.fields[dw.field] + (elem0 + e) * (unsigned long long)(2 * q2);
+                const double fx = fld[2 * pt], fy = fld[2 * pt + 1];
+                if (dw.kind == W_P1H)
+                    v = (fx * j11 - fy * j10) * w;
+                else if (dw.kind == W_P1V)
+                    v = -(fy * j00 - fx * j01) * w;
+                else if (dw.kind == W_P2H)
+                    v = -(fx * j10 + fy * j11) / det * w;
+                else
+                    v = -(fx * j00 + fy * j01) / det * w;
+                break;
             }
-            if (++l == nB2)
+            }
+            *W = v;
+        }
+    }
+}
+
+__device__ __forceinline__ int find_tb1(const DevTB *tbs, const DevRound &rd, int x)
+{
+    int t = rd.tb_begin;
+    while (t + 1 < rd.tb_end && x >= tbs[t + 1].x1_begin)
+        ++t;
+    return t;
+}
+__device__ __forceinline__ int find_tb2(const DevTB *tbs, const DevRound &rd, int x)
+{
+    int t = rd.tb_begin;
+    while (t + 1 < rd.tb_end && x >= tbs[t + 1].x2_begin)
+        ++t;
+    return t;
+}
+
+// ---- S1: T[(j,l)][a] = sum_b B_j(b) B2_l(b) W[a][b] -----------------------------------------------------
+template <int Q>
+__device__ __forceinline__ void phase_s1(const AsmArgs &args, double *smem, const DevRound &rd, const DevTB *tbs, int n_valid)
+{
+    const AsmLayout &L = args.lay;
+    const int ldq = L.ldq;
+    const int n_ea = L.epb * Q;
+    const float inv_ea = 1.0f / (float)n_ea;
+    const int *pairs = reinterpret_cast<const int *>(reinterpret_cast<const char *>(smem) + L.off_pairs);
+    for (int x = threadIdx.x; x < rd.x1_total; x += blockDim.x)
+    {
+        const DevTB &tb = tbs[find_tb1(tbs, rd, x)];
+        const int xl = x - tb.x1_begin;
+        const int sub = fast_div(xl, inv_ea), ea = xl - sub * n_ea;
+        const int e = ea / Q, a = ea - e * Q;
+        if (e >= n_valid)
+            continue;
+        double *slot = smem + L.off_slots + (size_t)e * L.slot_stride;
+        double g[Q];
+        load_row<Q>(g, slot + L.slot_w + tb.w * (Q * ldq) + a * ldq);
+        const int pk = tb.pkB;
+        const int np = L.pair_n[pk];
+        const int pb = (sub * np) / tb.n_sub1, pe = ((sub + 1) * np) / tb.n_sub1;
+        const int *pl = pairs + L.pair_off[pk];
+        const double *PT = reinterpret_cast<const double *>(reinterpret_cast<const char *>(smem) + L.off_pt[pk == PK_EN ? PK_NE : pk]);
+        double *T = slot + L.slot_t + tb.t_off + a;
+        const bool sym = pk <= PK_EE;
+        const int nB2 = tb.nB2;
+        for (int pi = pb; pi < pe; ++pi)
+        {
+            const int pr = pl[pi];
+            const int j = pr & 255, l = (pr >> 8) & 255;
+            const double acc = dot_row<Q>(PT + (pr >> 16) * ldq, g);
+            T[(j * nB2 + l) * ldq] = acc;
+            if (sym)
+                T[(l * nB2 + j) * ldq] = acc;
+        }
+    }
+}
+
+// ---- S2: D[(i,j),(k,l)] = sum_a A_i(a) A2_k(a) T[(j,l)][a] ------------------------------------------------
+template <int Q>
+__device__ __forceinline__ void phase_s2(const AsmArgs &args, double *smem, const DevRound &rd, const DevTB *tbs, int n_valid)
+{
+    const AsmLayout &L = args.lay;
+    const int ldq = L.ldq;
+    const int *pairs = reinterpret_cast<const int *>(reinterpret_cast<const char *>(smem) + L.off_pairs);
+    for (int x = threadIdx.x; x < rd.x2_total; x += blockDim.x)
+    {
+        const DevTB &tb = tbs[find_tb2(tbs, rd, x)];
+        const int nB = tb.nB, nB2 = tb.nB2;
+        const int nJL = nB * nB2, nJLP = (nJL + 1) >> 1, n_jle = L.epb * nJLP;
+        const int xl = x - tb.x2_begin;
+        const int sub = fast_div(xl, 1.0f / (float)n_jle), jle = xl - sub * n_jle;
+        const int e = fast_div(jle, 1.0f / (float)nJLP), jlp = jle - e * nJLP;
+        if (e >= n_valid)
+            continue;
+        double *slot = smem + L.off_slots + (size_t)e * L.slot_stride;
+        const int jl0 = 2 * jlp;
+        const bool has2 = jl0 + 1 < nJL;
+        const double *T = slot + L.slot_t + tb.t_off + jl0 * ldq;
+        double t0[Q], t1[Q];
+        load_row<Q>(t0, T);
+        load_row<Q>(t1, has2 ? T + ldq : T);
+        const int j0 = fast_div(jl0, 1.0f / (float)nB2), l0 = jl0 - j0 * nB2;
+        int j1 = j0, l1 = l0 + 1;
+        if (l1 == nB2)
+        {
+            l1 = 0;
+            ++j1;
+        }
+        const int rj0 = tb.r0 + j0, cl0 = tb.c0 + l0, rj1 = tb.r0 + j1, cl1 = tb.c0 + l1;
+        const int pk = tb.pkA;
+        const int np = L.pair_n[pk];
+        const int pb = (sub * np) / tb.n_sub2, pe = ((sub + 1) * np) / tb.n_sub2;
+        const int *pl = pairs + L.pair_off[pk];
+        const double *PT = reinterpret_cast<const double *>(reinterpret_cast<const char *>(smem) + L.off_pt[pk == PK_EN ? PK_NE : pk]);
+        double *D = slot + L.slot_arena + tb.dst_off;
+        const int ld = tb.ld;
+        const bool symA = pk <= PK_EE, direct = !tb.trans, flipped = tb.trans || tb.mirror;
+        for (int pi = pb; pi < pe; ++pi)
+        {
+            const int pr = pl[pi];
+            const int i = pr & 255, k = (pr >> 8) & 255;
+            double v0, v1;
+            dot_row2<Q>(PT + (pr >> 16) * ldq, t0, t1, v0, v1);
             {
-                l = 0;
-                ++j;
+                const int row = i * nB + rj0, col = k * nB2 + cl0;
+                if (direct)
+                    D[row * ld + col] = v0;
+                if (flipped)
+                    D[col * ld + row] = v0;
+                if (symA)
+                {
+                    const int row2 = k * nB + rj0, col2 = i * nB2 + cl0;
+                    if (direct)
+                        D[row2 * ld + col2] = v0;
+                    if (flipped)
+                        D[col2 * ld + row2] = v0;
+                }
+            }
+            if (has2)
+            {
+                const int row = i * nB + rj1, col = k * nB2 + cl1;
+                if (direct)
+                    D[row * ld + col] = v1;
+                if (flipped)
+                    D[col * ld + row] = v1;
+                if (symA)
+                {
+                    const int row2 = k * nB + rj1, col2 = i * nB2 + cl1;
+                    if (direct)
+                        D[row2 * ld + col2] = v1;
+                    if (flipped)
+                        D[col2 * ld + row2] = v1;
+                }
             }
         }
     }
 }
 
-__device__ __noinline__ void tensor_block_multi(const AsmShared &s, int wkind, const double *field, unsigned long long elem0,
-                                                   int dst_off, int ld, int r0, int c0, bool trans, bool mirror, bool sym,
-                                                   const double *A, int nA, const double *A2, int nA2, const double *B,
-                                                   int nB, const double *B2, int nB2)
+// in-place SPD inverse of the n x n matrix (leading dimension ld) at arena + off of every slot (Gauss-Jordan,
+// no pivoting needed); the column / row of the pivot are staged in the slot's T region
+__device__ __noinline__ void invert_spd_slots(const AsmArgs &args, double *smem, int off, int n, int ld, int n_valid, int *bad)
 {
-    const int np1 = s.p + 1;
-    phase_weight(s, wkind, field, elem0);
-    __syncthreads();
-    const bool sym1 = (B == B2);
-    phase_stage1(s, B, nB, B2, nB2, sym1, nB == np1 ? s.pairs_n : s.pairs_e);
-    __syncthreads();
-    phase_stage2(s, dst_off, ld, r0, c0, trans, mirror, sym, A, nA, A2, nA2, nB, nB2, nA == np1 ? s.pairs_n : s.pairs_e);
-    // the next phase_weight only writes G (not read by stage 2); stage 1 of the next block is behind a barrier
-}
-
-// in-place SPD inverse of the n x n matrices at arena + off of every slot (Gauss-Jordan, no pivoting)
-__device__ void invert_spd_multi(const AsmShared &s, int off, int n, int *bad)
-{
-    const float inv_n = 1.0f / (float)n;
+    const AsmLayout &L = args.lay;
+    const float inv_n = 1.0f / (float)n, inv_nn = 1.0f / (float)(n * n);
     for (int k = 0; k < n; ++k)
     {
         __syncthreads();
-        for (int idx = threadIdx.x; idx < (n << s.epb_shift); idx += blockDim.x)
+        for (int idx = threadIdx.x; idx < n_valid * n; idx += blockDim.x)
         {
-            const int e = idx & (s.epb - 1), i = idx >> s.epb_shift;
-            double *base = slot_base(s, e);
-            const double *D = base + s.sl.arena + off;
-            double *colk = base + s.sl.T, *rowk = colk + n;
-            colk[i] = D[i * n + k];
-            rowk[i] = D[k * n + i];
+            const int e = fast_div(idx, inv_n), i = idx - e * n;
+            double *slot = smem + L.off_slots + (size_t)e * L.slot_stride;
+            const double *D = slot + L.slot_arena + off;
+            double *colk = slot + L.slot_t, *rowk = colk + n;
+            colk[i] = D[i * ld + k];
+            rowk[i] = D[k * ld + i];
         }
         __syncthreads();
-        for (int idx = threadIdx.x; idx < ((n * n) << s.epb_shift); idx += blockDim.x)
+        for (int idx = threadIdx.x; idx < n_valid * n * n; idx += blockDim.x)
         {
-            const int e = idx & (s.epb - 1), ij = idx >> s.epb_shift;
-            if (e >= s.n_valid)
-                continue;
+            const int e = fast_div(idx, inv_nn), ij = idx - e * n * n;
             const int i = fast_div(ij, inv_n), j = ij - i * n;
-            double *base = slot_base(s, e);
-            double *D = base + s.sl.arena + off;
-            const double *colk = base + s.sl.T, *rowk = colk + n;
+            double *slot = smem + L.off_slots + (size_t)e * L.slot_stride;
+            double *D = slot + L.slot_arena + off;
+            const double *colk = slot + L.slot_t, *rowk = colk + n;
             const double pv = colk[k];
             if (ij == 0 && !(fabs(pv) > 1e-300))
                 bad[e] = 1;
@@ -300,80 +331,44 @@ __device__ void invert_spd_multi(const AsmShared &s, int off, int n, int *bad)
             else if (j == k)
                 v = -colk[i] * ip;
             else
-                v = fma(-colk[i] * ip, rowk[j], D[ij]);
-            D[ij] = v;
+                v = fma(-colk[i] * ip, rowk[j], D[i * ld + j]);
+            D[i * ld + j] = v;
         }
     }
     __syncthreads();
 }
 
-__device__ void compute_dense_multi(const AsmShared &s, const DevDense &dd, const double *const *fields,
-                                    unsigned long long elem0, int *bad)
-{
-    const int p = s.p, np1 = p + 1, nh = p * (p + 1);
-    const int off = dd.smem_off;
-    switch (dd.dk)
-    {
-    case DK_MASS0:
-        tensor_block_multi(s, W_M0, nullptr, elem0, off, np1 * np1, 0, 0, false, false, true, s.node, np1, s.node, np1, s.node,
-                           np1, s.node, np1);
-        break;
-    case DK_MASS2:
-        tensor_block_multi(s, W_M2, nullptr, elem0, off, p * p, 0, 0, false, false, true, s.edge, p, s.edge, p, s.edge, p,
-                           s.edge, p);
-        break;
-    case DK_MASS1: {
-        const int n1 = 2 * nh;
-        tensor_block_multi(s, W_HH, nullptr, elem0, off, n1, 0, 0, false, false, true, s.node, np1, s.node, np1, s.edge, p,
-                           s.edge, p);
-        tensor_block_multi(s, W_VV, nullptr, elem0, off, n1, nh, nh, false, false, true, s.edge, p, s.edge, p, s.node, np1,
-                           s.node, np1);
-        tensor_block_multi(s, W_HV, nullptr, elem0, off, n1, 0, nh, false, true, false, s.node, np1, s.edge, p, s.edge, p,
-                           s.node, np1);
-        break;
-    }
-    case DK_IPROD1: {
-        const double *fld = fields[dd.field];
-        const int ld = dd.transpose ? np1 * np1 : 2 * nh;
-        tensor_block_multi(s, W_P1H, fld, elem0, off, ld, 0, 0, dd.transpose, false, false, s.node, np1, s.node, np1, s.node,
-                           np1, s.edge, p);
-        tensor_block_multi(s, W_P1V, fld, elem0, off, ld, 0, nh, dd.transpose, false, false, s.node, np1, s.edge, p, s.node,
-                           np1, s.node, np1);
-        break;
-    }
-    case DK_IPROD2: {
-        const double *fld = fields[dd.field];
-        const int ld = dd.transpose ? 2 * nh : p * p;
-        tensor_block_multi(s, W_P2H, fld, elem0, off, ld, 0, 0, dd.transpose, false, false, s.node, np1, s.edge, p, s.edge, p,
-                           s.edge, p);
-        tensor_block_multi(s, W_P2V, fld, elem0, off, ld, nh, 0, dd.transpose, false, false, s.edge, p, s.edge, p, s.node, np1,
-                           s.edge, p);
-        break;
-    }
-    default:
-        break;
-    }
-    if (dd.inverse)
-        invert_spd_multi(s, off, dd.rows, bad);
-}
-
 // ---- emission ------------------------------------------------------------------------------------
-struct EmitCtx
+struct EmitTerm
 {
     const double *D; // dense matrix of the term in this slot
     int ld;
     double coef;
-    const int4 *lidx, *ridx; // incidence tables of the term (nullptr: none), already offset to the kind
-    const float4 *lsgn, *rsgn;
+    const DevIncRow *ltab, *rtab; // incidence rows of the term (nullptr: none)
 };
 
-// one block strip: rows [r0, r0 + nr) x 32 columns starting at c0; single-term blocks, NL x NR gathers
-template <int NL, int NR>
-__device__ __forceinline__ void emit_strip(const EmitCtx &t, int r0, int nr, int c, bool active, double *__restrict__ o, int N,
-                                           bool accumulate)
+__device__ __forceinline__ void load_inc(const DevIncRow *row, int (&idx)[4], double (&sgn)[4])
 {
-    int rc[NR];
-    double rs[NR];
+    const int4 iv = *reinterpret_cast<const int4 *>(row->idx);
+    const double2 s01 = *reinterpret_cast<const double2 *>(row->sgn);
+    const double2 s23 = *reinterpret_cast<const double2 *>(row->sgn + 2);
+    idx[0] = iv.x;
+    idx[1] = iv.y;
+    idx[2] = iv.z;
+    idx[3] = iv.w;
+    sgn[0] = s01.x;
+    sgn[1] = s01.y;
+    sgn[2] = s23.x;
+    sgn[3] = s23.y;
+}
+
+// one lane's share of a tile: column c, rows r0 + sub, r0 + sub + rstep, ... ; NL x NR gathers per entry
+template <int NL, int NR>
+__device__ __forceinline__ void emit_tile(const EmitTerm &t, int r0, int nr, int sub, int rstep, int c, bool active,
+                                          double *__restrict__ o, int N, bool accumulate)
+{
+    int rc[4];
+    double rs[4];
     if (NR == 1)
     {
         rc[0] = active ? c : 0;
@@ -381,45 +376,42 @@ __device__ __forceinline__ void emit_strip(const EmitCtx &t, int r0, int nr, int
     }
     else
     {
-        const int4 iv = active ? ld_ro(t.ridx + c) : make_int4(0, 0, 0, 0);
-        const float4 sv = active ? ld_ro(t.rsgn + c) : make_float4(0.f, 0.f, 0.f, 0.f);
-        const int ia[4] = {iv.x, iv.y, iv.z, iv.w};
-        const float sa[4] = {sv.x, sv.y, sv.z, sv.w};
+        load_inc(t.rtab + (active ? c : 0), rc, rs);
 #pragma unroll
         for (int b = 0; b < NR; ++b)
-        {
-            rc[b] = ia[b];
-            rs[b] = t.coef * (double)sa[b];
-        }
+            rs[b] *= t.coef;
     }
-    for (int r = 0; r < nr; ++r)
+    for (int r = sub; r < nr; r += rstep)
     {
-        int lr[NL];
-        double ls[NL];
+        double v = 0.0;
         if (NL == 1)
         {
-            lr[0] = (r0 + r) * t.ld;
-            ls[0] = 1.0;
+            const double *Dr = t.D + (r0 + r) * t.ld;
+#pragma unroll
+            for (int b = 0; b < NR; ++b)
+                v = fma(rs[b], Dr[rc[b]], v);
         }
         else
         {
-            const int4 iv = ld_ro(t.lidx + r0 + r);
-            const float4 sv = ld_ro(t.lsgn + r0 + r);
-            const int ia[4] = {iv.x, iv.y, iv.z, iv.w};
-            const float sa[4] = {sv.x, sv.y, sv.z, sv.w};
+            int li[4];
+            double ls[4];
+            load_inc(t.ltab + r0 + r, li, ls);
 #pragma unroll
             for (int a = 0; a < NL; ++a)
             {
-                lr[a] = ia[a] * t.ld;
-                ls[a] = (double)sa[a];
+                const double *Dr = t.D + li[a] * t.ld;
+                if (NR == 1)
+                    v = fma(ls[a], Dr[rc[0]], v);
+                else
+                {
+#pragma unroll
+                    for (int b = 0; b < NR; ++b)
+                        v = fma(ls[a] * rs[b], Dr[rc[b]], v);
+                }
             }
+            if (NR == 1)
+                v *= rs[0];
         }
-        double v = 0.0;
-#pragma unroll
-        for (int a = 0; a < NL; ++a)
-#pragma unroll
-            for (int b = 0; b < NR; ++b)
-                v = fma(NL == 1 ? rs[b] : ls[a] * rs[b], t.D[lr[a] + rc[b]], v);
         if (active)
         {
             if (accumulate)
@@ -435,162 +427,182 @@ __device__ __forceinline__ int inc_width(int kind) // non-zeros per row of E (le
     return kind < 0 ? 1 : ((kind == MFV2D_INC_10 || kind == MFV2D_INC_21_T) ? 2 : 4);
 }
 
-__global__ void __launch_bounds__(ASM_THREADS, 2) element_matrix_kernel(const AsmArgs args)
+__device__ __forceinline__ EmitTerm make_emit_term(const AsmArgs &args, const DevTerm &tm, const DevDense *dense,
+                                                   const DevIncRow *inc, const double *arena)
 {
-    MFV2D_DYN_SMEM(double, smem);
-    const int p = args.p, q = args.q, np1 = p + 1;
-    AsmShared s;
-    s.p = p;
-    s.q = q;
-    s.node = smem;
-    s.edge = s.node + np1 * q;
-    s.pnts = s.edge + p * q;
-    s.wgts = s.pnts + q;
-    int *pairs = reinterpret_cast<int *>(smem + ((args.tab_len + 1) & ~1));
-    const int n_pairs_n = np1 * (np1 + 1) / 2, n_pairs_e = p * (p + 1) / 2;
-    s.pairs_n = pairs;
-    s.pairs_e = pairs + n_pairs_n;
-    s.epb_shift = args.epb_shift;
-    s.epb = 1 << args.epb_shift;
-    s.cs = smem + args.slot_off - 8 * s.epb;
-    s.slot0 = smem + args.slot_off;
-    s.slot_stride = args.slot_stride;
-    s.sl = slot_layout(p, q);
-    __shared__ int bad[8];
+    const DevDense &dd = dense[tm.dense];
+    EmitTerm t;
+    t.D = arena + dd.smem_off;
+    t.ld = dd.ld;
+    t.coef = tm.coef;
+    t.ltab = tm.L >= 0 ? inc + args.lay.inc_row0[tm.L] : nullptr;
+    t.rtab = tm.R >= 0 ? inc + args.lay.inc_row0[tm.R ^ 2] : nullptr; // column c of E_R = row c of its transpose
+    return t;
+}
 
-    for (int i = threadIdx.x; i < args.tab_len; i += blockDim.x)
-        smem[i] = args.tab[i];
-    for (int n = threadIdx.x; n < np1 * np1; n += blockDim.x)
-    {
-        const int i = n / np1, k = n - i * np1;
-        if (i <= k)
-        {
-            // position of (i, k) in the row-wise enumeration of the upper triangle
-            pairs[i * np1 - i * (i - 1) / 2 + (k - i)] = (i << 8) | k;
-            if (k < p)
-                pairs[n_pairs_n + i * p - i * (i - 1) / 2 + (k - i)] = (i << 8) | k;
-        }
-    }
-
-    const DevStage *stages = reinterpret_cast<const DevStage *>(args.blob);
-    const DevDense *dense = reinterpret_cast<const DevDense *>(args.blob + args.off_dense);
-    const DevTerm *terms = reinterpret_cast<const DevTerm *>(args.blob + args.off_terms);
-    const DevBlock *blocks = reinterpret_cast<const DevBlock *>(args.blob + args.off_blocks);
-    const DevUnit *units = reinterpret_cast<const DevUnit *>(args.blob + args.off_units);
-    const int4 *inc_idx = reinterpret_cast<const int4 *>(args.inc_idx);
-    const float4 *inc_sgn = reinterpret_cast<const float4 *>(args.inc_sgn);
+__device__ __noinline__ void emit_stage(const AsmArgs &args, double *smem, const DevStage &sg, unsigned long long elem0,
+                                        int n_valid)
+{
+    const AsmLayout &L = args.lay;
+    const char *sb = reinterpret_cast<const char *>(smem);
+    const DevDense *dense = reinterpret_cast<const DevDense *>(sb + L.off_dense);
+    const DevTerm *terms = reinterpret_cast<const DevTerm *>(sb + L.off_terms);
+    const DevBlock *blocks = reinterpret_cast<const DevBlock *>(sb + L.off_blocks);
+    const DevUnit *units = reinterpret_cast<const DevUnit *>(sb + L.off_units);
+    const DevIncRow *inc = reinterpret_cast<const DevIncRow *>(sb + L.off_inc);
     const int warp = threadIdx.x >> 5, nwarps = MFV2D_NWARPS;
     const int N = args.n_total;
-    const unsigned long long n_groups = (args.n_elem + s.epb - 1) >> s.epb_shift;
-
-    for (unsigned long long grp = blockIdx.x; grp < n_groups; grp += gridDim.x)
+    const int n_units = sg.unit_end - sg.unit_begin;
+    const float inv_units = 1.0f / (float)n_units;
+    for (int w = warp; w < n_units * n_valid; w += nwarps)
     {
-        const unsigned long long elem0 = grp << s.epb_shift;
-        s.n_valid = (int)((args.n_elem - elem0) < (unsigned long long)s.epb ? (args.n_elem - elem0) : s.epb);
-        __syncthreads(); // the previous group's emission has finished reading shared memory
-        for (int i = threadIdx.x; i < 8 * s.n_valid; i += blockDim.x)
-            s.cs[i] = args.corners[elem0 * 8 + i];
-        for (int i = threadIdx.x; i < 8; i += blockDim.x)
-            bad[i] = 0;
-        __syncthreads();
-        phase_geometry(s);
-        for (int st = 0; st < args.n_stages; ++st)
+        const int e = fast_div(w, inv_units), u = w - e * n_units;
+        const DevUnit un = units[sg.unit_begin + u];
+        const DevBlock db = blocks[un.block];
+        const double *arena = smem + L.off_slots + (size_t)e * L.slot_stride + L.slot_arena;
+        double *const out = args.out + (elem0 + e) * args.out_stride + (size_t)(db.row0 + un.r0) * N + db.col0;
+        const int n_terms = db.term_end - db.term_begin;
+        const int rstep = 32 >> un.cl;
+        for (int lane = MFV2D_LANE0; lane < 32; lane += MFV2D_LANE_STEP)
         {
-            const DevStage sg = stages[st];
-            __syncthreads(); // geometry ready / previous stage's emission done
-            for (int d = sg.dense_begin; d < sg.dense_end; ++d)
-                compute_dense_multi(s, dense[d], args.fields, elem0, bad);
-            __syncthreads();
-            // emission: each warp takes (strip, slot) pairs; a strip is <= 16 rows x 32 columns of one block
-            const int n_units = sg.unit_end - sg.unit_begin;
-            for (int w = warp; w < (n_units << s.epb_shift); w += nwarps)
+            const int sub = lane >> un.cl;
+            const int c = un.c0 + (lane & ((1 << un.cl) - 1));
+            const bool active = c < db.ncols;
+            double *o = out + c;
+            if (n_terms == 0)
             {
-                const int e = w & (s.epb - 1);
-                if (e >= s.n_valid)
-                    continue;
-                const DevUnit un = units[sg.unit_begin + (w >> s.epb_shift)];
-                const DevBlock db = blocks[un.block];
-                const double *arena = slot_base(s, e) + s.sl.arena;
-                double *const out = args.out + (elem0 + e) * args.out_stride + (size_t)(db.row0 + un.r0) * N + db.col0;
-                const int n_terms = db.term_end - db.term_begin;
-                for (int lane = MFV2D_LANE0; lane < 32; lane += MFV2D_LANE_STEP)
+                if (active && !db.accumulate)
+                    for (int r = sub; r < un.nr; r += rstep)
+                        o[(size_t)r * N] = 0.0;
+                continue;
+            }
+            const DevTerm tm0 = terms[db.term_begin];
+            if (n_terms == 1 && tm0.dense >= 0)
+            {
+                const EmitTerm t = make_emit_term(args, tm0, dense, inc, arena);
+                const int nl = inc_width(tm0.L), nr_ = inc_width(tm0.R < 0 ? -1 : (tm0.R ^ 2));
+                const bool acc = db.accumulate;
+                switch (nl * 8 + nr_)
                 {
-                    const int c = un.c0 + lane;
-                    const bool active = c < db.ncols;
-                    double *o = out + c;
-                    if (n_terms == 0)
+                case 1 * 8 + 1:
+                    emit_tile<1, 1>(t, un.r0, un.nr, sub, rstep, c, active, o, N, acc);
+                    break;
+                case 1 * 8 + 2:
+                    emit_tile<1, 2>(t, un.r0, un.nr, sub, rstep, c, active, o, N, acc);
+                    break;
+                case 1 * 8 + 4:
+                    emit_tile<1, 4>(t, un.r0, un.nr, sub, rstep, c, active, o, N, acc);
+                    break;
+                case 2 * 8 + 1:
+                    emit_tile<2, 1>(t, un.r0, un.nr, sub, rstep, c, active, o, N, acc);
+                    break;
+                case 4 * 8 + 1:
+                    emit_tile<4, 1>(t, un.r0, un.nr, sub, rstep, c, active, o, N, acc);
+                    break;
+                default:
+                    emit_tile<4, 4>(t, un.r0, un.nr, sub, rstep, c, active, o, N, acc);
+                    break;
+                }
+                continue;
+            }
+            // several terms (or an identity): accumulate the terms of an entry in a register
+            for (int r = sub; r < un.nr; r += rstep)
+            {
+                double v = 0.0;
+                for (int ti = 0; ti < n_terms; ++ti)
+                {
+                    const DevTerm tm = terms[db.term_begin + ti];
+                    if (tm.dense < 0)
                     {
-                        if (active && !db.accumulate)
-                            for (int r = 0; r < un.nr; ++r)
-                                o[(size_t)r * N] = 0.0;
+                        v += (un.r0 + r == c) ? tm.coef : 0.0;
                         continue;
                     }
-                    for (int ti = 0; ti < n_terms; ++ti)
+                    const EmitTerm t = make_emit_term(args, tm, dense, inc, arena);
+                    int li[4] = {un.r0 + r, 0, 0, 0}, rc[4] = {active ? c : 0, 0, 0, 0};
+                    double ls[4] = {1.0, 0.0, 0.0, 0.0}, rs[4] = {1.0, 0.0, 0.0, 0.0};
+                    int nl = 1, nr_ = 1;
+                    if (t.ltab)
                     {
-                        const DevTerm tm = terms[db.term_begin + ti];
-                        const bool acc = db.accumulate || ti > 0;
-                        if (tm.dense < 0)
-                        {
-                            // coef * identity
-                            if (active)
-                                for (int r = 0; r < un.nr; ++r)
-                                {
-                                    const double v = (un.r0 + r == c) ? tm.coef : 0.0;
-                                    if (acc)
-                                        o[(size_t)r * N] += v;
-                                    else
-                                        o[(size_t)r * N] = v;
-                                }
-                            continue;
-                        }
-                        const DevDense dd = dense[tm.dense];
-                        EmitCtx t;
-                        t.D = arena + dd.smem_off;
-                        t.ld = dd.cols;
-                        t.coef = tm.coef;
-                        t.lidx = tm.L >= 0 ? inc_idx + args.inc_off[tm.L] : nullptr;
-                        t.lsgn = tm.L >= 0 ? inc_sgn + args.inc_off[tm.L] : nullptr;
-                        // column c of E_R = row c of its transpose
-                        t.ridx = tm.R >= 0 ? inc_idx + args.inc_off[tm.R ^ 2] : nullptr;
-                        t.rsgn = tm.R >= 0 ? inc_sgn + args.inc_off[tm.R ^ 2] : nullptr;
-                        const int nl = inc_width(tm.L), nr_ = inc_width(tm.R < 0 ? -1 : (tm.R ^ 2));
-                        switch (nl * 8 + nr_)
-                        {
-                        case 1 * 8 + 1:
-                            emit_strip<1, 1>(t, un.r0, un.nr, c, active, o, N, acc);
-                            break;
-                        case 1 * 8 + 2:
-                            emit_strip<1, 2>(t, un.r0, un.nr, c, active, o, N, acc);
-                            break;
-                        case 1 * 8 + 4:
-                            emit_strip<1, 4>(t, un.r0, un.nr, c, active, o, N, acc);
-                            break;
-                        case 2 * 8 + 1:
-                            emit_strip<2, 1>(t, un.r0, un.nr, c, active, o, N, acc);
-                            break;
-                        case 4 * 8 + 1:
-                            emit_strip<4, 1>(t, un.r0, un.nr, c, active, o, N, acc);
-                            break;
-                        case 2 * 8 + 2:
-                            emit_strip<2, 2>(t, un.r0, un.nr, c, active, o, N, acc);
-                            break;
-                        case 2 * 8 + 4:
-                            emit_strip<2, 4>(t, un.r0, un.nr, c, active, o, N, acc);
-                            break;
-                        case 4 * 8 + 2:
-                            emit_strip<4, 2>(t, un.r0, un.nr, c, active, o, N, acc);
-                            break;
-                        default:
-                            emit_strip<4, 4>(t, un.r0, un.nr, c, active, o, N, acc);
-                            break;
-                        }
+                        load_inc(t.ltab + un.r0 + r, li, ls);
+                        nl = 4;
                     }
+                    if (t.rtab)
+                    {
+                        load_inc(t.rtab + (active ? c : 0), rc, rs);
+                        nr_ = 4;
+                    }
+                    double s = 0.0;
+                    for (int a = 0; a < nl; ++a)
+                        for (int b = 0; b < nr_; ++b)
+                            s = fma(ls[a] * rs[b], t.D[li[a] * t.ld + rc[b]], s);
+                    v = fma(tm.coef, s, v);
+                }
+                if (active)
+                {
+                    if (db.accumulate)
+                        o[(size_t)r * N] += v;
+                    else
+                        o[(size_t)r * N] = v;
                 }
             }
         }
+    }
+}
+
+template <int Q> __global__ void __launch_bounds__(ASM_THREADS, 2) element_matrix_kernel(const AsmArgs args)
+{
+    MFV2D_DYN_SMEM(double, smem);
+    const AsmLayout &L = args.lay;
+    __shared__ int bad[8];
+    {
+        // descriptor blob -> shared memory, once per CTA
+        const double2 *src = reinterpret_cast<const double2 *>(args.blob);
+        double2 *dst = reinterpret_cast<double2 *>(smem);
+        for (int i = threadIdx.x; i < (L.blob_bytes >> 4); i += blockDim.x)
+            dst[i] = src[i];
+    }
+    const char *sb = reinterpret_cast<const char *>(smem);
+    const DevStage *stages = reinterpret_cast<const DevStage *>(sb + L.off_stages);
+    const DevDense *dense = reinterpret_cast<const DevDense *>(sb + L.off_dense);
+    const DevW *ws = reinterpret_cast<const DevW *>(sb + L.off_ws);
+    const DevTB *tbs = reinterpret_cast<const DevTB *>(sb + L.off_tbs);
+    const DevRound *rounds = reinterpret_cast<const DevRound *>(sb + L.off_rounds);
+    const double *tab = reinterpret_cast<const double *>(sb + L.off_tab);
+    const double *pnts = tab + (2 * args.p + 1) * Q, *wgts = pnts + Q;
+    const int epb = L.epb;
+    const unsigned long long n_groups = (args.n_elem + epb - 1) / epb;
+
+    for (unsigned long long grp = blockIdx.x; grp < n_groups; grp += gridDim.x)
+    {
+        const unsigned long long elem0 = grp * epb;
+        const int n_valid = (int)((args.n_elem - elem0) < (unsigned long long)epb ? (args.n_elem - elem0) : epb);
+        __syncthreads(); // blob in place / the previous pass has finished reading shared memory
+        for (int i = threadIdx.x; i < 8 * n_valid; i += blockDim.x)
+            smem[L.off_cs + i] = args.corners[elem0 * 8 + i];
+        for (int i = threadIdx.x; i < 8; i += blockDim.x)
+            bad[i] = 0;
+        for (int st = 0; st < L.n_stages; ++st)
+        {
+            const DevStage sg = stages[st];
+            __syncthreads(); // corners ready / previous stage's emission done
+            phase_weights<Q>(args, smem, sg, ws, pnts, wgts, elem0, n_valid);
+            for (int r = sg.round_begin; r < sg.round_end; ++r)
+            {
+                const DevRound rd = rounds[r];
+                __syncthreads();
+                phase_s1<Q>(args, smem, rd, tbs, n_valid);
+                __syncthreads();
+                phase_s2<Q>(args, smem, rd, tbs, n_valid);
+            }
+            for (int d = sg.dense_begin; d < sg.dense_end; ++d)
+                if (dense[d].inverse)
+                    invert_spd_slots(args, smem, dense[d].smem_off, dense[d].rows, dense[d].ld, n_valid, bad);
+            __syncthreads();
+            emit_stage(args, smem, sg, elem0, n_valid);
+        }
         __syncthreads();
         if (args.status)
-            for (int e = threadIdx.x; e < s.n_valid; e += blockDim.x)
+            for (int e = threadIdx.x; e < n_valid; e += blockDim.x)
                 args.status[elem0 + e] = bad[e] ? MFV2D_PIVOT_FAILED : MFV2D_SUCCESS;
     }
 }
@@ -657,22 +669,25 @@ static int geometry_batch(const mfv2d_elements *e, double *out, int space, int c
     return r;
 }
 
-// the dense arena one element needs (maximum over the stages), in doubles
-static int plan_arena_doubles(const mfv2d_plan *plan)
+// launch of the fused matrix kernel for a lowered plan; all pointers are device pointers
+template <int Q> static int launch_q(mfv2d_ctx *ctx, const AsmArgs &a, size_t n_elem)
 {
-    int max_arena = 0;
-    for (const DevStage &sg : plan->stages)
-        for (int d = sg.dense_begin; d < sg.dense_end; ++d)
-        {
-            const DevDense &dd = plan->dense[d];
-            const int end = dd.smem_off + ((dd.rows * dd.cols + 1) & ~1);
-            if (end > max_arena)
-                max_arena = end;
-        }
-    return max_arena;
+    const size_t smem = (size_t)a.lay.smem_bytes;
+    MFV2D_CUDA_CHECK(ctx, cudaFuncSetAttribute(element_matrix_kernel<Q>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int per_sm = 1;
+    MFV2D_CUDA_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, element_matrix_kernel<Q>, ASM_THREADS, smem));
+    if (per_sm < 1)
+        per_sm = 1;
+    const unsigned long long n_groups = (n_elem + a.lay.epb - 1) / a.lay.epb;
+    unsigned long long grid = (unsigned long long)ctx->sm_count * per_sm;
+    if (grid > n_groups)
+        grid = n_groups;
+    MFV2D_LAUNCH(element_matrix_kernel<Q>, (unsigned)grid, ASM_THREADS, smem, ctx->stream, a);
+    ctx->launches++;
+    MFV2D_CUDA_CHECK(ctx, cudaGetLastError());
+    return MFV2D_SUCCESS;
 }
 
-// launch of the fused matrix kernel for a lowered plan; all pointers are device pointers
 int launch_element_matrix(const mfv2d_plan *plan, const mfv2d_elements *e, const double *const *fields, double *d_out,
                           int32_t *d_status)
 {
@@ -680,59 +695,43 @@ int launch_element_matrix(const mfv2d_plan *plan, const mfv2d_elements *e, const
     if (e->n == 0)
         return MFV2D_SUCCESS;
     AsmArgs a{};
-    a.tab = plan->basis->d_tab;
-    a.inc_idx = plan->basis->d_inc_idx;
-    a.inc_sgn = plan->basis->d_inc_sgn;
-    a.corners = e->d_corners;
     a.blob = (const char *)plan->d_blob;
+    a.corners = e->d_corners;
     for (int i = 0; i < 16; ++i)
         a.fields[i] = (fields && i < plan->n_fields) ? fields[i] : nullptr;
     a.out = d_out;
     a.status = d_status;
     a.n_elem = e->n;
-    a.tab_len = plan->basis->tab_len;
     a.p = plan->p;
     a.q = plan->q;
-    for (int i = 0; i < 4; ++i)
-        a.inc_off[i] = plan->basis->inc_off[i];
-    a.n_stages = (int)plan->stages.size();
-    a.off_dense = plan->off_dense;
-    a.off_terms = plan->off_terms;
-    a.off_blocks = plan->off_blocks;
-    a.off_units = plan->off_units;
     a.n_total = plan->out_ld ? plan->out_ld : plan->n_total;
     a.out_stride = plan->out_stride ? plan->out_stride : (unsigned long long)plan->n_total * plan->n_total;
-    // slot size; the stride is padded to 4 (mod 16) doubles so that the slots of a pass sit in distinct banks
-    const SlotLayout sl = slot_layout(plan->p, plan->q);
-    int slot = sl.arena + plan_arena_doubles(plan);
-    slot = ((slot + 15) & ~15) + 4;
-    a.slot_stride = slot;
-    // elements per pass: as many as keep two CTAs per SM resident (<= ~110 KB each), at most 8
-    const size_t budget = (size_t)110 * 1024 / sizeof(double);
-    int shift = 0;
-    while (shift < 3 && (size_t)asm_fixed_doubles(plan->p, a.tab_len, 2 << shift) + (size_t)(2 << shift) * slot <= budget &&
-           (size_t)(2 << shift) <= e->n)
-        ++shift;
-    a.epb_shift = shift;
-    const int epb = 1 << shift;
-    a.slot_off = asm_fixed_doubles(plan->p, a.tab_len, epb);
-    const size_t smem = ((size_t)a.slot_off + (size_t)epb * slot + 8) * sizeof(double);
-    if (smem > ctx->smem_optin)
-        return mfv2d_fail(ctx, MFV2D_CUDA_UNSUPPORTED, "element matrices of order %d need %zu bytes of shared memory", plan->p,
-                          smem);
-    MFV2D_CUDA_CHECK(ctx, cudaFuncSetAttribute(element_matrix_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int per_sm = 1;
-    MFV2D_CUDA_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, element_matrix_kernel, ASM_THREADS, smem));
-    if (per_sm < 1)
-        per_sm = 1;
-    const unsigned long long n_groups = (e->n + epb - 1) / epb;
-    unsigned long long grid = (unsigned long long)ctx->sm_count * per_sm;
-    if (grid > n_groups)
-        grid = n_groups;
-    MFV2D_LAUNCH(element_matrix_kernel, (unsigned)grid, ASM_THREADS, smem, ctx->stream, a);
-    ctx->launches++;
-    MFV2D_CUDA_CHECK(ctx, cudaGetLastError());
-    return MFV2D_SUCCESS;
+    a.lay = plan->lay;
+    switch (plan->q)
+    {
+#define MFV2D_Q_CASE(Q)                                                                                        \
+    case Q:                                                                                                    \
+        return launch_q<Q>(ctx, a, e->n);
+        MFV2D_Q_CASE(2)
+        MFV2D_Q_CASE(3)
+        MFV2D_Q_CASE(4)
+        MFV2D_Q_CASE(5)
+        MFV2D_Q_CASE(6)
+        MFV2D_Q_CASE(7)
+        MFV2D_Q_CASE(8)
+        MFV2D_Q_CASE(9)
+        MFV2D_Q_CASE(10)
+        MFV2D_Q_CASE(11)
+        MFV2D_Q_CASE(12)
+        MFV2D_Q_CASE(13)
+        MFV2D_Q_CASE(14)
+        MFV2D_Q_CASE(15)
+        MFV2D_Q_CASE(16)
+#undef MFV2D_Q_CASE
+    default:
+        return mfv2d_fail(ctx, MFV2D_CUDA_UNSUPPORTED, "element matrices with %d quadrature points per direction (supported: 2..16)",
+                          plan->q);
+    }
 }
 
 extern "C" {

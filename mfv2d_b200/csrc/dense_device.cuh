@@ -71,20 +71,7 @@ __device__ __forceinline__ void tm_stage2(double *__restrict__ dst, int ld, int 
     }
 }
 
-// weight fields at the quadrature points (geo = j00, j01, j10, j11, det each q*q)
-enum
-{
-    W_M0,
-    W_M2,
-    W_HH,
-    W_VV,
-    W_HV,
-    W_P1H,
-    W_P1V,
-    W_P2H,
-    W_P2V
-};
-
+// weight fields at the quadrature points (geo = j00, j01, j10, j11, det each q*q); kinds W_* are in plan.cuh
 __device__ __forceinline__ void fill_weight(double *__restrict__ G, const double *__restrict__ geo, const double *__restrict__ wg,
                                             int q, int kind, const double *__restrict__ fld)
 {

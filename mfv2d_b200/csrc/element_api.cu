@@ -192,32 +192,12 @@ static int make_dense_plan(mfv2d_ctx *ctx, const mfv2d_basis *basis, int dk, int
     plan->field_form.assign(n_fields, -1);
     plan->mat_blocks.resize(1);
     plan->vec_blocks.resize(1);
-    // hand-lowered (plan_lower_matrix assumes square systems)
+    // one block, one term: the dense matrix itself (coef 1, no incidences), possibly rectangular
     plan->matrix_fused = true;
-    DevDense dd{dk, inverse, d.field, transpose, d.rows, d.cols, 0};
-    plan->dense.push_back(dd);
-    plan->terms.push_back(DevTerm{1.0, 0, -1, -1});
-    plan->blocks.push_back(DevBlock{0, 0, d.rows, d.cols, 0, 1, 0});
-    for (int c0 = 0; c0 < d.cols; c0 += 32)
-        for (int r0 = 0; r0 < d.rows; r0 += 8)
-            plan->units.push_back(DevUnit{0, (short)c0, (short)r0, (short)((d.rows - r0) < 8 ? (d.rows - r0) : 8)});
-    plan->stages.push_back(DevStage{0, 1, 0, 1, 0, (int)plan->units.size()});
-    std::vector<char> blob;
-    auto append = [&](const void *ptr, size_t bytes) {
-        size_t off = (blob.size() + 15) & ~size_t(15);
-        blob.resize(off + bytes);
-        memcpy(blob.data() + off, ptr, bytes);
-        return (int)off;
-    };
-    append(plan->stages.data(), plan->stages.size() * sizeof(DevStage));
-    plan->off_dense = append(plan->dense.data(), plan->dense.size() * sizeof(DevDense));
-    plan->off_terms = append(plan->terms.data(), plan->terms.size() * sizeof(DevTerm));
-    plan->off_blocks = append(plan->blocks.data(), plan->blocks.size() * sizeof(DevBlock));
-    plan->off_units = append(plan->units.data(), plan->units.size() * sizeof(DevUnit));
-    plan->blob_bytes = blob.size();
-    int r = mfv2d_cuda_malloc(ctx, blob.size(), &plan->d_blob);
-    if (!r)
-        r = mfv2d_cuda_upload(ctx, plan->d_blob, blob.data(), blob.size());
+    std::vector<std::vector<LoweredTerm>> lowered(1);
+    lowered[0].push_back(LoweredTerm{1.0, -1, -1, d, false});
+    const std::vector<int> roff{0, d.rows}, coff{0, d.cols};
+    const int r = plan_finalize_matrix(plan, lowered, 1, 1, roff, coff);
     if (r)
     {
         mfv2d_cuda_plan_destroy(plan);

@@ -355,22 +355,10 @@ int run_block(const Sym &s, const mfv2d_op_t *ops, int n_ops, int form_row, int 
 // ---- lowering of the matrix-mode programs to the fused assembly kernel --------------------------
 int plan_lower_matrix(mfv2d_plan *plan)
 {
-    const int p = plan->p, q = plan->q, nf = plan->n_forms;
+    const int nf = plan->n_forms;
     plan->matrix_fused = true;
-    plan->dense.clear();
-    plan->terms.clear();
-    plan->blocks.clear();
-    plan->units.clear();
-    plan->stages.clear();
-
-    struct LTerm
-    {
-        double coef;
-        int L, R;
-        Factor d;
-        bool identity;
-    };
-    std::vector<std::vector<LTerm>> lowered(nf * nf);
+    std::vector<std::vector<LoweredTerm>> lowered(nf * nf);
+    std::vector<char> present(nf * nf, 0);
     for (int b = 0; b < nf * nf; ++b)
     {
         const BlockProgram &bp = plan->mat_blocks[b];
@@ -378,13 +366,13 @@ int plan_lower_matrix(mfv2d_plan *plan)
             continue;
         if (bp.identity)
         {
-            LTerm lt{bp.identity_coef, -1, -1, Factor{}, true};
+            LoweredTerm lt{bp.identity_coef, -1, -1, Factor{}, true};
             lowered[b].push_back(lt);
             continue;
         }
         for (const Term &t : bp.terms)
         {
-            LTerm lt{t.coef, -1, -1, Factor{}, false};
+            LoweredTerm lt{t.coef, -1, -1, Factor{}, false};
             size_t i = 0;
             if (i < t.f.size() && !t.f[i].is_dense)
                 lt.R = t.f[i++].inc_kind;
@@ -405,11 +393,145 @@ int plan_lower_matrix(mfv2d_plan *plan)
             lowered[b].push_back(lt);
         }
     }
+    return plan_finalize_matrix(plan, lowered, nf, nf, plan->form_offsets, plan->form_offsets);
+}
 
-    // fixed shared memory: tables, geometry (5 q^2), weight field G (q^2), T scratch (q * (p+1)^2, padded)
-    const int fixed = asm_fixed_doubles(p, plan->basis->tab_len, 1) + slot_layout(p, q).arena;
-    const int capacity = (int)(plan->ctx->smem_optin / sizeof(double)) - fixed - 64;
+namespace
+{
+struct TBSpec
+{
+    int wkind, pkA, pkB, r0, c0, mirror;
+};
 
+// the tensor blocks of one dense matrix kind
+int dense_tensor_blocks(int dk, int p, TBSpec out[3])
+{
+    const int nh = p * (p + 1);
+    switch (dk)
+    {
+    case DK_MASS0:
+        out[0] = {W_M0, PK_NN, PK_NN, 0, 0, 0};
+        return 1;
+    case DK_MASS2:
+        out[0] = {W_M2, PK_EE, PK_EE, 0, 0, 0};
+        return 1;
+    case DK_MASS1: // hh: (node_eta i, edge_xi j); vv: (edge_eta i, node_xi j); hv and its mirror image
+        out[0] = {W_HH, PK_NN, PK_EE, 0, 0, 0};
+        out[1] = {W_VV, PK_EE, PK_NN, nh, nh, 0};
+        out[2] = {W_HV, PK_NE, PK_EN, 0, nh, 1};
+        return 3;
+    case DK_IPROD1: // (n0 x n1): rows (node_eta, node_xi); cols h (node_eta, edge_xi), v (edge_eta, node_xi)
+        out[0] = {W_P1H, PK_NN, PK_NE, 0, 0, 0};
+        out[1] = {W_P1V, PK_NE, PK_NN, 0, nh, 0};
+        return 2;
+    case DK_IPROD2: // (n1 x n2): rows h (node_eta, edge_xi), v (edge_eta, node_xi); cols (edge_eta, edge_xi)
+        out[0] = {W_P2H, PK_NE, PK_EE, 0, 0, 0};
+        out[1] = {W_P2V, PK_EE, PK_NE, nh, 0, 0};
+        return 2;
+    default:
+        return 0;
+    }
+}
+
+inline int pk_first(int pk, int p) { return (pk == PK_NN || pk == PK_NE) ? p + 1 : p; }
+inline int pk_second(int pk, int p) { return (pk == PK_NN || pk == PK_EN) ? p + 1 : p; }
+inline int pk_pairs(int pk, int p)
+{
+    const int n = p + 1;
+    switch (pk)
+    {
+    case PK_NN:
+        return n * (n + 1) / 2;
+    case PK_EE:
+        return p * (p + 1) / 2;
+    default:
+        return n * p;
+    }
+}
+} // namespace
+
+int plan_finalize_matrix(mfv2d_plan *plan, const std::vector<std::vector<LoweredTerm>> &lowered, int nrf, int ncf,
+                         const std::vector<int> &roff, const std::vector<int> &coff)
+{
+    mfv2d_ctx *ctx = plan->ctx;
+    const int p = plan->p, q = plan->q, np1 = p + 1;
+    const int ldq = asm_ldq(q);
+    const int threads = 256;
+
+    // ---- element-independent tables of the blob --------------------------------------------------
+    const mfv2d_basis *bs = plan->basis;
+    std::vector<DevIncRow> inc_rows(bs->inc_off[4]);
+    for (int r = 0; r < bs->inc_off[4]; ++r)
+        for (int t = 0; t < 4; ++t)
+        {
+            const int32_t v = bs->h_inc[(size_t)r * 4 + t];
+            inc_rows[r].idx[t] = v == 0 ? 0 : (v > 0 ? v - 1 : -v - 1);
+            inc_rows[r].sgn[t] = v == 0 ? 0.0 : (v > 0 ? 1.0 : -1.0);
+        }
+    std::vector<int32_t> pairs;
+    int pair_off[4], pair_n[4];
+    for (int pk = 0; pk < 4; ++pk)
+    {
+        pair_off[pk] = (int)pairs.size();
+        const int n1 = pk_first(pk, p), n2 = pk_second(pk, p);
+        int row = 0;
+        for (int i = 0; i < n1; ++i)
+            for (int k = 0; k < n2; ++k)
+            {
+                if ((pk == PK_NN || pk == PK_EE) && k < i)
+                    continue;
+                const int prow = pk == PK_EN ? k * p + i : row; // E_i N_k = row (k, i) of the NE table
+                pairs.push_back(i | (k << 8) | (prow << 16));
+                ++row;
+            }
+        pair_n[pk] = (int)pairs.size() - pair_off[pk];
+    }
+    std::vector<double> pt[3];
+    {
+        const double *node = bs->node.data(), *edge = bs->edge.data();
+        for (int pk = 0; pk < 3; ++pk)
+        {
+            const double *t1 = (pk == PK_EE) ? edge : node, *t2 = (pk == PK_NN) ? node : edge;
+            const int n1 = pk_first(pk, p), n2 = pk_second(pk, p);
+            for (int i = 0; i < n1; ++i)
+                for (int k = 0; k < n2; ++k)
+                {
+                    if (pk != PK_NE && k < i)
+                        continue;
+                    for (int a = 0; a < ldq; ++a)
+                        pt[pk].push_back(a < q ? t1[i * q + a] * t2[k * q + a] : 0.0);
+                }
+        }
+    }
+    std::vector<double> tab;
+    tab.insert(tab.end(), bs->node.begin(), bs->node.end());
+    tab.insert(tab.end(), bs->edge.begin(), bs->edge.end());
+    tab.insert(tab.end(), bs->pnts.begin(), bs->pnts.end());
+    tab.insert(tab.end(), bs->wgts.begin(), bs->wgts.end());
+    const size_t table_bytes = inc_rows.size() * sizeof(DevIncRow) + pairs.size() * 4 +
+                               (pt[0].size() + pt[1].size() + pt[2].size() + tab.size()) * 8 + 256;
+
+    // ---- stages: greedy packing of the dense matrices under a per-slot capacity -------------------
+    struct DenseNeed
+    {
+        int arena, t_sum, t_max;
+    };
+    auto dense_need = [&](const Factor &d, int *ld_out) {
+        const int ld = d.cols | 1;
+        TBSpec sp[3];
+        const int n = dense_tensor_blocks(d.dk, p, sp);
+        DenseNeed nd{(d.rows * ld + 1) & ~1, 0, 0};
+        for (int i = 0; i < n; ++i)
+        {
+            const int t = pk_first(sp[i].pkB, p) * pk_second(sp[i].pkB, p) * ldq;
+            nd.t_sum += t;
+            nd.t_max = t > nd.t_max ? t : nd.t_max;
+        }
+        if (d.inverse && nd.t_max < 2 * d.rows)
+            nd.t_sum = nd.t_max = 2 * d.rows; // scratch of the in-place inverse
+        *ld_out = ld;
+        return nd;
+    };
     auto find_dense = [&](std::vector<DevDense> &list, int begin, const Factor &d) {
         for (int i = begin; i < (int)list.size(); ++i)
             if (list[i].dk == d.dk && list[i].inverse == d.inverse && list[i].field == d.field &&
@@ -417,119 +539,349 @@ int plan_lower_matrix(mfv2d_plan *plan)
                 return i;
         return -1;
     };
+    const int wq = q * ldq; // doubles of one weight field
 
-    DevStage stage{};
-    stage.dense_begin = 0;
-    stage.block_begin = 0;
-    stage.unit_begin = 0;
-    int arena = 0, max_arena = 0;
-    std::vector<char> started(nf * nf, 0); // block already written in an earlier stage -> accumulate
+    // descriptor bytes are not known before the stages are; 6 KB covers every system the planner accepts
+    const size_t fixed_bytes = table_bytes + 6144;
+    const long long cap_max = ((long long)ctx->smem_optin - (long long)fixed_bytes - 8 * 64) / 8;
+    const long long cap_pref = (((long long)228 * 1024 - 2 * 1024) / 2 - (long long)fixed_bytes - 8 * 64) / 8;
 
-    auto close_stage = [&]() {
-        stage.dense_end = (int)plan->dense.size();
-        stage.block_end = (int)plan->blocks.size();
-        // units of this stage
-        for (int bi = stage.block_begin; bi < stage.block_end; ++bi)
+    auto build = [&](long long capacity, bool serial_rounds) -> int {
+        plan->dense.clear();
+        plan->terms.clear();
+        plan->blocks.clear();
+        plan->units.clear();
+        plan->stages.clear();
+        plan->ws.clear();
+        plan->tbs.clear();
+        plan->rounds.clear();
+        DevStage stage{};
+        int arena = 0, tsum = 0, tmax = 0;
+        std::vector<char> started(nrf * ncf, 0);
+        auto stage_slot = [&](int ar, int ts, int tm, int nw) { return (long long)nw * wq + (serial_rounds ? tm : ts) + ar; };
+        auto close_stage = [&]() {
+            stage.dense_end = (int)plan->dense.size();
+            stage.block_end = (int)plan->blocks.size();
+            stage.w_end = (int)plan->ws.size();
+            plan->stages.push_back(stage);
+            stage = DevStage{};
+            stage.dense_begin = (int)plan->dense.size();
+            stage.block_begin = (int)plan->blocks.size();
+            stage.w_begin = (int)plan->ws.size();
+            arena = tsum = tmax = 0;
+        };
+        for (int r = 0; r < nrf; ++r)
+            for (int c = 0; c < ncf; ++c)
+            {
+                const int b = r * ncf + c;
+                const std::vector<LoweredTerm> &lts = lowered[b];
+                size_t done = 0;
+                bool first = true;
+                while (first || done < lts.size())
+                {
+                    first = false;
+                    DevBlock db{};
+                    db.row0 = roff[r];
+                    db.col0 = coff[c];
+                    db.nrows = roff[r + 1] - db.row0;
+                    db.ncols = coff[c + 1] - db.col0;
+                    db.term_begin = (int)plan->terms.size();
+                    db.accumulate = started[b];
+                    size_t added = 0;
+                    for (; done < lts.size(); ++done, ++added)
+                    {
+                        const LoweredTerm &lt = lts[done];
+                        int di = -1;
+                        if (!lt.identity)
+                        {
+                            di = find_dense(plan->dense, stage.dense_begin, lt.d);
+                            if (di < 0)
+                            {
+                                int ld = 0;
+                                const DenseNeed nd = dense_need(lt.d, &ld);
+                                // weights this matrix adds to the stage
+                                TBSpec sp[3];
+                                const int ntb = dense_tensor_blocks(lt.d.dk, p, sp);
+                                int new_w = 0;
+                                for (int i = 0; i < ntb; ++i)
+                                {
+                                    bool have = false;
+                                    for (int w = stage.w_begin; w < (int)plan->ws.size(); ++w)
+                                        have |= plan->ws[w].kind == sp[i].wkind && plan->ws[w].field == lt.d.field;
+                                    new_w += have ? 0 : 1;
+                                }
+                                const int nw_now = (int)plan->ws.size() - stage.w_begin;
+                                const int tm = nd.t_max > tmax ? nd.t_max : tmax;
+                                if (stage_slot(nd.arena, nd.t_sum, nd.t_max, new_w) > capacity)
+                                    return MFV2D_CUDA_UNSUPPORTED;
+                                if (stage_slot(arena + nd.arena, tsum + nd.t_sum, tm, nw_now + new_w) > capacity)
+                                    break; // start a new stage
+                                DevDense dd{lt.d.dk, lt.d.inverse, lt.d.field, lt.d.transpose, lt.d.rows, lt.d.cols, arena, ld};
+                                for (int i = 0; i < ntb; ++i)
+                                {
+                                    int w = -1;
+                                    for (int k = stage.w_begin; k < (int)plan->ws.size(); ++k)
+                                        if (plan->ws[k].kind == sp[i].wkind && plan->ws[k].field == lt.d.field)
+                                            w = k - stage.w_begin;
+                                    if (w < 0)
+                                    {
+                                        plan->ws.push_back(DevW{sp[i].wkind, lt.d.field});
+                                        w = (int)plan->ws.size() - 1 - stage.w_begin;
+                                    }
+                                    DevTB tb{};
+                                    tb.w = w;
+                                    tb.pkA = sp[i].pkA;
+                                    tb.pkB = sp[i].pkB;
+                                    tb.nA = pk_first(tb.pkA, p);
+                                    tb.nA2 = pk_second(tb.pkA, p);
+                                    tb.nB = pk_first(tb.pkB, p);
+                                    tb.nB2 = pk_second(tb.pkB, p);
+                                    tb.dst_off = arena;
+                                    tb.ld = ld;
+                                    tb.r0 = sp[i].r0;
+                                    tb.c0 = sp[i].c0;
+                                    tb.trans = lt.d.transpose;
+                                    tb.mirror = sp[i].mirror;
+                                    tb.round = (int)plan->stages.size(); // stage index for now
+                                    plan->tbs.push_back(tb);
+                                }
+                                arena += nd.arena;
+                                tsum += nd.t_sum;
+                                tmax = tm;
+                                plan->dense.push_back(dd);
+                                di = (int)plan->dense.size() - 1;
+                            }
+                        }
+                        plan->terms.push_back(DevTerm{lt.coef, di, lt.L, lt.R});
+                    }
+                    db.term_end = (int)plan->terms.size();
+                    if (added > 0 || lts.empty())
+                    {
+                        plan->blocks.push_back(db);
+                        started[b] = 1;
+                    }
+                    if (done < lts.size())
+                        close_stage();
+                    if (lts.empty())
+                        break;
+                }
+            }
+        close_stage();
+        return MFV2D_SUCCESS;
+    };
+
+    bool serial = false;
+    long long cap_used = cap_pref;
+    int res = cap_pref > 0 ? build(cap_pref, false) : MFV2D_CUDA_UNSUPPORTED;
+    if (res != MFV2D_SUCCESS)
+    {
+        cap_used = cap_max;
+        res = build(cap_max, false);
+    }
+    if (res != MFV2D_SUCCESS)
+    {
+        serial = true;
+        res = build(cap_max, true);
+    }
+    if (res != MFV2D_SUCCESS)
+        return mfv2d_fail(ctx, MFV2D_CUDA_UNSUPPORTED,
+                          "an element matrix of order %d with %d quadrature points does not fit into shared memory", p, q);
+
+    // ---- emission units -----------------------------------------------------------------------------
+    for (DevStage &sg : plan->stages)
+    {
+        sg.unit_begin = (int)plan->units.size();
+        for (int bi = sg.block_begin; bi < sg.block_end; ++bi)
         {
             const DevBlock &db = plan->blocks[bi];
-            const int RG = 16; // rows per emission strip (ASM_ROWS_PER_UNIT)
-            for (int c0 = 0; c0 < db.ncols; c0 += 32)
-                for (int r0 = 0; r0 < db.nrows; r0 += RG)
+            // tile width: the widest of 32 / 16 / 8 lanes unless a narrower one wastes > 10 % fewer lanes
+            int cl = 5;
+            double best = (double)((db.ncols + 31) / 32 * 32) / db.ncols;
+            for (int c = 4; c >= 3; --c)
+            {
+                const int w = 1 << c;
+                const double waste = (double)((db.ncols + w - 1) / w * w) / db.ncols;
+                if (waste < best - 0.10)
                 {
-                    DevUnit u;
+                    best = waste;
+                    cl = c;
+                }
+            }
+            const int w = 1 << cl, rows_per_store = 32 >> cl;
+            const int rg = 8 * rows_per_store; // 8 warp stores per unit
+            for (int c0 = 0; c0 < db.ncols; c0 += w)
+                for (int r0 = 0; r0 < db.nrows; r0 += rg)
+                {
+                    DevUnit u{};
                     u.block = (short)bi;
                     u.c0 = (short)c0;
                     u.r0 = (short)r0;
-                    u.nr = (short)((db.nrows - r0) < RG ? (db.nrows - r0) : RG);
+                    u.nr = (short)((db.nrows - r0) < rg ? (db.nrows - r0) : rg);
+                    u.cl = (short)cl;
                     plan->units.push_back(u);
                 }
         }
-        stage.unit_end = (int)plan->units.size();
-        plan->stages.push_back(stage);
-        if (arena > max_arena)
-            max_arena = arena;
-        stage = DevStage{};
-        stage.dense_begin = (int)plan->dense.size();
-        stage.block_begin = (int)plan->blocks.size();
-        stage.unit_begin = (int)plan->units.size();
-        arena = 0;
-    };
+        sg.unit_end = (int)plan->units.size();
+    }
 
-    for (int r = 0; r < nf; ++r)
-        for (int c = 0; c < nf; ++c)
+    // ---- slot layout and elements per pass ---------------------------------------------------------
+    AsmLayout &L = plan->lay;
+    L = AsmLayout{};
+    L.ldq = ldq;
+    int slot_w = 0, slot_t = 0, slot_a = 0;
+    {
+        size_t tb_i = 0;
+        for (size_t si = 0; si < plan->stages.size(); ++si)
         {
-            const int b = r * nf + c;
-            const std::vector<LTerm> &lts = lowered[b];
-            size_t done = 0;
-            bool first = true;
-            while (first || done < lts.size())
+            const DevStage &sg = plan->stages[si];
+            const int nw = sg.w_end - sg.w_begin;
+            slot_w = nw * wq > slot_w ? nw * wq : slot_w;
+            int ar = 0, ts = 0, tm = 0;
+            for (int d = sg.dense_begin; d < sg.dense_end; ++d)
             {
-                first = false;
-                DevBlock db{};
-                db.row0 = plan->form_offsets[r];
-                db.col0 = plan->form_offsets[c];
-                db.nrows = plan->form_offsets[r + 1] - db.row0;
-                db.ncols = plan->form_offsets[c + 1] - db.col0;
-                db.term_begin = (int)plan->terms.size();
-                db.accumulate = started[b];
-                // add as many terms of the block as fit into the current stage
-                size_t added = 0;
-                for (; done < lts.size(); ++done, ++added)
-                {
-                    const LTerm &lt = lts[done];
-                    int di = -1;
-                    if (!lt.identity)
-                    {
-                        di = find_dense(plan->dense, stage.dense_begin, lt.d);
-                        if (di < 0)
-                        {
-                            const int need = ((lt.d.rows * lt.d.cols) + 1) & ~1;
-                            if (need > capacity)
-                                return mfv2d_fail(plan->ctx, MFV2D_CUDA_UNSUPPORTED,
-                                                  "a %d x %d element matrix does not fit into shared memory (order %d)",
-                                                  lt.d.rows, lt.d.cols, p);
-                            if (arena + need > capacity)
-                                break; // start a new stage
-                            DevDense dd{lt.d.dk, lt.d.inverse, lt.d.field, lt.d.transpose, lt.d.rows, lt.d.cols, arena};
-                            arena += need;
-                            plan->dense.push_back(dd);
-                            di = (int)plan->dense.size() - 1;
-                        }
-                    }
-                    DevTerm dt{lt.coef, di, lt.L, lt.R};
-                    plan->terms.push_back(dt);
-                }
-                db.term_end = (int)plan->terms.size();
-                if (added > 0 || lts.empty())
-                {
-                    plan->blocks.push_back(db);
-                    started[b] = 1;
-                }
-                if (done < lts.size())
-                    close_stage();
-                if (lts.empty())
-                    break;
+                const DevDense &dd = plan->dense[d];
+                const int end = dd.smem_off + ((dd.rows * dd.ld + 1) & ~1);
+                ar = end > ar ? end : ar;
+                if (dd.inverse)
+                    tm = 2 * dd.rows > tm ? 2 * dd.rows : tm;
             }
+            for (; tb_i < plan->tbs.size() && plan->tbs[tb_i].round == (int)si; ++tb_i)
+            {
+                const int t = plan->tbs[tb_i].nB * plan->tbs[tb_i].nB2 * ldq;
+                ts += t;
+                tm = t > tm ? t : tm;
+            }
+            const int tt = serial ? tm : (ts > tm ? ts : tm);
+            slot_t = tt > slot_t ? tt : slot_t;
+            slot_a = ar > slot_a ? ar : slot_a;
         }
-    close_stage();
-    plan->smem_doubles = fixed + max_arena;
+    }
+    L.slot_w = 0;
+    L.slot_t = (slot_w + 1) & ~1;
+    L.slot_arena = L.slot_t + ((slot_t + 1) & ~1);
+    int slot = L.slot_arena + slot_a + 2;
+    slot = ((slot + 15) & ~15) + 4; // slot stride = 4 (mod 16) doubles: the slots of a pass sit in distinct banks
+    L.slot_stride = slot;
+    {
+        // exact size of the blob (descriptors + tables), rounded section by section as `append` does
+        size_t desc = 0;
+        auto sec = [&](size_t bytes) { desc = ((desc + 15) & ~size_t(15)) + bytes; };
+        sec(plan->stages.size() * sizeof(DevStage));
+        sec(plan->dense.size() * sizeof(DevDense));
+        sec(plan->terms.size() * sizeof(DevTerm));
+        sec(plan->blocks.size() * sizeof(DevBlock));
+        sec(plan->units.size() * sizeof(DevUnit));
+        sec(plan->ws.size() * sizeof(DevW));
+        sec(plan->tbs.size() * sizeof(DevTB));
+        sec(plan->tbs.size() * sizeof(DevRound));
+        const long long fixed_exact = (long long)desc + (long long)table_bytes + 8 * 64 + 256;
+        long long per_cta = (cap_used == cap_pref ? ((long long)228 * 1024 - 2 * 1024) / 2 : (long long)ctx->smem_optin);
+        long long epb = (per_cta - fixed_exact) / 8 / slot;
+        if (epb < 1)
+        {
+            per_cta = (long long)ctx->smem_optin;
+            epb = (per_cta - fixed_exact) / 8 / slot;
+        }
+        if (epb < 1)
+            return mfv2d_fail(ctx, MFV2D_CUDA_UNSUPPORTED,
+                              "an element matrix of order %d with %d quadrature points does not fit into shared memory", p, q);
+        if (epb > 8)
+            epb = 8;
+        L.epb = (int)epb;
+    }
+    const int epb = L.epb;
 
-    // blob
+    // ---- rounds and the index spaces of the two contraction stages -----------------------------------
+    {
+        size_t tb_i = 0;
+        for (size_t si = 0; si < plan->stages.size(); ++si)
+        {
+            DevStage &sg = plan->stages[si];
+            sg.round_begin = (int)plan->rounds.size();
+            const size_t tb_first = tb_i;
+            while (tb_i < plan->tbs.size() && plan->tbs[tb_i].round == (int)si)
+                ++tb_i;
+            size_t a = tb_first;
+            while (a < tb_i)
+            {
+                const size_t b = serial ? a + 1 : tb_i;
+                DevRound rd{(int)a, (int)b, 0, 0};
+                // split the pair lists so that every round offers at least ~2 x `threads` work items
+                int t_off = 0;
+                for (int target = 4; target >= 1; --target)
+                {
+                    rd.x1_total = rd.x2_total = 0;
+                    for (size_t t = a; t < b; ++t)
+                    {
+                        DevTB &tb = plan->tbs[t];
+                        const int n1 = pk_pairs(tb.pkB, p), n2 = pk_pairs(tb.pkA, p);
+                        tb.n_sub1 = (n1 + target - 1) / target;
+                        tb.n_sub2 = (n2 + target - 1) / target;
+                        tb.x1_begin = rd.x1_total;
+                        tb.x2_begin = rd.x2_total;
+                        rd.x1_total += tb.n_sub1 * epb * q;
+                        rd.x2_total += tb.n_sub2 * epb * ((tb.nB * tb.nB2 + 1) / 2);
+                    }
+                    if (rd.x1_total >= 2 * threads && rd.x2_total >= 2 * threads)
+                        break;
+                }
+                for (size_t t = a; t < b; ++t)
+                {
+                    DevTB &tb = plan->tbs[t];
+                    tb.round = (int)plan->rounds.size();
+                    tb.t_off = t_off;
+                    t_off += tb.nB * tb.nB2 * ldq;
+                }
+                plan->rounds.push_back(rd);
+                a = b;
+            }
+            sg.round_end = (int)plan->rounds.size();
+        }
+    }
+
+    // ---- blob ------------------------------------------------------------------------------------------
     std::vector<char> blob;
     auto append = [&](const void *ptr, size_t bytes) {
         size_t off = (blob.size() + 15) & ~size_t(15);
         blob.resize(off + bytes);
-        memcpy(blob.data() + off, ptr, bytes);
+        if (bytes)
+            memcpy(blob.data() + off, ptr, bytes);
         return (int)off;
     };
-    append(plan->stages.data(), plan->stages.size() * sizeof(DevStage));
-    plan->off_dense = append(plan->dense.data(), plan->dense.size() * sizeof(DevDense));
-    plan->off_terms = append(plan->terms.data(), plan->terms.size() * sizeof(DevTerm));
-    plan->off_blocks = append(plan->blocks.data(), plan->blocks.size() * sizeof(DevBlock));
-    plan->off_units = append(plan->units.data(), plan->units.size() * sizeof(DevUnit));
-    plan->blob_bytes = blob.size();
-    MFV2D_TRY(mfv2d_cuda_malloc(plan->ctx, blob.size(), &plan->d_blob));
-    MFV2D_TRY(mfv2d_cuda_upload(plan->ctx, plan->d_blob, blob.data(), blob.size()));
+    L.n_stages = (int)plan->stages.size();
+    L.off_stages = append(plan->stages.data(), plan->stages.size() * sizeof(DevStage));
+    L.off_dense = append(plan->dense.data(), plan->dense.size() * sizeof(DevDense));
+    L.off_terms = append(plan->terms.data(), plan->terms.size() * sizeof(DevTerm));
+    L.off_blocks = append(plan->blocks.data(), plan->blocks.size() * sizeof(DevBlock));
+    L.off_units = append(plan->units.data(), plan->units.size() * sizeof(DevUnit));
+    L.off_ws = append(plan->ws.data(), plan->ws.size() * sizeof(DevW));
+    L.off_tbs = append(plan->tbs.data(), plan->tbs.size() * sizeof(DevTB));
+    L.off_rounds = append(plan->rounds.data(), plan->rounds.size() * sizeof(DevRound));
+    L.off_inc = append(inc_rows.data(), inc_rows.size() * sizeof(DevIncRow));
+    for (int k = 0; k < 4; ++k)
+        L.inc_row0[k] = bs->inc_off[k];
+    L.off_pairs = append(pairs.data(), pairs.size() * sizeof(int32_t));
+    for (int k = 0; k < 4; ++k)
+    {
+        L.pair_off[k] = pair_off[k];
+        L.pair_n[k] = pair_n[k];
+    }
+    for (int k = 0; k < 3; ++k)
+        L.off_pt[k] = append(pt[k].data(), pt[k].size() * sizeof(double));
+    L.off_tab = append(tab.data(), tab.size() * sizeof(double));
+    blob.resize((blob.size() + 15) & ~size_t(15));
+    L.blob_bytes = (int)blob.size();
+    L.off_cs = L.blob_bytes / 8;
+    L.off_slots = (L.off_cs + 8 * epb + 15) & ~15;
+    L.smem_bytes = (L.off_slots + epb * L.slot_stride + 8) * 8;
+    if ((size_t)L.smem_bytes > ctx->smem_optin)
+        return mfv2d_fail(ctx, MFV2D_CUDA_UNSUPPORTED, "assembly kernel needs %d bytes of shared memory (order %d, %d points)",
+                          L.smem_bytes, p, q);
+    if (plan->d_blob)
+        mfv2d_cuda_free(ctx, plan->d_blob);
+    plan->d_blob = nullptr;
+    MFV2D_TRY(mfv2d_cuda_malloc(ctx, blob.size(), &plan->d_blob));
+    MFV2D_TRY(mfv2d_cuda_upload(ctx, plan->d_blob, blob.data(), blob.size()));
     return MFV2D_SUCCESS;
 }
 

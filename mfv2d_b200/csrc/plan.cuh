@@ -41,11 +41,14 @@ struct BlockProgram
 };
 
 // ---- device-side description of the fused matrix path ---------------------------------------
+// Everything below is packed by the host into ONE blob (plan_finalize_matrix) that the assembly kernel
+// copies into shared memory once per CTA; all descriptor reads of the kernel are shared-memory reads.
 struct DevDense
 {
     int dk, inverse, field, transpose;
     int rows, cols;
-    int smem_off; // offset (in doubles) of the matrix inside the stage's shared-memory arena
+    int smem_off; // offset (in doubles) of the matrix inside the slot's arena
+    int ld;       // leading dimension inside the arena (cols rounded up to odd: conflict-free column walks)
 };
 
 struct DevTerm
@@ -55,12 +58,14 @@ struct DevTerm
     int L, R;  // incidence kinds applied on the left / right, -1: none
 };
 
-struct DevUnit // one warp work item: a strip of rows x 32 columns of one block
+struct DevUnit // one warp work item of the emission: nr rows x (1 << cl) columns of one block
 {
     short block; // index into blocks
     short c0;    // first column (relative to the block)
     short r0;    // first row (relative to the block)
     short nr;    // number of rows
+    short cl;    // log2 of the tile width in lanes (3, 4 or 5); 32 >> cl rows are written per warp store
+    short pad[3];
 };
 
 struct DevBlock
@@ -70,11 +75,88 @@ struct DevBlock
     int accumulate;           // 0: store, 1: add to what is already in the output
 };
 
+// kinds of weight fields at the quadrature points (Appendix A of SURVEY.md)
+enum
+{
+    W_M0,  // det w                                 (0-form mass)
+    W_M2,  // w / det                               (2-form mass)
+    W_HH,  // (j11^2 + j10^2) / det w               (1-form mass, h-h block)
+    W_VV,  // (j00^2 + j01^2) / det w               (v-v block)
+    W_HV,  // (j01 j11 + j00 j10) / det w           (h-v block)
+    W_P1H, // (fx j11 - fy j10) w                   (interior product 1 -> 0, h columns)
+    W_P1V, // -(fy j00 - fx j01) w                  (v columns)
+    W_P2H, // -(fx j10 + fy j11) / det w            (interior product 2 -> 1, h rows)
+    W_P2V  // -(fx j00 + fy j01) / det w            (v rows)
+};
+
+struct DevW // a weight field at the quadrature points (W_* of assembly.cu), `field` for interior products
+{
+    int kind, field;
+};
+
+// pair kinds: which two 1-D tables a product table row multiplies
+enum
+{
+    PK_NN = 0, // node x node, symmetric: rows enumerate i <= k
+    PK_EE = 1, // edge x edge, symmetric
+    PK_NE = 2, // node_i x edge_k, all pairs
+    PK_EN = 3, // edge_i x node_k, all pairs (rows of the NE table)
+};
+
+// One sum-factorised tensor block:  D[(i,j),(k,l)] = sum_a A_i(a) A2_k(a) sum_b B_j(b) B2_l(b) W(a,b)
+struct DevTB
+{
+    int w;                    // weight slot inside the stage
+    int pkA, pkB;             // pair kinds of (A, A2) and (B, B2)
+    int nA, nA2, nB, nB2;
+    int dst_off, ld, r0, c0;  // destination: arena offset, leading dimension, first row / column
+    int trans, mirror;        // write transposed only / also write the transposed entry
+    int t_off;                // offset of T[(j,l)][a] inside the slot's T region
+    int round;                // TB round inside the stage (rounds reuse the T region)
+    int x1_begin, n_sub1;     // stage-1 index space [x1_begin, x1_begin + n_sub1 * epb * q) of the round
+    int x2_begin, n_sub2;     // stage-2 index space [x2_begin, x2_begin + n_sub2 * epb * ceil(nB nB2 / 2))
+};
+
+struct DevRound
+{
+    int tb_begin, tb_end;
+    int x1_total, x2_total;
+};
+
 struct DevStage
 {
     int dense_begin, dense_end;
     int block_begin, block_end;
     int unit_begin, unit_end;
+    int w_begin, w_end;
+    int round_begin, round_end;
+};
+
+// row of an incidence matrix in gather form: up to 4 (column, sign) pairs, unused ones have sign 0
+struct DevIncRow
+{
+    int idx[4];
+    double sgn[4];
+};
+
+// byte offsets of the sections of the blob and the shared-memory layout of the assembly kernel
+struct AsmLayout
+{
+    int off_stages, off_dense, off_terms, off_blocks, off_units, off_ws, off_tbs, off_rounds;
+    int off_inc;      // DevIncRow rows of the four incidence kinds, inc_row0[kind] = first row
+    int inc_row0[4];
+    int off_pairs;    // int pair lists (i | k << 8 | product row << 16), pair_off / pair_n per pair kind
+    int pair_off[4], pair_n[4];
+    int off_pt[3];    // product tables NN, EE, NE: rows of ldq doubles
+    int off_tab;      // node | edge | pnts | wgts
+    int blob_bytes;
+    // shared memory (in doubles, after the blob): corners, then epb slots of [W | T | arena]
+    int ldq;          // padded quadrature row length
+    int epb;          // elements per pass
+    int off_cs, off_slots, slot_stride;
+    int slot_w, slot_t, slot_arena; // offsets inside a slot
+    int n_stages;
+    int smem_bytes;
 };
 
 struct mfv2d_plan
@@ -97,12 +179,13 @@ struct mfv2d_plan
     std::vector<DevBlock> blocks;
     std::vector<DevUnit> units;
     std::vector<DevStage> stages;
+    std::vector<DevW> ws;
+    std::vector<DevTB> tbs;
+    std::vector<DevRound> rounds;
+    AsmLayout lay{};
     int out_ld = 0;                    // 0: n_total (rectangular single-matrix plans override)
     unsigned long long out_stride = 0; // 0: n_total^2
-    int smem_doubles = 0; // dynamic shared memory of the matrix kernel (in doubles)
-    void *d_blob = nullptr; // device copy: [stages | dense | terms | blocks | units]
-    int off_dense = 0, off_terms = 0, off_blocks = 0, off_units = 0; // byte offsets inside the blob
-    size_t blob_bytes = 0;
+    void *d_blob = nullptr; // device copy of the descriptor blob (AsmLayout gives the sections)
 
     // vector path (flattened programs), see apply.cu
     std::vector<int32_t> vprog;
@@ -113,29 +196,25 @@ struct mfv2d_plan
     int mprog_off = 0, mcoef_off = 0; // matrix-mode programs (column-by-column fallback) follow the vector ones
 };
 
-// shared-memory layout of the assembly kernel (in doubles); used by the planner and the kernel.
-// One slot per element of a pass: geo 5 q^2 | G | T | arena
-struct SlotLayout
+// padded row length of the quadrature-indexed tables: even, and half of it odd, so that 16-byte
+// shared-memory reads of consecutive rows fall into distinct bank groups
+static inline __host__ __device__ int asm_ldq(int q)
 {
-    int G, T, ldT, arena;
-};
-static inline __host__ __device__ SlotLayout slot_layout(int p, int q)
-{
-    SlotLayout l;
-    const int q2 = q * q;
-    l.G = 5 * q2;
-    l.T = (l.G + q2 + 3) & ~3;
-    l.ldT = ((p + 1) * (p + 1) + 3) & ~3;
-    l.arena = l.T + q * l.ldT + 4;
+    int l = (q + 1) & ~1;
+    if (((l >> 1) & 1) == 0)
+        l += 2;
     return l;
 }
-// fixed part: tables | pair LUTs (two ints per double) | corners of the slots
-static inline __host__ __device__ int asm_fixed_doubles(int p, int tab_len, int epb)
-{
-    const int n_pairs = (p + 1) * (p + 2) / 2 + p * (p + 1) / 2;
-    int n = ((tab_len + 1) & ~1) + ((n_pairs + 1) >> 1) + 8 * epb;
-    return (n + 15) & ~15;
-}
 
+// lowered matrix blocks -> stages, tensor blocks, emission units, blob and shared-memory layout
+struct LoweredTerm
+{
+    double coef;
+    int L, R;
+    Factor d;
+    bool identity;
+};
+int plan_finalize_matrix(mfv2d_plan *plan, const std::vector<std::vector<LoweredTerm>> &lowered, int n_row_forms,
+                         int n_col_forms, const std::vector<int> &row_offsets, const std::vector<int> &col_offsets);
 int plan_lower_matrix(mfv2d_plan *plan);
 int plan_lower_vector(mfv2d_plan *plan);
