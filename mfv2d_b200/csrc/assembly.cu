@@ -118,7 +118,7 @@ __device__ __forceinline__ void phase_weights(const AsmArgs &args, double *smem,
         const double j11 = 0.25 * ((y3 - y0) * (1 - xi) + (y2 - y1) * (1 + xi));
         const double det = j00 * j11 - j10 * j01;
         const double w = wgts[a] * wgts[b];
-        double *W = smem + L.off_slots + (size_t)e * L.slot_stride + L.slot_w + a * ldq + b;
+        double *W = smem + L.off_slots + e * L.slot_stride + L.slot_w + a * ldq + b;
         for (int wi = sg.w_begin; wi < sg.w_end; ++wi, W += Q * ldq)
         {
             const DevW dw = ws[wi];
@@ -159,137 +159,100 @@ __device__ __forceinline__ void phase_weights(const AsmArgs &args, double *smem,
     }
 }
 
-__device__ __forceinline__ int find_tb1(const DevTB *tbs, const DevRound &rd, int x)
-{
-    int t = rd.tb_begin;
-    while (t + 1 < rd.tb_end && x >= tbs[t + 1].x1_begin)
-        ++t;
-    return t;
-}
-__device__ __forceinline__ int find_tb2(const DevTB *tbs, const DevRound &rd, int x)
-{
-    int t = rd.tb_begin;
-    while (t + 1 < rd.tb_end && x >= tbs[t + 1].x2_begin)
-        ++t;
-    return t;
-}
-
 // ---- S1: T[(j,l)][a] = sum_b B_j(b) B2_l(b) W[a][b] -----------------------------------------------------
+// work item (per element): tensor block, quadrature row a, a chunk of the block's (j,l) pair table
 template <int Q>
 __device__ __forceinline__ void phase_s1(const AsmArgs &args, double *smem, const DevRound &rd, const DevTB *tbs, int n_valid)
 {
     const AsmLayout &L = args.lay;
     const int ldq = L.ldq;
-    const int n_ea = L.epb * Q;
-    const float inv_ea = 1.0f / (float)n_ea;
-    const int *pairs = reinterpret_cast<const int *>(reinterpret_cast<const char *>(smem) + L.off_pairs);
-    for (int x = threadIdx.x; x < rd.x1_total; x += blockDim.x)
+    const char *sb = reinterpret_cast<const char *>(smem);
+    const int *xt = reinterpret_cast<const int *>(sb + L.off_x) + rd.x1_begin;
+    const DevS1Pair *s1 = reinterpret_cast<const DevS1Pair *>(sb + L.off_s1);
+    const int per = rd.x1_count;
+    const float inv_per = 1.0f / (float)per;
+    for (int x = threadIdx.x; x < per * n_valid; x += blockDim.x)
     {
-        const DevTB &tb = tbs[find_tb1(tbs, rd, x)];
-        const int xl = x - tb.x1_begin;
-        const int sub = fast_div(xl, inv_ea), ea = xl - sub * n_ea;
-        const int e = ea / Q, a = ea - e * Q;
-        if (e >= n_valid)
-            continue;
-        double *slot = smem + L.off_slots + (size_t)e * L.slot_stride;
+        const int e = fast_div(x, inv_per);
+        const int item = xt[x - e * per];
+        const DevTB &tb = tbs[rd.tb_begin + (item & 15)];
+        const int a = (item >> 4) & 31, pb = (item >> 9) & 255, len = item >> 17;
+        double *slot = smem + L.off_slots + e * L.slot_stride;
         double g[Q];
         load_row<Q>(g, slot + L.slot_w + tb.w * (Q * ldq) + a * ldq);
-        const int pk = tb.pkB;
-        const int np = L.pair_n[pk];
-        const int pb = (sub * np) / tb.n_sub1, pe = ((sub + 1) * np) / tb.n_sub1;
-        const int *pl = pairs + L.pair_off[pk];
-        const double *PT = reinterpret_cast<const double *>(reinterpret_cast<const char *>(smem) + L.off_pt[pk == PK_EN ? PK_NE : pk]);
         double *T = slot + L.slot_t + tb.t_off + a;
-        const bool sym = pk <= PK_EE;
-        const int nB2 = tb.nB2;
-        for (int pi = pb; pi < pe; ++pi)
+        const DevS1Pair *pr = s1 + tb.s1_tab + pb;
+        for (int n = 0; n < len; ++n)
         {
-            const int pr = pl[pi];
-            const int j = pr & 255, l = (pr >> 8) & 255;
-            const double acc = dot_row<Q>(PT + (pr >> 16) * ldq, g);
-            T[(j * nB2 + l) * ldq] = acc;
-            if (sym)
-                T[(l * nB2 + j) * ldq] = acc;
+            const int4 d = *reinterpret_cast<const int4 *>(pr + n);
+            const double acc = dot_row<Q>(smem + d.x, g);
+            T[d.y] = acc;
+            if (d.z >= 0)
+                T[d.z] = acc;
         }
     }
 }
 
 // ---- S2: D[(i,j),(k,l)] = sum_a A_i(a) A2_k(a) T[(j,l)][a] ------------------------------------------------
+// work item (per element): tensor block, the two columns (j0,l0) and the following one, a chunk of the (i,k) table
 template <int Q>
 __device__ __forceinline__ void phase_s2(const AsmArgs &args, double *smem, const DevRound &rd, const DevTB *tbs, int n_valid)
 {
     const AsmLayout &L = args.lay;
     const int ldq = L.ldq;
-    const int *pairs = reinterpret_cast<const int *>(reinterpret_cast<const char *>(smem) + L.off_pairs);
-    for (int x = threadIdx.x; x < rd.x2_total; x += blockDim.x)
+    const char *sb = reinterpret_cast<const char *>(smem);
+    const int *xt = reinterpret_cast<const int *>(sb + L.off_x) + rd.x2_begin;
+    const DevS2Pair *s2 = reinterpret_cast<const DevS2Pair *>(sb + L.off_s2);
+    const int per = rd.x2_count;
+    const float inv_per = 1.0f / (float)per;
+    for (int x = threadIdx.x; x < per * n_valid; x += blockDim.x)
     {
-        const DevTB &tb = tbs[find_tb2(tbs, rd, x)];
-        const int nB = tb.nB, nB2 = tb.nB2;
-        const int nJL = nB * nB2, nJLP = (nJL + 1) >> 1, n_jle = L.epb * nJLP;
-        const int xl = x - tb.x2_begin;
-        const int sub = fast_div(xl, 1.0f / (float)n_jle), jle = xl - sub * n_jle;
-        const int e = fast_div(jle, 1.0f / (float)nJLP), jlp = jle - e * nJLP;
-        if (e >= n_valid)
-            continue;
-        double *slot = smem + L.off_slots + (size_t)e * L.slot_stride;
-        const int jl0 = 2 * jlp;
-        const bool has2 = jl0 + 1 < nJL;
+        const int e = fast_div(x, inv_per);
+        const int item = xt[x - e * per];
+        const DevTB &tb = tbs[rd.tb_begin + (item & 15)];
+        const int j0 = (item >> 4) & 31, l0 = (item >> 9) & 31, pb = (item >> 14) & 255, len = item >> 22;
+        const int nB2 = tb.nB2, ld = tb.ld;
+        const int jl0 = j0 * nB2 + l0;
+        const bool has2 = jl0 + 1 < tb.nB * nB2;
+        double *slot = smem + L.off_slots + e * L.slot_stride;
         const double *T = slot + L.slot_t + tb.t_off + jl0 * ldq;
         double t0[Q], t1[Q];
         load_row<Q>(t0, T);
         load_row<Q>(t1, has2 ? T + ldq : T);
-        const int j0 = fast_div(jl0, 1.0f / (float)nB2), l0 = jl0 - j0 * nB2;
         int j1 = j0, l1 = l0 + 1;
         if (l1 == nB2)
         {
             l1 = 0;
             ++j1;
         }
-        const int rj0 = tb.r0 + j0, cl0 = tb.c0 + l0, rj1 = tb.r0 + j1, cl1 = tb.c0 + l1;
-        const int pk = tb.pkA;
-        const int np = L.pair_n[pk];
-        const int pb = (sub * np) / tb.n_sub2, pe = ((sub + 1) * np) / tb.n_sub2;
-        const int *pl = pairs + L.pair_off[pk];
-        const double *PT = reinterpret_cast<const double *>(reinterpret_cast<const char *>(smem) + L.off_pt[pk == PK_EN ? PK_NE : pk]);
         double *D = slot + L.slot_arena + tb.dst_off;
-        const int ld = tb.ld;
-        const bool symA = pk <= PK_EE, direct = !tb.trans, flipped = tb.trans || tb.mirror;
-        for (int pi = pb; pi < pe; ++pi)
+        double *Dd0 = D + (tb.r0 + j0) * ld + tb.c0 + l0, *Df0 = D + (tb.c0 + l0) * ld + tb.r0 + j0;
+        double *Dd1 = D + (tb.r0 + j1) * ld + tb.c0 + l1, *Df1 = D + (tb.c0 + l1) * ld + tb.r0 + j1;
+        const DevS2Pair *pr = s2 + tb.s2_tab + pb;
+        for (int n = 0; n < len; ++n)
         {
-            const int pr = pl[pi];
-            const int i = pr & 255, k = (pr >> 8) & 255;
+            const int4 d = *reinterpret_cast<const int4 *>(pr + n);
+            const int f1 = pr[n].f1;
             double v0, v1;
-            dot_row2<Q>(PT + (pr >> 16) * ldq, t0, t1, v0, v1);
-            {
-                const int row = i * nB + rj0, col = k * nB2 + cl0;
-                if (direct)
-                    D[row * ld + col] = v0;
-                if (flipped)
-                    D[col * ld + row] = v0;
-                if (symA)
-                {
-                    const int row2 = k * nB + rj0, col2 = i * nB2 + cl0;
-                    if (direct)
-                        D[row2 * ld + col2] = v0;
-                    if (flipped)
-                        D[col2 * ld + row2] = v0;
-                }
-            }
+            dot_row2<Q>(smem + d.x, t0, t1, v0, v1);
+            if (d.y >= 0)
+                Dd0[d.y] = v0;
+            if (d.z >= 0)
+                Df0[d.z] = v0;
+            if (d.w >= 0)
+                Dd0[d.w] = v0;
+            if (f1 >= 0)
+                Df0[f1] = v0;
             if (has2)
             {
-                const int row = i * nB + rj1, col = k * nB2 + cl1;
-                if (direct)
-                    D[row * ld + col] = v1;
-                if (flipped)
-                    D[col * ld + row] = v1;
-                if (symA)
-                {
-                    const int row2 = k * nB + rj1, col2 = i * nB2 + cl1;
-                    if (direct)
-                        D[row2 * ld + col2] = v1;
-                    if (flipped)
-                        D[col2 * ld + row2] = v1;
-                }
+                if (d.y >= 0)
+                    Dd1[d.y] = v1;
+                if (d.z >= 0)
+                    Df1[d.z] = v1;
+                if (d.w >= 0)
+                    Dd1[d.w] = v1;
+                if (f1 >= 0)
+                    Df1[f1] = v1;
             }
         }
     }
@@ -297,8 +260,9 @@ __device__ __forceinline__ void phase_s2(const AsmArgs &args, double *smem, cons
 
 // in-place SPD inverse of the n x n matrix (leading dimension ld) at arena + off of every slot (Gauss-Jordan,
 // no pivoting needed); the column / row of the pivot are staged in the slot's T region
-__device__ __noinline__ void invert_spd_slots(const AsmArgs &args, double *smem, int off, int n, int ld, int n_valid, int *bad)
+__device__ __forceinline__ void invert_spd_slots(const AsmArgs &args, int off, int n, int ld, int n_valid, int *bad)
 {
+    MFV2D_DYN_SMEM(double, smem);
     const AsmLayout &L = args.lay;
     const float inv_n = 1.0f / (float)n, inv_nn = 1.0f / (float)(n * n);
     for (int k = 0; k < n; ++k)
@@ -307,7 +271,7 @@ __device__ __noinline__ void invert_spd_slots(const AsmArgs &args, double *smem,
         for (int idx = threadIdx.x; idx < n_valid * n; idx += blockDim.x)
         {
             const int e = fast_div(idx, inv_n), i = idx - e * n;
-            double *slot = smem + L.off_slots + (size_t)e * L.slot_stride;
+            double *slot = smem + L.off_slots + e * L.slot_stride;
             const double *D = slot + L.slot_arena + off;
             double *colk = slot + L.slot_t, *rowk = colk + n;
             colk[i] = D[i * ld + k];
@@ -318,7 +282,7 @@ __device__ __noinline__ void invert_spd_slots(const AsmArgs &args, double *smem,
         {
             const int e = fast_div(idx, inv_nn), ij = idx - e * n * n;
             const int i = fast_div(ij, inv_n), j = ij - i * n;
-            double *slot = smem + L.off_slots + (size_t)e * L.slot_stride;
+            double *slot = smem + L.off_slots + e * L.slot_stride;
             double *D = slot + L.slot_arena + off;
             const double *colk = slot + L.slot_t, *rowk = colk + n;
             const double pv = colk[k];
@@ -349,20 +313,20 @@ struct EmitTerm
 
 __device__ __forceinline__ void load_inc(const DevIncRow *row, int (&idx)[4], double (&sgn)[4])
 {
-    const int4 iv = *reinterpret_cast<const int4 *>(row->idx);
-    const double2 s01 = *reinterpret_cast<const double2 *>(row->sgn);
-    const double2 s23 = *reinterpret_cast<const double2 *>(row->sgn + 2);
-    idx[0] = iv.x;
-    idx[1] = iv.y;
-    idx[2] = iv.z;
-    idx[3] = iv.w;
-    sgn[0] = s01.x;
-    sgn[1] = s01.y;
-    sgn[2] = s23.x;
-    sgn[3] = s23.y;
+    const int4 a = *reinterpret_cast<const int4 *>(row->e);
+    const int4 b = *reinterpret_cast<const int4 *>(row->e + 4);
+    idx[0] = a.x;
+    idx[1] = a.z;
+    idx[2] = b.x;
+    idx[3] = b.z;
+    sgn[0] = __hiloint2double(a.y, 0);
+    sgn[1] = __hiloint2double(a.w, 0);
+    sgn[2] = __hiloint2double(b.y, 0);
+    sgn[3] = __hiloint2double(b.w, 0);
 }
 
-// one lane's share of a tile: column c, rows r0 + sub, r0 + sub + rstep, ... ; NL x NR gathers per entry
+// one lane's share of a tile: column c, rows r0 + sub, r0 + sub + rstep, ... ; NL x NR gathers per entry.
+// D rows and output rows are walked with running offsets (no per-row multiplications).
 template <int NL, int NR>
 __device__ __forceinline__ void emit_tile(const EmitTerm &t, int r0, int nr, int sub, int rstep, int c, bool active,
                                           double *__restrict__ o, int N, bool accumulate)
@@ -381,29 +345,45 @@ __device__ __forceinline__ void emit_tile(const EmitTerm &t, int r0, int nr, int
         for (int b = 0; b < NR; ++b)
             rs[b] *= t.coef;
     }
-    for (int r = sub; r < nr; r += rstep)
+    o += (size_t)sub * N;
+    const size_t ostep = (size_t)rstep * N;
+    if (NL == 1)
     {
-        double v = 0.0;
-        if (NL == 1)
+        const double *Dr = t.D + (r0 + sub) * t.ld;
+        const int dstep = rstep * t.ld;
+        for (int r = sub; r < nr; r += rstep, Dr += dstep, o += ostep)
         {
-            const double *Dr = t.D + (r0 + r) * t.ld;
+            double v = rs[0] * Dr[rc[0]];
 #pragma unroll
-            for (int b = 0; b < NR; ++b)
+            for (int b = 1; b < NR; ++b)
                 v = fma(rs[b], Dr[rc[b]], v);
+            if (active)
+            {
+                if (accumulate)
+                    *o += v;
+                else
+                    *o = v;
+            }
         }
-        else
+    }
+    else
+    {
+        const DevIncRow *lt = t.ltab + r0 + sub;
+        const double *Dc = t.D + rc[0];
+        for (int r = sub; r < nr; r += rstep, lt += rstep, o += ostep)
         {
             int li[4];
             double ls[4];
-            load_inc(t.ltab + r0 + r, li, ls);
+            load_inc(lt, li, ls);
+            double v = 0.0;
 #pragma unroll
             for (int a = 0; a < NL; ++a)
             {
-                const double *Dr = t.D + li[a] * t.ld;
                 if (NR == 1)
-                    v = fma(ls[a], Dr[rc[0]], v);
+                    v = fma(ls[a], Dc[li[a] * t.ld], v);
                 else
                 {
+                    const double *Dr = t.D + li[a] * t.ld;
 #pragma unroll
                     for (int b = 0; b < NR; ++b)
                         v = fma(ls[a] * rs[b], Dr[rc[b]], v);
@@ -411,13 +391,13 @@ __device__ __forceinline__ void emit_tile(const EmitTerm &t, int r0, int nr, int
             }
             if (NR == 1)
                 v *= rs[0];
-        }
-        if (active)
-        {
-            if (accumulate)
-                o[(size_t)r * N] += v;
-            else
-                o[(size_t)r * N] = v;
+            if (active)
+            {
+                if (accumulate)
+                    *o += v;
+                else
+                    *o = v;
+            }
         }
     }
 }
@@ -440,9 +420,9 @@ __device__ __forceinline__ EmitTerm make_emit_term(const AsmArgs &args, const De
     return t;
 }
 
-__device__ __noinline__ void emit_stage(const AsmArgs &args, double *smem, const DevStage &sg, unsigned long long elem0,
-                                        int n_valid)
+__device__ __forceinline__ void emit_stage(const AsmArgs &args, const DevStage &sg, unsigned long long elem0, int n_valid)
 {
+    MFV2D_DYN_SMEM(double, smem); // re-declared here so that the compiler keeps every access in the shared window
     const AsmLayout &L = args.lay;
     const char *sb = reinterpret_cast<const char *>(smem);
     const DevDense *dense = reinterpret_cast<const DevDense *>(sb + L.off_dense);
@@ -459,7 +439,7 @@ __device__ __noinline__ void emit_stage(const AsmArgs &args, double *smem, const
         const int e = fast_div(w, inv_units), u = w - e * n_units;
         const DevUnit un = units[sg.unit_begin + u];
         const DevBlock db = blocks[un.block];
-        const double *arena = smem + L.off_slots + (size_t)e * L.slot_stride + L.slot_arena;
+        const double *arena = smem + L.off_slots + e * L.slot_stride + L.slot_arena;
         double *const out = args.out + (elem0 + e) * args.out_stride + (size_t)(db.row0 + un.r0) * N + db.col0;
         const int n_terms = db.term_end - db.term_begin;
         const int rstep = 32 >> un.cl;
@@ -472,8 +452,12 @@ __device__ __noinline__ void emit_stage(const AsmArgs &args, double *smem, const
             if (n_terms == 0)
             {
                 if (active && !db.accumulate)
-                    for (int r = sub; r < un.nr; r += rstep)
-                        o[(size_t)r * N] = 0.0;
+                {
+                    double *oz = o + (size_t)sub * N;
+                    const size_t ostep = (size_t)rstep * N;
+                    for (int r = sub; r < un.nr; r += rstep, oz += ostep)
+                        *oz = 0.0;
+                }
                 continue;
             }
             const DevTerm tm0 = terms[db.term_begin];
@@ -596,9 +580,9 @@ template <int Q> __global__ void __launch_bounds__(ASM_THREADS, 2) element_matri
             }
             for (int d = sg.dense_begin; d < sg.dense_end; ++d)
                 if (dense[d].inverse)
-                    invert_spd_slots(args, smem, dense[d].smem_off, dense[d].rows, dense[d].ld, n_valid, bad);
+                    invert_spd_slots(args, dense[d].smem_off, dense[d].rows, dense[d].ld, n_valid, bad);
             __syncthreads();
-            emit_stage(args, smem, sg, elem0, n_valid);
+            emit_stage(args, sg, elem0, n_valid);
         }
         __syncthreads();
         if (args.status)

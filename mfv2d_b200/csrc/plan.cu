@@ -460,14 +460,28 @@ int plan_finalize_matrix(mfv2d_plan *plan, const std::vector<std::vector<Lowered
 
     // ---- element-independent tables of the blob --------------------------------------------------
     const mfv2d_basis *bs = plan->basis;
-    std::vector<DevIncRow> inc_rows(bs->inc_off[4]);
-    for (int r = 0; r < bs->inc_off[4]; ++r)
-        for (int t = 0; t < 4; ++t)
-        {
-            const int32_t v = bs->h_inc[(size_t)r * 4 + t];
-            inc_rows[r].idx[t] = v == 0 ? 0 : (v > 0 ? v - 1 : -v - 1);
-            inc_rows[r].sgn[t] = v == 0 ? 0.0 : (v > 0 ? 1.0 : -1.0);
-        }
+    // incidence rows of the kinds the terms use (left: rows of E_L; right: rows of the transpose of E_R)
+    std::vector<DevIncRow> inc_rows;
+    int inc_row0[4] = {-1, -1, -1, -1};
+    for (const std::vector<LoweredTerm> &lts : lowered)
+        for (const LoweredTerm &lt : lts)
+            for (int kind : {lt.L, lt.R >= 0 ? (lt.R ^ 2) : -1})
+            {
+                if (kind < 0 || inc_row0[kind] >= 0)
+                    continue;
+                inc_row0[kind] = (int)inc_rows.size();
+                for (int r = bs->inc_off[kind]; r < bs->inc_off[kind + 1]; ++r)
+                {
+                    DevIncRow row{};
+                    for (int t = 0; t < 4; ++t)
+                    {
+                        const int32_t v = bs->h_inc[(size_t)r * 4 + t];
+                        row.e[2 * t] = v == 0 ? 0 : (v > 0 ? v - 1 : -v - 1);
+                        row.e[2 * t + 1] = v == 0 ? 0 : (v > 0 ? 0x3FF00000 : (int)0xBFF00000);
+                    }
+                    inc_rows.push_back(row);
+                }
+            }
     std::vector<int32_t> pairs;
     int pair_off[4], pair_n[4];
     for (int pk = 0; pk < 4; ++pk)
@@ -508,7 +522,7 @@ int plan_finalize_matrix(mfv2d_plan *plan, const std::vector<std::vector<Lowered
     tab.insert(tab.end(), bs->edge.begin(), bs->edge.end());
     tab.insert(tab.end(), bs->pnts.begin(), bs->pnts.end());
     tab.insert(tab.end(), bs->wgts.begin(), bs->wgts.end());
-    const size_t table_bytes = inc_rows.size() * sizeof(DevIncRow) + pairs.size() * 4 +
+    const size_t table_bytes = inc_rows.size() * sizeof(DevIncRow) + pairs.size() * (4 + 16 + 32) +
                                (pt[0].size() + pt[1].size() + pt[2].size() + tab.size()) * 8 + 256;
 
     // ---- stages: greedy packing of the dense matrices under a per-slot capacity -------------------
@@ -708,7 +722,7 @@ int plan_finalize_matrix(mfv2d_plan *plan, const std::vector<std::vector<Lowered
                 }
             }
             const int w = 1 << cl, rows_per_store = 32 >> cl;
-            const int rg = 8 * rows_per_store; // 8 warp stores per unit
+            const int rg = 64 * rows_per_store; // at most 64 warp stores per unit (the per-unit set-up is amortised)
             for (int c0 = 0; c0 < db.ncols; c0 += w)
                 for (int r0 = 0; r0 < db.nrows; r0 += rg)
                 {
@@ -762,36 +776,7 @@ int plan_finalize_matrix(mfv2d_plan *plan, const std::vector<std::vector<Lowered
     int slot = L.slot_arena + slot_a + 2;
     slot = ((slot + 15) & ~15) + 4; // slot stride = 4 (mod 16) doubles: the slots of a pass sit in distinct banks
     L.slot_stride = slot;
-    {
-        // exact size of the blob (descriptors + tables), rounded section by section as `append` does
-        size_t desc = 0;
-        auto sec = [&](size_t bytes) { desc = ((desc + 15) & ~size_t(15)) + bytes; };
-        sec(plan->stages.size() * sizeof(DevStage));
-        sec(plan->dense.size() * sizeof(DevDense));
-        sec(plan->terms.size() * sizeof(DevTerm));
-        sec(plan->blocks.size() * sizeof(DevBlock));
-        sec(plan->units.size() * sizeof(DevUnit));
-        sec(plan->ws.size() * sizeof(DevW));
-        sec(plan->tbs.size() * sizeof(DevTB));
-        sec(plan->tbs.size() * sizeof(DevRound));
-        const long long fixed_exact = (long long)desc + (long long)table_bytes + 8 * 64 + 256;
-        long long per_cta = (cap_used == cap_pref ? ((long long)228 * 1024 - 2 * 1024) / 2 : (long long)ctx->smem_optin);
-        long long epb = (per_cta - fixed_exact) / 8 / slot;
-        if (epb < 1)
-        {
-            per_cta = (long long)ctx->smem_optin;
-            epb = (per_cta - fixed_exact) / 8 / slot;
-        }
-        if (epb < 1)
-            return mfv2d_fail(ctx, MFV2D_CUDA_UNSUPPORTED,
-                              "an element matrix of order %d with %d quadrature points does not fit into shared memory", p, q);
-        if (epb > 8)
-            epb = 8;
-        L.epb = (int)epb;
-    }
-    const int epb = L.epb;
-
-    // ---- rounds and the index spaces of the two contraction stages -----------------------------------
+    // ---- rounds: groups of tensor blocks whose T arrays live at the same time -------------------------
     {
         size_t tb_i = 0;
         for (size_t si = 0; si < plan->stages.size(); ++si)
@@ -801,30 +786,12 @@ int plan_finalize_matrix(mfv2d_plan *plan, const std::vector<std::vector<Lowered
             const size_t tb_first = tb_i;
             while (tb_i < plan->tbs.size() && plan->tbs[tb_i].round == (int)si)
                 ++tb_i;
-            size_t a = tb_first;
-            while (a < tb_i)
+            int t_off = 0;
+            for (size_t a = tb_first; a < tb_i;)
             {
-                const size_t b = serial ? a + 1 : tb_i;
-                DevRound rd{(int)a, (int)b, 0, 0};
-                // split the pair lists so that every round offers at least ~2 x `threads` work items
-                int t_off = 0;
-                for (int target = 4; target >= 1; --target)
-                {
-                    rd.x1_total = rd.x2_total = 0;
-                    for (size_t t = a; t < b; ++t)
-                    {
-                        DevTB &tb = plan->tbs[t];
-                        const int n1 = pk_pairs(tb.pkB, p), n2 = pk_pairs(tb.pkA, p);
-                        tb.n_sub1 = (n1 + target - 1) / target;
-                        tb.n_sub2 = (n2 + target - 1) / target;
-                        tb.x1_begin = rd.x1_total;
-                        tb.x2_begin = rd.x2_total;
-                        rd.x1_total += tb.n_sub1 * epb * q;
-                        rd.x2_total += tb.n_sub2 * epb * ((tb.nB * tb.nB2 + 1) / 2);
-                    }
-                    if (rd.x1_total >= 2 * threads && rd.x2_total >= 2 * threads)
-                        break;
-                }
+                const size_t b = serial ? a + 1 : (a + 16 < tb_i ? a + 16 : tb_i); // 4 bits name a block inside a round
+                if (serial)
+                    t_off = 0;
                 for (size_t t = a; t < b; ++t)
                 {
                     DevTB &tb = plan->tbs[t];
@@ -832,14 +799,14 @@ int plan_finalize_matrix(mfv2d_plan *plan, const std::vector<std::vector<Lowered
                     tb.t_off = t_off;
                     t_off += tb.nB * tb.nB2 * ldq;
                 }
-                plan->rounds.push_back(rd);
+                plan->rounds.push_back(DevRound{(int)a, (int)b, 0, 0, 0, 0});
                 a = b;
             }
             sg.round_end = (int)plan->rounds.size();
         }
     }
 
-    // ---- blob ------------------------------------------------------------------------------------------
+    // ---- blob, part 1: the element-independent tables (their offsets go into the pair tables) -----------
     std::vector<char> blob;
     auto append = [&](const void *ptr, size_t bytes) {
         size_t off = (blob.size() + 15) & ~size_t(15);
@@ -848,6 +815,154 @@ int plan_finalize_matrix(mfv2d_plan *plan, const std::vector<std::vector<Lowered
             memcpy(blob.data() + off, ptr, bytes);
         return (int)off;
     };
+    for (int k = 0; k < 3; ++k)
+        L.off_pt[k] = append(pt[k].data(), pt[k].size() * sizeof(double));
+    L.off_tab = append(tab.data(), tab.size() * sizeof(double));
+    L.off_inc = append(inc_rows.data(), inc_rows.size() * sizeof(DevIncRow));
+    for (int k = 0; k < 4; ++k)
+        L.inc_row0[k] = inc_row0[k];
+
+    // per tensor block: what one (j,l) pair does in stage 1 and one (i,k) pair in stage 2
+    std::vector<DevS1Pair> s1tab;
+    std::vector<DevS2Pair> s2tab;
+    for (DevTB &tb : plan->tbs)
+    {
+        tb.s1_tab = (int)s1tab.size();
+        for (int n = 0; n < pair_n[tb.pkB]; ++n)
+        {
+            const int pr = pairs[pair_off[tb.pkB] + n];
+            const int j = pr & 255, l = (pr >> 8) & 255, row = pr >> 16;
+            DevS1Pair e{};
+            e.pt = L.off_pt[tb.pkB == PK_EN ? PK_NE : tb.pkB] / 8 + row * ldq;
+            e.t1 = (j * tb.nB2 + l) * ldq;
+            e.t2 = (tb.pkB <= PK_EE && j != l) ? (l * tb.nB2 + j) * ldq : -1;
+            s1tab.push_back(e);
+        }
+        tb.s2_tab = (int)s2tab.size();
+        for (int n = 0; n < pair_n[tb.pkA]; ++n)
+        {
+            const int pr = pairs[pair_off[tb.pkA] + n];
+            const int i = pr & 255, k = (pr >> 8) & 255, row = pr >> 16;
+            const bool direct = !tb.trans, flipped = tb.trans || tb.mirror, image = tb.pkA <= PK_EE && i != k;
+            DevS2Pair e{};
+            e.pt = L.off_pt[tb.pkA == PK_EN ? PK_NE : tb.pkA] / 8 + row * ldq;
+            e.d0 = direct ? i * tb.nB * tb.ld + k * tb.nB2 : -1;
+            e.f0 = flipped ? k * tb.nB2 * tb.ld + i * tb.nB : -1;
+            e.d1 = (direct && image) ? k * tb.nB * tb.ld + i * tb.nB2 : -1;
+            e.f1 = (flipped && image) ? i * tb.nB2 * tb.ld + k * tb.nB : -1;
+            s2tab.push_back(e);
+        }
+    }
+
+    // ---- chunking of the pair lists, elements per pass and the packed work items -------------------------
+    // cost model of a round: passes of `threads` work items, each item costs a set-up plus its pairs
+    auto choose = [&](int round, bool stage2, int epb, int min_chunk, int *count) {
+        const DevRound &rd = plan->rounds[round];
+        long long best_cost = -1;
+        int best = min_chunk;
+        for (int chunk = min_chunk; chunk <= 31; ++chunk)
+        {
+            long long items = 0;
+            for (int t = rd.tb_begin; t < rd.tb_end; ++t)
+            {
+                const DevTB &tb = plan->tbs[t];
+                const int np = pk_pairs(stage2 ? tb.pkA : tb.pkB, p);
+                const int per = stage2 ? (tb.nB * tb.nB2 + 1) / 2 : q;
+                items += (long long)((np + chunk - 1) / chunk) * per;
+            }
+            const long long passes = (items * epb + threads - 1) / threads;
+            const long long cost = passes * (30 + (stage2 ? 28 : 16) * chunk);
+            if (best_cost < 0 || cost < best_cost)
+            {
+                best_cost = cost;
+                best = chunk;
+                *count = (int)items;
+            }
+        }
+        return best;
+    };
+    std::vector<int32_t> xtab;
+    bool fits = false;
+    for (int min_chunk : {1, 4, 8, 16, 31})
+    {
+        // upper bound of the work-item table for chunks of at least min_chunk pairs
+        size_t x_bound = 0;
+        for (const DevTB &tb : plan->tbs)
+            x_bound += (size_t)((pk_pairs(tb.pkB, p) + min_chunk - 1) / min_chunk) * q +
+                       (size_t)((pk_pairs(tb.pkA, p) + min_chunk - 1) / min_chunk) * ((tb.nB * tb.nB2 + 1) / 2);
+        size_t fixed_exact = (blob.size() + 15) & ~size_t(15);
+        auto sec = [&](size_t bytes) { fixed_exact = ((fixed_exact + 15) & ~size_t(15)) + bytes; };
+        sec(plan->stages.size() * sizeof(DevStage));
+        sec(plan->dense.size() * sizeof(DevDense));
+        sec(plan->terms.size() * sizeof(DevTerm));
+        sec(plan->blocks.size() * sizeof(DevBlock));
+        sec(plan->units.size() * sizeof(DevUnit));
+        sec(plan->ws.size() * sizeof(DevW));
+        sec(plan->tbs.size() * sizeof(DevTB));
+        sec(plan->rounds.size() * sizeof(DevRound));
+        sec(s1tab.size() * sizeof(DevS1Pair));
+        sec(s2tab.size() * sizeof(DevS2Pair));
+        sec(x_bound * sizeof(int32_t));
+        fixed_exact += 8 * 64 + 256; // corners of up to 8 slots, alignment slack
+        long long per_cta = (cap_used == cap_pref ? ((long long)228 * 1024 - 2 * 1024) / 2 : (long long)ctx->smem_optin);
+        long long epb = (per_cta - (long long)fixed_exact) / 8 / slot;
+        if (epb < 1)
+        {
+            per_cta = (long long)ctx->smem_optin;
+            epb = (per_cta - (long long)fixed_exact) / 8 / slot;
+        }
+        if (epb < 1)
+            continue;
+        if (epb > 8)
+            epb = 8;
+        L.epb = (int)epb;
+        xtab.clear();
+        for (size_t r = 0; r < plan->rounds.size(); ++r)
+        {
+            DevRound &rd = plan->rounds[r];
+            int dummy = 0;
+            const int chunk1 = choose((int)r, false, L.epb, min_chunk, &dummy);
+            const int chunk2 = choose((int)r, true, L.epb, min_chunk, &dummy);
+            rd.x1_begin = (int)xtab.size();
+            for (int t = rd.tb_begin; t < rd.tb_end; ++t)
+            {
+                DevTB &tb = plan->tbs[t];
+                const int np = pk_pairs(tb.pkB, p);
+                tb.n_sub1 = (np + chunk1 - 1) / chunk1;
+                for (int sub = 0; sub < tb.n_sub1; ++sub)
+                {
+                    const int pb = sub * np / tb.n_sub1, pe = (sub + 1) * np / tb.n_sub1;
+                    for (int a = 0; a < q; ++a)
+                        xtab.push_back((t - rd.tb_begin) | (a << 4) | (pb << 9) | ((pe - pb) << 17));
+                }
+            }
+            rd.x1_count = (int)xtab.size() - rd.x1_begin;
+            rd.x2_begin = (int)xtab.size();
+            for (int t = rd.tb_begin; t < rd.tb_end; ++t)
+            {
+                DevTB &tb = plan->tbs[t];
+                const int np = pk_pairs(tb.pkA, p);
+                tb.n_sub2 = (np + chunk2 - 1) / chunk2;
+                const int nJL = tb.nB * tb.nB2;
+                for (int sub = 0; sub < tb.n_sub2; ++sub)
+                {
+                    const int pb = sub * np / tb.n_sub2, pe = (sub + 1) * np / tb.n_sub2;
+                    for (int jl = 0; jl < nJL; jl += 2)
+                        xtab.push_back((t - rd.tb_begin) | ((jl / tb.nB2) << 4) | ((jl % tb.nB2) << 9) | (pb << 14) |
+                                       ((pe - pb) << 22));
+                }
+            }
+            rd.x2_count = (int)xtab.size() - rd.x2_begin;
+        }
+        fits = true;
+        break;
+    }
+    if (!fits)
+        return mfv2d_fail(ctx, MFV2D_CUDA_UNSUPPORTED,
+                          "an element matrix of order %d with %d quadrature points does not fit into shared memory", p, q);
+    const int epb = L.epb;
+
+    // ---- blob, part 2: descriptors -----------------------------------------------------------------------
     L.n_stages = (int)plan->stages.size();
     L.off_stages = append(plan->stages.data(), plan->stages.size() * sizeof(DevStage));
     L.off_dense = append(plan->dense.data(), plan->dense.size() * sizeof(DevDense));
@@ -857,18 +972,9 @@ int plan_finalize_matrix(mfv2d_plan *plan, const std::vector<std::vector<Lowered
     L.off_ws = append(plan->ws.data(), plan->ws.size() * sizeof(DevW));
     L.off_tbs = append(plan->tbs.data(), plan->tbs.size() * sizeof(DevTB));
     L.off_rounds = append(plan->rounds.data(), plan->rounds.size() * sizeof(DevRound));
-    L.off_inc = append(inc_rows.data(), inc_rows.size() * sizeof(DevIncRow));
-    for (int k = 0; k < 4; ++k)
-        L.inc_row0[k] = bs->inc_off[k];
-    L.off_pairs = append(pairs.data(), pairs.size() * sizeof(int32_t));
-    for (int k = 0; k < 4; ++k)
-    {
-        L.pair_off[k] = pair_off[k];
-        L.pair_n[k] = pair_n[k];
-    }
-    for (int k = 0; k < 3; ++k)
-        L.off_pt[k] = append(pt[k].data(), pt[k].size() * sizeof(double));
-    L.off_tab = append(tab.data(), tab.size() * sizeof(double));
+    L.off_s1 = append(s1tab.data(), s1tab.size() * sizeof(DevS1Pair));
+    L.off_s2 = append(s2tab.data(), s2tab.size() * sizeof(DevS2Pair));
+    L.off_x = append(xtab.data(), xtab.size() * sizeof(int32_t));
     blob.resize((blob.size() + 15) & ~size_t(15));
     L.blob_bytes = (int)blob.size();
     L.off_cs = L.blob_bytes / 8;

@@ -113,14 +113,37 @@ struct DevTB
     int trans, mirror;        // write transposed only / also write the transposed entry
     int t_off;                // offset of T[(j,l)][a] inside the slot's T region
     int round;                // TB round inside the stage (rounds reuse the T region)
-    int x1_begin, n_sub1;     // stage-1 index space [x1_begin, x1_begin + n_sub1 * epb * q) of the round
-    int x2_begin, n_sub2;     // stage-2 index space [x2_begin, x2_begin + n_sub2 * epb * ceil(nB nB2 / 2))
+    int n_sub1, n_sub2;       // number of chunks the (j,l) / (i,k) pair lists are cut into
+    int s1_tab, s2_tab;       // first entry of the block's DevS1Pair / DevS2Pair tables
+    int pad;
 };
 
+// stage-1 work of one (j,l) pair: product-table row and where T goes
+struct DevS1Pair
+{
+    int pt;       // offset (doubles from the start of shared memory) of the row (B_j B2_l)(b)
+    int t1, t2;   // offsets of T[(j,l)][0] and of its mirror image T[(l,j)][0] (-1: none) inside the block's T
+    int pad;
+};
+
+// stage-2 work of one (i,k) pair: product-table row and the (up to four) images of the entry in the arena,
+// relative to a per-thread base: d* are added to (r0 + j) ld + c0 + l, f* to (c0 + l) ld + r0 + j; -1: none
+struct DevS2Pair
+{
+    int pt;
+    int d0, f0; // ((i,j),(k,l)) and its transposed image
+    int d1, f1; // ((k,j),(i,l)), the i <-> k image of a symmetric (A == A2) block, and its transposed image
+    int pad[3];
+};
+
+// work items of the two contraction stages for ONE element of a pass, packed into an int:
+//   stage 1: tb | a << 4 | first pair << 9 | number of pairs << 17
+//   stage 2: tb | j0 << 4 | l0 << 9 | first pair << 14 | number of pairs << 22     (columns (j0,l0) and the next one)
 struct DevRound
 {
     int tb_begin, tb_end;
-    int x1_total, x2_total;
+    int x1_begin, x1_count; // entries in the x tables (per element)
+    int x2_begin, x2_count;
 };
 
 struct DevStage
@@ -132,21 +155,21 @@ struct DevStage
     int round_begin, round_end;
 };
 
-// row of an incidence matrix in gather form: up to 4 (column, sign) pairs, unused ones have sign 0
+// row of an incidence matrix in gather form: up to 4 (column, sign) pairs.  The sign is kept as the HIGH word
+// of the double +1.0 / -1.0 / 0.0 (unused entry), so that a row is two 16-byte loads and the sign costs nothing
+// to rebuild (__hiloint2double(hi, 0)).
 struct DevIncRow
 {
-    int idx[4];
-    double sgn[4];
+    int e[8]; // idx0, sgn0.hi, idx1, sgn1.hi, ...
 };
 
 // byte offsets of the sections of the blob and the shared-memory layout of the assembly kernel
 struct AsmLayout
 {
     int off_stages, off_dense, off_terms, off_blocks, off_units, off_ws, off_tbs, off_rounds;
+    int off_s1, off_s2, off_x; // DevS1Pair / DevS2Pair tables and the packed work items
     int off_inc;      // DevIncRow rows of the four incidence kinds, inc_row0[kind] = first row
     int inc_row0[4];
-    int off_pairs;    // int pair lists (i | k << 8 | product row << 16), pair_off / pair_n per pair kind
-    int pair_off[4], pair_n[4];
     int off_pt[3];    // product tables NN, EE, NE: rows of ldq doubles
     int off_tab;      // node | edge | pnts | wgts
     int blob_bytes;

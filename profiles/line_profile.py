@@ -34,5 +34,5 @@ for r, l in zip(body, inst_lines):
     n, s = int(r[ii]), int(r[isamp])
     agg[l][0] += n; agg[l][1] += s
     tot[0] += n; tot[1] += s
-for l, (n, s) in sorted(agg.items(), key=lambda kv: -kv[1][1])[:60]:
+for l, (n, s) in sorted(agg.items(), key=lambda kv: -kv[1][1])[:int(sys.argv[4]) if len(sys.argv)>4 else 60]:
     print(f"{str(l):40s} inst {n:12d} {100*n/tot[0]:5.1f}%   samples {s:8d} {100*s/tot[1]:5.1f}%")

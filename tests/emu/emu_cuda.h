@@ -52,6 +52,13 @@ static inline float4 make_float4(float a, float b, float c, float d) { return fl
 static inline int4 make_int4(int a, int b, int c, int d) { return int4{a, b, c, d}; }
 static inline double2 make_double2(double a, double b) { return double2{a, b}; }
 
+static inline double __hiloint2double(int hi, int lo)
+{
+    const uint64_t u = ((uint64_t)(uint32_t)hi << 32) | (uint32_t)lo;
+    double d;
+    memcpy(&d, &u, 8);
+    return d;
+}
 static inline void __syncthreads() {}
 static inline void __syncwarp() {}
 template <typename T> static inline T __ldg(const T *p) { return *p; }
