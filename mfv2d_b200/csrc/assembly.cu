@@ -182,6 +182,7 @@ __device__ __forceinline__ void phase_s1(const AsmArgs &args, double *smem, cons
         load_row<Q>(g, slot + L.slot_w + tb.w * (Q * ldq) + a * ldq);
         double *T = slot + L.slot_t + tb.t_off + a;
         const DevS1Pair *pr = s1 + tb.s1_tab + pb;
+#pragma unroll 2
         for (int n = 0; n < len; ++n)
         {
             const int4 d = *reinterpret_cast<const int4 *>(pr + n);
@@ -213,22 +214,20 @@ __device__ __forceinline__ void phase_s2(const AsmArgs &args, double *smem, cons
         const int j0 = (item >> 4) & 31, l0 = (item >> 9) & 31, pb = (item >> 14) & 255, len = item >> 22;
         const int nB2 = tb.nB2, ld = tb.ld;
         const int jl0 = j0 * nB2 + l0;
-        const bool has2 = jl0 + 1 < tb.nB * nB2;
+        // the item's second column is half the block away, so that the lanes of a warp walk consecutive columns
+        const int nJL = tb.nB * nB2, jl1 = jl0 + ((nJL + 1) >> 1);
+        const bool has2 = jl1 < nJL;
         double *slot = smem + L.off_slots + e * L.slot_stride;
-        const double *T = slot + L.slot_t + tb.t_off + jl0 * ldq;
+        const double *T = slot + L.slot_t + tb.t_off;
         double t0[Q], t1[Q];
-        load_row<Q>(t0, T);
-        load_row<Q>(t1, has2 ? T + ldq : T);
-        int j1 = j0, l1 = l0 + 1;
-        if (l1 == nB2)
-        {
-            l1 = 0;
-            ++j1;
-        }
+        load_row<Q>(t0, T + jl0 * ldq);
+        load_row<Q>(t1, T + (has2 ? jl1 : jl0) * ldq);
+        const int j1 = fast_div(jl1, 1.0f / (float)nB2), l1 = jl1 - j1 * nB2;
         double *D = slot + L.slot_arena + tb.dst_off;
         double *Dd0 = D + (tb.r0 + j0) * ld + tb.c0 + l0, *Df0 = D + (tb.c0 + l0) * ld + tb.r0 + j0;
         double *Dd1 = D + (tb.r0 + j1) * ld + tb.c0 + l1, *Df1 = D + (tb.c0 + l1) * ld + tb.r0 + j1;
         const DevS2Pair *pr = s2 + tb.s2_tab + pb;
+#pragma unroll 2
         for (int n = 0; n < len; ++n)
         {
             const int4 d = *reinterpret_cast<const int4 *>(pr + n);
@@ -351,6 +350,7 @@ __device__ __forceinline__ void emit_tile(const EmitTerm &t, int r0, int nr, int
     {
         const double *Dr = t.D + (r0 + sub) * t.ld;
         const int dstep = rstep * t.ld;
+#pragma unroll 4
         for (int r = sub; r < nr; r += rstep, Dr += dstep, o += ostep)
         {
             double v = rs[0] * Dr[rc[0]];
@@ -370,6 +370,7 @@ __device__ __forceinline__ void emit_tile(const EmitTerm &t, int r0, int nr, int
     {
         const DevIncRow *lt = t.ltab + r0 + sub;
         const double *Dc = t.D + rc[0];
+#pragma unroll 4
         for (int r = sub; r < nr; r += rstep, lt += rstep, o += ostep)
         {
             int li[4];
@@ -455,6 +456,7 @@ __device__ __forceinline__ void emit_stage(const AsmArgs &args, const DevStage &
                 {
                     double *oz = o + (size_t)sub * N;
                     const size_t ostep = (size_t)rstep * N;
+#pragma unroll 4
                     for (int r = sub; r < un.nr; r += rstep, oz += ostep)
                         *oz = 0.0;
                 }

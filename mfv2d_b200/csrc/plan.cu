@@ -7,6 +7,8 @@
 // SURVEY.md (Q1 dense incidence fails, Q2 a dense*dense product drops the accumulated coefficient, Q3
 // SUM only for same-kind operands) - but a dense state is kept as a sum of product chains instead of
 // numbers.  The chains are then lowered to fused device work (assembly.cu, apply.cu).
+#include <cstdlib>
+
 #include "plan.cuh"
 
 namespace
@@ -456,7 +458,7 @@ int plan_finalize_matrix(mfv2d_plan *plan, const std::vector<std::vector<Lowered
     mfv2d_ctx *ctx = plan->ctx;
     const int p = plan->p, q = plan->q, np1 = p + 1;
     const int ldq = asm_ldq(q);
-    const int threads = 256;
+    const int threads = 256; // ASM_THREADS of assembly.cu
 
     // ---- element-independent tables of the blob --------------------------------------------------
     const mfv2d_basis *bs = plan->basis;
@@ -708,10 +710,10 @@ int plan_finalize_matrix(mfv2d_plan *plan, const std::vector<std::vector<Lowered
         for (int bi = sg.block_begin; bi < sg.block_end; ++bi)
         {
             const DevBlock &db = plan->blocks[bi];
-            // tile width: the widest of 32 / 16 / 8 lanes unless a narrower one wastes > 10 % fewer lanes
+            // tile width: 32 lanes, or 16 (one 128-byte row segment per half warp) if that wastes > 10 % fewer lanes
             int cl = 5;
             double best = (double)((db.ncols + 31) / 32 * 32) / db.ncols;
-            for (int c = 4; c >= 3; --c)
+            for (int c = 4; c >= 4; --c)
             {
                 const int w = 1 << c;
                 const double waste = (double)((db.ncols + w - 1) / w * w) / db.ncols;
@@ -947,7 +949,7 @@ int plan_finalize_matrix(mfv2d_plan *plan, const std::vector<std::vector<Lowered
                 for (int sub = 0; sub < tb.n_sub2; ++sub)
                 {
                     const int pb = sub * np / tb.n_sub2, pe = (sub + 1) * np / tb.n_sub2;
-                    for (int jl = 0; jl < nJL; jl += 2)
+                    for (int jl = 0; jl < (nJL + 1) / 2; ++jl) // columns jl and jl + ceil(nJL / 2)
                         xtab.push_back((t - rd.tb_begin) | ((jl / tb.nB2) << 4) | ((jl % tb.nB2) << 9) | (pb << 14) |
                                        ((pe - pb) << 22));
                 }
@@ -983,6 +985,22 @@ int plan_finalize_matrix(mfv2d_plan *plan, const std::vector<std::vector<Lowered
     if ((size_t)L.smem_bytes > ctx->smem_optin)
         return mfv2d_fail(ctx, MFV2D_CUDA_UNSUPPORTED, "assembly kernel needs %d bytes of shared memory (order %d, %d points)",
                           L.smem_bytes, p, q);
+    if (getenv("MFV2D_PLAN_DEBUG"))
+    {
+        fprintf(stderr, "[mfv2d plan] p %d q %d ldq %d: %zu stages, %zu dense, %zu tensor blocks, %zu units; epb %d, slot %d doubles "
+                        "(W %d, T %d, arena %d), blob %d B, smem %d B%s\n",
+                p, q, ldq, plan->stages.size(), plan->dense.size(), plan->tbs.size(), plan->units.size(), epb, L.slot_stride,
+                L.slot_t, L.slot_arena - L.slot_t, slot_a, L.blob_bytes, L.smem_bytes, serial ? ", serial rounds" : "");
+        for (size_t r = 0; r < plan->rounds.size(); ++r)
+        {
+            const DevRound &rd = plan->rounds[r];
+            fprintf(stderr, "  round %zu: S1 %d items/element, S2 %d items/element;", r, rd.x1_count, rd.x2_count);
+            for (int t = rd.tb_begin; t < rd.tb_end; ++t)
+                fprintf(stderr, " tb%d(%dx%d pairs, chunks %d/%d)", t, pk_pairs(plan->tbs[t].pkB, p), pk_pairs(plan->tbs[t].pkA, p),
+                        plan->tbs[t].n_sub1, plan->tbs[t].n_sub2);
+            fprintf(stderr, "\n");
+        }
+    }
     if (plan->d_blob)
         mfv2d_cuda_free(ctx, plan->d_blob);
     plan->d_blob = nullptr;
