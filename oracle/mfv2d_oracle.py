@@ -4,7 +4,7 @@ This file is the *checker*: only ``tests/``, ``__graft_entry__.smoke()`` and the
 ``cpu_baseline`` / ``--impl reference`` legs of ``bench.py`` may import it.  Nothing under
 ``mfv2d_b200/`` imports it, and the product path has no CPU fallback.
 
-Parity pin: every function here is checked in ``tests/test_oracle_vs_ref.py`` against the
+Parity pin: every function here is checked in ``tests/test_oracle.py (test_oracle_vs_live_reference)`` against the
 reference's own C extension compiled from /root/reference by ``oracle/build_ref.sh``
 (``oracle/_ref/_mfv2d_ref.so``) and against the committed fixtures in ``tests/golden``
 that were generated with the reference (``tests/golden/make_golden.py``).
