@@ -435,6 +435,343 @@ __global__ void __launch_bounds__(APPLY_THREADS) element_vector_kernel(const App
     }
 }
 
+// =====================================================================================================
+// Warp-per-element variant (the fast path): the same programs, but every element is handled by ONE warp
+// with its working vectors in a private shared-memory region, so that the phases are separated by
+// __syncwarp() instead of CTA barriers and the warps of a CTA run independently (they only share the
+// basis tables).  The Jacobian is recomputed from the corner coordinates held in registers wherever a
+// metric weight is needed.  Programs that contain an inverse mass and the column mode use the
+// CTA-per-element kernel above.
+// =====================================================================================================
+#define APPLYW_WARPS 8
+
+struct WarpView
+{
+    const double *node, *edge, *pnts, *wgts;
+    double *u0, *u1; // q^2 each
+    double *tmp;     // 2 (p+1) q
+    double *v0, *v1; // ping-pong coefficient vectors
+    double *xs, *ys; // N each
+    double cs[8];    // corners (registers)
+};
+
+// u[a][b] = sum_i A[i][a] sum_j c[i*nB + j] B[j][b]
+__device__ __forceinline__ void interp_w(const WarpView &s, int q, const double *__restrict__ c, const double *__restrict__ A,
+                                         int nA, const double *__restrict__ B, int nB, double *__restrict__ u)
+{
+    const float inv_q = 1.0f / (float)q;
+    for (int idx = MFV2D_LANE0; idx < nA * q; idx += MFV2D_LANE_STEP)
+    {
+        const int i = (int)(((float)idx + 0.5f) * inv_q), b = idx - i * q;
+        const double *ci = c + i * nB;
+        double r0 = 0.0, r1 = 0.0;
+        int j = 0;
+        for (; j + 1 < nB; j += 2)
+        {
+            r0 = fma(ci[j], B[j * q + b], r0);
+            r1 = fma(ci[j + 1], B[(j + 1) * q + b], r1);
+        }
+        if (j < nB)
+            r0 = fma(ci[j], B[j * q + b], r0);
+        s.tmp[idx] = r0 + r1;
+    }
+    __syncwarp();
+    for (int idx = MFV2D_LANE0; idx < q * q; idx += MFV2D_LANE_STEP)
+    {
+        const int a = (int)(((float)idx + 0.5f) * inv_q), b = idx - a * q;
+        double r0 = 0.0, r1 = 0.0;
+        int i = 0;
+        for (; i + 1 < nA; i += 2)
+        {
+            r0 = fma(A[i * q + a], s.tmp[i * q + b], r0);
+            r1 = fma(A[(i + 1) * q + a], s.tmp[(i + 1) * q + b], r1);
+        }
+        if (i < nA)
+            r0 = fma(A[i * q + a], s.tmp[i * q + b], r0);
+        u[idx] = r0 + r1;
+    }
+    __syncwarp();
+}
+
+// out[i*nB + j] = sum_a A[i][a] sum_b B[j][b] g[a][b]
+__device__ __forceinline__ void project_w(const WarpView &s, int q, const double *__restrict__ g, const double *__restrict__ A,
+                                          int nA, const double *__restrict__ B, int nB, double *__restrict__ out)
+{
+    const float inv_q = 1.0f / (float)q, inv_nb = 1.0f / (float)nB;
+    for (int idx = MFV2D_LANE0; idx < nA * q; idx += MFV2D_LANE_STEP)
+    {
+        const int i = (int)(((float)idx + 0.5f) * inv_q), b = idx - i * q;
+        const double *Ai = A + i * q;
+        double r0 = 0.0, r1 = 0.0;
+        int a = 0;
+        for (; a + 1 < q; a += 2)
+        {
+            r0 = fma(Ai[a], g[a * q + b], r0);
+            r1 = fma(Ai[a + 1], g[(a + 1) * q + b], r1);
+        }
+        if (a < q)
+            r0 = fma(Ai[a], g[a * q + b], r0);
+        s.tmp[idx] = r0 + r1;
+    }
+    __syncwarp();
+    for (int idx = MFV2D_LANE0; idx < nA * nB; idx += MFV2D_LANE_STEP)
+    {
+        const int i = (int)(((float)idx + 0.5f) * inv_nb), j = idx - i * nB;
+        const double *Bj = B + j * q, *ti = s.tmp + i * q;
+        double r0 = 0.0, r1 = 0.0;
+        int b = 0;
+        for (; b + 1 < q; b += 2)
+        {
+            r0 = fma(Bj[b], ti[b], r0);
+            r1 = fma(Bj[b + 1], ti[b + 1], r1);
+        }
+        if (b < q)
+            r0 = fma(Bj[b], ti[b], r0);
+        out[idx] = r0 + r1;
+    }
+    __syncwarp();
+}
+
+// pointwise metric scaling (modes as scale_points above), Jacobian recomputed from the corners
+__device__ __forceinline__ void scale_points_w(const WarpView &s, int q, int mode, const double *__restrict__ fld)
+{
+    const int q2 = q * q;
+    const float inv_q = 1.0f / (float)q;
+    const double x0 = s.cs[0], y0 = s.cs[1], x1 = s.cs[2], y1 = s.cs[3], x2 = s.cs[4], y2 = s.cs[5], x3 = s.cs[6], y3 = s.cs[7];
+    for (int idx = MFV2D_LANE0; idx < q2; idx += MFV2D_LANE_STEP)
+    {
+        const int a = (int)(((float)idx + 0.5f) * inv_q), b = idx - a * q;
+        const double eta = s.pnts[a], xi = s.pnts[b];
+        const double w = s.wgts[a] * s.wgts[b];
+        const double j00 = 0.25 * ((x1 - x0) * (1 - eta) + (x2 - x3) * (1 + eta));
+        const double j01 = 0.25 * ((y1 - y0) * (1 - eta) + (y2 - y3) * (1 + eta));
+        const double j10 = 0.25 * ((x3 - x0) * (1 - xi) + (x2 - x1) * (1 + xi));
+        const double j11 = 0.25 * ((y3 - y0) * (1 - xi) + (y2 - y1) * (1 + xi));
+        const double det = j00 * j11 - j10 * j01;
+        const double a0 = s.u0[idx];
+        switch (mode)
+        {
+        case 0:
+            s.u0[idx] = a0 * det * w;
+            break;
+        case 1:
+            s.u0[idx] = a0 * w / det;
+            break;
+        case 2: {
+            const double a1 = s.u1[idx];
+            const double khh = (j11 * j11 + j10 * j10) / det * w, kvv = (j00 * j00 + j01 * j01) / det * w,
+                         khv = (j01 * j11 + j00 * j10) / det * w;
+            s.u0[idx] = khh * a0 + khv * a1;
+            s.u1[idx] = khv * a0 + kvv * a1;
+            break;
+        }
+        case 3:
+        case 4: {
+            const double fx = fld[2 * idx], fy = fld[2 * idx + 1];
+            const double kh = (fx * j11 - fy * j10) * w, kv = -(fy * j00 - fx * j01) * w;
+            if (mode == 3)
+                s.u0[idx] = kh * a0 + kv * s.u1[idx];
+            else
+            {
+                s.u0[idx] = kh * a0;
+                s.u1[idx] = kv * a0;
+            }
+            break;
+        }
+        default: {
+            const double fx = fld[2 * idx], fy = fld[2 * idx + 1];
+            const double kh = -(fx * j10 + fy * j11) / det * w, kv = -(fx * j00 + fy * j01) / det * w;
+            if (mode == 6)
+                s.u0[idx] = kh * a0 + kv * s.u1[idx];
+            else
+            {
+                s.u0[idx] = kh * a0;
+                s.u1[idx] = kv * a0;
+            }
+            break;
+        }
+        }
+    }
+    __syncwarp();
+}
+
+struct ApplyWArgs
+{
+    ApplyArgs a;
+    int prog_len, n_coef, inc_rows; // sizes of the program / coefficient / incidence tables staged in shared memory
+    int warp_doubles;               // private doubles per warp
+};
+
+__global__ void __launch_bounds__(APPLYW_WARPS * 32) element_vector_warp_kernel(const ApplyWArgs wa)
+{
+    MFV2D_DYN_SMEM(double, smem);
+    const ApplyArgs &args = wa.a;
+    const int p = args.p, q = args.q, q2 = q * q, np1 = p + 1, nh = p * (p + 1);
+    const int N = args.n_total;
+    // CTA-shared: tables | coefficients | program | incidence maps
+    double *coef = smem + ((args.tab_len + 1) & ~1);
+    int *prog = reinterpret_cast<int *>(coef + ((wa.n_coef + 1) & ~1));
+    int4 *inc = reinterpret_cast<int4 *>(prog + ((wa.prog_len + 3) & ~3));
+    double *priv = reinterpret_cast<double *>(inc + wa.inc_rows);
+    for (int i = threadIdx.x; i < args.tab_len; i += blockDim.x)
+        smem[i] = args.tab[i];
+    for (int i = threadIdx.x; i < wa.n_coef; i += blockDim.x)
+        coef[i] = args.coef[i];
+    for (int i = threadIdx.x; i < wa.prog_len; i += blockDim.x)
+        prog[i] = args.prog[i];
+    for (int i = threadIdx.x; i < wa.inc_rows; i += blockDim.x)
+        inc[i] = reinterpret_cast<const int4 *>(args.inc)[i];
+    __syncthreads();
+
+    const int warp = threadIdx.x >> 5, nwarps = MFV2D_NWARPS;
+    WarpView s;
+    s.node = smem;
+    s.edge = s.node + np1 * q;
+    s.pnts = s.edge + p * q;
+    s.wgts = s.pnts + q;
+    double *w = priv + (size_t)warp * wa.warp_doubles;
+    s.u0 = w;
+    w += q2;
+    s.u1 = w;
+    w += q2;
+    s.tmp = w;
+    w += 2 * np1 * q;
+    s.v0 = w;
+    w += args.vmax;
+    s.v1 = w;
+    w += args.vmax;
+    s.xs = w;
+    w += N;
+    s.ys = w;
+    const int n_terms = prog[0];
+
+    for (unsigned long long elem = (unsigned long long)blockIdx.x * nwarps + warp; elem < args.n_elem;
+         elem += (unsigned long long)gridDim.x * nwarps)
+    {
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+            s.cs[i] = ld_ro(args.corners + elem * 8 + i);
+        __syncwarp();
+        for (int i = MFV2D_LANE0; i < N; i += MFV2D_LANE_STEP)
+        {
+            s.xs[i] = args.x[elem * N + i];
+            s.ys[i] = 0.0;
+        }
+        __syncwarp();
+        int pc = 1;
+        for (int t = 0; t < n_terms; ++t)
+        {
+            const int rf = prog[pc], cf = prog[pc + 1], ci = prog[pc + 2], nfac = prog[pc + 3];
+            pc += 4;
+            const int c0 = args.form_offsets[cf];
+            const int r0 = args.form_offsets[rf];
+            // the first factor reads the input segment in place
+            const double *cur = s.xs + c0;
+            double *nxt = s.v0;
+            int n_cur = args.form_offsets[cf + 1] - c0;
+            for (int f = 0; f < nfac; ++f, pc += 4)
+            {
+                const int type = prog[pc], fa = prog[pc + 1], fb = prog[pc + 2], fc = prog[pc + 3];
+                int n_out;
+                if (type == 0)
+                {
+                    const int rows = (fa == MFV2D_INC_10 || fa == MFV2D_INC_21_T) ? 2 * nh : (fa == MFV2D_INC_21 ? p * p : np1 * np1);
+                    const int4 *map = inc + args.inc_off[fa];
+                    for (int r = MFV2D_LANE0; r < rows; r += MFV2D_LANE_STEP)
+                    {
+                        const int4 e = map[r];
+                        const int ev[4] = {e.x, e.y, e.z, e.w};
+                        double acc = 0.0;
+#pragma unroll
+                        for (int k = 0; k < 4; ++k)
+                        {
+                            if (ev[k] == 0)
+                                break;
+                            const double v = cur[abs(ev[k]) - 1];
+                            acc += ev[k] < 0 ? -v : v;
+                        }
+                        nxt[r] = acc;
+                    }
+                    __syncwarp();
+                    n_out = rows;
+                }
+                else if (type == 1)
+                {
+                    if (fa == DK_MASS0)
+                    {
+                        interp_w(s, q, cur, s.node, np1, s.node, np1, s.u0);
+                        scale_points_w(s, q, 0, nullptr);
+                        project_w(s, q, s.u0, s.node, np1, s.node, np1, nxt);
+                        n_out = np1 * np1;
+                    }
+                    else if (fa == DK_MASS2)
+                    {
+                        interp_w(s, q, cur, s.edge, p, s.edge, p, s.u0);
+                        scale_points_w(s, q, 1, nullptr);
+                        project_w(s, q, s.u0, s.edge, p, s.edge, p, nxt);
+                        n_out = p * p;
+                    }
+                    else
+                    {
+                        interp_w(s, q, cur, s.node, np1, s.edge, p, s.u0);      // h part
+                        interp_w(s, q, cur + nh, s.edge, p, s.node, np1, s.u1); // v part
+                        scale_points_w(s, q, 2, nullptr);
+                        project_w(s, q, s.u0, s.node, np1, s.edge, p, nxt);
+                        project_w(s, q, s.u1, s.edge, p, s.node, np1, nxt + nh);
+                        n_out = 2 * nh;
+                    }
+                }
+                else
+                {
+                    const double *fld = args.fields[fb] + elem * (unsigned long long)(2 * q2);
+                    if (fa == DK_IPROD1 && !fc)
+                    { // (n0 x n1): 1-form in, 0-form out
+                        interp_w(s, q, cur, s.node, np1, s.edge, p, s.u0);
+                        interp_w(s, q, cur + nh, s.edge, p, s.node, np1, s.u1);
+                        scale_points_w(s, q, 3, fld);
+                        project_w(s, q, s.u0, s.node, np1, s.node, np1, nxt);
+                        n_out = np1 * np1;
+                    }
+                    else if (fa == DK_IPROD1)
+                    { // transposed: 0-form in, 1-form out
+                        interp_w(s, q, cur, s.node, np1, s.node, np1, s.u0);
+                        scale_points_w(s, q, 4, fld);
+                        project_w(s, q, s.u0, s.node, np1, s.edge, p, nxt);
+                        project_w(s, q, s.u1, s.edge, p, s.node, np1, nxt + nh);
+                        n_out = 2 * nh;
+                    }
+                    else if (!fc)
+                    { // (n1 x n2): 2-form in, 1-form out
+                        interp_w(s, q, cur, s.edge, p, s.edge, p, s.u0);
+                        scale_points_w(s, q, 5, fld);
+                        project_w(s, q, s.u0, s.node, np1, s.edge, p, nxt);
+                        project_w(s, q, s.u1, s.edge, p, s.node, np1, nxt + nh);
+                        n_out = 2 * nh;
+                    }
+                    else
+                    { // transposed: 1-form in, 2-form out
+                        interp_w(s, q, cur, s.node, np1, s.edge, p, s.u0);
+                        interp_w(s, q, cur + nh, s.edge, p, s.node, np1, s.u1);
+                        scale_points_w(s, q, 6, fld);
+                        project_w(s, q, s.u0, s.edge, p, s.edge, p, nxt);
+                        n_out = p * p;
+                    }
+                }
+                cur = nxt;
+                nxt = (nxt == s.v0) ? s.v1 : s.v0;
+                n_cur = n_out;
+            }
+            const double cf_ = coef[ci];
+            for (int i = MFV2D_LANE0; i < n_cur; i += MFV2D_LANE_STEP)
+                s.ys[r0 + i] = fma(cf_, cur[i], s.ys[r0 + i]);
+            __syncwarp();
+        }
+        for (int i = MFV2D_LANE0; i < N; i += MFV2D_LANE_STEP)
+            args.y[elem * N + i] = s.ys[i];
+        __syncwarp();
+    }
+}
+
 static int launch_apply(const mfv2d_plan *plan, const mfv2d_elements *e, const double *const *fields, const double *d_x,
                         double *d_y, int column_mode)
 {
@@ -470,6 +807,38 @@ static int launch_apply(const mfv2d_plan *plan, const mfv2d_elements *e, const d
         const int ldT = (np1 * np1 + 3) & ~3;
         const int nmax = 2 * p * np1;
         doubles += ((q2 + 1) & ~1) + q * ldT + 4 + (size_t)nmax * nmax + 8;
+    }
+    if (!column_mode && !plan->vector_needs_dense && e->n > 0)
+    {
+        // fast path: one warp per element
+        ApplyWArgs wa{};
+        wa.a = a;
+        const int n_prog_total = (int)plan->vprog.size(), n_coef_total = (int)plan->vcoef.size();
+        wa.prog_len = plan->mprog_off ? plan->mprog_off : n_prog_total;
+        wa.n_coef = plan->mcoef_off ? plan->mcoef_off : n_coef_total;
+        wa.inc_rows = plan->basis->inc_off[4];
+        wa.warp_doubles = (2 * q2 + 2 * np1 * q + 2 * a.vmax + 2 * a.n_total + 3) & ~1;
+        const size_t shared_part = (((size_t)a.tab_len + 1) & ~(size_t)1) * 8 + (((size_t)wa.n_coef + 1) & ~(size_t)1) * 8 +
+                                   (((size_t)wa.prog_len + 3) & ~(size_t)3) * 4 + (size_t)wa.inc_rows * 16;
+        const size_t smem_w = shared_part + (size_t)APPLYW_WARPS * wa.warp_doubles * 8;
+        if (smem_w <= ctx->smem_optin)
+        {
+            MFV2D_CUDA_CHECK(ctx, cudaFuncSetAttribute(element_vector_warp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                       (int)smem_w));
+            int per_sm_w = 1;
+            MFV2D_CUDA_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_w, element_vector_warp_kernel,
+                                                                                APPLYW_WARPS * 32, smem_w));
+            if (per_sm_w < 1)
+                per_sm_w = 1;
+            unsigned long long grid_w = (unsigned long long)ctx->sm_count * per_sm_w;
+            const unsigned long long need = (e->n + APPLYW_WARPS - 1) / APPLYW_WARPS;
+            if (grid_w > need)
+                grid_w = need;
+            MFV2D_LAUNCH(element_vector_warp_kernel, (unsigned)grid_w, APPLYW_WARPS * 32, smem_w, ctx->stream, wa);
+            ctx->launches++;
+            MFV2D_CUDA_CHECK(ctx, cudaGetLastError());
+            return MFV2D_SUCCESS;
+        }
     }
     const size_t smem = doubles * sizeof(double);
     if (smem > ctx->smem_optin)
