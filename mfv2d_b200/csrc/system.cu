@@ -62,14 +62,67 @@ struct mfv2d_system
 #define SYS_THREADS 256
 
 // ---- kernels -------------------------------------------------------------------------------------
-// y_e = M_e x_e for dense row-major blocks; one CTA per element, one warp per row, lanes over columns
+// y_e = M_e x_e for dense row-major blocks (LinearSystem.apply_diagonal / apply_diagonal_inverse with the stored
+// inverse, src/algebra/sparse_system.c:3-77).  HBM-read bound: 8 N_e^2 + 16 N_e bytes per element.
+// One CTA per element; a quarter warp (8 lanes) owns a row and reads it with 16-byte loads (VEC: even n and a
+// 16-byte aligned block) - four rows per warp and up to four loads per lane are in flight before the
+// 3-step shuffle reduction, which is what keeps enough bytes in flight per SM.
+template <bool VEC>
+__device__ __forceinline__ void block_gemv_rows(const double *__restrict__ A, const double *__restrict__ xs, double *__restrict__ y,
+                                                int n)
+{
+    const int warp = threadIdx.x >> 5, nwarps = MFV2D_NWARPS;
+#ifndef MFV2D_EMU
+    const int lane = threadIdx.x & 31, sub = lane >> 3, l8 = lane & 7;
+    for (int r0 = warp * 4; r0 < n; r0 += nwarps * 4)
+    {
+        const int r = r0 + sub;
+        double acc0 = 0.0, acc1 = 0.0;
+        if (r < n)
+        {
+            const double *row = A + (size_t)r * n;
+            if (VEC)
+            {
+#pragma unroll 4
+                for (int c = 2 * l8; c < n; c += 16)
+                {
+                    const double2 a = __ldcs(reinterpret_cast<const double2 *>(row + c));
+                    const double2 x = *reinterpret_cast<const double2 *>(xs + c);
+                    acc0 = fma(a.x, x.x, acc0);
+                    acc1 = fma(a.y, x.y, acc1);
+                }
+            }
+            else
+            {
+#pragma unroll 4
+                for (int c = l8; c < n; c += 8)
+                    acc0 = fma(__ldcs(row + c), xs[c], acc0);
+            }
+        }
+        double acc = acc0 + acc1;
+        acc += __shfl_xor_sync(0xffffffffu, acc, 4);
+        acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+        acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+        if (l8 == 0 && r < n)
+            y[r] = acc;
+    }
+#else
+    for (int r = warp; r < n; r += nwarps)
+    {
+        double acc = 0.0;
+        for (int c = 0; c < n; ++c)
+            acc = fma(A[(size_t)r * n + c], xs[c], acc);
+        y[r] = acc;
+    }
+#endif
+}
+
 __global__ void __launch_bounds__(SYS_THREADS) block_gemv_kernel(unsigned long long n_elem, const int64_t *__restrict__ boff,
                                                                 const int64_t *__restrict__ moff,
                                                                 const double *__restrict__ M, const double *__restrict__ x,
                                                                 double *__restrict__ y)
 {
     MFV2D_DYN_SMEM(double, xs);
-    const int warp = threadIdx.x >> 5, nwarps = MFV2D_NWARPS;
     for (unsigned long long e = blockIdx.x; e < n_elem; e += gridDim.x)
     {
         const int64_t o = boff[e];
@@ -79,16 +132,10 @@ __global__ void __launch_bounds__(SYS_THREADS) block_gemv_kernel(unsigned long l
         for (int i = threadIdx.x; i < n; i += blockDim.x)
             xs[i] = x[o + i];
         __syncthreads();
-        for (int r = warp; r < n; r += nwarps)
-        {
-            const double *row = A + (size_t)r * n;
-            double acc = 0.0;
-            for (int c = MFV2D_LANE0; c < n; c += MFV2D_LANE_STEP)
-                acc = fma(row[c], xs[c], acc);
-            acc = warp_sum(acc);
-            if (MFV2D_LANE0 == 0)
-                y[o + r] = acc;
-        }
+        if ((n & 1) == 0 && (reinterpret_cast<size_t>(A) & 15) == 0)
+            block_gemv_rows<true>(A, xs, y + o, n);
+        else
+            block_gemv_rows<false>(A, xs, y + o, n);
     }
 }
 
@@ -146,7 +193,8 @@ __global__ void __launch_bounds__(SYS_THREADS) schur_local_kernel(unsigned long 
     if (done && *done)
         return;
     const int warp = threadIdx.x >> 5, nwarps = MFV2D_NWARPS;
-    double *lam = lam_all + (size_t)warp * max_m;
+    double *lam = lam_all + (size_t)warp * (max_m + 32);
+    double *part = lam + max_m; // 32 doubles: partial sums of the column groups
     for (unsigned long long e = (unsigned long long)blockIdx.x * nwarps + warp; e < n_elem; e += (unsigned long long)gridDim.x * nwarps)
     {
         const int64_t s0 = slot_off[e];
@@ -156,9 +204,36 @@ __global__ void __launch_bounds__(SYS_THREADS) schur_local_kernel(unsigned long 
         for (int i = MFV2D_LANE0; i < m; i += MFV2D_LANE_STEP)
             lam[i] = t[slot_trace[s0 + i]];
         __syncwarp();
+#ifndef MFV2D_EMU
+        if (m <= 16)
+        {
+            // 32 / m column groups work side by side on the (coalesced) columns of S_e, then fold
+            const int lane = threadIdx.x & 31;
+            const int G = 32 / m, g = lane / m, r = lane - g * m;
+            double acc = 0.0;
+            if (g < G)
+            {
+#pragma unroll 4
+                for (int s = g; s < m; s += G)
+                    acc = fma(__ldcs(Se + (size_t)s * m + r), lam[s], acc);
+            }
+            __syncwarp();
+            part[lane] = acc;
+            __syncwarp();
+            if (lane < m)
+            {
+                double v = 0.0;
+                for (int k = 0; k < G; ++k)
+                    v += part[k * m + lane];
+                slot_val[s0 + lane] = v;
+            }
+            continue;
+        }
+#endif
         for (int r = MFV2D_LANE0; r < m; r += MFV2D_LANE_STEP)
         {
             double acc = 0.0;
+#pragma unroll 4
             for (int s = 0; s < m; ++s)
                 acc = fma(Se[(size_t)s * m + r], lam[s], acc);
             slot_val[s0 + r] = acc;
@@ -214,15 +289,20 @@ __global__ void __launch_bounds__(SYS_THREADS) dot_partial_kernel(long long n, c
     block_reduce_store(acc, partials);
 }
 
+// deterministic sum of the per-CTA partials by ONE warp (launch <<<1, 32>>>): lane-strided, then a butterfly
+__device__ __forceinline__ double warp_sum_partials(int n_partials, const double *__restrict__ partials)
+{
+    double s = 0.0;
+    for (int i = MFV2D_LANE0; i < n_partials; i += MFV2D_LANE_STEP)
+        s += partials[i];
+    return warp_sum(s);
+}
+
 __global__ void sum_partials_kernel(int n_partials, const double *__restrict__ partials, double *__restrict__ result)
 {
-    if (blockIdx.x == 0 && threadIdx.x == 0)
-    {
-        double s = 0.0;
-        for (int i = 0; i < n_partials; ++i)
-            s += partials[i];
+    const double s = warp_sum_partials(n_partials, partials);
+    if (threadIdx.x == 0)
         *result = s;
-    }
 }
 
 __global__ void axpby_kernel(long long n, double a, const double *__restrict__ x, double b, const double *__restrict__ y,
@@ -238,11 +318,9 @@ __global__ void axpby_kernel(long long n, double a, const double *__restrict__ x
 __global__ void cg_alpha_kernel(int n_partials, const double *__restrict__ partials, double *__restrict__ sc, int *flags,
                                 int precond)
 {
+    const double s = warp_sum_partials(n_partials, partials);
     if (blockIdx.x == 0 && threadIdx.x == 0 && !flags[0])
     {
-        double s = 0.0;
-        for (int i = 0; i < n_partials; ++i)
-            s += partials[i];
         sc[1] = s;
         sc[2] = (precond ? sc[5] : sc[0]) / s;
     }
@@ -282,14 +360,10 @@ __global__ void __launch_bounds__(SYS_THREADS) cg_update_kernel(long long n, con
 __global__ void cg_beta_kernel(int n_partials, const double *__restrict__ partials, const double *__restrict__ partials2,
                                double *__restrict__ sc, int *flags, int precond, int iter)
 {
+    const double s = warp_sum_partials(n_partials, partials);
+    const double s2 = precond ? warp_sum_partials(n_partials, partials2) : 0.0;
     if (blockIdx.x == 0 && threadIdx.x == 0 && !flags[0])
     {
-        double s = 0.0, s2 = 0.0;
-        for (int i = 0; i < n_partials; ++i)
-            s += partials[i];
-        if (precond)
-            for (int i = 0; i < n_partials; ++i)
-                s2 += partials2[i];
         flags[1] = iter;
         if (s < sc[4])
         {
@@ -370,7 +444,7 @@ static int sys_gemv(const mfv2d_system *s, const double *M, const double *x, dou
     mfv2d_ctx *ctx = s->ctx;
     if (s->n_elem == 0)
         return MFV2D_SUCCESS;
-    long long grid = (long long)ctx->sm_count * 4;
+    long long grid = (long long)ctx->sm_count * 8;
     if (grid > s->n_elem)
         grid = s->n_elem;
     MFV2D_LAUNCH(block_gemv_kernel, (unsigned)grid, SYS_THREADS, (size_t)(s->max_n + 2) * sizeof(double), ctx->stream,
@@ -437,7 +511,7 @@ static int sys_apply_schur(const mfv2d_system *s, const double *t_in, double *t_
         const long long cap = (long long)ctx->sm_count * 8;
         if (grid > cap)
             grid = cap;
-        MFV2D_LAUNCH(schur_local_kernel, (unsigned)grid, SYS_THREADS, (size_t)warps * (s->max_m + 1) * sizeof(double), ctx->stream,
+        MFV2D_LAUNCH(schur_local_kernel, (unsigned)grid, SYS_THREADS, (size_t)warps * (s->max_m + 1 + 32) * sizeof(double), ctx->stream,
                      (unsigned long long)s->n_elem, s->d_slot_off, s->d_slot_trace, s->d_s_off, s->d_S, t_in, s->d_slot_val,
                      s->max_m + 1, done);
         ctx->launches++;
