@@ -364,7 +364,10 @@ __global__ void cg_beta_kernel(int n_partials, const double *__restrict__ partia
     const double s2 = precond ? warp_sum_partials(n_partials, partials2) : 0.0;
     if (blockIdx.x == 0 && threadIdx.x == 0 && !flags[0])
     {
-        flags[1] = iter;
+        // flags[1] = index of the last iteration carried out (the reference's iter_cnt), counted on the device so
+        // that the launches of an iteration do not depend on it (CUDA graph replay); iter < 0 selects the counter
+        flags[1] = iter >= 0 ? iter : flags[3];
+        flags[3] += 1;
         if (s < sc[4])
         {
             sc[0] = s;
@@ -951,50 +954,83 @@ int mfv2d_cuda_solve_schur_cg(mfv2d_system *s, const double *rhs, const double *
             }
             cudaMemcpyAsync(p, res, nt * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream);
             const int check_every = 16;
+            // one CG iteration = 7 small launches; on one GPU a block of check_every iterations is captured ONCE
+            // into a CUDA graph and replayed (the kernels stop by themselves once the device flag is set)
+            auto enqueue_iteration = [&]() -> int {
+                MFV2D_TRY(sys_apply_schur(s, p, ap, flags));
+                MFV2D_LAUNCH(dot_partial_kernel, (unsigned)s->n_partials, SYS_THREADS, 0, ctx->stream, nt, (const double *)ap,
+                             (const double *)p, w, s->d_partials, (const int *)flags);
+                if (ctx->n_ranks > 1)
+                {
+                    MFV2D_LAUNCH(sum_partials_kernel, 1, 32, 0, ctx->stream, s->n_partials, (const double *)s->d_partials,
+                                 s->d_partials);
+                    MFV2D_TRY(comm_allreduce(ctx, s->d_partials, 1));
+                    MFV2D_LAUNCH(cg_alpha_kernel, 1, 32, 0, ctx->stream, 1, (const double *)s->d_partials, sc, flags, 0);
+                    ctx->launches++;
+                }
+                else
+                    MFV2D_LAUNCH(cg_alpha_kernel, 1, 32, 0, ctx->stream, s->n_partials, (const double *)s->d_partials, sc, flags,
+                                 0);
+                MFV2D_LAUNCH(cg_update_kernel, (unsigned)s->n_partials, SYS_THREADS, 0, ctx->stream, nt, (const double *)sc,
+                             (const int *)flags, (const double *)p, (const double *)ap, lam, res, w, (const double *)nullptr, z,
+                             s->d_partials, s->d_partials + s->n_partials);
+                if (ctx->n_ranks > 1)
+                {
+                    MFV2D_LAUNCH(sum_partials_kernel, 1, 32, 0, ctx->stream, s->n_partials, (const double *)s->d_partials,
+                                 s->d_partials);
+                    MFV2D_TRY(comm_allreduce(ctx, s->d_partials, 1));
+                    MFV2D_LAUNCH(cg_beta_kernel, 1, 32, 0, ctx->stream, 1, (const double *)s->d_partials,
+                                 (const double *)s->d_partials, sc, flags, 0, -1);
+                    ctx->launches++;
+                }
+                else
+                    MFV2D_LAUNCH(cg_beta_kernel, 1, 32, 0, ctx->stream, s->n_partials, (const double *)s->d_partials,
+                                 (const double *)(s->d_partials + s->n_partials), sc, flags, 0, -1);
+                MFV2D_LAUNCH(cg_direction_kernel, grid_for(ctx, nt, 256), 256, 0, ctx->stream, nt, (const double *)sc,
+                             (const int *)flags, (const double *)res, p);
+                ctx->launches += 5;
+                return MFV2D_SUCCESS;
+            };
+#ifndef MFV2D_EMU
+            cudaGraphExec_t graph_exec = nullptr;
+            if (ctx->n_ranks == 1 && max_iter >= 2 * check_every)
+            {
+                cudaGraph_t graph = nullptr;
+                const uint64_t launches_before = ctx->launches;
+                if (cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeThreadLocal) == cudaSuccess)
+                {
+                    int rc = MFV2D_SUCCESS;
+                    for (int k = 0; k < check_every && rc == MFV2D_SUCCESS; ++k)
+                        rc = enqueue_iteration();
+                    const cudaError_t ce = cudaStreamEndCapture(ctx->stream, &graph);
+                    if (rc != MFV2D_SUCCESS || ce != cudaSuccess || cudaGraphInstantiate(&graph_exec, graph, 0) != cudaSuccess)
+                        graph_exec = nullptr;
+                    if (graph)
+                        cudaGraphDestroy(graph);
+                }
+                cudaGetLastError();
+                ctx->launches = launches_before; // capturing is not launching
+            }
+#endif
             int it = 0;
             bool finished = false;
             while (it < max_iter && !finished)
             {
                 const int stop = (it + check_every < max_iter) ? it + check_every : max_iter;
-                for (; it < stop; ++it)
+#ifndef MFV2D_EMU
+                if (graph_exec && stop - it == check_every)
                 {
-                    // ap = S p ; pAp ; alpha
-                    if ((r = sys_apply_schur(s, p, ap, flags)))
+                    if (cudaGraphLaunch(graph_exec, ctx->stream) != cudaSuccess)
+                    {
+                        r = mfv2d_fail(ctx, MFV2D_CUDA_ERROR, "CG graph launch failed: %s", cudaGetErrorString(cudaGetLastError()));
                         break;
-                    MFV2D_LAUNCH(dot_partial_kernel, (unsigned)s->n_partials, SYS_THREADS, 0, ctx->stream, nt, (const double *)ap,
-                                 (const double *)p, w, s->d_partials, (const int *)flags);
-                    if (ctx->n_ranks > 1)
-                    {
-                        MFV2D_LAUNCH(sum_partials_kernel, 1, 32, 0, ctx->stream, s->n_partials, (const double *)s->d_partials,
-                                     s->d_partials);
-                        if ((r = comm_allreduce(ctx, s->d_partials, 1)))
-                            break;
-                        MFV2D_LAUNCH(cg_alpha_kernel, 1, 32, 0, ctx->stream, 1, (const double *)s->d_partials, sc, flags, 0);
-                        ctx->launches++;
                     }
-                    else
-                        MFV2D_LAUNCH(cg_alpha_kernel, 1, 32, 0, ctx->stream, s->n_partials, (const double *)s->d_partials, sc,
-                                     flags, 0);
-                    MFV2D_LAUNCH(cg_update_kernel, (unsigned)s->n_partials, SYS_THREADS, 0, ctx->stream, nt, (const double *)sc,
-                                 (const int *)flags, (const double *)p, (const double *)ap, lam, res, w, (const double *)nullptr, z,
-                                 s->d_partials, s->d_partials + s->n_partials);
-                    if (ctx->n_ranks > 1)
-                    {
-                        MFV2D_LAUNCH(sum_partials_kernel, 1, 32, 0, ctx->stream, s->n_partials, (const double *)s->d_partials,
-                                     s->d_partials);
-                        if ((r = comm_allreduce(ctx, s->d_partials, 1)))
-                            break;
-                        MFV2D_LAUNCH(cg_beta_kernel, 1, 32, 0, ctx->stream, 1, (const double *)s->d_partials,
-                                     (const double *)s->d_partials, sc, flags, 0, it);
-                        ctx->launches++;
-                    }
-                    else
-                        MFV2D_LAUNCH(cg_beta_kernel, 1, 32, 0, ctx->stream, s->n_partials, (const double *)s->d_partials,
-                                     (const double *)(s->d_partials + s->n_partials), sc, flags, 0, it);
-                    MFV2D_LAUNCH(cg_direction_kernel, grid_for(ctx, nt, 256), 256, 0, ctx->stream, nt, (const double *)sc,
-                                 (const int *)flags, (const double *)res, p);
-                    ctx->launches += 5;
+                    ctx->launches += 7 * check_every;
+                    it = stop;
                 }
+#endif
+                for (; it < stop && !r; ++it)
+                    r = enqueue_iteration();
                 if (r)
                     break;
                 if (cudaGetLastError() != cudaSuccess)
@@ -1010,6 +1046,10 @@ int mfv2d_cuda_solve_schur_cg(mfv2d_system *s, const double *rhs, const double *
                 it_done = hf[1];
                 finished = hf[0] != 0;
             }
+#ifndef MFV2D_EMU
+            if (graph_exec)
+                cudaGraphExecDestroy(graph_exec);
+#endif
             if (r)
                 break;
         }
