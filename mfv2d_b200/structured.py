@@ -94,3 +94,56 @@ def strip_partition(nh: int, nv: int, n_ranks: int) -> list[tuple[int, int]]:
     """Contiguous ranges of leaf indices (horizontal strips of whole element rows)."""
     rows = [nv * r // n_ranks for r in range(n_ranks + 1)]
     return [(rows[r] * nh, rows[r + 1] * nh) for r in range(n_ranks)]
+
+
+class ConstraintPartition:
+    """What one rank needs of a global constraint matrix ``N`` (COO over global dense columns) when the
+    elements - and with them contiguous ranges of dense columns - are split over ``n_ranks`` processes
+    (SURVEY.md 8e).
+
+    ``row, col, val``  the rank's rows of ``N`` restricted to its own columns, with LOCAL row and column
+                       indices, sorted by (row, col); ``n_trace`` local multipliers
+    ``global_rows``    global multiplier index of every local row (increasing)
+    ``shared_index``   local rows that other ranks hold too; ``slot`` their position in the packed
+                       interface buffer of ``n_slots`` doubles (same numbering on every rank)
+    ``owned``          1 where this rank is the lowest rank holding the multiplier (it alone counts the
+                       multiplier in dot products, which replaces TraceVector.dot's division by the sharing
+                       count, src/algebra/system_objects.c:1690-1696)
+    """
+
+    def __init__(self, row, col, val, n_trace, global_rows, shared_index, slot, n_slots, owned):
+        self.row, self.col, self.val, self.n_trace = row, col, val, int(n_trace)
+        self.global_rows, self.shared_index, self.slot = global_rows, shared_index, slot
+        self.n_slots, self.owned = int(n_slots), owned
+
+
+def partition_constraints(row: np.ndarray, col: np.ndarray, val: np.ndarray, n_trace: int, dense_bounds,
+                          rank: int) -> ConstraintPartition:
+    """Split the global constraint matrix for ``rank``.  ``dense_bounds[r]`` is the first global dense
+    column of rank ``r`` (``len == n_ranks + 1``).  Every rank calls this with the same global arrays and
+    obtains consistent interface slots without any communication: a multiplier is *shared* when its row
+    touches the columns of more than one rank (conforming edges on a cut: 2 ranks; a gauge row from
+    ``constrained_forms``: every rank), and the shared multipliers are numbered in increasing global order."""
+    row = np.asarray(row, np.int64)
+    col = np.asarray(col, np.int64)
+    val = np.asarray(val, np.float64)
+    bounds = np.asarray(dense_bounds, np.int64)
+    entry_rank = np.searchsorted(bounds, col, side="right") - 1
+    lo = np.full(n_trace, np.iinfo(np.int64).max, np.int64)
+    hi = np.full(n_trace, -1, np.int64)
+    np.minimum.at(lo, row, entry_rank)
+    np.maximum.at(hi, row, entry_rank)
+    is_shared = hi > lo
+    slot_of = np.cumsum(is_shared) - 1  # valid where is_shared
+    mine = entry_rank == rank
+    g_rows = np.unique(row[mine])
+    local_of = np.full(n_trace, -1, np.int64)
+    local_of[g_rows] = np.arange(g_rows.size)
+    l_row = local_of[row[mine]]
+    l_col = col[mine] - bounds[rank]
+    l_val = val[mine]
+    order = np.lexsort((l_col, l_row))
+    sh = np.flatnonzero(is_shared[g_rows])
+    owned = (lo[g_rows] == rank).astype(np.uint8)
+    return ConstraintPartition(l_row[order], l_col[order], l_val[order], g_rows.size, g_rows, sh.astype(np.int64),
+                               slot_of[g_rows[sh]].astype(np.int64), int(is_shared.sum()), owned)

@@ -1,0 +1,67 @@
+"""world_size-2 tests of the multi-GPU path.
+
+`-m "not gpu"`: two gloo processes run the partitioned Schur CG with numpy as the local engine
+(tests/dist_worker.py, mode numpy) - this covers the host logic the N > 1 path adds (strip partition,
+constraint partition, interface slots, ownership weights) against the reference's golden solution.
+`-m gpu`: the same through libmfv2d_cuda.so with NCCL, one process per GPU; skipped on a one-GPU box.
+"""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+WORKER = os.path.join(ROOT, "tests", "dist_worker.py")
+
+
+def _run(mode, fix, nh, nv, world, port):
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr", "127.0.0.1",
+           "--master-port", str(port), WORKER, mode, fix, str(nh), str(nv)]
+    res = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT)
+    assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
+    assert "dist_worker ok" in res.stdout, res.stdout[-2000:]
+
+
+def test_partition_is_consistent():
+    from mfv2d_b200 import structured as ST
+
+    nh, nv, p = 4, 6, 3
+    row, col, val, nt = ST.continuity_constraints_1form(nh, nv, p, [2, 3])
+    ne = 2 * p * (p + 1) + p * p
+    rng = np.random.default_rng(0)
+    x = rng.standard_normal(nh * nv * ne)
+    full = np.zeros(nt)
+    np.add.at(full, row, val * x[col])
+    for world in (1, 2, 3):
+        parts = ST.strip_partition(nh, nv, world)
+        bounds = [parts[r][0] * ne for r in range(world)] + [parts[-1][1] * ne]
+        tot, cnt, slots = np.zeros(nt), np.zeros(nt), {}
+        for r in range(world):
+            P = ST.partition_constraints(row, col, val, nt, bounds, r)
+            loc = np.zeros(P.n_trace)
+            np.add.at(loc, P.row, P.val * x[bounds[r]:bounds[r + 1]][P.col])
+            tot[P.global_rows] += loc
+            cnt[P.global_rows] += P.owned
+            for g, s in zip(P.global_rows[P.shared_index], P.slot):
+                assert slots.setdefault(int(g), int(s)) == int(s)  # same slot on every rank
+            assert np.all(np.diff(P.global_rows) > 0)
+        assert np.array_equal(tot, full) or np.allclose(tot, full, rtol=0, atol=1e-13)
+        assert np.all(cnt == 1)  # every multiplier has exactly one owner
+        assert len(slots) == (world - 1) * nh * p  # p multipliers per edge on every cut (one 1-form)
+
+
+@pytest.mark.parametrize("fix,nh,nv", [("solve_3x4_p4", 3, 4), ("solve_6x6_p3_def", 6, 6)])
+def test_gloo_world2_schur_cg(fix, nh, nv):
+    _run("numpy", fix, nh, nv, 2, 29611)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("fix,nh,nv", [("solve_10x10_p3", 10, 10), ("solve_6x6_p3_def", 6, 6)])
+def test_nccl_world2_schur_cg(fix, nh, nv):
+    import mfv2d_b200._capi as capi
+
+    if capi.lib().mfv2d_cuda_device_count() < 2:
+        pytest.skip("needs two GPUs (run with gpurun --gpus 2)")
+    _run("gpu", fix, nh, nv, 2, 29612)
