@@ -402,6 +402,34 @@ def run_ours(args):
                           "s": solve_s, "iterations": it, "residual": res, "multipliers": int(nt_glob),
                           "interface_multipliers": int(part.n_slots), "dense_dofs": int(n * s_ne * world)}
 
+        # slice of BASELINE.json configs[4]: mixed Poisson, order 6, the same number of elements per GPU
+        del system, xv, yv, rhs, phi, xs, lam, s_out
+        p6 = 6
+        b6 = M.Basis1D(p6, M.IntegrationRule1D(p6 + k))
+        batch6 = M.ElementBatch(M.Basis2D(b6, b6), d_corners, ctx)
+        ne6 = s_specs.total_size(p6, p6)
+        out6 = ctx.empty((n, ne6, ne6))
+        M.compute_element_matrices(s_specs, s_lhs, batch6, out=out6)
+        ctx.synchronize()
+        ctx.timer_start()
+        for _ in range(reps):
+            M.compute_element_matrices(s_specs, s_lhs, batch6, out=out6)
+        t = ctx.timer_stop() / reps
+        x6 = ctx.to_device(rng.standard_normal((n, ne6)))
+        y6 = ctx.empty((n, ne6))
+        M.compute_element_vectors(s_specs, s_lhs, batch6, x6, out=y6)
+        ctx.synchronize()
+        ctx.timer_start()
+        for _ in range(reps):
+            M.compute_element_vectors(s_specs, s_lhs, batch6, x6, out=y6)
+        t2 = ctx.timer_stop() / reps
+        extra["order6_mixed_poisson"] = {
+            "elements_per_gpu": n, "element_dofs": ne6,
+            "element_matrices_per_s": sum_over_ranks(dist, n / (t * 1e-3)),
+            "assembly_hbm_frac_per_gpu": (64 + 8 * ne6 * ne6) * n / (t * 1e-3) / 1e9 / peak,
+            "apply_recompute_gdofs": sum_over_ranks(dist, n * ne6 / (t2 * 1e-3) / 1e9)}
+        del out6, x6, y6
+
     line = {
         "metric": "element_matrices_per_s", "value": value, "unit": "element matrices/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,

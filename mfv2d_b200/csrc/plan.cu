@@ -885,8 +885,13 @@ int plan_finalize_matrix(mfv2d_plan *plan, const std::vector<std::vector<Lowered
     };
     std::vector<int32_t> xtab;
     bool fits = false;
-    for (int min_chunk : {1, 4, 8, 16, 31})
+    // first choice: two CTAs per SM (if the stages were packed for that), any chunking; then one CTA per SM
+    const long long cta_budget[2] = {cap_used == cap_pref ? ((long long)228 * 1024 - 2 * 1024) / 2 : (long long)ctx->smem_optin,
+                                     (long long)ctx->smem_optin};
+    for (int attempt = 0; attempt < 10 && !fits; ++attempt)
     {
+        const int min_chunk = (const int[]){1, 4, 8, 16, 31}[attempt % 5];
+        const long long per_cta = cta_budget[attempt / 5];
         // upper bound of the work-item table for chunks of at least min_chunk pairs
         size_t x_bound = 0;
         for (const DevTB &tb : plan->tbs)
@@ -906,13 +911,7 @@ int plan_finalize_matrix(mfv2d_plan *plan, const std::vector<std::vector<Lowered
         sec(s2tab.size() * sizeof(DevS2Pair));
         sec(x_bound * sizeof(int32_t));
         fixed_exact += 8 * 64 + 256; // corners of up to 8 slots, alignment slack
-        long long per_cta = (cap_used == cap_pref ? ((long long)228 * 1024 - 2 * 1024) / 2 : (long long)ctx->smem_optin);
         long long epb = (per_cta - (long long)fixed_exact) / 8 / slot;
-        if (epb < 1)
-        {
-            per_cta = (long long)ctx->smem_optin;
-            epb = (per_cta - (long long)fixed_exact) / 8 / slot;
-        }
         if (epb < 1)
             continue;
         if (epb > 8)
