@@ -236,10 +236,10 @@ def run_reference(args):
 
 
 def workload_config(n_gpus):
-    return {"workload": f"steady Stokes (vor0, vel1, prs2) element matrices, {N_SIDE}x{N_SIDE} elements per GPU, order {P_ORDER}, "
-                        f"integration order p+{K_OVER}, deformed unit square (BASELINE.json configs[1])",
-            "elements_per_gpu": N_SIDE * N_SIDE, "element_dofs": 81, "parallelism": f"elements x{n_gpus}, no collective",
-            "l2": "outputs (3.44 GB per step) are larger than L2; no flush needed"}
+    return {"workload": f"steady {'Stokes (vor0, vel1, prs2)' if SYSTEM == 'stokes' else 'mixed Poisson (q1, u2)'} element matrices, {N_SIDE}x{N_SIDE} elements per GPU, order {P_ORDER}, "
+                        f"integration order p+{K_OVER}, deformed unit square " + ("(BASELINE.json configs[1])" if SYSTEM == "stokes" else "(per-GPU slice of BASELINE.json configs[4])"),
+            "elements_per_gpu": N_SIDE * N_SIDE, "element_dofs": {"stokes": 81, "mixed_poisson": 120}.get(SYSTEM, 0) if P_ORDER in (4, 6) else 0, "parallelism": f"elements x{n_gpus}, no collective",
+            "l2": "outputs (3.4 GB per step or more) are larger than L2; no flush needed"}
 
 
 def run_ours(args):
@@ -457,7 +457,13 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--skip-extra", action="store_true", help="skip the apply / solve extras (profiling runs)")
     ap.add_argument("--skip-e2e", action="store_true", help="skip the host-buffer leg (profiling runs)")
+    ap.add_argument("--workload", default="stokes4", choices=["stokes4", "poisson6"],
+                    help="stokes4 = BASELINE.json configs[1] (the default and the reported metric); poisson6 = per-GPU slice of "
+                         "configs[4] (mixed Poisson, order 6), for profiling")
     args = ap.parse_args()
+    if args.workload == "poisson6":
+        global P_ORDER, SYSTEM
+        P_ORDER, SYSTEM = 6, "mixed_poisson"
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":
         run_reference(args)

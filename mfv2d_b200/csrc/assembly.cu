@@ -327,19 +327,18 @@ __device__ __forceinline__ void load_inc(const DevIncRow *row, int (&idx)[4], do
 // one lane's share of a tile: column c, rows r0 + sub, r0 + sub + rstep, ... ; NL x NR gathers per entry.
 // D rows and output rows are walked with running offsets (no per-row multiplications).
 template <int NL, int NR>
-__device__ __forceinline__ void emit_tile(const EmitTerm &t, int r0, int nr, int sub, int rstep, int c, bool active,
-                                          double *__restrict__ o, int N, bool accumulate)
+__device__ __forceinline__ void emit_tile(const EmitTerm &t, int r0, int nr, int sub, int rstep, int c, double *__restrict__ o, int N)
 {
     int rc[4];
     double rs[4];
     if (NR == 1)
     {
-        rc[0] = active ? c : 0;
+        rc[0] = c;
         rs[0] = t.coef;
     }
     else
     {
-        load_inc(t.rtab + (active ? c : 0), rc, rs);
+        load_inc(t.rtab + c, rc, rs);
 #pragma unroll
         for (int b = 0; b < NR; ++b)
             rs[b] *= t.coef;
@@ -357,20 +356,14 @@ __device__ __forceinline__ void emit_tile(const EmitTerm &t, int r0, int nr, int
 #pragma unroll
             for (int b = 1; b < NR; ++b)
                 v = fma(rs[b], Dr[rc[b]], v);
-            if (active)
-            {
-                if (accumulate)
-                    *o += v;
-                else
-                    *o = v;
-            }
+            *o = v;
         }
     }
     else
     {
         const DevIncRow *lt = t.ltab + r0 + sub;
         const double *Dc = t.D + rc[0];
-#pragma unroll 4
+#pragma unroll 2
         for (int r = sub; r < nr; r += rstep, lt += rstep, o += ostep)
         {
             int li[4];
@@ -392,13 +385,7 @@ __device__ __forceinline__ void emit_tile(const EmitTerm &t, int r0, int nr, int
             }
             if (NR == 1)
                 v *= rs[0];
-            if (active)
-            {
-                if (accumulate)
-                    *o += v;
-                else
-                    *o = v;
-            }
+            *o = v;
         }
     }
 }
@@ -421,7 +408,8 @@ __device__ __forceinline__ EmitTerm make_emit_term(const AsmArgs &args, const De
     return t;
 }
 
-__device__ __forceinline__ void emit_stage(const AsmArgs &args, const DevStage &sg, unsigned long long elem0, int n_valid)
+__device__ __forceinline__ void emit_stage(const AsmArgs &args, const DevStage &sg, unsigned long long elem0, int n_valid,
+                                           int *counter)
 {
     MFV2D_DYN_SMEM(double, smem); // re-declared here so that the compiler keeps every access in the shared window
     const AsmLayout &L = args.lay;
@@ -431,13 +419,19 @@ __device__ __forceinline__ void emit_stage(const AsmArgs &args, const DevStage &
     const DevBlock *blocks = reinterpret_cast<const DevBlock *>(sb + L.off_blocks);
     const DevUnit *units = reinterpret_cast<const DevUnit *>(sb + L.off_units);
     const DevIncRow *inc = reinterpret_cast<const DevIncRow *>(sb + L.off_inc);
-    const int warp = threadIdx.x >> 5, nwarps = MFV2D_NWARPS;
     const int N = args.n_total;
     const int n_units = sg.unit_end - sg.unit_begin;
-    const float inv_units = 1.0f / (float)n_units;
-    for (int w = warp; w < n_units * n_valid; w += nwarps)
+    const float inv_valid = 1.0f / (float)n_valid;
+    // units are sorted by decreasing cost; the warps fetch (unit, slot) pairs from a shared counter
+    for (;;)
     {
-        const int e = fast_div(w, inv_units), u = w - e * n_units;
+        int w = 0;
+        if (MFV2D_LANE0 == 0)
+            w = atomicAdd(counter, 1);
+        w = __shfl_sync(0xffffffffu, w, 0);
+        if (w >= n_units * n_valid)
+            break;
+        const int u = fast_div(w, inv_valid), e = w - u * n_valid;
         const DevUnit un = units[sg.unit_begin + u];
         const DevBlock db = blocks[un.block];
         const double *arena = smem + L.off_slots + e * L.slot_stride + L.slot_arena;
@@ -463,32 +457,33 @@ __device__ __forceinline__ void emit_stage(const AsmArgs &args, const DevStage &
                 continue;
             }
             const DevTerm tm0 = terms[db.term_begin];
-            if (n_terms == 1 && tm0.dense >= 0)
+            if (n_terms == 1 && tm0.dense >= 0 && !db.accumulate)
             {
                 const EmitTerm t = make_emit_term(args, tm0, dense, inc, arena);
                 const int nl = inc_width(tm0.L), nr_ = inc_width(tm0.R < 0 ? -1 : (tm0.R ^ 2));
-                const bool acc = db.accumulate;
+                if (!active)
+                    continue; // nothing below is warp-collective
                 switch (nl * 8 + nr_)
-                {
-                case 1 * 8 + 1:
-                    emit_tile<1, 1>(t, un.r0, un.nr, sub, rstep, c, active, o, N, acc);
-                    break;
-                case 1 * 8 + 2:
-                    emit_tile<1, 2>(t, un.r0, un.nr, sub, rstep, c, active, o, N, acc);
-                    break;
-                case 1 * 8 + 4:
-                    emit_tile<1, 4>(t, un.r0, un.nr, sub, rstep, c, active, o, N, acc);
-                    break;
-                case 2 * 8 + 1:
-                    emit_tile<2, 1>(t, un.r0, un.nr, sub, rstep, c, active, o, N, acc);
-                    break;
-                case 4 * 8 + 1:
-                    emit_tile<4, 1>(t, un.r0, un.nr, sub, rstep, c, active, o, N, acc);
-                    break;
-                default:
-                    emit_tile<4, 4>(t, un.r0, un.nr, sub, rstep, c, active, o, N, acc);
-                    break;
-                }
+                    {
+                    case 1 * 8 + 1:
+                        emit_tile<1, 1>(t, un.r0, un.nr, sub, rstep, c, o, N);
+                        break;
+                    case 1 * 8 + 2:
+                        emit_tile<1, 2>(t, un.r0, un.nr, sub, rstep, c, o, N);
+                        break;
+                    case 1 * 8 + 4:
+                        emit_tile<1, 4>(t, un.r0, un.nr, sub, rstep, c, o, N);
+                        break;
+                    case 2 * 8 + 1:
+                        emit_tile<2, 1>(t, un.r0, un.nr, sub, rstep, c, o, N);
+                        break;
+                    case 4 * 8 + 1:
+                        emit_tile<4, 1>(t, un.r0, un.nr, sub, rstep, c, o, N);
+                        break;
+                    default:
+                        emit_tile<4, 4>(t, un.r0, un.nr, sub, rstep, c, o, N);
+                        break;
+                    }
                 continue;
             }
             // several terms (or an identity): accumulate the terms of an entry in a register
@@ -540,6 +535,7 @@ template <int Q> __global__ void __launch_bounds__(ASM_THREADS, 2) element_matri
     MFV2D_DYN_SMEM(double, smem);
     const AsmLayout &L = args.lay;
     __shared__ int bad[8];
+    __shared__ int emit_counter;
     {
         // descriptor blob -> shared memory, once per CTA
         const double2 *src = reinterpret_cast<const double2 *>(args.blob);
@@ -571,6 +567,8 @@ template <int Q> __global__ void __launch_bounds__(ASM_THREADS, 2) element_matri
         {
             const DevStage sg = stages[st];
             __syncthreads(); // corners ready / previous stage's emission done
+            if (threadIdx.x == 0)
+                emit_counter = 0;
             phase_weights<Q>(args, smem, sg, ws, pnts, wgts, elem0, n_valid);
             for (int r = sg.round_begin; r < sg.round_end; ++r)
             {
@@ -584,7 +582,7 @@ template <int Q> __global__ void __launch_bounds__(ASM_THREADS, 2) element_matri
                 if (dense[d].inverse)
                     invert_spd_slots(args, dense[d].smem_off, dense[d].rows, dense[d].ld, n_valid, bad);
             __syncthreads();
-            emit_stage(args, sg, elem0, n_valid);
+            emit_stage(args, sg, elem0, n_valid, &emit_counter);
         }
         __syncthreads();
         if (args.status)

@@ -7,6 +7,7 @@
 // SURVEY.md (Q1 dense incidence fails, Q2 a dense*dense product drops the accumulated coefficient, Q3
 // SUM only for same-kind operands) - but a dense state is kept as a sum of product chains instead of
 // numbers.  The chains are then lowered to fused device work (assembly.cu, apply.cu).
+#include <algorithm>
 #include <cstdlib>
 
 #include "plan.cuh"
@@ -724,7 +725,7 @@ int plan_finalize_matrix(mfv2d_plan *plan, const std::vector<std::vector<Lowered
                 }
             }
             const int w = 1 << cl, rows_per_store = 32 >> cl;
-            const int rg = 64 * rows_per_store; // at most 64 warp stores per unit (the per-unit set-up is amortised)
+            const int rg = 32 * rows_per_store; // at most 32 warp stores per unit
             for (int c0 = 0; c0 < db.ncols; c0 += w)
                 for (int r0 = 0; r0 < db.nrows; r0 += rg)
                 {
@@ -737,6 +738,23 @@ int plan_finalize_matrix(mfv2d_plan *plan, const std::vector<std::vector<Lowered
                     plan->units.push_back(u);
                 }
         }
+        // heaviest units first: the warps of a CTA fetch units dynamically (longest-processing-time order)
+        auto unit_cost = [&](const DevUnit &u) {
+            const DevBlock &db = plan->blocks[u.block];
+            int gathers = 1;
+            for (int t = db.term_begin; t < db.term_end; ++t)
+            {
+                const DevTerm &tm = plan->terms[t];
+                const int nl = tm.L < 0 ? 1 : ((tm.L == MFV2D_INC_10 || tm.L == MFV2D_INC_21_T) ? 2 : 4);
+                const int rk = tm.R < 0 ? -1 : (tm.R ^ 2);
+                const int nr = rk < 0 ? 1 : ((rk == MFV2D_INC_10 || rk == MFV2D_INC_21_T) ? 2 : 4);
+                gathers += 2 * nl * nr + (nl > 1 ? 6 : 0);
+            }
+            const int iters = (u.nr + (32 >> u.cl) - 1) / (32 >> u.cl);
+            return 40 + iters * (6 + gathers);
+        };
+        std::stable_sort(plan->units.begin() + sg.unit_begin, plan->units.end(),
+                         [&](const DevUnit &a, const DevUnit &b) { return unit_cost(a) > unit_cost(b); });
         sg.unit_end = (int)plan->units.size();
     }
 
