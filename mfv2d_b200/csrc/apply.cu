@@ -436,238 +436,201 @@ __global__ void __launch_bounds__(APPLY_THREADS) element_vector_kernel(const App
 }
 
 // =====================================================================================================
-// Warp-per-element variant (the fast path): the same programs, but every element is handled by ONE warp
-// with its working vectors in a private shared-memory region, so that the phases are separated by
-// __syncwarp() instead of CTA barriers and the warps of a CTA run independently (they only share the
-// basis tables).  The Jacobian is recomputed from the corner coordinates held in registers wherever a
-// metric weight is needed.  Programs that contain an inverse mass and the column mode use the
-// CTA-per-element kernel above.
+// Register-tiled variant (the fast path).  A CTA works on `epb` elements per pass; every dense factor
+// (mass / interior product) of a program is applied by sum factorisation in three barrier-separated
+// phases whose threads keep a whole quadrature row or column in REGISTERS (template parameter Q) and read
+// the basis tables as warp-uniform 16-byte broadcasts:
+//   A  thread (e, i):  t[e][i][:] = sum_j c[e][i,j] B_j[:]                    (interpolate along xi)
+//   B  thread (e, b):  u[:] = sum_i A_i[:] t[e][i][b]  ->  metric weights at the points (:, b), Jacobian
+//                      from the corners  ->  t'[e][i][b] = A'_i[:] . g[:]     (eta interpolation, scaling,
+//                      eta projection; the values at the quadrature points never leave the registers)
+//   C  thread (e, i):  out[e][i,j] = B'_j[:] . t'[e][i][:]                     (project along xi)
+// Incidences are signed gathers between the ping-pong vectors.  Programs with an inverse mass and the
+// column mode use the CTA-per-element kernel above.
 // =====================================================================================================
-#define APPLYW_WARPS 8
+#define APPLYT_THREADS 256
 
-struct WarpView
+enum
 {
-    const double *node, *edge, *pnts, *wgts;
-    double *u0, *u1; // q^2 each
-    double *tmp;     // 2 (p+1) q
-    double *v0, *v1; // ping-pong coefficient vectors
-    double *xs, *ys; // N each
-    double cs[8];    // corners (registers)
+    TK_NODE = 0,
+    TK_EDGE = 1
 };
 
-// u[a][b] = sum_i A[i][a] sum_j c[i*nB + j] B[j][b]
-__device__ __forceinline__ void interp_w(const WarpView &s, int q, const double *__restrict__ c, const double *__restrict__ A,
-                                         int nA, const double *__restrict__ B, int nB, double *__restrict__ u)
+// one tensor component of a form: coefficient (i, j) multiplies A_i(eta) B_j(xi); stored at off + i nB + j
+struct TileComp
 {
-    const float inv_q = 1.0f / (float)q;
-    for (int idx = MFV2D_LANE0; idx < nA * q; idx += MFV2D_LANE_STEP)
+    int kA, kB, off;
+};
+
+struct TileOp
+{
+    int n_in, n_out, mode;
+    TileComp in[2], out[2];
+};
+
+__device__ __forceinline__ TileOp tile_op(int type, int fa, int fc, int p)
+{
+    const int nh = p * (p + 1);
+    const TileComp c0{TK_NODE, TK_NODE, 0}, c2{TK_EDGE, TK_EDGE, 0}, ch{TK_NODE, TK_EDGE, 0}, cv{TK_EDGE, TK_NODE, nh};
+    TileOp op;
+    op.in[1] = op.out[1] = c0;
+    if (type == 1)
     {
-        const int i = (int)(((float)idx + 0.5f) * inv_q), b = idx - i * q;
-        const double *ci = c + i * nB;
-        double r0 = 0.0, r1 = 0.0;
-        int j = 0;
-        for (; j + 1 < nB; j += 2)
+        if (fa == DK_MASS0)
         {
-            r0 = fma(ci[j], B[j * q + b], r0);
-            r1 = fma(ci[j + 1], B[(j + 1) * q + b], r1);
+            op.n_in = op.n_out = 1;
+            op.mode = 0;
+            op.in[0] = op.out[0] = c0;
         }
-        if (j < nB)
-            r0 = fma(ci[j], B[j * q + b], r0);
-        s.tmp[idx] = r0 + r1;
+        else if (fa == DK_MASS2)
+        {
+            op.n_in = op.n_out = 1;
+            op.mode = 1;
+            op.in[0] = op.out[0] = c2;
+        }
+        else
+        {
+            op.n_in = op.n_out = 2;
+            op.mode = 2;
+            op.in[0] = op.out[0] = ch;
+            op.in[1] = op.out[1] = cv;
+        }
     }
-    __syncwarp();
-    for (int idx = MFV2D_LANE0; idx < q * q; idx += MFV2D_LANE_STEP)
+    else if (fa == DK_IPROD1 && !fc) // (n0 x n1): 1-form in, 0-form out
     {
-        const int a = (int)(((float)idx + 0.5f) * inv_q), b = idx - a * q;
-        double r0 = 0.0, r1 = 0.0;
-        int i = 0;
-        for (; i + 1 < nA; i += 2)
-        {
-            r0 = fma(A[i * q + a], s.tmp[i * q + b], r0);
-            r1 = fma(A[(i + 1) * q + a], s.tmp[(i + 1) * q + b], r1);
-        }
-        if (i < nA)
-            r0 = fma(A[i * q + a], s.tmp[i * q + b], r0);
-        u[idx] = r0 + r1;
+        op.n_in = 2;
+        op.n_out = 1;
+        op.mode = 3;
+        op.in[0] = ch;
+        op.in[1] = cv;
+        op.out[0] = c0;
     }
-    __syncwarp();
+    else if (fa == DK_IPROD1) // transposed: 0-form in, 1-form out
+    {
+        op.n_in = 1;
+        op.n_out = 2;
+        op.mode = 4;
+        op.in[0] = c0;
+        op.out[0] = ch;
+        op.out[1] = cv;
+    }
+    else if (!fc) // (n1 x n2): 2-form in, 1-form out
+    {
+        op.n_in = 1;
+        op.n_out = 2;
+        op.mode = 5;
+        op.in[0] = c2;
+        op.out[0] = ch;
+        op.out[1] = cv;
+    }
+    else // transposed: 1-form in, 2-form out
+    {
+        op.n_in = 2;
+        op.n_out = 1;
+        op.mode = 6;
+        op.in[0] = ch;
+        op.in[1] = cv;
+        op.out[0] = c2;
+    }
+    return op;
 }
 
-// out[i*nB + j] = sum_a A[i][a] sum_b B[j][b] g[a][b]
-__device__ __forceinline__ void project_w(const WarpView &s, int q, const double *__restrict__ g, const double *__restrict__ A,
-                                          int nA, const double *__restrict__ B, int nB, double *__restrict__ out)
-{
-    const float inv_q = 1.0f / (float)q, inv_nb = 1.0f / (float)nB;
-    for (int idx = MFV2D_LANE0; idx < nA * q; idx += MFV2D_LANE_STEP)
-    {
-        const int i = (int)(((float)idx + 0.5f) * inv_q), b = idx - i * q;
-        const double *Ai = A + i * q;
-        double r0 = 0.0, r1 = 0.0;
-        int a = 0;
-        for (; a + 1 < q; a += 2)
-        {
-            r0 = fma(Ai[a], g[a * q + b], r0);
-            r1 = fma(Ai[a + 1], g[(a + 1) * q + b], r1);
-        }
-        if (a < q)
-            r0 = fma(Ai[a], g[a * q + b], r0);
-        s.tmp[idx] = r0 + r1;
-    }
-    __syncwarp();
-    for (int idx = MFV2D_LANE0; idx < nA * nB; idx += MFV2D_LANE_STEP)
-    {
-        const int i = (int)(((float)idx + 0.5f) * inv_nb), j = idx - i * nB;
-        const double *Bj = B + j * q, *ti = s.tmp + i * q;
-        double r0 = 0.0, r1 = 0.0;
-        int b = 0;
-        for (; b + 1 < q; b += 2)
-        {
-            r0 = fma(Bj[b], ti[b], r0);
-            r1 = fma(Bj[b + 1], ti[b + 1], r1);
-        }
-        if (b < q)
-            r0 = fma(Bj[b], ti[b], r0);
-        out[idx] = r0 + r1;
-    }
-    __syncwarp();
-}
-
-// pointwise metric scaling (modes as scale_points above), Jacobian recomputed from the corners
-__device__ __forceinline__ void scale_points_w(const WarpView &s, int q, int mode, const double *__restrict__ fld)
-{
-    const int q2 = q * q;
-    const float inv_q = 1.0f / (float)q;
-    const double x0 = s.cs[0], y0 = s.cs[1], x1 = s.cs[2], y1 = s.cs[3], x2 = s.cs[4], y2 = s.cs[5], x3 = s.cs[6], y3 = s.cs[7];
-    for (int idx = MFV2D_LANE0; idx < q2; idx += MFV2D_LANE_STEP)
-    {
-        const int a = (int)(((float)idx + 0.5f) * inv_q), b = idx - a * q;
-        const double eta = s.pnts[a], xi = s.pnts[b];
-        const double w = s.wgts[a] * s.wgts[b];
-        const double j00 = 0.25 * ((x1 - x0) * (1 - eta) + (x2 - x3) * (1 + eta));
-        const double j01 = 0.25 * ((y1 - y0) * (1 - eta) + (y2 - y3) * (1 + eta));
-        const double j10 = 0.25 * ((x3 - x0) * (1 - xi) + (x2 - x1) * (1 + xi));
-        const double j11 = 0.25 * ((y3 - y0) * (1 - xi) + (y2 - y1) * (1 + xi));
-        const double det = j00 * j11 - j10 * j01;
-        const double a0 = s.u0[idx];
-        switch (mode)
-        {
-        case 0:
-            s.u0[idx] = a0 * det * w;
-            break;
-        case 1:
-            s.u0[idx] = a0 * w / det;
-            break;
-        case 2: {
-            const double a1 = s.u1[idx];
-            const double khh = (j11 * j11 + j10 * j10) / det * w, kvv = (j00 * j00 + j01 * j01) / det * w,
-                         khv = (j01 * j11 + j00 * j10) / det * w;
-            s.u0[idx] = khh * a0 + khv * a1;
-            s.u1[idx] = khv * a0 + kvv * a1;
-            break;
-        }
-        case 3:
-        case 4: {
-            const double fx = fld[2 * idx], fy = fld[2 * idx + 1];
-            const double kh = (fx * j11 - fy * j10) * w, kv = -(fy * j00 - fx * j01) * w;
-            if (mode == 3)
-                s.u0[idx] = kh * a0 + kv * s.u1[idx];
-            else
-            {
-                s.u0[idx] = kh * a0;
-                s.u1[idx] = kv * a0;
-            }
-            break;
-        }
-        default: {
-            const double fx = fld[2 * idx], fy = fld[2 * idx + 1];
-            const double kh = -(fx * j10 + fy * j11) / det * w, kv = -(fx * j00 + fy * j01) / det * w;
-            if (mode == 6)
-                s.u0[idx] = kh * a0 + kv * s.u1[idx];
-            else
-            {
-                s.u0[idx] = kh * a0;
-                s.u1[idx] = kv * a0;
-            }
-            break;
-        }
-        }
-    }
-    __syncwarp();
-}
-
-struct ApplyWArgs
+struct ApplyTArgs
 {
     ApplyArgs a;
     int prog_len, n_coef, inc_rows; // sizes of the program / coefficient / incidence tables staged in shared memory
-    int warp_doubles;               // private doubles per warp
+    int epb;                        // elements per pass
+    int slot_doubles;               // private doubles per element slot
 };
 
-__global__ void __launch_bounds__(APPLYW_WARPS * 32) element_vector_warp_kernel(const ApplyWArgs wa)
+template <int Q> __device__ __forceinline__ void row_axpy(double (&acc)[Q], double c, const double *__restrict__ row)
+{
+#pragma unroll
+    for (int b = 0; b + 1 < Q; b += 2)
+    {
+        const double2 v = *reinterpret_cast<const double2 *>(row + b);
+        acc[b] = fma(c, v.x, acc[b]);
+        acc[b + 1] = fma(c, v.y, acc[b + 1]);
+    }
+    if (Q & 1)
+        acc[Q - 1] = fma(c, row[Q - 1], acc[Q - 1]);
+}
+
+template <int Q> __device__ __forceinline__ double row_dot(const double *__restrict__ row, const double (&g)[Q])
+{
+    double a0 = 0.0, a1 = 0.0;
+#pragma unroll
+    for (int b = 0; b + 1 < Q; b += 2)
+    {
+        const double2 v = *reinterpret_cast<const double2 *>(row + b);
+        a0 = fma(v.x, g[b], a0);
+        a1 = fma(v.y, g[b + 1], a1);
+    }
+    if (Q & 1)
+        a0 = fma(row[Q - 1], g[Q - 1], a0);
+    return a0 + a1;
+}
+
+template <int Q> __global__ void __launch_bounds__(APPLYT_THREADS, 2) element_vector_tile_kernel(const ApplyTArgs ta)
 {
     MFV2D_DYN_SMEM(double, smem);
-    const ApplyArgs &args = wa.a;
-    const int p = args.p, q = args.q, q2 = q * q, np1 = p + 1, nh = p * (p + 1);
+    constexpr int LDQ = (Q + 1) & ~1;
+    const ApplyArgs &args = ta.a;
+    const int p = args.p, np1 = p + 1, nh = p * (p + 1);
     const int N = args.n_total;
-    // CTA-shared: tables | coefficients | program | incidence maps
-    double *coef = smem + ((args.tab_len + 1) & ~1);
-    int *prog = reinterpret_cast<int *>(coef + ((wa.n_coef + 1) & ~1));
-    int4 *inc = reinterpret_cast<int4 *>(prog + ((wa.prog_len + 3) & ~3));
-    double *priv = reinterpret_cast<double *>(inc + wa.inc_rows);
-    for (int i = threadIdx.x; i < args.tab_len; i += blockDim.x)
-        smem[i] = args.tab[i];
-    for (int i = threadIdx.x; i < wa.n_coef; i += blockDim.x)
-        coef[i] = args.coef[i];
-    for (int i = threadIdx.x; i < wa.prog_len; i += blockDim.x)
-        prog[i] = args.prog[i];
-    for (int i = threadIdx.x; i < wa.inc_rows; i += blockDim.x)
-        inc[i] = reinterpret_cast<const int4 *>(args.inc)[i];
-    __syncthreads();
-
-    const int warp = threadIdx.x >> 5, nwarps = MFV2D_NWARPS;
-    WarpView s;
-    s.node = smem;
-    s.edge = s.node + np1 * q;
-    s.pnts = s.edge + p * q;
-    s.wgts = s.pnts + q;
-    double *w = priv + (size_t)warp * wa.warp_doubles;
-    s.u0 = w;
-    w += q2;
-    s.u1 = w;
-    w += q2;
-    s.tmp = w;
-    w += 2 * np1 * q;
-    s.v0 = w;
-    w += args.vmax;
-    s.v1 = w;
-    w += args.vmax;
-    s.xs = w;
-    w += N;
-    s.ys = w;
-    const int n_terms = prog[0];
-
-    for (unsigned long long elem = (unsigned long long)blockIdx.x * nwarps + warp; elem < args.n_elem;
-         elem += (unsigned long long)gridDim.x * nwarps)
+    // CTA-shared: padded tables | points, weights | coefficients | program | incidence maps | element slots
+    const int edge_off = np1 * LDQ; // node rows first, then the edge rows (LDQ doubles each): table k starts at k * edge_off
+    double *pnts = smem + (2 * p + 1) * LDQ, *wgts = pnts + LDQ;
+    double *coef = wgts + LDQ;
+    int *prog = reinterpret_cast<int *>(coef + ((ta.n_coef + 1) & ~1));
+    int4 *inc = reinterpret_cast<int4 *>(prog + ((ta.prog_len + 3) & ~3));
+    double *slots = reinterpret_cast<double *>(inc + ta.inc_rows);
+    for (int i = threadIdx.x; i < (2 * p + 1) * LDQ; i += blockDim.x)
     {
-#pragma unroll
-        for (int i = 0; i < 8; ++i)
-            s.cs[i] = ld_ro(args.corners + elem * 8 + i);
-        __syncwarp();
-        for (int i = MFV2D_LANE0; i < N; i += MFV2D_LANE_STEP)
+        const int r = i / LDQ, b = i - r * LDQ;
+        smem[i] = b < Q ? args.tab[r * Q + b] : 0.0; // tab = node (p+1) x q | edge p x q | pnts | wgts
+    }
+    for (int i = threadIdx.x; i < Q; i += blockDim.x)
+    {
+        pnts[i] = args.tab[(2 * p + 1) * Q + i];
+        wgts[i] = args.tab[(2 * p + 2) * Q + i];
+    }
+    for (int i = threadIdx.x; i < ta.n_coef; i += blockDim.x)
+        coef[i] = args.coef[i];
+    for (int i = threadIdx.x; i < ta.prog_len; i += blockDim.x)
+        prog[i] = args.prog[i];
+    for (int i = threadIdx.x; i < ta.inc_rows; i += blockDim.x)
+        inc[i] = reinterpret_cast<const int4 *>(args.inc)[i];
+    const int epb = ta.epb, SD = ta.slot_doubles;
+    const int off_xs = 8, off_ys = off_xs + N, off_va = off_ys + N, off_vb = off_va + args.vmax, off_t = off_vb + args.vmax;
+    const int n_terms_off = 0;
+    const unsigned long long n_groups = (args.n_elem + epb - 1) / epb;
+
+    for (unsigned long long grp = blockIdx.x; grp < n_groups; grp += gridDim.x)
+    {
+        const unsigned long long elem0 = grp * epb;
+        const int nv = (int)((args.n_elem - elem0) < (unsigned long long)epb ? (args.n_elem - elem0) : epb);
+        __syncthreads(); // tables staged / previous pass done with the slots
+        for (int i = threadIdx.x; i < nv * 8; i += blockDim.x)
+            slots[(i >> 3) * SD + (i & 7)] = args.corners[elem0 * 8 + i];
         {
-            s.xs[i] = args.x[elem * N + i];
-            s.ys[i] = 0.0;
+            const float inv_n = 1.0f / (float)N;
+            for (int i = threadIdx.x; i < nv * N; i += blockDim.x)
+            {
+                const int e = (int)(((float)i + 0.5f) * inv_n), k = i - e * N;
+                slots[e * SD + off_xs + k] = args.x[elem0 * N + i];
+                slots[e * SD + off_ys + k] = 0.0;
+            }
         }
-        __syncwarp();
+        __syncthreads();
+        const int n_terms = prog[n_terms_off];
         int pc = 1;
         for (int t = 0; t < n_terms; ++t)
         {
             const int rf = prog[pc], cf = prog[pc + 1], ci = prog[pc + 2], nfac = prog[pc + 3];
             pc += 4;
-            const int c0 = args.form_offsets[cf];
-            const int r0 = args.form_offsets[rf];
-            // the first factor reads the input segment in place
-            const double *cur = s.xs + c0;
-            double *nxt = s.v0;
+            const int c0 = args.form_offsets[cf], r0 = args.form_offsets[rf];
+            int cur = off_xs + c0, nxt = off_va; // offsets inside a slot; the first factor reads the input in place
             int n_cur = args.form_offsets[cf + 1] - c0;
             for (int f = 0; f < nfac; ++f, pc += 4)
             {
@@ -677,99 +640,230 @@ __global__ void __launch_bounds__(APPLYW_WARPS * 32) element_vector_warp_kernel(
                 {
                     const int rows = (fa == MFV2D_INC_10 || fa == MFV2D_INC_21_T) ? 2 * nh : (fa == MFV2D_INC_21 ? p * p : np1 * np1);
                     const int4 *map = inc + args.inc_off[fa];
-                    for (int r = MFV2D_LANE0; r < rows; r += MFV2D_LANE_STEP)
+                    const float inv_rows = 1.0f / (float)rows;
+                    for (int idx = threadIdx.x; idx < nv * rows; idx += blockDim.x)
                     {
-                        const int4 e = map[r];
-                        const int ev[4] = {e.x, e.y, e.z, e.w};
+                        const int e = (int)(((float)idx + 0.5f) * inv_rows), r = idx - e * rows;
+                        const double *src = slots + e * SD + cur;
+                        const int4 m = map[r];
+                        const int ev[4] = {m.x, m.y, m.z, m.w};
                         double acc = 0.0;
 #pragma unroll
                         for (int k = 0; k < 4; ++k)
                         {
                             if (ev[k] == 0)
                                 break;
-                            const double v = cur[abs(ev[k]) - 1];
+                            const double v = src[abs(ev[k]) - 1];
                             acc += ev[k] < 0 ? -v : v;
                         }
-                        nxt[r] = acc;
+                        slots[e * SD + nxt + r] = acc;
                     }
-                    __syncwarp();
+                    __syncthreads();
                     n_out = rows;
-                }
-                else if (type == 1)
-                {
-                    if (fa == DK_MASS0)
-                    {
-                        interp_w(s, q, cur, s.node, np1, s.node, np1, s.u0);
-                        scale_points_w(s, q, 0, nullptr);
-                        project_w(s, q, s.u0, s.node, np1, s.node, np1, nxt);
-                        n_out = np1 * np1;
-                    }
-                    else if (fa == DK_MASS2)
-                    {
-                        interp_w(s, q, cur, s.edge, p, s.edge, p, s.u0);
-                        scale_points_w(s, q, 1, nullptr);
-                        project_w(s, q, s.u0, s.edge, p, s.edge, p, nxt);
-                        n_out = p * p;
-                    }
-                    else
-                    {
-                        interp_w(s, q, cur, s.node, np1, s.edge, p, s.u0);      // h part
-                        interp_w(s, q, cur + nh, s.edge, p, s.node, np1, s.u1); // v part
-                        scale_points_w(s, q, 2, nullptr);
-                        project_w(s, q, s.u0, s.node, np1, s.edge, p, nxt);
-                        project_w(s, q, s.u1, s.edge, p, s.node, np1, nxt + nh);
-                        n_out = 2 * nh;
-                    }
                 }
                 else
                 {
-                    const double *fld = args.fields[fb] + elem * (unsigned long long)(2 * q2);
-                    if (fa == DK_IPROD1 && !fc)
-                    { // (n0 x n1): 1-form in, 0-form out
-                        interp_w(s, q, cur, s.node, np1, s.edge, p, s.u0);
-                        interp_w(s, q, cur + nh, s.edge, p, s.node, np1, s.u1);
-                        scale_points_w(s, q, 3, fld);
-                        project_w(s, q, s.u0, s.node, np1, s.node, np1, nxt);
-                        n_out = np1 * np1;
+                    const TileOp op = tile_op(type, fa, fc, p);
+                    const double *fld = op.mode >= 3 ? args.fields[fb] : nullptr;
+                    // ---- phase A: t[e][row][:] = sum_j c[i, j] B_j[:] ----
+                    const int nA0 = op.in[0].kA == TK_NODE ? np1 : p, nA1 = op.n_in > 1 ? (op.in[1].kA == TK_NODE ? np1 : p) : 0;
+                    {
+                        const int R = nA0 + nA1;
+                        const float inv_R = 1.0f / (float)R;
+                        for (int idx = threadIdx.x; idx < nv * R; idx += blockDim.x)
+                        {
+                            const int e = (int)(((float)idx + 0.5f) * inv_R), row = idx - e * R;
+                            const TileComp cmp = row < nA0 ? op.in[0] : op.in[1];
+                            const int i = row < nA0 ? row : row - nA0;
+                            const int nB = cmp.kB == TK_NODE ? np1 : p;
+                            const double *c = slots + e * SD + cur + cmp.off + i * nB;
+                            const double *B = (smem + (cmp.kB) * edge_off);
+                            double acc[Q];
+#pragma unroll
+                            for (int b = 0; b < Q; ++b)
+                                acc[b] = 0.0;
+                            for (int j = 0; j < nB; ++j)
+                                row_axpy<Q>(acc, c[j], B + j * LDQ);
+                            double *dst = slots + e * SD + off_t + row * LDQ;
+#pragma unroll
+                            for (int b = 0; b + 1 < Q; b += 2)
+                                *reinterpret_cast<double2 *>(dst + b) = make_double2(acc[b], acc[b + 1]);
+                            if (Q & 1)
+                                dst[Q - 1] = acc[Q - 1];
+                        }
                     }
-                    else if (fa == DK_IPROD1)
-                    { // transposed: 0-form in, 1-form out
-                        interp_w(s, q, cur, s.node, np1, s.node, np1, s.u0);
-                        scale_points_w(s, q, 4, fld);
-                        project_w(s, q, s.u0, s.node, np1, s.edge, p, nxt);
-                        project_w(s, q, s.u1, s.edge, p, s.node, np1, nxt + nh);
-                        n_out = 2 * nh;
+                    __syncthreads();
+                    // ---- phase B: eta interpolation, metric weights, eta projection; thread (e, b) ----
+                    const int nO0 = op.out[0].kA == TK_NODE ? np1 : p, nO1 = op.n_out > 1 ? (op.out[1].kA == TK_NODE ? np1 : p) : 0;
+                    for (int idx = threadIdx.x; idx < nv * Q; idx += blockDim.x)
+                    {
+                        const int e = idx / Q, b = idx - e * Q;
+                        double *slot = slots + e * SD;
+                        double *tcol = slot + off_t + b;
+                        double u0[Q], u1[Q];
+#pragma unroll
+                        for (int a = 0; a < Q; ++a)
+                            u0[a] = u1[a] = 0.0;
+                        {
+                            const double *A = (smem + op.in[0].kA * edge_off);
+                            for (int i = 0; i < nA0; ++i)
+                                row_axpy<Q>(u0, tcol[i * LDQ], A + i * LDQ);
+                            const double *A1 = (smem + op.in[1].kA * edge_off);
+                            for (int i = 0; i < nA1; ++i)
+                                row_axpy<Q>(u1, tcol[(nA0 + i) * LDQ], A1 + i * LDQ);
+                        }
+                        const double x0 = slot[0], y0 = slot[1], x1 = slot[2], y1 = slot[3], x2 = slot[4], y2 = slot[5], x3 = slot[6],
+                                     y3 = slot[7];
+                        const double xi = pnts[b], wb = wgts[b];
+                        const double j10 = 0.25 * ((x3 - x0) * (1 - xi) + (x2 - x1) * (1 + xi));
+                        const double j11 = 0.25 * ((y3 - y0) * (1 - xi) + (y2 - y1) * (1 + xi));
+                        const double *fp = fld ? fld + (elem0 + e) * (unsigned long long)(2 * Q * Q) + 2 * b : nullptr;
+#pragma unroll
+                        for (int a = 0; a < Q; ++a)
+                        {
+                            const double eta = pnts[a], w = wgts[a] * wb;
+                            const double j00 = 0.25 * ((x1 - x0) * (1 - eta) + (x2 - x3) * (1 + eta));
+                            const double j01 = 0.25 * ((y1 - y0) * (1 - eta) + (y2 - y3) * (1 + eta));
+                            const double det = j00 * j11 - j10 * j01;
+                            const double a0 = u0[a], a1 = u1[a];
+                            switch (op.mode)
+                            {
+                            case 0:
+                                u0[a] = a0 * det * w;
+                                break;
+                            case 1:
+                                u0[a] = a0 * w / det;
+                                break;
+                            case 2: {
+                                const double khh = (j11 * j11 + j10 * j10) / det * w, kvv = (j00 * j00 + j01 * j01) / det * w,
+                                             khv = (j01 * j11 + j00 * j10) / det * w;
+                                u0[a] = khh * a0 + khv * a1;
+                                u1[a] = khv * a0 + kvv * a1;
+                                break;
+                            }
+                            case 3:
+                            case 4: {
+                                const double fx = fp[2 * a * Q], fy = fp[2 * a * Q + 1];
+                                const double kh = (fx * j11 - fy * j10) * w, kv = -(fy * j00 - fx * j01) * w;
+                                if (op.mode == 3)
+                                    u0[a] = kh * a0 + kv * a1;
+                                else
+                                {
+                                    u0[a] = kh * a0;
+                                    u1[a] = kv * a0;
+                                }
+                                break;
+                            }
+                            default: {
+                                const double fx = fp[2 * a * Q], fy = fp[2 * a * Q + 1];
+                                const double kh = -(fx * j10 + fy * j11) / det * w, kv = -(fx * j00 + fy * j01) / det * w;
+                                if (op.mode == 6)
+                                    u0[a] = kh * a0 + kv * a1;
+                                else
+                                {
+                                    u0[a] = kh * a0;
+                                    u1[a] = kv * a0;
+                                }
+                                break;
+                            }
+                            }
+                        }
+                        {
+                            const double *A = (smem + op.out[0].kA * edge_off);
+                            for (int i = 0; i < nO0; ++i)
+                                tcol[i * LDQ] = row_dot<Q>(A + i * LDQ, u0);
+                            const double *A1 = (smem + op.out[1].kA * edge_off);
+                            for (int i = 0; i < nO1; ++i)
+                                tcol[(nO0 + i) * LDQ] = row_dot<Q>(A1 + i * LDQ, u1);
+                        }
                     }
-                    else if (!fc)
-                    { // (n1 x n2): 2-form in, 1-form out
-                        interp_w(s, q, cur, s.edge, p, s.edge, p, s.u0);
-                        scale_points_w(s, q, 5, fld);
-                        project_w(s, q, s.u0, s.node, np1, s.edge, p, nxt);
-                        project_w(s, q, s.u1, s.edge, p, s.node, np1, nxt + nh);
-                        n_out = 2 * nh;
+                    __syncthreads();
+                    // ---- phase C: out[i, j] = B_j[:] . t'[e][row][:] ; thread (e, row) ----
+                    {
+                        const int R = nO0 + nO1;
+                        const float inv_R = 1.0f / (float)R;
+                        for (int idx = threadIdx.x; idx < nv * R; idx += blockDim.x)
+                        {
+                            const int e = (int)(((float)idx + 0.5f) * inv_R), row = idx - e * R;
+                            const TileComp cmp = row < nO0 ? op.out[0] : op.out[1];
+                            const int i = row < nO0 ? row : row - nO0;
+                            const int nB = cmp.kB == TK_NODE ? np1 : p;
+                            const double *src = slots + e * SD + off_t + row * LDQ;
+                            double tr[Q];
+#pragma unroll
+                            for (int b = 0; b + 1 < Q; b += 2)
+                            {
+                                const double2 v = *reinterpret_cast<const double2 *>(src + b);
+                                tr[b] = v.x;
+                                tr[b + 1] = v.y;
+                            }
+                            if (Q & 1)
+                                tr[Q - 1] = src[Q - 1];
+                            const double *B = (smem + (cmp.kB) * edge_off);
+                            double *dst = slots + e * SD + nxt + cmp.off + i * nB;
+                            for (int j = 0; j < nB; ++j)
+                                dst[j] = row_dot<Q>(B + j * LDQ, tr);
+                        }
                     }
-                    else
-                    { // transposed: 1-form in, 2-form out
-                        interp_w(s, q, cur, s.node, np1, s.edge, p, s.u0);
-                        interp_w(s, q, cur + nh, s.edge, p, s.node, np1, s.u1);
-                        scale_points_w(s, q, 6, fld);
-                        project_w(s, q, s.u0, s.edge, p, s.edge, p, nxt);
-                        n_out = p * p;
-                    }
+                    __syncthreads();
+                    n_out = 0;
+                    for (int k = 0; k < op.n_out; ++k)
+                        n_out += (op.out[k].kA == TK_NODE ? np1 : p) * (op.out[k].kB == TK_NODE ? np1 : p);
                 }
                 cur = nxt;
-                nxt = (nxt == s.v0) ? s.v1 : s.v0;
+                nxt = (nxt == off_va) ? off_vb : off_va;
                 n_cur = n_out;
             }
             const double cf_ = coef[ci];
-            for (int i = MFV2D_LANE0; i < n_cur; i += MFV2D_LANE_STEP)
-                s.ys[r0 + i] = fma(cf_, cur[i], s.ys[r0 + i]);
-            __syncwarp();
+            const float inv_nc = 1.0f / (float)(n_cur > 0 ? n_cur : 1);
+            for (int idx = threadIdx.x; idx < nv * n_cur; idx += blockDim.x)
+            {
+                const int e = (int)(((float)idx + 0.5f) * inv_nc), k = idx - e * n_cur;
+                double *slot = slots + e * SD;
+                slot[off_ys + r0 + k] = fma(cf_, slot[cur + k], slot[off_ys + r0 + k]);
+            }
+            __syncthreads();
         }
-        for (int i = MFV2D_LANE0; i < N; i += MFV2D_LANE_STEP)
-            args.y[elem * N + i] = s.ys[i];
-        __syncwarp();
+        {
+            const float inv_n = 1.0f / (float)N;
+            for (int i = threadIdx.x; i < nv * N; i += blockDim.x)
+            {
+                const int e = (int)(((float)i + 0.5f) * inv_n), k = i - e * N;
+                args.y[elem0 * N + i] = slots[e * SD + off_ys + k];
+            }
+        }
     }
+}
+
+template <int Q> static int launch_tile_q(mfv2d_ctx *ctx, ApplyTArgs &ta, size_t fixed_bytes, size_t n_elem)
+{
+    // elements per pass: enough to keep the CTA's threads busy in the (e, row) / (e, column) phases, within
+    // half of the SM's shared memory so that two CTAs are resident
+    const size_t slot_bytes = (size_t)ta.slot_doubles * 8;
+    const size_t budget = ((size_t)228 * 1024 - 2048) / 2;
+    int epb = (int)((budget > fixed_bytes ? budget - fixed_bytes : 0) / slot_bytes);
+    const int want = (APPLYT_THREADS + Q - 1) / Q;
+    if (epb > want)
+        epb = want;
+    if (epb < 1)
+        epb = 1;
+    ta.epb = epb;
+    const size_t smem = fixed_bytes + (size_t)epb * slot_bytes;
+    if (smem > ctx->smem_optin)
+        return mfv2d_fail(ctx, MFV2D_CUDA_UNSUPPORTED, "element vectors need %zu bytes of shared memory", smem);
+    MFV2D_CUDA_CHECK(ctx, cudaFuncSetAttribute(element_vector_tile_kernel<Q>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int per_sm = 1;
+    MFV2D_CUDA_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, element_vector_tile_kernel<Q>, APPLYT_THREADS, smem));
+    if (per_sm < 1)
+        per_sm = 1;
+    unsigned long long grid = (unsigned long long)ctx->sm_count * per_sm;
+    const unsigned long long need = (n_elem + epb - 1) / epb;
+    if (grid > need)
+        grid = need;
+    MFV2D_LAUNCH(element_vector_tile_kernel<Q>, (unsigned)grid, APPLYT_THREADS, smem, ctx->stream, ta);
+    ctx->launches++;
+    MFV2D_CUDA_CHECK(ctx, cudaGetLastError());
+    return MFV2D_SUCCESS;
 }
 
 static int launch_apply(const mfv2d_plan *plan, const mfv2d_elements *e, const double *const *fields, const double *d_x,
@@ -808,36 +902,42 @@ static int launch_apply(const mfv2d_plan *plan, const mfv2d_elements *e, const d
         const int nmax = 2 * p * np1;
         doubles += ((q2 + 1) & ~1) + q * ldT + 4 + (size_t)nmax * nmax + 8;
     }
-    if (!column_mode && !plan->vector_needs_dense && e->n > 0)
+    if (!column_mode && !plan->vector_needs_dense && e->n > 0 && q >= 2 && q <= 16)
     {
-        // fast path: one warp per element
-        ApplyWArgs wa{};
-        wa.a = a;
+        // fast path: register-tiled kernel
+        ApplyTArgs ta{};
+        ta.a = a;
         const int n_prog_total = (int)plan->vprog.size(), n_coef_total = (int)plan->vcoef.size();
-        wa.prog_len = plan->mprog_off ? plan->mprog_off : n_prog_total;
-        wa.n_coef = plan->mcoef_off ? plan->mcoef_off : n_coef_total;
-        wa.inc_rows = plan->basis->inc_off[4];
-        wa.warp_doubles = (2 * q2 + 2 * np1 * q + 2 * a.vmax + 2 * a.n_total + 3) & ~1;
-        const size_t shared_part = (((size_t)a.tab_len + 1) & ~(size_t)1) * 8 + (((size_t)wa.n_coef + 1) & ~(size_t)1) * 8 +
-                                   (((size_t)wa.prog_len + 3) & ~(size_t)3) * 4 + (size_t)wa.inc_rows * 16;
-        const size_t smem_w = shared_part + (size_t)APPLYW_WARPS * wa.warp_doubles * 8;
-        if (smem_w <= ctx->smem_optin)
+        ta.prog_len = plan->mprog_off ? plan->mprog_off : n_prog_total;
+        ta.n_coef = plan->mcoef_off ? plan->mcoef_off : n_coef_total;
+        ta.inc_rows = plan->basis->inc_off[4];
+        const int ldq = (q + 1) & ~1;
+        ta.slot_doubles = (8 + 2 * a.n_total + 2 * a.vmax + (2 * p + 2) * ldq + 1) & ~1;
+        const size_t fixed_bytes = ((size_t)(2 * p + 1) * ldq + 2 * ldq + (((size_t)ta.n_coef + 1) & ~(size_t)1)) * 8 +
+                                   (((size_t)ta.prog_len + 3) & ~(size_t)3) * 4 + (size_t)ta.inc_rows * 16;
+        switch (q)
         {
-            MFV2D_CUDA_CHECK(ctx, cudaFuncSetAttribute(element_vector_warp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                                       (int)smem_w));
-            int per_sm_w = 1;
-            MFV2D_CUDA_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_w, element_vector_warp_kernel,
-                                                                                APPLYW_WARPS * 32, smem_w));
-            if (per_sm_w < 1)
-                per_sm_w = 1;
-            unsigned long long grid_w = (unsigned long long)ctx->sm_count * per_sm_w;
-            const unsigned long long need = (e->n + APPLYW_WARPS - 1) / APPLYW_WARPS;
-            if (grid_w > need)
-                grid_w = need;
-            MFV2D_LAUNCH(element_vector_warp_kernel, (unsigned)grid_w, APPLYW_WARPS * 32, smem_w, ctx->stream, wa);
-            ctx->launches++;
-            MFV2D_CUDA_CHECK(ctx, cudaGetLastError());
-            return MFV2D_SUCCESS;
+#define MFV2D_Q_CASE(Q)                                                                                        \
+    case Q:                                                                                                    \
+        return launch_tile_q<Q>(ctx, ta, fixed_bytes, e->n);
+            MFV2D_Q_CASE(2)
+            MFV2D_Q_CASE(3)
+            MFV2D_Q_CASE(4)
+            MFV2D_Q_CASE(5)
+            MFV2D_Q_CASE(6)
+            MFV2D_Q_CASE(7)
+            MFV2D_Q_CASE(8)
+            MFV2D_Q_CASE(9)
+            MFV2D_Q_CASE(10)
+            MFV2D_Q_CASE(11)
+            MFV2D_Q_CASE(12)
+            MFV2D_Q_CASE(13)
+            MFV2D_Q_CASE(14)
+            MFV2D_Q_CASE(15)
+            MFV2D_Q_CASE(16)
+#undef MFV2D_Q_CASE
+        default:
+            break;
         }
     }
     const size_t smem = doubles * sizeof(double);
