@@ -725,6 +725,7 @@ template <int Q> __global__ void __launch_bounds__(APPLYT_THREADS, 2) element_ve
                             const double j00 = 0.25 * ((x1 - x0) * (1 - eta) + (x2 - x3) * (1 + eta));
                             const double j01 = 0.25 * ((y1 - y0) * (1 - eta) + (y2 - y3) * (1 + eta));
                             const double det = j00 * j11 - j10 * j01;
+                            const double wod = w / det; // the only division per point
                             const double a0 = u0[a], a1 = u1[a];
                             switch (op.mode)
                             {
@@ -732,11 +733,11 @@ template <int Q> __global__ void __launch_bounds__(APPLYT_THREADS, 2) element_ve
                                 u0[a] = a0 * det * w;
                                 break;
                             case 1:
-                                u0[a] = a0 * w / det;
+                                u0[a] = a0 * wod;
                                 break;
                             case 2: {
-                                const double khh = (j11 * j11 + j10 * j10) / det * w, kvv = (j00 * j00 + j01 * j01) / det * w,
-                                             khv = (j01 * j11 + j00 * j10) / det * w;
+                                const double khh = (j11 * j11 + j10 * j10) * wod, kvv = (j00 * j00 + j01 * j01) * wod,
+                                             khv = (j01 * j11 + j00 * j10) * wod;
                                 u0[a] = khh * a0 + khv * a1;
                                 u1[a] = khv * a0 + kvv * a1;
                                 break;
@@ -756,7 +757,7 @@ template <int Q> __global__ void __launch_bounds__(APPLYT_THREADS, 2) element_ve
                             }
                             default: {
                                 const double fx = fp[2 * a * Q], fy = fp[2 * a * Q + 1];
-                                const double kh = -(fx * j10 + fy * j11) / det * w, kv = -(fx * j00 + fy * j01) / det * w;
+                                const double kh = -(fx * j10 + fy * j11) * wod, kv = -(fx * j00 + fy * j01) * wod;
                                 if (op.mode == 6)
                                     u0[a] = kh * a0 + kv * a1;
                                 else
