@@ -747,19 +747,50 @@ def _solve_linear_system(mat, rhs, /) -> np.ndarray:
 
 
 def compute_element_projector(form_orders, basis_in: Basis2D, space_out: ElementFemSpace2D, dual: bool = False):
-    """src/evaluation/element_system.c:480-643."""
+    """src/evaluation/element_system.c:480-643: per form, the mass between the output basis (rows) and
+    ``basis_in`` (columns) on ``space_out``'s geometry; ``dual=False`` multiplies by the inverse output mass.
+    ``form_orders`` is an ``_ElementFormSpecification`` (as in the reference) or a sequence of form orders; the
+    result is a tuple aligned with it (forms of equal order share one array, :621-630)."""
+    if not isinstance(basis_in, Basis2D):
+        raise TypeError("basis_in must be a Basis2D")
+    if not isinstance(space_out, ElementFemSpace2D):
+        raise TypeError("space_out must be an ElementFemSpace2D")
+    orders = form_orders.orders if isinstance(form_orders, _ElementFormSpecification) else tuple(int(o) for o in form_orders)
     batch = space_out.batch
     p_in, q_in = basis_in._square()
     if q_in != batch.q:
         raise ValueError("Input and output bases must share the integration rule.")
     b_in = batch.ctx.basis(p_in, q_in)
-    res = []
-    for order in form_orders:
-        order = int(order)
+    done: dict[int, np.ndarray] = {}
+    for order in orders:
+        if order in done:
+            continue
+        if order < FORM_ORDER_0 or order > FORM_ORDER_2:
+            raise ValueError(f"Invalid form order: {order}")
         n_out, n_in = _form_size(order, batch.p, batch.p), _form_size(order, p_in, p_in)
         out = np.empty((1, n_out, n_in))
         status = np.zeros(1, np.int32)
         check(lib().mfv2d_cuda_projector_batch(batch.handle, b_in.handle, order, int(bool(dual)), out.ctypes.data,
                                                status.ctypes.data, HOST), batch.ctx.handle)
-        res.append(out[0])
-    return tuple(res)
+        if status[0]:
+            raise _capi.Mfv2dCudaError(int(status[0]), _capi.result_name(int(status[0])), "output mass matrix could not be inverted")
+        done[order] = out[0]
+    return tuple(done[o] for o in orders)
+
+
+def compute_element_projectors(order: int, basis_in: Basis2D, batch: ElementBatch, dual: bool = False, out=None):
+    """Batched projector of one form order for every element of ``batch``: ``(n, n_k(out), n_k(in))``."""
+    p_in, q_in = basis_in._square()
+    if q_in != batch.q:
+        raise ValueError("Input and output bases must share the integration rule.")
+    b_in = batch.ctx.basis(p_in, q_in)
+    n_out, n_in = _form_size(int(order), batch.p, batch.p), _form_size(int(order), p_in, p_in)
+    out = batch._out(out, (batch.n, n_out, n_in))
+    space = space_of(out)
+    status = np.zeros(batch.n, np.int32) if space == HOST else None
+    check(lib().mfv2d_cuda_projector_batch(batch.handle, b_in.handle, int(order), int(bool(dual)), addr(out), addr(status), space),
+          batch.ctx.handle)
+    if status is not None and np.any(status):
+        bad = int(np.flatnonzero(status)[0])
+        raise _capi.Mfv2dCudaError(int(status[bad]), _capi.result_name(int(status[bad])), f"element {bad}: output mass matrix could not be inverted")
+    return out

@@ -315,6 +315,16 @@ static int dense_batch(const mfv2d_elements *e, int dk, int inverse, int transpo
     return r;
 }
 
+} // extern "C"
+
+// inverse mass matrices into device memory (used by projector.cu)
+int launch_mass_inverse_device(const mfv2d_elements *e, int form, double *d_out, int32_t *d_status)
+{
+    return dense_batch(e, DK_MASS0 + (form - 1), 1, 0, nullptr, d_out, d_status, MFV2D_DEVICE);
+}
+
+extern "C" {
+
 int mfv2d_cuda_mass_batch(const mfv2d_elements *e, int form, int inverse, double *out, int32_t *status, int space)
 {
     if (form < MFV2D_FORM_ORDER_0 || form > MFV2D_FORM_ORDER_2)

@@ -11,6 +11,7 @@ reference's own iterative solution (both stop at a residual tolerance), indices 
 from __future__ import annotations
 
 import numpy as np
+import pytest
 from conftest import golden, load_systems, relerr
 
 import fields as F
@@ -290,3 +291,39 @@ def check_linear_system(M, SV, ST, fix, nh, nv):
     a, b = g["x"], g["rhs"]
     assert relerr(SV.vec_axpby(2.0, a, -0.5, b), 2.0 * a - 0.5 * b) < 1e-15
     assert abs(SV.vec_dot(a, b) - a @ b) < 1e-10 * abs(a @ b) + 1e-12
+
+
+def check_projectors(M):
+    """compute_element_projector against the reference's own output (tests/golden/projector.npz) and the oracle."""
+    g = golden("projector.npz")
+    specs = M._ElementFormSpecification(("a", 1), ("b", 2), ("c", 3))
+    for po, pi, ro in g["cases"]:
+        po, pi, ro = int(po), int(pi), int(ro)
+        rule = M.IntegrationRule1D(ro)
+        bo1, bi1 = M.Basis1D(po, rule), M.Basis1D(pi, rule)
+        bo, bi = M.Basis2D(bo1, bo1), M.Basis2D(bi1, bi1)
+        for iq in (4, 5):
+            sp = M.ElementFemSpace2D(bo, np.ascontiguousarray(F.QUADS[iq]))
+            for dual in (False, True):
+                res = M.compute_element_projector(specs, bi, sp, dual)
+                assert len(res) == 3
+                for fo, m in zip((1, 2, 3), res):
+                    ref = g[f"po{po}_pi{pi}_r{ro}_q{iq}_d{int(dual)}_f{fo}"]
+                    assert m.shape == ref.shape
+                    assert relerr(m, ref) < (TOL_MAT if dual else TOL_INV), (po, pi, iq, dual, fo, relerr(m, ref))
+        # batched entry point and the oracle's two-basis mass on all the test quads
+        batch = M.ElementBatch(bo, np.ascontiguousarray(F.QUADS))
+        ob_o, ob_i = O.basis(po, ro + 1), O.basis(pi, ro + 1)
+        for fo in (1, 2, 3):
+            mm = M.compute_element_projectors(fo, bi, batch, dual=True)
+            assert relerr(mm, O.mass_double(ob_o, ob_i, F.QUADS, fo)) < TOL_MAT
+    # projecting onto the same basis is the identity; mismatched rules are rejected like the reference does
+    rule = M.IntegrationRule1D(6)
+    b1 = M.Basis1D(3, rule)
+    b = M.Basis2D(b1, b1)
+    sp = M.ElementFemSpace2D(b, np.ascontiguousarray(F.QUADS[6]))
+    for m in M.compute_element_projector((1, 2, 3), b, sp):
+        assert relerr(m, np.eye(m.shape[0])) < 1e-10
+    b2 = M.Basis1D(3, M.IntegrationRule1D(5))
+    with pytest.raises(ValueError):
+        M.compute_element_projector((1,), M.Basis2D(b2, b2), sp)

@@ -62,6 +62,10 @@ def test_fields(emu):
     P.check_fields(emu[0])
 
 
+def test_projectors(emu):
+    P.check_projectors(emu[0])
+
+
 def test_interior_products(emu):
     P.check_interior_products(emu[0], p=3, k=2)
 

@@ -60,6 +60,10 @@ def test_fields(gpu):
     P.check_fields(gpu[0])
 
 
+def test_projectors(gpu):
+    P.check_projectors(gpu[0])
+
+
 def test_interior_products(gpu):
     P.check_interior_products(gpu[0], p=4, k=2)
     P.check_interior_products(gpu[0], p=6, k=3)
