@@ -241,6 +241,32 @@ __global__ void __launch_bounds__(SYS_THREADS) schur_local_kernel(unsigned long 
     }
 }
 
+// slot_val[s0 + r] = S_e[r][r]: the elements' contributions to diag(S)
+__global__ void schur_diag_kernel(unsigned long long n_elem, const int64_t *__restrict__ slot_off, const int64_t *__restrict__ s_off,
+                                  const double *__restrict__ S, double *__restrict__ slot_val)
+{
+    for (unsigned long long e = blockIdx.x; e < n_elem; e += gridDim.x)
+    {
+        const int64_t s0 = slot_off[e];
+        const int m = (int)(slot_off[e + 1] - s0);
+        const double *Se = S + s_off[e];
+        for (int r = threadIdx.x; r < m; r += blockDim.x)
+            slot_val[s0 + r] = Se[(size_t)r * m + r];
+    }
+}
+
+// d[i] = 1 / d[i] (1 where the diagonal vanishes); z[i] = d[i] r[i]
+__global__ void jacobi_setup_kernel(long long n, double *__restrict__ d, const double *__restrict__ r, double *__restrict__ z)
+{
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    {
+        const double v = d[i];
+        const double inv = v != 0.0 ? 1.0 / v : 1.0;
+        d[i] = inv;
+        z[i] = inv * r[i];
+    }
+}
+
 // out[i] = sum of the slots of multiplier i; optionally partial sums of out[i] * w[i] (for p.Ap)
 __global__ void __launch_bounds__(SYS_THREADS) trace_gather_kernel(long long n_trace, const int64_t *__restrict__ tr_ptr,
                                                                   const int64_t *__restrict__ tr_slot,
@@ -943,16 +969,32 @@ int mfv2d_cuda_solve_schur_cg(mfv2d_system *s, const double *rhs, const double *
         {
             cudaMemcpyAsync(sc + 4, &h[4], sizeof(double), cudaMemcpyHostToDevice, ctx->stream);
             cudaStreamSynchronize(ctx->stream);
+            const double *dinv = nullptr;
             if (precondition)
             {
-                // Jacobi on the trace space: diag(S) gathered from the condensed blocks
-                // z0 = Minv r0, p0 = z0, rz = r0 . z0
-                // diag is computed by applying S to nothing special: use the slots' diagonal entries
-                // (kernel below is small: reuse csr structure) -> computed on first use
-                r = mfv2d_fail(ctx, MFV2D_CUDA_UNSUPPORTED, "preconditioned Schur CG is not implemented yet");
-                break;
+                // Jacobi on the trace space (not in the reference): diag(S) from the diagonals of the condensed blocks,
+                // summed per multiplier and over the ranks; z0 = D^-1 r0, p0 = z0, rz = r0 . z0
+                long long grid = (long long)ctx->sm_count * 8;
+                if (grid > s->n_elem)
+                    grid = s->n_elem;
+                if (s->n_elem)
+                {
+                    MFV2D_LAUNCH(schur_diag_kernel, (unsigned)grid, 32, 0, ctx->stream, (unsigned long long)s->n_elem, s->d_slot_off,
+                                 s->d_s_off, s->d_S, s->d_slot_val);
+                    ctx->launches++;
+                }
+                MFV2D_LAUNCH(trace_gather_kernel, grid_for(ctx, nt, SYS_THREADS), SYS_THREADS, 0, ctx->stream, nt, s->d_tr_ptr,
+                             s->d_tr_slot, s->d_slot_val, s->d_diag_inv, (const int *)nullptr);
+                ctx->launches++;
+                if ((r = sys_interface_sum(s, s->d_diag_inv, 0, nullptr)))
+                    break;
+                MFV2D_LAUNCH(jacobi_setup_kernel, grid_for(ctx, nt, 256), 256, 0, ctx->stream, nt, s->d_diag_inv, (const double *)res, z);
+                ctx->launches++;
+                if ((r = sys_dot_device(s, nt, res, z, w, sc + 5)))
+                    break;
+                dinv = s->d_diag_inv;
             }
-            cudaMemcpyAsync(p, res, nt * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream);
+            cudaMemcpyAsync(p, precondition ? z : res, nt * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream);
             const int check_every = 16;
             // one CG iteration = 7 small launches; on one GPU a block of check_every iterations is captured ONCE
             // into a CUDA graph and replayed (the kernels stop by themselves once the device flag is set)
@@ -965,29 +1007,31 @@ int mfv2d_cuda_solve_schur_cg(mfv2d_system *s, const double *rhs, const double *
                     MFV2D_LAUNCH(sum_partials_kernel, 1, 32, 0, ctx->stream, s->n_partials, (const double *)s->d_partials,
                                  s->d_partials);
                     MFV2D_TRY(comm_allreduce(ctx, s->d_partials, 1));
-                    MFV2D_LAUNCH(cg_alpha_kernel, 1, 32, 0, ctx->stream, 1, (const double *)s->d_partials, sc, flags, 0);
+                    MFV2D_LAUNCH(cg_alpha_kernel, 1, 32, 0, ctx->stream, 1, (const double *)s->d_partials, sc, flags, precondition);
                     ctx->launches++;
                 }
                 else
                     MFV2D_LAUNCH(cg_alpha_kernel, 1, 32, 0, ctx->stream, s->n_partials, (const double *)s->d_partials, sc, flags,
-                                 0);
+                                 precondition);
                 MFV2D_LAUNCH(cg_update_kernel, (unsigned)s->n_partials, SYS_THREADS, 0, ctx->stream, nt, (const double *)sc,
-                             (const int *)flags, (const double *)p, (const double *)ap, lam, res, w, (const double *)nullptr, z,
-                             s->d_partials, s->d_partials + s->n_partials);
+                             (const int *)flags, (const double *)p, (const double *)ap, lam, res, w, dinv, z, s->d_partials,
+                             s->d_partials + s->n_partials);
                 if (ctx->n_ranks > 1)
                 {
-                    MFV2D_LAUNCH(sum_partials_kernel, 1, 32, 0, ctx->stream, s->n_partials, (const double *)s->d_partials,
-                                 s->d_partials);
-                    MFV2D_TRY(comm_allreduce(ctx, s->d_partials, 1));
-                    MFV2D_LAUNCH(cg_beta_kernel, 1, 32, 0, ctx->stream, 1, (const double *)s->d_partials,
-                                 (const double *)s->d_partials, sc, flags, 0, -1);
-                    ctx->launches++;
+                    // r.r (and r.z) of all ranks: two scalars in one all-reduce
+                    MFV2D_LAUNCH(sum_partials_kernel, 1, 32, 0, ctx->stream, s->n_partials, (const double *)s->d_partials, sc + 8);
+                    MFV2D_LAUNCH(sum_partials_kernel, 1, 32, 0, ctx->stream, precondition ? s->n_partials : 0,
+                                 (const double *)(s->d_partials + s->n_partials), sc + 9);
+                    MFV2D_TRY(comm_allreduce(ctx, sc + 8, 2));
+                    MFV2D_LAUNCH(cg_beta_kernel, 1, 32, 0, ctx->stream, 1, (const double *)(sc + 8), (const double *)(sc + 9), sc, flags,
+                                 precondition, -1);
+                    ctx->launches += 2;
                 }
                 else
                     MFV2D_LAUNCH(cg_beta_kernel, 1, 32, 0, ctx->stream, s->n_partials, (const double *)s->d_partials,
-                                 (const double *)(s->d_partials + s->n_partials), sc, flags, 0, -1);
+                                 (const double *)(s->d_partials + s->n_partials), sc, flags, precondition, -1);
                 MFV2D_LAUNCH(cg_direction_kernel, grid_for(ctx, nt, 256), 256, 0, ctx->stream, nt, (const double *)sc,
-                             (const int *)flags, (const double *)res, p);
+                             (const int *)flags, (const double *)(precondition ? z : res), p);
                 ctx->launches += 5;
                 return MFV2D_SUCCESS;
             };
@@ -1088,10 +1132,147 @@ int mfv2d_cuda_solve_schur_cg(mfv2d_system *s, const double *rhs, const double *
     return r;
 }
 
-int mfv2d_cuda_solve_pcg(mfv2d_system *s, const double *, const double *, int, double, double, double *, double *, double *,
-                         int *, int)
+// solve_pcg_iterative (python/mfv2d/solving.py:634-684) with pcg_general (:280-347): preconditioned CG on the
+// saddle-point system K = [[A, N^T], [N, 0]] with the block-Jacobi preconditioner A^-1 (+) I.  Full vectors are
+// stored as [dense | trace] so that every BLAS-1 step and dot product is one launch; the scalars are read back
+// once per dot product (this driver follows the reference's control flow, including its degeneracy test; the
+// production path is the Schur-complement CG above).
+int mfv2d_cuda_solve_pcg(mfv2d_system *s, const double *rhs, const double *phi, int max_iter, double atol, double rtol, double *x,
+                         double *lambda, double *residual, int *iterations, int space)
 {
-    return mfv2d_fail(s->ctx, MFV2D_CUDA_UNSUPPORTED, "mfv2d_cuda_solve_pcg is not implemented yet");
+    mfv2d_ctx *ctx = s->ctx;
+    if (ctx->n_ranks > 1)
+        return mfv2d_fail(ctx, MFV2D_CUDA_UNSUPPORTED, "solve_pcg runs on one GPU (use solve_schur_cg for partitioned systems)");
+    const long long nd = s->n_dense, nt = s->n_trace, nf = nd + nt;
+    Staged srhs, sphi, sx, slam;
+    int r = stage_in(ctx, rhs, nd * sizeof(double), space, &srhs);
+    if (!r)
+        r = stage_in(ctx, phi, nt * sizeof(double), space, &sphi);
+    if (!r)
+        r = stage_out_alloc(ctx, x, nd * sizeof(double), space, &sx);
+    if (!r)
+        r = stage_out_alloc(ctx, lambda, nt * sizeof(double), space, &slam);
+    double *buf = nullptr;
+    if (!r)
+        r = mfv2d_cuda_malloc(ctx, (size_t)(6 * nf + 2 * nd + 8) * sizeof(double), (void **)&buf);
+    double res_mag2 = 0.0;
+    int iter_cnt = 0;
+    if (!r)
+    {
+        double *b = buf, *xs = b + nf, *res = xs + nf, *pv = res + nf, *z = pv + nf, *ap = z + nf, *t1 = ap + nf, *t2 = t1 + nd;
+        double *sc = ctx->d_scalars;
+        double h[4];
+        const unsigned gf = grid_for(ctx, nf, 256);
+        auto apply_system = [&](const double *v, double *out) -> int { // out = K v
+            MFV2D_TRY(sys_gemv(s, s->d_A, v, t1));
+            MFV2D_TRY(sys_spmv(s, nd, s->d_t_ptr, s->d_t_col, s->d_t_val, v + nd, t2));
+            if (nd)
+            {
+                MFV2D_LAUNCH(axpby_kernel, grid_for(ctx, nd, 256), 256, 0, ctx->stream, nd, 1.0, (const double *)t1, 1.0,
+                             (const double *)t2, out);
+                ctx->launches++;
+            }
+            return sys_spmv(s, nt, s->d_n_ptr, s->d_n_col, s->d_n_val, v, out + nd);
+        };
+        auto precondition = [&](const double *v, double *out) -> int { // out = (A^-1 (+) I) v
+            MFV2D_TRY(sys_gemv(s, s->d_Ainv, v, out));
+            if (nt)
+                MFV2D_CUDA_CHECK(ctx, cudaMemcpyAsync(out + nd, v + nd, nt * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream));
+            return MFV2D_SUCCESS;
+        };
+        auto dot = [&](const double *u, const double *v, double *result) -> int {
+            MFV2D_TRY(sys_dot_device(s, nf, u, v, nullptr, sc));
+            MFV2D_TRY(read_scalars(ctx, sc, 1, h));
+            *result = h[0];
+            return MFV2D_SUCCESS;
+        };
+        auto axpby = [&](double a, const double *u, double c, const double *v, double *out) {
+            MFV2D_LAUNCH(axpby_kernel, gf, 256, 0, ctx->stream, nf, a, u, c, v, out);
+            ctx->launches++;
+        };
+        do
+        {
+            cudaMemcpyAsync(b, srhs.dev, nd * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream);
+            if (nt)
+                cudaMemcpyAsync(b + nd, sphi.dev, nt * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream);
+            cudaMemsetAsync(xs, 0, nf * sizeof(double), ctx->stream);
+            // the initial guess is zero: res = rhs - K 0
+            cudaMemcpyAsync(res, b, nf * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream);
+            if ((r = precondition(res, z)))
+                break;
+            cudaMemcpyAsync(pv, z, nf * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream);
+            if ((r = dot(b, b, &res_mag2)))
+                break;
+            const double mag = sqrt(res_mag2);
+            const double tol = (mag * rtol > atol) ? atol : mag * rtol;
+            double rz = 0.0;
+            if ((r = dot(res, z, &rz)))
+                break;
+            for (iter_cnt = 0; iter_cnt < max_iter; ++iter_cnt)
+            {
+                if ((r = apply_system(pv, ap)))
+                    break;
+                double apa = 0.0;
+                if ((r = dot(ap, pv, &apa)))
+                    break;
+                if (log(fabs(apa)) - log(res_mag2) < log(1e-12)) // solving.py:331-332
+                {
+                    r = mfv2d_fail(ctx, MFV2D_UNSPECIFIED_ERROR, "System degenerated (matrix was probably not SPD).");
+                    break;
+                }
+                const double alpha = rz / apa;
+                axpby(1.0, xs, alpha, pv, xs);
+                axpby(1.0, res, -alpha, ap, res);
+                if ((r = dot(res, res, &res_mag2)))
+                    break;
+                if (res_mag2 < tol * tol)
+                    break;
+                if ((r = precondition(res, z)))
+                    break;
+                double new_rz = 0.0;
+                if ((r = dot(res, z, &new_rz)))
+                    break;
+                const double beta = new_rz / rz;
+                rz = new_rz;
+                axpby(1.0, z, beta, pv, pv);
+            }
+            if (r)
+                break;
+            if (iter_cnt == max_iter && max_iter > 0)
+                iter_cnt = max_iter - 1; // Python's loop variable after an exhausted range
+            cudaMemcpyAsync(sx.dev, xs, nd * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream);
+            if (nt)
+                cudaMemcpyAsync(slam.dev, xs + nd, nt * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream);
+            if (cudaGetLastError() != cudaSuccess)
+                r = mfv2d_fail(ctx, MFV2D_CUDA_ERROR, "PCG kernel launch failed");
+        } while (0);
+    }
+    if (!r)
+    {
+        r = stage_finish(&sx);
+        const int r2 = stage_finish(&slam);
+        if (!r)
+            r = r2;
+        if (!r)
+            r = mfv2d_cuda_synchronize(ctx);
+    }
+    else
+    {
+        stage_abort(&sx);
+        stage_abort(&slam);
+    }
+    stage_abort(&srhs);
+    stage_abort(&sphi);
+    if (buf)
+    {
+        mfv2d_cuda_synchronize(ctx);
+        mfv2d_cuda_free(ctx, buf);
+    }
+    if (residual)
+        *residual = sqrt(res_mag2);
+    if (iterations)
+        *iterations = iter_cnt;
+    return r;
 }
 
 int mfv2d_cuda_system_set_interface(mfv2d_system *s, size_t n_shared, const int64_t *shared_index, const int64_t *slot,

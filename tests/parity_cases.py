@@ -10,6 +10,9 @@ reference's own iterative solution (both stop at a residual tolerance), indices 
 """
 from __future__ import annotations
 
+import json
+import os
+
 import numpy as np
 import pytest
 from conftest import golden, load_systems, relerr
@@ -287,6 +290,19 @@ def check_linear_system(M, SV, ST, fix, nh, nv):
     r2 = g["con_rhs"] - sysm.apply_trace(x)
     rel = np.sqrt(r1 @ r1 + r2 @ r2) / np.sqrt(g["rhs"] @ g["rhs"] + g["con_rhs"] @ g["con_rhs"])
     assert rel < 1e-10, rel
+    # Jacobi-preconditioned Schur CG: same solution, no more iterations than the plain one
+    xj, lj, _, itj = SV.solve_schur_iterative(sysm, g["rhs"], g["con_rhs"], SV.ConvergenceSettings(2000, 1e-30, 1e-12), precondition=True)
+    assert relerr(xj, g["sol_dense"]) < 1e-8 and relerr(lj, g["sol_trace"]) < 1e-8
+    assert itj <= it
+    # solve_pcg_iterative (python/mfv2d/solving.py:634-684) with the reference's own settings; its iteration count
+    # on these systems is in tests/golden/pcg.json (the stopping test sits at 1e-30 absolute, so the count moves
+    # by a few percent with the rounding of the dot products)
+    with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "pcg.json")) as f:
+        ref_pcg = json.load(f)[fix]
+    xp, lp, resp, itp = SV.solve_pcg_iterative(sysm, g["rhs"], g["con_rhs"], SV.ConvergenceSettings(5000, 1e-30, 1e-10))
+    assert relerr(xp, g["sol_dense"]) < 1e-8 and relerr(lp, g["sol_trace"]) < 1e-8
+    assert resp < 1e-30
+    assert abs(itp - ref_pcg["iterations"]) <= max(12, ref_pcg["iterations"] // 10), (itp, ref_pcg)
     # BLAS-1
     a, b = g["x"], g["rhs"]
     assert relerr(SV.vec_axpby(2.0, a, -0.5, b), 2.0 * a - 0.5 * b) < 1e-15
