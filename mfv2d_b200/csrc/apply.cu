@@ -10,6 +10,9 @@
 // programs whose blocks are not of the form  coef * [E] * D * [E].
 #include "dense_device.cuh"
 
+#include <algorithm>
+#include <array>
+
 #define APPLY_THREADS 128
 
 // flattened program: [n_terms] then per term: row_form, col_form, coef_index, n_factors, 4 ints per factor
@@ -59,6 +62,8 @@ static void flatten(const mfv2d_plan *plan, const std::vector<BlockProgram> &blo
     prog[0] = n_terms;
 }
 
+static int plan_lower_vector_fused(mfv2d_plan *plan);
+
 int plan_lower_vector(mfv2d_plan *plan)
 {
     std::vector<int32_t> vprog, mprog;
@@ -80,7 +85,7 @@ int plan_lower_vector(mfv2d_plan *plan)
     MFV2D_TRY(mfv2d_cuda_malloc(plan->ctx, plan->vcoef.size() * sizeof(double), (void **)&plan->d_vcoef));
     MFV2D_TRY(mfv2d_cuda_upload(plan->ctx, plan->d_vprog, plan->vprog.data(), plan->vprog.size() * sizeof(int32_t)));
     MFV2D_TRY(mfv2d_cuda_upload(plan->ctx, plan->d_vcoef, plan->vcoef.data(), plan->vcoef.size() * sizeof(double)));
-    return MFV2D_SUCCESS;
+    return plan_lower_vector_fused(plan);
 }
 
 struct ApplyArgs
@@ -468,7 +473,7 @@ struct TileOp
     TileComp in[2], out[2];
 };
 
-__device__ __forceinline__ TileOp tile_op(int type, int fa, int fc, int p)
+__host__ __device__ __forceinline__ TileOp tile_op(int type, int fa, int fc, int p)
 {
     const int nh = p * (p + 1);
     const TileComp c0{TK_NODE, TK_NODE, 0}, c2{TK_EDGE, TK_EDGE, 0}, ch{TK_NODE, TK_EDGE, 0}, cv{TK_EDGE, TK_NODE, nh};
@@ -843,7 +848,7 @@ template <int Q> static int launch_tile_q(mfv2d_ctx *ctx, ApplyTArgs &ta, size_t
     const size_t slot_bytes = (size_t)ta.slot_doubles * 8;
     const size_t budget = ((size_t)228 * 1024 - 2048) / 2;
     int epb = (int)((budget > fixed_bytes ? budget - fixed_bytes : 0) / slot_bytes);
-    const int want = (APPLYT_THREADS + Q - 1) / Q;
+    const int want = APPLYT_THREADS / Q; // phase B: one thread per (element, quadrature column), one round
     if (epb > want)
         epb = want;
     if (epb < 1)
@@ -862,6 +867,770 @@ template <int Q> static int launch_tile_q(mfv2d_ctx *ctx, ApplyTArgs &ta, size_t
     if (grid > need)
         grid = need;
     MFV2D_LAUNCH(element_vector_tile_kernel<Q>, (unsigned)grid, APPLYT_THREADS, smem, ctx->stream, ta);
+    ctx->launches++;
+    MFV2D_CUDA_CHECK(ctx, cudaGetLastError());
+    return MFV2D_SUCCESS;
+}
+
+// =====================================================================================================
+// Fused matrix-free apply.  When every term of a vector program has the shape  coef * [E_L] * D * [E_R]
+// (D a mass or an interior-product matrix, at most one incidence on each side - all the reference's example
+// systems do), the terms do not depend on each other and are evaluated TOGETHER in five barrier-separated
+// phases per pass of `epb` elements instead of one chain after the other:
+//   pre   right incidences: signed gathers of x into the terms' input vectors
+//   A     thread (e, row pair):      t[i][:] = sum_j c[i, j] B_j[:]                (interpolate along xi)
+//   B     thread (e, b):             for every term (pair): interpolate along eta, metric (one division per
+//                                    point and pair), project along eta - the values at the points stay in registers
+//   C     thread (e, row pair):      out[i, j] = B'_j[:] . t'[i][:]                (project along xi)
+//   post  thread (e, k):             y[k] = sum_terms coef * (out[k] | left incidence of out), stored to HBM
+// The kernel is bound by shared-memory wavefronts (one 16-byte table read feeds two DFMAs), so rows that use the
+// same 1-D table are processed two at a time in A / C and terms of the same kind two at a time in B: every table
+// read then feeds four DFMAs, and the metric of a pair is computed once.  x and the corners of the next pass
+// are prefetched into registers under phases C / post.  All descriptors are resolved on the host
+// (plan_lower_vector_fused) into one int blob staged in shared memory.
+// =====================================================================================================
+static int inc_rows_of(int kind, int p)
+{
+    const int nh = p * (p + 1);
+    return (kind == MFV2D_INC_10 || kind == MFV2D_INC_21_T) ? 2 * nh : (kind == MFV2D_INC_21 ? p * p : (p + 1) * (p + 1));
+}
+
+struct FusedRow // one 1-D contraction row of phase A (src = coefficients, dst = t row) or C (src = dst = t row)
+{
+    int src, nB, kB, dst;
+    int g; // phase A: -1, or first row of the right incidence whose signed gathers of x (at src) are the coefficients
+};
+
+// rows with the same table (kB) two at a time; 8 ints per entry: src0, nB, kB, dst0, src1 (-1: single), dst1, g0, g1
+static void pair_rows(std::vector<FusedRow> rows, std::vector<int32_t> &out)
+{
+    std::stable_sort(rows.begin(), rows.end(), [](const FusedRow &a, const FusedRow &b) { return a.kB < b.kB; });
+    std::vector<int32_t> singles;
+    for (size_t i = 0; i < rows.size();)
+    {
+        if (i + 1 < rows.size() && rows[i + 1].kB == rows[i].kB)
+        {
+            out.insert(out.end(), {rows[i].src, rows[i].nB, rows[i].kB, rows[i].dst, rows[i + 1].src, rows[i + 1].dst, rows[i].g, rows[i + 1].g});
+            i += 2;
+        }
+        else
+        {
+            singles.insert(singles.end(), {rows[i].src, rows[i].nB, rows[i].kB, rows[i].dst, -1, -1, rows[i].g, -1});
+            i += 1;
+        }
+    }
+    out.insert(out.end(), singles.begin(), singles.end());
+}
+
+static int plan_lower_vector_fused(mfv2d_plan *plan)
+{
+    plan->vector_fused = false;
+    const int p = plan->p, q = plan->q, np1 = p + 1, nf = plan->n_forms, N = plan->n_total;
+    if (plan->vector_needs_dense || q < 2 || q > 16)
+        return MFV2D_SUCCESS;
+    const int ldt = asm_ldq(q); // t rows: 16-byte row accesses of consecutive rows fall into distinct bank groups
+    auto ksize = [&](int k) { return k == TK_NODE ? np1 : p; };
+    struct FT
+    {
+        int rf, cf, ci, L, R;
+        TileOp op;
+        int fld, dk, tr;
+    };
+    std::vector<FT> fts;
+    int ci = 0;
+    for (int r = 0; r < nf; ++r)
+        for (int c = 0; c < nf; ++c)
+        {
+            const BlockProgram &bp = plan->vec_blocks[r * nf + c];
+            if (!bp.present)
+                continue;
+            if (bp.identity)
+                return MFV2D_SUCCESS; // not a tensor term: the term-by-term kernel handles it
+            for (const Term &t : bp.terms)
+            {
+                FT ft{r, c, ci++, -1, -1, TileOp{}, 0, 0, 0};
+                int dense_at = -1;
+                for (size_t i = 0; i < t.f.size(); ++i)
+                    if (t.f[i].is_dense)
+                    {
+                        if (dense_at >= 0)
+                            return MFV2D_SUCCESS;
+                        dense_at = (int)i;
+                    }
+                if (dense_at < 0 || dense_at > 1 || (int)t.f.size() - dense_at > 2)
+                    return MFV2D_SUCCESS;
+                const Factor &d = t.f[dense_at];
+                if (d.inverse)
+                    return MFV2D_SUCCESS;
+                if (dense_at == 1)
+                    ft.R = t.f[0].inc_kind;
+                if ((int)t.f.size() == dense_at + 2)
+                    ft.L = t.f[dense_at + 1].inc_kind;
+                ft.op = tile_op(d.dk <= DK_MASS2 ? 1 : 2, d.dk, d.transpose, p);
+                ft.fld = d.dk <= DK_MASS2 ? 0 : d.field;
+                ft.dk = d.dk;
+                ft.tr = d.dk <= DK_MASS2 ? 0 : d.transpose;
+                fts.push_back(ft);
+            }
+        }
+    if (fts.empty() || fts.size() > 64)
+        return MFV2D_SUCCESS;
+
+    // slot layout: corners[2][8] (double buffered) | x[N] | t rows of all terms.  The results of phase C overwrite
+    // the head of their own t row, so neither the inputs after a right incidence nor the outputs need vectors
+    std::vector<int> t_off(fts.size()), n_in(fts.size()), n_out(fts.size());
+    int t_total = 0;
+    for (size_t i = 0; i < fts.size(); ++i)
+    {
+        const TileOp &op = fts[i].op;
+        int ni = 0, no = 0, ri = 0, ro = 0;
+        for (int k = 0; k < op.n_in; ++k)
+        {
+            ni += ksize(op.in[k].kA) * ksize(op.in[k].kB);
+            ri += ksize(op.in[k].kA);
+        }
+        for (int k = 0; k < op.n_out; ++k)
+        {
+            no += ksize(op.out[k].kA) * ksize(op.out[k].kB);
+            ro += ksize(op.out[k].kA);
+        }
+        n_in[i] = ni;
+        n_out[i] = no;
+        const int c0 = plan->form_offsets[fts[i].cf];
+        if (fts[i].R >= 0 ? inc_rows_of(fts[i].R, p) != ni : plan->form_offsets[fts[i].cf + 1] - c0 != ni)
+            return MFV2D_SUCCESS;
+        t_off[i] = t_total;
+        t_total += (ri > ro ? ri : ro) * ldt;
+    }
+    FusedVecInfo fv{};
+    fv.n_terms = (int)fts.size();
+    fv.off_vec = 16;
+    fv.off_t = fv.off_vec + ((N + 1) & ~1);
+    fv.slot_doubles = fv.off_t + t_total;
+    // thread (e, b) of phase B reads slot[e][... + b]: with the slot stride congruent to q modulo 16 doubles the
+    // addresses of a warp are congruent to the thread index, i.e. conflict free (even stride keeps 16-byte alignment)
+    while ((fv.slot_doubles & 15) != ((q + (q & 1)) & 15))
+        ++fv.slot_doubles;
+
+    std::vector<int32_t> rowA, termB, rowC, yrow((size_t)2 * N, 0), contrib;
+    std::vector<FusedRow> rowsA, rowsC;
+    std::vector<std::vector<std::array<int32_t, 8>>> per_row(N);
+    const int x_base = fv.off_vec, t_base = fv.off_t;
+    for (size_t i = 0; i < fts.size(); ++i)
+    {
+        const FT &ft = fts[i];
+        const TileOp &op = ft.op;
+        const int c0 = plan->form_offsets[ft.cf], r0 = plan->form_offsets[ft.rf];
+        int row = 0;
+        for (int k = 0; k < op.n_in; ++k)
+        {
+            const int nA = ksize(op.in[k].kA), nB = ksize(op.in[k].kB);
+            for (int a = 0; a < nA; ++a, ++row)
+            {
+                const int first = op.in[k].off + a * nB; // index of the row's first coefficient in the term's input vector
+                if (ft.R >= 0)
+                    rowsA.push_back({x_base + c0, nB, op.in[k].kB, t_base + t_off[i] + row * ldt, plan->basis->inc_off[ft.R] + first});
+                else
+                    rowsA.push_back({x_base + c0 + first, nB, op.in[k].kB, t_base + t_off[i] + row * ldt, -1});
+            }
+        }
+        // address (+1) of entry m of the term's output vector: head of the t row of its (component, row)
+        std::vector<int> out_addr(n_out[i]);
+        row = 0;
+        for (int k = 0; k < op.n_out; ++k)
+        {
+            const int nA = ksize(op.out[k].kA), nB = ksize(op.out[k].kB);
+            for (int a = 0; a < nA; ++a, ++row)
+            {
+                const int tr = t_base + t_off[i] + row * ldt;
+                rowsC.push_back({tr, nB, op.out[k].kB, tr, -1});
+                for (int j = 0; j < nB; ++j)
+                    out_addr[op.out[k].off + a * nB + j] = tr + j + 1;
+            }
+        }
+        const int n_rows_form = plan->form_offsets[ft.rf + 1] - r0;
+        if (ft.L >= 0)
+        {
+            if (inc_rows_of(ft.L, p) != n_rows_form)
+                return MFV2D_SUCCESS;
+            const int32_t *map = plan->basis->h_inc.data() + 4 * (size_t)plan->basis->inc_off[ft.L];
+            for (int k = 0; k < n_rows_form; ++k)
+            {
+                std::array<int32_t, 8> c{ft.ci, 0, 0, 0, 0, 0, 0, 0};
+                for (int z = 0; z < 4; ++z)
+                {
+                    const int32_t ev = map[4 * k + z];
+                    if (ev == 0)
+                        break;
+                    const int a = out_addr[(ev < 0 ? -ev : ev) - 1];
+                    c[1 + z] = ev < 0 ? -a : a;
+                }
+                per_row[r0 + k].push_back(c);
+            }
+        }
+        else
+        {
+            if (n_out[i] != n_rows_form)
+                return MFV2D_SUCCESS;
+            for (int k = 0; k < n_rows_form; ++k)
+                per_row[r0 + k].push_back({ft.ci, out_addr[k], 0, 0, 0, 0, 0, 0});
+        }
+    }
+    // phase B: terms with the same dense factor (kind, field, transposition) two at a time
+    {
+        std::vector<char> used(fts.size(), 0);
+        for (size_t i = 0; i < fts.size(); ++i)
+        {
+            if (used[i])
+                continue;
+            used[i] = 1;
+            int partner = -1;
+            for (size_t j = i + 1; j < fts.size(); ++j)
+                if (!used[j] && fts[j].dk == fts[i].dk && fts[j].fld == fts[i].fld && fts[j].tr == fts[i].tr)
+                {
+                    partner = (int)j;
+                    used[j] = 1;
+                    break;
+                }
+            const TileOp &op = fts[i].op;
+            termB.insert(termB.end(), {op.mode, fts[i].fld, t_base + t_off[i], ksize(op.in[0].kA), op.in[0].kA,
+                                       op.n_in > 1 ? ksize(op.in[1].kA) : 0, op.in[1].kA, ksize(op.out[0].kA), op.out[0].kA,
+                                       op.n_out > 1 ? ksize(op.out[1].kA) : 0, op.out[1].kA,
+                                       partner >= 0 ? t_base + t_off[partner] : -1});
+        }
+        fv.n_terms = (int)termB.size() / 12; // term groups
+    }
+    pair_rows(rowsA, rowA);
+    pair_rows(rowsC, rowC);
+    for (int k = 0; k < N; ++k)
+    {
+        yrow[2 * k] = (int32_t)(contrib.size() / 8);
+        yrow[2 * k + 1] = (int32_t)per_row[k].size();
+        for (const auto &c : per_row[k])
+            contrib.insert(contrib.end(), c.begin(), c.end());
+    }
+    fv.n_pre = 0;
+    fv.n_rowA = (int)rowA.size() / 8;
+    fv.n_rowC = (int)rowC.size() / 8;
+    fv.n_contrib = (int)contrib.size() / 8;
+    std::vector<int32_t> &blob = plan->fblob;
+    blob.clear();
+    auto put = [&](const std::vector<int32_t> &v) {
+        while (blob.size() & 3)
+            blob.push_back(0);
+        const int off = (int)blob.size();
+        blob.insert(blob.end(), v.begin(), v.end());
+        return off;
+    };
+    fv.off_pre = 0;
+    fv.off_rowA = put(rowA);
+    fv.off_termB = put(termB);
+    fv.off_rowC = put(rowC);
+    fv.off_yrow = put(yrow);
+    fv.off_contrib = put(contrib);
+    while (blob.size() & 3)
+        blob.push_back(0);
+    fv.blob_ints = (int)blob.size();
+    MFV2D_TRY(mfv2d_cuda_malloc(plan->ctx, blob.size() * sizeof(int32_t), (void **)&plan->d_fblob));
+    MFV2D_TRY(mfv2d_cuda_upload(plan->ctx, plan->d_fblob, blob.data(), blob.size() * sizeof(int32_t)));
+    plan->fv = fv;
+    plan->vector_fused = true;
+    if (getenv("MFV2D_PLAN_DEBUG"))
+        fprintf(stderr, "[mfv2d] fused vector plan: p %d q %d, %d term groups, %d pre, %d + %d row pairs, slot %d doubles, blob %d ints\n",
+                p, q, fv.n_terms, fv.n_pre, fv.n_rowA, fv.n_rowC, fv.slot_doubles, fv.blob_ints);
+    return MFV2D_SUCCESS;
+}
+
+struct FusedArgs
+{
+    ApplyArgs a;
+    FusedVecInfo fv;
+    const int32_t *blob;
+    int n_coef, inc_rows;
+    int epb; // elements per pass
+};
+
+__device__ __forceinline__ double signed_gather(const int4 m, const double *__restrict__ src)
+{
+    const int ev[4] = {m.x, m.y, m.z, m.w};
+    double acc = 0.0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+    {
+        if (ev[k] == 0)
+            break;
+        const double v = src[abs(ev[k]) - 1];
+        acc += ev[k] < 0 ? -v : v;
+    }
+    return acc;
+}
+
+// acc[n][:] += c[n] * row[:] for NT accumulator rows: one 16-byte table read feeds 2 NT DFMAs
+template <int Q, int NT> __device__ __forceinline__ void row_axpy_n(double (&acc)[NT][Q], const double (&c)[NT], const double *__restrict__ row)
+{
+#pragma unroll
+    for (int b = 0; b + 1 < Q; b += 2)
+    {
+        const double2 v = *reinterpret_cast<const double2 *>(row + b);
+#pragma unroll
+        for (int n = 0; n < NT; ++n)
+        {
+            acc[n][b] = fma(c[n], v.x, acc[n][b]);
+            acc[n][b + 1] = fma(c[n], v.y, acc[n][b + 1]);
+        }
+    }
+    if (Q & 1)
+    {
+        const double v = row[Q - 1];
+#pragma unroll
+        for (int n = 0; n < NT; ++n)
+            acc[n][Q - 1] = fma(c[n], v, acc[n][Q - 1]);
+    }
+}
+
+// acc[n][:] = c[n] * row[:]
+template <int Q, int NT> __device__ __forceinline__ void row_mul_n(double (&acc)[NT][Q], const double (&c)[NT], const double *__restrict__ row)
+{
+#pragma unroll
+    for (int b = 0; b + 1 < Q; b += 2)
+    {
+        const double2 v = *reinterpret_cast<const double2 *>(row + b);
+#pragma unroll
+        for (int n = 0; n < NT; ++n)
+        {
+            acc[n][b] = c[n] * v.x;
+            acc[n][b + 1] = c[n] * v.y;
+        }
+    }
+    if (Q & 1)
+    {
+        const double v = row[Q - 1];
+#pragma unroll
+        for (int n = 0; n < NT; ++n)
+            acc[n][Q - 1] = c[n] * v;
+    }
+}
+
+// res[n] = row[:] . g[n][:]
+template <int Q, int NT> __device__ __forceinline__ void row_dot_n(const double *__restrict__ row, const double (&g)[NT][Q], double (&res)[NT])
+{
+    double a0[NT], a1[NT];
+#pragma unroll
+    for (int n = 0; n < NT; ++n)
+        a0[n] = a1[n] = 0.0;
+#pragma unroll
+    for (int b = 0; b + 1 < Q; b += 2)
+    {
+        const double2 v = *reinterpret_cast<const double2 *>(row + b);
+#pragma unroll
+        for (int n = 0; n < NT; ++n)
+        {
+            a0[n] = fma(v.x, g[n][b], a0[n]);
+            a1[n] = fma(v.y, g[n][b + 1], a1[n]);
+        }
+    }
+    if (Q & 1)
+    {
+        const double v = row[Q - 1];
+#pragma unroll
+        for (int n = 0; n < NT; ++n)
+            a0[n] = fma(v, g[n][Q - 1], a0[n]);
+    }
+#pragma unroll
+    for (int n = 0; n < NT; ++n)
+        res[n] = a0[n] + a1[n];
+}
+
+// coefficient j of a phase-A row: read in place, or gathered from x through the right incidence
+__device__ __forceinline__ double fused_coef(const double *__restrict__ c, int g, int j, const int4 *__restrict__ inc)
+{
+    return g < 0 ? c[j] : signed_gather(inc[g + j], c);
+}
+
+template <int Q, int NT>
+__device__ __forceinline__ void fused_rows_a(const int4 d0, const int4 d1, double *__restrict__ slot, const double *__restrict__ smem, int edge_off,
+                                             const int4 *__restrict__ inc)
+{
+    constexpr int LDQ = (Q + 1) & ~1;
+    const double *c0 = slot + d0.x, *c1 = slot + (NT > 1 ? d1.x : d0.x);
+    const double *B = smem + d0.z * edge_off;
+    double acc[NT][Q];
+    {
+        // first coefficient: plain products instead of zero + fma
+        double c[NT];
+        c[0] = fused_coef(c0, d1.z, 0, inc);
+        if (NT > 1)
+            c[NT - 1] = fused_coef(c1, d1.w, 0, inc);
+        row_mul_n<Q, NT>(acc, c, B);
+    }
+    for (int j = 1; j < d0.y; ++j)
+    {
+        double c[NT];
+        c[0] = fused_coef(c0, d1.z, j, inc);
+        if (NT > 1)
+            c[NT - 1] = fused_coef(c1, d1.w, j, inc);
+        row_axpy_n<Q, NT>(acc, c, B + j * LDQ);
+    }
+#pragma unroll
+    for (int n = 0; n < NT; ++n)
+    {
+        double *dst = slot + (n == 0 ? d0.w : d1.y);
+#pragma unroll
+        for (int b = 0; b + 1 < Q; b += 2)
+            *reinterpret_cast<double2 *>(dst + b) = make_double2(acc[n][b], acc[n][b + 1]);
+        if (Q & 1)
+            dst[Q - 1] = acc[n][Q - 1];
+    }
+}
+
+// phase C: the nB results of a row overwrite the head of the row itself (it has been read into registers)
+template <int Q, int NT>
+__device__ __forceinline__ void fused_rows_c(const int4 d0, const int4 d1, double *__restrict__ slot, const double *__restrict__ smem, int edge_off)
+{
+    constexpr int LDQ = (Q + 1) & ~1;
+    double tr[NT][Q];
+#pragma unroll
+    for (int n = 0; n < NT; ++n)
+    {
+        const double *src = slot + (n == 0 ? d0.x : d1.x);
+#pragma unroll
+        for (int b = 0; b + 1 < Q; b += 2)
+        {
+            const double2 v = *reinterpret_cast<const double2 *>(src + b);
+            tr[n][b] = v.x;
+            tr[n][b + 1] = v.y;
+        }
+        if (Q & 1)
+            tr[n][Q - 1] = src[Q - 1];
+    }
+    const double *B = smem + d0.z * edge_off;
+    double *dst0 = slot + d0.x, *dst1 = slot + (NT > 1 ? d1.x : d0.x);
+    for (int j = 0; j < d0.y; ++j)
+    {
+        double res[NT];
+        row_dot_n<Q, NT>(B + j * LDQ, tr, res);
+        dst0[j] = res[0];
+        if (NT > 1)
+            dst1[j] = res[NT - 1];
+    }
+}
+
+// geometry of one quadrature column (fixed xi): what the metric at its Q points is computed from
+struct ColumnGeo
+{
+    double j10, j11, dx10, dx23, dy10, dy23, wb;
+};
+
+// one term (NT = 1) or two terms of the same kind (NT = 2) on the quadrature column b of one element
+template <int Q, int NT>
+__device__ __forceinline__ void fused_terms_b(const int *__restrict__ tb, double *__restrict__ slot, int b, const double *__restrict__ smem,
+                                              int edge_off, const double *__restrict__ pnts, const double *__restrict__ wgts,
+                                              const ColumnGeo &g, const double *__restrict__ fp)
+{
+    constexpr int LDQ = (Q + 1) & ~1;
+    const int LDT = asm_ldq(Q);
+    const int mode = tb[0];
+    double *tc[NT];
+    tc[0] = slot + tb[2] + b;
+    if (NT > 1)
+        tc[NT - 1] = slot + tb[11] + b;
+    const int nA0 = tb[3], nA1 = tb[5], nO0 = tb[7], nO1 = tb[9];
+    double u0[NT][Q], u1[NT][Q];
+#pragma unroll
+    for (int n = 0; n < NT; ++n)
+#pragma unroll
+        for (int a = 0; a < Q; ++a)
+            u0[n][a] = u1[n][a] = 0.0;
+    {
+        const double *A = smem + tb[4] * edge_off;
+        for (int i = 0; i < nA0; ++i)
+        {
+            double c[NT];
+#pragma unroll
+            for (int n = 0; n < NT; ++n)
+                c[n] = tc[n][i * LDT];
+            row_axpy_n<Q, NT>(u0, c, A + i * LDQ);
+        }
+        const double *A1 = smem + tb[6] * edge_off;
+        for (int i = 0; i < nA1; ++i)
+        {
+            double c[NT];
+#pragma unroll
+            for (int n = 0; n < NT; ++n)
+                c[n] = tc[n][(nA0 + i) * LDT];
+            row_axpy_n<Q, NT>(u1, c, A1 + i * LDQ);
+        }
+    }
+    {
+#pragma unroll
+        for (int a = 0; a < Q; ++a)
+        {
+            const double eta = pnts[a];
+            const double j00 = 0.25 * (g.dx10 * (1 - eta) + g.dx23 * (1 + eta));
+            const double j01 = 0.25 * (g.dy10 * (1 - eta) + g.dy23 * (1 + eta));
+            const double det = j00 * g.j11 - g.j10 * j01;
+            if (mode == 0)
+            {
+                const double k = det * (wgts[a] * g.wb);
+#pragma unroll
+                for (int n = 0; n < NT; ++n)
+                    u0[n][a] = u0[n][a] * k;
+                continue;
+            }
+            const double wod = wgts[a] * g.wb * fast_rcp(det); // one reciprocal per point and term group
+            if (mode == 1)
+            {
+#pragma unroll
+                for (int n = 0; n < NT; ++n)
+                    u0[n][a] = u0[n][a] * wod;
+            }
+            else if (mode == 2)
+            {
+                const double khh = (g.j11 * g.j11 + g.j10 * g.j10) * wod, kvv = (j00 * j00 + j01 * j01) * wod,
+                             khv = (j01 * g.j11 + j00 * g.j10) * wod;
+#pragma unroll
+                for (int n = 0; n < NT; ++n)
+                {
+                    const double a0 = u0[n][a], a1 = u1[n][a];
+                    u0[n][a] = khh * a0 + khv * a1;
+                    u1[n][a] = khv * a0 + kvv * a1;
+                }
+            }
+            else
+            {
+                const double fx = fp[2 * a * Q], fy = fp[2 * a * Q + 1];
+                double kh, kv;
+                if (mode <= 4)
+                {
+                    const double w = wgts[a] * g.wb;
+                    kh = (fx * g.j11 - fy * g.j10) * w;
+                    kv = -(fy * j00 - fx * j01) * w;
+                }
+                else
+                {
+                    kh = -(fx * g.j10 + fy * g.j11) * wod;
+                    kv = -(fx * j00 + fy * j01) * wod;
+                }
+#pragma unroll
+                for (int n = 0; n < NT; ++n)
+                {
+                    const double a0 = u0[n][a], a1 = u1[n][a];
+                    if (mode == 3 || mode == 6)
+                        u0[n][a] = kh * a0 + kv * a1;
+                    else
+                    {
+                        u0[n][a] = kh * a0;
+                        u1[n][a] = kv * a0;
+                    }
+                }
+            }
+        }
+    }
+    {
+        const double *A = smem + tb[8] * edge_off;
+        for (int i = 0; i < nO0; ++i)
+        {
+            double res[NT];
+            row_dot_n<Q, NT>(A + i * LDQ, u0, res);
+#pragma unroll
+            for (int n = 0; n < NT; ++n)
+                tc[n][i * LDT] = res[n];
+        }
+        const double *A1 = smem + tb[10] * edge_off;
+        for (int i = 0; i < nO1; ++i)
+        {
+            double res[NT];
+            row_dot_n<Q, NT>(A1 + i * LDQ, u1, res);
+#pragma unroll
+            for (int n = 0; n < NT; ++n)
+                tc[n][(nO0 + i) * LDT] = res[n];
+        }
+    }
+}
+
+template <int Q> __global__ void __launch_bounds__(APPLYT_THREADS, 2) element_vector_fused_kernel(const FusedArgs fa)
+{
+    MFV2D_DYN_SMEM(double, smem);
+    constexpr int LDQ = (Q + 1) & ~1;
+    const ApplyArgs &args = fa.a;
+    const FusedVecInfo &fv = fa.fv;
+    const int p = args.p, np1 = p + 1, N = args.n_total;
+    // CTA-shared: padded tables | points, weights | coefficients | descriptor blob | incidence maps | element slots
+    const int edge_off = np1 * LDQ;
+    double *pnts = smem + (2 * p + 1) * LDQ, *wgts = pnts + LDQ;
+    double *coef = wgts + LDQ;
+    int *blob = reinterpret_cast<int *>(coef + ((fa.n_coef + 1) & ~1));
+    int4 *inc = reinterpret_cast<int4 *>(blob + fv.blob_ints);
+    double *slots = reinterpret_cast<double *>(inc + fa.inc_rows);
+    const int epb = fa.epb, SD = fv.slot_doubles;
+    const int off_xs = fv.off_vec;
+    const unsigned long long n_groups = (args.n_elem + epb - 1) / epb;
+    const float inv_n = 1.0f / (float)N;
+
+    // x of a pass and its corners are copied global -> shared asynchronously (no registers in flight): issued
+    // right after phase A of the previous pass (x is dead from there on; the corners are double buffered)
+    auto prefetch = [&](unsigned long long grp, int parity) {
+        if (grp >= n_groups)
+            return;
+        const unsigned long long elem0 = grp * epb;
+        const int nv = (int)((args.n_elem - elem0) < (unsigned long long)epb ? (args.n_elem - elem0) : epb);
+        for (int i = threadIdx.x; i < nv * 8; i += blockDim.x)
+            cp_async8(slots + (i >> 3) * SD + parity * 8 + (i & 7), args.corners + elem0 * 8 + i);
+        for (int i = threadIdx.x; i < nv * N; i += blockDim.x)
+        {
+            const int e = (int)(((float)i + 0.5f) * inv_n);
+            cp_async8(slots + e * SD + off_xs + (i - e * N), args.x + elem0 * N + i);
+        }
+    };
+    prefetch(blockIdx.x, 0);
+
+    for (int i = threadIdx.x; i < (2 * p + 1) * LDQ; i += blockDim.x)
+    {
+        const int r = i / LDQ, b = i - r * LDQ;
+        smem[i] = b < Q ? args.tab[r * Q + b] : 0.0; // tab = node (p+1) x q | edge p x q | pnts | wgts
+    }
+    for (int i = threadIdx.x; i < Q; i += blockDim.x)
+    {
+        pnts[i] = args.tab[(2 * p + 1) * Q + i];
+        wgts[i] = args.tab[(2 * p + 2) * Q + i];
+    }
+    for (int i = threadIdx.x; i < fa.n_coef; i += blockDim.x)
+        coef[i] = args.coef[i];
+    for (int i = threadIdx.x; i < fv.blob_ints; i += blockDim.x)
+        blob[i] = fa.blob[i];
+    for (int i = threadIdx.x; i < fa.inc_rows; i += blockDim.x)
+        inc[i] = reinterpret_cast<const int4 *>(args.inc)[i];
+    const int4 *rowA = reinterpret_cast<const int4 *>(blob + fv.off_rowA);
+    const int *termB = blob + fv.off_termB;
+    const int4 *rowC = reinterpret_cast<const int4 *>(blob + fv.off_rowC);
+    const int2 *yrow = reinterpret_cast<const int2 *>(blob + fv.off_yrow);
+    const int4 *contrib = reinterpret_cast<const int4 *>(blob + fv.off_contrib);
+
+    int parity = 0;
+    for (unsigned long long grp = blockIdx.x; grp < n_groups; grp += gridDim.x, parity ^= 1)
+    {
+        const unsigned long long elem0 = grp * epb;
+        const int nv = (int)((args.n_elem - elem0) < (unsigned long long)epb ? (args.n_elem - elem0) : epb);
+        cp_async_wait_all();
+        __syncthreads(); // x / corners of this pass have landed; the previous pass is done with the t rows
+        // ---- phase A: t[row][:] = sum_j c[j] B_j[:], rows of the same table two at a time ----
+        {
+            const int R = fv.n_rowA;
+            const float inv_R = 1.0f / (float)R;
+            for (int idx = threadIdx.x; idx < nv * R; idx += blockDim.x)
+            {
+                const int e = (int)(((float)idx + 0.5f) * inv_R), row = idx - e * R;
+                double *slot = slots + e * SD;
+                const int4 d0 = rowA[2 * row], d1 = rowA[2 * row + 1];
+                if (d1.x >= 0)
+                    fused_rows_a<Q, 2>(d0, d1, slot, smem, edge_off, inc);
+                else
+                    fused_rows_a<Q, 1>(d0, d1, slot, smem, edge_off, inc);
+            }
+        }
+        __syncthreads();
+        prefetch(grp + gridDim.x, parity ^ 1);
+        // ---- phase B: thread (e, b) owns the quadrature column b of element e for all terms ----
+        for (int idx = threadIdx.x; idx < nv * Q; idx += blockDim.x)
+        {
+            const int e = idx / Q, b = idx - e * Q;
+            double *slot = slots + e * SD;
+            const double *cs = slot + parity * 8;
+            const double x0 = cs[0], y0 = cs[1], x1 = cs[2], y1 = cs[3], x2 = cs[4], y2 = cs[5], x3 = cs[6], y3 = cs[7];
+            const double xi = pnts[b];
+            ColumnGeo g;
+            g.wb = wgts[b];
+            g.j10 = 0.25 * ((x3 - x0) * (1 - xi) + (x2 - x1) * (1 + xi));
+            g.j11 = 0.25 * ((y3 - y0) * (1 - xi) + (y2 - y1) * (1 + xi));
+            g.dx10 = x1 - x0;
+            g.dx23 = x2 - x3;
+            g.dy10 = y1 - y0;
+            g.dy23 = y2 - y3;
+            for (int t = 0; t < fv.n_terms; ++t)
+            {
+                const int *tb = termB + 12 * t;
+                const double *fp = tb[0] >= 3 ? args.fields[tb[1]] + (elem0 + e) * (unsigned long long)(2 * Q * Q) + 2 * b : nullptr;
+                if (tb[11] >= 0)
+                    fused_terms_b<Q, 2>(tb, slot, b, smem, edge_off, pnts, wgts, g, fp);
+                else
+                    fused_terms_b<Q, 1>(tb, slot, b, smem, edge_off, pnts, wgts, g, fp);
+            }
+        }
+        __syncthreads();
+        // ---- phase C: out[i, j] = B_j[:] . t'[row][:], rows of the same table two at a time ----
+        {
+            const int R = fv.n_rowC;
+            const float inv_R = 1.0f / (float)R;
+            for (int idx = threadIdx.x; idx < nv * R; idx += blockDim.x)
+            {
+                const int e = (int)(((float)idx + 0.5f) * inv_R), row = idx - e * R;
+                double *slot = slots + e * SD;
+                const int4 d0 = rowC[2 * row], d1 = rowC[2 * row + 1];
+                if (d1.x >= 0)
+                    fused_rows_c<Q, 2>(d0, d1, slot, smem, edge_off);
+                else
+                    fused_rows_c<Q, 1>(d0, d1, slot, smem, edge_off);
+            }
+        }
+        __syncthreads();
+        // ---- post: y[k] = sum over the terms of coef * (signed sum of up to four outputs), stored to HBM ----
+        for (int i = threadIdx.x; i < nv * N; i += blockDim.x)
+        {
+            const int e = (int)(((float)i + 0.5f) * inv_n), k = i - e * N;
+            const double *slot = slots + e * SD - 1; // the addresses carry +1 so that their sign can be the sign of the entry
+            const int2 yr = yrow[k];
+            double acc = 0.0;
+            for (int c = yr.x; c < yr.x + yr.y; ++c)
+            {
+                const int4 c0 = contrib[2 * c];
+                double v = c0.y < 0 ? -slot[-c0.y] : slot[c0.y];
+                if (c0.z != 0)
+                {
+                    const int c1x = contrib[2 * c + 1].x;
+                    const double v1 = slot[abs(c0.z)];
+                    v += c0.z < 0 ? -v1 : v1;
+                    if (c0.w != 0)
+                    {
+                        const double v2 = slot[abs(c0.w)];
+                        v += c0.w < 0 ? -v2 : v2;
+                        if (c1x != 0)
+                        {
+                            const double v3 = slot[abs(c1x)];
+                            v += c1x < 0 ? -v3 : v3;
+                        }
+                    }
+                }
+                acc = fma(coef[c0.x], v, acc);
+            }
+            args.y[elem0 * N + i] = acc;
+        }
+    }
+}
+
+template <int Q> static int launch_fused_q(mfv2d_ctx *ctx, FusedArgs &fa, size_t fixed_bytes, size_t n_elem)
+{
+    const size_t slot_bytes = (size_t)fa.fv.slot_doubles * 8;
+    const size_t budget = ((size_t)228 * 1024 - 2048) / 2; // two CTAs per SM
+    int epb = (int)((budget > fixed_bytes ? budget - fixed_bytes : 0) / slot_bytes);
+    const int want = APPLYT_THREADS / Q; // phase B: one thread per (element, quadrature column), one round
+    if (epb > want)
+        epb = want;
+    if (epb < 1)
+        epb = 1;
+    fa.epb = epb;
+    const size_t smem = fixed_bytes + (size_t)epb * slot_bytes;
+    if (smem > ctx->smem_optin)
+        return -1; // the caller falls back to the term-by-term kernel
+    MFV2D_CUDA_CHECK(ctx, cudaFuncSetAttribute(element_vector_fused_kernel<Q>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int per_sm = 1;
+    MFV2D_CUDA_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, element_vector_fused_kernel<Q>, APPLYT_THREADS, smem));
+    if (per_sm < 1)
+        per_sm = 1;
+    unsigned long long grid = (unsigned long long)ctx->sm_count * per_sm;
+    const unsigned long long need = (n_elem + epb - 1) / epb;
+    if (grid > need)
+        grid = need;
+    MFV2D_LAUNCH(element_vector_fused_kernel<Q>, (unsigned)grid, APPLYT_THREADS, smem, ctx->stream, fa);
     ctx->launches++;
     MFV2D_CUDA_CHECK(ctx, cudaGetLastError());
     return MFV2D_SUCCESS;
@@ -902,6 +1671,46 @@ static int launch_apply(const mfv2d_plan *plan, const mfv2d_elements *e, const d
         const int ldT = (np1 * np1 + 3) & ~3;
         const int nmax = 2 * p * np1;
         doubles += ((q2 + 1) & ~1) + q * ldT + 4 + (size_t)nmax * nmax + 8;
+    }
+    if (!column_mode && plan->vector_fused && e->n > 0)
+    {
+        FusedArgs fa{};
+        fa.a = a;
+        fa.fv = plan->fv;
+        fa.blob = plan->d_fblob;
+        fa.n_coef = plan->mcoef_off ? plan->mcoef_off : (int)plan->vcoef.size();
+        fa.inc_rows = plan->basis->inc_off[4];
+        const int ldq = (q + 1) & ~1;
+        const size_t fixed_bytes = ((size_t)(2 * p + 1) * ldq + 2 * ldq + (((size_t)fa.n_coef + 1) & ~(size_t)1)) * 8 +
+                                   (size_t)fa.fv.blob_ints * 4 + (size_t)fa.inc_rows * 16;
+        int r = -1;
+        switch (q)
+        {
+#define MFV2D_Q_CASE(Q)                                                                                        \
+    case Q:                                                                                                    \
+        r = launch_fused_q<Q>(ctx, fa, fixed_bytes, e->n);                                                     \
+        break;
+            MFV2D_Q_CASE(2)
+            MFV2D_Q_CASE(3)
+            MFV2D_Q_CASE(4)
+            MFV2D_Q_CASE(5)
+            MFV2D_Q_CASE(6)
+            MFV2D_Q_CASE(7)
+            MFV2D_Q_CASE(8)
+            MFV2D_Q_CASE(9)
+            MFV2D_Q_CASE(10)
+            MFV2D_Q_CASE(11)
+            MFV2D_Q_CASE(12)
+            MFV2D_Q_CASE(13)
+            MFV2D_Q_CASE(14)
+            MFV2D_Q_CASE(15)
+            MFV2D_Q_CASE(16)
+#undef MFV2D_Q_CASE
+        default:
+            break;
+        }
+        if (r >= 0)
+            return r;
     }
     if (!column_mode && !plan->vector_needs_dense && e->n > 0 && q >= 2 && q <= 16)
     {

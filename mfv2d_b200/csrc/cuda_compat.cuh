@@ -28,6 +28,16 @@ __device__ __forceinline__ int4 ld_ro(const int4 *p) { return __ldg(p); }
 __device__ __forceinline__ int ld_ro(const int *p) { return __ldg(p); }
 __device__ __forceinline__ float4 ld_ro(const float4 *p) { return __ldg(p); }
 
+// 8-byte asynchronous global -> shared copy (LDGSTS): no registers are held while the data is in flight
+__device__ __forceinline__ void cp_async8(double *smem_dst, const double *gmem_src)
+{
+    const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;\n" ::"r"(d), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;\n" ::: "memory"); }
+// 1 / x, IEEE rounded, without the slow paths of the full division
+__device__ __forceinline__ double fast_rcp(double x) { return __drcp_rn(x); }
+
 #else // ---------------------------------------------------------------------------------------
 #include "../../tests/emu/emu_cuda.h"
 #endif

@@ -1124,6 +1124,8 @@ void mfv2d_cuda_plan_destroy(mfv2d_plan *plan)
         mfv2d_cuda_free(plan->ctx, plan->d_vprog);
     if (plan->d_vcoef)
         mfv2d_cuda_free(plan->ctx, plan->d_vcoef);
+    if (plan->d_fblob)
+        mfv2d_cuda_free(plan->ctx, plan->d_fblob);
     delete plan;
 }
 

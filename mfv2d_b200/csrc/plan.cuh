@@ -182,6 +182,16 @@ struct AsmLayout
     int smem_bytes;
 };
 
+// layout of the fused matrix-free apply (element_vector_fused_kernel): int offsets into the descriptor blob,
+// double offsets into an element slot
+struct FusedVecInfo
+{
+    int n_terms, n_pre, n_rowA, n_rowC, n_contrib;
+    int off_pre, off_rowA, off_termB, off_rowC, off_yrow, off_contrib; // ints, each a multiple of 4
+    int blob_ints;
+    int off_vec, off_t, slot_doubles; // slot: corners[8] | in / out vectors (aliased) | t rows
+};
+
 struct mfv2d_plan
 {
     mfv2d_ctx *ctx;
@@ -217,6 +227,12 @@ struct mfv2d_plan
     double *d_vcoef = nullptr;
     bool vector_needs_dense = false; // an inverse mass appears in a vector program
     int mprog_off = 0, mcoef_off = 0; // matrix-mode programs (column-by-column fallback) follow the vector ones
+
+    // fused vector path (apply.cu): every term is  coef * [E] * D * [E]  with D a mass / interior product
+    bool vector_fused = false;
+    FusedVecInfo fv{};
+    std::vector<int32_t> fblob;
+    int32_t *d_fblob = nullptr;
 };
 
 // padded row length of the quadrature-indexed tables: even, and half of it odd, so that 16-byte

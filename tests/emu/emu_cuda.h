@@ -226,3 +226,6 @@ template <typename F> static inline cudaError_t cudaOccupancyMaxActiveBlocksPerM
     *n = 1;
     return cudaSuccess;
 }
+static inline void cp_async8(double *smem_dst, const double *gmem_src) { *smem_dst = *gmem_src; }
+static inline void cp_async_wait_all() {}
+static inline double fast_rcp(double x) { return 1.0 / x; }
