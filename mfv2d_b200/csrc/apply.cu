@@ -904,11 +904,13 @@ struct FusedRow // one 1-D contraction row of phase A (src = coefficients, dst =
 // rows with the same table (kB) two at a time; 8 ints per entry: src0, nB, kB, dst0, src1 (-1: single), dst1, g0, g1
 static void pair_rows(std::vector<FusedRow> rows, std::vector<int32_t> &out)
 {
-    std::stable_sort(rows.begin(), rows.end(), [](const FusedRow &a, const FusedRow &b) { return a.kB < b.kB; });
+    std::stable_sort(rows.begin(), rows.end(), [](const FusedRow &a, const FusedRow &b) {
+        return (a.g >= 0) != (b.g >= 0) ? (a.g >= 0) < (b.g >= 0) : a.kB < b.kB; // gathered rows together: uniform warps
+    });
     std::vector<int32_t> singles;
     for (size_t i = 0; i < rows.size();)
     {
-        if (i + 1 < rows.size() && rows[i + 1].kB == rows[i].kB)
+        if (i + 1 < rows.size() && rows[i + 1].kB == rows[i].kB && (rows[i + 1].g >= 0) == (rows[i].g >= 0))
         {
             out.insert(out.end(), {rows[i].src, rows[i].nB, rows[i].kB, rows[i].dst, rows[i + 1].src, rows[i + 1].dst, rows[i].g, rows[i + 1].g});
             i += 2;
@@ -1005,14 +1007,41 @@ static int plan_lower_vector_fused(mfv2d_plan *plan)
     FusedVecInfo fv{};
     fv.n_terms = (int)fts.size();
     fv.off_vec = 16;
-    fv.off_t = fv.off_vec + ((N + 1) & ~1);
+    fv.off_t = fv.off_vec + ((N + 2) & ~1); // at least one pad cell after x: it holds 0.0 (target of unused gather entries)
+    const int zero_cell = fv.off_vec + N;
     fv.slot_doubles = fv.off_t + t_total;
     // thread (e, b) of phase B reads slot[e][... + b]: with the slot stride congruent to q modulo 16 doubles the
     // addresses of a warp are congruent to the thread index, i.e. conflict free (even stride keeps 16-byte alignment)
+    fv.slot_doubles += 6; // room for the per-element rotation of the slot base (0, 2, 4 or 6 doubles)
     while ((fv.slot_doubles & 15) != ((q + (q & 1)) & 15))
         ++fv.slot_doubles;
+    if (fv.slot_doubles > 32000)
+        return MFV2D_SUCCESS; // slot addresses are packed into 16 bits
 
-    std::vector<int32_t> rowA, termB, rowC, yrow((size_t)2 * N, 0), contrib;
+    std::vector<int32_t> rowA, termB, rowC, yrow((size_t)2 * N, 0), contrib, gtab;
+    // signed sum of up to four cells as (p0 + p1) - (n0 + n1): positive entries first, the zero cell where there is none
+    auto split_signs = [&](const int32_t *ev, const std::vector<int> *addr_of, int base, int32_t out[4]) -> bool {
+        int np = 0, nn = 0;
+        out[0] = out[1] = out[2] = out[3] = zero_cell;
+        for (int z = 0; z < 4 && ev[z] != 0; ++z)
+        {
+            const int idx = (ev[z] < 0 ? -ev[z] : ev[z]) - 1;
+            const int a = addr_of ? (*addr_of)[idx] : base + idx;
+            if (ev[z] > 0)
+            {
+                if (np == 2)
+                    return false;
+                out[np++] = a;
+            }
+            else
+            {
+                if (nn == 2)
+                    return false;
+                out[2 + nn++] = a;
+            }
+        }
+        return true;
+    };
     std::vector<FusedRow> rowsA, rowsC;
     std::vector<std::vector<std::array<int32_t, 8>>> per_row(N);
     const int x_base = fv.off_vec, t_base = fv.off_t;
@@ -1029,12 +1058,21 @@ static int plan_lower_vector_fused(mfv2d_plan *plan)
             {
                 const int first = op.in[k].off + a * nB; // index of the row's first coefficient in the term's input vector
                 if (ft.R >= 0)
-                    rowsA.push_back({x_base + c0, nB, op.in[k].kB, t_base + t_off[i] + row * ldt, plan->basis->inc_off[ft.R] + first});
+                {
+                    rowsA.push_back({x_base + c0, nB, op.in[k].kB, t_base + t_off[i] + row * ldt, (int)gtab.size() / 4});
+                    for (int j = 0; j < nB; ++j)
+                    {
+                        int32_t e4[4];
+                        if (!split_signs(plan->basis->h_inc.data() + 4 * (size_t)(plan->basis->inc_off[ft.R] + first + j), nullptr, x_base + c0, e4))
+                            return MFV2D_SUCCESS;
+                        gtab.insert(gtab.end(), e4, e4 + 4);
+                    }
+                }
                 else
                     rowsA.push_back({x_base + c0 + first, nB, op.in[k].kB, t_base + t_off[i] + row * ldt, -1});
             }
         }
-        // address (+1) of entry m of the term's output vector: head of the t row of its (component, row)
+        // address of entry m of the term's output vector: head of the t row of its (component, row)
         std::vector<int> out_addr(n_out[i]);
         row = 0;
         for (int k = 0; k < op.n_out; ++k)
@@ -1045,7 +1083,7 @@ static int plan_lower_vector_fused(mfv2d_plan *plan)
                 const int tr = t_base + t_off[i] + row * ldt;
                 rowsC.push_back({tr, nB, op.out[k].kB, tr, -1});
                 for (int j = 0; j < nB; ++j)
-                    out_addr[op.out[k].off + a * nB + j] = tr + j + 1;
+                    out_addr[op.out[k].off + a * nB + j] = tr + j;
             }
         }
         const int n_rows_form = plan->form_offsets[ft.rf + 1] - r0;
@@ -1056,16 +1094,10 @@ static int plan_lower_vector_fused(mfv2d_plan *plan)
             const int32_t *map = plan->basis->h_inc.data() + 4 * (size_t)plan->basis->inc_off[ft.L];
             for (int k = 0; k < n_rows_form; ++k)
             {
-                std::array<int32_t, 8> c{ft.ci, 0, 0, 0, 0, 0, 0, 0};
-                for (int z = 0; z < 4; ++z)
-                {
-                    const int32_t ev = map[4 * k + z];
-                    if (ev == 0)
-                        break;
-                    const int a = out_addr[(ev < 0 ? -ev : ev) - 1];
-                    c[1 + z] = ev < 0 ? -a : a;
-                }
-                per_row[r0 + k].push_back(c);
+                int32_t e4[4];
+                if (!split_signs(map + 4 * k, &out_addr, 0, e4))
+                    return MFV2D_SUCCESS;
+                per_row[r0 + k].push_back({ft.ci, e4[0], e4[1], e4[2], e4[3], 1, 0, 0});
             }
         }
         else
@@ -1073,7 +1105,7 @@ static int plan_lower_vector_fused(mfv2d_plan *plan)
             if (n_out[i] != n_rows_form)
                 return MFV2D_SUCCESS;
             for (int k = 0; k < n_rows_form; ++k)
-                per_row[r0 + k].push_back({ft.ci, out_addr[k], 0, 0, 0, 0, 0, 0});
+                per_row[r0 + k].push_back({ft.ci, out_addr[k], zero_cell, zero_cell, zero_cell, 0, 0, 0});
         }
     }
     // phase B: terms with the same dense factor (kind, field, transposition) two at a time
@@ -1104,15 +1136,16 @@ static int plan_lower_vector_fused(mfv2d_plan *plan)
     pair_rows(rowsC, rowC);
     for (int k = 0; k < N; ++k)
     {
-        yrow[2 * k] = (int32_t)(contrib.size() / 8);
+        yrow[2 * k] = (int32_t)(contrib.size() / 4);
         yrow[2 * k + 1] = (int32_t)per_row[k].size();
-        for (const auto &c : per_row[k])
-            contrib.insert(contrib.end(), c.begin(), c.end());
+        for (const auto &c : per_row[k]) // 16 bytes per contribution: coefficient, 2 + 2 16-bit addresses, flag (0: only the first)
+            contrib.insert(contrib.end(), {c[0], (int32_t)(((uint32_t)c[1] & 0xffffu) | ((uint32_t)c[2] << 16)),
+                                           (int32_t)(((uint32_t)c[3] & 0xffffu) | ((uint32_t)c[4] << 16)), c[5]});
     }
-    fv.n_pre = 0;
+    fv.n_pre = (int)gtab.size() / 4;
     fv.n_rowA = (int)rowA.size() / 8;
     fv.n_rowC = (int)rowC.size() / 8;
-    fv.n_contrib = (int)contrib.size() / 8;
+    fv.n_contrib = (int)contrib.size() / 4;
     std::vector<int32_t> &blob = plan->fblob;
     blob.clear();
     auto put = [&](const std::vector<int32_t> &v) {
@@ -1122,7 +1155,7 @@ static int plan_lower_vector_fused(mfv2d_plan *plan)
         blob.insert(blob.end(), v.begin(), v.end());
         return off;
     };
-    fv.off_pre = 0;
+    fv.off_pre = put(gtab);
     fv.off_rowA = put(rowA);
     fv.off_termB = put(termB);
     fv.off_rowC = put(rowC);
@@ -1242,33 +1275,35 @@ template <int Q, int NT> __device__ __forceinline__ void row_dot_n(const double 
 }
 
 // coefficient j of a phase-A row: read in place, or gathered from x through the right incidence
-__device__ __forceinline__ double fused_coef(const double *__restrict__ c, int g, int j, const int4 *__restrict__ inc)
+__device__ __forceinline__ double fused_coef(const double *__restrict__ slot, int src, int g, int j, const int4 *__restrict__ gtab)
 {
-    return g < 0 ? c[j] : signed_gather(inc[g + j], c);
+    if (g < 0)
+        return slot[src + j];
+    const int4 m = gtab[g + j]; // (p0 + p1) - (n0 + n1); unused entries point at the slot's zero cell
+    return (slot[m.x] + slot[m.y]) - (slot[m.z] + slot[m.w]);
 }
 
 template <int Q, int NT>
 __device__ __forceinline__ void fused_rows_a(const int4 d0, const int4 d1, double *__restrict__ slot, const double *__restrict__ smem, int edge_off,
-                                             const int4 *__restrict__ inc)
+                                             const int4 *__restrict__ gtab)
 {
     constexpr int LDQ = (Q + 1) & ~1;
-    const double *c0 = slot + d0.x, *c1 = slot + (NT > 1 ? d1.x : d0.x);
     const double *B = smem + d0.z * edge_off;
     double acc[NT][Q];
     {
         // first coefficient: plain products instead of zero + fma
         double c[NT];
-        c[0] = fused_coef(c0, d1.z, 0, inc);
+        c[0] = fused_coef(slot, d0.x, d1.z, 0, gtab);
         if (NT > 1)
-            c[NT - 1] = fused_coef(c1, d1.w, 0, inc);
+            c[NT - 1] = fused_coef(slot, d1.x, d1.w, 0, gtab);
         row_mul_n<Q, NT>(acc, c, B);
     }
     for (int j = 1; j < d0.y; ++j)
     {
         double c[NT];
-        c[0] = fused_coef(c0, d1.z, j, inc);
+        c[0] = fused_coef(slot, d0.x, d1.z, j, gtab);
         if (NT > 1)
-            c[NT - 1] = fused_coef(c1, d1.w, j, inc);
+            c[NT - 1] = fused_coef(slot, d1.x, d1.w, j, gtab);
         row_axpy_n<Q, NT>(acc, c, B + j * LDQ);
     }
 #pragma unroll
@@ -1463,6 +1498,9 @@ template <int Q> __global__ void __launch_bounds__(APPLYT_THREADS, 2) element_ve
     int4 *inc = reinterpret_cast<int4 *>(blob + fv.blob_ints);
     double *slots = reinterpret_cast<double *>(inc + fa.inc_rows);
     const int epb = fa.epb, SD = fv.slot_doubles;
+    // slot of element e: stride SD (congruent to Q modulo 16 doubles: phase B, lanes = (e, b), is conflict free) plus a
+    // small rotation so that 16-byte accesses of phases A / C, lanes = consecutive elements, fall into distinct bank groups
+#define SLOT(e) ((e) * SD + 2 * (((e) >> 1) & 3))
     const int off_xs = fv.off_vec;
     const unsigned long long n_groups = (args.n_elem + epb - 1) / epb;
     const float inv_n = 1.0f / (float)N;
@@ -1475,11 +1513,11 @@ template <int Q> __global__ void __launch_bounds__(APPLYT_THREADS, 2) element_ve
         const unsigned long long elem0 = grp * epb;
         const int nv = (int)((args.n_elem - elem0) < (unsigned long long)epb ? (args.n_elem - elem0) : epb);
         for (int i = threadIdx.x; i < nv * 8; i += blockDim.x)
-            cp_async8(slots + (i >> 3) * SD + parity * 8 + (i & 7), args.corners + elem0 * 8 + i);
+            cp_async8(slots + SLOT(i >> 3) + parity * 8 + (i & 7), args.corners + elem0 * 8 + i);
         for (int i = threadIdx.x; i < nv * N; i += blockDim.x)
         {
             const int e = (int)(((float)i + 0.5f) * inv_n);
-            cp_async8(slots + e * SD + off_xs + (i - e * N), args.x + elem0 * N + i);
+            cp_async8(slots + SLOT(e) + off_xs + (i - e * N), args.x + elem0 * N + i);
         }
     };
     prefetch(blockIdx.x, 0);
@@ -1494,12 +1532,15 @@ template <int Q> __global__ void __launch_bounds__(APPLYT_THREADS, 2) element_ve
         pnts[i] = args.tab[(2 * p + 1) * Q + i];
         wgts[i] = args.tab[(2 * p + 2) * Q + i];
     }
+    for (int i = threadIdx.x; i < epb; i += blockDim.x)
+        slots[SLOT(i) + off_xs + N] = 0.0; // the zero cell of every slot (never written again)
     for (int i = threadIdx.x; i < fa.n_coef; i += blockDim.x)
         coef[i] = args.coef[i];
     for (int i = threadIdx.x; i < fv.blob_ints; i += blockDim.x)
         blob[i] = fa.blob[i];
     for (int i = threadIdx.x; i < fa.inc_rows; i += blockDim.x)
         inc[i] = reinterpret_cast<const int4 *>(args.inc)[i];
+    const int4 *gtab = reinterpret_cast<const int4 *>(blob + fv.off_pre);
     const int4 *rowA = reinterpret_cast<const int4 *>(blob + fv.off_rowA);
     const int *termB = blob + fv.off_termB;
     const int4 *rowC = reinterpret_cast<const int4 *>(blob + fv.off_rowC);
@@ -1515,17 +1556,18 @@ template <int Q> __global__ void __launch_bounds__(APPLYT_THREADS, 2) element_ve
         __syncthreads(); // x / corners of this pass have landed; the previous pass is done with the t rows
         // ---- phase A: t[row][:] = sum_j c[j] B_j[:], rows of the same table two at a time ----
         {
+            // lanes = consecutive elements of ONE row pair: descriptors, tables and branches are warp uniform
             const int R = fv.n_rowA;
-            const float inv_R = 1.0f / (float)R;
+            const float inv_nv = 1.0f / (float)nv;
             for (int idx = threadIdx.x; idx < nv * R; idx += blockDim.x)
             {
-                const int e = (int)(((float)idx + 0.5f) * inv_R), row = idx - e * R;
-                double *slot = slots + e * SD;
+                const int row = (int)(((float)idx + 0.5f) * inv_nv), e = idx - row * nv;
+                double *slot = slots + SLOT(e);
                 const int4 d0 = rowA[2 * row], d1 = rowA[2 * row + 1];
                 if (d1.x >= 0)
-                    fused_rows_a<Q, 2>(d0, d1, slot, smem, edge_off, inc);
+                    fused_rows_a<Q, 2>(d0, d1, slot, smem, edge_off, gtab);
                 else
-                    fused_rows_a<Q, 1>(d0, d1, slot, smem, edge_off, inc);
+                    fused_rows_a<Q, 1>(d0, d1, slot, smem, edge_off, gtab);
             }
         }
         __syncthreads();
@@ -1534,7 +1576,7 @@ template <int Q> __global__ void __launch_bounds__(APPLYT_THREADS, 2) element_ve
         for (int idx = threadIdx.x; idx < nv * Q; idx += blockDim.x)
         {
             const int e = idx / Q, b = idx - e * Q;
-            double *slot = slots + e * SD;
+            double *slot = slots + SLOT(e);
             const double *cs = slot + parity * 8;
             const double x0 = cs[0], y0 = cs[1], x1 = cs[2], y1 = cs[3], x2 = cs[4], y2 = cs[5], x3 = cs[6], y3 = cs[7];
             const double xi = pnts[b];
@@ -1560,11 +1602,11 @@ template <int Q> __global__ void __launch_bounds__(APPLYT_THREADS, 2) element_ve
         // ---- phase C: out[i, j] = B_j[:] . t'[row][:], rows of the same table two at a time ----
         {
             const int R = fv.n_rowC;
-            const float inv_R = 1.0f / (float)R;
+            const float inv_nv = 1.0f / (float)nv;
             for (int idx = threadIdx.x; idx < nv * R; idx += blockDim.x)
             {
-                const int e = (int)(((float)idx + 0.5f) * inv_R), row = idx - e * R;
-                double *slot = slots + e * SD;
+                const int row = (int)(((float)idx + 0.5f) * inv_nv), e = idx - row * nv;
+                double *slot = slots + SLOT(e);
                 const int4 d0 = rowC[2 * row], d1 = rowC[2 * row + 1];
                 if (d1.x >= 0)
                     fused_rows_c<Q, 2>(d0, d1, slot, smem, edge_off);
@@ -1577,35 +1619,22 @@ template <int Q> __global__ void __launch_bounds__(APPLYT_THREADS, 2) element_ve
         for (int i = threadIdx.x; i < nv * N; i += blockDim.x)
         {
             const int e = (int)(((float)i + 0.5f) * inv_n), k = i - e * N;
-            const double *slot = slots + e * SD - 1; // the addresses carry +1 so that their sign can be the sign of the entry
+            const double *slot = slots + SLOT(e);
             const int2 yr = yrow[k];
             double acc = 0.0;
             for (int c = yr.x; c < yr.x + yr.y; ++c)
             {
-                const int4 c0 = contrib[2 * c];
-                double v = c0.y < 0 ? -slot[-c0.y] : slot[c0.y];
-                if (c0.z != 0)
-                {
-                    const int c1x = contrib[2 * c + 1].x;
-                    const double v1 = slot[abs(c0.z)];
-                    v += c0.z < 0 ? -v1 : v1;
-                    if (c0.w != 0)
-                    {
-                        const double v2 = slot[abs(c0.w)];
-                        v += c0.w < 0 ? -v2 : v2;
-                        if (c1x != 0)
-                        {
-                            const double v3 = slot[abs(c1x)];
-                            v += c1x < 0 ? -v3 : v3;
-                        }
-                    }
-                }
+                const int4 c0 = contrib[c];
+                double v = slot[c0.y & 0xffff];
+                if (c0.w) // left incidence: (p0 + p1) - (n0 + n1)
+                    v = (v + slot[(unsigned)c0.y >> 16]) - (slot[c0.z & 0xffff] + slot[(unsigned)c0.z >> 16]);
                 acc = fma(coef[c0.x], v, acc);
             }
             args.y[elem0 * N + i] = acc;
         }
     }
 }
+#undef SLOT
 
 template <int Q> static int launch_fused_q(mfv2d_ctx *ctx, FusedArgs &fa, size_t fixed_bytes, size_t n_elem)
 {
