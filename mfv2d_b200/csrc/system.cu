@@ -71,43 +71,52 @@ template <bool VEC>
 __device__ __forceinline__ void block_gemv_rows(const double *__restrict__ A, const double *__restrict__ xs, double *__restrict__ y,
                                                 int n)
 {
-    const int warp = threadIdx.x >> 5, nwarps = MFV2D_NWARPS;
 #ifndef MFV2D_EMU
     const int lane = threadIdx.x & 31, sub = lane >> 3, l8 = lane & 7;
-    for (int r0 = warp * 4; r0 < n; r0 += nwarps * 4)
+    // eight rows per trip (two independent quarter-warp rows per lane): ~2 n / 16 16-byte loads in flight per lane
+    for (int r0 = 0; r0 < n; r0 += 8)
     {
-        const int r = r0 + sub;
-        double acc0 = 0.0, acc1 = 0.0;
-        if (r < n)
+        const int ra = r0 + sub, rb = r0 + 4 + sub;
+        double a0 = 0.0, a1 = 0.0, b0 = 0.0, b1 = 0.0;
+        const double *rowa = A + (size_t)(ra < n ? ra : 0) * n, *rowb = A + (size_t)(rb < n ? rb : 0) * n;
+        if (VEC)
         {
-            const double *row = A + (size_t)r * n;
-            if (VEC)
-            {
 #pragma unroll 4
-                for (int c = 2 * l8; c < n; c += 16)
-                {
-                    const double2 a = __ldcs(reinterpret_cast<const double2 *>(row + c));
-                    const double2 x = *reinterpret_cast<const double2 *>(xs + c);
-                    acc0 = fma(a.x, x.x, acc0);
-                    acc1 = fma(a.y, x.y, acc1);
-                }
-            }
-            else
+            for (int c = 2 * l8; c < n; c += 16)
             {
-#pragma unroll 4
-                for (int c = l8; c < n; c += 8)
-                    acc0 = fma(__ldcs(row + c), xs[c], acc0);
+                const double2 va = __ldcs(reinterpret_cast<const double2 *>(rowa + c));
+                const double2 vb = __ldcs(reinterpret_cast<const double2 *>(rowb + c));
+                const double2 x = *reinterpret_cast<const double2 *>(xs + c);
+                a0 = fma(va.x, x.x, a0);
+                a1 = fma(va.y, x.y, a1);
+                b0 = fma(vb.x, x.x, b0);
+                b1 = fma(vb.y, x.y, b1);
             }
         }
-        double acc = acc0 + acc1;
+        else
+        {
+#pragma unroll 4
+            for (int c = l8; c < n; c += 8)
+            {
+                const double x = xs[c];
+                a0 = fma(__ldcs(rowa + c), x, a0);
+                b0 = fma(__ldcs(rowb + c), x, b0);
+            }
+        }
+        double acc = a0 + a1, bcc = b0 + b1;
         acc += __shfl_xor_sync(0xffffffffu, acc, 4);
+        bcc += __shfl_xor_sync(0xffffffffu, bcc, 4);
         acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+        bcc += __shfl_xor_sync(0xffffffffu, bcc, 2);
         acc += __shfl_xor_sync(0xffffffffu, acc, 1);
-        if (l8 == 0 && r < n)
-            y[r] = acc;
+        bcc += __shfl_xor_sync(0xffffffffu, bcc, 1);
+        if (l8 == 0 && ra < n)
+            y[ra] = acc;
+        if (l8 == 0 && rb < n)
+            y[rb] = bcc;
     }
 #else
-    for (int r = warp; r < n; r += nwarps)
+    for (int r = 0; r < n; ++r)
     {
         double acc = 0.0;
         for (int c = 0; c < n; ++c)
@@ -117,21 +126,29 @@ __device__ __forceinline__ void block_gemv_rows(const double *__restrict__ A, co
 #endif
 }
 
+// one WARP per element block, no CTA-wide barrier: the warp stages x_e in its own strip of shared memory and
+// streams the rows of A_e; the other warps of the SM cover its latencies
 __global__ void __launch_bounds__(SYS_THREADS) block_gemv_kernel(unsigned long long n_elem, const int64_t *__restrict__ boff,
                                                                 const int64_t *__restrict__ moff,
                                                                 const double *__restrict__ M, const double *__restrict__ x,
-                                                                double *__restrict__ y)
+                                                                double *__restrict__ y, int xs_stride)
 {
-    MFV2D_DYN_SMEM(double, xs);
-    for (unsigned long long e = blockIdx.x; e < n_elem; e += gridDim.x)
+    MFV2D_DYN_SMEM(double, xs_all);
+    const int warp = threadIdx.x >> 5, nwarps = MFV2D_NWARPS;
+    double *xs = xs_all + (size_t)warp * xs_stride;
+    for (unsigned long long e = (unsigned long long)blockIdx.x * nwarps + warp; e < n_elem; e += (unsigned long long)gridDim.x * nwarps)
     {
         const int64_t o = boff[e];
         const int n = (int)(boff[e + 1] - o);
         const double *A = M + moff[e];
-        __syncthreads();
-        for (int i = threadIdx.x; i < n; i += blockDim.x)
+#ifndef MFV2D_EMU
+        __syncwarp();
+#endif
+        for (int i = MFV2D_LANE0; i < n; i += MFV2D_LANE_STEP)
             xs[i] = x[o + i];
-        __syncthreads();
+#ifndef MFV2D_EMU
+        __syncwarp();
+#endif
         if ((n & 1) == 0 && (reinterpret_cast<size_t>(A) & 15) == 0)
             block_gemv_rows<true>(A, xs, y + o, n);
         else
@@ -473,11 +490,19 @@ static int sys_gemv(const mfv2d_system *s, const double *M, const double *x, dou
     mfv2d_ctx *ctx = s->ctx;
     if (s->n_elem == 0)
         return MFV2D_SUCCESS;
+    const int nwarps = SYS_THREADS / 32;
+    const int xs_stride = (s->max_n + 3) & ~1;
+    const size_t smem = (size_t)nwarps * xs_stride * sizeof(double);
+    if (smem > ctx->smem_optin)
+        return mfv2d_fail(ctx, MFV2D_CUDA_UNSUPPORTED, "block_gemv: blocks of %d rows need %zu bytes of shared memory", s->max_n, smem);
+    if (smem > 48 * 1024)
+        MFV2D_CUDA_CHECK(ctx, cudaFuncSetAttribute(block_gemv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     long long grid = (long long)ctx->sm_count * 8;
-    if (grid > s->n_elem)
-        grid = s->n_elem;
-    MFV2D_LAUNCH(block_gemv_kernel, (unsigned)grid, SYS_THREADS, (size_t)(s->max_n + 2) * sizeof(double), ctx->stream,
-                 (unsigned long long)s->n_elem, s->d_block_off, s->d_mat_off, M, x, y);
+    const long long need = (s->n_elem + nwarps - 1) / nwarps;
+    if (grid > need)
+        grid = need;
+    MFV2D_LAUNCH(block_gemv_kernel, (unsigned)grid, SYS_THREADS, smem, ctx->stream, (unsigned long long)s->n_elem, s->d_block_off,
+                 s->d_mat_off, M, x, y, xs_stride);
     ctx->launches++;
     MFV2D_CUDA_CHECK(ctx, cudaGetLastError());
     return MFV2D_SUCCESS;
