@@ -232,7 +232,7 @@ def run_reference(args):
         "cpu_baseline": {"value": v, "unit": "element matrices/s", "cores": cores, "kind": vals[-1]["kind"], "sample": vals[-1]["sample"]},
         "e2e": {"value": v, "unit": "element matrices/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def workload_config(n_gpus):
@@ -441,13 +441,35 @@ def run_ours(args):
     if rank == 0:
         if world == 1 and not args.no_cpu:
             line["cpu_baseline"] = cpu_baseline(1, args.cpu_seconds)
-        print(json.dumps(line), flush=True)
+        emit(line)
     barrier(dist)
     if dist is not None:
         dist.destroy_process_group()
 
 
+_JSON_FD = None
+
+
+def quiet_stdout():
+    """Native libraries (NCCL's version banner, ...) write to fd 1: keep the process's stdout for the ONE JSON line
+    and send everything else to stderr."""
+    global _JSON_FD
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
+
+
 def main():
+    quiet_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)

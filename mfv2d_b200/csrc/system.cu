@@ -555,7 +555,7 @@ static int sys_apply_trace(const mfv2d_system *s, const double *x, double *t)
     return sys_interface_sum(s, t, 0, nullptr);
 }
 
-static int sys_apply_schur(const mfv2d_system *s, const double *t_in, double *t_out, const int *done)
+static int sys_apply_schur(const mfv2d_system *s, const double *t_in, double *t_out, const int *done, bool interface_sum = true)
 {
     mfv2d_ctx *ctx = s->ctx;
     if (s->n_elem)
@@ -577,7 +577,7 @@ static int sys_apply_schur(const mfv2d_system *s, const double *t_in, double *t_
         ctx->launches++;
     }
     MFV2D_CUDA_CHECK(ctx, cudaGetLastError());
-    return sys_interface_sum(s, t_out, 0, nullptr);
+    return interface_sum ? sys_interface_sum(s, t_out, 0, nullptr) : MFV2D_SUCCESS;
 }
 
 // dot product of two trace (w = ownership weights) or dense (w = nullptr) vectors -> device scalar
@@ -1024,20 +1024,27 @@ int mfv2d_cuda_solve_schur_cg(mfv2d_system *s, const double *rhs, const double *
             // one CG iteration = 7 small launches; on one GPU a block of check_every iterations is captured ONCE
             // into a CUDA graph and replayed (the kernels stop by themselves once the device flag is set)
             auto enqueue_iteration = [&]() -> int {
-                MFV2D_TRY(sys_apply_schur(s, p, ap, flags));
-                MFV2D_LAUNCH(dot_partial_kernel, (unsigned)s->n_partials, SYS_THREADS, 0, ctx->stream, nt, (const double *)ap,
-                             (const double *)p, w, s->d_partials, (const int *)flags);
                 if (ctx->n_ranks > 1)
                 {
+                    // p . S p = sum over the ranks of p_r . (S_r p_r) (local, un-summed products, no ownership weights):
+                    // the scalar rides in the SAME all-reduce that sums the interface multipliers of S p
+                    MFV2D_TRY(sys_apply_schur(s, p, ap, flags, false));
+                    MFV2D_LAUNCH(dot_partial_kernel, (unsigned)s->n_partials, SYS_THREADS, 0, ctx->stream, nt, (const double *)ap,
+                                 (const double *)p, (const double *)nullptr, s->d_partials, (const int *)flags);
                     MFV2D_LAUNCH(sum_partials_kernel, 1, 32, 0, ctx->stream, s->n_partials, (const double *)s->d_partials,
                                  s->d_partials);
-                    MFV2D_TRY(comm_allreduce(ctx, s->d_partials, 1));
+                    MFV2D_TRY(sys_interface_sum(s, ap, 1, s->d_partials));
                     MFV2D_LAUNCH(cg_alpha_kernel, 1, 32, 0, ctx->stream, 1, (const double *)s->d_partials, sc, flags, precondition);
                     ctx->launches++;
                 }
                 else
+                {
+                    MFV2D_TRY(sys_apply_schur(s, p, ap, flags));
+                    MFV2D_LAUNCH(dot_partial_kernel, (unsigned)s->n_partials, SYS_THREADS, 0, ctx->stream, nt, (const double *)ap,
+                                 (const double *)p, w, s->d_partials, (const int *)flags);
                     MFV2D_LAUNCH(cg_alpha_kernel, 1, 32, 0, ctx->stream, s->n_partials, (const double *)s->d_partials, sc, flags,
                                  precondition);
+                }
                 MFV2D_LAUNCH(cg_update_kernel, (unsigned)s->n_partials, SYS_THREADS, 0, ctx->stream, nt, (const double *)sc,
                              (const int *)flags, (const double *)p, (const double *)ap, lam, res, w, dinv, z, s->d_partials,
                              s->d_partials + s->n_partials);
@@ -1062,7 +1069,9 @@ int mfv2d_cuda_solve_schur_cg(mfv2d_system *s, const double *rhs, const double *
             };
 #ifndef MFV2D_EMU
             cudaGraphExec_t graph_exec = nullptr;
-            if (ctx->n_ranks == 1 && max_iter >= 2 * check_every)
+            // (with more than one rank the NCCL all-reduces are captured too; MFV2D_CG_GRAPH=0 turns the graph off)
+            const char *graph_env = getenv("MFV2D_CG_GRAPH");
+            if (!(graph_env && graph_env[0] == '0') && max_iter >= 2 * check_every)
             {
                 cudaGraph_t graph = nullptr;
                 const uint64_t launches_before = ctx->launches;
@@ -1094,7 +1103,7 @@ int mfv2d_cuda_solve_schur_cg(mfv2d_system *s, const double *rhs, const double *
                         r = mfv2d_fail(ctx, MFV2D_CUDA_ERROR, "CG graph launch failed: %s", cudaGetErrorString(cudaGetLastError()));
                         break;
                     }
-                    ctx->launches += 7 * check_every;
+                    ctx->launches += (ctx->n_ranks > 1 ? 13 : 7) * check_every;
                     it = stop;
                 }
 #endif

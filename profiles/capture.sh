@@ -18,7 +18,7 @@ timeout 600 $NCU --set full --import-source on -k regex:element_matrix_kernel -s
     python bench.py --steps 2 --warmup 3 --no-cpu --skip-e2e --skip-extra > $O/ncu_a4.log 2>&1
 timeout 600 $NCU --set full --import-source on -k regex:element_matrix_kernel -s 2 -c 1 -f -o $O/asm6_full \
     python bench.py --workload poisson6 --steps 2 --warmup 3 --no-cpu --skip-e2e --skip-extra > $O/ncu_a6.log 2>&1
-timeout 600 $NCU --set full --import-source on -k regex:element_vector_tile_kernel -s 2 -c 1 -f -o $O/apply4_full \
+timeout 600 $NCU --set full --import-source on -k regex:element_vector_fused_kernel -s 2 -c 1 -f -o $O/apply4_full \
     python bench.py --steps 2 --warmup 3 --no-cpu --skip-e2e > $O/ncu_v4.log 2>&1
 timeout 600 $NCU --set full --import-source on -k regex:block_gemv_kernel -s 2 -c 1 -f -o $O/gemv_full \
     python bench.py --steps 2 --warmup 3 --no-cpu --skip-e2e > $O/ncu_g.log 2>&1

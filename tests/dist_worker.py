@@ -77,7 +77,17 @@ def main():
         def dot(a, b):  # ownership-weighted partial + all-reduce of one scalar
             return float(allreduce(np.array([np.sum(P.owned * a * b)]))[0])
 
-        schur = lambda t: iface_sum(N @ (Ainv @ (N.T @ t)))
+        def schur_and_dot(t):
+            # system.cu, N > 1: the local un-summed product S_r t and t . (S_r t) travel in ONE all-reduce
+            # (t . S t = sum_r t_r . S_r t_r because shared entries of t are identical on both ranks)
+            loc = N @ (Ainv @ (N.T @ t))
+            buf = np.zeros(P.n_slots + 1)
+            buf[P.slot] = loc[P.shared_index]
+            buf[-1] = t @ loc
+            buf = allreduce(buf)
+            loc[P.shared_index] = buf[P.slot]
+            return loc, float(buf[-1])
+
         inv_a_y = Ainv @ rhs_l
         r = iface_sum(N @ inv_a_y) - phi_l
         lam = np.zeros(P.n_trace)
@@ -86,8 +96,9 @@ def main():
         d = r.copy()
         it = 0
         while it < 2000 and rr >= tol2:
-            ad = schur(d)
-            alpha = rr / dot(d, ad)
+            ad, dad = schur_and_dot(d)
+            assert abs(dad - dot(d, ad)) <= 1e-9 * abs(dad)  # same number as the ownership-weighted dot of the summed product
+            alpha = rr / dad
             lam += alpha * d
             r -= alpha * ad
             rr_new = dot(r, r)
