@@ -136,6 +136,35 @@ def check_matrix_vector_consistency(M, name, p, k, n=16, seed=5):
     assert relerr(np.einsum("eij,ej->ei", mats, x), vecs) < 1e-12
 
 
+def check_mixed_order_buckets(M, orders=(2, 3, 5, 8), per_order=5, name="mixed_poisson", k=3, seed=9):
+    """BASELINE.json configs[3] (h/p-refined mesh, mixed orders 2-8): the leaf elements are bucketed by order, one
+    ElementBatch per (p, q) bucket, and the matrices / matrix-free vectors are scattered back to mesh order; every
+    element is compared with the oracle's restatement of the reference at its own order."""
+    s = SYSTEMS[name]
+    specs = specs_of(M, s)
+    rng = np.random.default_rng(seed)
+    unit = np.array([(-1, -1), (1, -1), (1, 1), (-1, 1)], float)
+    elem_orders = rng.permutation(np.repeat(np.array(orders), per_order))
+    corners = unit + rng.uniform(-0.25, 0.25, (elem_orders.size, 4, 2))
+    mats, vecs, xs = [None] * elem_orders.size, [None] * elem_orders.size, [None] * elem_orders.size
+    for p in sorted(set(int(o) for o in elem_orders)):
+        idx = np.flatnonzero(elem_orders == p)
+        batch = M.ElementBatch(make_basis(M, p, k), np.ascontiguousarray(corners[idx]))
+        ne = specs.total_size(p, p)
+        x = rng.standard_normal((idx.size, ne))
+        m = M.compute_element_matrices(specs, s["lhs"], batch, x)
+        v = M.compute_element_vectors(specs, s["lhs"], batch, x)
+        assert m.shape == (idx.size, ne, ne)
+        for j, e in enumerate(idx):
+            mats[e], vecs[e], xs[e] = m[j], v[j], x[j]
+    blocks, fs = O.decode_expressions(s["lhs"], s["form_names"])
+    for e, p in enumerate(elem_orders):
+        ob = O.basis(int(p), int(p) + k + 1)
+        ref = O.element_matrix(ob, corners[e], s["form_orders"], blocks, fs)
+        assert relerr(mats[e], ref) < TOL_MAT, (e, p)
+        assert relerr(vecs[e], ref @ xs[e]) < TOL_MAT, (e, p)
+
+
 def check_incidence(M, orders=(1, 2, 3, 5)):
     """tests/test_apply_incidence-c.py: all 8 incidence kernels against explicit matrices."""
     rng = np.random.default_rng(11)

@@ -48,6 +48,11 @@ def test_matrix_vector_consistency(gpu, name, p, k):
     P.check_matrix_vector_consistency(gpu[0], name, p, k, n=300)
 
 
+@pytest.mark.parametrize("name", ["mixed_poisson", "stokes"])
+def test_mixed_order_buckets(gpu, name):
+    P.check_mixed_order_buckets(gpu[0], orders=(2, 3, 4, 5, 6, 7, 8), per_order=9, name=name)
+
+
 def test_incidence(gpu):
     P.check_incidence(gpu[0], orders=(1, 2, 3, 4, 5, 8))
 
