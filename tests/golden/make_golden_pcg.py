@@ -1,4 +1,5 @@
-"""Iteration counts / residuals of the REFERENCE's solve_pcg_iterative (python/mfv2d/solving.py:634-684) on the
+"""Iteration counts / residuals of the REFERENCE's solve_pcg_iterative (python/mfv2d/solving.py:634-684; on the small
+systems also solve_cg_iterative :590-631 and solve_gmres_iterative :553-587) on the
 meshes of the solve_*.npz fixtures.  Build container only (needs /root/reference and oracle/_ref):
 
     python tests/golden/make_golden_pcg.py        ->  tests/golden/pcg.json
@@ -29,7 +30,8 @@ def main():
     from mfv2d.system import KFormSystem
     from mfv2d.mimetic2d import FemCache
     from mfv2d.solve_system import compute_element_rhs
-    from mfv2d.solving import ConvergenceSettings, LinearSystem, solve_pcg_iterative
+    from mfv2d.solving import (ConvergenceSettings, LinearSystem, solve_cg_iterative, solve_gmres_iterative,
+                               solve_pcg_iterative)
 
     def f_exact(x, y):
         return -2 * np.pi**2 * np.cos(np.pi * x) * np.cos(np.pi * y)
@@ -56,6 +58,20 @@ def main():
         sd, st, resid, iters = solve_pcg_iterative(ls, dv, tv, ConvergenceSettings(5000, 1e-30, 1e-10))
         name = f"solve_{nh}x{nv}_p{order}{'_def' if deformed else ''}"
         out[name] = {"iterations": int(iters), "residual": float(resid)}
+        if mesh.leaf_count <= 12:  # the other two drivers of solving.py on the small systems
+            ref_d, ref_t = np.array(sd.as_merged()), np.array(st.as_merged())
+
+            def err(d, t):
+                return float(max(np.abs(np.array(d.as_merged()) - ref_d).max() / np.abs(ref_d).max(),
+                                 np.abs(np.array(t.as_merged()) - ref_t).max() / np.abs(ref_t).max()))
+
+            for key, fn, settings in (("cg", solve_cg_iterative, ConvergenceSettings(3000, 1e-30, 1e-10)),
+                                      ("gmres", solve_gmres_iterative, ConvergenceSettings(400, 1e-30, 1e-10))):
+                try:
+                    d2, t2, r2, i2 = fn(ls, dv, tv, settings)
+                    out[name][key] = {"iterations": int(i2), "residual": float(r2), "err_vs_pcg": err(d2, t2)}
+                except Exception as exc:  # recorded: the reference's own driver does not run on its own system
+                    out[name][key] = {"reference_raises": f"{type(exc).__name__}: {exc}"}
         print(name, out[name])
     with open(os.path.join(HERE, "pcg.json"), "w") as f:
         json.dump(out, f, indent=1)
