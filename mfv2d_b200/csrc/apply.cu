@@ -1283,10 +1283,17 @@ __device__ __forceinline__ double fused_coef(const double *__restrict__ slot, in
     return (slot[m.x] + slot[m.y]) - (slot[m.z] + slot[m.w]);
 }
 
+// trip-count-2 unrolling of the row loops pays from 10 quadrature points on (measured: +6 % at Q = 10, -3 % at Q = 8)
+template <int Q> struct FusedUnroll
+{
+    static constexpr int value = Q >= 10 ? 2 : 1;
+};
+
 template <int Q, int NT>
 __device__ __forceinline__ void fused_rows_a(const int4 d0, const int4 d1, double *__restrict__ slot, const double *__restrict__ smem, int edge_off,
                                              const int4 *__restrict__ gtab)
 {
+    constexpr int UNR = FusedUnroll<Q>::value;
     constexpr int LDQ = (Q + 1) & ~1;
     const double *B = smem + d0.z * edge_off;
     double acc[NT][Q];
@@ -1298,6 +1305,7 @@ __device__ __forceinline__ void fused_rows_a(const int4 d0, const int4 d1, doubl
             c[NT - 1] = fused_coef(slot, d1.x, d1.w, 0, gtab);
         row_mul_n<Q, NT>(acc, c, B);
     }
+#pragma unroll(UNR)
     for (int j = 1; j < d0.y; ++j)
     {
         double c[NT];
@@ -1322,6 +1330,7 @@ __device__ __forceinline__ void fused_rows_a(const int4 d0, const int4 d1, doubl
 template <int Q, int NT>
 __device__ __forceinline__ void fused_rows_c(const int4 d0, const int4 d1, double *__restrict__ slot, const double *__restrict__ smem, int edge_off)
 {
+    constexpr int UNR = FusedUnroll<Q>::value;
     constexpr int LDQ = (Q + 1) & ~1;
     double tr[NT][Q];
 #pragma unroll
@@ -1340,6 +1349,7 @@ __device__ __forceinline__ void fused_rows_c(const int4 d0, const int4 d1, doubl
     }
     const double *B = smem + d0.z * edge_off;
     double *dst0 = slot + d0.x, *dst1 = slot + (NT > 1 ? d1.x : d0.x);
+#pragma unroll(UNR)
     for (int j = 0; j < d0.y; ++j)
     {
         double res[NT];
@@ -1362,6 +1372,7 @@ __device__ __forceinline__ void fused_terms_b(const int *__restrict__ tb, double
                                               int edge_off, const double *__restrict__ pnts, const double *__restrict__ wgts,
                                               const ColumnGeo &g, const double *__restrict__ fp)
 {
+    constexpr int UNR = FusedUnroll<Q>::value;
     constexpr int LDQ = (Q + 1) & ~1;
     const int LDT = asm_ldq(Q);
     const int mode = tb[0];
@@ -1378,6 +1389,7 @@ __device__ __forceinline__ void fused_terms_b(const int *__restrict__ tb, double
             u0[n][a] = u1[n][a] = 0.0;
     {
         const double *A = smem + tb[4] * edge_off;
+#pragma unroll(UNR)
         for (int i = 0; i < nA0; ++i)
         {
             double c[NT];
@@ -1387,6 +1399,7 @@ __device__ __forceinline__ void fused_terms_b(const int *__restrict__ tb, double
             row_axpy_n<Q, NT>(u0, c, A + i * LDQ);
         }
         const double *A1 = smem + tb[6] * edge_off;
+#pragma unroll(UNR)
         for (int i = 0; i < nA1; ++i)
         {
             double c[NT];
@@ -1463,6 +1476,7 @@ __device__ __forceinline__ void fused_terms_b(const int *__restrict__ tb, double
     }
     {
         const double *A = smem + tb[8] * edge_off;
+#pragma unroll(UNR)
         for (int i = 0; i < nO0; ++i)
         {
             double res[NT];
@@ -1472,6 +1486,7 @@ __device__ __forceinline__ void fused_terms_b(const int *__restrict__ tb, double
                 tc[n][i * LDT] = res[n];
         }
         const double *A1 = smem + tb[10] * edge_off;
+#pragma unroll(UNR)
         for (int i = 0; i < nO1; ++i)
         {
             double res[NT];
