@@ -63,6 +63,7 @@ static void flatten(const mfv2d_plan *plan, const std::vector<BlockProgram> &blo
 }
 
 static int plan_lower_vector_fused(mfv2d_plan *plan);
+static int plan_lower_vector_dmma(mfv2d_plan *plan);
 
 int plan_lower_vector(mfv2d_plan *plan)
 {
@@ -85,7 +86,8 @@ int plan_lower_vector(mfv2d_plan *plan)
     MFV2D_TRY(mfv2d_cuda_malloc(plan->ctx, plan->vcoef.size() * sizeof(double), (void **)&plan->d_vcoef));
     MFV2D_TRY(mfv2d_cuda_upload(plan->ctx, plan->d_vprog, plan->vprog.data(), plan->vprog.size() * sizeof(int32_t)));
     MFV2D_TRY(mfv2d_cuda_upload(plan->ctx, plan->d_vcoef, plan->vcoef.data(), plan->vcoef.size() * sizeof(double)));
-    return plan_lower_vector_fused(plan);
+    MFV2D_TRY(plan_lower_vector_fused(plan));
+    return plan_lower_vector_dmma(plan);
 }
 
 struct ApplyArgs
@@ -924,21 +926,17 @@ static void pair_rows(std::vector<FusedRow> rows, std::vector<int32_t> &out)
     out.insert(out.end(), singles.begin(), singles.end());
 }
 
-static int plan_lower_vector_fused(mfv2d_plan *plan)
+struct FT // one term  coef * [E_L] * D * [E_R]  of a vector program
 {
-    plan->vector_fused = false;
-    const int p = plan->p, q = plan->q, np1 = p + 1, nf = plan->n_forms, N = plan->n_total;
-    if (plan->vector_needs_dense || q < 2 || q > 16)
-        return MFV2D_SUCCESS;
-    const int ldt = asm_ldq(q); // t rows: 16-byte row accesses of consecutive rows fall into distinct bank groups
-    auto ksize = [&](int k) { return k == TK_NODE ? np1 : p; };
-    struct FT
-    {
-        int rf, cf, ci, L, R;
-        TileOp op;
-        int fld, dk, tr;
-    };
-    std::vector<FT> fts;
+    int rf, cf, ci, L, R;
+    TileOp op;
+    int fld, dk, tr;
+};
+
+// all terms of the vector program in evaluation order; false if one of them does not have the tensor shape
+static bool collect_tensor_terms(const mfv2d_plan *plan, std::vector<FT> &fts)
+{
+    const int p = plan->p, nf = plan->n_forms;
     int ci = 0;
     for (int r = 0; r < nf; ++r)
         for (int c = 0; c < nf; ++c)
@@ -947,7 +945,7 @@ static int plan_lower_vector_fused(mfv2d_plan *plan)
             if (!bp.present)
                 continue;
             if (bp.identity)
-                return MFV2D_SUCCESS; // not a tensor term: the term-by-term kernel handles it
+                return false; // not a tensor term: the term-by-term kernel handles it
             for (const Term &t : bp.terms)
             {
                 FT ft{r, c, ci++, -1, -1, TileOp{}, 0, 0, 0};
@@ -956,14 +954,14 @@ static int plan_lower_vector_fused(mfv2d_plan *plan)
                     if (t.f[i].is_dense)
                     {
                         if (dense_at >= 0)
-                            return MFV2D_SUCCESS;
+                            return false;
                         dense_at = (int)i;
                     }
                 if (dense_at < 0 || dense_at > 1 || (int)t.f.size() - dense_at > 2)
-                    return MFV2D_SUCCESS;
+                    return false;
                 const Factor &d = t.f[dense_at];
                 if (d.inverse)
-                    return MFV2D_SUCCESS;
+                    return false;
                 if (dense_at == 1)
                     ft.R = t.f[0].inc_kind;
                 if ((int)t.f.size() == dense_at + 2)
@@ -975,7 +973,19 @@ static int plan_lower_vector_fused(mfv2d_plan *plan)
                 fts.push_back(ft);
             }
         }
-    if (fts.empty() || fts.size() > 64)
+    return !fts.empty() && fts.size() <= 64;
+}
+
+static int plan_lower_vector_fused(mfv2d_plan *plan)
+{
+    plan->vector_fused = false;
+    const int p = plan->p, q = plan->q, np1 = p + 1, nf = plan->n_forms, N = plan->n_total;
+    if (plan->vector_needs_dense || q < 2 || q > 16)
+        return MFV2D_SUCCESS;
+    const int ldt = asm_ldq(q); // t rows: 16-byte row accesses of consecutive rows fall into distinct bank groups
+    auto ksize = [&](int k) { return k == TK_NODE ? np1 : p; };
+    std::vector<FT> fts;
+    if (!collect_tensor_terms(plan, fts))
         return MFV2D_SUCCESS;
 
     // slot layout: corners[2][8] (double buffered) | x[N] | t rows of all terms.  The results of phase C overwrite
@@ -1680,6 +1690,466 @@ template <int Q> static int launch_fused_q(mfv2d_ctx *ctx, FusedArgs &fa, size_t
     return MFV2D_SUCCESS;
 }
 
+// =====================================================================================================
+// Tensor-core variant of the fused apply for q <= 8 and p <= 7 (every 1-D extent fits one 8 x 8 tile):
+// ONE WARP PER ELEMENT, no CTA barrier.  All four contractions of a term are chains of fp64
+// mma.sync.m8n8k4 (DMMA): the 1-D basis tables live in REGISTERS as A / B fragments for the whole kernel, the
+// intermediate 8 x 8 tiles never leave the accumulator fragments (two shuffles turn a D fragment into the
+// next B or A fragment), and every lane owns two fixed quadrature points of the element, so the metric and its
+// reciprocal are computed once per point and element.  On B200 a DMMA issues at exactly the DFMA flop rate
+// (profiles/micro/dmma_rate_b200.txt): what it buys here is issue slots (256 FMAs per instruction) and all the
+// shared-memory traffic of the table reads.
+//   fragments (PTX ISA, m8n8k4.f64), g = lane / 4, t = lane % 4:
+//     A[m = g][k = t]      B[k = t][n = g]      C/D[m = g][n = 2 t], [m = g][n = 2 t + 1]
+// =====================================================================================================
+enum
+{
+    DM_STRIDE = 24 // ints per term descriptor
+};
+
+static int plan_lower_vector_dmma(mfv2d_plan *plan)
+{
+    plan->vector_dmma = false;
+    const int p = plan->p, q = plan->q, np1 = p + 1, N = plan->n_total;
+    if (plan->vector_needs_dense || q < 2 || q > 8 || np1 > 8)
+        return MFV2D_SUCCESS;
+    std::vector<FT> fts;
+    if (!collect_tensor_terms(plan, fts))
+        return MFV2D_SUCCESS;
+    auto ksize = [&](int k) { return k == TK_NODE ? np1 : p; };
+    // per-warp staging (doubles): x[2][Nx] (double buffered, each with a zero cell at N) | corners[2][8] | y[N] |
+    // output vector of the current term.  Gather addresses are relative to the current x buffer (right incidence)
+    // or to the strip (left incidence; the zero cell of buffer 0 serves as its zero)
+    const int zero_cell = N;
+    const int Nx = (N + 2) & ~1;
+    const int dump_cell = 2 * Nx + 16; // receives the stores of the tile's padding lanes
+    const int off_ys = 2 * Nx + 18;
+    const int off_outv = off_ys + ((N + 1) & ~1);
+    int max_out = 0;
+    std::vector<int32_t> terms, gtab, dtab, ltab, otab;
+    for (const FT &ft : fts)
+    {
+        const TileOp &op = ft.op;
+        int ni = 0, no = 0;
+        for (int k = 0; k < op.n_in; ++k)
+            ni += ksize(op.in[k].kA) * ksize(op.in[k].kB);
+        for (int k = 0; k < op.n_out; ++k)
+            no += ksize(op.out[k].kA) * ksize(op.out[k].kB);
+        max_out = no > max_out ? no : max_out;
+        const int c0 = plan->form_offsets[ft.cf], r0 = plan->form_offsets[ft.rf];
+        const int n_rows_form = plan->form_offsets[ft.rf + 1] - r0;
+        if (ft.R >= 0 ? inc_rows_of(ft.R, p) != ni : plan->form_offsets[ft.cf + 1] - c0 != ni)
+            return MFV2D_SUCCESS;
+        if (ft.L >= 0 ? inc_rows_of(ft.L, p) != n_rows_form : no != n_rows_form)
+            return MFV2D_SUCCESS;
+        // signed sum of up to four cells as (p0 + p1) - (n0 + n1); the zero cell where there is no entry
+        auto split = [&](const int32_t *ev, int base, std::vector<int32_t> &out) -> bool {
+            int32_t e4[4] = {zero_cell, zero_cell, zero_cell, zero_cell};
+            int np_ = 0, nn = 0;
+            for (int z = 0; z < 4 && ev[z] != 0; ++z)
+            {
+                const int a = base + (ev[z] < 0 ? -ev[z] : ev[z]) - 1;
+                if (ev[z] > 0 ? np_ == 2 : nn == 2)
+                    return false;
+                if (ev[z] > 0)
+                    e4[np_++] = a;
+                else
+                    e4[2 + nn++] = a;
+            }
+            out.insert(out.end(), e4, e4 + 4);
+            return true;
+        };
+        int lbase = -1;
+        if (ft.L >= 0)
+        {
+            lbase = (int)ltab.size() / 4;
+            for (int k = 0; k < n_rows_form; ++k)
+                if (!split(plan->basis->h_inc.data() + 4 * (size_t)(plan->basis->inc_off[ft.L] + k), off_outv, ltab))
+                    return MFV2D_SUCCESS;
+        }
+        // per-lane addresses (g = lane / 4, t = lane % 4): the coefficient c[i = g][j = 2 t + ks] of every input
+        // component as (p0 + p1) - (n0 + n1) in the x buffer (zero cell where there is nothing), and the two cells
+        // out[i = g][j = 2 t + s] of every output component in the strip (dump cell for the padding of the tile)
+        // gathered terms: int4 records, [component][k-step][lane]; direct terms: int2 {address of step 0, of step 1}, [component][lane]
+        const int lbase_in = ft.R >= 0 ? (int)gtab.size() / 4 : (int)dtab.size() / 2;
+        for (int k = 0; k < 2; ++k)
+        {
+            const int nA = k < op.n_in ? ksize(op.in[k].kA) : 0, nB = k < op.n_in ? ksize(op.in[k].kB) : 0;
+            if (ft.R >= 0)
+            {
+                for (int ks = 0; ks < 2; ++ks)
+                    for (int lane = 0; lane < 32; ++lane)
+                    {
+                        const int g = lane >> 2, j = 2 * (lane & 3) + ks;
+                        if (g < nA && j < nB)
+                        {
+                            if (!split(plan->basis->h_inc.data() + 4 * (size_t)(plan->basis->inc_off[ft.R] + op.in[k].off + g * nB + j), c0, gtab))
+                                return MFV2D_SUCCESS;
+                        }
+                        else
+                            gtab.insert(gtab.end(), {zero_cell, zero_cell, zero_cell, zero_cell});
+                    }
+            }
+            else
+                for (int lane = 0; lane < 32; ++lane)
+                    for (int ks = 0; ks < 2; ++ks)
+                    {
+                        const int g = lane >> 2, j = 2 * (lane & 3) + ks;
+                        dtab.push_back(g < nA && j < nB ? c0 + op.in[k].off + g * nB + j : zero_cell);
+                    }
+        }
+        const int lbase_out = (int)otab.size() / 2;
+        for (int k = 0; k < 2; ++k)
+            for (int lane = 0; lane < 32; ++lane)
+            {
+                const int g = lane >> 2, t = lane & 3;
+                const int nA = k < op.n_out ? ksize(op.out[k].kA) : 0, nB = k < op.n_out ? ksize(op.out[k].kB) : 0;
+                for (int sfx = 0; sfx < 2; ++sfx)
+                {
+                    const int j = 2 * t + sfx;
+                    if (g < nA && j < nB)
+                        otab.push_back((ft.L >= 0 ? off_outv : off_ys + r0) + op.out[k].off + g * nB + j);
+                    else
+                        otab.push_back(dump_cell);
+                }
+            }
+        const int32_t d[DM_STRIDE] = {op.mode, ft.fld, ft.ci, lbase_in, lbase_out, ft.R >= 0 ? 1 : 0, lbase, n_rows_form, off_ys + r0, 0, 0, 0,
+                                      0,       0,      0,     0,        0,         0,                0,     0,           0,           0, 0, 0};
+        terms.insert(terms.end(), d, d + DM_STRIDE);
+    }
+    std::vector<int32_t> blob;
+    auto put = [&](const std::vector<int32_t> &v) {
+        while (blob.size() & 3)
+            blob.push_back(0);
+        const int off = (int)blob.size();
+        blob.insert(blob.end(), v.begin(), v.end());
+        return off;
+    };
+    plan->dm_terms = (int)fts.size();
+    plan->dm_off_terms = put(terms);
+    plan->dm_off_gtab = put(gtab);
+    plan->dm_off_ltab = put(ltab);
+    plan->dm_off_otab = put(otab);
+    plan->dm_off_dtab = put(dtab);
+    while (blob.size() & 3)
+        blob.push_back(0);
+    plan->dm_blob_ints = (int)blob.size();
+    plan->dm_off_ys = off_ys;
+    plan->dm_off_outv = off_outv;
+    plan->dm_warp_doubles = (off_outv + max_out + 1) & ~1;
+    MFV2D_TRY(mfv2d_cuda_malloc(plan->ctx, blob.size() * sizeof(int32_t), (void **)&plan->d_dmblob));
+    MFV2D_TRY(mfv2d_cuda_upload(plan->ctx, plan->d_dmblob, blob.data(), blob.size() * sizeof(int32_t)));
+    plan->vector_dmma = true;
+    return MFV2D_SUCCESS;
+}
+
+#ifndef MFV2D_EMU
+struct DmmaArgs
+{
+    ApplyArgs a;
+    const int32_t *blob;
+    int n_terms, off_terms, off_gtab, off_ltab, off_otab, off_dtab, blob_ints;
+    int warp_doubles, off_ys, off_outv, n_coef;
+};
+
+#define DMMA_THREADS 256
+
+// D (8 x 8, fragment d0 / d1) += A (8 x 4, fragment a) * B (4 x 8, fragment b)
+__device__ __forceinline__ void dmma884(double &d0, double &d1, double a, double b)
+{
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n" : "+d"(d0), "+d"(d1) : "d"(a), "d"(b));
+}
+
+// Everything is kept TRANSPOSED with the xi index b as the row (m = g) of every tile, and the contraction index of
+// k-step ks is k = 2 t + ks: a D fragment X[g][2 t + s] then IS the A fragment of the next product (step ks = s), no
+// data movement; only the last product (which contracts b) needs the tile transposed through shuffles.
+struct DmmaLane
+{
+    int g, t, src0; // src0 = 8 t + g / 2: source lane of the transposing shuffle (k-step 0)
+    double fa[2][2]; // fa[kind][ks] = tab_kind[basis 2 t + ks][point g]
+    double fb[2][2]; // fb[kind][ks] = tab_kind[basis g][point 2 t + ks]
+};
+
+// values at the lane's two points (a = 2 t + s, b = g) of one input component (kA along eta, kB along xi);
+// `adr` = the lane's two address records {p0, p1, n0, n1} (k-steps 0 and 1) of the coefficient c[i = g][j = 2 t + ks]
+template <int KA, int KB>
+__device__ __forceinline__ void dmma_in(const DmmaLane &L, const double *__restrict__ xs, const int4 *__restrict__ gadr, const int2 *__restrict__ dadr,
+                                        bool gathered, double &u0, double &u1)
+{
+    // T^T[b][i] = sum_j B_j(b) c[i][j]:  A = B-table (m = b, k = j), B = c (k = j, n = i = g)
+    double c0, c1;
+    if (gathered)
+    {
+        const int4 q0 = gadr[0], q1 = gadr[32];
+        c0 = (xs[q0.x] + xs[q0.y]) - (xs[q0.z] + xs[q0.w]);
+        c1 = (xs[q1.x] + xs[q1.y]) - (xs[q1.z] + xs[q1.w]);
+    }
+    else
+    {
+        const int2 q = dadr[0];
+        c0 = xs[q.x];
+        c1 = xs[q.y];
+    }
+    double t0 = 0.0, t1 = 0.0;
+    dmma884(t0, t1, L.fa[KB][0], c0);
+    dmma884(t0, t1, L.fa[KB][1], c1);
+    // U^T[b][a] += sum_i T^T[b][i] A_i(a):  A = T^T straight from the D fragment, B = A-table (k = i, n = a = g)
+    dmma884(u0, u1, t0, L.fa[KA][0]);
+    dmma884(u0, u1, t1, L.fa[KA][1]);
+}
+
+// out[i][j] of one output component from the weighted values at the points; o0 / o1 = out[g][2 t], out[g][2 t + 1]
+template <int KA, int KB> __device__ __forceinline__ void dmma_out(const DmmaLane &L, double u0, double u1, double &o0, double &o1)
+{
+    // T'^T[b][i] = sum_a U'^T[b][a] A_i(a):  A = U'^T from the D fragment, B = A-table (k = a, n = i = g)
+    double t0 = 0.0, t1 = 0.0;
+    dmma884(t0, t1, u0, L.fb[KA][0]);
+    dmma884(t0, t1, u1, L.fb[KA][1]);
+    // out[i][j] = sum_b T'^T[b][i] B_j(b):  A[m = i = g][k = b = 2 t + ks] = T'^T[2 t + ks][g] lives in lane
+    // 4 (2 t + ks) + g / 2, register g % 2;  B = B-table (k = b, n = j = g)
+    o0 = o1 = 0.0;
+#pragma unroll
+    for (int ks = 0; ks < 2; ++ks)
+    {
+        const int src = L.src0 + 4 * ks;
+        const double v0 = __shfl_sync(0xffffffffu, t0, src), v1 = __shfl_sync(0xffffffffu, t1, src);
+        dmma884(o0, o1, (L.g & 1) ? v1 : v0, L.fb[KB][ks]);
+    }
+}
+
+__global__ void __launch_bounds__(DMMA_THREADS, 3) element_vector_dmma_kernel(const DmmaArgs da)
+{
+    MFV2D_DYN_SMEM(double, smem);
+    const ApplyArgs &args = da.a;
+    const int p = args.p, Q = args.q, np1 = p + 1, N = args.n_total, nh = p * np1;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+    DmmaLane L;
+    L.g = lane >> 2;
+    L.t = lane & 3;
+    L.src0 = 8 * L.t + (L.g >> 1);
+    const int g = L.g, t = L.t;
+    // CTA-shared: coefficients | descriptor blob ; then one staging strip per warp: x[2][Nx] | corners[2][8] | y | term output
+    double *coef = smem;
+    int *blob = reinterpret_cast<int *>(coef + ((da.n_coef + 1) & ~1));
+    double *wbuf = reinterpret_cast<double *>(blob + da.blob_ints) + (size_t)warp * da.warp_doubles;
+    for (int i = threadIdx.x; i < da.n_coef; i += blockDim.x)
+        coef[i] = args.coef[i];
+    for (int i = threadIdx.x; i < da.blob_ints; i += blockDim.x)
+        blob[i] = da.blob[i];
+    const int *terms = blob + da.off_terms;
+    const int4 *gtab = reinterpret_cast<const int4 *>(blob + da.off_gtab);
+    const int4 *ltab = reinterpret_cast<const int4 *>(blob + da.off_ltab);
+    const int2 *otab = reinterpret_cast<const int2 *>(blob + da.off_otab);
+    const int2 *dtab = reinterpret_cast<const int2 *>(blob + da.off_dtab);
+#pragma unroll
+    for (int k = 0; k < 2; ++k)
+    {
+        const double *tab = args.tab + (k ? np1 * Q : 0);
+        const int nk = k ? p : np1;
+#pragma unroll
+        for (int ks = 0; ks < 2; ++ks)
+        {
+            L.fa[k][ks] = (2 * t + ks < nk && g < Q) ? tab[(2 * t + ks) * Q + g] : 0.0;
+            L.fb[k][ks] = (g < nk && 2 * t + ks < Q) ? tab[g * Q + 2 * t + ks] : 0.0;
+        }
+    }
+    const double *pnts = args.tab + (2 * p + 1) * Q, *wgts = pnts + Q;
+    // the lane's two quadrature points: (eta_{2t+s}, xi_g); padded points carry weight 0
+    const bool vb = g < Q;
+    const double xi = vb ? pnts[g] : 0.0, wb = vb ? wgts[g] : 0.0;
+    double eta[2], wq[2];
+#pragma unroll
+    for (int s = 0; s < 2; ++s)
+    {
+        const bool va = 2 * t + s < Q;
+        eta[s] = va ? pnts[2 * t + s] : 0.0;
+        wq[s] = va ? wgts[2 * t + s] * wb : 0.0;
+    }
+    const int Nx = (N + 2) & ~1, off_cs = 2 * Nx;
+    if (lane == 0)
+        wbuf[N] = wbuf[Nx + N] = 0.0; // zero cells of both x buffers
+    __syncthreads();
+    double *ys = wbuf + da.off_ys, *outv = wbuf + da.off_outv;
+    const unsigned long long total_warps = (unsigned long long)gridDim.x * nwarps;
+    auto prefetch = [&](unsigned long long e, int buf) {
+        if (e >= args.n_elem)
+            return;
+        for (int i = lane; i < N; i += 32)
+            cp_async8(wbuf + buf * Nx + i, args.x + e * N + i);
+        if (lane < 8)
+            cp_async8(wbuf + off_cs + buf * 8 + lane, args.corners + e * 8 + lane);
+    };
+    unsigned long long e = (unsigned long long)blockIdx.x * nwarps + warp;
+    prefetch(e, 0);
+    for (int buf = 0; e < args.n_elem; e += total_warps, buf ^= 1)
+    {
+        cp_async_wait_all();
+        __syncwarp();
+        prefetch(e + total_warps, buf ^ 1);
+        const double *xs = wbuf + buf * Nx, *cs = wbuf + off_cs + buf * 8;
+        for (int i = lane; i < N; i += 32)
+            ys[i] = 0.0;
+        const double x0 = cs[0], y0 = cs[1], x1 = cs[2], y1 = cs[3], x2 = cs[4], y2 = cs[5], x3 = cs[6], y3 = cs[7];
+        const double j10 = 0.25 * ((x3 - x0) * (1 - xi) + (x2 - x1) * (1 + xi));
+        const double j11 = 0.25 * ((y3 - y0) * (1 - xi) + (y2 - y1) * (1 + xi));
+        double j00[2], j01[2], det[2], wod[2];
+#pragma unroll
+        for (int s = 0; s < 2; ++s)
+        {
+            j00[s] = 0.25 * ((x1 - x0) * (1 - eta[s]) + (x2 - x3) * (1 + eta[s]));
+            j01[s] = 0.25 * ((y1 - y0) * (1 - eta[s]) + (y2 - y3) * (1 + eta[s]));
+            det[s] = j00[s] * j11 - j10 * j01[s];
+            wod[s] = wq[s] * fast_rcp(det[s]);
+        }
+        __syncwarp();
+        for (int ti = 0; ti < da.n_terms; ++ti)
+        {
+            const int *d = terms + ti * DM_STRIDE;
+            const int mode = d[0], lbase = d[6];
+            const bool gathered = d[5] != 0, direct = lbase < 0;
+            const double cf = coef[d[2]];
+            const int4 *ga = gtab + d[3] + lane;  // + 64 for the second component
+            const int2 *dadr = dtab + d[3] + lane; // + 32 for the second component
+            double uh[2] = {0.0, 0.0}, uv[2] = {0.0, 0.0}, o0, o1;
+            // mode 0: M0   1: M2   2: M1   3: node x edge   4: its transpose   5: edge x surf   6: its transpose
+            if (mode == 0 || mode == 4)
+                dmma_in<0, 0>(L, xs, ga, dadr, gathered, uh[0], uh[1]);
+            else if (mode == 1 || mode == 5)
+                dmma_in<1, 1>(L, xs, ga, dadr, gathered, uh[0], uh[1]);
+            else
+            {
+                dmma_in<0, 1>(L, xs, ga, dadr, gathered, uh[0], uh[1]);
+                dmma_in<1, 0>(L, xs, ga + 64, dadr + 32, gathered, uv[0], uv[1]);
+            }
+#pragma unroll
+            for (int s = 0; s < 2; ++s)
+            {
+                const double a0 = uh[s], a1 = uv[s];
+                if (mode == 0)
+                    uh[s] = a0 * det[s] * wq[s];
+                else if (mode == 1)
+                    uh[s] = a0 * wod[s];
+                else if (mode == 2)
+                {
+                    const double khh = (j11 * j11 + j10 * j10) * wod[s], kvv = (j00[s] * j00[s] + j01[s] * j01[s]) * wod[s],
+                                 khv = (j01[s] * j11 + j00[s] * j10) * wod[s];
+                    uh[s] = khh * a0 + khv * a1;
+                    uv[s] = khv * a0 + kvv * a1;
+                }
+                else
+                {
+                    const bool ok = vb && 2 * t + s < Q;
+                    const double *fp = args.fields[d[1]] + ((e * Q + 2 * t + s) * (unsigned long long)Q + g) * 2;
+                    const double fx = ok ? fp[0] : 0.0, fy = ok ? fp[1] : 0.0;
+                    double kh, kv;
+                    if (mode <= 4)
+                    {
+                        kh = (fx * j11 - fy * j10) * wq[s];
+                        kv = -(fy * j00[s] - fx * j01[s]) * wq[s];
+                    }
+                    else
+                    {
+                        kh = -(fx * j10 + fy * j11) * wod[s];
+                        kv = -(fx * j00[s] + fy * j01[s]) * wod[s];
+                    }
+                    if (mode == 3 || mode == 6)
+                        uh[s] = kh * a0 + kv * a1;
+                    else
+                    {
+                        uh[s] = kh * a0;
+                        uv[s] = kv * a0;
+                    }
+                }
+            }
+            const int2 *oa = otab + d[4] + lane; // + 32 for the second component
+            const int2 w0 = oa[0];
+            if (mode == 0 || mode == 3)
+                dmma_out<0, 0>(L, uh[0], uh[1], o0, o1);
+            else if (mode == 1 || mode == 6)
+                dmma_out<1, 1>(L, uh[0], uh[1], o0, o1);
+            else
+                dmma_out<0, 1>(L, uh[0], uh[1], o0, o1);
+            if (direct)
+            {
+                wbuf[w0.x] = fma(cf, o0, wbuf[w0.x]);
+                wbuf[w0.y] = fma(cf, o1, wbuf[w0.y]);
+            }
+            else
+            {
+                wbuf[w0.x] = o0;
+                wbuf[w0.y] = o1;
+            }
+            if (mode == 2 || mode == 4 || mode == 5)
+            {
+                const int2 w1 = oa[32];
+                dmma_out<1, 0>(L, uv[0], uv[1], o0, o1);
+                if (direct)
+                {
+                    wbuf[w1.x] = fma(cf, o0, wbuf[w1.x]);
+                    wbuf[w1.y] = fma(cf, o1, wbuf[w1.y]);
+                }
+                else
+                {
+                    wbuf[w1.x] = o0;
+                    wbuf[w1.y] = o1;
+                }
+            }
+            __syncwarp();
+            if (!direct)
+            {
+                const int n_rows = d[7];
+                double *yr = wbuf + d[8];
+                for (int k = lane; k < n_rows; k += 32)
+                {
+                    const int4 q4 = ltab[lbase + k];
+                    const double v = (wbuf[q4.x] + wbuf[q4.y]) - (wbuf[q4.z] + wbuf[q4.w]);
+                    yr[k] = fma(cf, v, yr[k]);
+                }
+                __syncwarp();
+            }
+        }
+        for (int i = lane; i < N; i += 32)
+            args.y[e * N + i] = ys[i];
+        __syncwarp();
+    }
+}
+
+static int launch_dmma(mfv2d_ctx *ctx, const mfv2d_plan *plan, const ApplyArgs &a, size_t n_elem)
+{
+    DmmaArgs da{};
+    da.a = a;
+    da.blob = plan->d_dmblob;
+    da.n_terms = plan->dm_terms;
+    da.off_terms = plan->dm_off_terms;
+    da.off_gtab = plan->dm_off_gtab;
+    da.off_ltab = plan->dm_off_ltab;
+    da.off_otab = plan->dm_off_otab;
+    da.off_dtab = plan->dm_off_dtab;
+    da.blob_ints = plan->dm_blob_ints;
+    da.warp_doubles = plan->dm_warp_doubles;
+    da.off_ys = plan->dm_off_ys;
+    da.off_outv = plan->dm_off_outv;
+    da.n_coef = plan->mcoef_off ? plan->mcoef_off : (int)plan->vcoef.size();
+    const int nwarps = DMMA_THREADS / 32;
+    const size_t smem = (((size_t)da.n_coef + 1) & ~(size_t)1) * 8 + (size_t)da.blob_ints * 4 + (size_t)nwarps * da.warp_doubles * 8;
+    if (smem > ctx->smem_optin)
+        return -1;
+    MFV2D_CUDA_CHECK(ctx, cudaFuncSetAttribute(element_vector_dmma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int per_sm = 1;
+    MFV2D_CUDA_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, element_vector_dmma_kernel, DMMA_THREADS, smem));
+    if (per_sm < 1)
+        per_sm = 1;
+    unsigned long long grid = (unsigned long long)ctx->sm_count * per_sm;
+    const unsigned long long need = (n_elem + nwarps - 1) / nwarps;
+    if (grid > need)
+        grid = need;
+    MFV2D_LAUNCH(element_vector_dmma_kernel, (unsigned)grid, DMMA_THREADS, smem, ctx->stream, da);
+    ctx->launches++;
+    MFV2D_CUDA_CHECK(ctx, cudaGetLastError());
+    return MFV2D_SUCCESS;
+}
+#endif // MFV2D_EMU
+
 static int launch_apply(const mfv2d_plan *plan, const mfv2d_elements *e, const double *const *fields, const double *d_x,
                         double *d_y, int column_mode)
 {
@@ -1716,6 +2186,18 @@ static int launch_apply(const mfv2d_plan *plan, const mfv2d_elements *e, const d
         const int nmax = 2 * p * np1;
         doubles += ((q2 + 1) & ~1) + q * ldT + 4 + (size_t)nmax * nmax + 8;
     }
+#ifndef MFV2D_EMU
+    if (!column_mode && plan->vector_dmma && e->n > 0)
+    {
+        const char *env = getenv("MFV2D_APPLY_DMMA");
+        if (!(env && env[0] == '0'))
+        {
+            const int r = launch_dmma(ctx, plan, a, e->n);
+            if (r >= 0)
+                return r;
+        }
+    }
+#endif
     if (!column_mode && plan->vector_fused && e->n > 0)
     {
         FusedArgs fa{};

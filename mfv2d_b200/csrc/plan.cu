@@ -1126,6 +1126,8 @@ void mfv2d_cuda_plan_destroy(mfv2d_plan *plan)
         mfv2d_cuda_free(plan->ctx, plan->d_vcoef);
     if (plan->d_fblob)
         mfv2d_cuda_free(plan->ctx, plan->d_fblob);
+    if (plan->d_dmblob)
+        mfv2d_cuda_free(plan->ctx, plan->d_dmblob);
     delete plan;
 }
 

@@ -233,6 +233,12 @@ struct mfv2d_plan
     FusedVecInfo fv{};
     std::vector<int32_t> fblob;
     int32_t *d_fblob = nullptr;
+
+    // tensor-core (fp64 DMMA) vector path for q <= 8, p <= 7: one warp per element (apply.cu)
+    bool vector_dmma = false;
+    int dm_terms = 0, dm_off_terms = 0, dm_off_gtab = 0, dm_off_ltab = 0, dm_off_otab = 0, dm_off_dtab = 0, dm_blob_ints = 0;
+    int dm_warp_doubles = 0, dm_off_ys = 0, dm_off_outv = 0; // per-warp staging: x | zero cell | y | term output
+    int32_t *d_dmblob = nullptr;
 };
 
 // padded row length of the quadrature-indexed tables: even, and half of it odd, so that 16-byte
