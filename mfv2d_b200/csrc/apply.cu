@@ -1825,6 +1825,9 @@ static int plan_lower_vector_dmma(mfv2d_plan *plan)
         blob.insert(blob.end(), v.begin(), v.end());
         return off;
     };
+    for (std::vector<int32_t> *v : {&gtab, &dtab, &ltab, &otab}) // the kernel addresses shared memory by byte offsets
+        for (int32_t &a : *v)
+            a *= 8;
     plan->dm_terms = (int)fts.size();
     plan->dm_off_terms = put(terms);
     plan->dm_off_gtab = put(gtab);
@@ -1854,6 +1857,15 @@ struct DmmaArgs
 
 #define DMMA_THREADS 256
 
+// shared-memory accesses through 32-bit window addresses (the address tables hold byte offsets)
+__device__ __forceinline__ double lds64(unsigned a)
+{
+    double v;
+    asm volatile("ld.shared.f64 %0, [%1];\n" : "=d"(v) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ void sts64(unsigned a, double v) { asm volatile("st.shared.f64 [%0], %1;\n" ::"r"(a), "d"(v) : "memory"); }
+
 // D (8 x 8, fragment d0 / d1) += A (8 x 4, fragment a) * B (4 x 8, fragment b)
 __device__ __forceinline__ void dmma884(double &d0, double &d1, double a, double b)
 {
@@ -1873,7 +1885,7 @@ struct DmmaLane
 // values at the lane's two points (a = 2 t + s, b = g) of one input component (kA along eta, kB along xi);
 // `adr` = the lane's two address records {p0, p1, n0, n1} (k-steps 0 and 1) of the coefficient c[i = g][j = 2 t + ks]
 template <int KA, int KB>
-__device__ __forceinline__ void dmma_in(const DmmaLane &L, const double *__restrict__ xs, const int4 *__restrict__ gadr, const int2 *__restrict__ dadr,
+__device__ __forceinline__ void dmma_in(const DmmaLane &L, unsigned xs, const int4 *__restrict__ gadr, const int2 *__restrict__ dadr,
                                         bool gathered, double &u0, double &u1)
 {
     // T^T[b][i] = sum_j B_j(b) c[i][j]:  A = B-table (m = b, k = j), B = c (k = j, n = i = g)
@@ -1881,14 +1893,14 @@ __device__ __forceinline__ void dmma_in(const DmmaLane &L, const double *__restr
     if (gathered)
     {
         const int4 q0 = gadr[0], q1 = gadr[32];
-        c0 = (xs[q0.x] + xs[q0.y]) - (xs[q0.z] + xs[q0.w]);
-        c1 = (xs[q1.x] + xs[q1.y]) - (xs[q1.z] + xs[q1.w]);
+        c0 = (lds64(xs + q0.x) + lds64(xs + q0.y)) - (lds64(xs + q0.z) + lds64(xs + q0.w));
+        c1 = (lds64(xs + q1.x) + lds64(xs + q1.y)) - (lds64(xs + q1.z) + lds64(xs + q1.w));
     }
     else
     {
         const int2 q = dadr[0];
-        c0 = xs[q.x];
-        c1 = xs[q.y];
+        c0 = lds64(xs + q.x);
+        c1 = lds64(xs + q.y);
     }
     double t0 = 0.0, t1 = 0.0;
     dmma884(t0, t1, L.fa[KB][0], c0);
@@ -1969,7 +1981,8 @@ __global__ void __launch_bounds__(DMMA_THREADS, 3) element_vector_dmma_kernel(co
     if (lane == 0)
         wbuf[N] = wbuf[Nx + N] = 0.0; // zero cells of both x buffers
     __syncthreads();
-    double *ys = wbuf + da.off_ys, *outv = wbuf + da.off_outv;
+    double *ys = wbuf + da.off_ys;
+    const unsigned wsm = (unsigned)__cvta_generic_to_shared(wbuf);
     const unsigned long long total_warps = (unsigned long long)gridDim.x * nwarps;
     auto prefetch = [&](unsigned long long e, int buf) {
         if (e >= args.n_elem)
@@ -1986,7 +1999,8 @@ __global__ void __launch_bounds__(DMMA_THREADS, 3) element_vector_dmma_kernel(co
         cp_async_wait_all();
         __syncwarp();
         prefetch(e + total_warps, buf ^ 1);
-        const double *xs = wbuf + buf * Nx, *cs = wbuf + off_cs + buf * 8;
+        const double *cs = wbuf + off_cs + buf * 8;
+        const unsigned xs = wsm + (unsigned)(buf * Nx) * 8u;
         for (int i = lane; i < N; i += 32)
             ys[i] = 0.0;
         const double x0 = cs[0], y0 = cs[1], x1 = cs[2], y1 = cs[3], x2 = cs[4], y2 = cs[5], x3 = cs[6], y3 = cs[7];
@@ -2071,13 +2085,13 @@ __global__ void __launch_bounds__(DMMA_THREADS, 3) element_vector_dmma_kernel(co
                 dmma_out<0, 1>(L, uh[0], uh[1], o0, o1);
             if (direct)
             {
-                wbuf[w0.x] = fma(cf, o0, wbuf[w0.x]);
-                wbuf[w0.y] = fma(cf, o1, wbuf[w0.y]);
+                sts64(wsm + w0.x, fma(cf, o0, lds64(wsm + w0.x)));
+                sts64(wsm + w0.y, fma(cf, o1, lds64(wsm + w0.y)));
             }
             else
             {
-                wbuf[w0.x] = o0;
-                wbuf[w0.y] = o1;
+                sts64(wsm + w0.x, o0);
+                sts64(wsm + w0.y, o1);
             }
             if (mode == 2 || mode == 4 || mode == 5)
             {
@@ -2085,13 +2099,13 @@ __global__ void __launch_bounds__(DMMA_THREADS, 3) element_vector_dmma_kernel(co
                 dmma_out<1, 0>(L, uv[0], uv[1], o0, o1);
                 if (direct)
                 {
-                    wbuf[w1.x] = fma(cf, o0, wbuf[w1.x]);
-                    wbuf[w1.y] = fma(cf, o1, wbuf[w1.y]);
+                    sts64(wsm + w1.x, fma(cf, o0, lds64(wsm + w1.x)));
+                    sts64(wsm + w1.y, fma(cf, o1, lds64(wsm + w1.y)));
                 }
                 else
                 {
-                    wbuf[w1.x] = o0;
-                    wbuf[w1.y] = o1;
+                    sts64(wsm + w1.x, o0);
+                    sts64(wsm + w1.y, o1);
                 }
             }
             __syncwarp();
@@ -2102,7 +2116,7 @@ __global__ void __launch_bounds__(DMMA_THREADS, 3) element_vector_dmma_kernel(co
                 for (int k = lane; k < n_rows; k += 32)
                 {
                     const int4 q4 = ltab[lbase + k];
-                    const double v = (wbuf[q4.x] + wbuf[q4.y]) - (wbuf[q4.z] + wbuf[q4.w]);
+                    const double v = (lds64(wsm + q4.x) + lds64(wsm + q4.y)) - (lds64(wsm + q4.z) + lds64(wsm + q4.w));
                     yr[k] = fma(cf, v, yr[k]);
                 }
                 __syncwarp();
