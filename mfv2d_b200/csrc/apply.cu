@@ -443,16 +443,10 @@ __global__ void __launch_bounds__(APPLY_THREADS) element_vector_kernel(const App
 }
 
 // =====================================================================================================
-// Register-tiled variant (the fast path).  A CTA works on `epb` elements per pass; every dense factor
-// (mass / interior product) of a program is applied by sum factorisation in three barrier-separated
-// phases whose threads keep a whole quadrature row or column in REGISTERS (template parameter Q) and read
-// the basis tables as warp-uniform 16-byte broadcasts:
-//   A  thread (e, i):  t[e][i][:] = sum_j c[e][i,j] B_j[:]                    (interpolate along xi)
-//   B  thread (e, b):  u[:] = sum_i A_i[:] t[e][i][b]  ->  metric weights at the points (:, b), Jacobian
-//                      from the corners  ->  t'[e][i][b] = A'_i[:] . g[:]     (eta interpolation, scaling,
-//                      eta projection; the values at the quadrature points never leave the registers)
-//   C  thread (e, i):  out[e][i,j] = B'_j[:] . t'[e][i][:]                     (project along xi)
-// Incidences are signed gathers between the ping-pong vectors.  Programs with an inverse mass and the
+// Tensor terms.  A dense factor (mass / interior product) acts on a form through its tensor components: the
+// coefficient (i, j) of a component multiplies A_i(eta) B_j(xi) with A, B the nodal or the edge 1-D basis.  The
+// fast kernels below (fused DFMA kernel, tensor-core kernel) are built on this description; programs that do not
+// have the tensor shape (inverse mass inside a vector, identity blocks, two dense factors in one term) and the
 // column mode use the CTA-per-element kernel above.
 // =====================================================================================================
 #define APPLYT_THREADS 256
@@ -542,337 +536,6 @@ __host__ __device__ __forceinline__ TileOp tile_op(int type, int fa, int fc, int
     return op;
 }
 
-struct ApplyTArgs
-{
-    ApplyArgs a;
-    int prog_len, n_coef, inc_rows; // sizes of the program / coefficient / incidence tables staged in shared memory
-    int epb;                        // elements per pass
-    int slot_doubles;               // private doubles per element slot
-};
-
-template <int Q> __device__ __forceinline__ void row_axpy(double (&acc)[Q], double c, const double *__restrict__ row)
-{
-#pragma unroll
-    for (int b = 0; b + 1 < Q; b += 2)
-    {
-        const double2 v = *reinterpret_cast<const double2 *>(row + b);
-        acc[b] = fma(c, v.x, acc[b]);
-        acc[b + 1] = fma(c, v.y, acc[b + 1]);
-    }
-    if (Q & 1)
-        acc[Q - 1] = fma(c, row[Q - 1], acc[Q - 1]);
-}
-
-template <int Q> __device__ __forceinline__ double row_dot(const double *__restrict__ row, const double (&g)[Q])
-{
-    double a0 = 0.0, a1 = 0.0;
-#pragma unroll
-    for (int b = 0; b + 1 < Q; b += 2)
-    {
-        const double2 v = *reinterpret_cast<const double2 *>(row + b);
-        a0 = fma(v.x, g[b], a0);
-        a1 = fma(v.y, g[b + 1], a1);
-    }
-    if (Q & 1)
-        a0 = fma(row[Q - 1], g[Q - 1], a0);
-    return a0 + a1;
-}
-
-template <int Q> __global__ void __launch_bounds__(APPLYT_THREADS, 2) element_vector_tile_kernel(const ApplyTArgs ta)
-{
-    MFV2D_DYN_SMEM(double, smem);
-    constexpr int LDQ = (Q + 1) & ~1;
-    const ApplyArgs &args = ta.a;
-    const int p = args.p, np1 = p + 1, nh = p * (p + 1);
-    const int N = args.n_total;
-    // CTA-shared: padded tables | points, weights | coefficients | program | incidence maps | element slots
-    const int edge_off = np1 * LDQ; // node rows first, then the edge rows (LDQ doubles each): table k starts at k * edge_off
-    double *pnts = smem + (2 * p + 1) * LDQ, *wgts = pnts + LDQ;
-    double *coef = wgts + LDQ;
-    int *prog = reinterpret_cast<int *>(coef + ((ta.n_coef + 1) & ~1));
-    int4 *inc = reinterpret_cast<int4 *>(prog + ((ta.prog_len + 3) & ~3));
-    double *slots = reinterpret_cast<double *>(inc + ta.inc_rows);
-    for (int i = threadIdx.x; i < (2 * p + 1) * LDQ; i += blockDim.x)
-    {
-        const int r = i / LDQ, b = i - r * LDQ;
-        smem[i] = b < Q ? args.tab[r * Q + b] : 0.0; // tab = node (p+1) x q | edge p x q | pnts | wgts
-    }
-    for (int i = threadIdx.x; i < Q; i += blockDim.x)
-    {
-        pnts[i] = args.tab[(2 * p + 1) * Q + i];
-        wgts[i] = args.tab[(2 * p + 2) * Q + i];
-    }
-    for (int i = threadIdx.x; i < ta.n_coef; i += blockDim.x)
-        coef[i] = args.coef[i];
-    for (int i = threadIdx.x; i < ta.prog_len; i += blockDim.x)
-        prog[i] = args.prog[i];
-    for (int i = threadIdx.x; i < ta.inc_rows; i += blockDim.x)
-        inc[i] = reinterpret_cast<const int4 *>(args.inc)[i];
-    const int epb = ta.epb, SD = ta.slot_doubles;
-    const int off_xs = 8, off_ys = off_xs + N, off_va = off_ys + N, off_vb = off_va + args.vmax, off_t = off_vb + args.vmax;
-    const int n_terms_off = 0;
-    const unsigned long long n_groups = (args.n_elem + epb - 1) / epb;
-
-    for (unsigned long long grp = blockIdx.x; grp < n_groups; grp += gridDim.x)
-    {
-        const unsigned long long elem0 = grp * epb;
-        const int nv = (int)((args.n_elem - elem0) < (unsigned long long)epb ? (args.n_elem - elem0) : epb);
-        __syncthreads(); // tables staged / previous pass done with the slots
-        for (int i = threadIdx.x; i < nv * 8; i += blockDim.x)
-            slots[(i >> 3) * SD + (i & 7)] = args.corners[elem0 * 8 + i];
-        {
-            const float inv_n = 1.0f / (float)N;
-            for (int i = threadIdx.x; i < nv * N; i += blockDim.x)
-            {
-                const int e = (int)(((float)i + 0.5f) * inv_n), k = i - e * N;
-                slots[e * SD + off_xs + k] = args.x[elem0 * N + i];
-                slots[e * SD + off_ys + k] = 0.0;
-            }
-        }
-        __syncthreads();
-        const int n_terms = prog[n_terms_off];
-        int pc = 1;
-        for (int t = 0; t < n_terms; ++t)
-        {
-            const int rf = prog[pc], cf = prog[pc + 1], ci = prog[pc + 2], nfac = prog[pc + 3];
-            pc += 4;
-            const int c0 = args.form_offsets[cf], r0 = args.form_offsets[rf];
-            int cur = off_xs + c0, nxt = off_va; // offsets inside a slot; the first factor reads the input in place
-            int n_cur = args.form_offsets[cf + 1] - c0;
-            for (int f = 0; f < nfac; ++f, pc += 4)
-            {
-                const int type = prog[pc], fa = prog[pc + 1], fb = prog[pc + 2], fc = prog[pc + 3];
-                int n_out;
-                if (type == 0)
-                {
-                    const int rows = (fa == MFV2D_INC_10 || fa == MFV2D_INC_21_T) ? 2 * nh : (fa == MFV2D_INC_21 ? p * p : np1 * np1);
-                    const int4 *map = inc + args.inc_off[fa];
-                    const float inv_rows = 1.0f / (float)rows;
-                    for (int idx = threadIdx.x; idx < nv * rows; idx += blockDim.x)
-                    {
-                        const int e = (int)(((float)idx + 0.5f) * inv_rows), r = idx - e * rows;
-                        const double *src = slots + e * SD + cur;
-                        const int4 m = map[r];
-                        const int ev[4] = {m.x, m.y, m.z, m.w};
-                        double acc = 0.0;
-#pragma unroll
-                        for (int k = 0; k < 4; ++k)
-                        {
-                            if (ev[k] == 0)
-                                break;
-                            const double v = src[abs(ev[k]) - 1];
-                            acc += ev[k] < 0 ? -v : v;
-                        }
-                        slots[e * SD + nxt + r] = acc;
-                    }
-                    __syncthreads();
-                    n_out = rows;
-                }
-                else
-                {
-                    const TileOp op = tile_op(type, fa, fc, p);
-                    const double *fld = op.mode >= 3 ? args.fields[fb] : nullptr;
-                    // ---- phase A: t[e][row][:] = sum_j c[i, j] B_j[:] ----
-                    const int nA0 = op.in[0].kA == TK_NODE ? np1 : p, nA1 = op.n_in > 1 ? (op.in[1].kA == TK_NODE ? np1 : p) : 0;
-                    {
-                        const int R = nA0 + nA1;
-                        const float inv_R = 1.0f / (float)R;
-                        for (int idx = threadIdx.x; idx < nv * R; idx += blockDim.x)
-                        {
-                            const int e = (int)(((float)idx + 0.5f) * inv_R), row = idx - e * R;
-                            const TileComp cmp = row < nA0 ? op.in[0] : op.in[1];
-                            const int i = row < nA0 ? row : row - nA0;
-                            const int nB = cmp.kB == TK_NODE ? np1 : p;
-                            const double *c = slots + e * SD + cur + cmp.off + i * nB;
-                            const double *B = (smem + (cmp.kB) * edge_off);
-                            double acc[Q];
-#pragma unroll
-                            for (int b = 0; b < Q; ++b)
-                                acc[b] = 0.0;
-                            for (int j = 0; j < nB; ++j)
-                                row_axpy<Q>(acc, c[j], B + j * LDQ);
-                            double *dst = slots + e * SD + off_t + row * LDQ;
-#pragma unroll
-                            for (int b = 0; b + 1 < Q; b += 2)
-                                *reinterpret_cast<double2 *>(dst + b) = make_double2(acc[b], acc[b + 1]);
-                            if (Q & 1)
-                                dst[Q - 1] = acc[Q - 1];
-                        }
-                    }
-                    __syncthreads();
-                    // ---- phase B: eta interpolation, metric weights, eta projection; thread (e, b) ----
-                    const int nO0 = op.out[0].kA == TK_NODE ? np1 : p, nO1 = op.n_out > 1 ? (op.out[1].kA == TK_NODE ? np1 : p) : 0;
-                    for (int idx = threadIdx.x; idx < nv * Q; idx += blockDim.x)
-                    {
-                        const int e = idx / Q, b = idx - e * Q;
-                        double *slot = slots + e * SD;
-                        double *tcol = slot + off_t + b;
-                        double u0[Q], u1[Q];
-#pragma unroll
-                        for (int a = 0; a < Q; ++a)
-                            u0[a] = u1[a] = 0.0;
-                        {
-                            const double *A = (smem + op.in[0].kA * edge_off);
-                            for (int i = 0; i < nA0; ++i)
-                                row_axpy<Q>(u0, tcol[i * LDQ], A + i * LDQ);
-                            const double *A1 = (smem + op.in[1].kA * edge_off);
-                            for (int i = 0; i < nA1; ++i)
-                                row_axpy<Q>(u1, tcol[(nA0 + i) * LDQ], A1 + i * LDQ);
-                        }
-                        const double x0 = slot[0], y0 = slot[1], x1 = slot[2], y1 = slot[3], x2 = slot[4], y2 = slot[5], x3 = slot[6],
-                                     y3 = slot[7];
-                        const double xi = pnts[b], wb = wgts[b];
-                        const double j10 = 0.25 * ((x3 - x0) * (1 - xi) + (x2 - x1) * (1 + xi));
-                        const double j11 = 0.25 * ((y3 - y0) * (1 - xi) + (y2 - y1) * (1 + xi));
-                        const double *fp = fld ? fld + (elem0 + e) * (unsigned long long)(2 * Q * Q) + 2 * b : nullptr;
-#pragma unroll
-                        for (int a = 0; a < Q; ++a)
-                        {
-                            const double eta = pnts[a], w = wgts[a] * wb;
-                            const double j00 = 0.25 * ((x1 - x0) * (1 - eta) + (x2 - x3) * (1 + eta));
-                            const double j01 = 0.25 * ((y1 - y0) * (1 - eta) + (y2 - y3) * (1 + eta));
-                            const double det = j00 * j11 - j10 * j01;
-                            const double wod = w / det; // the only division per point
-                            const double a0 = u0[a], a1 = u1[a];
-                            switch (op.mode)
-                            {
-                            case 0:
-                                u0[a] = a0 * det * w;
-                                break;
-                            case 1:
-                                u0[a] = a0 * wod;
-                                break;
-                            case 2: {
-                                const double khh = (j11 * j11 + j10 * j10) * wod, kvv = (j00 * j00 + j01 * j01) * wod,
-                                             khv = (j01 * j11 + j00 * j10) * wod;
-                                u0[a] = khh * a0 + khv * a1;
-                                u1[a] = khv * a0 + kvv * a1;
-                                break;
-                            }
-                            case 3:
-                            case 4: {
-                                const double fx = fp[2 * a * Q], fy = fp[2 * a * Q + 1];
-                                const double kh = (fx * j11 - fy * j10) * w, kv = -(fy * j00 - fx * j01) * w;
-                                if (op.mode == 3)
-                                    u0[a] = kh * a0 + kv * a1;
-                                else
-                                {
-                                    u0[a] = kh * a0;
-                                    u1[a] = kv * a0;
-                                }
-                                break;
-                            }
-                            default: {
-                                const double fx = fp[2 * a * Q], fy = fp[2 * a * Q + 1];
-                                const double kh = -(fx * j10 + fy * j11) * wod, kv = -(fx * j00 + fy * j01) * wod;
-                                if (op.mode == 6)
-                                    u0[a] = kh * a0 + kv * a1;
-                                else
-                                {
-                                    u0[a] = kh * a0;
-                                    u1[a] = kv * a0;
-                                }
-                                break;
-                            }
-                            }
-                        }
-                        {
-                            const double *A = (smem + op.out[0].kA * edge_off);
-                            for (int i = 0; i < nO0; ++i)
-                                tcol[i * LDQ] = row_dot<Q>(A + i * LDQ, u0);
-                            const double *A1 = (smem + op.out[1].kA * edge_off);
-                            for (int i = 0; i < nO1; ++i)
-                                tcol[(nO0 + i) * LDQ] = row_dot<Q>(A1 + i * LDQ, u1);
-                        }
-                    }
-                    __syncthreads();
-                    // ---- phase C: out[i, j] = B_j[:] . t'[e][row][:] ; thread (e, row) ----
-                    {
-                        const int R = nO0 + nO1;
-                        const float inv_R = 1.0f / (float)R;
-                        for (int idx = threadIdx.x; idx < nv * R; idx += blockDim.x)
-                        {
-                            const int e = (int)(((float)idx + 0.5f) * inv_R), row = idx - e * R;
-                            const TileComp cmp = row < nO0 ? op.out[0] : op.out[1];
-                            const int i = row < nO0 ? row : row - nO0;
-                            const int nB = cmp.kB == TK_NODE ? np1 : p;
-                            const double *src = slots + e * SD + off_t + row * LDQ;
-                            double tr[Q];
-#pragma unroll
-                            for (int b = 0; b + 1 < Q; b += 2)
-                            {
-                                const double2 v = *reinterpret_cast<const double2 *>(src + b);
-                                tr[b] = v.x;
-                                tr[b + 1] = v.y;
-                            }
-                            if (Q & 1)
-                                tr[Q - 1] = src[Q - 1];
-                            const double *B = (smem + (cmp.kB) * edge_off);
-                            double *dst = slots + e * SD + nxt + cmp.off + i * nB;
-                            for (int j = 0; j < nB; ++j)
-                                dst[j] = row_dot<Q>(B + j * LDQ, tr);
-                        }
-                    }
-                    __syncthreads();
-                    n_out = 0;
-                    for (int k = 0; k < op.n_out; ++k)
-                        n_out += (op.out[k].kA == TK_NODE ? np1 : p) * (op.out[k].kB == TK_NODE ? np1 : p);
-                }
-                cur = nxt;
-                nxt = (nxt == off_va) ? off_vb : off_va;
-                n_cur = n_out;
-            }
-            const double cf_ = coef[ci];
-            const float inv_nc = 1.0f / (float)(n_cur > 0 ? n_cur : 1);
-            for (int idx = threadIdx.x; idx < nv * n_cur; idx += blockDim.x)
-            {
-                const int e = (int)(((float)idx + 0.5f) * inv_nc), k = idx - e * n_cur;
-                double *slot = slots + e * SD;
-                slot[off_ys + r0 + k] = fma(cf_, slot[cur + k], slot[off_ys + r0 + k]);
-            }
-            __syncthreads();
-        }
-        {
-            const float inv_n = 1.0f / (float)N;
-            for (int i = threadIdx.x; i < nv * N; i += blockDim.x)
-            {
-                const int e = (int)(((float)i + 0.5f) * inv_n), k = i - e * N;
-                args.y[elem0 * N + i] = slots[e * SD + off_ys + k];
-            }
-        }
-    }
-}
-
-template <int Q> static int launch_tile_q(mfv2d_ctx *ctx, ApplyTArgs &ta, size_t fixed_bytes, size_t n_elem)
-{
-    // elements per pass: enough to keep the CTA's threads busy in the (e, row) / (e, column) phases, within
-    // half of the SM's shared memory so that two CTAs are resident
-    const size_t slot_bytes = (size_t)ta.slot_doubles * 8;
-    const size_t budget = ((size_t)228 * 1024 - 2048) / 2;
-    int epb = (int)((budget > fixed_bytes ? budget - fixed_bytes : 0) / slot_bytes);
-    const int want = APPLYT_THREADS / Q; // phase B: one thread per (element, quadrature column), one round
-    if (epb > want)
-        epb = want;
-    if (epb < 1)
-        epb = 1;
-    ta.epb = epb;
-    const size_t smem = fixed_bytes + (size_t)epb * slot_bytes;
-    if (smem > ctx->smem_optin)
-        return mfv2d_fail(ctx, MFV2D_CUDA_UNSUPPORTED, "element vectors need %zu bytes of shared memory", smem);
-    MFV2D_CUDA_CHECK(ctx, cudaFuncSetAttribute(element_vector_tile_kernel<Q>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int per_sm = 1;
-    MFV2D_CUDA_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, element_vector_tile_kernel<Q>, APPLYT_THREADS, smem));
-    if (per_sm < 1)
-        per_sm = 1;
-    unsigned long long grid = (unsigned long long)ctx->sm_count * per_sm;
-    const unsigned long long need = (n_elem + epb - 1) / epb;
-    if (grid > need)
-        grid = need;
-    MFV2D_LAUNCH(element_vector_tile_kernel<Q>, (unsigned)grid, APPLYT_THREADS, smem, ctx->stream, ta);
-    ctx->launches++;
-    MFV2D_CUDA_CHECK(ctx, cudaGetLastError());
-    return MFV2D_SUCCESS;
-}
 
 // =====================================================================================================
 // Fused matrix-free apply.  When every term of a vector program has the shape  coef * [E_L] * D * [E_R]
@@ -2251,44 +1914,6 @@ static int launch_apply(const mfv2d_plan *plan, const mfv2d_elements *e, const d
         }
         if (r >= 0)
             return r;
-    }
-    if (!column_mode && !plan->vector_needs_dense && e->n > 0 && q >= 2 && q <= 16)
-    {
-        // fast path: register-tiled kernel
-        ApplyTArgs ta{};
-        ta.a = a;
-        const int n_prog_total = (int)plan->vprog.size(), n_coef_total = (int)plan->vcoef.size();
-        ta.prog_len = plan->mprog_off ? plan->mprog_off : n_prog_total;
-        ta.n_coef = plan->mcoef_off ? plan->mcoef_off : n_coef_total;
-        ta.inc_rows = plan->basis->inc_off[4];
-        const int ldq = (q + 1) & ~1;
-        ta.slot_doubles = (8 + 2 * a.n_total + 2 * a.vmax + (2 * p + 2) * ldq + 1) & ~1;
-        const size_t fixed_bytes = ((size_t)(2 * p + 1) * ldq + 2 * ldq + (((size_t)ta.n_coef + 1) & ~(size_t)1)) * 8 +
-                                   (((size_t)ta.prog_len + 3) & ~(size_t)3) * 4 + (size_t)ta.inc_rows * 16;
-        switch (q)
-        {
-#define MFV2D_Q_CASE(Q)                                                                                        \
-    case Q:                                                                                                    \
-        return launch_tile_q<Q>(ctx, ta, fixed_bytes, e->n);
-            MFV2D_Q_CASE(2)
-            MFV2D_Q_CASE(3)
-            MFV2D_Q_CASE(4)
-            MFV2D_Q_CASE(5)
-            MFV2D_Q_CASE(6)
-            MFV2D_Q_CASE(7)
-            MFV2D_Q_CASE(8)
-            MFV2D_Q_CASE(9)
-            MFV2D_Q_CASE(10)
-            MFV2D_Q_CASE(11)
-            MFV2D_Q_CASE(12)
-            MFV2D_Q_CASE(13)
-            MFV2D_Q_CASE(14)
-            MFV2D_Q_CASE(15)
-            MFV2D_Q_CASE(16)
-#undef MFV2D_Q_CASE
-        default:
-            break;
-        }
     }
     const size_t smem = doubles * sizeof(double);
     if (smem > ctx->smem_optin)
