@@ -120,7 +120,14 @@ class LinearSystem:
         self.handle = None
 
     # ---- operators (sparse_system.c:3-207); numpy in -> numpy out, DeviceArray in -> DeviceArray out ----
-    def _apply(self, fn, x, n_in: int, n_out: int, out=None):
+    def _apply(self, fn, x, n_in: int, n_out: int, out=None, dense_out: bool = True):
+        if isinstance(x, _SystemVector):  # DenseVector / TraceVector in -> vector object out (``out`` is written in place)
+            if x.parent is not self or (out is not None and out.parent is not self):
+                raise ValueError("vector does not belong to this system (MFV2D_BAD_VECTOR_PARENT)")
+            if out is None:
+                out = DenseVector(self) if dense_out else TraceVector(self)
+            self._apply(fn, x.data, n_in, n_out, out.data)
+            return out
         if isinstance(x, DeviceArray):
             out = out if out is not None else self.ctx.empty(n_out)
         else:
@@ -138,14 +145,14 @@ class LinearSystem:
         return self._apply(lib().mfv2d_cuda_system_apply_diagonal_inverse, x, self.n_dense, self.n_dense, out)
 
     def apply_trace(self, x, out=None):
-        return self._apply(lib().mfv2d_cuda_system_apply_trace, x, self.n_dense, self.n_trace, out)
+        return self._apply(lib().mfv2d_cuda_system_apply_trace, x, self.n_dense, self.n_trace, out, dense_out=False)
 
     def apply_trace_transpose(self, t, out=None):
         return self._apply(lib().mfv2d_cuda_system_apply_trace_transpose, t, self.n_trace, self.n_dense, out)
 
     def apply_full_trace_system(self, t, out=None):
         """``N A^-1 N^T t`` (solving.py:99-123) through the condensed per-element blocks."""
-        return self._apply(lib().mfv2d_cuda_system_apply_schur, t, self.n_trace, self.n_trace, out)
+        return self._apply(lib().mfv2d_cuda_system_apply_schur, t, self.n_trace, self.n_trace, out, dense_out=False)
 
     def set_interface(self, shared_index: np.ndarray, slot: np.ndarray, n_slots: int, owned: np.ndarray) -> None:
         """Multi-GPU: declare the multipliers shared with other ranks (see include/mfv2d_cuda.h)."""
@@ -160,6 +167,9 @@ class LinearSystem:
 def solve_schur_iterative(system: LinearSystem, rhs, constraints, convergence: ConvergenceSettings, precondition: bool = False):
     """python/mfv2d/solving.py:439-500: CG on ``N A^-1 N^T`` for the multipliers, then back substitution.
     Returns ``(x, lambda, residual, iterations)`` like the reference."""
+    if isinstance(rhs, _SystemVector):  # DenseVector / TraceVector in and out, like the reference
+        xd, ld, r, i = solve_schur_iterative(system, rhs.data, constraints.data, convergence, precondition)
+        return DenseVector.__new__(DenseVector)._init(system, xd), TraceVector.__new__(TraceVector)._init(system, ld), r, i
     dev = isinstance(rhs, DeviceArray)
     if dev:
         x, lam = system.ctx.empty(system.n_dense), system.ctx.empty(system.n_trace)
@@ -180,6 +190,9 @@ def solve_schur_iterative(system: LinearSystem, rhs, constraints, convergence: C
 
 def solve_pcg_iterative(system: LinearSystem, rhs, constraints, convergence: ConvergenceSettings):
     """python/mfv2d/solving.py:634-684: PCG on the saddle system with the block-Jacobi ``A^-1 (+) I``."""
+    if isinstance(rhs, _SystemVector):
+        xd, ld, r, i = solve_pcg_iterative(system, rhs.data, constraints.data, convergence)
+        return DenseVector.__new__(DenseVector)._init(system, xd), TraceVector.__new__(TraceVector)._init(system, ld), r, i
     dev = isinstance(rhs, DeviceArray)
     if dev:
         x, lam = system.ctx.empty(system.n_dense), system.ctx.empty(system.n_trace)
@@ -354,3 +367,125 @@ def solve_gmres_iterative(system: LinearSystem, rhs, constraints, convergence: C
         for i in range(k):
             sol.axpby(1.0, sol, float(alpha[i]), p_vecs[i])
     return _finish(sol, rhs, r_mag, k)
+
+
+# ---- DenseVector / TraceVector (src/algebra/system_objects.c:725-2152): device-resident counterparts --------------
+class _SystemVector:
+    """Common part of the two vector types: a DeviceArray that belongs to one LinearSystem.  The static methods write
+    into ``out`` and return it, like the reference's; operands of another system raise ``ValueError``
+    (MFV2D_BAD_VECTOR_PARENT, sparse_system.c:6-9)."""
+
+    _n_attr = ""
+
+    def __init__(self, parent: LinearSystem, data: DeviceArray):
+        self._parent, self.data = parent, data
+
+    @property
+    def parent(self) -> LinearSystem:
+        return self._parent
+
+    @classmethod
+    def _length(cls, parent: LinearSystem) -> int:
+        return int(getattr(parent, cls._n_attr))
+
+    @classmethod
+    def _from_host(cls, parent: LinearSystem, values):
+        n = cls._length(parent)
+        if values is None:
+            values = np.zeros(n)
+        values = np.ascontiguousarray(values, np.float64).ravel()
+        if values.size != n:
+            raise ValueError(f"expected {n} values for this system, got {values.size}")
+        return cls.__new__(cls)._init(parent, parent.ctx.to_device(values))
+
+    def _init(self, parent, data):
+        _SystemVector.__init__(self, parent, data)
+        return self
+
+    @staticmethod
+    def _check(*vs) -> LinearSystem:
+        parent = vs[0]._parent
+        for v in vs:
+            if type(v) is not type(vs[0]) or v._parent is not parent:
+                raise ValueError("vectors do not belong to the same system (MFV2D_BAD_VECTOR_PARENT)")
+        return parent
+
+    def as_merged(self) -> np.ndarray:
+        return self.data.get()
+
+    def copy(self):
+        out = type(self).__new__(type(self))._init(self._parent, self._parent.ctx.empty(self.data.size))
+        out.set_from(self)
+        return out
+
+    def set_from(self, other) -> None:
+        self._check(self, other)
+        if self.data.size:
+            vec_axpby(1.0, other.data, 0.0, other.data, out=self.data, ctx=self._parent.ctx)
+
+    @classmethod
+    def dot(cls, v1, v2, /) -> float:
+        parent = cls._check(v1, v2)
+        return vec_dot(v1.data, v2.data, ctx=parent.ctx) if v1.data.size else 0.0
+
+    @classmethod
+    def add(cls, v1, v2, out, k: float, /):
+        parent = cls._check(v1, v2, out)
+        if out.data.size:
+            vec_axpby(1.0, v1.data, float(k), v2.data, out=out.data, ctx=parent.ctx)
+        return out
+
+    @classmethod
+    def subtract(cls, v1, v2, out, k: float, /):
+        return cls.add(v1, v2, out, -float(k))
+
+    @classmethod
+    def scale(cls, v, x: float, out, /):
+        parent = cls._check(v, out)
+        if out.data.size:
+            vec_axpby(float(x), v.data, 0.0, v.data, out=out.data, ctx=parent.ctx)
+        return out
+
+    def __str__(self) -> str:
+        return f"{type(self).__name__}({self.as_merged()})"
+
+
+class DenseVector(_SystemVector):
+    """``DenseVector(parent, *blocks)`` (system_objects.c:725-830): one block of values per element, stored
+    concatenated on the device; no blocks = zero vector."""
+
+    _n_attr = "n_dense"
+
+    def __init__(self, parent: LinearSystem, /, *blocks):
+        if blocks and len(blocks) != parent.n_elem:
+            raise ValueError(f"expected {parent.n_elem} blocks, got {len(blocks)}")
+        for i, b in enumerate(blocks):
+            if np.size(b) != parent.offsets[i + 1] - parent.offsets[i]:
+                raise ValueError(f"block {i} does not have the size of the system's block")
+        values = np.concatenate([np.asarray(b, np.float64).ravel() for b in blocks]) if blocks else None
+        self._init(parent, self._from_host(parent, values).data)
+
+    def as_split(self) -> tuple:
+        merged, o = self.as_merged(), self._parent.offsets
+        return tuple(merged[o[i]:o[i + 1]].copy() for i in range(self._parent.n_elem))
+
+
+class TraceVector(_SystemVector):
+    """``TraceVector(parent[, values])`` (system_objects.c:1408-1523): one value per multiplier (the reference keeps a
+    copy per sharing element and divides its dot products by the sharing count; the merged form needs neither)."""
+
+    _n_attr = "n_trace"
+
+    def __init__(self, parent: LinearSystem, value=None, /):
+        self._init(parent, self._from_host(parent, value).data)
+
+    def as_split(self) -> tuple:
+        """per element: (indices of its multipliers, their values) - the content of the reference's SparseVectors"""
+        merged = self.as_merged()
+        row, col, _ = self._parent.con
+        elem = np.searchsorted(self._parent.offsets, col, side="right") - 1
+        out = []
+        for e in range(self._parent.n_elem):
+            idx = np.unique(row[elem == e])
+            out.append((idx, merged[idx]))
+        return tuple(out)

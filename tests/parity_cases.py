@@ -345,6 +345,31 @@ def check_linear_system(M, SV, ST, fix, nh, nv):
             xg, lg, rg, itg = SV.solve_gmres_iterative(sysm, g["rhs"], g["con_rhs"], SV.ConvergenceSettings(n_full + 20, 1e-9, 1.0))
             assert itg < n_full + 19 and rg < 1e-9
             assert relerr(xg, g["sol_dense"]) < 1e-8 and relerr(lg, g["sol_trace"]) < 1e-8
+    # DenseVector / TraceVector objects (system_objects.c:725-2152) around the same device operations
+    dv, dw = SV.DenseVector(sysm, *np.split(g["x"], sysm.offsets[1:-1])), SV.DenseVector(sysm)
+    tv = SV.TraceVector(sysm, g["trace_in"])
+    assert dv.parent is sysm and np.array_equal(dv.as_merged(), g["x"]) and np.array_equal(dw.as_merged(), np.zeros(sysm.n_dense))
+    assert len(dv.as_split()) == sysm.n_elem and np.array_equal(np.concatenate(dv.as_split()), g["x"])
+    assert relerr(sysm.apply_diagonal(dv, dw).as_merged(), g["apply_diagonal"]) < 1e-12
+    assert relerr(sysm.apply_trace(dv).as_merged(), g["apply_trace"]) < 1e-12
+    assert relerr(sysm.apply_trace_transpose(tv).as_merged(), g["apply_trace_transpose"]) < 1e-12
+    SV.DenseVector.add(dv, dw, dw, -0.5)
+    assert relerr(dw.as_merged(), g["x"] - 0.5 * g["apply_diagonal"]) < 1e-14
+    SV.DenseVector.subtract(dv, dv.copy(), dw, 3.0)
+    assert relerr(dw.as_merged(), -2.0 * g["x"]) < 1e-15
+    SV.TraceVector.scale(tv, 2.0, tv)
+    assert relerr(tv.as_merged(), 2.0 * g["trace_in"]) < 1e-15
+    assert abs(SV.TraceVector.dot(tv, tv) - 4.0 * g["trace_in"] @ g["trace_in"]) < 1e-10 * abs(4.0 * g["trace_in"] @ g["trace_in"]) + 1e-300
+    idx0, val0 = tv.as_split()[0]
+    assert np.array_equal(val0, 2.0 * g["trace_in"][idx0]) and idx0.size > 0
+    xs_, ls_, _, its_ = SV.solve_schur_iterative(sysm, SV.DenseVector(sysm, *np.split(g["rhs"], sysm.offsets[1:-1])),
+                                                SV.TraceVector(sysm, g["con_rhs"]), SV.ConvergenceSettings(2000, 1e-30, 1e-12))
+    assert isinstance(xs_, SV.DenseVector) and its_ == it and np.array_equal(xs_.as_merged(), x) and np.array_equal(ls_.as_merged(), lam)
+    other = SV.LinearSystem(mats, (row, col, val), nt)
+    with pytest.raises(ValueError):
+        SV.DenseVector.add(dv, SV.DenseVector(other), dw, 1.0)
+    with pytest.raises(ValueError):
+        other.apply_diagonal(dv)
     # BLAS-1
     a, b = g["x"], g["rhs"]
     assert relerr(SV.vec_axpby(2.0, a, -0.5, b), 2.0 * a - 0.5 * b) < 1e-15
