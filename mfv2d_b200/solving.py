@@ -72,7 +72,13 @@ class LinearSystem:
     ``constraints``: sequence of :class:`Constraint`, or a COO triple ``(row, col, val)`` over global
     dense columns together with ``n_trace``."""
 
-    def __init__(self, element_matrices, constraints, n_trace: int | None = None, ctx: Context | None = None):
+    def __init__(self, element_matrices, constraints=None, n_trace: int | None = None, *args, ctx: Context | None = None):
+        if isinstance(element_matrices, (int, np.integer)):
+            # the reference's own call, LinearSystem(n_elem, form_specs, orders, element_matrices, constraints)
+            # (python/mfv2d/solving.py:41-60): block sizes follow from the matrices themselves
+            n_elem, (element_matrices, constraints), n_trace = int(element_matrices), args[:2], None
+            if len(element_matrices) != n_elem:
+                raise ValueError(f"expected {n_elem} element matrices, got {len(element_matrices)}")
         self.ctx = ctx or get_context()
         if isinstance(element_matrices, DeviceArray):
             n, ne, ne2 = element_matrices.shape

@@ -365,7 +365,14 @@ def check_linear_system(M, SV, ST, fix, nh, nv):
     xs_, ls_, _, its_ = SV.solve_schur_iterative(sysm, SV.DenseVector(sysm, *np.split(g["rhs"], sysm.offsets[1:-1])),
                                                 SV.TraceVector(sysm, g["con_rhs"]), SV.ConvergenceSettings(2000, 1e-30, 1e-12))
     assert isinstance(xs_, SV.DenseVector) and its_ == it and np.array_equal(xs_.as_merged(), x) and np.array_equal(ls_.as_merged(), lam)
-    other = SV.LinearSystem(mats, (row, col, val), nt)
+    # the reference's constructor call: LinearSystem(n_elem, form_specs, orders, element_matrices, constraints)
+    cons = [SV.Constraint(float(g["con_rhs"][i]), *[SV.ElementConstraint(int(e_), col[(row == i) & (el == e_)] - sysm.offsets[e_],
+                                                                           val[(row == i) & (el == e_)])
+                                                     for e_ in np.unique(el[row == i])])
+            for el in [np.searchsorted(sysm.offsets, col, side="right") - 1] for i in range(nt)]
+    other = SV.LinearSystem(sysm.n_elem, specs, np.full((sysm.n_elem, 2), p), list(mats), cons)
+    assert other.n_trace == nt and np.array_equal(other.constraint_rhs, g["con_rhs"])
+    assert relerr(other.apply_trace(g["x"]), g["apply_trace"]) < 1e-12
     with pytest.raises(ValueError):
         SV.DenseVector.add(dv, SV.DenseVector(other), dw, 1.0)
     with pytest.raises(ValueError):
