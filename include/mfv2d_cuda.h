@@ -228,6 +228,12 @@ MFV2D_API int mfv2d_cuda_interprod_batch(const mfv2d_elements *elems, int start_
  * dofs[n_elem][n_k] -> out[n_elem][q][q] (0-/2-forms) or out[n_elem][q][q][2] (1-forms). */
 MFV2D_API int mfv2d_cuda_reconstruct_batch(const mfv2d_elements *elems, int form, const double *dofs,
                                            double *out, int space);
+/* Dual degrees of freedom (L2 projection integrals) of a function given by its values at the quadrature points
+ * (element_dual_dofs, python/mfv2d/mimetic2d.py:1003-1123; the per-element NumPy loops behind compute_element_rhs,
+ * python/mfv2d/solve_system.py:129-160).  values[n_elem][q][q] (0-/2-forms) or [n_elem][q][q][2] (1-forms)
+ * -> out[n_elem][n_k]. */
+MFV2D_API int mfv2d_cuda_dual_dofs_batch(const mfv2d_elements *elems, int form, const double *values, double *out,
+                                         int space);
 /* Two-basis masses / projectors (compute_element_projector, src/evaluation/element_system.c:480-643;
  * compute_mass_matrix_*_double, fem_space.c:847-1055).  elems_out carries the output basis and the
  * geometry, basis_in must share its integration rule.  dual != 0: out = M_mixed (n_k(out) x n_k(in));

@@ -487,6 +487,26 @@ class ElementBatch:
         check(lib().mfv2d_cuda_reconstruct_batch(self.handle, int(order), addr(dofs), addr(out), space_of(dofs, out)), self.ctx.handle)
         return out
 
+    def dual_dofs(self, order: int, function, out=None):
+        """Dual degrees of freedom ``(n, n_k)`` of ``function(x, y)`` on every element of the batch
+        (``element_dual_dofs``, python/mfv2d/mimetic2d.py:1003-1123).  The callable is evaluated ONCE on the stacked
+        coordinates ``(n, q, q)``; ``function`` may also be the array of its values at the quadrature points."""
+        order = int(order)
+        shape = (self.n, self.q, self.q, 2) if order == FORM_ORDER_1 else (self.n, self.q, self.q)
+        if callable(function):
+            xy = self.coordinates()
+            xy = xy.get() if isinstance(xy, DeviceArray) else xy
+            vals = np.asarray(function(xy[:, 0], xy[:, 1]), np.float64)
+        else:
+            vals = function
+        if not isinstance(vals, DeviceArray):
+            vals = np.ascontiguousarray(np.broadcast_to(np.asarray(vals, np.float64), shape)) if np.shape(vals) != shape else np.ascontiguousarray(vals, np.float64)
+        if tuple(vals.shape) != shape:
+            raise ValueError(f"function values have the shape {tuple(vals.shape)}, expected {shape}")
+        out = self._out(out, (self.n, self.form_size(order)))
+        check(lib().mfv2d_cuda_dual_dofs_batch(self.handle, order, addr(vals), addr(out), space_of(vals, out)), self.ctx.handle)
+        return out
+
     def evaluate_callable_fields(self, plan: Plan) -> np.ndarray | None:
         """Evaluate the plan's callable fields on the stacked quadrature coordinates of the whole batch
         (ONE Python call per field instead of one per element, integrating_fields.c:78-126)."""
@@ -794,3 +814,8 @@ def compute_element_projectors(order: int, basis_in: Basis2D, batch: ElementBatc
         bad = int(np.flatnonzero(status)[0])
         raise _capi.Mfv2dCudaError(int(status[bad]), _capi.result_name(int(status[bad])), f"element {bad}: output mass matrix could not be inverted")
     return out
+
+
+def element_dual_dofs(order, element_space: ElementFemSpace2D, function) -> np.ndarray:
+    """``mfv2d.mimetic2d.element_dual_dofs`` (python/mfv2d/mimetic2d.py:1003-1123) for one element: batch of one."""
+    return element_space.batch.dual_dofs(int(order), function)[0]

@@ -207,6 +207,83 @@ static int make_dense_plan(mfv2d_ctx *ctx, const mfv2d_basis *basis, int dk, int
     return MFV2D_SUCCESS;
 }
 
+// ---- dual degrees of freedom of a function (element_dual_dofs, python/mfv2d/mimetic2d.py:1003-1123) ----------
+// dofs_i = integral of f against basis function i: the values of f at the q x q points are weighted with the
+// quadrature weights and the metric of the reference's formulas (0-forms: det; 1-forms: the rows of J, no
+// determinant; 2-forms: nothing) and contracted with the two 1-D tables.  One CTA per element.
+__global__ void __launch_bounds__(128) dual_dofs_kernel(const double *__restrict__ tab, int p, int q, const double *__restrict__ corners,
+                                                         unsigned long long n_elem, int form, const double *__restrict__ fvals,
+                                                         double *__restrict__ out)
+{
+    MFV2D_DYN_SMEM(double, gw); // weighted point values: one (0-/2-forms) or two (1-forms) fields of q*q doubles
+    const int q2 = q * q, np1 = p + 1, nh = p * np1;
+    const double *node = tab, *edge = tab + np1 * q, *pnts = edge + p * q, *wgts = pnts + q;
+    const int nk = form == MFV2D_FORM_ORDER_0 ? np1 * np1 : (form == MFV2D_FORM_ORDER_1 ? 2 * nh : p * p);
+    const int ncomp = form == MFV2D_FORM_ORDER_1 ? 2 : 1;
+    for (unsigned long long e = blockIdx.x; e < n_elem; e += gridDim.x)
+    {
+        const double *cs = corners + e * 8;
+        const double *f = fvals + e * (unsigned long long)q2 * ncomp;
+        __syncthreads();
+        for (int pt = threadIdx.x; pt < q2; pt += blockDim.x)
+        {
+            const int a = pt / q, b = pt - a * q;
+            const double eta = pnts[a], xi = pnts[b], w = wgts[a] * wgts[b];
+            const double x0 = cs[0], y0 = cs[1], x1 = cs[2], y1 = cs[3], x2 = cs[4], y2 = cs[5], x3 = cs[6], y3 = cs[7];
+            const double j00 = 0.25 * ((x1 - x0) * (1 - eta) + (x2 - x3) * (1 + eta));
+            const double j01 = 0.25 * ((y1 - y0) * (1 - eta) + (y2 - y3) * (1 + eta));
+            const double j10 = 0.25 * ((x3 - x0) * (1 - xi) + (x2 - x1) * (1 + xi));
+            const double j11 = 0.25 * ((y3 - y0) * (1 - xi) + (y2 - y1) * (1 + xi));
+            if (form == MFV2D_FORM_ORDER_0)
+                gw[pt] = f[pt] * w * (j00 * j11 - j10 * j01);
+            else if (form == MFV2D_FORM_ORDER_2)
+                gw[pt] = f[pt] * w;
+            else
+            {
+                const double fx = f[2 * pt] * w, fy = f[2 * pt + 1] * w;
+                gw[pt] = j10 * fx + j11 * fy;      // f_eta: tested against edge_xi x node_eta
+                gw[q2 + pt] = j00 * fx + j01 * fy; // f_xi:  tested against node_xi x edge_eta
+            }
+        }
+        __syncthreads();
+        for (int idx = threadIdx.x; idx < nk; idx += blockDim.x)
+        {
+            const double *A, *B, *g = gw; // A: table along eta (rows a), B: along xi (columns b)
+            int i, j;
+            if (form == MFV2D_FORM_ORDER_0)
+            {
+                j = idx / np1, i = idx - j * np1;
+                A = node + j * q, B = node + i * q;
+            }
+            else if (form == MFV2D_FORM_ORDER_2)
+            {
+                j = idx / p, i = idx - j * p;
+                A = edge + j * q, B = edge + i * q;
+            }
+            else if (idx < nh)
+            {
+                j = idx / p, i = idx - j * p;
+                A = node + j * q, B = edge + i * q;
+            }
+            else
+            {
+                j = (idx - nh) / np1, i = (idx - nh) - j * np1;
+                A = edge + j * q, B = node + i * q;
+                g = gw + q2;
+            }
+            double acc = 0.0;
+            for (int a = 0; a < q; ++a)
+            {
+                double row = 0.0;
+                for (int b = 0; b < q; ++b)
+                    row = fma(B[b], g[a * q + b], row);
+                acc = fma(A[a], row, acc);
+            }
+            out[e * (unsigned long long)nk + idx] = acc;
+        }
+    }
+}
+
 extern "C" {
 
 int mfv2d_cuda_reconstruct_batch(const mfv2d_elements *e, int form, const double *dofs, double *out, int space)
@@ -224,6 +301,36 @@ int mfv2d_cuda_reconstruct_batch(const mfv2d_elements *e, int form, const double
     int r = stage_out_alloc(ctx, out, e->n * per * sizeof(double), space, &o);
     if (!r)
         r = launch_reconstruct(e, form, (const double *)in.dev, nk, (double *)o.dev);
+    if (!r)
+        r = stage_finish(&o);
+    else
+        stage_abort(&o);
+    stage_abort(&in);
+    return r;
+}
+
+int mfv2d_cuda_dual_dofs_batch(const mfv2d_elements *e, int form, const double *values, double *out, int space)
+{
+    mfv2d_ctx *ctx = e->ctx;
+    const int p = e->basis->p, q = e->basis->q;
+    const int nk = form_size(form, p);
+    if (nk < 0)
+        return mfv2d_fail(ctx, MFV2D_BAD_ENUM, "dual_dofs_batch: invalid form order %d", form);
+    if (e->n == 0)
+        return MFV2D_SUCCESS;
+    const size_t per = (size_t)q * q * (form == MFV2D_FORM_ORDER_1 ? 2 : 1);
+    Staged in, o;
+    MFV2D_TRY(stage_in(ctx, values, e->n * per * sizeof(double), space, &in));
+    int r = stage_out_alloc(ctx, out, e->n * nk * sizeof(double), space, &o);
+    if (!r)
+    {
+        const size_t grid = e->n < (size_t)ctx->sm_count * 8 ? e->n : (size_t)ctx->sm_count * 8;
+        MFV2D_LAUNCH(dual_dofs_kernel, (unsigned)grid, 128, (size_t)2 * q * q * sizeof(double), ctx->stream, e->basis->d_tab, p, q,
+                     e->d_corners, (unsigned long long)e->n, form, (const double *)in.dev, (double *)o.dev);
+        ctx->launches++;
+        if (cudaGetLastError() != cudaSuccess)
+            r = mfv2d_fail(ctx, MFV2D_CUDA_ERROR, "dual_dofs kernel failed to launch");
+    }
     if (!r)
         r = stage_finish(&o);
     else

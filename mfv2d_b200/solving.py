@@ -495,3 +495,18 @@ class TraceVector(_SystemVector):
             idx = np.unique(row[elem == e])
             out.append((idx, merged[idx]))
         return tuple(out)
+
+
+def compute_linear_system(form_specs, expressions, batch, constraints, n_trace: int | None = None, degrees_of_freedom=None,
+                          field_values=None) -> LinearSystem:
+    """The per-element loop of ``compute_linear_system`` (python/mfv2d/solve_system.py:988-1008) collapsed: all element
+    matrices of one ``(p, q)`` bucket in ONE launch, left on the device and handed to :class:`LinearSystem` without a
+    host copy.  ``batch`` is an ``ElementBatch``; ``constraints`` as for ``LinearSystem``.
+    Mixed-order meshes: one call per bucket for the matrices (``compute_element_matrices``), then
+    ``LinearSystem(list_of_host_matrices, constraints)``."""
+    from . import _mfv2d as M
+
+    ne = form_specs.total_size(batch.p, batch.p)
+    out = batch.ctx.empty((batch.n, ne, ne))
+    M.compute_element_matrices(form_specs, expressions, batch, degrees_of_freedom, field_values, out=out)
+    return LinearSystem(out, constraints, n_trace, ctx=batch.ctx)

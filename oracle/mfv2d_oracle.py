@@ -414,6 +414,22 @@ def reconstruct_field(b: Basis, corners, form: int, dofs: np.ndarray) -> np.ndar
 
 
 # ----------------------------------------------------------------------------------------
+# dual degrees of freedom of a function (python/mfv2d/mimetic2d.py:1003-1123)
+# ----------------------------------------------------------------------------------------
+def dual_dofs(b: Basis, corners, form: int, fvals: np.ndarray) -> np.ndarray:
+    """fvals: values of the function at the quadrature points, (q, q) or (q, q, 2) for 1-forms."""
+    j00, j01, j10, j11, det = jacobian(corners, b.pnts)
+    w = b.wgts[:, None] * b.wgts[None, :]
+    if form == FORM_ORDER_0:
+        return np.einsum("wab,ab->w", _phi0(b), fvals * w * det)
+    if form == FORM_ORDER_2:
+        return np.einsum("wab,ab->w", _phi2(b), fvals * w)
+    f_xi = (j00 * fvals[..., 0] + j01 * fvals[..., 1]) * w
+    f_eta = (j10 * fvals[..., 0] + j11 * fvals[..., 1]) * w
+    return np.concatenate([np.einsum("wab,ab->w", _phi1h(b), f_eta), np.einsum("wab,ab->w", _phi1v(b), f_xi)])
+
+
+# ----------------------------------------------------------------------------------------
 # bytecode VM (src/evaluation/element_eval.c:18-479, src/algebra/matrix.c:188-276)
 # ----------------------------------------------------------------------------------------
 @dataclass

@@ -165,6 +165,44 @@ def check_mixed_order_buckets(M, orders=(2, 3, 5, 8), per_order=5, name="mixed_p
         assert relerr(vecs[e], ref @ xs[e]) < TOL_MAT, (e, p)
 
 
+def _dual_f_scalar(x, y):
+    return np.sin(1.3 * x + 0.2) * np.cos(0.7 * y) + 0.5 * x * y
+
+
+def _dual_f_vector(x, y):
+    return np.stack((np.cos(x) * y + 1.0, np.sin(0.5 * y) - 0.25 * x * x), axis=-1)
+
+
+def check_dual_dofs(M, cases=((1, 2), (3, 3), (4, 2), (6, 3))):
+    """element_dual_dofs (python/mfv2d/mimetic2d.py:1003-1123): against the reference's own output
+    (tests/golden/dual_dofs.npz, same functions as tests/golden/make_golden_dual.py) and the oracle on all quads."""
+    g = golden("dual_dofs.npz")
+    for p, k in cases:
+        basis = make_basis(M, p, k)
+        batch = M.ElementBatch(basis, np.ascontiguousarray(F.QUADS))
+        ob = O.basis(p, p + k + 1)
+        for fo, fn in ((1, _dual_f_scalar), (2, _dual_f_vector), (3, _dual_f_scalar)):
+            d = batch.dual_dofs(fo, fn)
+            assert d.shape == (len(F.QUADS), batch.form_size(fo))
+            for iq in (2, 4, 5):
+                ref = g[f"p{p}k{k}q{iq}_f{fo}"]
+                assert relerr(d[iq], ref) < TOL_MAT, (p, k, iq, fo, relerr(d[iq], ref))
+            for iq, quad in enumerate(F.QUADS):
+                x, y = O.physical_coordinates(quad, ob.pnts)
+                assert relerr(d[iq], O.dual_dofs(ob, quad, fo, fn(x, y))) < TOL_MAT, (p, k, iq, fo)
+        sp = M.ElementFemSpace2D(basis, np.ascontiguousarray(F.QUADS[4]))
+        assert relerr(M.element_dual_dofs(2, sp, _dual_f_vector), g[f"p{p}k{k}q4_f2"]) < TOL_MAT
+    # consistency with the mass matrix: the dual dofs of a reconstructed field are M times its primal dofs (1- and
+    # 2-forms; the reference's 0-form reconstruction carries an extra det, integrating_fields.c:238-262)
+    p, k = 3, 3
+    batch = M.ElementBatch(make_basis(M, p, k), np.ascontiguousarray(F.QUADS))
+    rng = np.random.default_rng(4)
+    for fo in (2, 3):
+        c = rng.standard_normal((len(F.QUADS), batch.form_size(fo)))
+        vals = batch.reconstruct(fo, c)
+        assert relerr(batch.dual_dofs(fo, vals), np.einsum("eij,ej->ei", batch.mass(fo), c)) < 1e-11, fo
+
+
 def check_incidence(M, orders=(1, 2, 3, 5)):
     """tests/test_apply_incidence-c.py: all 8 incidence kernels against explicit matrices."""
     rng = np.random.default_rng(11)
@@ -365,6 +403,10 @@ def check_linear_system(M, SV, ST, fix, nh, nv):
     xs_, ls_, _, its_ = SV.solve_schur_iterative(sysm, SV.DenseVector(sysm, *np.split(g["rhs"], sysm.offsets[1:-1])),
                                                 SV.TraceVector(sysm, g["con_rhs"]), SV.ConvergenceSettings(2000, 1e-30, 1e-12))
     assert isinstance(xs_, SV.DenseVector) and its_ == it and np.array_equal(xs_.as_merged(), x) and np.array_equal(ls_.as_merged(), lam)
+    # the assembly loop of the callers collapsed: matrices stay on the device (solve_system.py:988-1008)
+    dev_sys = SV.compute_linear_system(specs, s["lhs"], batch, (row, col, val), nt)
+    assert relerr(dev_sys.apply_diagonal(g["x"]), g["apply_diagonal"]) < 1e-12
+    assert relerr(dev_sys.apply_full_trace_system(t), composed) < 1e-11
     # the reference's constructor call: LinearSystem(n_elem, form_specs, orders, element_matrices, constraints)
     cons = [SV.Constraint(float(g["con_rhs"][i]), *[SV.ElementConstraint(int(e_), col[(row == i) & (el == e_)] - sysm.offsets[e_],
                                                                            val[(row == i) & (el == e_)])

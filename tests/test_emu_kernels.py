@@ -45,6 +45,10 @@ def test_system_golden(emu, name):
     P.check_system_golden(emu[0], name, cases=((1, 2), (3, 3), (4, 2), (5, 0)))
 
 
+def test_dual_dofs(emu):
+    P.check_dual_dofs(emu[0])
+
+
 def test_mixed_order_buckets(emu):
     P.check_mixed_order_buckets(emu[0], orders=(2, 3, 5), per_order=2)
 

@@ -97,3 +97,16 @@ def test_oracle_vs_live_reference():
             mr = rng.standard_normal((5, e.shape[0]))
             assert relerr(mr @ e, ref.check_incidence(mr, p, t % 2, t >= 2, True)) < 1e-15
         del sp
+
+
+def test_dual_dofs_vs_golden():
+    """oracle.dual_dofs against the reference's element_dual_dofs (tests/golden/dual_dofs.npz)."""
+    import parity_cases as P
+
+    g = golden("dual_dofs.npz")
+    for p, k in ((1, 2), (3, 3), (4, 2), (6, 3)):
+        ob = O.basis(p, p + k + 1)
+        for iq in (2, 4, 5):
+            x, y = O.physical_coordinates(F.QUADS[iq], ob.pnts)
+            for fo, fn in ((1, P._dual_f_scalar), (2, P._dual_f_vector), (3, P._dual_f_scalar)):
+                assert relerr(O.dual_dofs(ob, F.QUADS[iq], fo, fn(x, y)), g[f"p{p}k{k}q{iq}_f{fo}"]) < 1e-13
