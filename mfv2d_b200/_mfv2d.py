@@ -819,3 +819,33 @@ def compute_element_projectors(order: int, basis_in: Basis2D, batch: ElementBatc
 def element_dual_dofs(order, element_space: ElementFemSpace2D, function) -> np.ndarray:
     """``mfv2d.mimetic2d.element_dual_dofs`` (python/mfv2d/mimetic2d.py:1003-1123) for one element: batch of one."""
     return element_space.batch.dual_dofs(int(order), function)[0]
+
+
+def compute_element_rhs(system, space_or_batch) -> np.ndarray:
+    """``compute_element_rhs`` (python/mfv2d/solve_system.py:129-160): the projections of the right-hand-side functions
+    of every equation, concatenated in equation order.  ``system`` is the reference's ``KFormSystem`` (or anything with
+    ``equations[i].weight.order`` and ``equations[i].right.explicit_terms`` = ``(k, projection)`` pairs whose
+    projections carry ``.func``).  With an :class:`ElementBatch` the result is ``(n, N_e)`` and every function is
+    called once on the stacked coordinates; with an :class:`ElementFemSpace2D` it is the reference's ``(N_e,)``.
+    The projections of one equation are linear in the function, so the weighted sum is formed on the function values
+    and projected once."""
+    single = isinstance(space_or_batch, ElementFemSpace2D)
+    batch = space_or_batch.batch if single else space_or_batch
+    xy = None
+    parts = []
+    for eq in system.equations:
+        order = int(eq.weight.order)
+        shape = (batch.n, batch.q, batch.q, 2) if order == FORM_ORDER_1 else (batch.n, batch.q, batch.q)
+        vals = None
+        for k, f in eq.right.explicit_terms:
+            fn = getattr(f, "func", None)  # only element projections carry a function (solve_system.py:117-119)
+            if fn is None:
+                continue
+            if xy is None:
+                xy = batch.coordinates()
+                xy = xy.get() if isinstance(xy, DeviceArray) else xy
+            v = float(k) * np.broadcast_to(np.asarray(fn(xy[:, 0], xy[:, 1]), np.float64), shape)
+            vals = v if vals is None else vals + v
+        parts.append(np.zeros((batch.n, batch.form_size(order))) if vals is None else batch.dual_dofs(order, np.ascontiguousarray(vals)))
+    out = np.concatenate(parts, axis=1)
+    return out[0] if single else out

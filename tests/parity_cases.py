@@ -403,6 +403,15 @@ def check_linear_system(M, SV, ST, fix, nh, nv):
     xs_, ls_, _, its_ = SV.solve_schur_iterative(sysm, SV.DenseVector(sysm, *np.split(g["rhs"], sysm.offsets[1:-1])),
                                                 SV.TraceVector(sysm, g["con_rhs"]), SV.ConvergenceSettings(2000, 1e-30, 1e-12))
     assert isinstance(xs_, SV.DenseVector) and its_ == it and np.array_equal(xs_.as_merged(), x) and np.array_equal(ls_.as_merged(), lam)
+    # compute_element_rhs (solve_system.py:129-160) of the same system: the fixture's rhs IS the reference's output
+    from types import SimpleNamespace as NS
+
+    def f_exact(x_, y_):
+        return -2 * np.pi**2 * np.cos(np.pi * x_) * np.cos(np.pi * y_)
+
+    duck = NS(equations=[NS(weight=NS(order=2), right=NS(explicit_terms=[])),
+                         NS(weight=NS(order=3), right=NS(explicit_terms=[(1.0, NS(func=f_exact, weight=NS(order=3)))]))])
+    assert relerr(M.compute_element_rhs(duck, batch).ravel(), g["rhs"]) < 1e-12
     # the assembly loop of the callers collapsed: matrices stay on the device (solve_system.py:988-1008)
     dev_sys = SV.compute_linear_system(specs, s["lhs"], batch, (row, col, val), nt)
     assert relerr(dev_sys.apply_diagonal(g["x"]), g["apply_diagonal"]) < 1e-12
