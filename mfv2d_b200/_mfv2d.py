@@ -849,3 +849,25 @@ def compute_element_rhs(system, space_or_batch) -> np.ndarray:
         parts.append(np.zeros((batch.n, batch.form_size(order))) if vals is None else batch.dual_dofs(order, np.ascontiguousarray(vals)))
     out = np.concatenate(parts, axis=1)
     return out[0] if single else out
+
+
+def _mass_expressions(form_specs: _ElementFormSpecification, inverse: bool):
+    """block-diagonal bytecode: (MASS, order, inverse) on the diagonal, nothing elsewhere"""
+    n = len(form_specs)
+    return [[[(MATOP_MASS, int(form_specs[i][1]), bool(inverse))] if i == j else None for j in range(n)] for i in range(n)]
+
+
+def compute_element_dual_from_primal(form_specs: _ElementFormSpecification, primal, space_or_batch):
+    """``compute_element_dual_from_primal`` (python/mfv2d/solve_system.py:302-325): ``dual_k = M_k primal_k`` for every
+    form of the element - the matrix-free apply of the block-diagonal mass system (no mass matrix is formed).
+    ``primal`` is ``(N_e,)`` with an :class:`ElementFemSpace2D` or ``(n, N_e)`` with an :class:`ElementBatch`."""
+    if isinstance(space_or_batch, ElementFemSpace2D):
+        return compute_element_vector(form_specs, _mass_expressions(form_specs, False), space_or_batch, primal)
+    return compute_element_vectors(form_specs, _mass_expressions(form_specs, False), space_or_batch, primal)
+
+
+def compute_element_primal_from_dual(form_specs: _ElementFormSpecification, dual, space_or_batch):
+    """``compute_element_primal_from_dual`` (python/mfv2d/solve_system.py:328-351): ``primal_k = M_k^-1 dual_k``."""
+    if isinstance(space_or_batch, ElementFemSpace2D):
+        return compute_element_vector(form_specs, _mass_expressions(form_specs, True), space_or_batch, dual)
+    return compute_element_vectors(form_specs, _mass_expressions(form_specs, True), space_or_batch, dual)

@@ -192,6 +192,18 @@ def check_dual_dofs(M, cases=((1, 2), (3, 3), (4, 2), (6, 3))):
                 assert relerr(d[iq], O.dual_dofs(ob, quad, fo, fn(x, y))) < TOL_MAT, (p, k, iq, fo)
         sp = M.ElementFemSpace2D(basis, np.ascontiguousarray(F.QUADS[4]))
         assert relerr(M.element_dual_dofs(2, sp, _dual_f_vector), g[f"p{p}k{k}q4_f2"]) < TOL_MAT
+    # compute_element_dual_from_primal / _primal_from_dual (solve_system.py:302-351): block-diagonal mass applies
+    specs3 = M._ElementFormSpecification(("a", 1), ("b", 2), ("c", 3))
+    batch3 = M.ElementBatch(make_basis(M, 3, 3), np.ascontiguousarray(F.QUADS))
+    rng3 = np.random.default_rng(8)
+    prim = rng3.standard_normal((len(F.QUADS), specs3.total_size(3, 3)))
+    ref_dual = np.concatenate([np.einsum("eij,ej->ei", batch3.mass(fo), prim[:, o:o + batch3.form_size(fo)])
+                               for fo, o in zip((1, 2, 3), (0, batch3.form_size(1), batch3.form_size(1) + batch3.form_size(2)))], axis=1)
+    dual = M.compute_element_dual_from_primal(specs3, prim, batch3)
+    assert relerr(dual, ref_dual) < TOL_MAT
+    assert relerr(M.compute_element_primal_from_dual(specs3, dual, batch3), prim) < 1e-9
+    sp3 = M.ElementFemSpace2D(make_basis(M, 3, 3), np.ascontiguousarray(F.QUADS[4]))
+    assert relerr(M.compute_element_dual_from_primal(specs3, prim[4], sp3), ref_dual[4]) < TOL_MAT
     # consistency with the mass matrix: the dual dofs of a reconstructed field are M times its primal dofs (1- and
     # 2-forms; the reference's 0-form reconstruction carries an extra det, integrating_fields.c:238-262)
     p, k = 3, 3
