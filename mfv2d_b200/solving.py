@@ -79,6 +79,8 @@ class LinearSystem:
             n_elem, (element_matrices, constraints), n_trace = int(element_matrices), args[:2], None
             if len(element_matrices) != n_elem:
                 raise ValueError(f"expected {n_elem} element matrices, got {len(element_matrices)}")
+        if ctx is None and args and isinstance(args[0], Context):
+            ctx = args[0]  # LinearSystem(matrices, constraints, n_trace, ctx)
         self.ctx = ctx or get_context()
         if isinstance(element_matrices, DeviceArray):
             n, ne, ne2 = element_matrices.shape
