@@ -257,6 +257,133 @@ __device__ __forceinline__ void phase_s2(const AsmArgs &args, double *smem, cons
     }
 }
 
+#ifndef MFV2D_EMU
+// ---- S1 + S2 on the tensor cores (Q <= 8) --------------------------------------------------------------
+// mma.sync m8n8k4 f64: lane (g = lane / 4, t = lane % 4) holds A[m = g][k = t], B[k = t][n = g] and
+// D[m = g][n = 2t, 2t + 1].  The two k-steps of a contraction over 8 quadrature points take the points 2t and
+// 2t + 1, so that a lane's pair of D values of stage 1 (T[(j,l) = g][a = 2t, 2t + 1]) is exactly its pair of B
+// operands of stage 2: T never leaves the registers and the two stages need no barrier between them.
+__device__ __forceinline__ void asm_dmma(double &d0, double &d1, double a, double b)
+{
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0, %1}, {%2}, {%3}, {%0, %1};"
+                 : "+d"(d0), "+d"(d1)
+                 : "d"(a), "d"(b));
+}
+
+// work item (per element): tensor block, tile of 8 (j,l) pairs, tile of 8 (i,k) pairs.  Stage 1: T = PT_B (8 pairs
+// x Q) W^T (Q x Q rows a) - two instructions, recomputed per (i,k) tile rather than shared; stage 2: PT_A (8 pairs
+// x Q) T^T, scattered to all images of the entries in the arena.
+template <int Q>
+__device__ __forceinline__ void phase_tc(const AsmArgs &args, double *smem, const DevStage &sg, const DevTB *tbs, int n_valid)
+{
+    const AsmLayout &L = args.lay;
+    const int ldq = L.ldq;
+    const char *sb = reinterpret_cast<const char *>(smem);
+    const int *xt = reinterpret_cast<const int *>(sb + L.off_tc) + sg.tc_begin;
+    const DevS1Pair *s1 = reinterpret_cast<const DevS1Pair *>(sb + L.off_s1);
+    const DevS2Pair *s2 = reinterpret_cast<const DevS2Pair *>(sb + L.off_s2);
+    const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+    const bool q0 = 2 * t < Q, q1 = 2 * t + 1 < Q; // the lane's two quadrature points exist
+    const int per = sg.tc_count;
+    const float inv_per = 1.0f / (float)per;
+    for (int x = threadIdx.x >> 5; x < per * n_valid; x += blockDim.x >> 5)
+    {
+        const int e = fast_div(x, inv_per);
+        const int item = xt[x - e * per];
+        const DevTB &tb = tbs[item & 0xffff];
+        const int nt = (item >> 16) & 255, mt = item >> 24;
+        double *slot = smem + L.off_slots + e * L.slot_stride;
+        const int npA = tb.npA, npB = tb.npB, ld = tb.ld;
+        // stage 1
+        double2 w = *reinterpret_cast<const double2 *>(slot + L.slot_w + tb.w * (Q * ldq) + (g < Q ? g : 0) * ldq + 2 * t);
+        w.x = (g < Q && q0) ? w.x : 0.0;
+        w.y = (g < Q && q1) ? w.y : 0.0;
+        const DevS1Pair *pjl = s1 + tb.s1_tab;
+        const int njl = 8 * nt + g;
+        double2 pb = *reinterpret_cast<const double2 *>(smem + pjl[njl < npB ? njl : 0].pt + 2 * t);
+        pb.x = (njl < npB && q0) ? pb.x : 0.0;
+        pb.y = (njl < npB && q1) ? pb.y : 0.0;
+        double T0 = 0.0, T1 = 0.0;
+        asm_dmma(T0, T1, pb.x, w.x);
+        asm_dmma(T0, T1, pb.y, w.y);
+        // the lane's two columns of stage 2: pairs 8 nt + 2t and the next one
+        const int c = 8 * nt + 2 * t;
+        const bool vc0 = c < npB, vc1 = c + 1 < npB;
+        const int4 e0 = *reinterpret_cast<const int4 *>(pjl + (vc0 ? c : 0));
+        const int4 e1 = *reinterpret_cast<const int4 *>(pjl + (vc1 ? c + 1 : 0));
+        const int j0 = e0.w & 255, l0 = e0.w >> 8, j1 = e1.w & 255, l1 = e1.w >> 8;
+        const bool m0 = vc0 && e0.z >= 0, m1 = vc1 && e1.z >= 0; // the (l,j) image exists
+        double *D = slot + L.slot_arena + tb.dst_off;
+        // direct entries live at row r0 + (i,j), column c0 + (k,l); flipped ones at the transposed place
+        double *Dd0 = D + (tb.r0 + j0) * ld + tb.c0 + l0, *Df0 = D + (tb.c0 + l0) * ld + tb.r0 + j0;
+        double *Dm0 = D + (tb.r0 + l0) * ld + tb.c0 + j0, *Dn0 = D + (tb.c0 + j0) * ld + tb.r0 + l0;
+        double *Dd1 = D + (tb.r0 + j1) * ld + tb.c0 + l1, *Df1 = D + (tb.c0 + l1) * ld + tb.r0 + j1;
+        double *Dm1 = D + (tb.r0 + l1) * ld + tb.c0 + j1, *Dn1 = D + (tb.c0 + j1) * ld + tb.r0 + l1;
+        const DevS2Pair *pik = s2 + tb.s2_tab;
+        {
+            const int nik = 8 * mt + g;
+            const bool vik = nik < npA;
+            const DevS2Pair *pr = pik + (vik ? nik : 0);
+            const int4 d = *reinterpret_cast<const int4 *>(pr);
+            const int f1 = pr->f1;
+            double2 pa = *reinterpret_cast<const double2 *>(smem + d.x + 2 * t);
+            pa.x = (vik && q0) ? pa.x : 0.0;
+            pa.y = (vik && q1) ? pa.y : 0.0;
+            double v0 = 0.0, v1 = 0.0;
+            asm_dmma(v0, v1, pa.x, T0);
+            asm_dmma(v0, v1, pa.y, T1);
+            if (vik)
+            {
+                if (d.y >= 0)
+                {
+                    if (vc0)
+                        Dd0[d.y] = v0;
+                    if (m0)
+                        Dm0[d.y] = v0;
+                    if (vc1)
+                        Dd1[d.y] = v1;
+                    if (m1)
+                        Dm1[d.y] = v1;
+                }
+                if (d.z >= 0)
+                {
+                    if (vc0)
+                        Df0[d.z] = v0;
+                    if (m0)
+                        Dn0[d.z] = v0;
+                    if (vc1)
+                        Df1[d.z] = v1;
+                    if (m1)
+                        Dn1[d.z] = v1;
+                }
+                if (d.w >= 0)
+                {
+                    if (vc0)
+                        Dd0[d.w] = v0;
+                    if (m0)
+                        Dm0[d.w] = v0;
+                    if (vc1)
+                        Dd1[d.w] = v1;
+                    if (m1)
+                        Dm1[d.w] = v1;
+                }
+                if (f1 >= 0)
+                {
+                    if (vc0)
+                        Df0[f1] = v0;
+                    if (m0)
+                        Dn0[f1] = v0;
+                    if (vc1)
+                        Df1[f1] = v1;
+                    if (m1)
+                        Dn1[f1] = v1;
+                }
+            }
+        }
+    }
+}
+#endif
+
 // in-place SPD inverse of the n x n matrix (leading dimension ld) at arena + off of every slot (Gauss-Jordan,
 // no pivoting needed); the column / row of the pivot are staged in the slot's T region
 __device__ __forceinline__ void invert_spd_slots(const AsmArgs &args, int off, int n, int ld, int n_valid, int *bad)
@@ -570,14 +697,22 @@ template <int Q> __global__ void __launch_bounds__(ASM_THREADS, 2) element_matri
             if (threadIdx.x == 0)
                 emit_counter = 0;
             phase_weights<Q>(args, smem, sg, ws, pnts, wgts, elem0, n_valid);
-            for (int r = sg.round_begin; r < sg.round_end; ++r)
+#ifndef MFV2D_EMU
+            if (Q <= 8 && L.use_tc)
             {
-                const DevRound rd = rounds[r];
                 __syncthreads();
-                phase_s1<Q>(args, smem, rd, tbs, n_valid);
-                __syncthreads();
-                phase_s2<Q>(args, smem, rd, tbs, n_valid);
+                phase_tc<Q>(args, smem, sg, tbs, n_valid);
             }
+            else
+#endif
+                for (int r = sg.round_begin; r < sg.round_end; ++r)
+                {
+                    const DevRound rd = rounds[r];
+                    __syncthreads();
+                    phase_s1<Q>(args, smem, rd, tbs, n_valid);
+                    __syncthreads();
+                    phase_s2<Q>(args, smem, rd, tbs, n_valid);
+                }
             for (int d = sg.dense_begin; d < sg.dense_end; ++d)
                 if (dense[d].inverse)
                     invert_spd_slots(args, dense[d].smem_off, dense[d].rows, dense[d].ld, n_valid, bad);

@@ -762,6 +762,13 @@ int plan_finalize_matrix(mfv2d_plan *plan, const std::vector<std::vector<Lowered
     AsmLayout &L = plan->lay;
     L = AsmLayout{};
     L.ldq = ldq;
+    // q <= 8: the two contraction stages run on the tensor cores and T stays in registers (assembly.cu, phase_tc)
+#ifdef MFV2D_EMU
+    const bool use_tc = false;
+#else
+    const char *tc_env = getenv("MFV2D_ASM_DMMA");
+    const bool use_tc = q <= 8 && !(tc_env && tc_env[0] == '0');
+#endif
     int slot_w = 0, slot_t = 0, slot_a = 0;
     {
         size_t tb_i = 0;
@@ -781,7 +788,7 @@ int plan_finalize_matrix(mfv2d_plan *plan, const std::vector<std::vector<Lowered
             }
             for (; tb_i < plan->tbs.size() && plan->tbs[tb_i].round == (int)si; ++tb_i)
             {
-                const int t = plan->tbs[tb_i].nB * plan->tbs[tb_i].nB2 * ldq;
+                const int t = use_tc ? 0 : plan->tbs[tb_i].nB * plan->tbs[tb_i].nB2 * ldq;
                 ts += t;
                 tm = t > tm ? t : tm;
             }
@@ -848,6 +855,8 @@ int plan_finalize_matrix(mfv2d_plan *plan, const std::vector<std::vector<Lowered
     for (DevTB &tb : plan->tbs)
     {
         tb.s1_tab = (int)s1tab.size();
+        tb.npA = pair_n[tb.pkA];
+        tb.npB = pair_n[tb.pkB];
         for (int n = 0; n < pair_n[tb.pkB]; ++n)
         {
             const int pr = pairs[pair_off[tb.pkB] + n];
@@ -856,6 +865,7 @@ int plan_finalize_matrix(mfv2d_plan *plan, const std::vector<std::vector<Lowered
             e.pt = L.off_pt[tb.pkB == PK_EN ? PK_NE : tb.pkB] / 8 + row * ldq;
             e.t1 = (j * tb.nB2 + l) * ldq;
             e.t2 = (tb.pkB <= PK_EE && j != l) ? (l * tb.nB2 + j) * ldq : -1;
+            e.jl = j | (l << 8);
             s1tab.push_back(e);
         }
         tb.s2_tab = (int)s2tab.size();
@@ -873,6 +883,20 @@ int plan_finalize_matrix(mfv2d_plan *plan, const std::vector<std::vector<Lowered
             s2tab.push_back(e);
         }
     }
+
+    // work items of the tensor-core contraction: one warp takes 8 (j,l) pairs x 8 (i,k) pairs of one tensor block
+    std::vector<int32_t> tctab;
+    for (DevStage &sg : plan->stages)
+    {
+        sg.tc_begin = (int)tctab.size();
+        if (sg.round_end > sg.round_begin)
+            for (int t = plan->rounds[sg.round_begin].tb_begin; t < plan->rounds[sg.round_end - 1].tb_end; ++t)
+                for (int nt = 0; 8 * nt < plan->tbs[t].npB; ++nt)
+                    for (int mt = 0; 8 * mt < plan->tbs[t].npA; ++mt)
+                        tctab.push_back(t | (nt << 16) | (mt << 24));
+        sg.tc_count = (int)tctab.size() - sg.tc_begin;
+    }
+    L.use_tc = use_tc;
 
     // ---- chunking of the pair lists, elements per pass and the packed work items -------------------------
     // cost model of a round: passes of `threads` work items, each item costs a set-up plus its pairs
@@ -928,6 +952,7 @@ int plan_finalize_matrix(mfv2d_plan *plan, const std::vector<std::vector<Lowered
         sec(s1tab.size() * sizeof(DevS1Pair));
         sec(s2tab.size() * sizeof(DevS2Pair));
         sec(x_bound * sizeof(int32_t));
+        sec(tctab.size() * sizeof(int32_t));
         fixed_exact += 8 * 64 + 256; // corners of up to 8 slots, alignment slack
         long long epb = (per_cta - (long long)fixed_exact) / 8 / slot;
         if (epb < 1)
@@ -994,6 +1019,7 @@ int plan_finalize_matrix(mfv2d_plan *plan, const std::vector<std::vector<Lowered
     L.off_s1 = append(s1tab.data(), s1tab.size() * sizeof(DevS1Pair));
     L.off_s2 = append(s2tab.data(), s2tab.size() * sizeof(DevS2Pair));
     L.off_x = append(xtab.data(), xtab.size() * sizeof(int32_t));
+    L.off_tc = append(tctab.data(), tctab.size() * sizeof(int32_t));
     blob.resize((blob.size() + 15) & ~size_t(15));
     L.blob_bytes = (int)blob.size();
     L.off_cs = L.blob_bytes / 8;

@@ -115,7 +115,7 @@ struct DevTB
     int round;                // TB round inside the stage (rounds reuse the T region)
     int n_sub1, n_sub2;       // number of chunks the (j,l) / (i,k) pair lists are cut into
     int s1_tab, s2_tab;       // first entry of the block's DevS1Pair / DevS2Pair tables
-    int pad;
+    int npA, npB;             // entries of the (i,k) / (j,l) pair tables
 };
 
 // stage-1 work of one (j,l) pair: product-table row and where T goes
@@ -123,7 +123,7 @@ struct DevS1Pair
 {
     int pt;       // offset (doubles from the start of shared memory) of the row (B_j B2_l)(b)
     int t1, t2;   // offsets of T[(j,l)][0] and of its mirror image T[(l,j)][0] (-1: none) inside the block's T
-    int pad;
+    int jl;       // j | l << 8
 };
 
 // stage-2 work of one (i,k) pair: product-table row and the (up to four) images of the entry in the arena,
@@ -153,6 +153,7 @@ struct DevStage
     int unit_begin, unit_end;
     int w_begin, w_end;
     int round_begin, round_end;
+    int tc_begin, tc_count; // tensor-core work items of the stage (per element): tensor block | (j,l) tile << 16 | (i,k) tile << 24
 };
 
 // row of an incidence matrix in gather form: up to 4 (column, sign) pairs.  The sign is kept as the HIGH word
@@ -168,6 +169,7 @@ struct AsmLayout
 {
     int off_stages, off_dense, off_terms, off_blocks, off_units, off_ws, off_tbs, off_rounds;
     int off_s1, off_s2, off_x; // DevS1Pair / DevS2Pair tables and the packed work items
+    int off_tc, use_tc;        // work items of the tensor-core contraction (q <= 8), 1: the kernel takes that path
     int off_inc;      // DevIncRow rows of the four incidence kinds, inc_row0[kind] = first row
     int inc_row0[4];
     int off_pt[3];    // product tables NN, EE, NE: rows of ldq doubles
