@@ -270,9 +270,8 @@ __device__ __forceinline__ void asm_dmma(double &d0, double &d1, double a, doubl
                  : "d"(a), "d"(b));
 }
 
-// work item (per element): tensor block, tile of 8 (j,l) pairs, tile of 8 (i,k) pairs.  Stage 1: T = PT_B (8 pairs
-// x Q) W^T (Q x Q rows a) - two instructions, recomputed per (i,k) tile rather than shared; stage 2: PT_A (8 pairs
-// x Q) T^T, scattered to all images of the entries in the arena.
+// work item (per element): tensor block, tile of 8 (j,l) pairs.  Stage 1: T = PT_B (8 pairs x Q) W^T (Q x Q rows a);
+// stage 2, per tile of 8 (i,k) pairs: PT_A (8 pairs x Q) T^T, scattered to all images of the entries in the arena.
 template <int Q>
 __device__ __forceinline__ void phase_tc(const AsmArgs &args, double *smem, const DevStage &sg, const DevTB *tbs, int n_valid)
 {

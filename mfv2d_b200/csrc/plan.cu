@@ -458,7 +458,15 @@ int plan_finalize_matrix(mfv2d_plan *plan, const std::vector<std::vector<Lowered
 {
     mfv2d_ctx *ctx = plan->ctx;
     const int p = plan->p, q = plan->q, np1 = p + 1;
-    const int ldq = asm_ldq(q);
+    // q <= 8: the two contraction stages run on the tensor cores and T stays in registers (assembly.cu, phase_tc);
+    // its 16-byte fragment loads want rows of 8 doubles, the scalar path's row walks the padded length
+#ifdef MFV2D_EMU
+    const bool use_tc = false;
+#else
+    const char *tc_env = getenv("MFV2D_ASM_DMMA");
+    const bool use_tc = q <= 8 && !(tc_env && tc_env[0] == '0');
+#endif
+    const int ldq = use_tc ? 8 : asm_ldq(q);
     const int threads = 256; // ASM_THREADS of assembly.cu
 
     // ---- element-independent tables of the blob --------------------------------------------------
@@ -762,13 +770,6 @@ int plan_finalize_matrix(mfv2d_plan *plan, const std::vector<std::vector<Lowered
     AsmLayout &L = plan->lay;
     L = AsmLayout{};
     L.ldq = ldq;
-    // q <= 8: the two contraction stages run on the tensor cores and T stays in registers (assembly.cu, phase_tc)
-#ifdef MFV2D_EMU
-    const bool use_tc = false;
-#else
-    const char *tc_env = getenv("MFV2D_ASM_DMMA");
-    const bool use_tc = q <= 8 && !(tc_env && tc_env[0] == '0');
-#endif
     int slot_w = 0, slot_t = 0, slot_a = 0;
     {
         size_t tb_i = 0;
@@ -884,7 +885,7 @@ int plan_finalize_matrix(mfv2d_plan *plan, const std::vector<std::vector<Lowered
         }
     }
 
-    // work items of the tensor-core contraction: one warp takes 8 (j,l) pairs x 8 (i,k) pairs of one tensor block
+    // work items of the tensor-core contraction: one warp takes 8 (j,l) pairs of one tensor block
     std::vector<int32_t> tctab;
     for (DevStage &sg : plan->stages)
     {

@@ -153,7 +153,7 @@ struct DevStage
     int unit_begin, unit_end;
     int w_begin, w_end;
     int round_begin, round_end;
-    int tc_begin, tc_count; // tensor-core work items of the stage (per element): tensor block | (j,l) tile << 16 | (i,k) tile << 24
+    int tc_begin, tc_count; // tensor-core work items of the stage (per element): tensor block | (j,l) tile << 16
 };
 
 // row of an incidence matrix in gather form: up to 4 (column, sign) pairs.  The sign is kept as the HIGH word
