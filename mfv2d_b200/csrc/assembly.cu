@@ -258,11 +258,12 @@ __device__ __forceinline__ void phase_s2(const AsmArgs &args, double *smem, cons
 }
 
 #ifndef MFV2D_EMU
-// ---- S1 + S2 on the tensor cores (Q <= 8) --------------------------------------------------------------
+// ---- S1 + S2 on the tensor cores --------------------------------------------------------------
 // mma.sync m8n8k4 f64: lane (g = lane / 4, t = lane % 4) holds A[m = g][k = t], B[k = t][n = g] and
 // D[m = g][n = 2t, 2t + 1].  The two k-steps of a contraction over 8 quadrature points take the points 2t and
 // 2t + 1, so that a lane's pair of D values of stage 1 (T[(j,l) = g][a = 2t, 2t + 1]) is exactly its pair of B
-// operands of stage 2: T never leaves the registers and the two stages need no barrier between them.
+// operands of stage 2: T never leaves the registers and the two stages need no barrier between them.  More than
+// 8 points: NQ = 2 tiles of 8 (zero-padded by predicates), the same correspondence per tile.
 __device__ __forceinline__ void asm_dmma(double &d0, double &d1, double a, double b)
 {
     asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0, %1}, {%2}, {%3}, {%0, %1};"
@@ -282,7 +283,7 @@ __device__ __forceinline__ void phase_tc(const AsmArgs &args, double *smem, cons
     const DevS1Pair *s1 = reinterpret_cast<const DevS1Pair *>(sb + L.off_s1);
     const DevS2Pair *s2 = reinterpret_cast<const DevS2Pair *>(sb + L.off_s2);
     const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
-    const bool q0 = 2 * t < Q, q1 = 2 * t + 1 < Q; // the lane's two quadrature points exist
+    constexpr int NQ = (Q + 7) / 8; // tiles of 8 quadrature points
     const int per = sg.tc_count;
     const float inv_per = 1.0f / (float)per;
     for (int x = threadIdx.x >> 5; x < per * n_valid; x += blockDim.x >> 5)
@@ -293,18 +294,39 @@ __device__ __forceinline__ void phase_tc(const AsmArgs &args, double *smem, cons
         const int nt = (item >> 16) & 255, mt = item >> 24;
         double *slot = smem + L.off_slots + e * L.slot_stride;
         const int npA = tb.npA, npB = tb.npB, ld = tb.ld;
-        // stage 1
-        double2 w = *reinterpret_cast<const double2 *>(slot + L.slot_w + tb.w * (Q * ldq) + (g < Q ? g : 0) * ldq + 2 * t);
-        w.x = (g < Q && q0) ? w.x : 0.0;
-        w.y = (g < Q && q1) ? w.y : 0.0;
+        // stage 1: NQ tiles of 8 rows a, NQ pairs of k-steps over b
+        double T[NQ][2];
+        {
+            const DevS1Pair *pjl0 = s1 + tb.s1_tab;
+            const int njl = 8 * nt + g;
+            const bool vjl = njl < npB;
+            const double *ptb = smem + pjl0[vjl ? njl : 0].pt + 2 * t;
+            const double *wf = slot + L.slot_w + tb.w * (Q * ldq) + 2 * t;
+            double2 pb[NQ];
+#pragma unroll
+            for (int kb = 0; kb < NQ; ++kb)
+            {
+                pb[kb] = *reinterpret_cast<const double2 *>(ptb + 8 * kb);
+                pb[kb].x = (vjl && 8 * kb + 2 * t < Q) ? pb[kb].x : 0.0;
+                pb[kb].y = (vjl && 8 * kb + 2 * t + 1 < Q) ? pb[kb].y : 0.0;
+            }
+#pragma unroll
+            for (int na = 0; na < NQ; ++na)
+            {
+                const int a = 8 * na + g;
+                T[na][0] = T[na][1] = 0.0;
+#pragma unroll
+                for (int kb = 0; kb < NQ; ++kb)
+                {
+                    double2 w = *reinterpret_cast<const double2 *>(wf + (a < Q ? a : 0) * ldq + 8 * kb);
+                    w.x = (a < Q && 8 * kb + 2 * t < Q) ? w.x : 0.0;
+                    w.y = (a < Q && 8 * kb + 2 * t + 1 < Q) ? w.y : 0.0;
+                    asm_dmma(T[na][0], T[na][1], pb[kb].x, w.x);
+                    asm_dmma(T[na][0], T[na][1], pb[kb].y, w.y);
+                }
+            }
+        }
         const DevS1Pair *pjl = s1 + tb.s1_tab;
-        const int njl = 8 * nt + g;
-        double2 pb = *reinterpret_cast<const double2 *>(smem + pjl[njl < npB ? njl : 0].pt + 2 * t);
-        pb.x = (njl < npB && q0) ? pb.x : 0.0;
-        pb.y = (njl < npB && q1) ? pb.y : 0.0;
-        double T0 = 0.0, T1 = 0.0;
-        asm_dmma(T0, T1, pb.x, w.x);
-        asm_dmma(T0, T1, pb.y, w.y);
         // the lane's two columns of stage 2: pairs 8 nt + 2t and the next one
         const int c = 8 * nt + 2 * t;
         const bool vc0 = c < npB, vc1 = c + 1 < npB;
@@ -325,12 +347,16 @@ __device__ __forceinline__ void phase_tc(const AsmArgs &args, double *smem, cons
             const DevS2Pair *pr = pik + (vik ? nik : 0);
             const int4 d = *reinterpret_cast<const int4 *>(pr);
             const int f1 = pr->f1;
-            double2 pa = *reinterpret_cast<const double2 *>(smem + d.x + 2 * t);
-            pa.x = (vik && q0) ? pa.x : 0.0;
-            pa.y = (vik && q1) ? pa.y : 0.0;
             double v0 = 0.0, v1 = 0.0;
-            asm_dmma(v0, v1, pa.x, T0);
-            asm_dmma(v0, v1, pa.y, T1);
+#pragma unroll
+            for (int ka = 0; ka < NQ; ++ka)
+            {
+                double2 pa = *reinterpret_cast<const double2 *>(smem + d.x + 8 * ka + 2 * t);
+                pa.x = (vik && 8 * ka + 2 * t < Q) ? pa.x : 0.0;
+                pa.y = (vik && 8 * ka + 2 * t + 1 < Q) ? pa.y : 0.0;
+                asm_dmma(v0, v1, pa.x, T[ka][0]);
+                asm_dmma(v0, v1, pa.y, T[ka][1]);
+            }
             if (vik)
             {
                 if (d.y >= 0)
@@ -697,7 +723,7 @@ template <int Q> __global__ void __launch_bounds__(ASM_THREADS, 2) element_matri
                 emit_counter = 0;
             phase_weights<Q>(args, smem, sg, ws, pnts, wgts, elem0, n_valid);
 #ifndef MFV2D_EMU
-            if (Q <= 8 && L.use_tc)
+            if (L.use_tc)
             {
                 __syncthreads();
                 phase_tc<Q>(args, smem, sg, tbs, n_valid);

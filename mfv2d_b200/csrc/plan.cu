@@ -459,14 +459,16 @@ int plan_finalize_matrix(mfv2d_plan *plan, const std::vector<std::vector<Lowered
     mfv2d_ctx *ctx = plan->ctx;
     const int p = plan->p, q = plan->q, np1 = p + 1;
     // q <= 8: the two contraction stages run on the tensor cores and T stays in registers (assembly.cu, phase_tc);
-    // its 16-byte fragment loads want rows of 8 doubles, the scalar path's row walks the padded length
+    // its 16-byte fragment loads want rows of 8 doubles, the scalar path's row walks the padded length.  With two
+    // tiles of 8 points (q > 8) the path is correct but slower than the scalar one (mixed Poisson p6: 20.9M against
+    // 26.3M matrices/s), so it is only taken on request (MFV2D_ASM_DMMA=2; =0 turns it off altogether)
 #ifdef MFV2D_EMU
     const bool use_tc = false;
 #else
     const char *tc_env = getenv("MFV2D_ASM_DMMA");
-    const bool use_tc = q <= 8 && !(tc_env && tc_env[0] == '0');
+    const bool use_tc = (tc_env && tc_env[0] == '2') || (q <= 8 && !(tc_env && tc_env[0] == '0'));
 #endif
-    const int ldq = use_tc ? 8 : asm_ldq(q);
+    const int ldq = (use_tc && q <= 8) ? 8 : asm_ldq(q);
     const int threads = 256; // ASM_THREADS of assembly.cu
 
     // ---- element-independent tables of the blob --------------------------------------------------
