@@ -871,3 +871,7 @@ def compute_element_primal_from_dual(form_specs: _ElementFormSpecification, dual
     if isinstance(space_or_batch, ElementFemSpace2D):
         return compute_element_vector(form_specs, _mass_expressions(form_specs, True), space_or_batch, dual)
     return compute_element_vectors(form_specs, _mass_expressions(form_specs, True), space_or_batch, dual)
+
+
+# host containers of the module (src/algebra/svector.c, src/algebra/crs_matrix.c): same names as ``mfv2d._mfv2d``
+from .sparse import MatrixCRS, SparseVector  # noqa: E402,F401

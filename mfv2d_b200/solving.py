@@ -15,6 +15,7 @@ import numpy as np
 
 from ._capi import DEVICE, HOST, check, lib
 from .runtime import Context, DeviceArray, addr, get_context, space_of
+from .sparse import MatrixCRS, SparseVector, constraint_blocks_to_coo
 
 
 @dataclass(frozen=True)
@@ -63,6 +64,24 @@ def constraints_to_coo(constraints: Sequence[Constraint], offsets: np.ndarray):
     return row[order], col[order], val[order]
 
 
+def _is_block_pairs(obj) -> bool:
+    return (isinstance(obj, (tuple, list)) and len(obj) > 0
+            and all(isinstance(b, (tuple, list)) and len(b) == 2 and isinstance(b[1], MatrixCRS) for b in obj))
+
+
+def _check_trace_lists(pairs, n_trace: int, offsets: np.ndarray, indices: np.ndarray) -> None:
+    """``offsets`` / ``indices`` of the extension's constructor (sparse_system.h:27-32) against the constraint blocks:
+    multiplier ``i`` must list exactly the elements whose block has a non-empty row ``i``."""
+    if offsets.ndim != 1 or offsets.size != n_trace + 1 or indices.ndim != 1 or (offsets.size and offsets[-1] != indices.size):
+        raise ValueError("trace offsets / indices do not describe one element list per constraint row")
+    rows = [np.stack([m.nonempty_rows.astype(np.int64), np.full(m.nonempty_rows.size, e, np.int64)], 1) for e, (_, m) in enumerate(pairs)]
+    have = np.concatenate(rows) if rows else np.zeros((0, 2), np.int64)
+    want = np.stack([np.repeat(np.arange(n_trace), np.diff(offsets.astype(np.int64))), indices.astype(np.int64)], 1)
+    key = lambda a: a[np.lexsort((a[:, 1], a[:, 0]))]
+    if have.shape != want.shape or not np.array_equal(key(have), key(want)):
+        raise ValueError("trace offsets / indices disagree with the non-empty rows of the constraint blocks")
+
+
 class LinearSystem:
     """``[[A, N^T], [N, 0]]`` with block-diagonal ``A`` (one dense block per element) and the
     constraint matrix ``N`` (system_new / system_fill_out, src/algebra/system_objects.c:73-199).
@@ -79,6 +98,20 @@ class LinearSystem:
             n_elem, (element_matrices, constraints), n_trace = int(element_matrices), args[:2], None
             if len(element_matrices) != n_elem:
                 raise ValueError(f"expected {n_elem} element matrices, got {len(element_matrices)}")
+        elif _is_block_pairs(element_matrices):
+            # the extension type's own call, LinearSystem(blocks, offsets, indices) with blocks = ((A_e, MatrixCRS), ...)
+            # (system_new, src/algebra/system_objects.c:73-199): ``offsets`` / ``indices`` list the elements of
+            # every multiplier and are implied by the constraint blocks; they are checked, not needed
+            pairs, trace_offsets, trace_indices = element_matrices, constraints, n_trace
+            element_matrices = [a for a, _ in pairs]
+            n_trace = pairs[0][1].shape[0] if pairs else 0
+            sizes0 = np.array([np.shape(a)[0] for a in element_matrices], np.int64)
+            for a, m in pairs:
+                if m.shape != (n_trace, np.shape(a)[1]):
+                    raise ValueError(f"constraint block of shape {m.shape} does not match ({n_trace}, {np.shape(a)[1]})")
+            constraints = constraint_blocks_to_coo([m for _, m in pairs], np.concatenate([[0], np.cumsum(sizes0)]))
+            if trace_offsets is not None:
+                _check_trace_lists(pairs, n_trace, np.asarray(trace_offsets), np.asarray(trace_indices))
         if ctx is None and args and isinstance(args[0], Context):
             ctx = args[0]  # LinearSystem(matrices, constraints, n_trace, ctx)
         self.ctx = ctx or get_context()
@@ -126,6 +159,30 @@ class LinearSystem:
         except Exception:
             pass
         self.handle = None
+
+    def get_dense_blocks(self) -> tuple:
+        """The element matrices ``A_e`` as host arrays (system_objects.c:201-244)."""
+        if isinstance(self._blocks, DeviceArray):
+            flat = self._blocks.get().ravel()
+        else:
+            flat = self._blocks
+        o, sq = self.offsets, np.concatenate([[0], np.cumsum(np.diff(self.offsets) ** 2)])
+        return tuple(flat[sq[e]:sq[e + 1]].reshape(o[e + 1] - o[e], o[e + 1] - o[e]).copy() for e in range(self.n_elem))
+
+    def get_constraint_blocks(self) -> tuple:
+        """The per-element constraint blocks ``N_e`` as ``n_trace x N_e`` MatrixCRS (system_objects.c:246-290)."""
+        row, col, val = self.con
+        elem = np.searchsorted(self.offsets, col, side="right") - 1
+        order = np.lexsort((col, row, elem))
+        row, col, val, elem = row[order], col[order], val[order], elem[order]
+        first = np.searchsorted(elem, np.arange(self.n_elem + 1))
+        out = []
+        for e in range(self.n_elem):
+            lo, hi = first[e], first[e + 1]
+            m = MatrixCRS(self.n_trace, int(self.offsets[e + 1] - self.offsets[e]))
+            m.set_from_data(val[lo:hi], col[lo:hi] - self.offsets[e], np.bincount(row[lo:hi], minlength=self.n_trace))
+            out.append(m)
+        return tuple(out)
 
     # ---- operators (sparse_system.c:3-207); numpy in -> numpy out, DeviceArray in -> DeviceArray out ----
     def _apply(self, fn, x, n_in: int, n_out: int, out=None, dense_out: bool = True):
@@ -488,14 +545,18 @@ class TraceVector(_SystemVector):
         self._init(parent, self._from_host(parent, value).data)
 
     def as_split(self) -> tuple:
-        """per element: (indices of its multipliers, their values) - the content of the reference's SparseVectors"""
+        """per element: a SparseVector of dimension ``n_trace`` with the values of its multipliers
+        (trace_vector_as_split, system_objects.c:1560-1600)"""
         merged = self.as_merged()
         row, col, _ = self._parent.con
         elem = np.searchsorted(self._parent.offsets, col, side="right") - 1
+        order = np.lexsort((row, elem))
+        row, elem = row[order], elem[order]
+        first = np.searchsorted(elem, np.arange(self._parent.n_elem + 1))
         out = []
         for e in range(self._parent.n_elem):
-            idx = np.unique(row[elem == e])
-            out.append((idx, merged[idx]))
+            idx = np.unique(row[first[e]:first[e + 1]])
+            out.append(SparseVector._make(self._parent.n_trace, idx.astype(np.uint64), merged[idx]))
         return tuple(out)
 
 

@@ -356,6 +356,42 @@ def check_linear_system(M, SV, ST, fix, nh, nv):
     assert relerr(sysm.apply_diagonal_inverse(g["x"]), g["apply_diagonal_inverse"]) < 1e-9
     assert relerr(sysm.apply_trace(g["x"]), g["apply_trace"]) < 1e-12
     assert relerr(sysm.apply_trace_transpose(g["trace_in"]), g["apply_trace_transpose"]) < 1e-12
+    # the extension type's own constructor, LinearSystem(((A_e, MatrixCRS), ...), offsets, indices), fed the way
+    # python/mfv2d/solving.py:62-97 feeds it: one build_row per (constraint, element)
+    blocks = sysm.get_constraint_blocks()
+    dense = sysm.get_dense_blocks()
+    assert len(blocks) == len(dense) == sysm.n_elem and np.array_equal(dense[0], mats[0]) and blocks[0].shape == (nt, ne)
+    elem = col // ne
+    rebuilt = tuple((dense[e], SV.MatrixCRS(nt, ne)) for e in range(sysm.n_elem))
+    order_rc = np.lexsort((col, elem, row))
+    r_s, e_s, c_s, v_s = row[order_rc], elem[order_rc], col[order_rc] - elem[order_rc] * ne, val[order_rc]
+    cuts = np.flatnonzero(np.diff(r_s * sysm.n_elem + e_s)) + 1
+    starts, stops = np.concatenate([[0], cuts]), np.concatenate([cuts, [r_s.size]])
+    next_row = np.zeros(sysm.n_elem, np.int64)
+    t_len, t_elem = np.zeros(nt, np.int64), []
+    for lo, hi in zip(starts, stops):
+        e, r = int(e_s[lo]), int(r_s[lo])
+        for empty in range(next_row[e], r):
+            rebuilt[e][1].build_row(empty)
+        rebuilt[e][1].build_row(r, SV.SparseVector.from_entries(ne, c_s[lo:hi], v_s[lo:hi]))
+        next_row[e] = r + 1
+        t_len[r] += 1
+        t_elem.append(e)
+    for e in range(sysm.n_elem):
+        for empty in range(next_row[e], nt):
+            rebuilt[e][1].build_row(empty)
+        assert np.array_equal(rebuilt[e][1].position_pairs, blocks[e].position_pairs) and np.array_equal(rebuilt[e][1].values, blocks[e].values)
+    t_off = np.concatenate([[0], np.cumsum(t_len)]).astype(np.uint32)
+    sys2 = SV.LinearSystem(rebuilt, t_off, np.array(t_elem, np.uint32))
+    assert np.array_equal(sys2.apply_trace(g["x"]), sysm.apply_trace(g["x"]))
+    assert np.array_equal(sys2.apply_diagonal_inverse(g["x"]), sysm.apply_diagonal_inverse(g["x"]))
+    assert np.array_equal(sys2.apply_trace_transpose(g["trace_in"]), sysm.apply_trace_transpose(g["trace_in"]))
+    try:
+        SV.LinearSystem(rebuilt, t_off, np.array(t_elem[::-1], np.uint32))
+        raise AssertionError("wrong element lists accepted")
+    except ValueError:
+        pass
+    del sys2
     t = g["trace_in"]
     composed = sysm.apply_trace(sysm.apply_diagonal_inverse(sysm.apply_trace_transpose(t)))
     assert relerr(sysm.apply_full_trace_system(t), composed) < 1e-12
@@ -411,7 +447,8 @@ def check_linear_system(M, SV, ST, fix, nh, nv):
     SV.TraceVector.scale(tv, 2.0, tv)
     assert relerr(tv.as_merged(), 2.0 * g["trace_in"]) < 1e-15
     assert abs(SV.TraceVector.dot(tv, tv) - 4.0 * g["trace_in"] @ g["trace_in"]) < 1e-10 * abs(4.0 * g["trace_in"] @ g["trace_in"]) + 1e-300
-    idx0, val0 = tv.as_split()[0]
+    sv0 = tv.as_split()[0]
+    idx0, val0 = sv0.indices.astype(np.int64), sv0.values
     assert np.array_equal(val0, 2.0 * g["trace_in"][idx0]) and idx0.size > 0
     xs_, ls_, _, its_ = SV.solve_schur_iterative(sysm, SV.DenseVector(sysm, *np.split(g["rhs"], sysm.offsets[1:-1])),
                                                 SV.TraceVector(sysm, g["con_rhs"]), SV.ConvergenceSettings(2000, 1e-30, 1e-12))
