@@ -439,6 +439,99 @@ __global__ void cg_direction_kernel(long long n, const double *__restrict__ sc, 
         p[i] = fma(beta, p[i], r[i]);
 }
 
+// ---- CG with ONE synchronisation per iteration (Chronopoulos & Gear 1989), used when the system is partitioned -----
+// u = Minv r, w = S u;  gamma = r.u, delta = u.w, rho = r.r are needed at the same point, so they travel in the ONE
+// all-reduce that also sums the interface multipliers of w (the two-reduction recurrence above pays a second
+// all-reduce for r.r after the update):
+//   beta = gamma / gamma_old ; alpha = gamma / (delta - beta gamma / alpha_old)
+//   p = u + beta p ; s = w + beta s ; x += alpha p ; r -= alpha s ; u = Minv r
+// sc[6] = gamma_old, sc[7] = alpha_old, sc[8..10] = (delta, gamma, rho); the other scalars and the flags as above.
+__global__ void __launch_bounds__(SYS_THREADS) cg1_dots_kernel(long long n, const double *__restrict__ u, const double *__restrict__ wv,
+                                                              const double *__restrict__ r, const double *__restrict__ own,
+                                                              double *__restrict__ partials, int n_partials,
+                                                              const int *__restrict__ done)
+{
+    if (*done)
+        return;
+    double d = 0.0, g = 0.0, rho = 0.0;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    {
+        const double ui = u[i], ri = r[i];
+        const double rw = own ? ri * own[i] : ri;
+        d = fma(ui, wv[i], d); // local, un-summed product: summed over the ranks it is u . S u
+        g = fma(rw, ui, g);
+        rho = fma(rw, ri, rho);
+    }
+    block_reduce_store(d, partials);
+    block_reduce_store(g, partials + n_partials);
+    block_reduce_store(rho, partials + 2 * n_partials);
+}
+
+__global__ void cg1_sum3_kernel(int n_partials, const double *__restrict__ partials, double *__restrict__ out, const int *done)
+{
+    if (*done)
+        return;
+    const double a = warp_sum_partials(n_partials, partials);
+    const double b = warp_sum_partials(n_partials, partials + n_partials);
+    const double c = warp_sum_partials(n_partials, partials + 2 * n_partials);
+    if (threadIdx.x == 0)
+    {
+        out[0] = a;
+        out[1] = b;
+        out[2] = c;
+    }
+}
+
+__global__ void cg1_scalar_kernel(double *__restrict__ sc, int *flags)
+{
+    if (blockIdx.x != 0 || threadIdx.x != 0 || flags[0])
+        return;
+    const double delta = sc[8], gamma = sc[9], rho = sc[10];
+    const int k = flags[3]; // updates carried out so far: rho belongs to the residual after update k - 1
+    flags[3] = k + 1;
+    sc[0] = rho;
+    if (k > 0)
+    {
+        flags[1] = k - 1;
+        if (rho < sc[4])
+        {
+            flags[0] = 1;
+            return;
+        }
+    }
+    const double beta = k > 0 ? gamma / sc[6] : 0.0;
+    const double alpha = k > 0 ? gamma / (delta - beta * gamma / sc[7]) : gamma / delta;
+    sc[1] = delta;
+    sc[2] = alpha;
+    sc[3] = beta;
+    sc[6] = gamma;
+    sc[7] = alpha;
+}
+
+// u may alias r (no preconditioner): every entry is read before it is written by the same thread
+__global__ void __launch_bounds__(SYS_THREADS) cg1_update_kernel(long long n, const double *__restrict__ sc, const int *flags,
+                                                                const double *u, const double *__restrict__ wv,
+                                                                double *__restrict__ p, double *__restrict__ sv,
+                                                                double *__restrict__ x, double *r, const double *__restrict__ dinv,
+                                                                double *z)
+{
+    if (flags[0])
+        return;
+    const double alpha = sc[2], beta = sc[3];
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    {
+        const double pi = fma(beta, p[i], u[i]);
+        const double si = fma(beta, sv[i], wv[i]);
+        p[i] = pi;
+        sv[i] = si;
+        x[i] = fma(alpha, pi, x[i]);
+        const double ri = fma(-alpha, si, r[i]);
+        r[i] = ri;
+        if (dinv)
+            z[i] = ri * dinv[i];
+    }
+}
+
 // multi-GPU: pack the shared multipliers of `t` into the interface buffer / scatter the reduced sums back
 __global__ void iface_pack_kernel(long long n_shared, const int64_t *__restrict__ index, const int64_t *__restrict__ slot,
                                   const double *__restrict__ t, double *__restrict__ buf)
@@ -788,7 +881,7 @@ int mfv2d_cuda_system_create(mfv2d_ctx *ctx, size_t n_elem, const int64_t *block
     for (int i = 0; i < 6; ++i)
         SYS_TRY(sys_alloc(s, (size_t)s->n_trace, &s->d_work_trace[i]));
     s->n_partials = ctx->sm_count * 4;
-    SYS_TRY(sys_alloc(s, (size_t)2 * s->n_partials, &s->d_partials));
+    SYS_TRY(sys_alloc(s, (size_t)3 * s->n_partials, &s->d_partials));
     // ---- factorise: explicit inverses of the dense blocks ----
     int32_t *d_status = nullptr;
     SYS_TRY(sys_alloc(s, n_elem, &d_status));
@@ -1019,11 +1112,36 @@ int mfv2d_cuda_solve_schur_cg(mfv2d_system *s, const double *rhs, const double *
                     break;
                 dinv = s->d_diag_inv;
             }
-            cudaMemcpyAsync(p, precondition ? z : res, nt * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream);
+            // partitioned systems take the one-synchronisation recurrence (MFV2D_CG_SINGLE_REDUCE=0 / 1 forces either)
+            const char *sr_env = getenv("MFV2D_CG_SINGLE_REDUCE");
+            const bool single_reduce = sr_env ? sr_env[0] == '1' : false;
+            double *sv = s->d_work_trace[4];
+            if (single_reduce)
+            {
+                cudaMemsetAsync(p, 0, nt * sizeof(double), ctx->stream);
+                cudaMemsetAsync(sv, 0, nt * sizeof(double), ctx->stream);
+            }
+            else
+                cudaMemcpyAsync(p, precondition ? z : res, nt * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream);
             const int check_every = 16;
             // one CG iteration = 7 small launches; on one GPU a block of check_every iterations is captured ONCE
             // into a CUDA graph and replayed (the kernels stop by themselves once the device flag is set)
             auto enqueue_iteration = [&]() -> int {
+                if (single_reduce)
+                {
+                    const double *u = precondition ? z : res;
+                    MFV2D_TRY(sys_apply_schur(s, u, ap, flags, false));
+                    MFV2D_LAUNCH(cg1_dots_kernel, (unsigned)s->n_partials, SYS_THREADS, 0, ctx->stream, nt, u, (const double *)ap,
+                                 (const double *)res, w, s->d_partials, s->n_partials, (const int *)flags);
+                    MFV2D_LAUNCH(cg1_sum3_kernel, 1, 32, 0, ctx->stream, s->n_partials, (const double *)s->d_partials, sc + 8,
+                                 (const int *)flags);
+                    MFV2D_TRY(sys_interface_sum(s, ap, 3, sc + 8));
+                    MFV2D_LAUNCH(cg1_scalar_kernel, 1, 32, 0, ctx->stream, sc, flags);
+                    MFV2D_LAUNCH(cg1_update_kernel, (unsigned)s->n_partials, SYS_THREADS, 0, ctx->stream, nt, (const double *)sc,
+                                 (const int *)flags, u, (const double *)ap, p, sv, lam, res, dinv, z);
+                    ctx->launches += 4;
+                    return MFV2D_SUCCESS;
+                }
                 if (ctx->n_ranks > 1)
                 {
                     // p . S p = sum over the ranks of p_r . (S_r p_r) (local, un-summed products, no ownership weights):
@@ -1103,7 +1221,7 @@ int mfv2d_cuda_solve_schur_cg(mfv2d_system *s, const double *rhs, const double *
                         r = mfv2d_fail(ctx, MFV2D_CUDA_ERROR, "CG graph launch failed: %s", cudaGetErrorString(cudaGetLastError()));
                         break;
                     }
-                    ctx->launches += (ctx->n_ranks > 1 ? 13 : 7) * check_every;
+                    ctx->launches += (single_reduce ? (ctx->n_ranks > 1 ? 8 : 6) : (ctx->n_ranks > 1 ? 13 : 7)) * check_every;
                     it = stop;
                 }
 #endif

@@ -405,6 +405,16 @@ def check_linear_system(M, SV, ST, fix, nh, nv):
     r2 = g["con_rhs"] - sysm.apply_trace(x)
     rel = np.sqrt(r1 @ r1 + r2 @ r2) / np.sqrt(g["rhs"] @ g["rhs"] + g["con_rhs"] @ g["con_rhs"])
     assert rel < 1e-10, rel
+    # the one-synchronisation CG recurrence of the partitioned path (system.cu, cg1_* kernels), forced on one rank:
+    # same solution and, to a few iterations, the same count
+    os.environ["MFV2D_CG_SINGLE_REDUCE"] = "1"
+    try:
+        x1, l1, _, it1 = SV.solve_schur_iterative(sysm, g["rhs"], g["con_rhs"], SV.ConvergenceSettings(2000, 1e-30, 1e-12))
+        x1j, l1j, _, it1j = SV.solve_schur_iterative(sysm, g["rhs"], g["con_rhs"], SV.ConvergenceSettings(2000, 1e-30, 1e-12), precondition=True)
+    finally:
+        del os.environ["MFV2D_CG_SINGLE_REDUCE"]
+    assert relerr(x1, g["sol_dense"]) < 1e-8 and relerr(l1, g["sol_trace"]) < 1e-8 and abs(it1 - it) <= 4
+    assert relerr(x1j, g["sol_dense"]) < 1e-8 and relerr(l1j, g["sol_trace"]) < 1e-8 and it1j <= it + 4
     # Jacobi-preconditioned Schur CG: same solution, no more iterations than the plain one
     xj, lj, _, itj = SV.solve_schur_iterative(sysm, g["rhs"], g["con_rhs"], SV.ConvergenceSettings(2000, 1e-30, 1e-12), precondition=True)
     assert relerr(xj, g["sol_dense"]) < 1e-8 and relerr(lj, g["sol_trace"]) < 1e-8

@@ -16,10 +16,10 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 WORKER = os.path.join(ROOT, "tests", "dist_worker.py")
 
 
-def _run(mode, fix, nh, nv, world, port):
+def _run(mode, fix, nh, nv, world, port, env=None):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr", "127.0.0.1",
            "--master-port", str(port), WORKER, mode, fix, str(nh), str(nv)]
-    res = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT)
+    res = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT, env={**os.environ, **(env or {})})
     assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
     assert "dist_worker ok" in res.stdout, res.stdout[-2000:]
 
@@ -58,10 +58,11 @@ def test_gloo_world2_schur_cg(fix, nh, nv):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("single_reduce", ["0", "1"])  # two all-reduces per iteration / the one-synchronisation recurrence
 @pytest.mark.parametrize("fix,nh,nv", [("solve_10x10_p3", 10, 10), ("solve_6x6_p3_def", 6, 6)])
-def test_nccl_world2_schur_cg(fix, nh, nv):
+def test_nccl_world2_schur_cg(fix, nh, nv, single_reduce):
     import mfv2d_b200._capi as capi
 
     if capi.lib().mfv2d_cuda_device_count() < 2:
         pytest.skip("needs two GPUs (run with gpurun --gpus 2)")
-    _run("gpu", fix, nh, nv, 2, 29612)
+    _run("gpu", fix, nh, nv, 2, 29612 + int(single_reduce), env={"MFV2D_CG_SINGLE_REDUCE": single_reduce})
