@@ -1114,7 +1114,7 @@ int mfv2d_cuda_solve_schur_cg(mfv2d_system *s, const double *rhs, const double *
             }
             // partitioned systems take the one-synchronisation recurrence (MFV2D_CG_SINGLE_REDUCE=0 / 1 forces either)
             const char *sr_env = getenv("MFV2D_CG_SINGLE_REDUCE");
-            const bool single_reduce = sr_env ? sr_env[0] == '1' : false;
+            const bool single_reduce = sr_env ? sr_env[0] == '1' : ctx->n_ranks > 1;
             double *sv = s->d_work_trace[4];
             if (single_reduce)
             {
