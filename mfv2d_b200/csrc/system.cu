@@ -1259,6 +1259,24 @@ int mfv2d_cuda_solve_schur_cg(mfv2d_system *s, const double *rhs, const double *
             MFV2D_LAUNCH(axpby_kernel, grid_for(ctx, nd, 256), 256, 0, ctx->stream, nd, 1.0, (const double *)inv_a_y, -1.0,
                          (const double *)tmp_d2, (double *)sx.dev);
             ctx->launches++;
+            // one step of iterative refinement of the element-local solves, x += A^-1 (y - N^T lambda - A x): the blocks
+            // are applied as explicit inverses, whose residual grows with cond(A_e) (the 1-form and 2-form masses of a
+            // small element differ by 1/h^2); MFV2D_SCHUR_REFINE=0 turns it off
+            const char *rf_env = getenv("MFV2D_SCHUR_REFINE");
+            if (!(rf_env && rf_env[0] == '0'))
+            {
+                if ((r = sys_gemv(s, s->d_A, (const double *)sx.dev, tmp_d2)))
+                    break;
+                MFV2D_LAUNCH(axpby_kernel, grid_for(ctx, nd, 256), 256, 0, ctx->stream, nd, 1.0, (const double *)srhs.dev, -1.0,
+                             (const double *)tmp_d2, tmp_d2);
+                MFV2D_LAUNCH(axpby_kernel, grid_for(ctx, nd, 256), 256, 0, ctx->stream, nd, 1.0, (const double *)tmp_d2, -1.0,
+                             (const double *)tmp_d, tmp_d2);
+                if ((r = sys_gemv(s, s->d_Ainv, tmp_d2, inv_a_y)))
+                    break;
+                MFV2D_LAUNCH(axpby_kernel, grid_for(ctx, nd, 256), 256, 0, ctx->stream, nd, 1.0, (const double *)sx.dev, 1.0,
+                             (const double *)inv_a_y, (double *)sx.dev);
+                ctx->launches += 3;
+            }
         }
     } while (0);
     if (!r)
