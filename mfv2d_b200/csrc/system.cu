@@ -1241,6 +1241,8 @@ int mfv2d_cuda_solve_schur_cg(mfv2d_system *s, const double *rhs, const double *
                 res_mag2 = h[0];
                 it_done = hf[1];
                 finished = hf[0] != 0;
+                if (single_reduce && !finished)
+                    it_done = it - 1; // the one-synchronisation recurrence tests the residual one product later
             }
 #ifndef MFV2D_EMU
             if (graph_exec)
