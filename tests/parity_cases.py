@@ -528,3 +528,43 @@ def check_projectors(M):
     b2 = M.Basis1D(3, M.IntegrationRule1D(5))
     with pytest.raises(ValueError):
         M.compute_element_projector((1,), M.Basis2D(b2, b2), sp)
+
+
+def check_saddle_residual_small_elements(M, SV, ST, nh=12, nv=10, p=4, scale=2e-3):
+    """north_star: solutions within 1e-10 relative residual.  On small elements (h ~ 1e-3, as on the 1000 x 1000 mesh of
+    BASELINE.json configs[4]) the 2-form mass is ~1/h^2 times the 1-form mass and the element blocks, applied as
+    explicit inverses, lose cond(A_e) * eps: the solve's refinement step (system.cu) has to bring the residual of
+    the saddle-point system [[A, N^T], [N, 0]] back below the gate."""
+    s = SYSTEMS["mixed_poisson"]
+    specs = specs_of(M, s)
+
+    def deform(xi, eta):
+        return (xi + 0.1 * np.sin(np.pi * xi) * np.sin(np.pi * eta), eta - 0.1 * np.sin(np.pi * xi) * np.sin(np.pi * eta))
+
+    corners = np.ascontiguousarray(ST.unit_square_corners(nh, nv, deform) * scale)
+    batch = M.ElementBatch(make_basis(M, p, 3), corners)
+    mats = M.compute_element_matrices(specs, s["lhs"], batch)
+    row, col, val, nt = ST.continuity_constraints_1form(nh, nv, p, s["form_orders"])
+    sysm = SV.LinearSystem(mats, (row, col, val), nt)
+    # right-hand side as in profiles/config4_solve.py: dual DoFs of a smooth source on the 2-form rows
+    ne = specs.total_size(p, p)
+    rhs = np.zeros((corners.shape[0], ne))
+    rhs[:, specs.form_offset(1, p, p):] = batch.dual_dofs(s["form_orders"][1], lambda x, y: np.cos(np.pi * x / scale) * np.cos(np.pi * y / scale))
+    rhs, phi = rhs.ravel(), np.zeros(nt)
+
+    def residual(refine):
+        os.environ["MFV2D_SCHUR_REFINE"] = refine
+        try:
+            x, lam, _, it = SV.solve_schur_iterative(sysm, rhs, phi, SV.ConvergenceSettings(20000, 1e300, 1e-13))
+        finally:
+            del os.environ["MFV2D_SCHUR_REFINE"]
+        r1 = rhs - sysm.apply_diagonal(x) - sysm.apply_trace_transpose(lam)
+        r2 = phi - sysm.apply_trace(x)
+        return np.sqrt(r1 @ r1 + r2 @ r2) / np.sqrt(rhs @ rhs), it
+
+    res_plain, it0 = residual("0")
+    res_refined, it1 = residual("1")
+    assert it0 == it1 and it0 < 20000
+    assert res_refined < 1e-10, (res_plain, res_refined)
+    assert res_refined <= res_plain
+    return res_plain, res_refined

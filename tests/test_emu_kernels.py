@@ -89,3 +89,7 @@ def test_generic_chain(emu):
 @pytest.mark.parametrize("fix,nh,nv", [("solve_3x4_p4", 3, 4), ("solve_5x2_p5_def", 5, 2), ("solve_6x6_p3_def", 6, 6)])
 def test_linear_system(emu, fix, nh, nv):
     P.check_linear_system(*emu, fix, nh, nv)
+
+
+def test_saddle_residual_small_elements(emu):
+    P.check_saddle_residual_small_elements(*emu, nh=6, nv=5, p=3)

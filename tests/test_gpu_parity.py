@@ -92,6 +92,10 @@ def test_linear_system(gpu, fix, nh, nv):
     P.check_linear_system(*gpu, fix, nh, nv)
 
 
+def test_saddle_residual_small_elements(gpu):
+    P.check_saddle_residual_small_elements(*gpu, nh=6, nv=5, p=6)
+
+
 def test_empty_batches(gpu):
     M = gpu[0]
     b = P.make_basis(M, 3, 3)
