@@ -564,7 +564,7 @@ def check_saddle_residual_small_elements(M, SV, ST, nh=12, nv=10, p=4, scale=2e-
 
     res_plain, it0 = residual("0")
     res_refined, it1 = residual("1")
-    assert it0 == it1 and it0 < 20000
+    assert abs(it0 - it1) <= 2 and it0 < 20000
     assert res_refined < 1e-10, (res_plain, res_refined)
     assert res_refined <= res_plain
     return res_plain, res_refined
