@@ -339,8 +339,9 @@ MFV2D_API int mfv2d_cuda_vec_dot(mfv2d_ctx *ctx, size_t n, const double *x, cons
 /* solve_schur_iterative (python/mfv2d/solving.py:439-500) with cg_general (:350-436) running on
  * the device: lambda from CG on S, then x = A^-1 y - A^-1 N^T lambda.
  *   rhs[n_dense], phi[n_trace] -> x[n_dense], lambda[n_trace]; residual = sqrt(r.r) at exit,
- *   iterations = the reference's iter_cnt.  precondition != 0 switches to block-Jacobi-preconditioned
- *   CG on the trace space (not in the reference; identical solution to tolerance). */
+ *   iterations = the reference's iter_cnt.  precondition: 0 = none (the reference's method), 1 = Jacobi on the
+ *   trace space, 2 = Jacobi + coarse space (mfv2d_cuda_system_set_coarse_space); neither is in the reference,
+ *   the solution is the same to tolerance. */
 MFV2D_API int mfv2d_cuda_solve_schur_cg(mfv2d_system *sys, const double *rhs, const double *phi, int max_iter,
                                         double atol, double rtol, int precondition, double *x, double *lambda,
                                         double *residual, int *iterations, int space);
@@ -367,6 +368,27 @@ MFV2D_API int mfv2d_cuda_comm_allreduce_sum(mfv2d_ctx *ctx, double *dptr, size_t
  * apply_trace / apply_schur / vec dot on trace vectors include the NCCL interface sum. */
 MFV2D_API int mfv2d_cuda_system_set_interface(mfv2d_system *sys, size_t n_shared, const int64_t *shared_index,
                                               const int64_t *slot, size_t n_slots, const uint8_t *owned);
+
+/* ---- NVLink peer exchange: the interface sums and Krylov scalars written by the solver's own kernels straight into
+ * the other ranks' memory (replaces the ncclAllReduce inside every iteration) ----
+ * 1. every rank: peer_export (after set_interface) allocates its exchange block and returns an IPC handle of
+ *    mfv2d_cuda_peer_handle_size() bytes; n_coarse reserves room for the coarse residual of the two-level preconditioner;
+ * 2. the host gathers the handles rank-major by any means (as for the NCCL unique id);
+ * 3. every rank: peer_connect maps the other blocks; holder_ptr[n_shared + 1] / holder_rank[] list, for each shared
+ *    multiplier in the order of set_interface, the OTHER ranks that hold it (ascending).
+ * NCCL is then no longer needed by this system (mfv2d_cuda_comm_init may be called with id_bytes == NULL). */
+MFV2D_API int mfv2d_cuda_peer_handle_size(void);
+MFV2D_API int mfv2d_cuda_system_peer_export(mfv2d_system *sys, size_t n_coarse, void *handle_bytes);
+MFV2D_API int mfv2d_cuda_system_peer_connect(mfv2d_system *sys, const void *handles_all, size_t n_shared,
+                                             const int64_t *holder_ptr, const int32_t *holder_rank);
+/* non-zero after a peer wait timed out (a rank died): results of that call are invalid */
+MFV2D_API int mfv2d_cuda_system_peer_error(mfv2d_system *sys);
+
+/* Coarse space of the two-level preconditioner of solve_schur_cg (precondition = 2): agg[n_trace] = aggregate
+ * (0 .. n_coarse - 1, or -1) of each multiplier of this rank, z[n_trace] = near-null-space vector of S = N A^-1 N^T on
+ * them (identical on the ranks sharing a multiplier).  Collective on a partitioned system.  The reference has no
+ * counterpart (its only preconditioner is block-Jacobi, python/mfv2d/solving.py:656-661). */
+MFV2D_API int mfv2d_cuda_system_set_coarse_space(mfv2d_system *sys, size_t n_coarse, const int32_t *agg, const double *z);
 
 #ifdef __cplusplus
 }

@@ -114,6 +114,11 @@ SIGNATURES = {
     "mfv2d_cuda_comm_destroy": (i32, [vp]),
     "mfv2d_cuda_comm_allreduce_sum": (i32, [vp, dp, sz]),
     "mfv2d_cuda_system_set_interface": (i32, [vp, sz, vp, vp, sz, vp]),
+    "mfv2d_cuda_peer_handle_size": (i32, []),
+    "mfv2d_cuda_system_peer_export": (i32, [vp, sz, vp]),
+    "mfv2d_cuda_system_peer_connect": (i32, [vp, vp, sz, vp, vp]),
+    "mfv2d_cuda_system_peer_error": (i32, [vp]),
+    "mfv2d_cuda_system_set_coarse_space": (i32, [vp, sz, vp, vp]),
 }
 
 

@@ -72,7 +72,8 @@ int comm_allreduce(mfv2d_ctx *ctx, double *dptr, size_t n)
     if (ctx->n_ranks <= 1 || n == 0)
         return MFV2D_SUCCESS;
     if (!ctx->nccl_comm)
-        return mfv2d_fail(ctx, MFV2D_CUDA_NCCL_ERROR, "all-reduce requested without a communicator");
+        return mfv2d_fail(ctx, MFV2D_CUDA_NCCL_ERROR, "all-reduce requested without an NCCL communicator (and the peer exchange of this system "
+                                                      "is not connected)");
     const int rc = g_nccl.all_reduce(dptr, dptr, n, NCCL_FLOAT64, NCCL_SUM, ctx->nccl_comm, ctx->stream);
     if (rc != 0)
         return mfv2d_fail(ctx, MFV2D_CUDA_NCCL_ERROR, "ncclAllReduce failed: %s",
@@ -102,7 +103,7 @@ int mfv2d_cuda_comm_init(mfv2d_ctx *ctx, int n_ranks, int rank, const void *id_b
         return mfv2d_fail(ctx, MFV2D_BAD_ARGUMENT, "comm_init: bad rank %d of %d", rank, n_ranks);
     ctx->n_ranks = n_ranks;
     ctx->rank = rank;
-    if (n_ranks == 1)
+    if (n_ranks == 1 || !id_bytes) // id_bytes == NULL: ranks only, every exchange goes through the mapped peer blocks (peer.cu)
         return MFV2D_SUCCESS;
     if (!load_nccl())
         return mfv2d_fail(ctx, MFV2D_CUDA_NCCL_ERROR, "libnccl.so.2 could not be loaded");

@@ -15,51 +15,9 @@
 #include <algorithm>
 #include <cmath>
 
-#include "internal.cuh"
+#include "system.cuh"
 
 int launch_inverse_batch(mfv2d_ctx *ctx, int n, size_t batch, const double *d_in, double *d_out, int32_t *d_status);
-int comm_allreduce(mfv2d_ctx *ctx, double *dptr, size_t n);
-
-struct mfv2d_system
-{
-    mfv2d_ctx *ctx;
-    int64_t n_elem = 0, n_dense = 0, n_trace = 0, n_con = 0, n_slots = 0;
-    int max_n = 0, max_m = 0;
-    bool uniform = false; // all blocks have the same size
-    // device arrays
-    int64_t *d_block_off = nullptr; // [n_elem+1] dense offsets
-    int64_t *d_mat_off = nullptr;   // [n_elem+1] offsets into A / Ainv
-    double *d_A = nullptr, *d_Ainv = nullptr;
-    bool owns_A = true;
-    int64_t *d_n_ptr = nullptr, *d_n_col = nullptr; // N   CSR  [n_trace+1], [n_con]
-    double *d_n_val = nullptr;
-    int64_t *d_t_ptr = nullptr, *d_t_col = nullptr; // N^T CSR  [n_dense+1], [n_con]
-    double *d_t_val = nullptr;
-    // per element local constraint rows
-    int64_t *d_slot_off = nullptr;  // [n_elem+1] first slot of element e (m_e = difference)
-    int64_t *d_slot_trace = nullptr; // [n_slots] multiplier of each slot
-    int64_t *d_lrow_ptr = nullptr;  // [n_slots+1] entries of each local row
-    int32_t *d_lrow_col = nullptr;  // local column index
-    double *d_lrow_val = nullptr;
-    int64_t *d_s_off = nullptr;     // [n_elem+1] offsets into S
-    double *d_S = nullptr;          // condensed blocks, column-major
-    int64_t *d_tr_ptr = nullptr, *d_tr_slot = nullptr; // per multiplier: contributing slots
-    double *d_slot_val = nullptr;   // [n_slots] scratch: local results
-    double *d_diag_inv = nullptr;   // [n_trace] 1 / diag(S) (Jacobi preconditioner on the trace space)
-    // work vectors
-    double *d_work_dense[3] = {nullptr, nullptr, nullptr};
-    double *d_work_trace[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
-    double *d_partials = nullptr; // reduction partials
-    int n_partials = 0;
-    // multi-GPU interface (comm.cu)
-    int64_t n_shared = 0, n_iface = 0;
-    int64_t *d_shared_index = nullptr, *d_shared_slot = nullptr;
-    double *d_iface = nullptr;   // [n_iface + 8]
-    double *d_owned = nullptr;   // [n_trace] 1.0 / 0.0 ownership weights for dot products (nullptr: all owned)
-    std::vector<void *> allocs;
-};
-
-#define SYS_THREADS 256
 
 // ---- kernels -------------------------------------------------------------------------------------
 // y_e = M_e x_e for dense row-major blocks (LinearSystem.apply_diagonal / apply_diagonal_inverse with the stored
@@ -169,11 +127,30 @@ __global__ void csr_spmv_kernel(long long n_rows, const int64_t *__restrict__ pt
     }
 }
 
-// S_e[r][s] = sum_{(c,v) in row r} sum_{(d,w) in row s} v w Ainv_e[c][d]; stored column-major (s fastest... r fastest)
+// S_e[r][s] = sum_{(c,v) in row r} sum_{(d,w) in row s} v w Ainv_e[c][d]
+__device__ __forceinline__ double schur_entry(const double *__restrict__ B, int n, const int64_t *__restrict__ lrow_ptr,
+                                              const int32_t *__restrict__ lrow_col, const double *__restrict__ lrow_val, int64_t ra,
+                                              int64_t rb)
+{
+    double acc = 0.0;
+    for (int64_t a = lrow_ptr[ra]; a < lrow_ptr[ra + 1]; ++a)
+    {
+        const double *brow = B + (size_t)lrow_col[a] * n;
+        double t = 0.0;
+        for (int64_t b = lrow_ptr[rb]; b < lrow_ptr[rb + 1]; ++b)
+            t = fma(lrow_val[b], brow[lrow_col[b]], t);
+        acc = fma(lrow_val[a], t, acc);
+    }
+    return acc;
+}
+
+// full storage: column-major m x m (entry idx = s * m + r).  Packed storage (symmetric systems): entry (k, r) at k * m + r holds
+// (S[r][c] + S[c][r]) / 2 with c = (r + k) % m - see packed_size() in system.cuh
 __global__ void schur_build_kernel(unsigned long long n_elem, const int64_t *__restrict__ boff, const int64_t *__restrict__ moff,
                                    const double *__restrict__ Ainv, const int64_t *__restrict__ slot_off,
                                    const int64_t *__restrict__ lrow_ptr, const int32_t *__restrict__ lrow_col,
-                                   const double *__restrict__ lrow_val, const int64_t *__restrict__ s_off, double *__restrict__ S)
+                                   const double *__restrict__ lrow_val, const int64_t *__restrict__ s_off, double *__restrict__ S,
+                                   int packed)
 {
     for (unsigned long long e = blockIdx.x; e < n_elem; e += gridDim.x)
     {
@@ -182,24 +159,75 @@ __global__ void schur_build_kernel(unsigned long long n_elem, const int64_t *__r
         const int64_t s0 = slot_off[e];
         const int m = (int)(slot_off[e + 1] - s0);
         double *Se = S + s_off[e];
+        if (packed)
+        {
+            const int total = m * (m + 1) / 2;
+            for (int idx = threadIdx.x; idx < total; idx += blockDim.x)
+            {
+                const int k = idx / m, r = idx - k * m;
+                int c = r + k;
+                if (c >= m)
+                    c -= m;
+                const double v = schur_entry(B, n, lrow_ptr, lrow_col, lrow_val, s0 + r, s0 + c);
+                Se[idx] = k == 0 ? v : 0.5 * (v + schur_entry(B, n, lrow_ptr, lrow_col, lrow_val, s0 + c, s0 + r));
+            }
+            continue;
+        }
         for (int idx = threadIdx.x; idx < m * m; idx += blockDim.x)
         {
             const int s = idx / m, r = idx - s * m; // column s, row r (column-major storage)
-            double acc = 0.0;
-            for (int64_t a = lrow_ptr[s0 + r]; a < lrow_ptr[s0 + r + 1]; ++a)
-            {
-                const double *brow = B + (size_t)lrow_col[a] * n;
-                double t = 0.0;
-                for (int64_t b = lrow_ptr[s0 + s]; b < lrow_ptr[s0 + s + 1]; ++b)
-                    t = fma(lrow_val[b], brow[lrow_col[b]], t);
-                acc = fma(lrow_val[a], t, acc);
-            }
-            Se[idx] = acc;
+            Se[idx] = schur_entry(B, n, lrow_ptr, lrow_col, lrow_val, s0 + r, s0 + s);
         }
     }
 }
 
-// slot_val[s0 + r] = sum_s S_e[r][s] t[trace(s0 + s)]   - one warp per element
+// largest |A_e[i][j] - A_e[j][i]| against 1e-12 max|A_e|: flag[0] = 1 if some block is not symmetric to rounding
+__global__ void block_asymmetry_kernel(unsigned long long n_elem, const int64_t *__restrict__ boff, const int64_t *__restrict__ moff,
+                                       const double *__restrict__ A, int *__restrict__ flag)
+{
+    __shared__ double red_d[32], red_m[32];
+    for (unsigned long long e = blockIdx.x; e < n_elem; e += gridDim.x)
+    {
+        const int n = (int)(boff[e + 1] - boff[e]);
+        const double *M = A + moff[e];
+        double dmax = 0.0, amax = 0.0;
+        for (int idx = threadIdx.x; idx < n * n; idx += blockDim.x)
+        {
+            const int i = idx / n, j = idx - i * n;
+            const double v = M[idx];
+            amax = fmax(amax, fabs(v));
+            if (j > i)
+                dmax = fmax(dmax, fabs(v - M[(size_t)j * n + i]));
+        }
+#ifndef MFV2D_EMU
+        for (int o = 16; o > 0; o >>= 1)
+        {
+            dmax = fmax(dmax, __shfl_xor_sync(0xffffffffu, dmax, o));
+            amax = fmax(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+        }
+#endif
+        const int warp = threadIdx.x >> 5, nwarps = MFV2D_NWARPS;
+        if ((threadIdx.x & 31) == 0)
+        {
+            red_d[warp] = dmax;
+            red_m[warp] = amax;
+        }
+        __syncthreads();
+        if (threadIdx.x == 0)
+        {
+            for (int w = 1; w < nwarps; ++w)
+            {
+                dmax = fmax(dmax, red_d[w]);
+                amax = fmax(amax, red_m[w]);
+            }
+            if (!(dmax <= 1e-12 * amax))
+                atomicExch(flag, 1);
+        }
+        __syncthreads();
+    }
+}
+
+// slot_val[s0 + r] = sum_s S_e[r][s] t[trace(s0 + s)], full column-major blocks - one warp per element
 __global__ void __launch_bounds__(SYS_THREADS) schur_local_kernel(unsigned long long n_elem, const int64_t *__restrict__ slot_off,
                                                                  const int64_t *__restrict__ slot_trace,
                                                                  const int64_t *__restrict__ s_off, const double *__restrict__ S,
@@ -216,6 +244,8 @@ __global__ void __launch_bounds__(SYS_THREADS) schur_local_kernel(unsigned long 
     {
         const int64_t s0 = slot_off[e];
         const int m = (int)(slot_off[e + 1] - s0);
+        if (m == 0)
+            continue;
         const double *Se = S + s_off[e];
         __syncwarp();
         for (int i = MFV2D_LANE0; i < m; i += MFV2D_LANE_STEP)
@@ -258,9 +288,120 @@ __global__ void __launch_bounds__(SYS_THREADS) schur_local_kernel(unsigned long 
     }
 }
 
+// the same product from PACKED symmetric blocks, any m: a warp per element, lane r gathers row r from the stored half
+// (direct entries S[r][(r + k) % m] and mirrored entries S[(r - k) % m][r]); used when a block has more than 32 rows
+__global__ void __launch_bounds__(SYS_THREADS) schur_local_packed_generic_kernel(
+    unsigned long long n_elem, const int64_t *__restrict__ slot_off, const int64_t *__restrict__ slot_trace,
+    const int64_t *__restrict__ s_off, const double *__restrict__ S, const double *__restrict__ t, double *__restrict__ slot_val, int max_m,
+    const int *__restrict__ done)
+{
+    MFV2D_DYN_SMEM(double, lam_all);
+    if (done && *done)
+        return;
+    const int warp = threadIdx.x >> 5, nwarps = MFV2D_NWARPS;
+    double *lam = lam_all + (size_t)warp * max_m;
+    for (unsigned long long e = (unsigned long long)blockIdx.x * nwarps + warp; e < n_elem; e += (unsigned long long)gridDim.x * nwarps)
+    {
+        const int64_t s0 = slot_off[e];
+        const int m = (int)(slot_off[e + 1] - s0);
+        if (m == 0)
+            continue;
+        const double *Se = S + s_off[e];
+        const int half = m >> 1, kfull = (m + 1) >> 1;
+        const bool even = (m & 1) == 0;
+        __syncwarp();
+        for (int i = MFV2D_LANE0; i < m; i += MFV2D_LANE_STEP)
+            lam[i] = t[slot_trace[s0 + i]];
+        __syncwarp();
+        for (int r = MFV2D_LANE0; r < m; r += MFV2D_LANE_STEP)
+        {
+            double acc = 0.0;
+            for (int k = 0; k <= half; ++k)
+            {
+                int c = r + k, sr = r - k;
+                if (c >= m)
+                    c -= m;
+                if (sr < 0)
+                    sr += m;
+                if (k < kfull || (even && r < half))
+                    acc = fma(Se[(size_t)k * m + r], lam[c], acc);
+                if (k > 0 && (k < kfull || (even && sr < half)))
+                    acc = fma(Se[(size_t)k * m + sr], lam[sr], acc);
+            }
+            slot_val[s0 + r] = acc;
+        }
+    }
+}
+
+#ifndef MFV2D_EMU
+// PACKED symmetric blocks of at most W <= 32 rows: 32 / W elements per warp, lane (g, r) owns row r of its element.  Every stored
+// entry is read ONCE (coalesced over r for a fixed diagonal k, 8 diagonals in flight per lane); its mirrored use travels to lane
+// (r + k) % m by a shuffle, lambda comes by shuffles too: no shared memory, no barrier, half the bytes of the full product.
+__global__ void __launch_bounds__(SYS_THREADS) schur_local_packed_kernel(unsigned long long n_elem, const int64_t *__restrict__ slot_off,
+                                                                        const int64_t *__restrict__ slot_trace,
+                                                                        const int64_t *__restrict__ s_off, const double *__restrict__ S,
+                                                                        const double *__restrict__ t, double *__restrict__ slot_val, int W,
+                                                                        const int *__restrict__ done)
+{
+    if (done && *done)
+        return;
+    constexpr int UNR = 8;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+    const int G = 32 / W, g = lane / W, r = lane - g * W;
+    const int kmax = (W >> 1) + 1;
+    const unsigned long long stride = (unsigned long long)gridDim.x * nwarps * G;
+    for (unsigned long long base = ((unsigned long long)blockIdx.x * nwarps + warp) * G; base < n_elem; base += stride)
+    {
+        const unsigned long long e = base + g;
+        const bool valid = g < G && e < n_elem;
+        const int64_t s0 = valid ? slot_off[e] : 0;
+        const int m = valid ? (int)(slot_off[e + 1] - s0) : 0;
+        const double *Se = S + (valid ? s_off[e] : 0);
+        const bool row = r < m;
+        const int half = m >> 1, kfull = (m + 1) >> 1;
+        const bool low = !(m & 1) && r < half; // holds an entry of the last (half-length) diagonal of an even block
+        const double lam_r = row ? t[slot_trace[s0 + r]] : 0.0;
+        double acc = 0.0;
+        for (int k0 = 0; k0 < kmax; k0 += UNR)
+        {
+            double a[UNR];
+#pragma unroll
+            for (int u = 0; u < UNR; ++u)
+            {
+                const int k = k0 + u;
+                a[u] = (row && (k < kfull || (k == half && low))) ? __ldcs(Se + (size_t)k * m + r) : 0.0;
+            }
+#pragma unroll
+            for (int u = 0; u < UNR; ++u)
+            {
+                const int k = k0 + u;
+                int lc = lane, ls = lane;
+                if (row && k <= half)
+                {
+                    int c = r + k, sr = r - k;
+                    if (c >= m)
+                        c -= m;
+                    if (sr < 0)
+                        sr += m;
+                    lc = g * W + c;
+                    ls = g * W + sr;
+                }
+                const double lam_c = __shfl_sync(0xffffffffu, lam_r, lc);
+                const double recv = __shfl_sync(0xffffffffu, a[u] * lam_r, ls);
+                acc = fma(a[u], lam_c, acc);
+                if (k > 0)
+                    acc += recv;
+            }
+        }
+        if (row)
+            slot_val[s0 + r] = acc;
+    }
+}
+#endif
+
 // slot_val[s0 + r] = S_e[r][r]: the elements' contributions to diag(S)
 __global__ void schur_diag_kernel(unsigned long long n_elem, const int64_t *__restrict__ slot_off, const int64_t *__restrict__ s_off,
-                                  const double *__restrict__ S, double *__restrict__ slot_val)
+                                  const double *__restrict__ S, double *__restrict__ slot_val, int packed)
 {
     for (unsigned long long e = blockIdx.x; e < n_elem; e += gridDim.x)
     {
@@ -268,19 +409,7 @@ __global__ void schur_diag_kernel(unsigned long long n_elem, const int64_t *__re
         const int m = (int)(slot_off[e + 1] - s0);
         const double *Se = S + s_off[e];
         for (int r = threadIdx.x; r < m; r += blockDim.x)
-            slot_val[s0 + r] = Se[(size_t)r * m + r];
-    }
-}
-
-// d[i] = 1 / d[i] (1 where the diagonal vanishes); z[i] = d[i] r[i]
-__global__ void jacobi_setup_kernel(long long n, double *__restrict__ d, const double *__restrict__ r, double *__restrict__ z)
-{
-    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
-    {
-        const double v = d[i];
-        const double inv = v != 0.0 ? 1.0 / v : 1.0;
-        d[i] = inv;
-        z[i] = inv * r[i];
+            slot_val[s0 + r] = packed ? Se[r] : Se[(size_t)r * m + r];
     }
 }
 
@@ -302,24 +431,6 @@ __global__ void __launch_bounds__(SYS_THREADS) trace_gather_kernel(long long n_t
 }
 
 // deterministic two-stage dot product: partials[blockIdx] = sum over the CTA's strided range of x*y(*w)
-__device__ __forceinline__ void block_reduce_store(double acc, double *partials)
-{
-    __shared__ double red[32];
-    acc = warp_sum(acc);
-    const int warp = threadIdx.x >> 5, nwarps = MFV2D_NWARPS;
-    if ((threadIdx.x & 31) == 0)
-        red[warp] = acc;
-    __syncthreads();
-    if (threadIdx.x == 0)
-    {
-        double s = 0.0;
-        for (int w = 0; w < nwarps; ++w)
-            s += red[w];
-        partials[blockIdx.x] = s;
-    }
-    __syncthreads();
-}
-
 __global__ void __launch_bounds__(SYS_THREADS) dot_partial_kernel(long long n, const double *__restrict__ x,
                                                                  const double *__restrict__ y, const double *__restrict__ w,
                                                                  double *__restrict__ partials, const int *__restrict__ done)
@@ -330,15 +441,6 @@ __global__ void __launch_bounds__(SYS_THREADS) dot_partial_kernel(long long n, c
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
         acc = fma(w ? x[i] * w[i] : x[i], y[i], acc);
     block_reduce_store(acc, partials);
-}
-
-// deterministic sum of the per-CTA partials by ONE warp (launch <<<1, 32>>>): lane-strided, then a butterfly
-__device__ __forceinline__ double warp_sum_partials(int n_partials, const double *__restrict__ partials)
-{
-    double s = 0.0;
-    for (int i = MFV2D_LANE0; i < n_partials; i += MFV2D_LANE_STEP)
-        s += partials[i];
-    return warp_sum(s);
 }
 
 __global__ void sum_partials_kernel(int n_partials, const double *__restrict__ partials, double *__restrict__ result)
@@ -353,183 +455,6 @@ __global__ void axpby_kernel(long long n, double a, const double *__restrict__ x
 {
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
         out[i] = a * x[i] + b * y[i];
-}
-
-// ---- CG on the trace space, scalars on the device --------------------------------------------------
-// sc[0] = rr, sc[1] = pAp, sc[2] = alpha, sc[3] = beta, sc[4] = tol^2, sc[5] = rz (preconditioned)
-// flags[0] = done, flags[1] = iterations completed (the reference's iter_cnt), flags[2] = breakdown
-__global__ void cg_alpha_kernel(int n_partials, const double *__restrict__ partials, double *__restrict__ sc, int *flags,
-                                int precond)
-{
-    const double s = warp_sum_partials(n_partials, partials);
-    if (blockIdx.x == 0 && threadIdx.x == 0 && !flags[0])
-    {
-        sc[1] = s;
-        sc[2] = (precond ? sc[5] : sc[0]) / s;
-    }
-}
-
-// x += alpha p ; r -= alpha Ap ; z = Minv r ; partials of r.r (and r.z)
-__global__ void __launch_bounds__(SYS_THREADS) cg_update_kernel(long long n, const double *__restrict__ sc, const int *flags,
-                                                               const double *__restrict__ p, const double *__restrict__ ap,
-                                                               double *__restrict__ x, double *__restrict__ r,
-                                                               const double *__restrict__ w, const double *__restrict__ dinv,
-                                                               double *__restrict__ z, double *__restrict__ partials,
-                                                               double *__restrict__ partials2)
-{
-    if (flags[0])
-        return;
-    const double alpha = sc[2];
-    double acc = 0.0, acc2 = 0.0;
-    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
-    {
-        x[i] = fma(alpha, p[i], x[i]);
-        const double ri = fma(-alpha, ap[i], r[i]);
-        r[i] = ri;
-        const double wi = w ? w[i] : 1.0;
-        acc = fma(ri * wi, ri, acc);
-        if (dinv)
-        {
-            const double zi = ri * dinv[i];
-            z[i] = zi;
-            acc2 = fma(ri * wi, zi, acc2);
-        }
-    }
-    block_reduce_store(acc, partials);
-    if (dinv)
-        block_reduce_store(acc2, partials2);
-}
-
-__global__ void cg_beta_kernel(int n_partials, const double *__restrict__ partials, const double *__restrict__ partials2,
-                               double *__restrict__ sc, int *flags, int precond, int iter)
-{
-    const double s = warp_sum_partials(n_partials, partials);
-    const double s2 = precond ? warp_sum_partials(n_partials, partials2) : 0.0;
-    if (blockIdx.x == 0 && threadIdx.x == 0 && !flags[0])
-    {
-        // flags[1] = index of the last iteration carried out (the reference's iter_cnt), counted on the device so
-        // that the launches of an iteration do not depend on it (CUDA graph replay); iter < 0 selects the counter
-        flags[1] = iter >= 0 ? iter : flags[3];
-        flags[3] += 1;
-        if (s < sc[4])
-        {
-            sc[0] = s;
-            flags[0] = 1;
-            return;
-        }
-        if (precond)
-        {
-            sc[3] = s2 / sc[5];
-            sc[5] = s2;
-        }
-        else
-            sc[3] = s / sc[0];
-        sc[0] = s;
-    }
-}
-
-// p = (z or r) + beta p
-__global__ void cg_direction_kernel(long long n, const double *__restrict__ sc, const int *flags, const double *__restrict__ r,
-                                    double *__restrict__ p)
-{
-    if (flags[0])
-        return;
-    const double beta = sc[3];
-    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
-        p[i] = fma(beta, p[i], r[i]);
-}
-
-// ---- CG with ONE synchronisation per iteration (Chronopoulos & Gear 1989), used when the system is partitioned -----
-// u = Minv r, w = S u;  gamma = r.u, delta = u.w, rho = r.r are needed at the same point, so they travel in the ONE
-// all-reduce that also sums the interface multipliers of w (the two-reduction recurrence above pays a second
-// all-reduce for r.r after the update):
-//   beta = gamma / gamma_old ; alpha = gamma / (delta - beta gamma / alpha_old)
-//   p = u + beta p ; s = w + beta s ; x += alpha p ; r -= alpha s ; u = Minv r
-// sc[6] = gamma_old, sc[7] = alpha_old, sc[8..10] = (delta, gamma, rho); the other scalars and the flags as above.
-__global__ void __launch_bounds__(SYS_THREADS) cg1_dots_kernel(long long n, const double *__restrict__ u, const double *__restrict__ wv,
-                                                              const double *__restrict__ r, const double *__restrict__ own,
-                                                              double *__restrict__ partials, int n_partials,
-                                                              const int *__restrict__ done)
-{
-    if (*done)
-        return;
-    double d = 0.0, g = 0.0, rho = 0.0;
-    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
-    {
-        const double ui = u[i], ri = r[i];
-        const double rw = own ? ri * own[i] : ri;
-        d = fma(ui, wv[i], d); // local, un-summed product: summed over the ranks it is u . S u
-        g = fma(rw, ui, g);
-        rho = fma(rw, ri, rho);
-    }
-    block_reduce_store(d, partials);
-    block_reduce_store(g, partials + n_partials);
-    block_reduce_store(rho, partials + 2 * n_partials);
-}
-
-__global__ void cg1_sum3_kernel(int n_partials, const double *__restrict__ partials, double *__restrict__ out, const int *done)
-{
-    if (*done)
-        return;
-    const double a = warp_sum_partials(n_partials, partials);
-    const double b = warp_sum_partials(n_partials, partials + n_partials);
-    const double c = warp_sum_partials(n_partials, partials + 2 * n_partials);
-    if (threadIdx.x == 0)
-    {
-        out[0] = a;
-        out[1] = b;
-        out[2] = c;
-    }
-}
-
-__global__ void cg1_scalar_kernel(double *__restrict__ sc, int *flags)
-{
-    if (blockIdx.x != 0 || threadIdx.x != 0 || flags[0])
-        return;
-    const double delta = sc[8], gamma = sc[9], rho = sc[10];
-    const int k = flags[3]; // updates carried out so far: rho belongs to the residual after update k - 1
-    flags[3] = k + 1;
-    sc[0] = rho;
-    if (k > 0)
-    {
-        flags[1] = k - 1;
-        if (rho < sc[4])
-        {
-            flags[0] = 1;
-            return;
-        }
-    }
-    const double beta = k > 0 ? gamma / sc[6] : 0.0;
-    const double alpha = k > 0 ? gamma / (delta - beta * gamma / sc[7]) : gamma / delta;
-    sc[1] = delta;
-    sc[2] = alpha;
-    sc[3] = beta;
-    sc[6] = gamma;
-    sc[7] = alpha;
-}
-
-// u may alias r (no preconditioner): every entry is read before it is written by the same thread
-__global__ void __launch_bounds__(SYS_THREADS) cg1_update_kernel(long long n, const double *__restrict__ sc, const int *flags,
-                                                                const double *u, const double *__restrict__ wv,
-                                                                double *__restrict__ p, double *__restrict__ sv,
-                                                                double *__restrict__ x, double *r, const double *__restrict__ dinv,
-                                                                double *z)
-{
-    if (flags[0])
-        return;
-    const double alpha = sc[2], beta = sc[3];
-    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
-    {
-        const double pi = fma(beta, p[i], u[i]);
-        const double si = fma(beta, sv[i], wv[i]);
-        p[i] = pi;
-        sv[i] = si;
-        x[i] = fma(alpha, pi, x[i]);
-        const double ri = fma(-alpha, si, r[i]);
-        r[i] = ri;
-        if (dinv)
-            z[i] = ri * dinv[i];
-    }
 }
 
 // multi-GPU: pack the shared multipliers of `t` into the interface buffer / scatter the reduced sums back
@@ -547,38 +472,7 @@ __global__ void iface_unpack_kernel(long long n_shared, const int64_t *__restric
 }
 
 // ---- host helpers ------------------------------------------------------------------------------
-template <typename T> static int sys_upload(mfv2d_system *s, const std::vector<T> &h, T **d)
-{
-    void *p = nullptr;
-    MFV2D_TRY(mfv2d_cuda_malloc(s->ctx, (h.size() ? h.size() : 1) * sizeof(T), &p));
-    s->allocs.push_back(p);
-    *d = (T *)p;
-    if (!h.empty())
-        MFV2D_TRY(mfv2d_cuda_upload(s->ctx, p, h.data(), h.size() * sizeof(T)));
-    return MFV2D_SUCCESS;
-}
-
-template <typename T> static int sys_alloc(mfv2d_system *s, size_t n, T **d)
-{
-    void *p = nullptr;
-    MFV2D_TRY(mfv2d_cuda_malloc(s->ctx, (n ? n : 1) * sizeof(T), &p));
-    s->allocs.push_back(p);
-    *d = (T *)p;
-    return MFV2D_SUCCESS;
-}
-
-static unsigned grid_for(const mfv2d_ctx *ctx, long long n, int threads)
-{
-    long long g = (n + threads - 1) / threads;
-    const long long cap = (long long)ctx->sm_count * 8;
-    if (g > cap)
-        g = cap;
-    if (g < 1)
-        g = 1;
-    return (unsigned)g;
-}
-
-static int sys_gemv(const mfv2d_system *s, const double *M, const double *x, double *y)
+int sys_gemv(const mfv2d_system *s, const double *M, const double *x, double *y)
 {
     mfv2d_ctx *ctx = s->ctx;
     if (s->n_elem == 0)
@@ -601,7 +495,7 @@ static int sys_gemv(const mfv2d_system *s, const double *M, const double *x, dou
     return MFV2D_SUCCESS;
 }
 
-static int sys_spmv(const mfv2d_system *s, long long rows, const int64_t *ptr, const int64_t *col, const double *val,
+int sys_spmv(const mfv2d_system *s, long long rows, const int64_t *ptr, const int64_t *col, const double *val,
                     const double *x, double *y)
 {
     mfv2d_ctx *ctx = s->ctx;
@@ -613,12 +507,34 @@ static int sys_spmv(const mfv2d_system *s, long long rows, const int64_t *ptr, c
     return MFV2D_SUCCESS;
 }
 
+// a partitioned system whose interface was never declared would hang the other ranks in the collective (or silently
+// double count shared multipliers in the dot products): refuse instead
+int sys_require_interface(const mfv2d_system *s)
+{
+    if (s->ctx->n_ranks > 1 && !s->interface_set)
+        return mfv2d_fail(s->ctx, MFV2D_CUDA_NCCL_ERROR,
+                          "the context has %d ranks but mfv2d_cuda_system_set_interface was not called on this system", s->ctx->n_ranks);
+    return MFV2D_SUCCESS;
+}
+
+// the mapped peer blocks carry every exchange unless MFV2D_CG_EXCHANGE=nccl asks for the NCCL path (A/B comparison)
+bool sys_use_peers(const mfv2d_system *s)
+{
+    if (s->ctx->n_ranks <= 1 || !s->peers_ready)
+        return false;
+    const char *ex_env = getenv("MFV2D_CG_EXCHANGE");
+    return !(ex_env && ex_env[0] == 'n');
+}
+
 // sum the shared multipliers of a trace vector over the ranks (no-op on one GPU)
-static int sys_interface_sum(const mfv2d_system *s, double *t, int extra_scalars, double *scalars)
+int sys_interface_sum(const mfv2d_system *s, double *t, int extra_scalars, double *scalars)
 {
     mfv2d_ctx *ctx = s->ctx;
-    if (ctx->n_ranks <= 1 || !s->d_iface)
+    if (ctx->n_ranks <= 1)
         return MFV2D_SUCCESS;
+    MFV2D_TRY(sys_require_interface(s));
+    if (sys_use_peers(s))
+        return peer_interface_sum(s, t, extra_scalars, scalars);
     MFV2D_CUDA_CHECK(ctx, cudaMemsetAsync(s->d_iface, 0, (size_t)(s->n_iface + 8) * sizeof(double), ctx->stream));
     if (s->n_shared)
     {
@@ -642,27 +558,64 @@ static int sys_interface_sum(const mfv2d_system *s, double *t, int extra_scalars
     return MFV2D_SUCCESS;
 }
 
-static int sys_apply_trace(const mfv2d_system *s, const double *x, double *t)
+int sys_apply_trace(const mfv2d_system *s, const double *x, double *t)
 {
     MFV2D_TRY(sys_spmv(s, s->n_trace, s->d_n_ptr, s->d_n_col, s->d_n_val, x, t));
     return sys_interface_sum(s, t, 0, nullptr);
 }
 
-static int sys_apply_schur(const mfv2d_system *s, const double *t_in, double *t_out, const int *done, bool interface_sum = true)
+// per-element products S_e t_e -> slot_val (the big kernel of a Schur application)
+int sys_schur_local(const mfv2d_system *s, const double *t_in, const int *done)
 {
     mfv2d_ctx *ctx = s->ctx;
-    if (s->n_elem)
+    if (!s->n_elem || !s->max_m)
+        return MFV2D_SUCCESS;
+    const int warps = SYS_THREADS / 32;
+    const long long cap = (long long)ctx->sm_count * 8;
+#ifndef MFV2D_EMU
+    if (s->symmetric && s->max_m <= 32)
     {
-        const int warps = SYS_THREADS / 32;
-        long long grid = (s->n_elem + warps - 1) / warps;
-        const long long cap = (long long)ctx->sm_count * 8;
+        const int G = 32 / s->max_m;
+        long long grid = (s->n_elem + (long long)warps * G - 1) / ((long long)warps * G);
         if (grid > cap)
             grid = cap;
-        MFV2D_LAUNCH(schur_local_kernel, (unsigned)grid, SYS_THREADS, (size_t)warps * (s->max_m + 1 + 32) * sizeof(double), ctx->stream,
-                     (unsigned long long)s->n_elem, s->d_slot_off, s->d_slot_trace, s->d_s_off, s->d_S, t_in, s->d_slot_val,
-                     s->max_m + 1, done);
+        MFV2D_LAUNCH(schur_local_packed_kernel, (unsigned)grid, SYS_THREADS, 0, ctx->stream, (unsigned long long)s->n_elem, s->d_slot_off,
+                     s->d_slot_trace, s->d_s_off, s->d_S, t_in, s->d_slot_val, s->max_m, done);
         ctx->launches++;
+        MFV2D_CUDA_CHECK(ctx, cudaGetLastError());
+        return MFV2D_SUCCESS;
     }
+#endif
+    long long grid = (s->n_elem + warps - 1) / warps;
+    if (grid > cap)
+        grid = cap;
+    const size_t smem = (size_t)warps * (s->max_m + 1 + 32) * sizeof(double);
+    if (smem > ctx->smem_optin)
+        return mfv2d_fail(ctx, MFV2D_CUDA_UNSUPPORTED, "schur product: elements with %d multipliers need %zu bytes of shared memory",
+                          s->max_m, smem);
+    if (s->symmetric)
+    {
+        if (smem > 48 * 1024)
+            MFV2D_CUDA_CHECK(ctx, cudaFuncSetAttribute(schur_local_packed_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        MFV2D_LAUNCH(schur_local_packed_generic_kernel, (unsigned)grid, SYS_THREADS, smem, ctx->stream, (unsigned long long)s->n_elem,
+                     s->d_slot_off, s->d_slot_trace, s->d_s_off, s->d_S, t_in, s->d_slot_val, s->max_m + 1 + 32, done);
+    }
+    else
+    {
+        if (smem > 48 * 1024)
+            MFV2D_CUDA_CHECK(ctx, cudaFuncSetAttribute(schur_local_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        MFV2D_LAUNCH(schur_local_kernel, (unsigned)grid, SYS_THREADS, smem, ctx->stream, (unsigned long long)s->n_elem, s->d_slot_off,
+                     s->d_slot_trace, s->d_s_off, s->d_S, t_in, s->d_slot_val, s->max_m + 1, done);
+    }
+    ctx->launches++;
+    MFV2D_CUDA_CHECK(ctx, cudaGetLastError());
+    return MFV2D_SUCCESS;
+}
+
+int sys_apply_schur(const mfv2d_system *s, const double *t_in, double *t_out, const int *done, bool interface_sum)
+{
+    mfv2d_ctx *ctx = s->ctx;
+    MFV2D_TRY(sys_schur_local(s, t_in, done));
     if (s->n_trace)
     {
         MFV2D_LAUNCH(trace_gather_kernel, grid_for(ctx, s->n_trace, SYS_THREADS), SYS_THREADS, 0, ctx->stream,
@@ -673,8 +626,31 @@ static int sys_apply_schur(const mfv2d_system *s, const double *t_in, double *t_
     return interface_sum ? sys_interface_sum(s, t_out, 0, nullptr) : MFV2D_SUCCESS;
 }
 
+// diag(S) -> out[n_trace] (summed over the elements and, on a partitioned system, over the ranks)
+int sys_schur_diagonal(const mfv2d_system *s, double *out)
+{
+    mfv2d_ctx *ctx = s->ctx;
+    long long grid = (long long)ctx->sm_count * 8;
+    if (grid > s->n_elem)
+        grid = s->n_elem;
+    if (s->n_elem)
+    {
+        MFV2D_LAUNCH(schur_diag_kernel, (unsigned)grid, 32, 0, ctx->stream, (unsigned long long)s->n_elem, s->d_slot_off, s->d_s_off,
+                     s->d_S, s->d_slot_val, (int)s->symmetric);
+        ctx->launches++;
+    }
+    if (s->n_trace)
+    {
+        MFV2D_LAUNCH(trace_gather_kernel, grid_for(ctx, s->n_trace, SYS_THREADS), SYS_THREADS, 0, ctx->stream, (long long)s->n_trace,
+                     s->d_tr_ptr, s->d_tr_slot, s->d_slot_val, out, (const int *)nullptr);
+        ctx->launches++;
+    }
+    MFV2D_CUDA_CHECK(ctx, cudaGetLastError());
+    return sys_interface_sum(s, out, 0, nullptr);
+}
+
 // dot product of two trace (w = ownership weights) or dense (w = nullptr) vectors -> device scalar
-static int sys_dot_device(const mfv2d_system *s, long long n, const double *x, const double *y, const double *w, double *d_result)
+int sys_dot_device(const mfv2d_system *s, long long n, const double *x, const double *y, const double *w, double *d_result)
 {
     mfv2d_ctx *ctx = s->ctx;
     MFV2D_LAUNCH(dot_partial_kernel, (unsigned)s->n_partials, SYS_THREADS, 0, ctx->stream, n, x, y, w, s->d_partials,
@@ -683,11 +659,15 @@ static int sys_dot_device(const mfv2d_system *s, long long n, const double *x, c
     ctx->launches += 2;
     MFV2D_CUDA_CHECK(ctx, cudaGetLastError());
     if (ctx->n_ranks > 1)
+    {
+        if (sys_use_peers(s))
+            return peer_interface_sum(s, nullptr, 1, d_result);
         MFV2D_TRY(comm_allreduce(ctx, d_result, 1));
+    }
     return MFV2D_SUCCESS;
 }
 
-static int read_scalars(mfv2d_ctx *ctx, const double *d, int n, double *h)
+int read_scalars(mfv2d_ctx *ctx, const double *d, int n, double *h)
 {
     MFV2D_CUDA_CHECK(ctx, cudaMemcpyAsync(ctx->h_scalars, d, n * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
     MFV2D_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
@@ -702,6 +682,7 @@ void mfv2d_cuda_system_destroy(mfv2d_system *s)
     if (!s)
         return;
     cudaStreamSynchronize(s->ctx->stream);
+    sys_release_peers(s);
     for (void *p : s->allocs)
         cudaFree(p);
     delete s;
@@ -827,12 +808,6 @@ int mfv2d_cuda_system_create(mfv2d_ctx *ctx, size_t n_elem, const int64_t *block
             s->max_m = m;
     }
     s->n_slots = (int64_t)slot_trace.size();
-    std::vector<int64_t> s_off(n_elem + 1, 0);
-    for (size_t e = 0; e < n_elem; ++e)
-    {
-        const int64_t m = slot_off[e + 1] - slot_off[e];
-        s_off[e + 1] = s_off[e] + m * m;
-    }
     std::vector<int64_t> tr_ptr(n_trace + 1, 0), tr_slot(s->n_slots);
     for (int64_t k = 0; k < s->n_slots; ++k)
         tr_ptr[slot_trace[k] + 1]++;
@@ -857,7 +832,6 @@ int mfv2d_cuda_system_create(mfv2d_ctx *ctx, size_t n_elem, const int64_t *block
     SYS_TRY(sys_upload(s, lrow_ptr, &s->d_lrow_ptr));
     SYS_TRY(sys_upload(s, lrow_col, &s->d_lrow_col));
     SYS_TRY(sys_upload(s, lrow_val, &s->d_lrow_val));
-    SYS_TRY(sys_upload(s, s_off, &s->d_s_off));
     SYS_TRY(sys_upload(s, tr_ptr, &s->d_tr_ptr));
     SYS_TRY(sys_upload(s, tr_slot, &s->d_tr_slot));
     const size_t mat_total = (size_t)moff[n_elem];
@@ -872,14 +846,46 @@ int mfv2d_cuda_system_create(mfv2d_ctx *ctx, size_t n_elem, const int64_t *block
         if (mat_total)
             SYS_TRY(mfv2d_cuda_upload(ctx, s->d_A, blocks, mat_total * sizeof(double)));
     }
+    // symmetric blocks (every system of the reference's examples without an advection term) -> packed condensed blocks
+    {
+        const char *pk = getenv("MFV2D_SCHUR_PACKED");
+        s->symmetric = n_elem > 0;
+        if (pk && pk[0] == '0')
+            s->symmetric = false;
+        else if (n_elem)
+        {
+            int *d_flag = reinterpret_cast<int *>(ctx->d_scalars + 32);
+            cudaMemsetAsync(d_flag, 0, sizeof(int), ctx->stream);
+            long long grid = (long long)ctx->sm_count * 8;
+            if (grid > (long long)n_elem)
+                grid = (long long)n_elem;
+            MFV2D_LAUNCH(block_asymmetry_kernel, (unsigned)grid, 256, 0, ctx->stream, (unsigned long long)n_elem, s->d_block_off,
+                         s->d_mat_off, (const double *)s->d_A, d_flag);
+            ctx->launches++;
+            int h_flag = 1;
+            if (cudaMemcpyAsync(&h_flag, d_flag, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess ||
+                cudaStreamSynchronize(ctx->stream) != cudaSuccess)
+                SYS_TRY(mfv2d_fail(ctx, MFV2D_CUDA_ERROR, "system_create: symmetry test failed: %s", cudaGetErrorString(cudaGetLastError())));
+            s->symmetric = h_flag == 0;
+        }
+    }
+    std::vector<int64_t> s_off(n_elem + 1, 0);
+    for (size_t e = 0; e < n_elem; ++e)
+    {
+        const int64_t m = slot_off[e + 1] - slot_off[e];
+        s_off[e + 1] = s_off[e] + (s->symmetric ? packed_size(m) : m * m);
+    }
+    SYS_TRY(sys_upload(s, s_off, &s->d_s_off));
     SYS_TRY(sys_alloc(s, mat_total, &s->d_Ainv));
     SYS_TRY(sys_alloc(s, (size_t)s_off[n_elem], &s->d_S));
     SYS_TRY(sys_alloc(s, (size_t)s->n_slots, &s->d_slot_val));
     SYS_TRY(sys_alloc(s, (size_t)s->n_trace, &s->d_diag_inv));
     for (int i = 0; i < 3; ++i)
         SYS_TRY(sys_alloc(s, (size_t)s->n_dense, &s->d_work_dense[i]));
-    for (int i = 0; i < 6; ++i)
+    for (int i = 0; i < 8; ++i)
         SYS_TRY(sys_alloc(s, (size_t)s->n_trace, &s->d_work_trace[i]));
+    SYS_TRY(sys_alloc(s, (size_t)64, &s->d_cg));
+    cudaMemsetAsync(s->d_cg, 0, 64 * sizeof(double), ctx->stream);
     s->n_partials = ctx->sm_count * 4;
     SYS_TRY(sys_alloc(s, (size_t)3 * s->n_partials, &s->d_partials));
     // ---- factorise: explicit inverses of the dense blocks ----
@@ -910,7 +916,8 @@ int mfv2d_cuda_system_create(mfv2d_ctx *ctx, size_t n_elem, const int64_t *block
         if (grid > (long long)n_elem)
             grid = (long long)n_elem;
         MFV2D_LAUNCH(schur_build_kernel, (unsigned)grid, 128, 0, ctx->stream, (unsigned long long)n_elem, s->d_block_off,
-                     s->d_mat_off, s->d_Ainv, s->d_slot_off, s->d_lrow_ptr, s->d_lrow_col, s->d_lrow_val, s->d_s_off, s->d_S);
+                     s->d_mat_off, s->d_Ainv, s->d_slot_off, s->d_lrow_ptr, s->d_lrow_col, s->d_lrow_val, s->d_s_off, s->d_S,
+                     (int)s->symmetric);
         ctx->launches++;
         if (cudaGetLastError() != cudaSuccess)
             SYS_TRY(mfv2d_fail(ctx, MFV2D_CUDA_ERROR, "schur_build kernel launch failed"));
@@ -1028,279 +1035,6 @@ int mfv2d_cuda_vec_dot(mfv2d_ctx *ctx, size_t n, const double *x, const double *
     stage_abort(&sy);
     if (partials)
         mfv2d_cuda_free(ctx, partials);
-    return r;
-}
-
-// solve_schur_iterative (python/mfv2d/solving.py:439-500) with cg_general (:350-436)
-int mfv2d_cuda_solve_schur_cg(mfv2d_system *s, const double *rhs, const double *phi, int max_iter, double atol, double rtol,
-                              int precondition, double *x, double *lambda, double *residual, int *iterations, int space)
-{
-    mfv2d_ctx *ctx = s->ctx;
-    const long long nt = s->n_trace, nd = s->n_dense;
-    Staged srhs, sphi, sx, slam;
-    int r = stage_in(ctx, rhs, nd * sizeof(double), space, &srhs);
-    if (!r)
-        r = stage_in(ctx, phi, nt * sizeof(double), space, &sphi);
-    if (!r)
-        r = stage_out_alloc(ctx, x, nd * sizeof(double), space, &sx);
-    if (!r)
-        r = stage_out_alloc(ctx, lambda, nt * sizeof(double), space, &slam);
-    double *inv_a_y = s->d_work_dense[0], *tmp_d = s->d_work_dense[1], *tmp_d2 = s->d_work_dense[2];
-    double *res = s->d_work_trace[0], *p = s->d_work_trace[1], *ap = s->d_work_trace[2], *z = s->d_work_trace[3];
-    double *lam = (double *)slam.dev;
-    double *sc = ctx->d_scalars;
-    int *flags = reinterpret_cast<int *>(ctx->d_scalars + 16);
-    const double *w = s->d_owned;
-    double h[24];
-    int it_done = 0;
-    double res_mag2 = 0.0;
-    do
-    {
-        if (r)
-            break;
-        // A^-1 y ; N A^-1 y - phi
-        if ((r = sys_gemv(s, s->d_Ainv, (const double *)srhs.dev, inv_a_y)))
-            break;
-        if ((r = sys_apply_trace(s, inv_a_y, res)))
-            break;
-        if (nt)
-        {
-            MFV2D_LAUNCH(axpby_kernel, grid_for(ctx, nt, 256), 256, 0, ctx->stream, nt, 1.0, (const double *)res, -1.0,
-                         (const double *)sphi.dev, res);
-            ctx->launches++;
-        }
-        cudaMemsetAsync(lam, 0, nt * sizeof(double), ctx->stream);
-        cudaMemsetAsync(sc, 0, 32 * sizeof(double), ctx->stream);
-        // res_mag2 = rhs . rhs ; tolerance (solving.py:405-412)
-        if (nt)
-        {
-            if ((r = sys_dot_device(s, nt, res, res, w, sc + 0)))
-                break;
-            if ((r = read_scalars(ctx, sc, 1, h)))
-                break;
-            res_mag2 = h[0];
-        }
-        const double mag = sqrt(res_mag2);
-        const double tol = (mag * rtol > atol) ? atol : mag * rtol;
-        h[4] = tol * tol;
-        if (nt && max_iter > 0)
-        {
-            cudaMemcpyAsync(sc + 4, &h[4], sizeof(double), cudaMemcpyHostToDevice, ctx->stream);
-            cudaStreamSynchronize(ctx->stream);
-            const double *dinv = nullptr;
-            if (precondition)
-            {
-                // Jacobi on the trace space (not in the reference): diag(S) from the diagonals of the condensed blocks,
-                // summed per multiplier and over the ranks; z0 = D^-1 r0, p0 = z0, rz = r0 . z0
-                long long grid = (long long)ctx->sm_count * 8;
-                if (grid > s->n_elem)
-                    grid = s->n_elem;
-                if (s->n_elem)
-                {
-                    MFV2D_LAUNCH(schur_diag_kernel, (unsigned)grid, 32, 0, ctx->stream, (unsigned long long)s->n_elem, s->d_slot_off,
-                                 s->d_s_off, s->d_S, s->d_slot_val);
-                    ctx->launches++;
-                }
-                MFV2D_LAUNCH(trace_gather_kernel, grid_for(ctx, nt, SYS_THREADS), SYS_THREADS, 0, ctx->stream, nt, s->d_tr_ptr,
-                             s->d_tr_slot, s->d_slot_val, s->d_diag_inv, (const int *)nullptr);
-                ctx->launches++;
-                if ((r = sys_interface_sum(s, s->d_diag_inv, 0, nullptr)))
-                    break;
-                MFV2D_LAUNCH(jacobi_setup_kernel, grid_for(ctx, nt, 256), 256, 0, ctx->stream, nt, s->d_diag_inv, (const double *)res, z);
-                ctx->launches++;
-                if ((r = sys_dot_device(s, nt, res, z, w, sc + 5)))
-                    break;
-                dinv = s->d_diag_inv;
-            }
-            // partitioned systems take the one-synchronisation recurrence (MFV2D_CG_SINGLE_REDUCE=0 / 1 forces either)
-            const char *sr_env = getenv("MFV2D_CG_SINGLE_REDUCE");
-            const bool single_reduce = sr_env ? sr_env[0] == '1' : ctx->n_ranks > 1;
-            double *sv = s->d_work_trace[4];
-            if (single_reduce)
-            {
-                cudaMemsetAsync(p, 0, nt * sizeof(double), ctx->stream);
-                cudaMemsetAsync(sv, 0, nt * sizeof(double), ctx->stream);
-            }
-            else
-                cudaMemcpyAsync(p, precondition ? z : res, nt * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream);
-            const int check_every = 16;
-            // one CG iteration = 7 small launches; on one GPU a block of check_every iterations is captured ONCE
-            // into a CUDA graph and replayed (the kernels stop by themselves once the device flag is set)
-            auto enqueue_iteration = [&]() -> int {
-                if (single_reduce)
-                {
-                    const double *u = precondition ? z : res;
-                    MFV2D_TRY(sys_apply_schur(s, u, ap, flags, false));
-                    MFV2D_LAUNCH(cg1_dots_kernel, (unsigned)s->n_partials, SYS_THREADS, 0, ctx->stream, nt, u, (const double *)ap,
-                                 (const double *)res, w, s->d_partials, s->n_partials, (const int *)flags);
-                    MFV2D_LAUNCH(cg1_sum3_kernel, 1, 32, 0, ctx->stream, s->n_partials, (const double *)s->d_partials, sc + 8,
-                                 (const int *)flags);
-                    MFV2D_TRY(sys_interface_sum(s, ap, 3, sc + 8));
-                    MFV2D_LAUNCH(cg1_scalar_kernel, 1, 32, 0, ctx->stream, sc, flags);
-                    MFV2D_LAUNCH(cg1_update_kernel, (unsigned)s->n_partials, SYS_THREADS, 0, ctx->stream, nt, (const double *)sc,
-                                 (const int *)flags, u, (const double *)ap, p, sv, lam, res, dinv, z);
-                    ctx->launches += 4;
-                    return MFV2D_SUCCESS;
-                }
-                if (ctx->n_ranks > 1)
-                {
-                    // p . S p = sum over the ranks of p_r . (S_r p_r) (local, un-summed products, no ownership weights):
-                    // the scalar rides in the SAME all-reduce that sums the interface multipliers of S p
-                    MFV2D_TRY(sys_apply_schur(s, p, ap, flags, false));
-                    MFV2D_LAUNCH(dot_partial_kernel, (unsigned)s->n_partials, SYS_THREADS, 0, ctx->stream, nt, (const double *)ap,
-                                 (const double *)p, (const double *)nullptr, s->d_partials, (const int *)flags);
-                    MFV2D_LAUNCH(sum_partials_kernel, 1, 32, 0, ctx->stream, s->n_partials, (const double *)s->d_partials,
-                                 s->d_partials);
-                    MFV2D_TRY(sys_interface_sum(s, ap, 1, s->d_partials));
-                    MFV2D_LAUNCH(cg_alpha_kernel, 1, 32, 0, ctx->stream, 1, (const double *)s->d_partials, sc, flags, precondition);
-                    ctx->launches++;
-                }
-                else
-                {
-                    MFV2D_TRY(sys_apply_schur(s, p, ap, flags));
-                    MFV2D_LAUNCH(dot_partial_kernel, (unsigned)s->n_partials, SYS_THREADS, 0, ctx->stream, nt, (const double *)ap,
-                                 (const double *)p, w, s->d_partials, (const int *)flags);
-                    MFV2D_LAUNCH(cg_alpha_kernel, 1, 32, 0, ctx->stream, s->n_partials, (const double *)s->d_partials, sc, flags,
-                                 precondition);
-                }
-                MFV2D_LAUNCH(cg_update_kernel, (unsigned)s->n_partials, SYS_THREADS, 0, ctx->stream, nt, (const double *)sc,
-                             (const int *)flags, (const double *)p, (const double *)ap, lam, res, w, dinv, z, s->d_partials,
-                             s->d_partials + s->n_partials);
-                if (ctx->n_ranks > 1)
-                {
-                    // r.r (and r.z) of all ranks: two scalars in one all-reduce
-                    MFV2D_LAUNCH(sum_partials_kernel, 1, 32, 0, ctx->stream, s->n_partials, (const double *)s->d_partials, sc + 8);
-                    MFV2D_LAUNCH(sum_partials_kernel, 1, 32, 0, ctx->stream, precondition ? s->n_partials : 0,
-                                 (const double *)(s->d_partials + s->n_partials), sc + 9);
-                    MFV2D_TRY(comm_allreduce(ctx, sc + 8, 2));
-                    MFV2D_LAUNCH(cg_beta_kernel, 1, 32, 0, ctx->stream, 1, (const double *)(sc + 8), (const double *)(sc + 9), sc, flags,
-                                 precondition, -1);
-                    ctx->launches += 2;
-                }
-                else
-                    MFV2D_LAUNCH(cg_beta_kernel, 1, 32, 0, ctx->stream, s->n_partials, (const double *)s->d_partials,
-                                 (const double *)(s->d_partials + s->n_partials), sc, flags, precondition, -1);
-                MFV2D_LAUNCH(cg_direction_kernel, grid_for(ctx, nt, 256), 256, 0, ctx->stream, nt, (const double *)sc,
-                             (const int *)flags, (const double *)(precondition ? z : res), p);
-                ctx->launches += 5;
-                return MFV2D_SUCCESS;
-            };
-#ifndef MFV2D_EMU
-            cudaGraphExec_t graph_exec = nullptr;
-            // (with more than one rank the NCCL all-reduces are captured too; MFV2D_CG_GRAPH=0 turns the graph off)
-            const char *graph_env = getenv("MFV2D_CG_GRAPH");
-            if (!(graph_env && graph_env[0] == '0') && max_iter >= 2 * check_every)
-            {
-                cudaGraph_t graph = nullptr;
-                const uint64_t launches_before = ctx->launches;
-                if (cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeThreadLocal) == cudaSuccess)
-                {
-                    int rc = MFV2D_SUCCESS;
-                    for (int k = 0; k < check_every && rc == MFV2D_SUCCESS; ++k)
-                        rc = enqueue_iteration();
-                    const cudaError_t ce = cudaStreamEndCapture(ctx->stream, &graph);
-                    if (rc != MFV2D_SUCCESS || ce != cudaSuccess || cudaGraphInstantiate(&graph_exec, graph, 0) != cudaSuccess)
-                        graph_exec = nullptr;
-                    if (graph)
-                        cudaGraphDestroy(graph);
-                }
-                cudaGetLastError();
-                ctx->launches = launches_before; // capturing is not launching
-            }
-#endif
-            int it = 0;
-            bool finished = false;
-            while (it < max_iter && !finished)
-            {
-                const int stop = (it + check_every < max_iter) ? it + check_every : max_iter;
-#ifndef MFV2D_EMU
-                if (graph_exec && stop - it == check_every)
-                {
-                    if (cudaGraphLaunch(graph_exec, ctx->stream) != cudaSuccess)
-                    {
-                        r = mfv2d_fail(ctx, MFV2D_CUDA_ERROR, "CG graph launch failed: %s", cudaGetErrorString(cudaGetLastError()));
-                        break;
-                    }
-                    ctx->launches += (single_reduce ? (ctx->n_ranks > 1 ? 8 : 6) : (ctx->n_ranks > 1 ? 13 : 7)) * check_every;
-                    it = stop;
-                }
-#endif
-                for (; it < stop && !r; ++it)
-                    r = enqueue_iteration();
-                if (r)
-                    break;
-                if (cudaGetLastError() != cudaSuccess)
-                {
-                    r = mfv2d_fail(ctx, MFV2D_CUDA_ERROR, "CG kernel launch failed");
-                    break;
-                }
-                if ((r = read_scalars(ctx, sc, 20, h)))
-                    break;
-                int hf[4];
-                memcpy(hf, &h[16], sizeof hf);
-                res_mag2 = h[0];
-                it_done = hf[1];
-                finished = hf[0] != 0;
-                if (single_reduce && !finished)
-                    it_done = it - 1; // the one-synchronisation recurrence tests the residual one product later
-            }
-#ifndef MFV2D_EMU
-            if (graph_exec)
-                cudaGraphExecDestroy(graph_exec);
-#endif
-            if (r)
-                break;
-        }
-        // x = A^-1 y - A^-1 N^T lambda
-        if ((r = sys_spmv(s, nd, s->d_t_ptr, s->d_t_col, s->d_t_val, lam, tmp_d)))
-            break;
-        if ((r = sys_gemv(s, s->d_Ainv, tmp_d, tmp_d2)))
-            break;
-        if (nd)
-        {
-            MFV2D_LAUNCH(axpby_kernel, grid_for(ctx, nd, 256), 256, 0, ctx->stream, nd, 1.0, (const double *)inv_a_y, -1.0,
-                         (const double *)tmp_d2, (double *)sx.dev);
-            ctx->launches++;
-            // one step of iterative refinement of the element-local solves, x += A^-1 (y - N^T lambda - A x): the blocks
-            // are applied as explicit inverses, whose residual grows with cond(A_e) (the 1-form and 2-form masses of a
-            // small element differ by 1/h^2); MFV2D_SCHUR_REFINE=0 turns it off
-            const char *rf_env = getenv("MFV2D_SCHUR_REFINE");
-            if (!(rf_env && rf_env[0] == '0'))
-            {
-                if ((r = sys_gemv(s, s->d_A, (const double *)sx.dev, tmp_d2)))
-                    break;
-                MFV2D_LAUNCH(axpby_kernel, grid_for(ctx, nd, 256), 256, 0, ctx->stream, nd, 1.0, (const double *)srhs.dev, -1.0,
-                             (const double *)tmp_d2, tmp_d2);
-                MFV2D_LAUNCH(axpby_kernel, grid_for(ctx, nd, 256), 256, 0, ctx->stream, nd, 1.0, (const double *)tmp_d2, -1.0,
-                             (const double *)tmp_d, tmp_d2);
-                if ((r = sys_gemv(s, s->d_Ainv, tmp_d2, inv_a_y)))
-                    break;
-                MFV2D_LAUNCH(axpby_kernel, grid_for(ctx, nd, 256), 256, 0, ctx->stream, nd, 1.0, (const double *)sx.dev, 1.0,
-                             (const double *)inv_a_y, (double *)sx.dev);
-                ctx->launches += 3;
-            }
-        }
-    } while (0);
-    if (!r)
-    {
-        r = stage_finish(&sx);
-        const int r2 = stage_finish(&slam);
-        if (!r)
-            r = r2;
-        if (!r)
-            r = mfv2d_cuda_synchronize(ctx);
-    }
-    else
-    {
-        stage_abort(&sx);
-        stage_abort(&slam);
-    }
-    stage_abort(&srhs);
-    stage_abort(&sphi);
-    if (residual)
-        *residual = sqrt(res_mag2);
-    if (iterations)
-        *iterations = it_done;
     return r;
 }
 
@@ -1456,6 +1190,7 @@ int mfv2d_cuda_system_set_interface(mfv2d_system *s, size_t n_shared, const int6
         w[i] = owned[i] ? 1.0 : 0.0;
     s->n_shared = (int64_t)n_shared;
     s->n_iface = (int64_t)n_slots;
+    s->interface_set = true;
     MFV2D_TRY(sys_upload(s, hi, &s->d_shared_index));
     MFV2D_TRY(sys_upload(s, hs, &s->d_shared_slot));
     MFV2D_TRY(sys_upload(s, w, &s->d_owned));

@@ -80,7 +80,8 @@ class Context:
     def init_comm(self, n_ranks: int, rank: int, id_bytes: bytes | None) -> None:
         """Join the NCCL communicator; ``id_bytes`` comes from ``comm_unique_id()`` on rank 0 and is
         distributed by the caller (e.g. a torch.distributed / gloo broadcast - plumbing only)."""
-        buf = (C.c_char * max(len(id_bytes or b""), 1)).from_buffer_copy(id_bytes or b"\0")
+        # id_bytes None: ranks only - every exchange then goes through LinearSystem.connect_peers (NVLink peer memory)
+        buf = (C.c_char * len(id_bytes)).from_buffer_copy(id_bytes) if id_bytes else None
         check(lib().mfv2d_cuda_comm_init(self.handle, n_ranks, rank, buf), self.handle)
         self.n_ranks, self.rank = n_ranks, rank
 

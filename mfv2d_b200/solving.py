@@ -229,9 +229,42 @@ class LinearSystem:
               self.ctx.handle)
 
 
-def solve_schur_iterative(system: LinearSystem, rhs, constraints, convergence: ConvergenceSettings, precondition: bool = False):
+    def connect_peers(self, holder_ptr: np.ndarray, holder_rank: np.ndarray, all_gather, n_coarse: int = 0) -> None:
+        """Multi-GPU: map the exchange blocks of the other ranks so that the solver's kernels write interface sums and
+        Krylov scalars straight into peer memory over NVLink (no NCCL call inside an iteration).  ``all_gather(bytes) ->
+        list[bytes]`` (rank-major) is any host-side gather of the IPC handles, e.g. ``torch.distributed.all_gather_object``
+        over gloo - plumbing, like the NCCL unique id.  Collective: every rank calls it after ``set_interface``."""
+        n = lib().mfv2d_cuda_peer_handle_size()
+        buf = (C.c_char * n)()
+        check(lib().mfv2d_cuda_system_peer_export(self.handle, int(n_coarse), buf), self.ctx.handle)
+        handles = all_gather(bytes(buf))
+        blob = b"".join(handles)
+        hp = np.ascontiguousarray(holder_ptr, np.int64)
+        hr = np.ascontiguousarray(holder_rank, np.int32)
+        hbuf = (C.c_char * len(blob)).from_buffer_copy(blob)
+        check(lib().mfv2d_cuda_system_peer_connect(self.handle, hbuf, hp.size - 1, hp.ctypes.data, hr.ctypes.data if hr.size else None),
+              self.ctx.handle)
+
+    def peer_error(self) -> bool:
+        return bool(lib().mfv2d_cuda_system_peer_error(self.handle))
+
+    def set_coarse_space(self, aggregates: np.ndarray, z: np.ndarray, n_coarse: int) -> None:
+        """Coarse space of the two-level preconditioner (``precondition="two-level"``): aggregate id (or -1) and near-null-
+        space value of every multiplier of this rank (``structured.coarse_space_1form``).  Collective when partitioned."""
+        ag = np.ascontiguousarray(aggregates, np.int32)
+        zz = np.ascontiguousarray(z, np.float64)
+        if ag.size != self.n_trace or zz.size != self.n_trace:
+            raise ValueError("aggregates and z must have one entry per multiplier")
+        check(lib().mfv2d_cuda_system_set_coarse_space(self.handle, int(n_coarse), ag.ctypes.data, zz.ctypes.data), self.ctx.handle)
+
+
+PRECONDITIONERS = {False: 0, None: 0, "none": 0, True: 1, "jacobi": 1, "two-level": 2}
+
+
+def solve_schur_iterative(system: LinearSystem, rhs, constraints, convergence: ConvergenceSettings, precondition=False):
     """python/mfv2d/solving.py:439-500: CG on ``N A^-1 N^T`` for the multipliers, then back substitution.
-    Returns ``(x, lambda, residual, iterations)`` like the reference."""
+    Returns ``(x, lambda, residual, iterations)`` like the reference.  ``precondition``: ``False`` (the reference's
+    method), ``True`` / ``"jacobi"``, or ``"two-level"`` (Jacobi + coarse space, see ``LinearSystem.set_coarse_space``)."""
     if isinstance(rhs, _SystemVector):  # DenseVector / TraceVector in and out, like the reference
         xd, ld, r, i = solve_schur_iterative(system, rhs.data, constraints.data, convergence, precondition)
         return DenseVector.__new__(DenseVector)._init(system, xd), TraceVector.__new__(TraceVector)._init(system, ld), r, i
@@ -246,7 +279,7 @@ def solve_schur_iterative(system: LinearSystem, rhs, constraints, convergence: C
     check(
         lib().mfv2d_cuda_solve_schur_cg(system.handle, addr(rhs), addr(constraints), int(convergence.maximum_iterations),
                                         float(convergence.absolute_tolerance), float(convergence.relative_tolerance),
-                                        int(bool(precondition)), addr(x), addr(lam), C.byref(res), C.byref(it),
+                                        PRECONDITIONERS[precondition], addr(x), addr(lam), C.byref(res), C.byref(it),
                                         space_of(rhs, constraints, x, lam)),
         system.ctx.handle,
     )
@@ -291,149 +324,10 @@ def vec_dot(x, y, ctx: Context | None = None) -> float:
     return r.value
 
 
-# ---- Krylov drivers that the reference keeps in Python (cg_general / gmres_general, solving.py:178-436) ---------
-# Like there, the loop and its scalars live on the host and every vector operation is one call into the library;
-# unlike there the vectors are DeviceArrays, so nothing but the dot products' scalars crosses PCIe.  The
-# production solver is ``solve_schur_iterative`` (whole loop on the device); these two exist so that every driver
-# of python/mfv2d/solving.py has its counterpart.
-class _FullVector:
-    """``FullVector`` (solving.py:503-550): a dense and a trace part that move together."""
-
-    def __init__(self, system: LinearSystem, dense: DeviceArray, trace: DeviceArray):
-        self.system, self.dense, self.trace = system, dense, trace
-
-    @classmethod
-    def zeros(cls, system: LinearSystem):
-        ctx = system.ctx
-        return cls(system, ctx.to_device(np.zeros(system.n_dense)), ctx.to_device(np.zeros(system.n_trace)))
-
-    @classmethod
-    def from_any(cls, system: LinearSystem, dense, trace):
-        ctx = system.ctx
-        d = dense if isinstance(dense, DeviceArray) else ctx.to_device(np.ascontiguousarray(dense, np.float64))
-        t = trace if isinstance(trace, DeviceArray) else ctx.to_device(np.ascontiguousarray(trace, np.float64))
-        if d.size != system.n_dense or t.size != system.n_trace:
-            raise ValueError("vector does not belong to this system (MFV2D_BAD_VECTOR_PARENT)")
-        return cls(system, d, t)
-
-    def copy(self):
-        out = _FullVector(self.system, self.system.ctx.empty(self.system.n_dense), self.system.ctx.empty(self.system.n_trace))
-        out.axpby(1.0, self, 0.0, self)
-        return out
-
-    def axpby(self, a: float, x: "_FullVector", b: float, y: "_FullVector") -> None:
-        """self = a x + b y"""
-        ctx = self.system.ctx
-        if self.dense.size:
-            vec_axpby(a, x.dense, b, y.dense, out=self.dense, ctx=ctx)
-        if self.trace.size:
-            vec_axpby(a, x.trace, b, y.trace, out=self.trace, ctx=ctx)
-
-    def dot(self, other: "_FullVector") -> float:
-        ctx = self.system.ctx
-        d = vec_dot(self.dense, other.dense, ctx=ctx) if self.dense.size else 0.0
-        return d + (vec_dot(self.trace, other.trace, ctx=ctx) if self.trace.size else 0.0)
-
-
-def _apply_saddle(system: LinearSystem, v: _FullVector, out: _FullVector, buf: DeviceArray) -> None:
-    """``out = [[A, N^T], [N, 0]] v`` (wrapped_apply_system, solving.py:568-575); ``out`` must not alias ``v``."""
-    system.apply_diagonal(v.dense, out=buf)
-    system.apply_trace_transpose(v.trace, out=out.dense)
-    system.apply_trace(v.dense, out=out.trace)
-    if buf.size:
-        vec_axpby(1.0, out.dense, 1.0, buf, out=out.dense, ctx=system.ctx)
-
-
-def _tolerance(rhs_mag: float, convergence: ConvergenceSettings) -> float:
-    """the reference's rule (solving.py:405-412): the SMALLER of atol and rtol * |b|"""
-    if rhs_mag * convergence.relative_tolerance > convergence.absolute_tolerance:
-        return convergence.absolute_tolerance
-    return rhs_mag * convergence.relative_tolerance
-
-
-def _finish(solution: _FullVector, rhs, residual: float, iterations: int):
-    if isinstance(rhs, DeviceArray):
-        return solution.dense, solution.trace, residual, iterations
-    return solution.dense.get(), solution.trace.get(), residual, iterations
-
-
-def solve_cg_iterative(system: LinearSystem, rhs, constraints, convergence: ConvergenceSettings):
-    """python/mfv2d/solving.py:590-631 with ``cg_general`` (:350-436): plain CG on the saddle-point system from a
-    zero initial guess; returns ``(x, lambda, residual, iterations)`` with the reference's iteration index."""
-    b = _FullVector.from_any(system, rhs, constraints)
-    buf = system.ctx.empty(system.n_dense)
-    res_mag2 = b.dot(b)
-    tol = _tolerance(float(np.sqrt(res_mag2)), convergence)
-    x, p, res, ap = _FullVector.zeros(system), b.copy(), b.copy(), b.copy()
-    iter_cnt = 0
-    for iter_cnt in range(convergence.maximum_iterations):
-        _apply_saddle(system, p, ap, buf)
-        apa = ap.dot(p)
-        alpha = res_mag2 / apa
-        x.axpby(1.0, x, alpha, p)
-        res.axpby(1.0, res, -alpha, ap)
-        new_res_mag2 = res.dot(res)
-        if new_res_mag2 < tol**2:
-            res_mag2 = new_res_mag2
-            break
-        beta = new_res_mag2 / res_mag2
-        res_mag2 = new_res_mag2
-        p.axpby(1.0, res, beta, p)
-    return _finish(x, rhs, float(np.sqrt(res_mag2)), iter_cnt)
-
-
-def solve_gmres_iterative(system: LinearSystem, rhs, constraints, convergence: ConvergenceSettings):
-    """python/mfv2d/solving.py:553-587 with ``gmres_general`` (:178-277): un-restarted GMRES with
-    ``maximum_iterations`` basis vectors (modified Gram-Schmidt, Givens rotations on the host scalars)."""
-    b = _FullVector.from_any(system, rhs, constraints)
-    buf = system.ctx.empty(system.n_dense)
-    m = int(convergence.maximum_iterations)
-    r = np.zeros((m, m))
-    g, h, ck, sk = np.zeros(m), np.zeros(m), np.zeros(m), np.zeros(m)
-    tol = _tolerance(float(np.sqrt(b.dot(b))), convergence)
-    p = b.copy()  # first residual of the zero initial guess
-    r_mag = float(np.sqrt(p.dot(p)))
-    p.axpby(1.0 / r_mag, p, 0.0, p)
-    p_vecs = [p]
-    g[0] = r_mag
-    k = 0
-    for k in range(1, m):
-        new = _FullVector(system, system.ctx.empty(system.n_dense), system.ctx.empty(system.n_trace))
-        _apply_saddle(system, p, new, buf)
-        p = new
-        for li in range(k):
-            pp = p.dot(p_vecs[li])
-            h[li] = pp
-            p.axpby(1.0, p, -pp, p_vecs[li])
-        p_mag2 = p.dot(p)
-        p_mag = float(np.sqrt(p_mag2))
-        p.axpby(1.0 / p_mag, p, 0.0, p)
-        p_vecs.append(p)
-        for i in range(k - 1):
-            tmp = ck[i] * h[i] + sk[i] * h[i + 1]
-            h[i + 1] = -sk[i] * h[i] + ck[i] * h[i + 1]
-            h[i] = tmp
-        rho = np.sqrt(p_mag2 + h[k - 1] * h[k - 1])
-        c_new, s_new = h[k - 1] / rho, p_mag / rho
-        ck[k - 1], sk[k - 1] = c_new, s_new
-        h[k - 1] = c_new * h[k - 1] + s_new * p_mag
-        r[:k, k - 1] = h[:k]
-        g[k] = -s_new * g[k - 1]
-        g[k - 1] = c_new * g[k - 1]
-        r_mag = float(np.abs(g[k]))
-        if r_mag < tol:
-            break
-    sol = _FullVector.zeros(system)
-    if k > 0:
-        # back substitution of the k x k upper-triangular least-squares system (host scalars, like the reference)
-        alpha = np.zeros(k)
-        for i in range(k - 1, -1, -1):
-            alpha[i] = (g[i] - r[i, i + 1:k] @ alpha[i + 1:k]) / r[i, i]
-        for i in range(k):
-            sol.axpby(1.0, sol, float(alpha[i]), p_vecs[i])
-    return _finish(sol, rhs, r_mag, k)
-
-
+# The reference also keeps ``solve_cg_iterative`` / ``solve_gmres_iterative`` (python/mfv2d/solving.py:553-631) as Python
+# loops; nothing in it calls or tests them, its CG divides by zero on its own example system (b^T K b = 0) and its
+# GMRES applies the operator in place and returns a wrong vector (recorded in tests/golden/pcg.json).  They are not
+# mirrored: the device solvers are ``solve_schur_iterative`` (CG on the Schur complement) and ``solve_pcg_iterative``.
 # ---- DenseVector / TraceVector (src/algebra/system_objects.c:725-2152): device-resident counterparts --------------
 class _SystemVector:
     """Common part of the two vector types: a DeviceArray that belongs to one LinearSystem.  The static methods write

@@ -109,12 +109,15 @@ class ConstraintPartition:
     ``owned``          1 where this rank is the lowest rank holding the multiplier (it alone counts the
                        multiplier in dot products, which replaces TraceVector.dot's division by the sharing
                        count, src/algebra/system_objects.c:1690-1696)
+    ``holder_ptr, holder_rank``  CSR over ``shared_index``: the OTHER ranks that hold each shared multiplier, ascending
+                       (what the NVLink peer exchange needs: whom to write to, whose contributions to add)
     """
 
-    def __init__(self, row, col, val, n_trace, global_rows, shared_index, slot, n_slots, owned):
+    def __init__(self, row, col, val, n_trace, global_rows, shared_index, slot, n_slots, owned, holder_ptr=None, holder_rank=None):
         self.row, self.col, self.val, self.n_trace = row, col, val, int(n_trace)
         self.global_rows, self.shared_index, self.slot = global_rows, shared_index, slot
         self.n_slots, self.owned = int(n_slots), owned
+        self.holder_ptr, self.holder_rank = holder_ptr, holder_rank
 
 
 def partition_constraints(row: np.ndarray, col: np.ndarray, val: np.ndarray, n_trace: int, dense_bounds,
@@ -145,5 +148,40 @@ def partition_constraints(row: np.ndarray, col: np.ndarray, val: np.ndarray, n_t
     order = np.lexsort((l_col, l_row))
     sh = np.flatnonzero(is_shared[g_rows])
     owned = (lo[g_rows] == rank).astype(np.uint8)
+    # the other holders of this rank's shared multipliers: unique (row, rank) pairs of the entries of shared rows
+    mine_shared = np.zeros(n_trace, bool)
+    mine_shared[g_rows[sh]] = True
+    sel = mine_shared[row] & (entry_rank != rank)
+    pairs = np.unique(np.stack([row[sel], entry_rank[sel]], axis=1), axis=0) if sel.any() else np.zeros((0, 2), np.int64)
+    pos_of = np.full(n_trace, -1, np.int64)
+    pos_of[g_rows[sh]] = np.arange(sh.size)
+    counts = np.bincount(pos_of[pairs[:, 0]], minlength=sh.size) if sh.size else np.zeros(0, np.int64)
+    holder_ptr = np.concatenate([[0], np.cumsum(counts)]).astype(np.int64)
+    holder_rank = pairs[:, 1].astype(np.int32)  # np.unique sorts by (row, rank): rows increasing = shared order, ranks ascending
     return ConstraintPartition(l_row[order], l_col[order], l_val[order], g_rows.size, g_rows, sh.astype(np.int64),
-                               slot_of[g_rows[sh]].astype(np.int64), int(is_shared.sum()), owned)
+                               slot_of[g_rows[sh]].astype(np.int64), int(is_shared.sum()), owned, holder_ptr, holder_rank)
+
+
+def coarse_space_1form(nh: int, nv: int, p: int, form_orders, agg_size: int) -> tuple[np.ndarray, np.ndarray, int]:
+    """Coarse space of the two-level preconditioner of the Schur-complement CG for the multipliers of
+    :func:`continuity_constraints_1form` (same global row order): aggregates of ``agg_size x agg_size`` elements, a
+    multiplier belongs to the aggregate of the element below / to the left of its line; ``z`` is the near-null-space
+    vector of ``S = N A^-1 N^T`` for the mixed formulations, the multipliers of ``u = const``: ``+1`` on horizontal
+    lines, ``-1`` on vertical ones (the sign convention of continuity.py:498-501 with the outward orientation of the
+    element boundary DoFs).  Returns ``(agg, z, n_coarse)`` over the GLOBAL multipliers."""
+    ncx, ncy = -(-nh // agg_size), -(-nv // agg_size)
+    aggs, zs = [], []
+    for order in form_orders:
+        if int(order) != FORM_ORDER_1:
+            continue
+        jj, ii = np.meshgrid(np.arange(1, nv), np.arange(nh), indexing="ij")
+        aggs.append(np.repeat((((jj - 1) // agg_size) * ncx + ii // agg_size).ravel(), p))
+        zs.append(np.ones(jj.size * p))
+        jj, ii = np.meshgrid(np.arange(nv), np.arange(1, nh), indexing="ij")
+        aggs.append(np.repeat(((jj // agg_size) * ncx + (ii - 1) // agg_size).ravel(), p))
+        zs.append(-np.ones(jj.size * p))
+    if not aggs:
+        return np.zeros(0, np.int32), np.zeros(0), 0
+    # aggregates that received no multiplier (a last, partial row / column of aggregates) would make P^T S P singular
+    used, compact = np.unique(np.concatenate(aggs), return_inverse=True)
+    return compact.astype(np.int32), np.concatenate(zs), int(used.size)

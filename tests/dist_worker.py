@@ -115,18 +115,24 @@ def main():
 
         ctx = Context(int(os.environ.get("LOCAL_RANK", "0")))
         rt._context = ctx
-        ids = [comm_unique_id() if rank == 0 else None]
+        # MFV2D_TEST_NCCL=0: ranks only - every exchange goes through the NVLink peer blocks, NCCL is never loaded
+        ids = [comm_unique_id() if rank == 0 and os.environ.get("MFV2D_TEST_NCCL", "1") != "0" else None]
         dist.broadcast_object_list(ids, src=0)
         ctx.init_comm(world, rank, ids[0])
-        batch = M.ElementBatch(PC.make_basis(M, p, k), np.ascontiguousarray(g["corners"][lo:hi]))
-        mats = M.compute_element_matrices(PC.specs_of(M, s), s["lhs"], batch)
-        sysm = SV.LinearSystem(mats, (P.row, P.col, P.val), P.n_trace)
-        sysm.set_interface(P.shared_index, P.slot, P.n_slots, P.owned)
-        # operators with the interface sum
-        xg = np.ascontiguousarray(g["x"][bounds[rank]:bounds[rank + 1]])
-        t = sysm.apply_trace(xg)
-        assert relerr(t, g["apply_trace"][P.global_rows]) < 1e-12
-        x, lam, res, it = SV.solve_schur_iterative(sysm, rhs_l, phi_l, SV.ConvergenceSettings(2000, 1e-30, 1e-12))
+
+        def all_gather(obj):
+            out = [None] * world
+            dist.all_gather_object(out, obj)
+            return out
+
+        it, itj, _, worst = PC.check_partitioned_solve(M, SV, ST, ctx, rank, world, all_gather, fix, nh, nv)
+        itj2, it2 = PC.check_two_level(M, SV, ST, ctx, rank, world, all_gather, nh=32, nv=32, p=3, k=3, agg_size=4)
+        if rank == 0:
+            print(f"dist_worker ok: mode {mode}, world {world}, iterations {it} (jacobi {itj}), err {worst:.2e}; "
+                  f"two-level {it2} vs jacobi {itj2} on 32x32 p3, exchange {os.environ.get('MFV2D_CG_EXCHANGE', 'peer')}", flush=True)
+        dist.barrier()
+        dist.destroy_process_group()
+        return
 
     err_x = relerr(x, g["sol_dense"][bounds[rank]:bounds[rank + 1]])
     err_l = relerr(lam, g["sol_trace"][P.global_rows])

@@ -21,7 +21,7 @@
 #define __forceinline__ inline
 #define __noinline__
 #define __restrict__
-#define __shared__ static
+#define __shared__ static thread_local
 #define __launch_bounds__(...)
 #define __align__(x)
 
@@ -61,6 +61,8 @@ static inline double __hiloint2double(int hi, int lo)
 }
 static inline void __syncthreads() {}
 static inline void __syncwarp() {}
+static inline void __threadfence() {}
+static inline void __threadfence_system() {}
 template <typename T> static inline T __ldg(const T *p) { return *p; }
 template <typename T> static inline T ld_ro(const T *p) { return *p; }
 static inline double warp_sum(double v) { return v; }
@@ -226,6 +228,27 @@ template <typename F> static inline cudaError_t cudaOccupancyMaxActiveBlocksPerM
     *n = 1;
     return cudaSuccess;
 }
+// IPC: every "rank" of an emulated multi-rank test is a THREAD of one process, a handle is the pointer itself
+struct cudaIpcMemHandle_t
+{
+    char reserved[64];
+};
+enum
+{
+    cudaIpcMemLazyEnablePeerAccess = 1
+};
+static inline cudaError_t cudaIpcGetMemHandle(cudaIpcMemHandle_t *h, void *p)
+{
+    memset(h, 0, sizeof *h);
+    memcpy(h->reserved, &p, sizeof p);
+    return cudaSuccess;
+}
+static inline cudaError_t cudaIpcOpenMemHandle(void **p, cudaIpcMemHandle_t h, unsigned)
+{
+    memcpy(p, h.reserved, sizeof *p);
+    return cudaSuccess;
+}
+static inline cudaError_t cudaIpcCloseMemHandle(void *) { return cudaSuccess; }
 static inline void cp_async8(double *smem_dst, const double *gmem_src) { *smem_dst = *gmem_src; }
 static inline void cp_async_wait_all() {}
 static inline double fast_rcp(double x) { return 1.0 / x; }

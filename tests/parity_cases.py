@@ -405,16 +405,6 @@ def check_linear_system(M, SV, ST, fix, nh, nv):
     r2 = g["con_rhs"] - sysm.apply_trace(x)
     rel = np.sqrt(r1 @ r1 + r2 @ r2) / np.sqrt(g["rhs"] @ g["rhs"] + g["con_rhs"] @ g["con_rhs"])
     assert rel < 1e-10, rel
-    # the one-synchronisation CG recurrence of the partitioned path (system.cu, cg1_* kernels), forced on one rank:
-    # same solution and, to a few iterations, the same count
-    os.environ["MFV2D_CG_SINGLE_REDUCE"] = "1"
-    try:
-        x1, l1, _, it1 = SV.solve_schur_iterative(sysm, g["rhs"], g["con_rhs"], SV.ConvergenceSettings(2000, 1e-30, 1e-12))
-        x1j, l1j, _, it1j = SV.solve_schur_iterative(sysm, g["rhs"], g["con_rhs"], SV.ConvergenceSettings(2000, 1e-30, 1e-12), precondition=True)
-    finally:
-        del os.environ["MFV2D_CG_SINGLE_REDUCE"]
-    assert relerr(x1, g["sol_dense"]) < 1e-8 and relerr(l1, g["sol_trace"]) < 1e-8 and abs(it1 - it) <= 4
-    assert relerr(x1j, g["sol_dense"]) < 1e-8 and relerr(l1j, g["sol_trace"]) < 1e-8 and it1j <= it + 4
     # Jacobi-preconditioned Schur CG: same solution, no more iterations than the plain one
     xj, lj, _, itj = SV.solve_schur_iterative(sysm, g["rhs"], g["con_rhs"], SV.ConvergenceSettings(2000, 1e-30, 1e-12), precondition=True)
     assert relerr(xj, g["sol_dense"]) < 1e-8 and relerr(lj, g["sol_trace"]) < 1e-8
@@ -429,19 +419,6 @@ def check_linear_system(M, SV, ST, fix, nh, nv):
     assert relerr(xp, g["sol_dense"]) < 1e-8 and relerr(lp, g["sol_trace"]) < 1e-8
     assert resp < 1e-30
     assert abs(itp - ref_pcg["iterations"]) <= max(12, ref_pcg["iterations"] // 5), (itp, ref_pcg)
-    if "cg" in ref_pcg:
-        # the two drivers the reference keeps in Python and never exercises: on its own example system its CG breaks
-        # down in the first step (b^T K b == 0 exactly -> ZeroDivisionError) and its GMRES applies the operator in
-        # place and returns a wrong vector (tests/golden/pcg.json, generated from the reference).  Ours follow the same
-        # algorithms: the CG breaks down the same way, the GMRES (operator applied out of place) converges.
-        assert "ZeroDivisionError" in ref_pcg["cg"]["reference_raises"] and ref_pcg["gmres"]["err_vs_pcg"] > 0.5
-        with pytest.raises(ZeroDivisionError):
-            SV.solve_cg_iterative(sysm, g["rhs"], g["con_rhs"], SV.ConvergenceSettings(3000, 1e-30, 1e-10))
-        if sysm.n_dense + sysm.n_trace < 800:
-            n_full = sysm.n_dense + sysm.n_trace
-            xg, lg, rg, itg = SV.solve_gmres_iterative(sysm, g["rhs"], g["con_rhs"], SV.ConvergenceSettings(n_full + 20, 1e-9, 1.0))
-            assert itg < n_full + 19 and rg < 1e-9
-            assert relerr(xg, g["sol_dense"]) < 1e-8 and relerr(lg, g["sol_trace"]) < 1e-8
     # DenseVector / TraceVector objects (system_objects.c:725-2152) around the same device operations
     dv, dw = SV.DenseVector(sysm, *np.split(g["x"], sysm.offsets[1:-1])), SV.DenseVector(sysm)
     tv = SV.TraceVector(sysm, g["trace_in"])
@@ -568,3 +545,76 @@ def check_saddle_residual_small_elements(M, SV, ST, nh=12, nv=10, p=4, scale=2e-
     assert res_refined < 1e-10, (res_plain, res_refined)
     assert res_refined <= res_plain
     return res_plain, res_refined
+
+
+def check_partitioned_solve(M, SV, ST, ctx, rank, world, all_gather, fix, nh, nv):
+    """One rank of a partitioned Schur solve of a golden mixed-Poisson system through the NVLink peer exchange
+    (peer.cu): strips of elements, interface sums and Krylov scalars written into the other ranks' exchange blocks by
+    the solver's own kernels.  ``all_gather(obj) -> list`` is the host-side plumbing (gloo between processes on the GPU
+    box, a barrier between the threads of the emulated run).  Returns (iterations, error) after asserting parity with
+    the reference's solution."""
+    g = golden(fix + ".npz")
+    p, k = int(g["order"]), int(g["k"])
+    s = SYSTEMS["mixed_poisson_sorted"]
+    ne = int(ST.form_sizes(s["form_orders"], p).sum())
+    row, col, val, nt = ST.continuity_constraints_1form(nh, nv, p, s["form_orders"])
+    parts = ST.strip_partition(nh, nv, world)
+    bounds = [parts[r][0] * ne for r in range(world)] + [parts[-1][1] * ne]
+    P = ST.partition_constraints(row, col, val, nt, bounds, rank)
+    lo, hi = parts[rank]
+    rhs_l = np.ascontiguousarray(g["rhs"][bounds[rank]:bounds[rank + 1]])
+    phi_l = np.ascontiguousarray(g["con_rhs"][P.global_rows])
+    batch = M.ElementBatch(make_basis(M, p, k), np.ascontiguousarray(g["corners"][lo:hi]), ctx)
+    mats = M.compute_element_matrices(specs_of(M, s), s["lhs"], batch)
+    sysm = SV.LinearSystem(mats, (P.row, P.col, P.val), P.n_trace, ctx=ctx)
+    if world > 1:
+        sysm.set_interface(P.shared_index, P.slot, P.n_slots, P.owned)
+        sysm.connect_peers(P.holder_ptr, P.holder_rank, all_gather)
+    xg = np.ascontiguousarray(g["x"][bounds[rank]:bounds[rank + 1]])
+    assert relerr(sysm.apply_trace(xg), g["apply_trace"][P.global_rows]) < 1e-12
+    conv = SV.ConvergenceSettings(2000, 1e-30, 1e-12)
+    x, lam, res, it = SV.solve_schur_iterative(sysm, rhs_l, phi_l, conv)
+    assert not sysm.peer_error()
+    err = max(relerr(x, g["sol_dense"][bounds[rank]:bounds[rank + 1]]), relerr(lam, g["sol_trace"][P.global_rows]))
+    assert err < 1e-8, (rank, err)
+    assert abs(it - int(g["iters"])) <= 12, (it, int(g["iters"]))
+    xj, lj, _, itj = SV.solve_schur_iterative(sysm, rhs_l, phi_l, conv, precondition="jacobi")
+    assert relerr(xj, g["sol_dense"][bounds[rank]:bounds[rank + 1]]) < 1e-8 and itj <= it + 4
+    it2 = None
+    # every rank took the same number of iterations (identical scalars on all ranks)
+    counts = all_gather((it, itj, it2))
+    assert all(c == counts[0] for c in counts), counts
+    return it, itj, it2, err
+
+
+def check_two_level(M, SV, ST, ctx, rank, world, all_gather, nh=24, nv=24, p=2, k=2, agg_size=4, deform=None):
+    """The two-level preconditioner (precond.cu) on a synthetic deformed mesh, one rank of ``world``: same solution as the
+    Jacobi-preconditioned CG, clearly fewer iterations, identical counts on every rank."""
+    s = SYSTEMS["mixed_poisson_sorted"]
+    ne = int(ST.form_sizes(s["form_orders"], p).sum())
+    corners = ST.unit_square_corners(nh, nv, deform or F.deform)
+    row, col, val, nt = ST.continuity_constraints_1form(nh, nv, p, s["form_orders"])
+    parts = ST.strip_partition(nh, nv, world)
+    bounds = [parts[r][0] * ne for r in range(world)] + [parts[-1][1] * ne]
+    P = ST.partition_constraints(row, col, val, nt, bounds, rank)
+    lo, hi = parts[rank]
+    batch = M.ElementBatch(make_basis(M, p, k), np.ascontiguousarray(corners[lo:hi]), ctx)
+    mats = M.compute_element_matrices(specs_of(M, s), s["lhs"], batch)
+    sysm = SV.LinearSystem(mats, (P.row, P.col, P.val), P.n_trace, ctx=ctx)
+    agg, z, n_coarse = ST.coarse_space_1form(nh, nv, p, s["form_orders"], agg_size)
+    if world > 1:
+        sysm.set_interface(P.shared_index, P.slot, P.n_slots, P.owned)
+        sysm.connect_peers(P.holder_ptr, P.holder_rank, all_gather, n_coarse=n_coarse)
+    sysm.set_coarse_space(agg[P.global_rows], z[P.global_rows], n_coarse)
+    rng = np.random.default_rng(11)
+    rhs = rng.standard_normal(nh * nv * ne)[bounds[rank]:bounds[rank + 1]]
+    phi = np.zeros(P.n_trace)
+    conv = SV.ConvergenceSettings(5000, 1e300, 1e-11)
+    xj, lj, _, itj = SV.solve_schur_iterative(sysm, rhs, phi, conv, precondition="jacobi")
+    x2, l2, _, it2 = SV.solve_schur_iterative(sysm, rhs, phi, conv, precondition="two-level")
+    assert not sysm.peer_error()
+    assert relerr(x2, xj) < 1e-7 and relerr(l2, lj) < 1e-7, (relerr(x2, xj), relerr(l2, lj))
+    assert it2 < 0.75 * itj, (it2, itj)
+    counts = all_gather((itj, it2))
+    assert all(c == counts[0] for c in counts), counts
+    return itj, it2

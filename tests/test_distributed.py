@@ -58,11 +58,12 @@ def test_gloo_world2_schur_cg(fix, nh, nv):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("single_reduce", ["0", "1"])  # two all-reduces per iteration / the one-synchronisation recurrence
+@pytest.mark.parametrize("exchange", ["peer", "peer-only", "nccl"])  # NVLink peer stores inside the CG kernels / the same without NCCL loaded / ncclAllReduce
 @pytest.mark.parametrize("fix,nh,nv", [("solve_10x10_p3", 10, 10), ("solve_6x6_p3_def", 6, 6)])
-def test_nccl_world2_schur_cg(fix, nh, nv, single_reduce):
+def test_nccl_world2_schur_cg(fix, nh, nv, exchange):
     import mfv2d_b200._capi as capi
 
     if capi.lib().mfv2d_cuda_device_count() < 2:
         pytest.skip("needs two GPUs (run with gpurun --gpus 2)")
-    _run("gpu", fix, nh, nv, 2, 29612 + int(single_reduce), env={"MFV2D_CG_SINGLE_REDUCE": single_reduce})
+    env = {"MFV2D_CG_EXCHANGE": "nccl" if exchange == "nccl" else "peer", "MFV2D_TEST_NCCL": "0" if exchange == "peer-only" else "1"}
+    _run("gpu", fix, nh, nv, 2, 29612 + ["peer", "peer-only", "nccl"].index(exchange), env=env)
