@@ -158,6 +158,10 @@ MFV2D_API uint64_t mfv2d_cuda_launch_count(const mfv2d_ctx *ctx);
 /* write `bytes` of zeros-then-ones through a scratch buffer larger than L2 (bench L2 flush) */
 MFV2D_API int mfv2d_cuda_flush_l2(mfv2d_ctx *ctx);
 
+/* measured fp64 peaks of the device (TFLOP/s): mma.sync.m8n8k4.f64 chains and DFMA chains; the denominator of the
+ * matrix-free apply's roofline in bench.py (no counterpart in the reference) */
+MFV2D_API int mfv2d_cuda_measure_fp64_peak(mfv2d_ctx *ctx, double *tflops_dmma, double *tflops_dfma);
+
 /* =========================================================================================
  * polynomial tables (host code; O(p*q) doubles, computed once per (p, q))
  * ========================================================================================= */
@@ -384,11 +388,16 @@ MFV2D_API int mfv2d_cuda_system_peer_connect(mfv2d_system *sys, const void *hand
 /* non-zero after a peer wait timed out (a rank died): results of that call are invalid */
 MFV2D_API int mfv2d_cuda_system_peer_error(mfv2d_system *sys);
 
-/* Coarse space of the two-level preconditioner of solve_schur_cg (precondition = 2): agg[n_trace] = aggregate
- * (0 .. n_coarse - 1, or -1) of each multiplier of this rank, z[n_trace] = near-null-space vector of S = N A^-1 N^T on
- * them (identical on the ranks sharing a multiplier).  Collective on a partitioned system.  The reference has no
- * counterpart (its only preconditioner is block-Jacobi, python/mfv2d/solving.py:656-661). */
-MFV2D_API int mfv2d_cuda_system_set_coarse_space(mfv2d_system *sys, size_t n_coarse, const int32_t *agg, const double *z);
+/* Aggregate hierarchy of the additive multilevel preconditioner of solve_schur_cg (precondition = 2):
+ *   M^-1 = diag(S)^-1 + sum_l P_l diag(P_l^T S P_l)^-1 P_l^T + P_L (P_L^T S P_L)^-1 P_L^T,
+ * P_l = one column per aggregate of level l holding z (the near-null-space vector of S = N A^-1 N^T) on the aggregate.
+ *   n_agg[n_levels]; agg[n_levels][n_trace] = aggregate (or -1) of every multiplier of this rank on each level;
+ *   exact_last != 0: the last level is solved exactly (global aggregate ids, <= 4096); the other levels are rank-local
+ *   and must leave out the multipliers shared with other ranks.
+ * Collective on a partitioned system.  The reference has no counterpart (its only preconditioner is block-Jacobi on the
+ * saddle system, python/mfv2d/solving.py:656-661). */
+MFV2D_API int mfv2d_cuda_system_set_coarse_space(mfv2d_system *sys, int n_levels, const int64_t *n_agg, const int32_t *agg,
+                                                 const double *z, int exact_last);
 
 #ifdef __cplusplus
 }

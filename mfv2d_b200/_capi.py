@@ -69,6 +69,7 @@ SIGNATURES = {
     "mfv2d_cuda_timer_stop": (i32, [vp, C.POINTER(dbl)]),
     "mfv2d_cuda_launch_count": (C.c_uint64, [vp]),
     "mfv2d_cuda_flush_l2": (i32, [vp]),
+    "mfv2d_cuda_measure_fp64_peak": (i32, [vp, C.POINTER(dbl), C.POINTER(dbl)]),
     "mfv2d_gll": (i32, [i32, i32, dbl, dp, dp]),
     "mfv2d_lagrange1d": (i32, [i32, dp, i32, dp, dp]),
     "mfv2d_dlagrange1d": (i32, [i32, dp, i32, dp, dp]),
@@ -118,7 +119,7 @@ SIGNATURES = {
     "mfv2d_cuda_system_peer_export": (i32, [vp, sz, vp]),
     "mfv2d_cuda_system_peer_connect": (i32, [vp, vp, sz, vp, vp]),
     "mfv2d_cuda_system_peer_error": (i32, [vp]),
-    "mfv2d_cuda_system_set_coarse_space": (i32, [vp, sz, vp, vp]),
+    "mfv2d_cuda_system_set_coarse_space": (i32, [vp, i32, vp, vp, vp, i32]),
 }
 
 

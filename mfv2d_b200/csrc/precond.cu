@@ -1,16 +1,20 @@
 // Two-level preconditioner for the Schur-complement CG on the trace space ("includes a trace-space
 // preconditioner"; the reference has only block-Jacobi on the saddle system, python/mfv2d/solving.py:656-661).
 //
-//   M^-1 = D^-1 + P Ac^-1 P^T,   D = diag(S),   Ac = P^T S P
+//   M^-1 = D^-1 + sum_l P_l D_l^-1 P_l^T + P_L A_L^-1 P_L^T,   D = diag(S),  D_l = diag(P_l^T S P_l),  A_L = P_L^T S P_L
 //
-// P has ONE column per aggregate of multipliers: the near-null-space vector z of S (for the mixed Poisson / Darcy systems
-// the multipliers of u = const, +-1 per multiplier) restricted to the aggregate.  The CG iteration count of the plain
-// method grows like 1/h (12 201 iterations on the 10^6-element mesh of BASELINE.json configs[4]); with aggregates of
-// H x H elements it is bounded independently of the mesh size for fixed H (measured: tests/test_precond.py).
-// Ac (n_c <= 4096) is assembled element by element from the condensed blocks, summed over the ranks, inverted ONCE on
-// the device (dense.cu) and kept as a dense inverse: per iteration the coarse solve is one n_c x n_c mat-vec that every
-// rank performs redundantly on the all-reduced restriction - which travels through the same NVLink peer exchange as the
-// interface multipliers (type 1 area), or through ncclAllReduce when the peers are not mapped.
+// an additive multilevel (BPX-type) preconditioner.  Every level l has ONE vector per aggregate of multipliers: the
+// near-null-space vector z of S (for the mixed Poisson / Darcy systems the multipliers of u = const, +-1 per multiplier)
+// restricted to the aggregate.  The intermediate levels (aggregates of a few elements, local to a rank: shared
+// multipliers are left out of them) only need the DIAGONAL of their coarse operator; the last level (<= 4096 aggregates,
+// global) is solved exactly: A_L is assembled element by element from the condensed blocks, summed over the ranks,
+// inverted ONCE on the device (dense.cu) and kept as a dense inverse, so that per iteration the coarse solve is one
+// mat-vec that every rank performs redundantly on the all-reduced restriction - which travels through the same NVLink
+// peer exchange as the interface multipliers (type 1 area), or through ncclAllReduce when the peers are not mapped.
+// The CG iteration count of the plain method grows like 1/h (12 201 iterations on the 10^6-element mesh of
+// BASELINE.json configs[4]); with the hierarchy it is bounded for a fixed size of the last level's aggregates.
+// Four launches per application: chunk partial sums of all levels | per-aggregate sums (scaled by D_l^-1, or sent to the
+// peers) | coarse mat-vec | prolongation of all levels.
 #include <algorithm>
 
 #include "system.cuh"
@@ -18,30 +22,34 @@
 int launch_inverse_batch(mfv2d_ctx *ctx, int n, size_t batch, const double *d_in, double *d_out, int32_t *d_status);
 
 #define COARSE_MAX 4096
+#define COARSE_MAX_LEVELS 6
+#define COARSE_CHUNK 256
 
-// Ac[a(r)][a(s)] += z_r z_s S_e[r][s] over the slots of every element (atomics: set-up only; the order of the sums, and
-// with it the last bits of the PRECONDITIONER, may differ from run to run - the solution does not depend on it)
+// coarse operator entries from the condensed blocks: z_r z_s S_e[r][s] is added to out[a(r) * nc + a(s)] (full = 1) or, only
+// where a(r) == a(s), to out[a(r)] (full = 0: the diagonal of P^T S P).  Atomics: set-up only; the order of the sums, and
+// with it the last bits of the PRECONDITIONER, may differ from run to run - the solution does not depend on it.
 __global__ void coarse_assemble_kernel(unsigned long long n_elem, const int64_t *__restrict__ slot_off, const int64_t *__restrict__ slot_trace,
                                        const int64_t *__restrict__ s_off, const double *__restrict__ S, int packed,
-                                       const int32_t *__restrict__ agg, const double *__restrict__ cz, long long nc, double *__restrict__ Ac)
+                                       const int32_t *__restrict__ agg, const double *__restrict__ cz, long long nc, int full,
+                                       double *__restrict__ out)
 {
     for (unsigned long long e = blockIdx.x; e < n_elem; e += gridDim.x)
     {
         const int64_t s0 = slot_off[e];
         const int m = (int)(slot_off[e + 1] - s0);
         const double *Se = S + s_off[e];
-        const int half = m >> 1, kfull = (m + 1) >> 1;
+        const int half = m >> 1;
         for (int idx = threadIdx.x; idx < m * m; idx += blockDim.x)
         {
             const int s = idx / m, r = idx - s * m;
             const int64_t ir = slot_trace[s0 + r], is = slot_trace[s0 + s];
             const int ar = agg[ir], as = agg[is];
-            if (ar < 0 || as < 0)
+            if (ar < 0 || as < 0 || (!full && ar != as))
                 continue;
             double v;
             if (packed)
             {
-                // entry (k, row) with (row + k) % m = col, k <= m / 2
+                // S[r][s] is stored as entry (k, r), k = (s - r) mod m, if k is in the stored half, else as its mirror image
                 int k = s - r;
                 if (k < 0)
                     k += m;
@@ -51,36 +59,65 @@ __global__ void coarse_assemble_kernel(unsigned long long n_elem, const int64_t 
                     k = m - k;
                     row = s;
                 }
-                (void)kfull;
                 v = Se[(size_t)k * m + row];
             }
             else
                 v = Se[idx];
-            atomicAdd(&Ac[(size_t)ar * nc + as], cz[ir] * cz[is] * v);
+            atomicAdd(full ? &out[(size_t)ar * nc + as] : &out[ar], cz[ir] * cz[is] * v);
         }
+    }
+}
+
+// d[i] = 1 / d[i] (1 where it vanishes)
+__global__ void reciprocal_kernel(long long n, double *__restrict__ d)
+{
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+        d[i] = d[i] != 0.0 ? 1.0 / d[i] : 1.0;
+}
+
+// part[c] = sum over the multipliers i of chunk c of own_i z_i r_i (one warp per chunk, fixed order)
+__global__ void __launch_bounds__(SYS_THREADS) coarse_chunk_kernel(long long n_chunks, const int64_t *__restrict__ chunk_ptr,
+                                                                  const int64_t *__restrict__ chunk_idx, const double *__restrict__ cz,
+                                                                  const double *__restrict__ own, const double *__restrict__ r,
+                                                                  double *__restrict__ part, const int *__restrict__ done)
+{
+    if (done && *done)
+        return;
+    const int warp = threadIdx.x >> 5, nwarps = MFV2D_NWARPS;
+    for (long long c = (long long)blockIdx.x * nwarps + warp; c < n_chunks; c += (long long)gridDim.x * nwarps)
+    {
+        double acc = 0.0;
+        for (int64_t k = chunk_ptr[c] + MFV2D_LANE0; k < chunk_ptr[c + 1]; k += MFV2D_LANE_STEP)
+        {
+            const int64_t i = chunk_idx[k];
+            acc = fma(cz[i], own ? r[i] * own[i] : r[i], acc);
+        }
+        acc = warp_sum(acc);
+        if (MFV2D_LANE0 == 0)
+            part[c] = acc;
     }
 }
 
 struct CoarseArgs
 {
-    long long nc;
-    const int64_t *cg_ptr, *cg_idx;
-    const double *cz, *own, *r;
-    double *rc;   // [nc] this rank's restriction
-    int *tickets; // CTA ticket counter (last-block pattern)
+    long long n_agg_total, exact_begin, n_exact; // aggregates of all levels; the exact level is the tail [exact_begin, +n_exact)
+    const int64_t *aggchunk_ptr;                 // [n_agg_total + 1] chunks of each aggregate (contiguous)
+    const double *part, *ldinv;                  // chunk partial sums; 1 / D_l per aggregate of the diagonal levels
+    double *y;                                   // [n_agg_total] scaled restrictions (diagonal levels) | this rank's rc (exact level)
+    int *tickets;                                // CTA ticket counter (last-block pattern)
     const int *done;
     PeerView pv;
 };
 
-// rc[I] = sum over the multipliers i of aggregate I of own_i z_i r_i (one warp per aggregate, fixed order); on a partitioned
-// system the values are written into the type-1 area of every peer and the last CTA releases the epoch flag
-__global__ void __launch_bounds__(SYS_THREADS) coarse_restrict_kernel(const CoarseArgs a)
+// y[J] = (sum of the chunks of aggregate J) / D_l for the diagonal levels; for the exact level the sums are this rank's part
+// of the restricted residual: written into the type-1 area of every peer, and the last CTA releases the epoch flag
+__global__ void __launch_bounds__(SYS_THREADS) coarse_aggregate_kernel(const CoarseArgs a)
 {
     if (a.done && *a.done)
         return;
     __shared__ int s_last;
     const PeerView &pv = a.pv;
-    const bool peers = pv.n_ranks > 1;
+    const bool peers = pv.n_ranks > 1 && a.n_exact > 0;
     unsigned long long e = 0;
     int parity = 0;
     if (peers)
@@ -90,24 +127,20 @@ __global__ void __launch_bounds__(SYS_THREADS) coarse_restrict_kernel(const Coar
         e = pv.epoch[1] + 1;
         parity = (int)(e & 1);
     }
-    const int warp = threadIdx.x >> 5, nwarps = MFV2D_NWARPS;
-    for (long long I = (long long)blockIdx.x * nwarps + warp; I < a.nc; I += (long long)gridDim.x * nwarps)
+    for (long long J = blockIdx.x * (long long)blockDim.x + threadIdx.x; J < a.n_agg_total; J += (long long)gridDim.x * blockDim.x)
     {
         double acc = 0.0;
-        for (int64_t k = a.cg_ptr[I] + MFV2D_LANE0; k < a.cg_ptr[I + 1]; k += MFV2D_LANE_STEP)
+        for (int64_t c = a.aggchunk_ptr[J]; c < a.aggchunk_ptr[J + 1]; ++c)
+            acc += a.part[c];
+        if (J < a.exact_begin)
+            a.y[J] = acc * a.ldinv[J];
+        else
         {
-            const int64_t i = a.cg_idx[k];
-            const double ri = a.own ? a.r[i] * a.own[i] : a.r[i];
-            acc = fma(a.cz[i], ri, acc);
-        }
-        acc = warp_sum(acc);
-        if (MFV2D_LANE0 == 0)
-        {
-            a.rc[I] = acc;
+            a.y[J] = acc;
             if (peers)
                 for (int r = 0; r < pv.n_ranks; ++r)
                     if (r != pv.rank)
-                        peer_region(pv, r, 1, parity, pv.rank)[I] = acc;
+                        peer_region(pv, r, 1, parity, pv.rank)[J - a.exact_begin] = acc;
         }
     }
     if (!peers)
@@ -130,7 +163,8 @@ __global__ void __launch_bounds__(SYS_THREADS) coarse_restrict_kernel(const Coar
     }
 }
 
-// yc = Ac^-1 (sum over the ranks of rc), one warp per row; every CTA forms the rank-ordered sum in shared memory
+// yc = A_L^-1 (sum over the ranks of rc), one warp per row; every CTA forms the rank-ordered sum in shared memory.
+// rc and yc may not alias: rc = y[exact_begin ...] (input), yc = separate array
 __global__ void __launch_bounds__(SYS_THREADS) coarse_solve_kernel(long long nc, const double *__restrict__ Ainv, const double *__restrict__ rc,
                                                                   double *__restrict__ yc, const int *__restrict__ done, PeerView pv)
 {
@@ -168,131 +202,81 @@ __global__ void __launch_bounds__(SYS_THREADS) coarse_solve_kernel(long long nc,
     }
 }
 
-// z[i] += cz[i] yc[agg[i]]
-__global__ void coarse_prolong_kernel(long long n, const int32_t *__restrict__ agg, const double *__restrict__ cz, const double *__restrict__ yc,
-                                      double *__restrict__ z, const int *__restrict__ done)
+// z[i] += cz[i] * sum over the levels of y_l[agg_l[i]]  (the exact level reads yc)
+__global__ void coarse_prolong_kernel(long long n, int n_levels, const int32_t *__restrict__ lagg, const long long *__restrict__ agg_off,
+                                      long long exact_begin, const double *__restrict__ cz, const double *__restrict__ y,
+                                      const double *__restrict__ yc, double *__restrict__ z, const int *__restrict__ done)
 {
     if (done && *done)
         return;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
     {
-        const int a = agg[i];
-        if (a >= 0)
-            z[i] = fma(cz[i], yc[a], z[i]);
+        double acc = 0.0;
+        for (int l = 0; l < n_levels; ++l)
+        {
+            const int a = lagg[(size_t)l * n + i];
+            if (a >= 0)
+            {
+                const long long J = agg_off[l] + a;
+                acc += J < exact_begin ? y[J] : yc[J - exact_begin];
+            }
+        }
+        z[i] = fma(cz[i], acc, z[i]);
     }
 }
 
-// z += P Ac^-1 P^T r  (three launches; `done` = the CG's device flag so that a captured iteration stops by itself)
+// z += sum_l P_l D_l^-1 P_l^T r + P_L A_L^-1 P_L^T r  (`done` = the CG's device flag: a captured iteration stops by itself)
 int coarse_correction(mfv2d_system *s, const double *r, double *z, const int *done, bool use_peers)
 {
     mfv2d_ctx *ctx = s->ctx;
-    const long long nc = s->n_coarse;
-    if (!s->coarse_ready || nc == 0 || s->n_trace == 0)
+    if (!s->coarse_ready || s->n_trace == 0)
         return MFV2D_SUCCESS;
     const int warps = SYS_THREADS / 32;
+    const long long cap = (long long)ctx->sm_count * 8;
     PeerView one;
-    const unsigned grid = (unsigned)std::min<long long>((nc + warps - 1) / warps, (long long)ctx->sm_count * 4);
-    CoarseArgs ca{nc, s->d_cg_ptr, s->d_cg_idx, s->d_cz, s->d_owned, r, s->d_rc, reinterpret_cast<int *>(s->d_cg + 40), done,
-                  use_peers ? s->peer : one};
-    MFV2D_LAUNCH(coarse_restrict_kernel, grid, SYS_THREADS, 0, ctx->stream, ca);
-    if (ctx->n_ranks > 1 && !use_peers)
-        MFV2D_TRY(comm_allreduce(ctx, s->d_rc, (size_t)nc));
-    const size_t smem = (size_t)nc * sizeof(double);
-    MFV2D_LAUNCH(coarse_solve_kernel, grid, SYS_THREADS, smem, ctx->stream, nc, (const double *)s->d_Ac_inv, (const double *)s->d_rc, s->d_yc,
-                 done, use_peers ? s->peer : one);
-    MFV2D_LAUNCH(coarse_prolong_kernel, grid_for(ctx, s->n_trace, 256), 256, 0, ctx->stream, (long long)s->n_trace,
-                 (const int32_t *)s->d_agg, (const double *)s->d_cz, (const double *)s->d_yc, z, done);
-    ctx->launches += 3;
+    if (s->n_chunks)
+    {
+        MFV2D_LAUNCH(coarse_chunk_kernel, (unsigned)std::min<long long>((s->n_chunks + warps - 1) / warps, cap), SYS_THREADS, 0, ctx->stream,
+                     s->n_chunks, (const int64_t *)s->d_chunk_ptr, (const int64_t *)s->d_chunk_idx, (const double *)s->d_cz,
+                     (const double *)s->d_owned, r, s->d_cpart, done);
+        ctx->launches++;
+    }
+    CoarseArgs ca{s->n_agg_total, s->exact_begin, s->n_exact, s->d_aggchunk_ptr, s->d_cpart, s->d_ldinv, s->d_cy,
+                  reinterpret_cast<int *>(s->d_cg + 40), done, use_peers ? s->peer : one};
+    MFV2D_LAUNCH(coarse_aggregate_kernel, grid_for(ctx, s->n_agg_total, SYS_THREADS), SYS_THREADS, 0, ctx->stream, ca);
+    ctx->launches++;
+    if (s->n_exact)
+    {
+        if (ctx->n_ranks > 1 && !use_peers)
+            MFV2D_TRY(comm_allreduce(ctx, s->d_cy + s->exact_begin, (size_t)s->n_exact));
+        const unsigned grid = (unsigned)std::min<long long>((s->n_exact + warps - 1) / warps, (long long)ctx->sm_count * 4);
+        MFV2D_LAUNCH(coarse_solve_kernel, grid, SYS_THREADS, (size_t)s->n_exact * sizeof(double), ctx->stream, s->n_exact,
+                     (const double *)s->d_Ac_inv, (const double *)(s->d_cy + s->exact_begin), s->d_yc, done, use_peers ? s->peer : one);
+        ctx->launches++;
+    }
+    MFV2D_LAUNCH(coarse_prolong_kernel, grid_for(ctx, s->n_trace, 256), 256, 0, ctx->stream, (long long)s->n_trace, s->n_clevels,
+                 (const int32_t *)s->d_lagg, (const long long *)s->d_agg_off, s->exact_begin, (const double *)s->d_cz,
+                 (const double *)s->d_cy, (const double *)s->d_yc, z, done);
+    ctx->launches++;
     MFV2D_CUDA_CHECK(ctx, cudaGetLastError());
     return MFV2D_SUCCESS;
 }
 
 extern "C" {
 
-// Declare the coarse space of the two-level preconditioner: agg[n_trace] = aggregate (0 .. n_coarse-1, or -1) of every
-// multiplier of THIS rank, z[n_trace] = the near-null-space vector of S on them (both must agree between the ranks that
-// share a multiplier).  Assembles Ac = P^T S P from the condensed blocks, sums it over the ranks and inverts it.
+// Declare the aggregate hierarchy of the multilevel preconditioner (precondition = 2 of solve_schur_cg).
+//   n_levels, n_agg[n_levels]     aggregates per level
+//   agg[n_levels][n_trace]        aggregate (0 .. n_agg[l] - 1, or -1) of every multiplier of THIS rank on level l
+//   z[n_trace]                    near-null-space vector of S on them (identical on the ranks sharing a multiplier)
+//   exact_last                    != 0: the last level is solved exactly; its aggregates are numbered GLOBALLY (the same ids
+//                                 on every rank, n_agg <= 4096); all other levels are rank-local and must not contain
+//                                 shared multipliers
 // Collective on a partitioned system (after set_interface / peer_connect).
-int mfv2d_cuda_system_set_coarse_space(mfv2d_system *s, size_t n_coarse, const int32_t *agg, const double *z)
+int mfv2d_cuda_system_set_coarse_space(mfv2d_system *s, int n_levels, const int64_t *n_agg, const int32_t *agg, const double *z,
+                                       int exact_last)
 {
     mfv2d_ctx *ctx = s->ctx;
     s->coarse_ready = false;
-    if (n_coarse == 0)
-        return MFV2D_SUCCESS;
-    if (n_coarse > COARSE_MAX)
-        return mfv2d_fail(ctx, MFV2D_CUDA_UNSUPPORTED, "set_coarse_space: at most %d aggregates (the coarse operator is kept as a dense inverse)", COARSE_MAX);
-    MFV2D_TRY(sys_require_interface(s));
-    const bool use_peers = sys_use_peers(s);
-    if (use_peers && (int64_t)n_coarse > s->n_coarse_cap)
-        return mfv2d_fail(ctx, MFV2D_BAD_ARGUMENT, "set_coarse_space: %zu aggregates, but peer_export reserved room for %lld", n_coarse,
-                          (long long)s->n_coarse_cap);
-    const int64_t nt = s->n_trace;
-    std::vector<int32_t> h_agg(agg, agg + nt);
-    std::vector<double> h_z(z, z + nt);
-    std::vector<int64_t> ptr(n_coarse + 1, 0), idx;
-    for (int64_t i = 0; i < nt; ++i)
-    {
-        if (h_agg[i] >= (int64_t)n_coarse)
-            return mfv2d_fail(ctx, MFV2D_INDEX_OUT_OF_RANGE, "set_coarse_space: aggregate %d of multiplier %lld is out of range", h_agg[i],
-                              (long long)i);
-        if (h_agg[i] >= 0)
-            ptr[h_agg[i] + 1]++;
-    }
-    for (size_t a = 0; a < n_coarse; ++a)
-        ptr[a + 1] += ptr[a];
-    idx.resize((size_t)ptr[n_coarse]);
-    {
-        std::vector<int64_t> fill(ptr.begin(), ptr.end() - 1);
-        for (int64_t i = 0; i < nt; ++i)
-            if (h_agg[i] >= 0)
-                idx[fill[h_agg[i]]++] = i;
-    }
-    s->n_coarse = (int64_t)n_coarse;
-    MFV2D_TRY(sys_upload(s, h_agg, &s->d_agg));
-    MFV2D_TRY(sys_upload(s, h_z, &s->d_cz));
-    MFV2D_TRY(sys_upload(s, ptr, &s->d_cg_ptr));
-    MFV2D_TRY(sys_upload(s, idx, &s->d_cg_idx));
-    const size_t nn = n_coarse * n_coarse;
-    double *d_Ac = nullptr;
-    int32_t *d_status = nullptr;
-    MFV2D_TRY(sys_alloc(s, nn, &d_Ac));
-    MFV2D_TRY(sys_alloc(s, nn, &s->d_Ac_inv));
-    MFV2D_TRY(sys_alloc(s, n_coarse, &s->d_rc));
-    MFV2D_TRY(sys_alloc(s, n_coarse, &s->d_yc));
-    MFV2D_TRY(sys_alloc(s, (size_t)2, &d_status));
-    MFV2D_CUDA_CHECK(ctx, cudaMemsetAsync(d_Ac, 0, nn * sizeof(double), ctx->stream));
-    if (s->n_elem)
-    {
-        long long grid = (long long)ctx->sm_count * 8;
-        if (grid > s->n_elem)
-            grid = s->n_elem;
-        MFV2D_LAUNCH(coarse_assemble_kernel, (unsigned)grid, 128, 0, ctx->stream, (unsigned long long)s->n_elem, s->d_slot_off, s->d_slot_trace,
-                     s->d_s_off, (const double *)s->d_S, (int)s->symmetric, (const int32_t *)s->d_agg, (const double *)s->d_cz,
-                     (long long)n_coarse, d_Ac);
-        ctx->launches++;
-        MFV2D_CUDA_CHECK(ctx, cudaGetLastError());
-    }
-    if (ctx->n_ranks > 1)
-    {
-        if (use_peers)
-        {
-            // row by row through the type-1 area of the exchange blocks (n_coarse doubles per exchange)
-            for (size_t row = 0; row < n_coarse; ++row)
-                MFV2D_TRY(peer_dense_sum(s, d_Ac + row * n_coarse, (long long)n_coarse));
-        }
-        else
-            MFV2D_TRY(comm_allreduce(ctx, d_Ac, nn));
-    }
-    MFV2D_TRY(launch_inverse_batch(ctx, (int)n_coarse, 1, d_Ac, s->d_Ac_inv, d_status));
-    int32_t st = 0;
-    MFV2D_TRY(mfv2d_cuda_download(ctx, &st, d_status, sizeof st));
-    if (st != MFV2D_SUCCESS)
-        return mfv2d_fail(ctx, MFV2D_PIVOT_FAILED, "set_coarse_space: the coarse operator P^T S P is singular (an aggregate without multipliers, "
-                                                   "or a system whose Schur complement has a null space along z)");
-    const size_t smem = n_coarse * sizeof(double);
-    if (smem > 48 * 1024)
-        MFV2D_CUDA_CHECK(ctx, cudaFuncSetAttribute(coarse_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    s->coarse_ready = true;
 #ifndef MFV2D_EMU
     if (s->cg_graph_exec)
     {
@@ -300,6 +284,133 @@ int mfv2d_cuda_system_set_coarse_space(mfv2d_system *s, size_t n_coarse, const i
         s->cg_graph_exec = nullptr;
     }
 #endif
+    if (n_levels == 0)
+        return MFV2D_SUCCESS;
+    if (n_levels < 0 || n_levels > COARSE_MAX_LEVELS)
+        return mfv2d_fail(ctx, MFV2D_BAD_ARGUMENT, "set_coarse_space: 1 to %d levels", COARSE_MAX_LEVELS);
+    MFV2D_TRY(sys_require_interface(s));
+    const bool use_peers = sys_use_peers(s);
+    const int64_t nt = s->n_trace;
+    const int64_t n_exact = exact_last ? n_agg[n_levels - 1] : 0;
+    if (n_exact > COARSE_MAX)
+        return mfv2d_fail(ctx, MFV2D_CUDA_UNSUPPORTED, "set_coarse_space: the exact level has %lld aggregates, at most %d (its operator is kept as a "
+                                                       "dense inverse)", (long long)n_exact, COARSE_MAX);
+    if (use_peers && n_exact > s->n_coarse_cap)
+        return mfv2d_fail(ctx, MFV2D_BAD_ARGUMENT, "set_coarse_space: %lld global aggregates, but peer_export reserved room for %lld",
+                          (long long)n_exact, (long long)s->n_coarse_cap);
+    std::vector<long long> agg_off(n_levels, 0);
+    long long total = 0;
+    for (int l = 0; l < n_levels; ++l)
+    {
+        agg_off[l] = total;
+        total += n_agg[l];
+    }
+    const long long exact_begin = total - n_exact;
+    // chunk lists: the multipliers of every aggregate in increasing order, cut into chunks of COARSE_CHUNK
+    std::vector<int64_t> count((size_t)total + 1, 0);
+    for (int l = 0; l < n_levels; ++l)
+        for (int64_t i = 0; i < nt; ++i)
+        {
+            const int32_t a = agg[(size_t)l * nt + i];
+            if (a >= n_agg[l])
+                return mfv2d_fail(ctx, MFV2D_INDEX_OUT_OF_RANGE, "set_coarse_space: aggregate %d of multiplier %lld on level %d is out of range", a,
+                                  (long long)i, l);
+            if (a >= 0)
+                count[agg_off[l] + a + 1]++;
+        }
+    for (long long J = 0; J < total; ++J)
+        count[J + 1] += count[J];
+    std::vector<int64_t> idx((size_t)count[total]);
+    {
+        std::vector<int64_t> fill(count.begin(), count.end() - 1);
+        for (int l = 0; l < n_levels; ++l)
+            for (int64_t i = 0; i < nt; ++i)
+            {
+                const int32_t a = agg[(size_t)l * nt + i];
+                if (a >= 0)
+                    idx[fill[agg_off[l] + a]++] = i;
+            }
+    }
+    std::vector<int64_t> chunk_ptr(1, 0), aggchunk_ptr((size_t)total + 1, 0);
+    for (long long J = 0; J < total; ++J)
+    {
+        for (int64_t k = count[J]; k < count[J + 1]; k += COARSE_CHUNK)
+            chunk_ptr.push_back(std::min<int64_t>(k + COARSE_CHUNK, count[J + 1]));
+        aggchunk_ptr[J + 1] = (int64_t)chunk_ptr.size() - 1;
+    }
+    s->n_clevels = n_levels;
+    s->n_agg_total = total;
+    s->exact_begin = exact_begin;
+    s->n_exact = n_exact;
+    s->n_chunks = (long long)chunk_ptr.size() - 1;
+    std::vector<int32_t> h_agg(agg, agg + (size_t)n_levels * nt);
+    std::vector<double> h_z(z, z + nt);
+    MFV2D_TRY(sys_upload(s, h_agg, &s->d_lagg));
+    MFV2D_TRY(sys_upload(s, agg_off, &s->d_agg_off));
+    MFV2D_TRY(sys_upload(s, h_z, &s->d_cz));
+    MFV2D_TRY(sys_upload(s, chunk_ptr, &s->d_chunk_ptr));
+    MFV2D_TRY(sys_upload(s, idx, &s->d_chunk_idx));
+    MFV2D_TRY(sys_upload(s, aggchunk_ptr, &s->d_aggchunk_ptr));
+    MFV2D_TRY(sys_alloc(s, (size_t)s->n_chunks, &s->d_cpart));
+    MFV2D_TRY(sys_alloc(s, (size_t)total, &s->d_cy));
+    MFV2D_TRY(sys_alloc(s, (size_t)exact_begin, &s->d_ldinv));
+    MFV2D_TRY(sys_alloc(s, (size_t)n_exact, &s->d_yc));
+    long long grid = (long long)ctx->sm_count * 8;
+    if (grid > s->n_elem)
+        grid = s->n_elem;
+    // diagonal levels: D_l = diag(P_l^T S P_l) -> 1 / D_l (1 where an aggregate's diagonal vanishes)
+    if (exact_begin)
+        MFV2D_CUDA_CHECK(ctx, cudaMemsetAsync(s->d_ldinv, 0, (size_t)exact_begin * sizeof(double), ctx->stream));
+    for (int l = 0; l < n_levels - (exact_last ? 1 : 0) && s->n_elem; ++l)
+    {
+        MFV2D_LAUNCH(coarse_assemble_kernel, (unsigned)grid, 128, 0, ctx->stream, (unsigned long long)s->n_elem, s->d_slot_off, s->d_slot_trace,
+                     s->d_s_off, (const double *)s->d_S, (int)s->symmetric, (const int32_t *)(s->d_lagg + (size_t)l * nt), (const double *)s->d_cz,
+                     (long long)n_agg[l], 0, s->d_ldinv + agg_off[l]);
+        ctx->launches++;
+    }
+    if (exact_begin)
+    {
+        MFV2D_LAUNCH(reciprocal_kernel, grid_for(ctx, exact_begin, 256), 256, 0, ctx->stream, exact_begin, s->d_ldinv);
+        ctx->launches++;
+    }
+    MFV2D_CUDA_CHECK(ctx, cudaGetLastError());
+    if (n_exact)
+    {
+        const size_t nn = (size_t)n_exact * n_exact;
+        double *d_Ac = nullptr;
+        int32_t *d_status = nullptr;
+        MFV2D_TRY(sys_alloc(s, nn, &d_Ac));
+        MFV2D_TRY(sys_alloc(s, nn, &s->d_Ac_inv));
+        MFV2D_TRY(sys_alloc(s, (size_t)2, &d_status));
+        MFV2D_CUDA_CHECK(ctx, cudaMemsetAsync(d_Ac, 0, nn * sizeof(double), ctx->stream));
+        if (s->n_elem)
+        {
+            MFV2D_LAUNCH(coarse_assemble_kernel, (unsigned)grid, 128, 0, ctx->stream, (unsigned long long)s->n_elem, s->d_slot_off,
+                         s->d_slot_trace, s->d_s_off, (const double *)s->d_S, (int)s->symmetric,
+                         (const int32_t *)(s->d_lagg + (size_t)(n_levels - 1) * nt), (const double *)s->d_cz, (long long)n_exact, 1, d_Ac);
+            ctx->launches++;
+            MFV2D_CUDA_CHECK(ctx, cudaGetLastError());
+        }
+        if (ctx->n_ranks > 1)
+        {
+            if (use_peers) // row by row through the type-1 area of the exchange blocks
+                for (int64_t row = 0; row < n_exact; ++row)
+                    MFV2D_TRY(peer_dense_sum(s, d_Ac + (size_t)row * n_exact, (long long)n_exact));
+            else
+                MFV2D_TRY(comm_allreduce(ctx, d_Ac, nn));
+        }
+        MFV2D_TRY(launch_inverse_batch(ctx, (int)n_exact, 1, d_Ac, s->d_Ac_inv, d_status));
+        int32_t st = 0;
+        MFV2D_TRY(mfv2d_cuda_download(ctx, &st, d_status, sizeof st));
+        if (st != MFV2D_SUCCESS)
+            return mfv2d_fail(ctx, MFV2D_PIVOT_FAILED, "set_coarse_space: the coarse operator P^T S P is singular (an aggregate without multipliers, "
+                                                       "or a Schur complement with a null space along z)");
+        const size_t smem = (size_t)n_exact * sizeof(double);
+        if (smem > 48 * 1024)
+            MFV2D_CUDA_CHECK(ctx, cudaFuncSetAttribute(coarse_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    }
+    MFV2D_TRY(mfv2d_cuda_synchronize(ctx));
+    s->coarse_ready = true;
     return MFV2D_SUCCESS;
 }
 

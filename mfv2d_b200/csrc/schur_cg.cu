@@ -46,6 +46,7 @@ struct CgGatherArgs
 {
     long long n_trace;
     const int64_t *tr_ptr, *tr_slot;
+    const int32_t *tr2; // fixed-width (two slots per multiplier) form of the same lists, or nullptr
     const double *slot_val, *u, *r, *own;
     double *w, *partials, *sc;
     const int32_t *shared_of;
@@ -75,8 +76,17 @@ __global__ void __launch_bounds__(SYS_THREADS) cg1_gather_kernel(const CgGatherA
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < a.n_trace; i += (long long)gridDim.x * blockDim.x)
     {
         double acc = 0.0;
-        for (int64_t k = a.tr_ptr[i]; k < a.tr_ptr[i + 1]; ++k)
-            acc += a.slot_val[a.tr_slot[k]];
+        if (a.tr2)
+        {
+            const int2 sl = reinterpret_cast<const int2 *>(a.tr2)[i];
+            if (sl.x >= 0)
+                acc += a.slot_val[sl.x];
+            if (sl.y >= 0)
+                acc += a.slot_val[sl.y];
+        }
+        else
+            for (int64_t k = a.tr_ptr[i]; k < a.tr_ptr[i + 1]; ++k)
+                acc += a.slot_val[a.tr_slot[k]];
         a.w[i] = acc;
         const double ui = a.u[i], ri = a.r[i];
         const double rw = a.own ? ri * a.own[i] : ri;
@@ -372,7 +382,7 @@ int mfv2d_cuda_solve_schur_cg(mfv2d_system *s, const double *rhs, const double *
                 break;
             }
             PeerView one; // a view with one rank: nothing is sent or awaited inside the kernels
-            CgGatherArgs ga{nt, s->d_tr_ptr, s->d_tr_slot, s->d_slot_val, u, res, own, ap, s->d_partials, sc, s->d_shared_of,
+            CgGatherArgs ga{nt, s->d_tr_ptr, s->d_tr_slot, s->d_tr2, s->d_slot_val, u, res, own, ap, s->d_partials, sc, s->d_shared_of,
                             s->d_shared_slot, s->d_holder_ptr, s->d_holder_rank, use_peers ? s->peer : one};
             CgUpdateArgs ua{nt, sc, u, ap, p, sv, lam, res, dinv, z, s->d_shared_of, s->d_shared_slot, s->d_holder_ptr, s->d_holder_rank,
                             use_peers ? s->peer : one};

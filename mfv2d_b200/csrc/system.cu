@@ -334,68 +334,138 @@ __global__ void __launch_bounds__(SYS_THREADS) schur_local_packed_generic_kernel
 }
 
 #ifndef MFV2D_EMU
+// row r of a packed block times lambda for a block of ANY size m <= W (boundary elements, mixed warps): per-entry index arithmetic
+__device__ __forceinline__ double packed_row_general(const double *__restrict__ Se, int m, int W, int g, int r, int lane, double lam_r)
+{
+    constexpr int UNR = 4;
+    const bool row = r < m;
+    const int half = m >> 1, kfull = (m + 1) >> 1;
+    const int kmax = (W >> 1) + 1;
+    const bool low = !(m & 1) && r < half; // holds an entry of the last (half-length) diagonal of an even block
+    double acc = 0.0;
+    for (int k0 = 0; k0 < kmax; k0 += UNR)
+    {
+        double a[UNR];
+#pragma unroll
+        for (int u = 0; u < UNR; ++u)
+        {
+            const int k = k0 + u;
+            a[u] = (row && (k < kfull || (k == half && low))) ? __ldcs(Se + (size_t)k * m + r) : 0.0;
+        }
+#pragma unroll
+        for (int u = 0; u < UNR; ++u)
+        {
+            const int k = k0 + u;
+            int lc = lane, ls = lane;
+            if (row && k <= half)
+            {
+                int c = r + k, sr = r - k;
+                if (c >= m)
+                    c -= m;
+                if (sr < 0)
+                    sr += m;
+                lc = g * W + c;
+                ls = g * W + sr;
+            }
+            const double lam_c = __shfl_sync(0xffffffffu, lam_r, lc);
+            const double recv = __shfl_sync(0xffffffffu, a[u] * lam_r, ls);
+            acc = fma(a[u], lam_c, acc);
+            if (k > 0)
+                acc += recv;
+        }
+    }
+    return acc;
+}
+
 // PACKED symmetric blocks of at most W <= 32 rows: 32 / W elements per warp, lane (g, r) owns row r of its element.  Every stored
-// entry is read ONCE (coalesced over r for a fixed diagonal k, 8 diagonals in flight per lane); its mirrored use travels to lane
-// (r + k) % m by a shuffle, lambda comes by shuffles too: no shared memory, no barrier, half the bytes of the full product.
-__global__ void __launch_bounds__(SYS_THREADS) schur_local_packed_kernel(unsigned long long n_elem, const int64_t *__restrict__ slot_off,
-                                                                        const int64_t *__restrict__ slot_trace,
-                                                                        const int64_t *__restrict__ s_off, const double *__restrict__ S,
-                                                                        const double *__restrict__ t, double *__restrict__ slot_val, int W,
-                                                                        const int *__restrict__ done)
+// entry is read ONCE (coalesced over r for a fixed diagonal k) and ALL diagonals of a block are requested before the first is
+// used (W is a template parameter: the walk is fully unrolled, one memory latency per element).  The mirrored use of an entry and
+// the lambda values travel between the lanes by shuffles with ONE fixed source lane (r - 1 mod W): walking the diagonals from the
+// last to the first, T <- rotate(T + a_k lambda_r) delivers a_k lambda_r to lane r + k after k rotations, and L <- rotate(L)
+// turns lambda[r + k] into lambda[r + k - 1].  No shared memory, no barrier, no per-entry index arithmetic, half the bytes
+// of the full product.  The 16-byte element descriptor of the NEXT element is requested before the current block is streamed.
+template <int W>
+__global__ void __launch_bounds__(SYS_THREADS, 4) schur_local_packed_kernel(unsigned long long n_elem, const SchurElemDesc *__restrict__ desc,
+                                                                           const int32_t *__restrict__ slot_trace32,
+                                                                           const double *__restrict__ S, const double *__restrict__ t,
+                                                                           double *__restrict__ slot_val, const int *__restrict__ done)
 {
     if (done && *done)
         return;
-    constexpr int UNR = 8;
+    constexpr int G = 32 / W, KF = (W + 1) / 2, K = W / 2; // full diagonals 0 .. KF-1; an even block adds the half diagonal K
+    constexpr bool EVEN = (W & 1) == 0;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
-    const int G = 32 / W, g = lane / W, r = lane - g * W;
-    const int kmax = (W >> 1) + 1;
+    const int g = lane / W, r = lane - g * W;
     const unsigned long long stride = (unsigned long long)gridDim.x * nwarps * G;
-    for (unsigned long long base = ((unsigned long long)blockIdx.x * nwarps + warp) * G; base < n_elem; base += stride)
+    unsigned long long base = ((unsigned long long)blockIdx.x * nwarps + warp) * G;
+    if (base >= n_elem)
+        return;
+    auto load_desc = [&](unsigned long long b) {
+        SchurElemDesc d{0, 0, 0};
+        const unsigned long long e = b + g;
+        if (g < G && e < n_elem)
+            d = desc[e];
+        return d;
+    };
+    SchurElemDesc cur = load_desc(base);
+    double lam_r = r < cur.m ? t[slot_trace32[cur.s0 + r]] : 0.0;
+    for (; base < n_elem; base += stride)
     {
-        const unsigned long long e = base + g;
-        const bool valid = g < G && e < n_elem;
-        const int64_t s0 = valid ? slot_off[e] : 0;
-        const int m = valid ? (int)(slot_off[e + 1] - s0) : 0;
-        const double *Se = S + (valid ? s_off[e] : 0);
-        const bool row = r < m;
-        const int half = m >> 1, kfull = (m + 1) >> 1;
-        const bool low = !(m & 1) && r < half; // holds an entry of the last (half-length) diagonal of an even block
-        const double lam_r = row ? t[slot_trace[s0 + r]] : 0.0;
-        double acc = 0.0;
-        for (int k0 = 0; k0 < kmax; k0 += UNR)
+        const bool more = base + stride < n_elem;
+        SchurElemDesc nxt{0, 0, 0};
+        if (more)
+            nxt = load_desc(base + stride);
+        const int m = cur.m;
+        const double *Se = S + cur.s_off;
+        const bool act = g < G && base + g < n_elem;
+        double acc;
+        if (__all_sync(0xffffffffu, !act || m == W))
         {
-            double a[UNR];
+            double a[KF], ah = 0.0;
 #pragma unroll
-            for (int u = 0; u < UNR; ++u)
-            {
-                const int k = k0 + u;
-                a[u] = (row && (k < kfull || (k == half && low))) ? __ldcs(Se + (size_t)k * m + r) : 0.0;
-            }
+            for (int k = 0; k < KF; ++k)
+                a[k] = act ? __ldcs(Se + k * W + r) : 0.0;
+            if (EVEN)
+                ah = (act && r < K) ? __ldcs(Se + K * W + r) : 0.0;
+            const int src = act ? g * W + (r == 0 ? W - 1 : r - 1) : lane; // idle lanes shuffle with themselves
+            double L = __shfl_sync(0xffffffffu, lam_r, act ? g * W + (r + K >= W ? r + K - W : r + K) : lane);
+            double T = 0.0;
+            acc = 0.0;
 #pragma unroll
-            for (int u = 0; u < UNR; ++u)
+            for (int k = K; k >= 1; --k)
             {
-                const int k = k0 + u;
-                int lc = lane, ls = lane;
-                if (row && k <= half)
-                {
-                    int c = r + k, sr = r - k;
-                    if (c >= m)
-                        c -= m;
-                    if (sr < 0)
-                        sr += m;
-                    lc = g * W + c;
-                    ls = g * W + sr;
-                }
-                const double lam_c = __shfl_sync(0xffffffffu, lam_r, lc);
-                const double recv = __shfl_sync(0xffffffffu, a[u] * lam_r, ls);
-                acc = fma(a[u], lam_c, acc);
-                if (k > 0)
-                    acc += recv;
+                const double ak = (EVEN && k == K) ? ah : a[k < KF ? k : 0];
+                acc = fma(ak, L, acc);
+                T = fma(ak, lam_r, T);
+                T = __shfl_sync(0xffffffffu, T, src);
+                if (k > 1)
+                    L = __shfl_sync(0xffffffffu, L, src);
             }
+            acc += fma(a[0], lam_r, T);
         }
-        if (row)
-            slot_val[s0 + r] = acc;
+        else
+            acc = packed_row_general(Se, m, W, g, r, lane, lam_r);
+        if (r < m)
+            slot_val[cur.s0 + r] = acc;
+        cur = nxt;
+        lam_r = (more && r < cur.m) ? t[slot_trace32[cur.s0 + r]] : 0.0;
     }
+}
+
+typedef void (*schur_packed_fn)(unsigned long long, const SchurElemDesc *, const int32_t *, const double *, const double *, double *,
+                                const int *);
+static schur_packed_fn schur_packed_for(int max_m, int *width)
+{
+    // widths of the conforming meshes (4 p multipliers per element, p = 1 .. 8) and the sizes in between
+#define SP_CASE(Wv)                                                                                            \
+    if (max_m <= Wv)                                                                                           \
+    {                                                                                                          \
+        *width = Wv;                                                                                           \
+        return schur_local_packed_kernel<Wv>;                                                                  \
+    }
+    SP_CASE(4) SP_CASE(8) SP_CASE(12) SP_CASE(16) SP_CASE(20) SP_CASE(24) SP_CASE(28) SP_CASE(32)
+#undef SP_CASE
+    return nullptr;
 }
 #endif
 
@@ -573,14 +643,19 @@ int sys_schur_local(const mfv2d_system *s, const double *t_in, const int *done)
     const int warps = SYS_THREADS / 32;
     const long long cap = (long long)ctx->sm_count * 8;
 #ifndef MFV2D_EMU
-    if (s->symmetric && s->max_m <= 32)
+    if (s->symmetric && s->max_m <= 32 && s->d_edesc)
     {
-        const int G = 32 / s->max_m;
+        int W = 32;
+        const schur_packed_fn fn = schur_packed_for(s->max_m, &W);
+        const int G = 32 / W;
         long long grid = (s->n_elem + (long long)warps * G - 1) / ((long long)warps * G);
-        if (grid > cap)
-            grid = cap;
-        MFV2D_LAUNCH(schur_local_packed_kernel, (unsigned)grid, SYS_THREADS, 0, ctx->stream, (unsigned long long)s->n_elem, s->d_slot_off,
-                     s->d_slot_trace, s->d_s_off, s->d_S, t_in, s->d_slot_val, s->max_m, done);
+        int per_sm = 0; // one wave of resident CTAs: a second, partly filled wave would cost up to a whole pass
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, SYS_THREADS, 0) != cudaSuccess || per_sm < 1)
+            per_sm = 4;
+        if (grid > (long long)ctx->sm_count * per_sm)
+            grid = (long long)ctx->sm_count * per_sm;
+        fn<<<(unsigned)grid, SYS_THREADS, 0, ctx->stream>>>((unsigned long long)s->n_elem, (const SchurElemDesc *)s->d_edesc,
+                                                            (const int32_t *)s->d_slot_trace32, (const double *)s->d_S, t_in, s->d_slot_val, done);
         ctx->launches++;
         MFV2D_CUDA_CHECK(ctx, cudaGetLastError());
         return MFV2D_SUCCESS;
@@ -834,6 +909,20 @@ int mfv2d_cuda_system_create(mfv2d_ctx *ctx, size_t n_elem, const int64_t *block
     SYS_TRY(sys_upload(s, lrow_val, &s->d_lrow_val));
     SYS_TRY(sys_upload(s, tr_ptr, &s->d_tr_ptr));
     SYS_TRY(sys_upload(s, tr_slot, &s->d_tr_slot));
+    {
+        // conforming meshes: at most two elements per multiplier -> a fixed-width 32-bit table for the CG's gather kernel
+        bool two = s->n_slots < (int64_t)1 << 31;
+        for (size_t i = 0; i < n_trace && two; ++i)
+            two = tr_ptr[i + 1] - tr_ptr[i] <= 2;
+        if (two && n_trace)
+        {
+            std::vector<int32_t> tr2(2 * n_trace, -1);
+            for (size_t i = 0; i < n_trace; ++i)
+                for (int64_t k = tr_ptr[i]; k < tr_ptr[i + 1]; ++k)
+                    tr2[2 * i + (k - tr_ptr[i])] = (int32_t)tr_slot[k];
+            SYS_TRY(sys_upload(s, tr2, &s->d_tr2));
+        }
+    }
     const size_t mat_total = (size_t)moff[n_elem];
     if (blocks_space == MFV2D_DEVICE)
     {
@@ -876,6 +965,16 @@ int mfv2d_cuda_system_create(mfv2d_ctx *ctx, size_t n_elem, const int64_t *block
         s_off[e + 1] = s_off[e] + (s->symmetric ? packed_size(m) : m * m);
     }
     SYS_TRY(sys_upload(s, s_off, &s->d_s_off));
+    if (s->n_slots < (int64_t)1 << 31 && (int64_t)n_trace < (int64_t)1 << 31)
+    {
+        // compact per-element descriptors and 32-bit multiplier indices for the packed Schur product
+        std::vector<SchurElemDesc> edesc(n_elem);
+        for (size_t e = 0; e < n_elem; ++e)
+            edesc[e] = SchurElemDesc{(long long)s_off[e], (int)slot_off[e], (int)(slot_off[e + 1] - slot_off[e])};
+        std::vector<int32_t> st32(slot_trace.begin(), slot_trace.end());
+        SYS_TRY(sys_upload(s, edesc, &s->d_edesc));
+        SYS_TRY(sys_upload(s, st32, &s->d_slot_trace32));
+    }
     SYS_TRY(sys_alloc(s, mat_total, &s->d_Ainv));
     SYS_TRY(sys_alloc(s, (size_t)s_off[n_elem], &s->d_S));
     SYS_TRY(sys_alloc(s, (size_t)s->n_slots, &s->d_slot_val));

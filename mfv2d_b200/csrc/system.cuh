@@ -89,6 +89,13 @@ __device__ __forceinline__ void peer_wait_all(const PeerView &pv, int type, unsi
     __syncthreads();
 }
 
+// per-element descriptor of the packed Schur product: one 16-byte load gives the block, the first slot and the block size
+struct __align__(16) SchurElemDesc
+{
+    long long s_off;
+    int s0, m;
+};
+
 struct mfv2d_system
 {
     mfv2d_ctx *ctx;
@@ -111,20 +118,28 @@ struct mfv2d_system
     int64_t *d_lrow_ptr = nullptr;   // [n_slots+1] entries of each local row
     int32_t *d_lrow_col = nullptr;   // local column index
     double *d_lrow_val = nullptr;
+    SchurElemDesc *d_edesc = nullptr; // [n_elem] (s_off, first slot, m) when the counts fit 32 bits
+    int32_t *d_slot_trace32 = nullptr; // [n_slots] 32-bit copy of d_slot_trace
     int64_t *d_s_off = nullptr; // [n_elem+1] offsets into S
     double *d_S = nullptr;      // condensed blocks: column-major m x m, or packed "cyclic half" m (m + 1) / 2 when symmetric
     int64_t *d_tr_ptr = nullptr, *d_tr_slot = nullptr; // per multiplier: contributing slots
+    int32_t *d_tr2 = nullptr;                          // [n_trace][2] the same as a fixed-width table (-1: none) when no multiplier has more than two slots
     double *d_slot_val = nullptr;                      // [n_slots] scratch: local results
     double *d_diag_inv = nullptr;                      // [n_trace] 1 / diag(S) (Jacobi preconditioner on the trace space)
-    // two-level preconditioner on the trace space (precond.cu): Jacobi + a coarse space of one vector per aggregate
-    int64_t n_coarse = 0;
-    int32_t *d_agg = nullptr;       // [n_trace] aggregate of each multiplier (-1: none)
-    double *d_cz = nullptr;         // [n_trace] near-null-space vector (the coarse basis restricted to the aggregates)
-    int64_t *d_cg_ptr = nullptr;    // [n_coarse+1] multipliers of each aggregate ...
-    int64_t *d_cg_idx = nullptr;    // ... in increasing order
-    double *d_Ac_inv = nullptr;     // [n_coarse^2] inverse of P^T S P, row-major
-    double *d_rc = nullptr;         // [n_coarse] restricted residual (this rank's part), then its sum
-    double *d_yc = nullptr;         // [n_coarse] coarse correction
+    // multilevel preconditioner on the trace space (precond.cu): Jacobi + one vector per aggregate on every level
+    int n_clevels = 0;
+    long long n_agg_total = 0, exact_begin = 0, n_exact = 0, n_chunks = 0;
+    int32_t *d_lagg = nullptr;          // [n_clevels][n_trace] aggregate of each multiplier on each level (-1: none)
+    long long *d_agg_off = nullptr;     // [n_clevels] first aggregate of the level in the concatenated numbering
+    double *d_cz = nullptr;             // [n_trace] near-null-space vector
+    int64_t *d_chunk_ptr = nullptr;     // [n_chunks+1] multipliers of each chunk (<= COARSE_CHUNK of one aggregate) ...
+    int64_t *d_chunk_idx = nullptr;     // ... in increasing order
+    int64_t *d_aggchunk_ptr = nullptr;  // [n_agg_total+1] chunks of each aggregate
+    double *d_cpart = nullptr;          // [n_chunks] partial restrictions
+    double *d_ldinv = nullptr;          // [exact_begin] 1 / diag(P_l^T S P_l)
+    double *d_cy = nullptr;             // [n_agg_total] scaled restrictions | this rank's part of the exact level's residual
+    double *d_yc = nullptr;             // [n_exact] correction of the exact level
+    double *d_Ac_inv = nullptr;         // [n_exact^2] inverse of P_L^T S P_L, row-major
     bool coarse_ready = false;
     // work vectors
     double *d_work_dense[3] = {nullptr, nullptr, nullptr};

@@ -62,6 +62,12 @@ class Context:
         check(lib().mfv2d_cuda_timer_stop(self.handle, C.byref(ms)), self.handle)
         return ms.value
 
+    def measure_fp64_peak(self) -> tuple[float, float]:
+        """(DMMA, DFMA) fp64 TFLOP/s of this device, measured now (mfv2d_cuda_measure_fp64_peak)."""
+        a, b = C.c_double(), C.c_double()
+        check(lib().mfv2d_cuda_measure_fp64_peak(self.handle, C.byref(a), C.byref(b)), self.handle)
+        return a.value, b.value
+
     def flush_l2(self) -> None:
         check(lib().mfv2d_cuda_flush_l2(self.handle), self.handle)
 

@@ -248,23 +248,26 @@ class LinearSystem:
     def peer_error(self) -> bool:
         return bool(lib().mfv2d_cuda_system_peer_error(self.handle))
 
-    def set_coarse_space(self, aggregates: np.ndarray, z: np.ndarray, n_coarse: int) -> None:
-        """Coarse space of the two-level preconditioner (``precondition="two-level"``): aggregate id (or -1) and near-null-
-        space value of every multiplier of this rank (``structured.coarse_space_1form``).  Collective when partitioned."""
-        ag = np.ascontiguousarray(aggregates, np.int32)
+    def set_coarse_space(self, aggregates: np.ndarray, z: np.ndarray, n_agg, exact_last: bool = True) -> None:
+        """Aggregate hierarchy of the multilevel preconditioner (``precondition="multilevel"``): ``aggregates[level, multiplier]``
+        (aggregate id or -1) and the near-null-space value ``z`` of every multiplier of this rank
+        (``structured.coarse_hierarchy_1form`` + ``localize_hierarchy``).  Collective when partitioned."""
+        ag = np.ascontiguousarray(np.atleast_2d(aggregates), np.int32)
         zz = np.ascontiguousarray(z, np.float64)
-        if ag.size != self.n_trace or zz.size != self.n_trace:
-            raise ValueError("aggregates and z must have one entry per multiplier")
-        check(lib().mfv2d_cuda_system_set_coarse_space(self.handle, int(n_coarse), ag.ctypes.data, zz.ctypes.data), self.ctx.handle)
+        na = np.ascontiguousarray(n_agg, np.int64)
+        if ag.shape[1] != self.n_trace or zz.size != self.n_trace or na.size != ag.shape[0]:
+            raise ValueError("aggregates must be (levels, n_trace), z (n_trace,), n_agg (levels,)")
+        check(lib().mfv2d_cuda_system_set_coarse_space(self.handle, ag.shape[0], na.ctypes.data, ag.ctypes.data, zz.ctypes.data,
+                                                       int(bool(exact_last))), self.ctx.handle)
 
 
-PRECONDITIONERS = {False: 0, None: 0, "none": 0, True: 1, "jacobi": 1, "two-level": 2}
+PRECONDITIONERS = {False: 0, None: 0, "none": 0, True: 1, "jacobi": 1, "multilevel": 2}
 
 
 def solve_schur_iterative(system: LinearSystem, rhs, constraints, convergence: ConvergenceSettings, precondition=False):
     """python/mfv2d/solving.py:439-500: CG on ``N A^-1 N^T`` for the multipliers, then back substitution.
     Returns ``(x, lambda, residual, iterations)`` like the reference.  ``precondition``: ``False`` (the reference's
-    method), ``True`` / ``"jacobi"``, or ``"two-level"`` (Jacobi + coarse space, see ``LinearSystem.set_coarse_space``)."""
+    method), ``True`` / ``"jacobi"``, or ``"multilevel"`` (Jacobi + aggregate hierarchy, see ``LinearSystem.set_coarse_space``)."""
     if isinstance(rhs, _SystemVector):  # DenseVector / TraceVector in and out, like the reference
         xd, ld, r, i = solve_schur_iterative(system, rhs.data, constraints.data, convergence, precondition)
         return DenseVector.__new__(DenseVector)._init(system, xd), TraceVector.__new__(TraceVector)._init(system, ld), r, i

@@ -162,26 +162,59 @@ def partition_constraints(row: np.ndarray, col: np.ndarray, val: np.ndarray, n_t
                                slot_of[g_rows[sh]].astype(np.int64), int(is_shared.sum()), owned, holder_ptr, holder_rank)
 
 
-def coarse_space_1form(nh: int, nv: int, p: int, form_orders, agg_size: int) -> tuple[np.ndarray, np.ndarray, int]:
-    """Coarse space of the two-level preconditioner of the Schur-complement CG for the multipliers of
-    :func:`continuity_constraints_1form` (same global row order): aggregates of ``agg_size x agg_size`` elements, a
-    multiplier belongs to the aggregate of the element below / to the left of its line; ``z`` is the near-null-space
-    vector of ``S = N A^-1 N^T`` for the mixed formulations, the multipliers of ``u = const``: ``+1`` on horizontal
-    lines, ``-1`` on vertical ones (the sign convention of continuity.py:498-501 with the outward orientation of the
-    element boundary DoFs).  Returns ``(agg, z, n_coarse)`` over the GLOBAL multipliers."""
-    ncx, ncy = -(-nh // agg_size), -(-nv // agg_size)
-    aggs, zs = [], []
+def coarse_hierarchy_1form(nh: int, nv: int, p: int, form_orders, mid_sizes=(4,), exact_size: int = 16, strip_rows=None):
+    """Aggregate hierarchy of the multilevel preconditioner of the Schur-complement CG (precond.cu) for the multipliers of
+    :func:`continuity_constraints_1form` (same global row order).  A multiplier belongs to the aggregate of the element
+    below / to the left of its line.  Levels ``mid_sizes`` (aggregates of ``H x H`` elements, confined to one rank's strip
+    when ``strip_rows`` = first element row of every rank + ``[nv]`` is given), then the exact level of
+    ``exact_size x exact_size`` elements, numbered globally.  ``z`` is the near-null-space vector of ``S = N A^-1 N^T``
+    for the mixed formulations, the multipliers of ``u = const``: ``+1`` on horizontal lines, ``-1`` on vertical ones
+    (sign convention of continuity.py:498-501 with the outward orientation of the element boundary DoFs).
+
+    Returns ``(agg, z, n_agg)``: ``agg[level, global multiplier]`` (compact ids per level), ``n_agg[level]``."""
+    strip_rows = np.asarray(strip_rows if strip_rows is not None else [0, nv], np.int64)
+    ei, ej, zs = [], [], []
     for order in form_orders:
         if int(order) != FORM_ORDER_1:
             continue
-        jj, ii = np.meshgrid(np.arange(1, nv), np.arange(nh), indexing="ij")
-        aggs.append(np.repeat((((jj - 1) // agg_size) * ncx + ii // agg_size).ravel(), p))
+        jj, ii = np.meshgrid(np.arange(1, nv), np.arange(nh), indexing="ij")  # horizontal lines: element below
+        ei.append(np.repeat(ii.ravel(), p))
+        ej.append(np.repeat((jj - 1).ravel(), p))
         zs.append(np.ones(jj.size * p))
-        jj, ii = np.meshgrid(np.arange(nv), np.arange(1, nh), indexing="ij")
-        aggs.append(np.repeat(((jj // agg_size) * ncx + (ii - 1) // agg_size).ravel(), p))
+        jj, ii = np.meshgrid(np.arange(nv), np.arange(1, nh), indexing="ij")  # vertical lines: element to the left
+        ei.append(np.repeat((ii - 1).ravel(), p))
+        ej.append(np.repeat(jj.ravel(), p))
         zs.append(-np.ones(jj.size * p))
-    if not aggs:
-        return np.zeros(0, np.int32), np.zeros(0), 0
-    # aggregates that received no multiplier (a last, partial row / column of aggregates) would make P^T S P singular
-    used, compact = np.unique(np.concatenate(aggs), return_inverse=True)
-    return compact.astype(np.int32), np.concatenate(zs), int(used.size)
+    if not ei:
+        return np.zeros((0, 0), np.int32), np.zeros(0), []
+    ei, ej, z = np.concatenate(ei), np.concatenate(ej), np.concatenate(zs)
+    strip = np.searchsorted(strip_rows, ej, side="right") - 1
+    jl = ej - strip_rows[strip]
+    levels, n_agg = [], []
+    for H in mid_sizes:
+        key = (strip * (nv + 1) + jl // H) * (nh + 1) + ei // H
+        used, compact = np.unique(key, return_inverse=True)
+        levels.append(compact.astype(np.int32))
+        n_agg.append(int(used.size))
+    if exact_size:
+        key = (ej // exact_size) * (nh + 1) + ei // exact_size
+        used, compact = np.unique(key, return_inverse=True)  # aggregates without a multiplier would make P^T S P singular
+        levels.append(compact.astype(np.int32))
+        n_agg.append(int(used.size))
+    return np.stack(levels), z, n_agg
+
+
+def localize_hierarchy(agg: np.ndarray, z: np.ndarray, n_agg, part: "ConstraintPartition", exact_last: bool = True):
+    """This rank's view of a global hierarchy: rows = its multipliers; on the rank-local levels the shared multipliers are
+    left out (-1) and the ids are compacted; the exact level keeps its global ids."""
+    loc = np.ascontiguousarray(agg[:, part.global_rows]).astype(np.int32)
+    counts = list(n_agg)
+    n_local = loc.shape[0] - (1 if exact_last else 0)
+    for lvl in range(n_local):
+        a = loc[lvl]
+        a[part.shared_index] = -1
+        keep = a >= 0
+        used, compact = np.unique(a[keep], return_inverse=True)
+        a[keep] = compact
+        counts[lvl] = int(used.size)
+    return loc, np.ascontiguousarray(z[part.global_rows]), counts

@@ -33,7 +33,10 @@ def main():
     ap.add_argument("--order", type=int, default=6)
     ap.add_argument("--rtol", type=float, default=1e-10)
     ap.add_argument("--max-iter", type=int, default=60000)
-    ap.add_argument("--precondition", action="store_true")
+    ap.add_argument("--precondition", default="none", choices=["none", "jacobi", "multilevel"])
+    ap.add_argument("--agg", type=int, default=25, help="aggregate size (elements per side) of the exact coarse level")
+    ap.add_argument("--mid", default="5", help="comma-separated aggregate sizes of the diagonal (rank-local) levels")
+    ap.add_argument("--source", default="smooth", choices=["smooth", "random"])
     ap.add_argument("--repeat", type=int, default=2)
     args = ap.parse_args()
     rank, world, local, dist = B.dist_setup(args.gpus)
@@ -98,16 +101,37 @@ def main():
     host_s = time.perf_counter() - t_host
     t0 = time.perf_counter()
     system = SV.LinearSystem(mats, (part.row, part.col, part.val), part.n_trace, ctx)
+    n_coarse = 0
+    if args.precondition == "multilevel":
+        mids = tuple(int(v) for v in args.mid.split(",") if v)
+        agg, zc, n_agg = ST.coarse_hierarchy_1form(nh, nv, p, orders, mids, args.agg, [parts[r][0] // nh for r in range(world)] + [nv])
+        n_coarse = n_agg[-1]
     if world > 1:
         system.set_interface(part.shared_index, part.slot, part.n_slots, part.owned)
+
+        def all_gather(obj):
+            out = [None] * world
+            dist.all_gather_object(out, obj)
+            return out
+
+        system.connect_peers(part.holder_ptr, part.holder_rank, all_gather, n_coarse=n_coarse)
     ctx.synchronize()
     setup_s = B.max_over_ranks(dist, time.perf_counter() - t0)
+    coarse_s = 0.0
+    if n_coarse:
+        t0 = time.perf_counter()
+        system.set_coarse_space(*ST.localize_hierarchy(agg, zc, n_agg, part))
+        ctx.synchronize()
+        coarse_s = B.max_over_ranks(dist, time.perf_counter() - t0)
 
     # ---- right-hand side: dual DoFs of the source on the 2-form rows, zero on the 1-form rows ----
     rhs_h = np.zeros((n, ne))
     off_u = specs.form_offset(1, p, p) if hasattr(specs, "form_offset") else ne - p * p
-    f = batch.dual_dofs(orders[1], source)
-    rhs_h[:, off_u:] = f.get() if hasattr(f, "get") else f
+    if args.source == "random":
+        rhs_h[:] = np.random.default_rng(100 + rank).standard_normal(rhs_h.shape)
+    else:
+        f = batch.dual_dofs(orders[1], source)
+        rhs_h[:, off_u:] = f.get() if hasattr(f, "get") else f
     rhs = ctx.to_device(rhs_h.ravel())
     phi = ctx.to_device(np.zeros(part.n_trace))
     solve_times = []
@@ -117,6 +141,7 @@ def main():
         t0 = time.perf_counter()
         xs, lam, res, it = SV.solve_schur_iterative(system, rhs, phi, SV.ConvergenceSettings(args.max_iter, 1e300, args.rtol),
                                                     precondition=args.precondition)
+        assert not system.peer_error()
         ctx.synchronize()
         solve_times.append(B.max_over_ranks(dist, time.perf_counter() - t0))
     solve_s = solve_times[-1]
@@ -135,9 +160,9 @@ def main():
         "assembly": {"ms": asm_ms, "element_matrices_per_s": total / (asm_ms * 1e-3),
                      "hbm_frac_per_gpu": (64 + 8 * ne * ne) * n / (asm_ms * 1e-3) / 1e9 / peak},
         "apply_recompute": {"ms": app_ms, "gdofs": total * ne / (app_ms * 1e-3) / 1e9},
-        "system_setup_s": setup_s, "host_mesh_and_constraints_s": host_s,
-        "solve": {"method": "CG on the Schur complement N A^-1 N^T" + (", Jacobi" if args.precondition else ""), "rtol": args.rtol, "s": solve_s, "s_all_solves": solve_times,
-                  "recurrence": os.environ.get("MFV2D_CG_SINGLE_REDUCE", "default"), "graph": os.environ.get("MFV2D_CG_GRAPH", "default"),
+        "system_setup_s": setup_s, "coarse_setup_s": coarse_s, "n_coarse": int(n_coarse), "host_mesh_and_constraints_s": host_s,
+        "solve": {"method": "CG on the Schur complement N A^-1 N^T" + f", preconditioner {args.precondition}", "rtol": args.rtol, "s": solve_s, "s_all_solves": solve_times,
+                  "exchange": os.environ.get("MFV2D_CG_EXCHANGE", "peer" if world > 1 else "-"), "graph": os.environ.get("MFV2D_CG_GRAPH", "default"),
                   "iterations": int(it), "us_per_iteration": solve_s / max(int(it), 1) * 1e6, "cg_residual": float(res),
                   "saddle_relative_residual": float(np.sqrt(num / den))},
     }

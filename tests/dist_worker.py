@@ -126,10 +126,10 @@ def main():
             return out
 
         it, itj, _, worst = PC.check_partitioned_solve(M, SV, ST, ctx, rank, world, all_gather, fix, nh, nv)
-        itj2, it2 = PC.check_two_level(M, SV, ST, ctx, rank, world, all_gather, nh=32, nv=32, p=3, k=3, agg_size=4)
+        itj2, it2 = PC.check_multilevel(M, SV, ST, ctx, rank, world, all_gather, nh=32, nv=32, p=3, k=3, mid_sizes=(2,), exact_size=8)
         if rank == 0:
             print(f"dist_worker ok: mode {mode}, world {world}, iterations {it} (jacobi {itj}), err {worst:.2e}; "
-                  f"two-level {it2} vs jacobi {itj2} on 32x32 p3, exchange {os.environ.get('MFV2D_CG_EXCHANGE', 'peer')}", flush=True)
+                  f"multilevel {it2} vs jacobi {itj2} on 32x32 p3, exchange {os.environ.get('MFV2D_CG_EXCHANGE', 'peer')}", flush=True)
         dist.barrier()
         dist.destroy_process_group()
         return

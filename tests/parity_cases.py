@@ -587,8 +587,8 @@ def check_partitioned_solve(M, SV, ST, ctx, rank, world, all_gather, fix, nh, nv
     return it, itj, it2, err
 
 
-def check_two_level(M, SV, ST, ctx, rank, world, all_gather, nh=24, nv=24, p=2, k=2, agg_size=4, deform=None):
-    """The two-level preconditioner (precond.cu) on a synthetic deformed mesh, one rank of ``world``: same solution as the
+def check_multilevel(M, SV, ST, ctx, rank, world, all_gather, nh=24, nv=24, p=2, k=2, mid_sizes=(2,), exact_size=6, deform=None):
+    """The multilevel preconditioner (precond.cu) on a synthetic deformed mesh, one rank of ``world``: same solution as the
     Jacobi-preconditioned CG, clearly fewer iterations, identical counts on every rank."""
     s = SYSTEMS["mixed_poisson_sorted"]
     ne = int(ST.form_sizes(s["form_orders"], p).sum())
@@ -601,17 +601,18 @@ def check_two_level(M, SV, ST, ctx, rank, world, all_gather, nh=24, nv=24, p=2, 
     batch = M.ElementBatch(make_basis(M, p, k), np.ascontiguousarray(corners[lo:hi]), ctx)
     mats = M.compute_element_matrices(specs_of(M, s), s["lhs"], batch)
     sysm = SV.LinearSystem(mats, (P.row, P.col, P.val), P.n_trace, ctx=ctx)
-    agg, z, n_coarse = ST.coarse_space_1form(nh, nv, p, s["form_orders"], agg_size)
+    strip_rows = [parts[r][0] // nh for r in range(world)] + [nv]
+    agg, z, n_agg = ST.coarse_hierarchy_1form(nh, nv, p, s["form_orders"], mid_sizes, exact_size, strip_rows)
     if world > 1:
         sysm.set_interface(P.shared_index, P.slot, P.n_slots, P.owned)
-        sysm.connect_peers(P.holder_ptr, P.holder_rank, all_gather, n_coarse=n_coarse)
-    sysm.set_coarse_space(agg[P.global_rows], z[P.global_rows], n_coarse)
+        sysm.connect_peers(P.holder_ptr, P.holder_rank, all_gather, n_coarse=n_agg[-1])
+    sysm.set_coarse_space(*ST.localize_hierarchy(agg, z, n_agg, P))
     rng = np.random.default_rng(11)
     rhs = rng.standard_normal(nh * nv * ne)[bounds[rank]:bounds[rank + 1]]
     phi = np.zeros(P.n_trace)
     conv = SV.ConvergenceSettings(5000, 1e300, 1e-11)
     xj, lj, _, itj = SV.solve_schur_iterative(sysm, rhs, phi, conv, precondition="jacobi")
-    x2, l2, _, it2 = SV.solve_schur_iterative(sysm, rhs, phi, conv, precondition="two-level")
+    x2, l2, _, it2 = SV.solve_schur_iterative(sysm, rhs, phi, conv, precondition="multilevel")
     assert not sysm.peer_error()
     assert relerr(x2, xj) < 1e-7 and relerr(l2, lj) < 1e-7, (relerr(x2, xj), relerr(l2, lj))
     assert it2 < 0.75 * itj, (it2, itj)

@@ -78,6 +78,6 @@ def test_peer_exchange_schur_cg(emu, world):
 
 
 @pytest.mark.parametrize("world", [1, 2, 3])
-def test_two_level(emu, world):
-    res = run_ranks(emu, world, P.check_two_level)
+def test_multilevel(emu, world):
+    res = run_ranks(emu, world, P.check_multilevel)
     assert all(r == res[0] for r in res)
