@@ -1,21 +1,29 @@
 #!/usr/bin/env python
-"""Benchmark of the element hot path (BASELINE.json metric: element matrices/sec, fp64).
+"""Benchmark of the element hot path (BASELINE.json metric: element matrices/sec and matrix-free apply GDoF/s (fp64); solve s).
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
 
-A "step" is one pass of the hot path over one batch: the assembly of ALL element matrices of the
-workload (config 2 of BASELINE.json: steady Stokes, 256 x 256 elements, order 4, integration order p + 3,
-sinusoidally deformed unit square, N_e = 81).  With N > 1 (torchrun, one process per GPU) every rank
-assembles its own copy-sized partition of an N-times larger mesh ("weak" scaling); assembly needs no
-collective.
+A "step" is one pass of the hot path over one batch: the assembly of ALL element matrices of the workload
+(BASELINE.json configs[1]: steady Stokes, 256 x 256 elements, order 4, integration order p + 3, sinusoidally
+deformed unit square, N_e = 81).  With N > 1 (torchrun, one process per GPU) every rank assembles its own
+copy-sized partition of an N-times larger mesh ("weak" scaling); assembly needs no collective.
 
-`value`     element matrices/s, whole job, inputs (corners) and outputs resident in HBM, CUDA events.
-`e2e`       the same through the C-ABI with HOST buffers: corners copied H2D and the element matrices
-            copied D2H to pinned memory inside the timed region.
-`roofline`  HBM-write roofline of the assembly kernel: (64 + 8 N_e^2) bytes per element / kernel time.
-`cpu_baseline`  the reference's own C path (oracle/_ref, built from /root/reference by oracle/build_ref.sh)
-            or the numpy oracle port, timed on a bounded sample on this box's host cores.
-`extra`     matrix-free apply GDoF/s (recompute and stored-block variants) and Schur-CG solve seconds.
+Top-level keys of the ONE JSON line:
+`value`         element matrices/s, whole job, inputs (corners) and outputs resident in HBM, CUDA events.
+`e2e`           the same through the C-ABI with HOST buffers: corners copied H2D and the element matrices copied D2H to
+                pinned memory inside the timed region.
+`roofline`      HBM-write roofline of the assembly kernel: (64 + 8 N_e^2) bytes per element / kernel time.
+`apply`         matrix-free apply (compute_element_vector semantics, recompute variant), mixed Poisson order 6 (the
+                north_star order) and Stokes order 4: GDoF/s, fp64 roofline (flops per element from SURVEY.md 8d's MAC
+                formula against the DMMA / DFMA peak measured in this process), CPU baseline.
+`apply_stored`  y_e = A_e x_e with the stored blocks (LinearSystem.apply_diagonal): GDoF/s, HBM-read roofline, CPU baseline.
+`solve`         BASELINE.json configs[4], weak-scaled: mixed Poisson order 6 on a deformed 1000 x (125 N) mesh (N = 8 is the
+                full 10^6-element mesh), smooth right-hand side, Schur-complement CG with the multilevel preconditioner,
+                interface sums and CG scalars through NVLink peer stores inside the CG kernels: seconds, iterations,
+                us / iteration, and the relative residual of the SADDLE-POINT system summed over the ranks.  The run
+                EXITS NON-ZERO when that residual exceeds north_star's 1e-10.
+`cpu_baseline`  the reference's own C path (oracle/_ref, built from /root/reference by oracle/build_ref.sh) or the numpy
+                oracle port, timed on a bounded sample on this box's host cores.
 """
 from __future__ import annotations
 
@@ -238,8 +246,133 @@ def run_reference(args):
 def workload_config(n_gpus):
     return {"workload": f"steady {'Stokes (vor0, vel1, prs2)' if SYSTEM == 'stokes' else 'mixed Poisson (q1, u2)'} element matrices, {N_SIDE}x{N_SIDE} elements per GPU, order {P_ORDER}, "
                         f"integration order p+{K_OVER}, deformed unit square " + ("(BASELINE.json configs[1])" if SYSTEM == "stokes" else "(per-GPU slice of BASELINE.json configs[4])"),
-            "elements_per_gpu": N_SIDE * N_SIDE, "element_dofs": {"stokes": 81, "mixed_poisson": 120}.get(SYSTEM, 0) if P_ORDER in (4, 6) else 0, "parallelism": f"elements x{n_gpus}, no collective",
+            "elements_per_gpu": N_SIDE * N_SIDE, "element_dofs": {"stokes": 81, "mixed_poisson": 120}.get(SYSTEM, 0) if P_ORDER in (4, 6) else 0,
+            "parallelism": f"elements x{n_gpus}: assembly and apply need no collective; the solve (key `solve`) exchanges interface sums and CG scalars "
+                           "through NVLink peer stores",
             "l2": "outputs (3.4 GB per step or more) are larger than L2; no flush needed"}
+
+
+def apply_macs(system: str, p: int, q: int) -> int:
+    """MACs of one matrix-free element apply, SURVEY.md 8(d): I(A, B) = A B q + A q^2 per tensor interpolation (its transpose
+    costs the same); M0 x = 2 I(p+1, p+1) + q^2, M2 x = 2 I(p, p) + q^2, M1 x = 2 [I(p+1, p) + I(p, p+1)] + 4 q^2, geometry
+    15 q^2 once per element; incidences and scalings are not counted."""
+    def interp(a, b):
+        return a * b * q + a * q * q
+
+    m0 = 2 * interp(p + 1, p + 1) + q * q
+    m2 = 2 * interp(p, p) + q * q
+    m1 = 2 * (interp(p + 1, p) + interp(p, p + 1)) + 4 * q * q
+    geo = 15 * q * q
+    if system == "mixed_poisson":  # M1 x_q, M2 x_u, M2 (E21 x_q)
+        return m1 + 2 * m2 + geo
+    if system == "stokes":  # M0 x_vor, M1 (E10 x_vor), E10^T (M1 x_vel), M2 (E21 x_vel), E21^T (M2 x_prs)
+        return m0 + 2 * m1 + 2 * m2 + geo
+    raise ValueError(system)
+
+
+def source_exact(x, y):
+    """right-hand side of examples/steady/plot_mixed_poisson.py:125-143 (smooth)"""
+    return 2.0 * np.pi**2 * np.cos(np.pi * x) * np.cos(np.pi * y)
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU baselines of the apply / stored apply / solve legs: the reference's own C code on one host core
+# ------------------------------------------------------------------------------------------------
+def cpu_baseline_apply(seconds: float):
+    """compute_element_vector (src/evaluation/element_system.c:245-411), mixed Poisson order 6, one core."""
+    from oracle.ref_loader import load_ref
+
+    ref = load_ref()
+    p, k = 6, K_OVER
+    names, orders, lhs = load_system("mixed_poisson")
+    from mfv2d_b200.structured import unit_square_corners
+
+    corners = unit_square_corners(64, 64, deform)
+    rng = np.random.default_rng(3)
+    ne = 2 * p * (p + 1) + p * p
+    done, t0 = 0, time.perf_counter()
+    if ref is not None:
+        rule = ref.IntegrationRule1D(p + k)
+        b1 = ref.Basis1D(p, rule)
+        b2 = ref.Basis2D(b1, b1)
+        specs = ref._ElementFormSpecification(*zip(names, orders))
+        x = rng.standard_normal(ne)
+        for c in corners:
+            sp = ref.ElementFemSpace2D(b2, np.ascontiguousarray(c))
+            ref.compute_element_vector(specs, lhs, sp, x)
+            done += 1
+            if time.perf_counter() - t0 > seconds:
+                break
+        kind = "reference"
+    else:
+        from oracle import mfv2d_oracle as O
+
+        ob = O.basis(p, p + k + 1)
+        blocks, fs = O.decode_expressions(lhs, names)
+        x = rng.standard_normal(ne)
+        for c in corners:
+            O.element_vector(ob, c, orders, blocks, x, fs)
+            done += 1
+            if time.perf_counter() - t0 > seconds:
+                break
+        kind = "port"
+    t = time.perf_counter() - t0
+    return {"value": done * ne / t / 1e9, "unit": "GDoF/s", "cores": 1, "kind": kind,
+            "sample": f"{done} elements of a deformed 64x64 p6 mixed-Poisson mesh (ElementFemSpace2D + compute_element_vector per element, "
+                      f"as the reference's callers do), {t:.1f} s on one core; per-element cost is independent of mesh size"}
+
+
+def cpu_baseline_system(seconds: float):
+    """LinearSystem.apply_diagonal (src/algebra/sparse_system.c:3-40) and solve_schur_iterative (python/mfv2d/solving.py:439-500)
+    of the reference on a small mixed-Poisson mesh: its C operators driven by oracle/ref_solve.py."""
+    from oracle.ref_loader import load_ref
+
+    ref = load_ref()
+    if ref is None:
+        return None, None
+    from mfv2d_b200 import structured as ST
+    from oracle import ref_solve as RS
+
+    p, k, nh = 6, K_OVER, 12
+    names, orders, lhs = load_system("mixed_poisson")
+    rule = ref.IntegrationRule1D(p + k)
+    b1 = ref.Basis1D(p, rule)
+    b2 = ref.Basis2D(b1, b1)
+    specs = ref._ElementFormSpecification(*zip(names, orders))
+    corners = ST.unit_square_corners(nh, nh, deform)
+    mats = np.stack([ref.compute_element_matrix(specs, lhs, ref.ElementFemSpace2D(b2, np.ascontiguousarray(c))) for c in corners])
+    ne = mats.shape[1]
+    row, col, val, nt = ST.continuity_constraints_1form(nh, nh, p, orders)
+    t0 = time.perf_counter()
+    system = RS.build_system(ref, mats, row, col, val, nt)
+    build_s = time.perf_counter() - t0
+    rng = np.random.default_rng(4)
+    x = ref.DenseVector(system, *rng.standard_normal((nh * nh, ne)))
+    y = ref.DenseVector(system)
+    reps, t0 = 0, time.perf_counter()
+    while time.perf_counter() - t0 < min(seconds, 3.0):
+        system.apply_diagonal(x, y)
+        reps += 1
+    t = (time.perf_counter() - t0) / reps
+    stored = {"value": nh * nh * ne / t / 1e9, "unit": "GDoF/s", "cores": 1, "kind": "reference",
+              "sample": f"LinearSystem.apply_diagonal on {nh}x{nh} p{p} mixed-Poisson blocks (N_e = {ne}), {reps} applications, one core"}
+    # right-hand side as in the GPU leg: dual DoFs of the smooth source on the 2-form rows
+    from oracle import mfv2d_oracle as O
+
+    ob = O.basis(p, p + k + 1)
+    rhs = np.zeros((nh * nh, ne))
+    for e, c in enumerate(corners):
+        xx, yy = O.physical_coordinates(c, ob.pnts)
+        rhs[e, ne - p * p:] = O.dual_dofs(ob, c, 3, source_exact(xx, yy))
+    t0 = time.perf_counter()
+    xs, lam, res, it = RS.solve_schur(ref, system, list(rhs), np.zeros(nt), 20000, 1e300, 1e-10)
+    t = time.perf_counter() - t0
+    solve = {"value": t, "unit": "s", "cores": 1, "kind": "reference",
+             "iterations": int(it) + 1, "us_per_iteration_per_element": t / (it + 1) / (nh * nh) * 1e6,
+             "sample": f"solve_schur_iterative on a deformed {nh}x{nh} p{p} mixed-Poisson mesh ({nh * nh} elements, {nt} multipliers), rtol 1e-10, "
+                       f"the reference's C operators (LU solves of the {ne}x{ne} blocks per application) driven by its own CG loop; "
+                       f"LinearSystem construction took {build_s:.1f} s on top; cost per iteration is proportional to the element count"}
+    return stored, solve
 
 
 def run_ours(args):
@@ -262,21 +395,23 @@ def run_ours(args):
     full = ST.unit_square_corners(N_SIDE, N_SIDE * world, deform)
     lo, hi = ST.strip_partition(N_SIDE, N_SIDE * world, world)[rank]
     corners = np.ascontiguousarray(full[lo:hi])
+    del full
     n = corners.shape[0]
     ne = specs.total_size(p, p)
     d_corners = ctx.to_device(corners)
     batch = M.ElementBatch(basis, d_corners, ctx)
     out = ctx.empty((n, ne, ne))
+    peak, peak_src = measured_peaks()
 
     def step_device():
         M.compute_element_matrices(specs, lhs, batch, out=out)
 
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()  # sampled over ALL timed regions of this run (assembly, apply, solve)
     for _ in range(args.warmup):
         step_device()
     ctx.synchronize()
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
     barrier(dist)
     ctx.synchronize()
     l0 = ctx.launch_count
@@ -287,164 +422,226 @@ def run_ours(args):
     ctx.synchronize()
     barrier(dist)
     launches = ctx.launch_count - l0
-    clocks = None
     ms = max_over_ranks(dist, ms)
     total_elems = sum_over_ranks(dist, float(n))
     ms_per_step = ms / args.steps
     value = total_elems / (ms_per_step * 1e-3)
 
     # per-launch kernel duration (the step is exactly one kernel launch): roofline of the assembly kernel
-    kern_ms = ms_per_step
     alg_bytes = (64 + 8 * ne * ne) * n
-    peak, peak_src = measured_peaks()
-    achieved = alg_bytes / (kern_ms * 1e-3) / 1e9
+    achieved = alg_bytes / (ms_per_step * 1e-3) / 1e9
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
-                "kernel": "element_matrix_kernel", "peak_source": peak_src,
-                "algorithmic_bytes_per_element": 64 + 8 * ne * ne}
+                "kernel": "element_matrix_kernel", "peak_source": peak_src, "algorithmic_bytes_per_element": 64 + 8 * ne * ne}
     tr_path = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tr_path):
         with open(tr_path) as f:
             roofline["traffic"] = json.load(f).get("element_matrix_kernel_bytes_per_launch")
 
     # ---- e2e: host buffers through the C-ABI, copies inside the timed region ----
-    h_corners = ctx.pinned((n, 4, 2))
-    h_corners[:] = corners
-    h_out = ctx.pinned((n, ne, ne))
-    hbatch = M.ElementBatch(basis, h_corners, ctx)
+    e2e_value, check_sum = None, None
+    if not args.skip_e2e:
+        h_corners = ctx.pinned((n, 4, 2))
+        h_corners[:] = corners
+        h_out = ctx.pinned((n, ne, ne))
+        hbatch = M.ElementBatch(basis, h_corners, ctx)
 
-    def step_host():
-        hbatch.set_corners(h_corners)
-        M.compute_element_matrices(specs, lhs, hbatch, out=h_out)
+        def step_host():
+            hbatch.set_corners(h_corners)
+            M.compute_element_matrices(specs, lhs, hbatch, out=h_out)
 
-    if args.skip_e2e:
-        e2e_steps = 0
-    else:
         step_host()
-        e2e_steps = max(1, min(args.steps, 3))
-    ctx.synchronize()
-    barrier(dist)
-    t0 = time.perf_counter()
-    ctx.timer_start()
-    for _ in range(e2e_steps):
-        step_host()
-    e2e_ms = ctx.timer_stop()
-    ctx.synchronize()
-    e2e_wall = (time.perf_counter() - t0) * 1e3
-    e2e_ms = max_over_ranks(dist, max(e2e_ms, e2e_wall))
-    e2e_value = total_elems / (e2e_ms / e2e_steps * 1e-3) if e2e_steps else None
-    check_sum = float(h_out[0].sum()) if e2e_steps else None
-    if rank == 0:
-        clocks = sampler.stop()
-    del h_out, hbatch
-
-    # ---- extra metrics on rank-local data: matrix-free apply and the Schur-CG solve ----
-    extra = {}
-    if not args.skip_extra:
-        rng = np.random.default_rng(rank)
-        x = ctx.to_device(rng.standard_normal((n, ne)))
-        y = ctx.empty((n, ne))
-        M.compute_element_vectors(specs, lhs, batch, x, out=y)
+        e2e_steps = max(1, min(args.steps, 5))
         ctx.synchronize()
-        ctx.timer_start()
-        reps = 5
-        for _ in range(reps):
-            M.compute_element_vectors(specs, lhs, batch, x, out=y)
-        t = ctx.timer_stop() / reps
-        extra["apply_recompute_gdofs"] = sum_over_ranks(dist, n * ne / (t * 1e-3) / 1e9)
-        # stored blocks: y_e = A_e x_e with the assembled matrices (LinearSystem.apply_diagonal)
-        nh = N_SIDE
-        s_names, s_orders, s_lhs = load_system("mixed_poisson")
-        s_specs = M._ElementFormSpecification(*zip(s_names, s_orders))
-        s_ne = s_specs.total_size(p, p)
-        s_out = ctx.empty((n, s_ne, s_ne))
-        M.compute_element_matrices(s_specs, s_lhs, batch, out=s_out)
-        # the GLOBAL Darcy system of the nh x (nh * world) mesh, split into the ranks' strips: interface multipliers
-        # are summed and the CG scalars reduced over NCCL (one process per GPU); with one rank nothing is shared
-        row, col, val, nt_glob = ST.continuity_constraints_1form(nh, (n // nh) * world, p, s_orders)
-        parts = ST.strip_partition(nh, (n // nh) * world, world)
-        bounds = [parts[r][0] * s_ne for r in range(world)] + [parts[-1][1] * s_ne]
-        part = ST.partition_constraints(row, col, val, nt_glob, bounds, rank)
-        del row, col, val
-        nt = part.n_trace
-        if world > 1:
-            from mfv2d_b200.runtime import comm_unique_id
-
-            ids = [comm_unique_id() if rank == 0 else None]
-            dist.broadcast_object_list(ids, src=0)
-            ctx.init_comm(world, rank, ids[0])
-        t0 = time.perf_counter()
-        system = SV.LinearSystem(s_out, (part.row, part.col, part.val), nt, ctx)
-        if world > 1:
-            system.set_interface(part.shared_index, part.slot, part.n_slots, part.owned)
-        ctx.synchronize()
-        extra["system_setup_s"] = time.perf_counter() - t0
-        xv = ctx.to_device(rng.standard_normal(n * s_ne))
-        yv = ctx.empty(n * s_ne)
-        system.apply_diagonal(xv, yv)
-        ctx.synchronize()
-        ctx.timer_start()
-        for _ in range(reps):
-            system.apply_diagonal(xv, yv)
-        t = ctx.timer_stop() / reps
-        extra["apply_stored_gdofs"] = sum_over_ranks(dist, n * s_ne / (t * 1e-3) / 1e9)
-        extra["apply_stored_gbs_per_gpu"] = (8 * s_ne * s_ne + 16 * s_ne) * n / (t * 1e-3) / 1e9
-        # Darcy (mixed Poisson) solve, f = random, rtol 1e-10
-        rhs = ctx.to_device(rng.standard_normal(n * s_ne))
-        phi = ctx.to_device(np.zeros(nt))
         barrier(dist)
-        ctx.synchronize()
         t0 = time.perf_counter()
-        xs, lam, res, it = SV.solve_schur_iterative(system, rhs, phi, SV.ConvergenceSettings(20000, 1e300, 1e-10))
-        ctx.synchronize()
-        solve_s = max_over_ranks(dist, time.perf_counter() - t0)
-        extra["solve"] = {"system": f"mixed Poisson (Darcy) {nh}x{(n // nh) * world} p{p}, {world} strip(s), random rhs, rtol 1e-10, "
-                                    "Schur-complement CG on the device" + (", interface sums and dots over NCCL" if world > 1 else ""),
-                          "s": solve_s, "iterations": it, "residual": res, "multipliers": int(nt_glob),
-                          "interface_multipliers": int(part.n_slots), "dense_dofs": int(n * s_ne * world)}
-
-        # slice of BASELINE.json configs[4]: mixed Poisson, order 6, the same number of elements per GPU
-        del system, xv, yv, rhs, phi, xs, lam, s_out
-        p6 = 6
-        b6 = M.Basis1D(p6, M.IntegrationRule1D(p6 + k))
-        batch6 = M.ElementBatch(M.Basis2D(b6, b6), d_corners, ctx)
-        ne6 = s_specs.total_size(p6, p6)
-        out6 = ctx.empty((n, ne6, ne6))
-        M.compute_element_matrices(s_specs, s_lhs, batch6, out=out6)
-        ctx.synchronize()
         ctx.timer_start()
-        for _ in range(reps):
-            M.compute_element_matrices(s_specs, s_lhs, batch6, out=out6)
-        t = ctx.timer_stop() / reps
-        x6 = ctx.to_device(rng.standard_normal((n, ne6)))
-        y6 = ctx.empty((n, ne6))
-        M.compute_element_vectors(s_specs, s_lhs, batch6, x6, out=y6)
+        for _ in range(e2e_steps):
+            step_host()
+        e2e_ms = ctx.timer_stop()
         ctx.synchronize()
-        ctx.timer_start()
-        for _ in range(reps):
-            M.compute_element_vectors(s_specs, s_lhs, batch6, x6, out=y6)
-        t2 = ctx.timer_stop() / reps
-        extra["order6_mixed_poisson"] = {
-            "elements_per_gpu": n, "element_dofs": ne6,
-            "element_matrices_per_s": sum_over_ranks(dist, n / (t * 1e-3)),
-            "assembly_hbm_frac_per_gpu": (64 + 8 * ne6 * ne6) * n / (t * 1e-3) / 1e9 / peak,
-            "apply_recompute_gdofs": sum_over_ranks(dist, n * ne6 / (t2 * 1e-3) / 1e9)}
-        del out6, x6, y6
+        e2e_wall = (time.perf_counter() - t0) * 1e3
+        e2e_ms = max_over_ranks(dist, max(e2e_ms, e2e_wall))
+        e2e_value = total_elems / (e2e_ms / e2e_steps * 1e-3)
+        check_sum = float(h_out[0].sum())
+        del h_out, hbatch
+    del out
 
     line = {
         "metric": "element_matrices_per_s", "value": value, "unit": "element matrices/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f64", "data": "synthetic", "config": workload_config(world), "clocks": clocks,
+        "dtype": "f64", "data": "synthetic", "config": workload_config(world), "clocks": None,
         "e2e": {"value": e2e_value, "unit": "element matrices/s", "h2d_bytes_per_step": int(corners.nbytes),
                 "d2h_bytes_per_step": int(n * ne * ne * 8), "checksum_first_matrix": check_sum},
-        "gpu_launches": int(launches), "roofline": roofline, "extra": extra,
+        "gpu_launches": int(launches), "roofline": roofline,
     }
+    failed = None
+    if not args.skip_extra:
+        dmma_tf, dfma_tf = ctx.measure_fp64_peak()
+        fp64_peak = max(dmma_tf, dfma_tf)
+        reps = 10
+        rng = np.random.default_rng(rank)
+
+        def time_apply(sys_name, specs_, lhs_, batch_, ne_, p_):
+            x = ctx.to_device(rng.standard_normal((n, ne_)))
+            y = ctx.empty((n, ne_))
+            for _ in range(3):
+                M.compute_element_vectors(specs_, lhs_, batch_, x, out=y)
+            ctx.synchronize()
+            barrier(dist)
+            ctx.timer_start()
+            for _ in range(reps):
+                M.compute_element_vectors(specs_, lhs_, batch_, x, out=y)
+            t = max_over_ranks(dist, ctx.timer_stop() / reps)
+            macs = apply_macs(sys_name, p_, p_ + k + 1)
+            tf = 2.0 * macs * n / (t * 1e-3) / 1e12
+            return {"value": total_elems * ne_ / (t * 1e-3) / 1e9, "unit": "GDoF/s", "ms": t, "elements_per_gpu": n, "element_dofs": ne_,
+                    "roofline": {"bound": "fp64", "achieved": tf, "peak": fp64_peak, "unit": "TFLOP/s", "frac": tf / fp64_peak, "traffic": None,
+                                 "flops_per_element": 2 * macs, "algorithmic_bytes_per_element": 64 + 16 * ne_,
+                                 "peak_source": f"measured in this process: mma.sync.m8n8k4.f64 chains {dmma_tf:.1f}, DFMA chains {dfma_tf:.1f} TFLOP/s "
+                                                "(mfv2d_cuda_measure_fp64_peak)"}}
+
+        # matrix-free apply, Stokes order 4 (the assembly workload) and mixed Poisson order 6 (north_star's order)
+        apply4 = time_apply("stokes", specs, lhs, batch, ne, p) if SYSTEM == "stokes" else None
+        s_names, s_orders, s_lhs = load_system("mixed_poisson")
+        s_specs = M._ElementFormSpecification(*zip(s_names, s_orders))
+        p6 = 6
+        b6 = M.Basis1D(p6, M.IntegrationRule1D(p6 + k))
+        basis6 = M.Basis2D(b6, b6)
+        ne6 = s_specs.total_size(p6, p6)
+        batch6 = M.ElementBatch(basis6, d_corners, ctx)
+        apply6 = time_apply("mixed_poisson", s_specs, s_lhs, batch6, ne6, p6)
+        line["apply"] = dict(apply6, workload=f"compute_element_vector semantics (recompute), mixed Poisson order 6, {n} deformed elements per GPU",
+                             stokes_order4=apply4)
+        del batch6
+
+        # ---- BASELINE.json configs[4], weak-scaled: 1000 x (125 world) elements, mixed Poisson order 6 ----
+        nh, rows_per = args.solve_cols, args.solve_rows
+        nv = rows_per * world
+        t_host = time.perf_counter()
+        parts = ST.strip_partition(nh, nv, world)
+        flo, fhi = parts[rank]
+        xi, eta = np.meshgrid(np.linspace(-1, 1, nh + 1), np.linspace(-1, 1, nv + 1)[flo // nh:fhi // nh + 1])
+        px, py = deform(xi, eta)
+        pts = np.stack((px, py), axis=-1)
+        c6 = np.empty((fhi // nh - flo // nh, nh, 4, 2))
+        c6[:, :, 0], c6[:, :, 1], c6[:, :, 2], c6[:, :, 3] = pts[:-1, :-1], pts[:-1, 1:], pts[1:, 1:], pts[1:, :-1]
+        c6 = np.ascontiguousarray(c6.reshape(-1, 4, 2))
+        n6 = c6.shape[0]
+        row, col, val, nt_glob = ST.continuity_constraints_1form(nh, nv, p6, s_orders)
+        bounds = [parts[r][0] * ne6 for r in range(world)] + [parts[-1][1] * ne6]
+        part = ST.partition_constraints(row, col, val, nt_glob, bounds, rank)
+        del row, col, val
+        strip_rows = [parts[r][0] // nh for r in range(world)] + [nv]
+        mids = tuple(int(v) for v in args.solve_mid.split(",") if v)
+        agg, zc, n_agg = ST.coarse_hierarchy_1form(nh, nv, p6, s_orders, mids, args.solve_agg, strip_rows)
+        hier = ST.localize_hierarchy(agg, zc, n_agg, part)
+        del agg, zc
+        host_s = time.perf_counter() - t_host
+        if world > 1:
+            ctx.init_comm(world, rank, None)  # ranks only: every exchange goes through the NVLink peer blocks, NCCL is not loaded
+        t0 = time.perf_counter()
+        solve_batch = M.ElementBatch(basis6, ctx.to_device(c6), ctx)
+        mats6 = ctx.empty((n6, ne6, ne6))
+        M.compute_element_matrices(s_specs, s_lhs, solve_batch, out=mats6)
+        system = SV.LinearSystem(mats6, (part.row, part.col, part.val), part.n_trace, ctx)
+        if world > 1:
+            system.set_interface(part.shared_index, part.slot, part.n_slots, part.owned)
+
+            def all_gather(obj):
+                outl = [None] * world
+                dist.all_gather_object(outl, obj)
+                return outl
+
+            system.connect_peers(part.holder_ptr, part.holder_rank, all_gather, n_coarse=n_agg[-1])
+        ctx.synchronize()
+        setup_s = max_over_ranks(dist, time.perf_counter() - t0)
+        t0 = time.perf_counter()
+        system.set_coarse_space(*hier)
+        ctx.synchronize()
+        coarse_s = max_over_ranks(dist, time.perf_counter() - t0)
+
+        # stored-block apply on the same blocks (LinearSystem.apply_diagonal): HBM read bound
+        xv = ctx.to_device(rng.standard_normal(n6 * ne6))
+        yv = ctx.empty(n6 * ne6)
+        system.apply_diagonal(xv, yv)
+        ctx.synchronize()
+        barrier(dist)
+        ctx.timer_start()
+        for _ in range(5):
+            system.apply_diagonal(xv, yv)
+        t = max_over_ranks(dist, ctx.timer_stop() / 5)
+        sb = (8 * ne6 * ne6 + 16 * ne6) * n6 / (t * 1e-3) / 1e9
+        line["apply_stored"] = {"value": sum_over_ranks(dist, float(n6)) * ne6 / (t * 1e-3) / 1e9, "unit": "GDoF/s", "ms": t,
+                                "workload": f"y_e = A_e x_e, stored mixed-Poisson order-6 blocks (N_e = {ne6}), {n6} elements per GPU",
+                                "roofline": {"bound": "hbm", "achieved": sb, "peak": peak, "unit": "GB/s", "frac": sb / peak, "traffic": None,
+                                             "kernel": "block_gemv_kernel", "algorithmic_bytes_per_element": 8 * ne6 * ne6 + 16 * ne6,
+                                             "peak_source": peak_src}}
+        del xv, yv
+
+        # smooth right-hand side: dual DoFs of source_exact on the 2-form rows; HOST buffers in, HOST solution out
+        rhs_h = np.zeros((n6, ne6))
+        fdual = solve_batch.dual_dofs(s_orders[1], source_exact)
+        rhs_h[:, ne6 - p6 * p6:] = fdual.get() if hasattr(fdual, "get") else fdual
+        rhs_h = rhs_h.ravel()
+        phi_h = np.zeros(part.n_trace)
+        conv = SV.ConvergenceSettings(20000, 1e300, args.solve_rtol)
+        times = []
+        for _ in range(2):  # the first solve instantiates the CUDA graph of 16 iterations
+            barrier(dist)
+            ctx.synchronize()
+            t0 = time.perf_counter()
+            xs, lam, res, it = SV.solve_schur_iterative(system, rhs_h, phi_h, conv, precondition="multilevel")
+            ctx.synchronize()
+            times.append(max_over_ranks(dist, time.perf_counter() - t0))
+        peer_bad = system.peer_error() if world > 1 else False
+        # residual of the saddle-point system [[A, N^T], [N, 0]] (x, lambda) = (rhs, 0), with the library's own operators,
+        # ownership-weighted over the ranks (north_star: <= 1e-10)
+        r1 = system.apply_diagonal(xs) + system.apply_trace_transpose(lam) - rhs_h
+        r2 = system.apply_trace(xs)
+        own = np.asarray(part.owned, bool) if world > 1 else np.ones(part.n_trace, bool)
+        num = sum_over_ranks(dist, float(r1 @ r1 + r2[own] @ r2[own]))
+        den = sum_over_ranks(dist, float(rhs_h @ rhs_h))
+        saddle = float(np.sqrt(num / den))
+        solve_s = times[-1]
+        # per-iteration byte model: packed condensed blocks + slot vectors + gather / update vectors of the CG
+        m_e = 4 * p6
+        it_bytes = n6 * (m_e * (m_e + 1) // 2 * 8 + m_e * (8 + 4 + 8)) + part.n_trace * (48 + 88)
+        line["solve"] = {
+            "system": f"mixed Poisson (q1, u2) order {p6} on a deformed {nh}x{nv} quad mesh, {world} strip(s) of {rows_per} rows "
+                      + ("= BASELINE.json configs[4] (10^6 elements)" if nh * nv == 1000000 else "(per-GPU share of BASELINE.json configs[4], weak-scaled)"),
+            "method": "CG on the Schur complement N A^-1 N^T (packed symmetric condensed blocks), additive multilevel preconditioner "
+                      f"(Jacobi + aggregates of {args.solve_mid}^2 elements + exact level of {args.solve_agg}^2 elements, {n_agg[-1]} global aggregates)"
+                      + (", interface sums and CG scalars by NVLink peer stores inside the CG kernels (no NCCL)" if world > 1 else ""),
+            "rhs": "dual DoFs of 2 pi^2 cos(pi x) cos(pi y) (plot_mixed_poisson.py's source_exact), host buffers in / out", "rtol": args.solve_rtol,
+            "s": solve_s, "s_first_solve": times[0], "iterations": int(it), "us_per_iteration": solve_s / max(int(it), 1) * 1e6,
+            "cg_residual": float(res), "saddle_relative_residual": saddle, "gate": 1e-10, "peer_error": bool(peer_bad),
+            "elements": int(nh * nv), "dense_dofs": int(nh * nv * ne6), "multipliers": int(nt_glob), "interface_multipliers": int(part.n_slots),
+            "system_setup_s": setup_s, "preconditioner_setup_s": coarse_s, "host_mesh_constraints_partition_s": host_s,
+            "pipeline_s": host_s + setup_s + coarse_s + times[0],
+            "roofline": {"bound": "hbm", "achieved": it_bytes / (solve_s / max(int(it), 1)) / 1e9, "peak": peak, "unit": "GB/s",
+                         "frac": it_bytes / (solve_s / max(int(it), 1)) / 1e9 / peak, "traffic": None, "kernel": "one CG iteration (schur_local_packed + "
+                         "cg1_gather + cg1_update; the preconditioner's kernels are not counted as useful bytes)", "algorithmic_bytes_per_iteration": int(it_bytes),
+                         "peak_source": peak_src}}
+        if not (saddle <= 1e-10) or peer_bad:
+            failed = f"solve: saddle-point relative residual {saddle:.3e} exceeds 1e-10" if not peer_bad else "solve: peer exchange timed out"
+        del system, mats6, xs, lam
     if rank == 0:
+        line["clocks"] = sampler.stop()
         if world == 1 and not args.no_cpu:
             line["cpu_baseline"] = cpu_baseline(1, args.cpu_seconds)
+            line["vs_cpu_baseline"] = {"value": value / line["cpu_baseline"]["value"], "e2e": (e2e_value or 0.0) / line["cpu_baseline"]["value"]}
+            if not args.skip_extra:
+                line["apply"]["cpu_baseline"] = cpu_baseline_apply(min(args.cpu_seconds, 6.0))
+                stored_b, solve_b = cpu_baseline_system(min(args.cpu_seconds, 6.0))
+                line["apply_stored"]["cpu_baseline"] = stored_b
+                line["solve"]["cpu_baseline"] = solve_b
         emit(line)
     barrier(dist)
     if dist is not None:
         dist.destroy_process_group()
+    if failed:
+        sys.stderr.write("bench.py: FAILED parity gate: " + failed + "\n")
+        sys.exit(3)
 
 
 _JSON_FD = None
@@ -477,11 +674,16 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu", action="store_true")
-    ap.add_argument("--skip-extra", action="store_true", help="skip the apply / solve extras (profiling runs)")
+    ap.add_argument("--skip-extra", action="store_true", help="skip the apply / solve legs (profiling runs)")
     ap.add_argument("--skip-e2e", action="store_true", help="skip the host-buffer leg (profiling runs)")
     ap.add_argument("--workload", default="stokes4", choices=["stokes4", "poisson6"],
                     help="stokes4 = BASELINE.json configs[1] (the default and the reported metric); poisson6 = per-GPU slice of "
                          "configs[4] (mixed Poisson, order 6), for profiling")
+    ap.add_argument("--solve-cols", type=int, default=1000, help="elements per row of the solve leg's mesh (configs[4]: 1000)")
+    ap.add_argument("--solve-rows", type=int, default=125, help="element rows PER GPU of the solve leg's mesh (8 x 125 = configs[4])")
+    ap.add_argument("--solve-agg", type=int, default=20, help="aggregate size of the exact coarse level (elements per side)")
+    ap.add_argument("--solve-mid", default="5", help="aggregate sizes of the diagonal levels, comma separated")
+    ap.add_argument("--solve-rtol", type=float, default=1e-11, help="relative tolerance of the Schur CG (the saddle-point gate is 1e-10)")
     args = ap.parse_args()
     if args.workload == "poisson6":
         global P_ORDER, SYSTEM

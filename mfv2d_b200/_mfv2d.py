@@ -448,8 +448,12 @@ class ElementBatch:
         nk = self.form_size(order)
         out = self._out(out, (self.n, nk, nk))
         space = space_of(out)
-        status = np.zeros(self.n, np.int32) if space == HOST else None
+        status = None
+        if inverse:  # a singular block must surface as MFV2D_PIVOT_FAILED like in the reference, for device outputs too
+            status = np.zeros(self.n, np.int32) if space == HOST else self.ctx.empty(self.n, np.int32)
         check(lib().mfv2d_cuda_mass_batch(self.handle, order, int(bool(inverse)), addr(out), addr(status), space), self.ctx.handle)
+        if isinstance(status, DeviceArray):
+            status = status.get()
         if status is not None and np.any(status):
             bad = int(np.flatnonzero(status)[0])
             raise _capi.Mfv2dCudaError(int(status[bad]), _capi.result_name(int(status[bad])), f"element {bad}: mass matrix could not be inverted")

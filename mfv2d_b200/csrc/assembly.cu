@@ -437,7 +437,7 @@ __device__ __forceinline__ void invert_spd_slots(const AsmArgs &args, int off, i
             double *D = slot + L.slot_arena + off;
             const double *colk = slot + L.slot_t, *rowk = colk + n;
             const double pv = colk[k];
-            if (ij == 0 && !(fabs(pv) > 1e-300))
+            if (ij == 0 && !(fabs(pv) > 1e-12)) // decompose_pivoted_lu's tolerance (src/algebra/matrix.c:454-457)
                 bad[e] = 1;
             const double ip = 1.0 / pv;
             double v;

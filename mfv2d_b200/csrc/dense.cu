@@ -225,6 +225,60 @@ __global__ void __launch_bounds__(DENSE_THREADS) solve_kernel(int n, int nrhs, u
     }
 }
 
+// ---- one LARGE definite matrix (the coarse operator of the multilevel preconditioner, precond.cu): in-place Gauss-Jordan
+// without pivoting, the whole device working on every elimination step (two launches per pivot)
+__global__ void gj_snapshot_kernel(int n, int k, const double *__restrict__ M, double *__restrict__ colk, double *__restrict__ rowk,
+                                   int *__restrict__ flag, double tiny)
+{
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+    {
+        colk[i] = M[(size_t)i * n + k];
+        rowk[i] = M[(size_t)k * n + i];
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0 && !(fabs(M[(size_t)k * n + k]) > tiny))
+        *flag = 1;
+}
+
+__global__ void __launch_bounds__(256) gj_update_kernel(int n, int k, double *__restrict__ M, const double *__restrict__ colk,
+                                                        const double *__restrict__ rowk)
+{
+    const double ip = 1.0 / colk[k];
+    const size_t nn = (size_t)n * n;
+    for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < nn; idx += (size_t)gridDim.x * blockDim.x)
+    {
+        const int i = (int)(idx / n), j = (int)(idx - (size_t)i * n);
+        double v;
+        if (i == k)
+            v = (j == k) ? ip : rowk[j] * ip;
+        else if (j == k)
+            v = -colk[i] * ip;
+        else
+            v = fma(-colk[i] * ip, rowk[j], M[idx]);
+        M[idx] = v;
+    }
+}
+
+// M (n x n, definite) <- M^-1 in place; *d_flag (device int, zeroed here) is set when a pivot vanishes
+int launch_inverse_definite_large(mfv2d_ctx *ctx, int n, double *d_M, int *d_flag)
+{
+    double *scratch = nullptr;
+    MFV2D_TRY(mfv2d_cuda_malloc(ctx, (size_t)2 * n * sizeof(double), (void **)&scratch));
+    MFV2D_CUDA_CHECK(ctx, cudaMemsetAsync(d_flag, 0, sizeof(int), ctx->stream));
+    const size_t nn = (size_t)n * n;
+    unsigned grid = (unsigned)((nn + 255) / 256);
+    if (grid > (unsigned)ctx->sm_count * 8)
+        grid = (unsigned)ctx->sm_count * 8;
+    for (int k = 0; k < n; ++k)
+    {
+        MFV2D_LAUNCH(gj_snapshot_kernel, (unsigned)((n + 255) / 256), 256, 0, ctx->stream, n, k, (const double *)d_M, scratch, scratch + n,
+                     d_flag, 1e-300);
+        MFV2D_LAUNCH(gj_update_kernel, grid, 256, 0, ctx->stream, n, k, d_M, (const double *)scratch, (const double *)(scratch + n));
+    }
+    ctx->launches += 2 * (uint64_t)n;
+    MFV2D_CUDA_CHECK(ctx, cudaGetLastError());
+    return mfv2d_cuda_free(ctx, scratch);
+}
+
 // device-pointer entry used by system.cu as well
 int launch_inverse_batch(mfv2d_ctx *ctx, int n, size_t batch, const double *d_in, double *d_out, int32_t *d_status)
 {

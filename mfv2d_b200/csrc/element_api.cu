@@ -518,13 +518,31 @@ int mfv2d_cuda_element_matrix_batch(const mfv2d_plan *plan, const mfv2d_elements
         r = resolve_fields(plan, e, (const double *)d.dev, field_values, space, &fs);
     if (!r)
         r = stage_out_alloc(ctx, out, e->n * N * N * sizeof(double), space, &o);
+    // a MASS(inv) that survives in the plan can hit a singular block (collapsed element): the reference raises
+    // MFV2D_PIVOT_FAILED (matrix_full_invert -> decompose_pivoted_lu, src/algebra/matrix.c:361-460) - so do we
+    bool has_inverse = false;
+    for (const DevDense &dd : plan->dense)
+        has_inverse = has_inverse || dd.inverse;
+    int32_t *d_status = nullptr;
+    if (!r && plan->matrix_fused && has_inverse)
+        r = mfv2d_cuda_malloc(ctx, e->n * sizeof(int32_t), (void **)&d_status);
     if (!r)
     {
         if (plan->matrix_fused)
-            r = launch_element_matrix(plan, e, fs.ptr, (double *)o.dev, nullptr);
+            r = launch_element_matrix(plan, e, fs.ptr, (double *)o.dev, d_status);
         else
             r = launch_matrix_by_columns(plan, e, fs.ptr, (double *)o.dev);
     }
+    if (!r && d_status)
+    {
+        std::vector<int32_t> st(e->n);
+        r = mfv2d_cuda_download(ctx, st.data(), d_status, e->n * sizeof(int32_t));
+        for (size_t i = 0; i < e->n && !r; ++i)
+            if (st[i] != MFV2D_SUCCESS)
+                r = mfv2d_fail(ctx, MFV2D_PIVOT_FAILED, "element_matrix_batch: an inverse mass matrix of element %zu is singular", i);
+    }
+    if (d_status)
+        mfv2d_cuda_free(ctx, d_status);
     if (!r)
         r = stage_finish(&o);
     else

@@ -19,7 +19,7 @@
 
 #include "system.cuh"
 
-int launch_inverse_batch(mfv2d_ctx *ctx, int n, size_t batch, const double *d_in, double *d_out, int32_t *d_status);
+int launch_inverse_definite_large(mfv2d_ctx *ctx, int n, double *d_M, int *d_flag);
 
 #define COARSE_MAX 4096
 #define COARSE_MAX_LEVELS 6
@@ -379,9 +379,9 @@ int mfv2d_cuda_system_set_coarse_space(mfv2d_system *s, int n_levels, const int6
         const size_t nn = (size_t)n_exact * n_exact;
         double *d_Ac = nullptr;
         int32_t *d_status = nullptr;
-        MFV2D_TRY(sys_alloc(s, nn, &d_Ac));
         MFV2D_TRY(sys_alloc(s, nn, &s->d_Ac_inv));
         MFV2D_TRY(sys_alloc(s, (size_t)2, &d_status));
+        d_Ac = s->d_Ac_inv; // assembled, summed and inverted in place
         MFV2D_CUDA_CHECK(ctx, cudaMemsetAsync(d_Ac, 0, nn * sizeof(double), ctx->stream));
         if (s->n_elem)
         {
@@ -399,7 +399,8 @@ int mfv2d_cuda_system_set_coarse_space(mfv2d_system *s, int n_levels, const int6
             else
                 MFV2D_TRY(comm_allreduce(ctx, d_Ac, nn));
         }
-        MFV2D_TRY(launch_inverse_batch(ctx, (int)n_exact, 1, d_Ac, s->d_Ac_inv, d_status));
+        // P^T S P is definite like S: no pivoting, every elimination step runs on the whole device
+        MFV2D_TRY(launch_inverse_definite_large(ctx, (int)n_exact, d_Ac, d_status));
         int32_t st = 0;
         MFV2D_TRY(mfv2d_cuda_download(ctx, &st, d_status, sizeof st));
         if (st != MFV2D_SUCCESS)
