@@ -349,6 +349,12 @@ MFV2D_API int mfv2d_cuda_vec_dot(mfv2d_ctx *ctx, size_t n, const double *x, cons
 MFV2D_API int mfv2d_cuda_solve_schur_cg(mfv2d_system *sys, const double *rhs, const double *phi, int max_iter,
                                         double atol, double rtol, int precondition, double *x, double *lambda,
                                         double *residual, int *iterations, int space);
+/* The same for systems whose element blocks are NOT symmetric (advection terms): BiCGStab on S, right-preconditioned with
+ * diag(S) when precondition != 0.  The reference has no iterative counterpart (its CG needs symmetry; production path:
+ * SuperLU, python/mfv2d/solve_system_2d.py:258-282). */
+MFV2D_API int mfv2d_cuda_solve_schur_bicgstab(mfv2d_system *sys, const double *rhs, const double *phi, int max_iter,
+                                              double atol, double rtol, int precondition, double *x, double *lambda,
+                                              double *residual, int *iterations, int space);
 /* solve_pcg_iterative (solving.py:634-684): PCG on [[A, N^T], [N, 0]] with (A^-1 (+) I). */
 MFV2D_API int mfv2d_cuda_solve_pcg(mfv2d_system *sys, const double *rhs, const double *phi, int max_iter,
                                    double atol, double rtol, double *x, double *lambda, double *residual,

@@ -127,6 +127,7 @@ __global__ void __launch_bounds__(SYS_THREADS) coarse_aggregate_kernel(const Coa
         e = pv.epoch[1] + 1;
         parity = (int)(e & 1);
     }
+    bool wrote = false;
     for (long long J = blockIdx.x * (long long)blockDim.x + threadIdx.x; J < a.n_agg_total; J += (long long)gridDim.x * blockDim.x)
     {
         double acc = 0.0;
@@ -138,14 +139,18 @@ __global__ void __launch_bounds__(SYS_THREADS) coarse_aggregate_kernel(const Coa
         {
             a.y[J] = acc;
             if (peers)
+            {
                 for (int r = 0; r < pv.n_ranks; ++r)
                     if (r != pv.rank)
                         peer_region(pv, r, 1, parity, pv.rank)[J - a.exact_begin] = acc;
+                wrote = true;
+            }
         }
     }
     if (!peers)
         return;
-    peer_fence(); // every writer orders its own remote stores before the CTA's ticket
+    if (wrote)
+        peer_fence(); // every writer orders its own remote stores before the CTA's ticket
     __syncthreads();
     if (threadIdx.x == 0)
     {
@@ -345,6 +350,14 @@ int mfv2d_cuda_system_set_coarse_space(mfv2d_system *s, int n_levels, const int6
     s->n_chunks = (long long)chunk_ptr.size() - 1;
     std::vector<int32_t> h_agg(agg, agg + (size_t)n_levels * nt);
     std::vector<double> h_z(z, z + nt);
+    if (s->scaled)
+    {
+        // the blocks are those of D S D: its near-null-space vector is D^-1 z
+        std::vector<double> rs((size_t)nt);
+        MFV2D_TRY(mfv2d_cuda_download(ctx, rs.data(), s->d_rs, (size_t)nt * sizeof(double)));
+        for (int64_t i = 0; i < nt; ++i)
+            h_z[i] /= rs[i];
+    }
     MFV2D_TRY(sys_upload(s, h_agg, &s->d_lagg));
     MFV2D_TRY(sys_upload(s, agg_off, &s->d_agg_off));
     MFV2D_TRY(sys_upload(s, h_z, &s->d_cz));

@@ -73,6 +73,7 @@ __global__ void __launch_bounds__(SYS_THREADS) cg1_gather_kernel(const CgGatherA
         parity = (int)(e & 1);
     }
     double d = 0.0, g = 0.0, rho = 0.0;
+    bool wrote = false;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < a.n_trace; i += (long long)gridDim.x * blockDim.x)
     {
         double acc = 0.0;
@@ -101,10 +102,11 @@ __global__ void __launch_bounds__(SYS_THREADS) cg1_gather_kernel(const CgGatherA
                 const long long sl = a.shared_slot[j];
                 for (int64_t h = a.holder_ptr[j]; h < a.holder_ptr[j + 1]; ++h)
                     peer_region(pv, a.holder_rank[h], 0, parity, pv.rank)[sl] = acc;
+                wrote = true;
             }
         }
     }
-    if (peers)
+    if (wrote)
         peer_fence(); // every writer orders its own remote stores before the CTA's ticket
     const int np = gridDim.x;
     block_reduce_store(d, a.partials);
@@ -327,6 +329,8 @@ int mfv2d_cuda_solve_schur_cg(mfv2d_system *s, const double *rhs, const double *
                          (const double *)sphi.dev, res);
             ctx->launches++;
         }
+        if ((r = sys_scale_rows(s, res, false))) // the CG runs on the equilibrated system D S D (D lambda') = D b
+            break;
         if (cudaMemsetAsync(lam, 0, (nt ? nt : 1) * sizeof(double), ctx->stream) != cudaSuccess ||
             cudaMemsetAsync(sc, 0, 32 * sizeof(double), ctx->stream) != cudaSuccess)
         {
@@ -496,6 +500,8 @@ int mfv2d_cuda_solve_schur_cg(mfv2d_system *s, const double *rhs, const double *
                 res_mag2 = h[0];
             }
         }
+        if ((r = sys_scale_rows(s, lam, false))) // lambda = D lambda'
+            break;
         if (nt && cudaMemcpyAsync(slam.dev, lam, nt * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream) != cudaSuccess)
         {
             r = mfv2d_fail(ctx, MFV2D_CUDA_ERROR, "solve_schur_cg: copy of lambda failed: %s", cudaGetErrorString(cudaGetLastError()));

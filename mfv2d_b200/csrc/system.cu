@@ -527,6 +527,24 @@ __global__ void axpby_kernel(long long n, double a, const double *__restrict__ x
         out[i] = a * x[i] + b * y[i];
 }
 
+// v[i] *= d[i] (inverse = 0) or v[i] /= d[i] (inverse = 1)
+__global__ void scale_by_kernel(long long n, const double *__restrict__ d, double *__restrict__ v, int inverse)
+{
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+        v[i] = inverse ? v[i] / d[i] : v[i] * d[i];
+}
+
+int sys_scale_rows(const mfv2d_system *s, double *v, bool inverse)
+{
+    if (!s->scaled || !s->n_trace)
+        return MFV2D_SUCCESS;
+    MFV2D_LAUNCH(scale_by_kernel, grid_for(s->ctx, s->n_trace, 256), 256, 0, s->ctx->stream, (long long)s->n_trace, (const double *)s->d_rs, v,
+                 (int)inverse);
+    s->ctx->launches++;
+    MFV2D_CUDA_CHECK(s->ctx, cudaGetLastError());
+    return MFV2D_SUCCESS;
+}
+
 // multi-GPU: pack the shared multipliers of `t` into the interface buffer / scatter the reduced sums back
 __global__ void iface_pack_kernel(long long n_shared, const int64_t *__restrict__ index, const int64_t *__restrict__ slot,
                                   const double *__restrict__ t, double *__restrict__ buf)
@@ -856,6 +874,26 @@ int mfv2d_cuda_system_create(mfv2d_ctx *ctx, size_t n_elem, const int64_t *block
         for (size_t k = 0; k < n_con; ++k)
             order[fill[elem_of[k]]++] = (int64_t)k;
     }
+    // Row equilibration of the CONDENSED system only: S' = D S D with D = 2^-round(log2 max|row of N|) (exact scaling).  The
+    // hanging-side rows of non-conforming meshes carry coefficients up to 1e8 (inverse interpolation matrices,
+    // python/mfv2d/continuity.py:256-265), which would put 16 orders of magnitude between the entries of S and make the
+    // residual test of the CG blind to every other row.  Conforming rows (+-1) get D = 1: nothing changes for them, bit for
+    // bit.  N, A and the operators keep the caller's scaling; partitioned systems are not equilibrated (shared rows would
+    // need the same D on every rank; conforming cuts have +-1 anyway).
+    std::vector<double> rs(n_trace, 1.0);
+    if (ctx->n_ranks <= 1)
+    {
+        std::vector<double> mx(n_trace, 0.0);
+        for (size_t k = 0; k < n_con; ++k)
+            mx[con_row[k]] = std::max(mx[con_row[k]], std::fabs(con_val[k]));
+        for (size_t i = 0; i < n_trace; ++i)
+            if (mx[i] > 0.0 && std::isfinite(mx[i]))
+            {
+                rs[i] = std::ldexp(1.0, -(int)std::lround(std::log2(mx[i])));
+                if (rs[i] != 1.0)
+                    s->scaled = true;
+            }
+    }
     std::vector<int64_t> slot_off(n_elem + 1, 0), slot_trace, lrow_ptr(1, 0);
     std::vector<int32_t> lrow_col(n_con);
     std::vector<double> lrow_val(n_con);
@@ -873,7 +911,7 @@ int mfv2d_cuda_system_create(mfv2d_ctx *ctx, size_t n_elem, const int64_t *block
                 prev_row = con_row[k];
             }
             lrow_col[a] = (int32_t)(con_col[k] - boff[e]);
-            lrow_val[a] = con_val[k];
+            lrow_val[a] = con_val[k] * rs[con_row[k]];
         }
         if (prev_row >= 0)
             lrow_ptr.push_back(ecount[e + 1]);
@@ -909,6 +947,8 @@ int mfv2d_cuda_system_create(mfv2d_ctx *ctx, size_t n_elem, const int64_t *block
     SYS_TRY(sys_upload(s, lrow_val, &s->d_lrow_val));
     SYS_TRY(sys_upload(s, tr_ptr, &s->d_tr_ptr));
     SYS_TRY(sys_upload(s, tr_slot, &s->d_tr_slot));
+    if (s->scaled)
+        SYS_TRY(sys_upload(s, rs, &s->d_rs));
     {
         // conforming meshes: at most two elements per multiplier -> a fixed-width 32-bit table for the CG's gather kernel
         bool two = s->n_slots < (int64_t)1 << 31;
@@ -1074,8 +1114,16 @@ int mfv2d_cuda_system_apply_trace_transpose(const mfv2d_system *s, const double 
 
 int mfv2d_cuda_system_apply_schur(const mfv2d_system *s, const double *t_in, double *t_out, int space)
 {
-    return sys_unary(s, t_in, s->n_trace, t_out, s->n_trace, space,
-                     [&](const double *di, double *dout) { return sys_apply_schur(s, di, dout, nullptr); });
+    return sys_unary(s, t_in, s->n_trace, t_out, s->n_trace, space, [&](const double *di, double *dout) {
+        if (!s->scaled)
+            return sys_apply_schur(s, di, dout, nullptr);
+        // the stored blocks are those of S' = D S D: S t = D^-1 S' (D^-1 t)
+        double *tmp = s->d_work_trace[7];
+        MFV2D_CUDA_CHECK(s->ctx, cudaMemcpyAsync(tmp, di, (size_t)s->n_trace * sizeof(double), cudaMemcpyDeviceToDevice, s->ctx->stream));
+        MFV2D_TRY(sys_scale_rows(s, tmp, true));
+        MFV2D_TRY(sys_apply_schur(s, tmp, dout, nullptr));
+        return sys_scale_rows(s, dout, true);
+    });
 }
 
 int mfv2d_cuda_vec_axpby(mfv2d_ctx *ctx, size_t n, double a, const double *x, double b, const double *y, double *out,

@@ -102,6 +102,8 @@ struct mfv2d_system
     int64_t n_elem = 0, n_dense = 0, n_trace = 0, n_con = 0, n_slots = 0;
     int max_n = 0, max_m = 0;
     bool uniform = false; // all blocks have the same size
+    bool scaled = false;    // the condensed blocks are those of D S D, D = d_rs (row equilibration, system.cu)
+    double *d_rs = nullptr; // [n_trace] power-of-two row scales (only when scaled)
     bool symmetric = false; // every A_e is symmetric to rounding: S_e is stored packed (half the bytes per application)
     // device arrays
     int64_t *d_block_off = nullptr; // [n_elem+1] dense offsets
@@ -216,6 +218,7 @@ int sys_apply_schur(const mfv2d_system *s, const double *t_in, double *t_out, co
 int sys_schur_diagonal(const mfv2d_system *s, double *out);
 int sys_dot_device(const mfv2d_system *s, long long n, const double *x, const double *y, const double *w, double *d_result);
 int sys_require_interface(const mfv2d_system *s);
+int sys_scale_rows(const mfv2d_system *s, double *v, bool inverse);
 bool sys_use_peers(const mfv2d_system *s);
 int read_scalars(mfv2d_ctx *ctx, const double *d, int n, double *h);
 void sys_release_peers(mfv2d_system *s);

@@ -289,6 +289,30 @@ def solve_schur_iterative(system: LinearSystem, rhs, constraints, convergence: C
     return x, lam, res.value, it.value
 
 
+def solve_schur_bicgstab(system: LinearSystem, rhs, constraints, convergence: ConvergenceSettings, precondition=True):
+    """The Schur-complement solve for NON-symmetric element blocks (advection terms): BiCGStab on ``N A^-1 N^T`` on the
+    device, then the back substitution.  Same arguments and return value as :func:`solve_schur_iterative`; the reference
+    has no iterative solver for such systems (production path: SuperLU, python/mfv2d/solve_system_2d.py:258-282)."""
+    if isinstance(rhs, _SystemVector):
+        xd, ld, r, i = solve_schur_bicgstab(system, rhs.data, constraints.data, convergence, precondition)
+        return DenseVector.__new__(DenseVector)._init(system, xd), TraceVector.__new__(TraceVector)._init(system, ld), r, i
+    if isinstance(rhs, DeviceArray):
+        x, lam = system.ctx.empty(system.n_dense), system.ctx.empty(system.n_trace)
+    else:
+        rhs = np.ascontiguousarray(rhs, np.float64)
+        constraints = np.ascontiguousarray(constraints, np.float64)
+        x, lam = np.empty(system.n_dense), np.empty(system.n_trace)
+    res, it = C.c_double(), C.c_int()
+    check(
+        lib().mfv2d_cuda_solve_schur_bicgstab(system.handle, addr(rhs), addr(constraints), int(convergence.maximum_iterations),
+                                              float(convergence.absolute_tolerance), float(convergence.relative_tolerance),
+                                              int(bool(precondition)), addr(x), addr(lam), C.byref(res), C.byref(it),
+                                              space_of(rhs, constraints, x, lam)),
+        system.ctx.handle,
+    )
+    return x, lam, res.value, it.value
+
+
 def solve_pcg_iterative(system: LinearSystem, rhs, constraints, convergence: ConvergenceSettings):
     """python/mfv2d/solving.py:634-684: PCG on the saddle system with the block-Jacobi ``A^-1 (+) I``."""
     if isinstance(rhs, _SystemVector):
@@ -470,3 +494,68 @@ def compute_linear_system(form_specs, expressions, batch, constraints, n_trace: 
     out = batch.ctx.empty((batch.n, ne, ne))
     M.compute_element_matrices(form_specs, expressions, batch, degrees_of_freedom, field_values, out=out)
     return LinearSystem(out, constraints, n_trace, ctx=batch.ctx)
+
+
+class ConstraintConditioner:
+    """Well-conditioned replacement of ill-scaled constraint rows (the hanging-side rows of non-conforming meshes).
+
+    The reference expresses a hanging side through inverse interpolation matrices (``np.linalg.inv``,
+    python/mfv2d/continuity.py:256-265); between elements whose orders differ by several units those rows carry coefficients
+    up to 1e8 and are nearly linearly dependent, which its direct solver (SuperLU with partial pivoting) absorbs but which
+    puts cond(N A^-1 N^T) beyond 1e16 for any Krylov method on the multipliers.  Rows that couple the same set of elements
+    span the same constraint space as any basis of their row space, so each such group ``B`` (g x c) is replaced by the
+    orthonormal rows ``Q^T`` of its QR factorisation ``B^T = Q R``:  ``B = R^T Q^T``.  The solution ``x`` is unchanged;
+    right-hand sides and multipliers map as ``phi' = R^-T phi`` and ``lambda = R^-1 lambda'``.  Groups whose rows are plain
+    conforming rows (two entries of magnitude one) are left untouched, bit for bit."""
+
+    def __init__(self, row, col, val, n_trace: int, offsets):
+        row, col, val = np.asarray(row, np.int64), np.asarray(col, np.int64), np.asarray(val, np.float64)
+        offsets = np.asarray(offsets, np.int64)
+        elem = np.searchsorted(offsets, col, side="right") - 1
+        starts = np.searchsorted(row, np.arange(n_trace + 1))
+        keys: dict = {}
+        plain = np.ones(n_trace, bool)
+        for i in range(n_trace):
+            lo, hi = starts[i], starts[i + 1]
+            keys.setdefault(tuple(np.unique(elem[lo:hi]).tolist()), []).append(i)
+            plain[i] = hi - lo <= 2 and bool(np.all(np.abs(val[lo:hi]) == 1.0))
+        new_rows, new_cols, new_vals = [], [], []
+        self.blocks: list[tuple[np.ndarray, np.ndarray]] = []  # (rows of the group, R^T)
+        keep = np.ones(row.size, bool)
+        for rows_g in keys.values():
+            rows_g = np.array(rows_g)
+            if np.all(plain[rows_g]):
+                continue
+            sel = np.concatenate([np.arange(starts[i], starts[i + 1]) for i in rows_g])
+            keep[sel] = False
+            cols_g, inv = np.unique(col[sel], return_inverse=True)
+            local_row = np.concatenate([np.full(starts[i + 1] - starts[i], k) for k, i in enumerate(rows_g)])
+            B = np.zeros((rows_g.size, cols_g.size))
+            B[local_row, inv] = val[sel]
+            Q, R = np.linalg.qr(B.T)  # B^T = Q R
+            if np.min(np.abs(np.diag(R))) <= 1e-13 * np.max(np.abs(np.diag(R))):
+                raise ValueError("a group of constraint rows is rank deficient")
+            self.blocks.append((rows_g, R.T.copy()))
+            rr, cc = np.nonzero(np.abs(Q.T) > 1e-15)
+            new_rows.append(rows_g[rr])
+            new_cols.append(cols_g[cc])
+            new_vals.append(Q.T[rr, cc])
+        r = np.concatenate([row[keep]] + new_rows)
+        c = np.concatenate([col[keep]] + new_cols)
+        v = np.concatenate([val[keep]] + new_vals)
+        o = np.lexsort((c, r))
+        self.row, self.col, self.val = r[o], c[o], v[o]
+
+    def rhs(self, phi: np.ndarray) -> np.ndarray:
+        """phi' = R^-T phi"""
+        out = np.array(phi, np.float64)
+        for rows_g, rt in self.blocks:
+            out[rows_g] = np.linalg.solve(rt, out[rows_g])
+        return out
+
+    def multipliers(self, lam: np.ndarray) -> np.ndarray:
+        """lambda = R^-1 lambda'"""
+        out = np.array(lam, np.float64)
+        for rows_g, rt in self.blocks:
+            out[rows_g] = np.linalg.solve(rt.T, out[rows_g])
+        return out

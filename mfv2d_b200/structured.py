@@ -39,55 +39,230 @@ def form_sizes(form_orders, p: int) -> np.ndarray:
     return np.array([size[int(o)] for o in form_orders], np.int64)
 
 
-def continuity_constraints_1form(nh: int, nv: int, p: int, form_orders) -> tuple[np.ndarray, np.ndarray, np.ndarray, int]:
-    """Continuity rows of the 1-form unknowns on the conforming ``nh x nv`` mesh of uniform order p, in
-    the reference's order (continuity.py:650-683, 498-508): for each 1-form of the system, first the
-    interior horizontal lines (line index ``nh*j + i``, j = 1..nv-1), then the interior vertical lines
-    (``j*(nh+1) + i``, i = 1..nh-1); ``p`` rows per line.
-
-    Returns COO arrays (row, global dense column, value) sorted by (row, column) and the row count."""
+def _form_offsets(form_orders, p: int):
     sizes = form_sizes(form_orders, p)
-    offs = np.concatenate([[0], np.cumsum(sizes)])
-    ne = int(offs[-1])
-    nh_edges = p * (p + 1)
+    return np.concatenate([[0], np.cumsum(sizes)]), int(sizes.sum())
+
+
+def _interior_lines(nh: int, nv: int):
+    """(first element, second element, horizontal?) of every interior line in the reference's line order: horizontal lines
+    ``nh*j + i`` (j = 1..nv-1; first = element below, its TOP side; second = element above, its BOTTOM side), then vertical
+    lines ``j*(nh+1) + i`` (i = 1..nh-1; first = element to the right, its LEFT side; second = element to the left, its
+    RIGHT side) - the ``dual_line.begin / end`` order of continuity.py:650-683 on ``unit_square_mesh``."""
+    jj, ii = np.meshgrid(np.arange(1, nv), np.arange(nh), indexing="ij")
+    h1, h2 = (ii + nh * (jj - 1)).ravel(), (ii + nh * jj).ravel()
+    jj, ii = np.meshgrid(np.arange(nv), np.arange(1, nh), indexing="ij")
+    v1, v2 = (ii + nh * jj).ravel(), (ii - 1 + nh * jj).ravel()
+    return (h1, h2), (v1, v2)
+
+
+def continuity_constraints(nh: int, nv: int, p: int, form_orders) -> tuple[np.ndarray, np.ndarray, np.ndarray, int]:
+    """All continuity rows of ``connect_elements`` (python/mfv2d/continuity.py:610-759) on the conforming ``nh x nv`` mesh of
+    uniform order ``p``, in the reference's order: for every unknown form in turn - a 0-form contributes its edge rows
+    (``p - 1`` interior nodes per interior line, coefficient +1 on the first element and -1 on the second, second side
+    traversed in reverse, :491-519) followed by its corner chains (one row per consecutive pair of the elements around a
+    mesh node in the order top-left, bottom-right, bottom-left, top-right, :321-368, 689-716); a 1-form contributes ``p``
+    rows per interior line with sign ``sgn1 * sgn2`` (:498-501); 2-forms contribute nothing.
+
+    Returns COO arrays (row, global dense column, value) sorted by (row, column) and the row count; pinned bit for bit to
+    the reference's output in tests/golden/constraints.npz."""
+    offs, ne = _form_offsets(form_orders, p)
+    (h1, h2), (v1, v2) = _interior_lines(nh, nv)
+    np1 = p + 1
     rows, cols, vals = [], [], []
     row0 = 0
-    k = np.arange(p)[::-1]  # DoFs along a side are traversed in reverse
+
+    def add(n_rows, e_first, d_first, e_second, d_second):
+        nonlocal row0
+        r = row0 + np.arange(n_rows)
+        rows.extend([r, r])
+        cols.extend([e_first * ne + d_first, e_second * ne + d_second])
+        vals.extend([np.full(n_rows, 1.0), np.full(n_rows, -1.0)])
+        row0 += n_rows
+
     for f, order in enumerate(form_orders):
-        if int(order) != FORM_ORDER_1:
-            continue
-        o1 = int(offs[f])
-        # horizontal interior lines: element below (top side, +1) and element above (bottom side, -1)
-        jj, ii = np.meshgrid(np.arange(1, nv), np.arange(nh), indexing="ij")
-        e_below = (ii + nh * (jj - 1)).ravel()
-        e_above = (ii + nh * jj).ravel()
-        n_l = e_below.size
-        r = row0 + (np.arange(n_l)[:, None] * p + np.arange(p)[None, :])
-        top = o1 + p * p + k  # h(p, c)
-        bot = o1 + k  # h(0, c)
-        rows += [r.ravel(), r.ravel()]
-        cols += [(e_below[:, None] * ne + top[None, :]).ravel(), (e_above[:, None] * ne + bot[None, :]).ravel()]
-        vals += [np.full(n_l * p, 1.0), np.full(n_l * p, -1.0)]
-        row0 += n_l * p
-        # vertical interior lines: element on the right (left side, +1) and on the left (right side, -1)
-        jj, ii = np.meshgrid(np.arange(nv), np.arange(1, nh), indexing="ij")
-        e_right = (ii + nh * jj).ravel()
-        e_left = (ii - 1 + nh * jj).ravel()
-        n_l = e_right.size
-        r = row0 + (np.arange(n_l)[:, None] * p + np.arange(p)[None, :])
-        left = o1 + nh_edges + (p + 1) * k  # v(r, 0)
-        right = o1 + nh_edges + (p + 1) * k + p  # v(r, p)
-        rows += [r.ravel(), r.ravel()]
-        cols += [(e_right[:, None] * ne + left[None, :]).ravel(), (e_left[:, None] * ne + right[None, :]).ravel()]
-        vals += [np.full(n_l * p, 1.0), np.full(n_l * p, -1.0)]
-        row0 += n_l * p
+        o = int(offs[f])
+        order = int(order)
+        if order == FORM_ORDER_0:
+            c = np.arange(p - 1, 0, -1)  # interior nodes of a side, traversed counter-clockwise on the first element
+            if c.size:
+                # horizontal lines: top side of the element below, node (p, c); bottom side of the element above, node (0, c)
+                add(h1.size * c.size, np.repeat(h1, c.size), np.tile(o + p * np1 + c, h1.size), np.repeat(h2, c.size), np.tile(o + c, h1.size))
+                # vertical lines: left side of the right element, node (r, 0); right side of the left element, node (r, p)
+                add(v1.size * c.size, np.repeat(v1, c.size), np.tile(o + c * np1, v1.size), np.repeat(v2, c.size), np.tile(o + c * np1 + p, v1.size))
+            # corner chains, mesh nodes in index order j*(nh+1) + i: elements around the node in the order
+            # top-left, bottom-right, bottom-left, top-right, each with ITS corner DoF at the node
+            jj, ii = np.meshgrid(np.arange(nv + 1), np.arange(nh + 1), indexing="ij")
+            jj, ii = jj.ravel(), ii.ravel()
+            cand = [  # (element column, element row, local DoF)
+                (ii - 1, jj, p),  # element up-left of the node: its bottom-right corner
+                (ii, jj - 1, p * np1),  # element down-right: its top-left corner
+                (ii - 1, jj - 1, np1 * np1 - 1),  # element down-left: its top-right corner
+                (ii, jj, 0),  # element up-right: its bottom-left corner
+            ]
+            elem = np.stack([np.where((ci >= 0) & (ci < nh) & (cj >= 0) & (cj < nv), ci + nh * cj, -1) for ci, cj, _ in cand], axis=1)
+            dof = np.array([d for _, _, d in cand])
+            present = elem >= 0
+            # compact every node's list to the front (stable), then chain consecutive pairs
+            order_idx = np.argsort(~present, axis=1, kind="stable")
+            elem_s = np.take_along_axis(elem, order_idx, axis=1)
+            dof_s = dof[order_idx]
+            count = present.sum(axis=1)
+            node_ids = np.flatnonzero(count > 1)
+            reps = count[node_ids] - 1
+            n_rows = int(reps.sum())
+            if n_rows:
+                node_rep = np.repeat(node_ids, reps)
+                k_in = np.arange(n_rows) - np.repeat(np.cumsum(reps) - reps, reps)
+                add(n_rows, elem_s[node_rep, k_in], o + dof_s[node_rep, k_in], elem_s[node_rep, k_in + 1], o + dof_s[node_rep, k_in + 1])
+        elif order == FORM_ORDER_1:
+            k = np.arange(p)[::-1]  # DoFs along a side are traversed in reverse
+            nh_edges = p * np1
+            # horizontal lines: top side of the element below h(p, c) (+1), bottom side of the element above h(0, c) (-1)
+            add(h1.size * p, np.repeat(h1, p), np.tile(o + p * p + k, h1.size), np.repeat(h2, p), np.tile(o + k, h1.size))
+            # vertical lines: left side of the right element v(r, 0) (+1), right side of the left element v(r, p) (-1)
+            add(v1.size * p, np.repeat(v1, p), np.tile(o + nh_edges + np1 * k, v1.size), np.repeat(v2, p), np.tile(o + nh_edges + np1 * k + p, v1.size))
     if not rows:
         return np.zeros(0, np.int64), np.zeros(0, np.int64), np.zeros(0), 0
     row = np.concatenate(rows).astype(np.int64)
     col = np.concatenate(cols).astype(np.int64)
     val = np.concatenate(vals)
-    order = np.lexsort((col, row))
-    return row[order], col[order], val[order], row0
+    order_rc = np.lexsort((col, row))
+    return row[order_rc], col[order_rc], val[order_rc], row0
+
+
+def continuity_constraints_1form(nh: int, nv: int, p: int, form_orders) -> tuple[np.ndarray, np.ndarray, np.ndarray, int]:
+    """The rows of :func:`continuity_constraints` for systems without 0-forms (kept as the historic entry point)."""
+    return continuity_constraints(nh, nv, p, form_orders)
+
+
+def gauge_constraint(n_elem: int, p: int, form_orders, form_index: int) -> tuple[np.ndarray, np.ndarray]:
+    """Columns and coefficients of ONE ``constrained_forms`` row (continuity.py:775-794): every DoF of the form in every
+    element, coefficient 1."""
+    offs, ne = _form_offsets(form_orders, p)
+    d = np.arange(int(offs[form_index]), int(offs[form_index + 1]))
+    col = (np.arange(n_elem)[:, None] * ne + d[None, :]).ravel()
+    return col.astype(np.int64), np.ones(col.size)
+
+
+def boundary_lines(nh: int, nv: int):
+    """``mesh.boundary_indices`` of ``unit_square_mesh`` as (element, side) pairs in the reference's order: bottom lines,
+    top lines, then per element row its left and right line.  Sides: 1 bottom, 2 right, 3 top, 4 left."""
+    out = [(i, 1) for i in range(nh)] + [(i + nh * (nv - 1), 3) for i in range(nh)]
+    for j in range(nv):
+        out += [(nh * j, 4), (nh - 1 + nh * j, 2)]
+    return out
+
+
+def _side_dofs(side: int, order: int, p: int) -> np.ndarray:
+    """element_boundary_dofs (python/mfv2d/mimetic2d.py:712-800) for ``order_1 == order_2 == p``."""
+    np1 = p + 1
+    if order == FORM_ORDER_1:
+        return {1: np.arange(p), 2: p * np1 + p + np.arange(p) * np1, 3: (p * p + np.arange(p))[::-1], 4: (p * np1 + np.arange(p) * np1)[::-1]}[side]
+    return {1: np.arange(np1), 2: p + np.arange(np1) * np1, 3: (np1 * p + np.arange(np1))[::-1], 4: (np.arange(np1) * np1)[::-1]}[side]
+
+
+def strong_bc_constraints(nh: int, nv: int, p: int, form_orders, form_index: int, func: Callable, corners: np.ndarray, roots: np.ndarray,
+                          rule_nodes: np.ndarray, rule_weights: np.ndarray) -> tuple[np.ndarray, np.ndarray]:
+    """Strong boundary-condition rows on the whole boundary of the structured mesh (``mesh_boundary_conditions`` /
+    ``_element_strong_boundary_condition``, python/mfv2d/boundary.py:228-498): one row per constrained DoF.
+
+    0-forms take ``func`` at the GLL nodes of the (straight) element side, a mesh node already constrained by an earlier
+    line is skipped (:455-470); 1-forms take the flux of ``func`` through each sub-edge, integrated with the 1-D rule of
+    the basis.  ``roots`` = Basis1D.roots of order p, ``rule_*`` = its IntegrationRule1D.  Returns (global dense columns,
+    values) in the reference's row order."""
+    offs, ne = _form_offsets(form_orders, p)
+    order = int(form_orders[form_index])
+    o = int(offs[form_index])
+    set_nodes = np.zeros((nv + 1, nh + 1), bool)
+    cols, vals = [], []
+    for e, side in boundary_lines(nh, nv):
+        ei, ej = e % nh, e // nh
+        p0, p1 = corners[e, side - 1], corners[e, side & 3]
+        dx, dy = (p1[0] - p0[0]) / 2, (p1[1] - p0[1]) / 2
+        xv = (p1[0] + p0[0]) / 2 + dx * roots
+        yv = (p1[1] + p0[1]) / 2 + dy * roots
+        dofs = _side_dofs(side, order, p) + o
+        if order == FORM_ORDER_0:
+            v = np.asarray(func(xv, yv), np.float64) * np.ones(p + 1)
+            # mesh nodes of the side's first / last corner (corner k of element (ei, ej): 0 BL, 1 BR, 2 TR, 3 TL)
+            node_of = [(ej, ei), (ej, ei + 1), (ej + 1, ei + 1), (ej + 1, ei)]
+            n0, n1 = node_of[side - 1], node_of[side & 3]
+            lo, hi = (1 if set_nodes[n0] else 0), (p if set_nodes[n1] else p + 1)
+            set_nodes[n0] = set_nodes[n1] = True
+            dofs, v = dofs[lo:hi], v[lo:hi]
+        else:
+            ndir = 2 * ((side & 2) >> 1) - 1
+            v = np.zeros(p)
+            for i in range(p):
+                xc = (xv[i + 1] + xv[i]) / 2 + (xv[i + 1] - xv[i]) / 2 * rule_nodes
+                yc = (yv[i + 1] + yv[i]) / 2 + (yv[i + 1] - yv[i]) / 2 * rule_nodes
+                ddx, ddy = (xv[i + 1] - xv[i]) / 2, (yv[i + 1] - yv[i]) / 2
+                normal = ndir * np.array((ddy, -ddx))
+                fv = np.asarray(func(xc, yc), np.float64)
+                v[i] = np.sum((fv[..., 0] * normal[0] + fv[..., 1] * normal[1]) * rule_weights)
+        cols.append(e * ne + dofs)
+        vals.append(v)
+    return np.concatenate(cols).astype(np.int64), np.concatenate(vals)
+
+
+def system_constraints(nh: int, nv: int, p: int, form_orders, constrained_forms=(), strong_bcs=(), corners=None, roots=None, rule_nodes=None,
+                       rule_weights=None):
+    """The whole constraint matrix of ``add_system_constraints`` (python/mfv2d/continuity.py:762-872) for a conforming
+    structured mesh, as COO over global dense columns plus the right-hand side: continuity rows, then one row per
+    ``constrained_forms`` entry ``(value, form index)``, then the strong-BC rows of ``strong_bcs`` entries
+    ``(form index, func)`` (one boundary condition per form, on the whole boundary)."""
+    row, col, val, n = continuity_constraints(nh, nv, p, form_orders)
+    rows, cols, vals, rhs = [row], [col], [val], [np.zeros(n)]
+    for value, fi in constrained_forms:
+        c, v = gauge_constraint(nh * nv, p, form_orders, fi)
+        rows.append(np.full(c.size, n, np.int64))
+        cols.append(c)
+        vals.append(v)
+        rhs.append(np.array([float(value)]))
+        n += 1
+    if strong_bcs:
+        # rows are ordered by boundary line first, by equation second (boundary.py:439-470): merge the per-form row lists
+        per_form = []
+        for fi, func in sorted(strong_bcs, key=lambda t: t[0]):
+            order = int(form_orders[fi])
+            per_line = (p + 1) if order == FORM_ORDER_0 else p
+            c, v = strong_bc_constraints(nh, nv, p, form_orders, fi, func, corners, roots, rule_nodes, rule_weights)
+            # line index of every row: 1-forms have p rows per line; 0-forms a variable number (skipped nodes)
+            if order == FORM_ORDER_1:
+                line = np.repeat(np.arange(c.size // p), p)
+            else:
+                line = np.searchsorted(np.cumsum(_bc0_counts(nh, nv, p)), np.arange(c.size), side="right")
+            per_form.append((fi, c, v, line))
+            del per_line
+        allc = np.concatenate([t[1] for t in per_form])
+        allv = np.concatenate([t[2] for t in per_form])
+        alll = np.concatenate([t[3] for t in per_form])
+        allf = np.concatenate([np.full(t[1].size, t[0]) for t in per_form])
+        seq = np.concatenate([np.arange(t[1].size) for t in per_form])
+        order_bc = np.lexsort((seq, allf, alll))
+        c, v = allc[order_bc], allv[order_bc]
+        rows.append(n + np.arange(c.size))
+        cols.append(c)
+        vals.append(np.ones(c.size))
+        rhs.append(v)
+        n += c.size
+    row, col, val = np.concatenate(rows), np.concatenate(cols), np.concatenate(vals)
+    order_rc = np.lexsort((col, row))
+    return row[order_rc], col[order_rc], val[order_rc], np.concatenate(rhs), n
+
+
+def _bc0_counts(nh: int, nv: int, p: int) -> np.ndarray:
+    """Number of 0-form strong-BC rows contributed by each boundary line (first-come ownership of the mesh nodes)."""
+    set_nodes = np.zeros((nv + 1, nh + 1), bool)
+    out = []
+    for e, side in boundary_lines(nh, nv):
+        ei, ej = e % nh, e // nh
+        node_of = [(ej, ei), (ej, ei + 1), (ej + 1, ei + 1), (ej + 1, ei)]
+        n0, n1 = node_of[side - 1], node_of[side & 3]
+        out.append(p + 1 - int(set_nodes[n0]) - int(set_nodes[n1]))
+        set_nodes[n0] = set_nodes[n1] = True
+    return np.array(out, np.int64)
 
 
 def strip_partition(nh: int, nv: int, n_ranks: int) -> list[tuple[int, int]]:

@@ -619,3 +619,103 @@ def check_multilevel(M, SV, ST, ctx, rank, world, all_gather, nh=24, nv=24, p=2,
     counts = all_gather((itj, it2))
     assert all(c == counts[0] for c in counts), counts
     return itj, it2
+
+
+def check_hp_refined(M, SV, ST, fixture="hp_refined", gate=1e-10):
+    """BASELINE.json configs[3]: the h/p-refined, non-conforming meshes of tests/golden/hp_refined*.npz (93 leaves, hanging-side
+    constraint rows with up to 26 entries - all produced by the reference).  Element matrices per (p, q) bucket, ONE
+    LinearSystem with blocks of several different sizes (the non-uniform path of system.cu), its operators against the
+    reference-assembled ones, and the Schur-complement solve (constraint groups of hanging sides re-expressed in an
+    orthonormal basis, solving.ConstraintConditioner) checked by the relative residual of the REFERENCE-assembled
+    saddle-point system.  `hp_refined` (orders 2..8) has hanging-side coefficients up to 4e8: the
+    reference's own SuperLU solution leaves 1.7e-10 there, the gate for it is therefore looser; `hp_refined_345`
+    (orders 2..5) meets north_star's 1e-10."""
+    g = golden(fixture + ".npz")
+    s = SYSTEMS["mixed_poisson_sorted"]
+    specs = specs_of(M, s)
+    k = int(g["k"])
+    orders = g["orders"][:, 0].astype(int)
+    assert np.array_equal(g["orders"][:, 0], g["orders"][:, 1])
+    mats = [None] * orders.size
+    for p in np.unique(orders):
+        idx = np.flatnonzero(orders == p)
+        batch = M.ElementBatch(make_basis(M, int(p), k), np.ascontiguousarray(g["corners"][idx]))
+        out = M.compute_element_matrices(specs, s["lhs"], batch)
+        for j, e in enumerate(idx):
+            mats[e] = out[j]
+    assert relerr(mats[0], g["mat_first"]) < TOL_MAT and relerr(mats[-1], g["mat_last"]) < TOL_MAT
+    sizes = np.array([m.shape[0] for m in mats])
+    off = np.concatenate([[0], np.cumsum(sizes)])
+    assert np.array_equal(sizes, [specs.total_size(int(p), int(p)) for p in orders]) and len(set(sizes.tolist())) >= 4
+    row = g["con_row"].astype(np.int64)
+    col = off[g["con_elem"].astype(np.int64)] + g["con_dof"].astype(np.int64)
+    o = np.lexsort((col, row))
+    row, col, val = row[o], col[o], g["con_val"][o]
+    nt = g["con_rhs"].size
+    sysm = SV.LinearSystem(mats, (row, col, val), nt)
+    assert relerr(sysm.apply_diagonal(g["x"]), g["apply_diagonal"]) < 1e-12
+    assert relerr(sysm.apply_diagonal_inverse(g["x"]), g["apply_diagonal_inverse"]) < 1e-8
+    assert relerr(sysm.apply_trace(g["x"]), g["apply_trace"]) < 1e-12
+    assert relerr(sysm.apply_trace_transpose(g["trace_in"]), g["apply_trace_transpose"]) < 1e-12
+    t = g["trace_in"]
+    composed = sysm.apply_trace(sysm.apply_diagonal_inverse(sysm.apply_trace_transpose(t)))
+    assert relerr(sysm.apply_full_trace_system(t), composed) < 1e-10
+    cond = SV.ConstraintConditioner(row, col, val, nt, off)
+    assert len(cond.blocks) > 10
+    sysc = SV.LinearSystem(mats, (cond.row, cond.col, cond.val), nt)
+    x, lam_c, res, it = SV.solve_schur_iterative(sysc, g["rhs"], cond.rhs(g["con_rhs"]), SV.ConvergenceSettings(20000, 1e300, 1e-13), precondition="jacobi")
+    lam = cond.multipliers(lam_c)
+    # residual of the REFERENCE-assembled saddle-point system (its N, its A) with our solution
+    r1 = g["rhs"] - sysm.apply_diagonal(x) - sysm.apply_trace_transpose(lam)
+    r2 = g["con_rhs"] - sysm.apply_trace(x)
+    rel = np.sqrt(r1 @ r1 + r2 @ r2) / np.sqrt(g["rhs"] @ g["rhs"] + g["con_rhs"] @ g["con_rhs"])
+    assert rel < gate, rel
+    assert relerr(x, g["sol_dense"]) < 1e-7, relerr(x, g["sol_dense"])
+    assert it < 3000, it
+    return it, rel
+
+
+def check_time_march(M, SV, ST):
+    """BASELINE.json configs[2] (slice): three trapezoidal steps of the unsteady advection-diffusion system on 8 x 8 elements
+    of order 4 against the reference's own march (tests/golden/timemarch_advdif.npz, produced by solve_system_2d): element
+    matrices with the 2/dt mass terms, BiCGStab on the (non-symmetric) Schur complement instead of SuperLU, dual <- primal
+    by the matrix-free mass apply."""
+    from mfv2d_b200 import callers as CL
+
+    g = golden("timemarch_advdif.npz")
+    raw = json.loads(str(g["codes"]))
+
+    def dec(codes):
+        out = []
+        for rowc in codes:
+            r = []
+            for blk in rowc:
+                if blk is None:
+                    r.append(None)
+                    continue
+                ops = []
+                for item in blk:
+                    item = list(item)
+                    if item[0] == 7 and isinstance(item[2], str) and item[2].startswith("fn:"):
+                        item[2] = F.FIELDS[item[2][3:]]
+                    ops.append(tuple(item))
+                r.append(tuple(ops))
+            out.append(tuple(r))
+        return tuple(out)
+
+    lhs = dec(raw["lhs"])
+    assert raw["rhs"] is None
+    p, k = int(g["order"]), int(g["k"])
+    specs = M._ElementFormSpecification(*zip(raw["form_names"], raw["form_orders"]))
+    batch = M.ElementBatch(make_basis(M, p, k), np.ascontiguousarray(g["corners"]))
+    mat0 = M.compute_element_matrices(specs, lhs, batch)[0]
+    assert relerr(mat0, g["mat0"]) < TOL_MAT
+    assert relerr(mat0, mat0.T) > 1e-3  # the advection term makes the blocks non-symmetric
+    nt = g["con_rhs"].size
+    sols, iters = CL.trapezoidal_march(specs, lhs, None, batch, (g["con_row"], g["con_col"], g["con_val"]), nt, g["con_rhs"], g["explicit"],
+                                       [raw["form_names"].index("u")], float(g["dt"]), int(g["nt"]))
+    ref = g["solutions"]
+    assert len(sols) == ref.shape[0] - 1
+    for i, s in enumerate(sols):
+        assert relerr(s, ref[i + 1]) < 1e-8, (i, relerr(s, ref[i + 1]))
+    return iters

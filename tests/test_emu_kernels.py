@@ -93,3 +93,12 @@ def test_linear_system(emu, fix, nh, nv):
 
 def test_saddle_residual_small_elements(emu):
     P.check_saddle_residual_small_elements(*emu, nh=6, nv=5, p=3)
+
+
+@pytest.mark.parametrize("fixture,gate", [("hp_refined_345", 1e-10), ("hp_refined", 2e-7)])
+def test_hp_refined(emu, fixture, gate):
+    print(P.check_hp_refined(*emu, fixture, gate))
+
+
+def test_time_march(emu):
+    print(P.check_time_march(*emu))

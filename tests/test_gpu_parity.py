@@ -96,6 +96,17 @@ def test_saddle_residual_small_elements(gpu):
     P.check_saddle_residual_small_elements(*gpu, nh=6, nv=5, p=6)
 
 
+@pytest.mark.parametrize("fixture,gate", [("hp_refined_345", 1e-10), ("hp_refined", 2e-7)])
+def test_hp_refined(gpu, fixture, gate):
+    """BASELINE.json configs[3]: non-conforming h/p-refined mesh, blocks of several sizes in one LinearSystem"""
+    P.check_hp_refined(*gpu, fixture, gate)
+
+
+def test_time_march(gpu):
+    """BASELINE.json configs[2] (slice): trapezoidal march of unsteady advection-diffusion against the reference's own march"""
+    P.check_time_march(*gpu)
+
+
 def test_empty_batches(gpu):
     M = gpu[0]
     b = P.make_basis(M, 3, 3)
