@@ -232,6 +232,12 @@ MFV2D_API int mfv2d_cuda_interprod_batch(const mfv2d_elements *elems, int start_
  * dofs[n_elem][n_k] -> out[n_elem][q][q] (0-/2-forms) or out[n_elem][q][q][2] (1-forms). */
 MFV2D_API int mfv2d_cuda_reconstruct_batch(const mfv2d_elements *elems, int form, const double *dofs,
                                            double *out, int space);
+/* Reconstruction on an arbitrary tensor grid of reference points: out[n_elem][m_eta][m_xi] (0-/2-forms) or [...][2]
+ * (1-forms) at (xi[b], eta[a]).  Replaces the per-element NumPy double loops of `reconstruct`
+ * (python/mfv2d/mimetic2d.py:1172-1279) behind reconstruct_mesh_from_solution (python/mfv2d/solve_system.py:163-271).
+ * 0-forms: plain interpolant; 1-forms: pushed forward with the Jacobian / det; 2-forms: / det. */
+MFV2D_API int mfv2d_cuda_reconstruct_grid_batch(const mfv2d_elements *elems, int form, const double *dofs, int m_xi,
+                                                const double *xi, int m_eta, const double *eta, double *out, int space);
 /* Dual degrees of freedom (L2 projection integrals) of a function given by its values at the quadrature points
  * (element_dual_dofs, python/mfv2d/mimetic2d.py:1003-1123; the per-element NumPy loops behind compute_element_rhs,
  * python/mfv2d/solve_system.py:129-160).  values[n_elem][q][q] (0-/2-forms) or [n_elem][q][q][2] (1-forms)

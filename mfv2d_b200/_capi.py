@@ -86,6 +86,7 @@ SIGNATURES = {
     "mfv2d_cuda_mass_batch": (i32, [vp, i32, i32, dp, vp, i32]),
     "mfv2d_cuda_interprod_batch": (i32, [vp, i32, i32, dp, dp, i32]),
     "mfv2d_cuda_reconstruct_batch": (i32, [vp, i32, dp, dp, i32]),
+    "mfv2d_cuda_reconstruct_grid_batch": (i32, [vp, i32, dp, i32, dp, i32, dp, dp, i32]),
     "mfv2d_cuda_dual_dofs_batch": (i32, [vp, i32, dp, dp, i32]),
     "mfv2d_cuda_projector_batch": (i32, [vp, vp, i32, i32, dp, vp, i32]),
     "mfv2d_cuda_incidence_apply": (i32, [vp, i32, i32, i32, sz, i32, dp, dp, i32]),

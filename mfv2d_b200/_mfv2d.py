@@ -411,6 +411,7 @@ class ElementBatch:
         if len(shape) != 3 or shape[1:] != (4, 2):
             raise ValueError(f"corners must have the shape (n, 4, 2), got {shape}")
         self.n = int(shape[0])
+        self._corners = corners  # kept for corners_host() (reconstruct_mesh_from_solution needs the point coordinates)
         h = C.c_void_p()
         check(
             lib().mfv2d_cuda_elements_create(self.ctx.handle, self.basis.handle, self.n, addr(corners), space_of(corners), C.byref(h)),
@@ -418,7 +419,12 @@ class ElementBatch:
         )
         self.handle = h
 
+    def corners_host(self) -> np.ndarray:
+        c = self._corners
+        return c.get() if isinstance(c, DeviceArray) else np.asarray(c)
+
     def set_corners(self, corners) -> None:
+        self._corners = corners
         check(lib().mfv2d_cuda_elements_set_corners(self.handle, addr(corners), space_of(corners)), self.ctx.handle)
 
     def __del__(self):
@@ -489,6 +495,18 @@ class ElementBatch:
         shape = (self.n, self.q, self.q, 2) if int(order) == FORM_ORDER_1 else (self.n, self.q, self.q)
         out = self._out(out, shape)
         check(lib().mfv2d_cuda_reconstruct_batch(self.handle, int(order), addr(dofs), addr(out), space_of(dofs, out)), self.ctx.handle)
+        return out
+
+    def reconstruct_grid(self, order: int, dofs, xi, eta, out=None):
+        """Values of a k-form on the tensor grid ``(eta[a], xi[b])`` of reference points from its primal DoFs ``(n, n_k)``:
+        ``(n, len(eta), len(xi))`` or ``(..., 2)`` for 1-forms (``reconstruct``, python/mfv2d/mimetic2d.py:1172-1279, for
+        all elements of the batch in one launch)."""
+        xi = np.ascontiguousarray(xi, np.float64).ravel()
+        eta = np.ascontiguousarray(eta, np.float64).ravel()
+        shape = (self.n, eta.size, xi.size, 2) if int(order) == FORM_ORDER_1 else (self.n, eta.size, xi.size)
+        out = self._out(out, shape)
+        check(lib().mfv2d_cuda_reconstruct_grid_batch(self.handle, int(order), addr(dofs), xi.size, xi.ctypes.data, eta.size, eta.ctypes.data,
+                                                      addr(out), space_of(dofs, out)), self.ctx.handle)
         return out
 
     def dual_dofs(self, order: int, function, out=None):
@@ -875,6 +893,41 @@ def compute_element_primal_from_dual(form_specs: _ElementFormSpecification, dual
     if isinstance(space_or_batch, ElementFemSpace2D):
         return compute_element_vector(form_specs, _mass_expressions(form_specs, True), space_or_batch, dual)
     return compute_element_vectors(form_specs, _mass_expressions(form_specs, True), space_or_batch, dual)
+
+
+def reconstruct(fem_space: "ElementFemSpace2D", form_order: int, dofs, xi, eta) -> np.ndarray:
+    """``reconstruct`` (python/mfv2d/mimetic2d.py:1172-1279) for points that form a tensor grid: ``xi`` of shape ``(1, m)``
+    (or ``(m,)``) and ``eta`` of shape ``(k, 1)`` as ``reconstruct_mesh_from_solution`` passes them; returns ``(k, m)`` or
+    ``(k, m, 2)``."""
+    xi, eta = np.asarray(xi, np.float64), np.asarray(eta, np.float64)
+    if not ((xi.ndim == 1 or (xi.ndim == 2 and xi.shape[0] == 1)) and (eta.ndim == 1 or (eta.ndim == 2 and eta.shape[1] == 1))):
+        raise ValueError("reconstruct: xi must be (m,) or (1, m) and eta (k,) or (k, 1) - a tensor grid of reference points")
+    c = np.ascontiguousarray(dofs, np.float64)
+    if c.ndim != 1:
+        raise ValueError("Coefficient array must be one dimensional.")
+    if c.size != _form_size(int(form_order), fem_space.batch.p, fem_space.batch.p):
+        raise ValueError("The number of degrees of freedom is not correct.")
+    return fem_space.batch.reconstruct_grid(int(form_order), c[None, :], xi.ravel(), eta.ravel())[0]
+
+
+def reconstruct_mesh_from_solution(form_specs: _ElementFormSpecification, recon_order: int | None, batch: "ElementBatch", solution):
+    """``reconstruct_mesh_from_solution`` (python/mfv2d/solve_system.py:163-271) without the graphics stack (pyvista / VTK:
+    unavailable on this box): the point coordinates and the reconstructed unknowns on the uniform
+    ``(recon_order + 1)^2`` grid of every element as plain arrays - ``{"x", "y": (n, m, m), name: (n, m, m[, 2]), ...}`` in the
+    element / row-major point order in which the reference concatenates them into its ``UnstructuredGrid``."""
+    m = (batch.p if recon_order is None else int(recon_order)) + 1
+    nodes = np.linspace(-1.0, +1.0, m)
+    sol = solution if isinstance(solution, DeviceArray) else np.ascontiguousarray(solution, np.float64).reshape(batch.n, -1)
+    host = sol.get() if isinstance(sol, DeviceArray) else sol
+    corners = batch.corners_host()
+    xi, eta = nodes[None, None, :], nodes[None, :, None]
+    w = [(1 - xi) * (1 - eta) / 4, (1 + xi) * (1 - eta) / 4, (1 + xi) * (1 + eta) / 4, (1 - xi) * (1 + eta) / 4]
+    out = {"x": sum(corners[:, k, 0][:, None, None] * w[k] for k in range(4)), "y": sum(corners[:, k, 1][:, None, None] * w[k] for k in range(4))}
+    for idx, (name, order) in enumerate(zip(form_specs.names, form_specs.orders)):
+        o = form_specs.form_offset(idx, batch.p, batch.p)
+        dofs = np.ascontiguousarray(host[:, o:o + form_specs.form_size(idx, batch.p, batch.p)])
+        out[name] = batch.reconstruct_grid(int(order), dofs, nodes, nodes)
+    return out
 
 
 # host containers of the module (src/algebra/svector.c, src/algebra/crs_matrix.c): same names as ``mfv2d._mfv2d``

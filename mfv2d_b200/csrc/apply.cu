@@ -841,6 +841,9 @@ static int plan_lower_vector_fused(mfv2d_plan *plan)
     MFV2D_TRY(mfv2d_cuda_upload(plan->ctx, plan->d_fblob, blob.data(), blob.size() * sizeof(int32_t)));
     plan->fv = fv;
     plan->vector_fused = true;
+    plan->warp_ok = true;
+    for (const FT &ft : fts)
+        plan->warp_ok = plan->warp_ok && ft.op.mode <= 2;
     if (getenv("MFV2D_PLAN_DEBUG"))
         fprintf(stderr, "[mfv2d] fused vector plan: p %d q %d, %d term groups, %d pre, %d + %d row pairs, slot %d doubles, blob %d ints\n",
                 p, q, fv.n_terms, fv.n_pre, fv.n_rowA, fv.n_rowC, fv.slot_doubles, fv.blob_ints);
@@ -1353,6 +1356,8 @@ template <int Q> static int launch_fused_q(mfv2d_ctx *ctx, FusedArgs &fa, size_t
     return MFV2D_SUCCESS;
 }
 
+#include "apply_warp.cuh"
+
 // =====================================================================================================
 // Tensor-core variant of the fused apply for q <= 8 and p <= 7 (every 1-D extent fits one 8 x 8 tile):
 // ONE WARP PER ELEMENT, no CTA barrier.  All four contractions of a term are chains of fp64
@@ -1864,6 +1869,24 @@ static int launch_apply(const mfv2d_plan *plan, const mfv2d_elements *e, const d
         doubles += ((q2 + 1) & ~1) + q * ldT + 4 + (size_t)nmax * nmax + 8;
     }
 #ifndef MFV2D_EMU
+    if (!column_mode && plan->vector_fused && plan->warp_ok && e->n > 0)
+    {
+        // warp-autonomous kernel with the tables as uniform-register operands: an experiment that did NOT pay on B200
+        // (28.6 against 39.0 GDoF/s at order 6, profiles/r2/ncu_full_element_vector_warp_poisson6_r02.csv: every DFMA needs
+        // its own ULDC, 1 721 warp instructions per element); kept behind MFV2D_APPLY_WARP=1 and covered by a parity test
+        const char *env = getenv("MFV2D_APPLY_WARP");
+        if (env && env[0] == '1')
+        {
+            FusedArgs fa{};
+            fa.a = a;
+            fa.fv = plan->fv;
+            fa.blob = plan->d_fblob;
+            fa.n_coef = plan->mcoef_off ? plan->mcoef_off : (int)plan->vcoef.size();
+            const int r = launch_warp(ctx, plan, fa, e->n);
+            if (r >= 0)
+                return r;
+        }
+    }
     if (!column_mode && plan->vector_dmma && e->n > 0)
     {
         const char *env = getenv("MFV2D_APPLY_DMMA");

@@ -156,6 +156,223 @@ __global__ void __launch_bounds__(DENSE_THREADS) inverse_kernel(int n, unsigned 
     }
 }
 
+#ifndef MFV2D_EMU
+// ---- register-resident batched inverse (n <= 128) ------------------------------------------------------------------
+// The same partially pivoted Gauss-Jordan sweep, but the working copy of the block never touches shared memory: the CTA
+// is a TI x 16 grid of threads and thread (ti, tj) keeps the entries (ti + TI a, tj + 16 b) of the block in REGISTERS for
+// the whole elimination (cyclic distribution: every thread stays busy until the last column).  Per pivot only the pivot
+// column and the two swapped rows cross the CTA through shared memory (2 n + 16 doubles), so a step is RA + CB
+// shared-memory reads for RA x CB fused multiply-adds per thread, where inverse_kernel pays three reads and a write per
+// FMA.  Row swaps are undone as a column permutation when the inverse is written out.  Pivot test of
+// decompose_pivoted_lu (src/algebra/matrix.c:454-457): |pivot| < 1e-12 -> MFV2D_PIVOT_FAILED.
+template <int TI, int RA, int CB>
+__global__ void __launch_bounds__(TI * 16) inverse_reg_kernel(int n, unsigned long long batch, const double *__restrict__ in,
+                                                             double *__restrict__ out, int32_t *__restrict__ status)
+{
+    constexpr int TJ = 16, NT = TI * TJ;
+    __shared__ double colk[TI * RA], row_a[TJ * CB], row_b[TJ * CB], cand_v[TI];
+    __shared__ int cand_i[TI], piv[TI * RA], cperm[TJ * CB], cinv[TJ * CB];
+    const int tj = threadIdx.x & 15, ti = threadIdx.x >> 4;
+    const size_t nn = (size_t)n * n;
+    for (unsigned long long blk = blockIdx.x; blk < batch; blk += gridDim.x)
+    {
+        const double *src = in + blk * nn;
+        double e[RA][CB];
+#pragma unroll
+        for (int a = 0; a < RA; ++a)
+#pragma unroll
+            for (int b = 0; b < CB; ++b)
+            {
+                const int i = ti + TI * a, j = tj + TJ * b;
+                e[a][b] = (i < n && j < n) ? src[(size_t)i * n + j] : (i == j ? 1.0 : 0.0); // identity padding
+            }
+        int bad = 0;
+        for (int k = 0; k < n; ++k)
+        {
+            const int kb = k >> 4, ktj = k & 15, ka = k / TI, kti = k - ka * TI;
+            // 1. pivot search in column k, rows >= k: the 16-lane column owners propose, everybody picks the winner
+            if (tj == ktj)
+            {
+                double best = -1.0;
+                int bi = k;
+#pragma unroll
+                for (int a = 0; a < RA; ++a)
+                {
+                    const int i = ti + TI * a;
+                    double v = 0.0;
+#pragma unroll
+                    for (int b = 0; b < CB; ++b)
+                        if (b == kb)
+                            v = fabs(e[a][b]);
+                    if (i >= k && i < n && v > best)
+                    {
+                        best = v;
+                        bi = i;
+                    }
+                }
+                cand_v[ti] = best;
+                cand_i[ti] = bi;
+            }
+            __syncthreads();
+            // every warp reduces the TI candidates by itself (no second barrier, no serial scan)
+            int r;
+            {
+                const int lane = threadIdx.x & 31;
+                double best = lane < TI ? cand_v[lane] : -2.0;
+                int bi = lane < TI ? cand_i[lane] : 0x7fffffff;
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1)
+                {
+                    const double ov = __shfl_xor_sync(0xffffffffu, best, o);
+                    const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+                    if (ov > best || (ov == best && oi < bi))
+                    {
+                        best = ov;
+                        bi = oi;
+                    }
+                }
+                if (!(best >= PIVOT_TOL))
+                    bad = 1;
+                r = bi;
+                if (threadIdx.x == 0)
+                    piv[k] = r;
+            }
+            const int ra = r / TI, rti = r - ra * TI;
+            // 2. rows k and r and the (pre-swap) pivot column through shared memory: row_a = old row r (the new pivot row),
+            //    row_b = old row k
+            if (ti == rti)
+            {
+#pragma unroll
+                for (int a = 0; a < RA; ++a)
+                    if (a == ra)
+#pragma unroll
+                        for (int b = 0; b < CB; ++b)
+                            row_a[tj + TJ * b] = e[a][b];
+            }
+            if (ti == kti)
+            {
+#pragma unroll
+                for (int a = 0; a < RA; ++a)
+                    if (a == ka)
+#pragma unroll
+                        for (int b = 0; b < CB; ++b)
+                            row_b[tj + TJ * b] = e[a][b];
+            }
+            if (tj == ktj)
+            {
+#pragma unroll
+                for (int a = 0; a < RA; ++a)
+#pragma unroll
+                    for (int b = 0; b < CB; ++b)
+                        if (b == kb)
+                            colk[ti + TI * a] = e[a][b];
+            }
+            __syncthreads();
+            if (r != k)
+            {
+                if (ti == kti)
+                {
+#pragma unroll
+                    for (int a = 0; a < RA; ++a)
+                        if (a == ka)
+#pragma unroll
+                            for (int b = 0; b < CB; ++b)
+                                e[a][b] = row_a[tj + TJ * b];
+                }
+                if (ti == rti)
+                {
+#pragma unroll
+                    for (int a = 0; a < RA; ++a)
+                        if (a == ra)
+#pragma unroll
+                            for (int b = 0; b < CB; ++b)
+                                e[a][b] = row_b[tj + TJ * b];
+                }
+            }
+            // 4. Gauss-Jordan update of the whole block in registers
+            const double ip = 1.0 / row_a[k];
+            double rk[CB];
+#pragma unroll
+            for (int b = 0; b < CB; ++b)
+                rk[b] = row_a[tj + TJ * b];
+#pragma unroll
+            for (int a = 0; a < RA; ++a)
+            {
+                const int i = ti + TI * a;
+                const double f = -colk[i == k ? r : (i == r ? k : i)] * ip; // the column was published before the swap
+#pragma unroll
+                for (int b = 0; b < CB; ++b)
+                {
+                    const int j = tj + TJ * b;
+                    double v;
+                    if (i == k)
+                        v = (j == k) ? ip : rk[b] * ip;
+                    else if (j == k)
+                        v = f;
+                    else
+                        v = fma(f, rk[b], e[a][b]);
+                    e[a][b] = v;
+                }
+            }
+            // colk / row_a / row_b are read here and rewritten after the NEXT step's first barrier; cand_* are rewritten before
+            // it, but were last read before this step's second barrier: two barriers per pivot are enough
+        }
+        // (P A)^-1 = A^-1 P^-1: the row swaps come back as column swaps in reverse order -> one permutation of the columns
+        __syncthreads();
+        for (int j = threadIdx.x; j < TJ * CB; j += NT)
+            cperm[j] = cinv[j] = j;
+        __syncthreads();
+        if (threadIdx.x == 0)
+        {
+            // cperm[c] = output position of working column c, cinv = its inverse; the swaps (k, piv[k]), k = n-1 .. 0, exchange
+            // the columns that CURRENTLY sit at positions k and piv[k]
+            for (int k = n - 1; k >= 0; --k)
+            {
+                const int r = piv[k];
+                if (r != k)
+                {
+                    const int ca = cinv[k], cb = cinv[r];
+                    cperm[ca] = r;
+                    cperm[cb] = k;
+                    cinv[k] = cb;
+                    cinv[r] = ca;
+                }
+            }
+        }
+        __syncthreads();
+        double *dst = out + blk * nn;
+#pragma unroll
+        for (int a = 0; a < RA; ++a)
+#pragma unroll
+            for (int b = 0; b < CB; ++b)
+            {
+                const int i = ti + TI * a, j = tj + TJ * b;
+                if (i < n && j < n)
+                    dst[(size_t)i * n + cperm[j]] = e[a][b];
+            }
+        if (status && threadIdx.x == 0)
+            status[blk] = bad ? MFV2D_PIVOT_FAILED : MFV2D_SUCCESS;
+        __syncthreads();
+    }
+}
+
+template <int TI, int RA, int CB>
+static int launch_inverse_reg(mfv2d_ctx *ctx, int n, size_t batch, const double *d_in, double *d_out, int32_t *d_status)
+{
+    int per_sm = 1;
+    MFV2D_CUDA_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, inverse_reg_kernel<TI, RA, CB>, TI * 16, 0));
+    if (per_sm < 1)
+        per_sm = 1;
+    size_t grid = (size_t)ctx->sm_count * per_sm;
+    if (grid > batch)
+        grid = batch;
+    inverse_reg_kernel<TI, RA, CB><<<(unsigned)grid, TI * 16, 0, ctx->stream>>>(n, (unsigned long long)batch, d_in, d_out, d_status);
+    ctx->launches++;
+    MFV2D_CUDA_CHECK(ctx, cudaGetLastError());
+    return MFV2D_SUCCESS;
+}
+#endif
+
 // Gaussian elimination with partial pivoting on the augmented system [A | B] (n x (n + nrhs)), then
 // back substitution; the working copy W has leading dimension ld = n + nrhs.
 __global__ void __launch_bounds__(DENSE_THREADS) solve_kernel(int n, int nrhs, unsigned long long batch,
@@ -284,6 +501,27 @@ int launch_inverse_batch(mfv2d_ctx *ctx, int n, size_t batch, const double *d_in
 {
     if (batch == 0 || n == 0)
         return MFV2D_SUCCESS;
+#ifndef MFV2D_EMU
+    {
+        // register-resident kernel for blocks up to 128 x 128 (MFV2D_INVERSE_REG=0: the shared-memory kernel)
+        const char *env = getenv("MFV2D_INVERSE_REG");
+        if (!(env && env[0] == '0') && d_in != d_out)
+        {
+            if (n <= 16)
+                return launch_inverse_reg<16, 1, 1>(ctx, n, batch, d_in, d_out, d_status);
+            if (n <= 32)
+                return launch_inverse_reg<16, 2, 2>(ctx, n, batch, d_in, d_out, d_status);
+            if (n <= 48)
+                return launch_inverse_reg<16, 3, 3>(ctx, n, batch, d_in, d_out, d_status);
+            if (n <= 64)
+                return launch_inverse_reg<16, 4, 4>(ctx, n, batch, d_in, d_out, d_status);
+            if (n <= 96)
+                return launch_inverse_reg<16, 6, 6>(ctx, n, batch, d_in, d_out, d_status);
+            if (n <= 128)
+                return launch_inverse_reg<32, 4, 8>(ctx, n, batch, d_in, d_out, d_status);
+        }
+    }
+#endif
     const size_t head = (size_t)2 * n + (n + 1) / 2 + 4;
     const size_t smem_full = (head + (size_t)n * n) * sizeof(double);
     const int use_smem = smem_full <= ctx->smem_optin;

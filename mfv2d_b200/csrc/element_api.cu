@@ -80,6 +80,103 @@ __global__ void reconstruct_kernel(const double *__restrict__ tab, int p, int q,
     }
 }
 
+// ---- reconstruction on an arbitrary tensor grid of reference points (reconstruct, python/mfv2d/mimetic2d.py:1172-1279) ----
+// out[e][a][b](,2) at (xi_b, eta_a).  Unlike the integrating-field variant above the 0-form carries no Jacobian factor.
+// tx / ty = [node (p+1) x m | edge p x m | points m] of the xi / eta points.
+__global__ void reconstruct_grid_kernel(const double *__restrict__ tx, int mx, const double *__restrict__ ty, int my, int p,
+                                        const double *__restrict__ corners, unsigned long long n_elem, int form,
+                                        const double *__restrict__ dofs, long long dof_stride, double *__restrict__ out)
+{
+    const int m2 = mx * my;
+    const double *node_x = tx, *edge_x = tx + (p + 1) * mx, *px = edge_x + p * mx;
+    const double *node_y = ty, *edge_y = ty + (p + 1) * my, *py = edge_y + p * my;
+    const unsigned long long total = n_elem * m2;
+    for (unsigned long long g = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; g < total;
+         g += (unsigned long long)gridDim.x * blockDim.x)
+    {
+        const unsigned long long e = g / m2;
+        const int idx = (int)(g - e * m2);
+        const int a = idx / mx, b = idx - a * mx;
+        const double *d = dofs + e * dof_stride;
+        if (form == MFV2D_FORM_ORDER_0)
+        {
+            double s = 0.0;
+            for (int i = 0; i <= p; ++i)
+            {
+                double r = 0.0;
+                for (int j = 0; j <= p; ++j)
+                    r = fma(d[i * (p + 1) + j], node_x[j * mx + b], r);
+                s = fma(r, node_y[i * my + a], s);
+            }
+            out[g] = s;
+            continue;
+        }
+        const double *c = corners + e * 8;
+        const double eta = py[a], xi = px[b];
+        const double x0 = c[0], y0 = c[1], x1 = c[2], y1 = c[3], x2 = c[4], y2 = c[5], x3 = c[6], y3 = c[7];
+        const double j00 = 0.25 * ((x1 - x0) * (1 - eta) + (x2 - x3) * (1 + eta));
+        const double j01 = 0.25 * ((y1 - y0) * (1 - eta) + (y2 - y3) * (1 + eta));
+        const double j10 = 0.25 * ((x3 - x0) * (1 - xi) + (x2 - x1) * (1 + xi));
+        const double j11 = 0.25 * ((y3 - y0) * (1 - xi) + (y2 - y1) * (1 + xi));
+        const double det = j00 * j11 - j10 * j01;
+        if (form == MFV2D_FORM_ORDER_2)
+        {
+            double s = 0.0;
+            for (int i = 0; i < p; ++i)
+            {
+                double r = 0.0;
+                for (int j = 0; j < p; ++j)
+                    r = fma(d[i * p + j], edge_x[j * mx + b], r);
+                s = fma(r, edge_y[i * my + a], s);
+            }
+            out[g] = s / det;
+        }
+        else
+        {
+            double v_eta = 0.0, v_xi = 0.0; // h part -> eta component, v part -> xi component
+            for (int i = 0; i <= p; ++i)
+            {
+                double r = 0.0;
+                for (int j = 0; j < p; ++j)
+                    r = fma(d[i * p + j], edge_x[j * mx + b], r);
+                v_eta = fma(r, node_y[i * my + a], v_eta);
+            }
+            const double *dv = d + p * (p + 1);
+            for (int i = 0; i < p; ++i)
+            {
+                double r = 0.0;
+                for (int j = 0; j <= p; ++j)
+                    r = fma(dv[i * (p + 1) + j], node_x[j * mx + b], r);
+                v_xi = fma(r, edge_y[i * my + a], v_xi);
+            }
+            out[2 * g] = (j00 * v_xi + j10 * v_eta) / det;
+            out[2 * g + 1] = (j01 * v_xi + j11 * v_eta) / det;
+        }
+    }
+}
+
+// [node (p+1) x m | edge p x m | points m] of arbitrary points: node_i = l_i(x), edge_j = -sum_{i<=j} l_i'(x) (basis.c:77-86)
+static void host_point_tables(const mfv2d_basis *basis, int m, const double *pts, std::vector<double> &tab)
+{
+    const int p = basis->p, np1 = p + 1;
+    std::vector<double> val((size_t)m * np1), der((size_t)m * np1);
+    host_lagrange(np1, basis->roots.data(), m, pts, val.data());
+    host_dlagrange(np1, basis->roots.data(), m, pts, der.data());
+    tab.assign((size_t)(2 * p + 2) * m, 0.0);
+    for (int k = 0; k < m; ++k)
+    {
+        double acc = 0.0;
+        for (int i = 0; i < np1; ++i)
+        {
+            tab[(size_t)i * m + k] = val[(size_t)k * np1 + i];
+            acc -= der[(size_t)k * np1 + i];
+            if (i < p)
+                tab[(size_t)(np1 + i) * m + k] = acc;
+        }
+        tab[(size_t)(2 * p + 1) * m + k] = pts[k];
+    }
+}
+
 static int launch_reconstruct(const mfv2d_elements *e, int form, const double *d_dofs, long long dof_stride, double *d_out)
 {
     mfv2d_ctx *ctx = e->ctx;
@@ -306,6 +403,53 @@ int mfv2d_cuda_reconstruct_batch(const mfv2d_elements *e, int form, const double
     else
         stage_abort(&o);
     stage_abort(&in);
+    return r;
+}
+
+int mfv2d_cuda_reconstruct_grid_batch(const mfv2d_elements *e, int form, const double *dofs, int m_xi, const double *xi, int m_eta,
+                                      const double *eta, double *out, int space)
+{
+    mfv2d_ctx *ctx = e->ctx;
+    const int p = e->basis->p;
+    const int nk = form_size(form, p);
+    if (nk < 0)
+        return mfv2d_fail(ctx, MFV2D_BAD_ENUM, "reconstruct_grid_batch: invalid form order %d", form);
+    if (m_xi < 1 || m_eta < 1 || !xi || !eta)
+        return mfv2d_fail(ctx, MFV2D_BAD_ARGUMENT, "reconstruct_grid_batch: at least one point per direction");
+    if (e->n == 0)
+        return MFV2D_SUCCESS;
+    std::vector<double> tx, ty;
+    host_point_tables(e->basis, m_xi, xi, tx);
+    host_point_tables(e->basis, m_eta, eta, ty);
+    double *d_tab = nullptr;
+    MFV2D_TRY(mfv2d_cuda_malloc(ctx, (tx.size() + ty.size()) * sizeof(double), (void **)&d_tab));
+    int r = mfv2d_cuda_upload(ctx, d_tab, tx.data(), tx.size() * sizeof(double));
+    if (!r)
+        r = mfv2d_cuda_upload(ctx, d_tab + tx.size(), ty.data(), ty.size() * sizeof(double));
+    const size_t per = (size_t)m_xi * m_eta * (form == MFV2D_FORM_ORDER_1 ? 2 : 1);
+    Staged in, o;
+    if (!r)
+        r = stage_in(ctx, dofs, e->n * nk * sizeof(double), space, &in);
+    if (!r)
+        r = stage_out_alloc(ctx, out, e->n * per * sizeof(double), space, &o);
+    if (!r)
+    {
+        size_t blocks = (e->n * m_xi * m_eta + 127) / 128;
+        if (blocks > (size_t)ctx->sm_count * 32)
+            blocks = (size_t)ctx->sm_count * 32;
+        MFV2D_LAUNCH(reconstruct_grid_kernel, (unsigned)blocks, 128, 0, ctx->stream, (const double *)d_tab, m_xi,
+                     (const double *)(d_tab + tx.size()), m_eta, p, (const double *)e->d_corners, (unsigned long long)e->n, form,
+                     (const double *)in.dev, (long long)nk, (double *)o.dev);
+        ctx->launches++;
+        if (cudaGetLastError() != cudaSuccess)
+            r = mfv2d_fail(ctx, MFV2D_CUDA_ERROR, "reconstruct_grid kernel launch failed");
+    }
+    if (!r)
+        r = stage_finish(&o);
+    else
+        stage_abort(&o);
+    stage_abort(&in);
+    mfv2d_cuda_free(ctx, d_tab);
     return r;
 }
 

@@ -237,6 +237,7 @@ struct mfv2d_plan
     int32_t *d_fblob = nullptr;
 
     // tensor-core (fp64 DMMA) vector path for q <= 8, p <= 7: one warp per element (apply.cu)
+    bool warp_ok = false; // every fused term is a mass term (modes 0-2): the warp-autonomous kernel applies (apply_warp.cuh)
     bool vector_dmma = false;
     int dm_terms = 0, dm_off_terms = 0, dm_off_gtab = 0, dm_off_ltab = 0, dm_off_otab = 0, dm_off_dtab = 0, dm_blob_ints = 0;
     int dm_warp_doubles = 0, dm_off_ys = 0, dm_off_outv = 0; // per-warp staging: x | zero cell | y | term output

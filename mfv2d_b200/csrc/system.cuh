@@ -34,9 +34,11 @@ __device__ __forceinline__ unsigned long long peer_load_flag(const unsigned long
     asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
     return v;
 }
+// the flag stores follow ONE peer_fence() (fence.sys + relaxed store = release pattern); a st.release.sys per peer would
+// serialise one NVLink round trip per rank (measured: +47 us per iteration on 8 GPUs)
 __device__ __forceinline__ void peer_store_flag(unsigned long long *p, unsigned long long v)
 {
-    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+    asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 __device__ __forceinline__ double peer_load(const double *p) { return __ldcg(p); } // written by another GPU: never from L1
 __device__ __forceinline__ void peer_backoff() { __nanosleep(64); }

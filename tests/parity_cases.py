@@ -719,3 +719,51 @@ def check_time_march(M, SV, ST):
     for i, s in enumerate(sols):
         assert relerr(s, ref[i + 1]) < 1e-8, (i, relerr(s, ref[i + 1]))
     return iters
+
+
+def check_reconstruct_grid(M, p=4, k=2):
+    """reconstruct (python/mfv2d/mimetic2d.py:1172-1279) on tensor grids of arbitrary reference points, restated here with
+    numpy straight from the formulas (Lagrange values for nodal factors, minus the running sum of derivatives for edge
+    factors, push-forward with the Jacobian), and reconstruct_mesh_from_solution's arrays."""
+    rng = np.random.default_rng(12)
+    ob = O.basis(p, p + k + 1)
+    roots = O.gll(p + 1)[0]
+    xi, eta = np.linspace(-1, 1, 7), np.array([-0.9, -0.2, 0.35, 1.0])
+    batch = M.ElementBatch(make_basis(M, p, k), np.ascontiguousarray(F.QUADS))
+    nx, ny = O.lagrange1d(roots, xi), O.lagrange1d(roots, eta)  # (m, p+1)
+    ex, ey = -np.cumsum(O.dlagrange1d(roots, xi), axis=1)[:, :p], -np.cumsum(O.dlagrange1d(roots, eta), axis=1)[:, :p]
+    for order, nk in ((1, (p + 1) ** 2), (2, 2 * p * (p + 1)), (3, p * p)):
+        dofs = rng.standard_normal((F.QUADS.shape[0], nk))
+        got = batch.reconstruct_grid(order, dofs, xi, eta)
+        for e, quad in enumerate(F.QUADS):
+            c = dofs[e]
+            if order == 1:
+                ref = np.einsum("ij,ai,bj->ab", c.reshape(p + 1, p + 1), ny, nx)
+            else:
+                x0, y0, x1, y1, x2, y2, x3, y3 = quad.ravel()
+                X, E = xi[None, :], eta[:, None]
+                j00 = 0.25 * ((x1 - x0) * (1 - E) + (x2 - x3) * (1 + E)) + 0 * X
+                j01 = 0.25 * ((y1 - y0) * (1 - E) + (y2 - y3) * (1 + E)) + 0 * X
+                j10 = 0.25 * ((x3 - x0) * (1 - X) + (x2 - x1) * (1 + X)) + 0 * E
+                j11 = 0.25 * ((y3 - y0) * (1 - X) + (y2 - y1) * (1 + X)) + 0 * E
+                det = j00 * j11 - j10 * j01
+                if order == 3:
+                    ref = np.einsum("ij,ai,bj->ab", c.reshape(p, p), ey, ex) / det
+                else:
+                    v_eta = np.einsum("ij,ai,bj->ab", c[: p * (p + 1)].reshape(p + 1, p), ny, ex)
+                    v_xi = np.einsum("ij,ai,bj->ab", c[p * (p + 1):].reshape(p, p + 1), ey, nx)
+                    ref = np.stack((v_xi * j00 + v_eta * j10, v_xi * j01 + v_eta * j11), axis=-1) / det[..., None]
+            assert relerr(got[e], ref) < 1e-12, (order, e, relerr(got[e], ref))
+        # the per-element entry point with the argument shapes reconstruct_mesh_from_solution uses
+        sp = M.ElementFemSpace2D(make_basis(M, p, k), np.ascontiguousarray(F.QUADS[4]))
+        one = M.reconstruct(sp, order, dofs[4], xi[None, :], eta[:, None])
+        assert np.array_equal(one, got[4])
+    # at the quadrature points the grid variant agrees with the integrating-field reconstruction up to its Jacobian factor
+    dofs = rng.standard_normal((F.QUADS.shape[0], p * p))
+    assert relerr(batch.reconstruct_grid(3, dofs, ob.pnts, ob.pnts), batch.reconstruct(3, dofs)) < 1e-12
+    specs = M._ElementFormSpecification(("q", 2), ("u", 3))
+    sol = rng.standard_normal((F.QUADS.shape[0], specs.total_size(p, p)))
+    grid = M.reconstruct_mesh_from_solution(specs, 5, batch, sol)
+    assert grid["x"].shape == (F.QUADS.shape[0], 6, 6) and grid["q"].shape == (F.QUADS.shape[0], 6, 6, 2) and grid["u"].shape == grid["x"].shape
+    assert np.allclose(grid["x"][:, 0, 0], F.QUADS[:, 0, 0]) and np.allclose(grid["y"][:, -1, -1], F.QUADS[:, 2, 1])
+    assert relerr(grid["u"], batch.reconstruct_grid(3, np.ascontiguousarray(sol[:, 2 * p * (p + 1):]), np.linspace(-1, 1, 6), np.linspace(-1, 1, 6))) == 0.0

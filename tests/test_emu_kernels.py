@@ -102,3 +102,7 @@ def test_hp_refined(emu, fixture, gate):
 
 def test_time_march(emu):
     print(P.check_time_march(*emu))
+
+
+def test_reconstruct_grid(emu):
+    P.check_reconstruct_grid(emu[0])

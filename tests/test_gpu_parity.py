@@ -102,6 +102,18 @@ def test_hp_refined(gpu, fixture, gate):
     P.check_hp_refined(*gpu, fixture, gate)
 
 
+def test_reconstruct_grid(gpu):
+    P.check_reconstruct_grid(gpu[0])
+
+
+def test_apply_warp_kernel(gpu, monkeypatch):
+    """the warp-autonomous apply kernel (apply_warp.cuh; opt-in, slower than the CTA-phase kernel on B200) stays parity-green"""
+    monkeypatch.setenv("MFV2D_APPLY_WARP", "1")
+    P.check_matrix_vector_consistency(gpu[0], "mixed_poisson", 6, 3)
+    P.check_matrix_vector_consistency(gpu[0], "stokes", 4, 3)
+    P.check_matrix_vector_consistency(gpu[0], "direct_poisson", 5, 3)
+
+
 def test_time_march(gpu):
     """BASELINE.json configs[2] (slice): trapezoidal march of unsteady advection-diffusion against the reference's own march"""
     P.check_time_march(*gpu)
