@@ -41,10 +41,32 @@ def _check_array(a, ndim: int | None, name: str, dtype=np.float64) -> np.ndarray
 # =============================================================================================
 # polynomials (src/polynomials/*.c)
 # =============================================================================================
-def compute_gll(order: int, max_iter: int = 10, tol: float = 1e-15) -> tuple[np.ndarray, np.ndarray]:
+class GLLCache:
+    """Cache of Gauss-Lobatto rules (src/polynomials/gauss_lobatto.c:273-348, 386-452): one entry per order with the tolerance
+    it was computed to; an entry serves every request whose tolerance is not larger than the recorded one (:273-294)."""
+
+    def __init__(self):
+        self._entries: dict[int, tuple[float, np.ndarray, np.ndarray]] = {}
+
+    def clear(self) -> None:
+        self._entries.clear()
+
+    def usage(self) -> tuple[tuple[int, float], ...]:
+        return tuple((o, t) for o, (t, _, _) in sorted(self._entries.items()))
+
+
+DEFAULT_GLL_CACHE = GLLCache()
+
+
+def compute_gll(order: int, max_iter: int = 10, tol: float = 1e-15, cache: GLLCache | None = DEFAULT_GLL_CACHE) -> tuple[np.ndarray, np.ndarray]:
     """Gauss-Lobatto-Legendre nodes and weights of ``order + 1`` points
     (src/polynomials/gauss_lobatto.c:163-271; order 0 gives x = 0, w = 2, :251-256)."""
     order = int(order)
+    if cache is not None and not isinstance(cache, GLLCache):
+        raise TypeError("cache must be a GLLCache or None")
+    if cache is not None and order in cache._entries and cache._entries[order][0] >= tol and max_iter >= 0 and tol >= 0:
+        _, cx, cw = cache._entries[order]
+        return cx.copy(), cw.copy()
     if order < 0:
         raise ValueError(f"Order must be non-negative, but was given as {order}.")
     if max_iter < 0:
@@ -60,6 +82,8 @@ def compute_gll(order: int, max_iter: int = 10, tol: float = 1e-15) -> tuple[np.
         warnings.warn(f"Not all Gauss-Lobatto nodes converged in {max_iter} iterations to tolerance {tol}", RuntimeWarning)
     else:
         check(rc)
+    if cache is not None:
+        cache._entries[order] = (float(tol), x.copy(), w.copy())
     return x, w
 
 
@@ -198,7 +222,12 @@ class _ElementFormSpecification:
     """Names and orders of the unknown forms of an element system; DoF layout = concatenation of the
     forms in this order (src/evaluation/forms.c:47-72)."""
 
-    def __init__(self, *specs: tuple[str, int]):
+    def __new__(cls, *specs: tuple[str, int]):
+        # like the extension type, everything happens in __new__ (src/evaluation/forms.c:150-260): the reference's own subclass
+        # ElementFormSpecification passes converted arguments to super().__new__ (python/mfv2d/system.py:21-24)
+        self = super().__new__(cls)
+        if not specs:
+            raise TypeError("At least one form specification is required.")
         forms = []
         for s in specs:
             if not isinstance(s, tuple) or len(s) != 2:
@@ -206,6 +235,8 @@ class _ElementFormSpecification:
             name, order = s
             if not isinstance(name, str):
                 raise TypeError("Form name must be a string.")
+            if len(name.encode()) > 31:  # MAXIMUM_FORM_NAME_LENGTH (src/evaluation/forms.c:199)
+                raise ValueError(f"Form name {name!r} is longer than 31 bytes.")
             order = int(order)
             if order < FORM_ORDER_0 or order > FORM_ORDER_2:
                 raise ValueError(f"Invalid form order: {order}")
@@ -214,6 +245,7 @@ class _ElementFormSpecification:
         if len(set(names)) != len(names):
             raise ValueError("Form names must be unique.")
         self._forms = tuple(forms)
+        return self
 
     @property
     def orders(self) -> tuple[int, ...]:
@@ -720,7 +752,8 @@ def compute_integrating_fields(fem_space: ElementFemSpace2D, form_specs: _Elemen
                 raise ValueError(f"Field callable returned the shape {v.shape}, expected {want}.")
             out.append(np.ascontiguousarray(v))
         else:
-            idx = int(info)
+            # the name of an unknown (bytecode.c:131-199 resolves INTERPROD fields the same way) or its index
+            idx = form_specs.names.index(info) if isinstance(info, str) else int(info)
             if form_specs.orders[idx] != order:
                 raise ValueError("Field order does not match the order of the unknown it is taken from.")
             seg = np.ascontiguousarray(dofs[offs[idx] : offs[idx + 1]]).reshape(1, -1)

@@ -2,6 +2,8 @@
 // incidence application and bytecode-driven element matrices.
 #include "plan.cuh"
 
+int launch_inverse_batch(mfv2d_ctx *ctx, int n, size_t batch, const double *d_in, double *d_out, int32_t *d_status);
+
 int launch_element_matrix(const mfv2d_plan *plan, const mfv2d_elements *e, const double *const *fields, double *d_out,
                           int32_t *d_status);
 int launch_element_vector(const mfv2d_plan *plan, const mfv2d_elements *e, const double *const *fields,
@@ -524,6 +526,45 @@ int mfv2d_cuda_incidence_apply(mfv2d_ctx *ctx, int p, int kind, int right, size_
     return r;
 }
 
+// Mass matrices whose staged form does not fit into shared memory (orders >= 9 with the default integration order): the
+// one-block system (MASS form) evaluated column by column with the matrix-free kernels, then - for the inverse - the
+// batched dense inverse.  Slow path for completeness of the per-element API; the batched hot path never gets here.
+static int mass_batch_large(const mfv2d_elements *e, int form, int inverse, double *out, int32_t *status, int space)
+{
+    mfv2d_ctx *ctx = e->ctx;
+    const int32_t form_orders[1] = {form};
+    const uint8_t present[1] = {1};
+    const int32_t op_offsets[2] = {0, 1};
+    const mfv2d_op_t ops[1] = {{MFV2D_MATOP_MASS, form, 0, 0, 0.0}};
+    mfv2d_plan *plan = nullptr;
+    MFV2D_TRY(mfv2d_cuda_plan_create(ctx, e->basis, 1, form_orders, present, op_offsets, ops, 0, nullptr, &plan));
+    const size_t nk = (size_t)plan->n_total;
+    Staged o, st;
+    int r = stage_out_alloc(ctx, out, e->n * nk * nk * sizeof(double), space, &o);
+    if (!r)
+        r = stage_out_alloc(ctx, status, status ? e->n * sizeof(int32_t) : 0, space, &st);
+    if (!r)
+        r = mfv2d_cuda_element_matrix_batch(plan, e, nullptr, nullptr, (double *)o.dev, MFV2D_DEVICE);
+    if (!r && inverse)
+        r = launch_inverse_batch(ctx, (int)nk, e->n, (const double *)o.dev, (double *)o.dev, (int32_t *)st.dev);
+    else if (!r && st.dev)
+        r = mfv2d_cuda_memset(ctx, st.dev, 0, e->n * sizeof(int32_t));
+    if (!r)
+    {
+        r = stage_finish(&o);
+        const int r2 = stage_finish(&st);
+        if (!r)
+            r = r2;
+    }
+    else
+    {
+        stage_abort(&o);
+        stage_abort(&st);
+    }
+    mfv2d_cuda_plan_destroy(plan);
+    return r;
+}
+
 static int dense_batch(const mfv2d_elements *e, int dk, int inverse, int transpose, const double *field, double *out,
                        int32_t *status, int space)
 {
@@ -531,7 +572,12 @@ static int dense_batch(const mfv2d_elements *e, int dk, int inverse, int transpo
     if (e->n == 0)
         return MFV2D_SUCCESS;
     mfv2d_plan *plan = nullptr;
-    MFV2D_TRY(make_dense_plan(ctx, e->basis, dk, inverse, transpose, field ? 1 : 0, &plan));
+    {
+        const int rp = make_dense_plan(ctx, e->basis, dk, inverse, transpose, field ? 1 : 0, &plan);
+        if (rp == MFV2D_CUDA_UNSUPPORTED && dk <= DK_MASS2 && !field)
+            return mass_batch_large(e, dk - DK_MASS0 + 1, inverse, out, status, space);
+        MFV2D_TRY(rp);
+    }
     const DevDense &dd = plan->dense[0];
     const int q = e->basis->q;
     Staged f, o, st;

@@ -241,6 +241,10 @@ int mfv2d_cuda_system_peer_connect(mfv2d_system *s, const void *handles_all, siz
     MFV2D_CUDA_CHECK(ctx, cudaMemsetAsync(p, 0, 64, ctx->stream));
     pv.epoch = (unsigned long long *)p;
     pv.error = (int *)((char *)p + 32);
+    {
+        const char *dbg = getenv("MFV2D_PEER_DEBUG");
+        pv.dbg = dbg ? atoi(dbg) : 0;
+    }
     MFV2D_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
     s->peers_ready = true;
     return MFV2D_SUCCESS;

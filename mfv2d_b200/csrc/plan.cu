@@ -396,7 +396,17 @@ int plan_lower_matrix(mfv2d_plan *plan)
             lowered[b].push_back(lt);
         }
     }
-    return plan_finalize_matrix(plan, lowered, nf, nf, plan->form_offsets, plan->form_offsets);
+    const int res = plan_finalize_matrix(plan, lowered, nf, nf, plan->form_offsets, plan->form_offsets);
+    if (res == MFV2D_CUDA_UNSUPPORTED)
+    {
+        // the staged dense matrices of this (system, p, q) do not fit into shared memory (e.g. Navier-Stokes at order 8): the
+        // matrix is then evaluated column by column with the matrix-free kernels (launch_matrix_by_columns) - slower, same result
+        plan->matrix_fused = false;
+        plan->stages.clear();
+        plan->units.clear();
+        return MFV2D_SUCCESS;
+    }
+    return res;
 }
 
 namespace

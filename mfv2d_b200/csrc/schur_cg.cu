@@ -106,7 +106,7 @@ __global__ void __launch_bounds__(SYS_THREADS) cg1_gather_kernel(const CgGatherA
             }
         }
     }
-    if (wrote)
+    if (wrote && !(pv.dbg & 1))
         peer_fence(); // every writer orders its own remote stores before the CTA's ticket
     const int np = gridDim.x;
     block_reduce_store(d, a.partials);

@@ -1185,149 +1185,6 @@ int mfv2d_cuda_vec_dot(mfv2d_ctx *ctx, size_t n, const double *x, const double *
     return r;
 }
 
-// solve_pcg_iterative (python/mfv2d/solving.py:634-684) with pcg_general (:280-347): preconditioned CG on the
-// saddle-point system K = [[A, N^T], [N, 0]] with the block-Jacobi preconditioner A^-1 (+) I.  Full vectors are
-// stored as [dense | trace] so that every BLAS-1 step and dot product is one launch; the scalars are read back
-// once per dot product (this driver follows the reference's control flow, including its degeneracy test; the
-// production path is the Schur-complement CG above).
-int mfv2d_cuda_solve_pcg(mfv2d_system *s, const double *rhs, const double *phi, int max_iter, double atol, double rtol, double *x,
-                         double *lambda, double *residual, int *iterations, int space)
-{
-    mfv2d_ctx *ctx = s->ctx;
-    if (ctx->n_ranks > 1)
-        return mfv2d_fail(ctx, MFV2D_CUDA_UNSUPPORTED, "solve_pcg runs on one GPU (use solve_schur_cg for partitioned systems)");
-    const long long nd = s->n_dense, nt = s->n_trace, nf = nd + nt;
-    Staged srhs, sphi, sx, slam;
-    int r = stage_in(ctx, rhs, nd * sizeof(double), space, &srhs);
-    if (!r)
-        r = stage_in(ctx, phi, nt * sizeof(double), space, &sphi);
-    if (!r)
-        r = stage_out_alloc(ctx, x, nd * sizeof(double), space, &sx);
-    if (!r)
-        r = stage_out_alloc(ctx, lambda, nt * sizeof(double), space, &slam);
-    double *buf = nullptr;
-    if (!r)
-        r = mfv2d_cuda_malloc(ctx, (size_t)(6 * nf + 2 * nd + 8) * sizeof(double), (void **)&buf);
-    double res_mag2 = 0.0;
-    int iter_cnt = 0;
-    if (!r)
-    {
-        double *b = buf, *xs = b + nf, *res = xs + nf, *pv = res + nf, *z = pv + nf, *ap = z + nf, *t1 = ap + nf, *t2 = t1 + nd;
-        double *sc = ctx->d_scalars;
-        double h[4];
-        const unsigned gf = grid_for(ctx, nf, 256);
-        auto apply_system = [&](const double *v, double *out) -> int { // out = K v
-            MFV2D_TRY(sys_gemv(s, s->d_A, v, t1));
-            MFV2D_TRY(sys_spmv(s, nd, s->d_t_ptr, s->d_t_col, s->d_t_val, v + nd, t2));
-            if (nd)
-            {
-                MFV2D_LAUNCH(axpby_kernel, grid_for(ctx, nd, 256), 256, 0, ctx->stream, nd, 1.0, (const double *)t1, 1.0,
-                             (const double *)t2, out);
-                ctx->launches++;
-            }
-            return sys_spmv(s, nt, s->d_n_ptr, s->d_n_col, s->d_n_val, v, out + nd);
-        };
-        auto precondition = [&](const double *v, double *out) -> int { // out = (A^-1 (+) I) v
-            MFV2D_TRY(sys_gemv(s, s->d_Ainv, v, out));
-            if (nt)
-                MFV2D_CUDA_CHECK(ctx, cudaMemcpyAsync(out + nd, v + nd, nt * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream));
-            return MFV2D_SUCCESS;
-        };
-        auto dot = [&](const double *u, const double *v, double *result) -> int {
-            MFV2D_TRY(sys_dot_device(s, nf, u, v, nullptr, sc));
-            MFV2D_TRY(read_scalars(ctx, sc, 1, h));
-            *result = h[0];
-            return MFV2D_SUCCESS;
-        };
-        auto axpby = [&](double a, const double *u, double c, const double *v, double *out) {
-            MFV2D_LAUNCH(axpby_kernel, gf, 256, 0, ctx->stream, nf, a, u, c, v, out);
-            ctx->launches++;
-        };
-        do
-        {
-            cudaMemcpyAsync(b, srhs.dev, nd * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream);
-            if (nt)
-                cudaMemcpyAsync(b + nd, sphi.dev, nt * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream);
-            cudaMemsetAsync(xs, 0, nf * sizeof(double), ctx->stream);
-            // the initial guess is zero: res = rhs - K 0
-            cudaMemcpyAsync(res, b, nf * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream);
-            if ((r = precondition(res, z)))
-                break;
-            cudaMemcpyAsync(pv, z, nf * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream);
-            if ((r = dot(b, b, &res_mag2)))
-                break;
-            const double mag = sqrt(res_mag2);
-            const double tol = (mag * rtol > atol) ? atol : mag * rtol;
-            double rz = 0.0;
-            if ((r = dot(res, z, &rz)))
-                break;
-            for (iter_cnt = 0; iter_cnt < max_iter; ++iter_cnt)
-            {
-                if ((r = apply_system(pv, ap)))
-                    break;
-                double apa = 0.0;
-                if ((r = dot(ap, pv, &apa)))
-                    break;
-                if (log(fabs(apa)) - log(res_mag2) < log(1e-12)) // solving.py:331-332
-                {
-                    r = mfv2d_fail(ctx, MFV2D_UNSPECIFIED_ERROR, "System degenerated (matrix was probably not SPD).");
-                    break;
-                }
-                const double alpha = rz / apa;
-                axpby(1.0, xs, alpha, pv, xs);
-                axpby(1.0, res, -alpha, ap, res);
-                if ((r = dot(res, res, &res_mag2)))
-                    break;
-                if (res_mag2 < tol * tol)
-                    break;
-                if ((r = precondition(res, z)))
-                    break;
-                double new_rz = 0.0;
-                if ((r = dot(res, z, &new_rz)))
-                    break;
-                const double beta = new_rz / rz;
-                rz = new_rz;
-                axpby(1.0, z, beta, pv, pv);
-            }
-            if (r)
-                break;
-            if (iter_cnt == max_iter && max_iter > 0)
-                iter_cnt = max_iter - 1; // Python's loop variable after an exhausted range
-            cudaMemcpyAsync(sx.dev, xs, nd * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream);
-            if (nt)
-                cudaMemcpyAsync(slam.dev, xs + nd, nt * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream);
-            if (cudaGetLastError() != cudaSuccess)
-                r = mfv2d_fail(ctx, MFV2D_CUDA_ERROR, "PCG kernel launch failed");
-        } while (0);
-    }
-    if (!r)
-    {
-        r = stage_finish(&sx);
-        const int r2 = stage_finish(&slam);
-        if (!r)
-            r = r2;
-        if (!r)
-            r = mfv2d_cuda_synchronize(ctx);
-    }
-    else
-    {
-        stage_abort(&sx);
-        stage_abort(&slam);
-    }
-    stage_abort(&srhs);
-    stage_abort(&sphi);
-    if (buf)
-    {
-        mfv2d_cuda_synchronize(ctx);
-        mfv2d_cuda_free(ctx, buf);
-    }
-    if (residual)
-        *residual = sqrt(res_mag2);
-    if (iterations)
-        *iterations = iter_cnt;
-    return r;
-}
-
 int mfv2d_cuda_system_set_interface(mfv2d_system *s, size_t n_shared, const int64_t *shared_index, const int64_t *slot,
                                     size_t n_slots, const uint8_t *owned)
 {

@@ -22,6 +22,7 @@ struct PeerView
     unsigned char *base[MFV2D_MAX_PEERS] = {};
     unsigned long long *epoch = nullptr; // device counters [2]: exchanges of each type started by this rank
     int *error = nullptr;                // device flag: set when a wait timed out
+    int dbg = 0;                         // MFV2D_PEER_DEBUG bits (timing experiments only): 1 = no per-writer fence
 };
 #define PEER_FLAG_BYTES 512 // flags live in the first 2 * 16 * 8 = 256 bytes, the data area starts here
 #define PEER_XSCALARS 4     // scalars that ride behind the interface values

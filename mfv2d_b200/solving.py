@@ -91,6 +91,12 @@ class LinearSystem:
     ``constraints``: sequence of :class:`Constraint`, or a COO triple ``(row, col, val)`` over global
     dense columns together with ``n_trace``."""
 
+    def __new__(cls, *args, **kwargs):
+        # the reference's Python subclass builds the blocks in ITS __new__ and hands them to super().__new__
+        # (python/mfv2d/solving.py:41-97); Python then calls __init__ with the subclass's own arguments, which the
+        # five-argument form below accepts
+        return object.__new__(cls)
+
     def __init__(self, element_matrices, constraints=None, n_trace: int | None = None, *args, ctx: Context | None = None):
         if isinstance(element_matrices, (int, np.integer)):
             # the reference's own call, LinearSystem(n_elem, form_specs, orders, element_matrices, constraints)

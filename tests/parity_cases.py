@@ -580,7 +580,9 @@ def check_partitioned_solve(M, SV, ST, ctx, rank, world, all_gather, fix, nh, nv
     assert abs(it - int(g["iters"])) <= 12, (it, int(g["iters"]))
     xj, lj, _, itj = SV.solve_schur_iterative(sysm, rhs_l, phi_l, conv, precondition="jacobi")
     assert relerr(xj, g["sol_dense"][bounds[rank]:bounds[rank + 1]]) < 1e-8 and itj <= it + 4
-    it2 = None
+    # solve_pcg_iterative on the partitioned saddle-point system: device scalars, interface sums, ownership-weighted dots
+    xp, lp, _, it2 = SV.solve_pcg_iterative(sysm, rhs_l, phi_l, SV.ConvergenceSettings(5000, 1e-30, 1e-10))
+    assert relerr(xp, g["sol_dense"][bounds[rank]:bounds[rank + 1]]) < 1e-8 and relerr(lp, g["sol_trace"][P.global_rows]) < 1e-8
     # every rank took the same number of iterations (identical scalars on all ranks)
     counts = all_gather((it, itj, it2))
     assert all(c == counts[0] for c in counts), counts
