@@ -76,14 +76,17 @@ __global__ void pcg_scalar_kernel(double *__restrict__ sc, int step)
     }
 }
 
-// out = x + (s * *c) y
+// out = x + (s * *c) y.  Product and sum are rounded SEPARATELY, as in the reference's x86 build of the vector updates
+// (system_objects.c: no fused multiply-add without -mfma): this recurrence on the indefinite saddle-point system amplifies
+// rounding differences by about 100x every ten iterations, and with the same arithmetic as the reference it follows the
+// reference's trajectory for longer.
 __global__ void pcg_axpy_kernel(long long n, double *out, const double *x, const double *y, const double *c, double s, const int *__restrict__ done)
 {
     if (*done)
         return;
     const double a = s * c[0];
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
-        out[i] = fma(a, y[i], x[i]);
+        out[i] = __dadd_rn(x[i], __dmul_rn(a, y[i]));
 }
 
 extern "C" int mfv2d_cuda_solve_pcg(mfv2d_system *s, const double *rhs, const double *phi, int max_iter, double atol, double rtol, double *x,

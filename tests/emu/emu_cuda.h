@@ -237,6 +237,14 @@ enum
 {
     cudaIpcMemLazyEnablePeerAccess = 1
 };
+// separately rounded product and sum (the emulation is built without -mfma: no contraction)
+static inline double __dmul_rn(double a, double b) { return a * b; }
+static inline double __dadd_rn(double a, double b) { return a + b; }
+template <typename T> static inline cudaError_t cudaGetSymbolAddress(void **p, T &symbol)
+{
+    *p = (void *)&symbol;
+    return cudaSuccess;
+}
 static inline cudaError_t cudaIpcGetMemHandle(cudaIpcMemHandle_t *h, void *p)
 {
     memset(h, 0, sizeof *h);
