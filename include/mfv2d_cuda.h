@@ -304,6 +304,20 @@ MFV2D_API int mfv2d_cuda_inverse_batch(mfv2d_ctx *ctx, int n, size_t batch, cons
 MFV2D_API int mfv2d_cuda_solve_batch(mfv2d_ctx *ctx, int n, int nrhs, size_t batch, const double *a,
                                      const double *b, double *x, int32_t *status, int space);
 
+/* out = in^-1 for ONE definite n x n matrix (row-major) WITHOUT any device allocation.
+ *   NO COUNTERPART IN THE REFERENCE: added for callers that cannot call
+ *   cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  Same arithmetic as the
+ *   device-wide Gauss-Jordan that inverts the coarse operator of the multilevel preconditioner (no pivoting:
+ *   symmetric definite input), with its 2n doubles of scratch in a static 64 KiB device array of the library.
+ *   in, out (n*n doubles, may alias) and status (one int32: 0 or MFV2D_PIVOT_FAILED) are DEVICE pointers of the
+ *   caller; the work is queued on the context's stream and the call does not synchronise.
+ *   n > MFV2D_NOALLOC_INVERSE_MAX_N returns MFV2D_CUDA_UNSUPPORTED.  The scratch is shared by all calls on a
+ *   device: calls that overlap on the GPU race.  The first call on each device resolves the scratch address
+ *   (cudaGetSymbolAddress): make it before a graph capture starts. */
+#define MFV2D_NOALLOC_INVERSE_MAX_N 4096
+MFV2D_API int mfv2d_cuda_inverse_definite_noalloc(mfv2d_ctx *ctx, int n, const double *in, double *out,
+                                                  int32_t *status);
+
 /* =========================================================================================
  * element-block linear system (src/algebra/sparse_system.{h,c}, system_objects.c)
  * ========================================================================================= */

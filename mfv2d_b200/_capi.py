@@ -96,6 +96,7 @@ SIGNATURES = {
     "mfv2d_cuda_element_matrix_batch": (i32, [vp, vp, dp, dp, dp, i32]),
     "mfv2d_cuda_element_vector_batch": (i32, [vp, vp, dp, dp, dp, i32]),
     "mfv2d_cuda_inverse_batch": (i32, [vp, i32, sz, dp, dp, vp, i32]),
+    "mfv2d_cuda_inverse_definite_noalloc": (i32, [vp, i32, vp, vp, vp]),
     "mfv2d_cuda_solve_batch": (i32, [vp, i32, i32, sz, dp, dp, dp, vp, i32]),
     "mfv2d_cuda_system_create": (i32, [vp, sz, vp, dp, i32, sz, sz, vp, vp, dp, C.POINTER(vp)]),
     "mfv2d_cuda_system_destroy": (None, [vp]),
