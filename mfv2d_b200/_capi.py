@@ -130,6 +130,9 @@ def _use_library_for_testing(path: str) -> None:
     """Point the binding at another build of the same C-ABI.  Only tests/emu uses this (the host
     emulation of the kernels, see tests/emu/emu_cuda.h); nothing in the package calls it."""
     global _lib, _lib_path
+    if os.path.abspath(path) != os.path.abspath(LIB_PATH) and os.environ.get("MFV2D_TEST_HOOKS") != "1":
+        raise RuntimeError("only libmfv2d_cuda.so may back mfv2d_b200; another build of the C-ABI is accepted under "
+                           "MFV2D_TEST_HOOKS=1 alone (tests/conftest.py sets it; the product never does)")
     _lib = None
     _lib_path = path
     from . import runtime

@@ -5,7 +5,7 @@ python/mfv2d/examples.py:11-73) and its constraints through a recursive per-edge
 (``connect_elements``, python/mfv2d/continuity.py:610-759).  For the synthetic structured configs of
 BASELINE.json (up to 10^6 elements) those are generated here directly as flat arrays, reproducing the
 reference's leaf order, row order, DoF order and coefficients exactly (pinned against reference output
-in tests/golden/solve_*.npz and constraints_*.npz).
+in tests/golden/solve_*.npz, constraints.npz and hp_refined*.npz, each written by a committed make_golden*.py).
 """
 from __future__ import annotations
 

@@ -11,6 +11,7 @@ if ROOT not in sys.path:
 sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
 
 GOLDEN = os.path.join(ROOT, "tests", "golden")
+os.environ.setdefault("MFV2D_TEST_HOOKS", "1")  # lets _capi._use_library_for_testing load the host-emulation build
 
 
 def pytest_configure(config):

@@ -31,6 +31,7 @@ def main():
 
         import mfv2d_b200._capi as capi
 
+        os.environ.setdefault("MFV2D_TEST_HOOKS", "1")
         capi._use_library_for_testing(build())
     from oracle.ref_loader import load_ref
 

@@ -12,8 +12,9 @@ Outputs (all small, committed):
   solve_<mesh>.npz    mixed-Poisson element-block system of the reference's tests/test_solving.py:
                       corners, constraints (COO), right-hand sides, reference operator outputs and
                       the reference's solve_schur_iterative solution
-  constraints_<...>.npz  constraint rows produced by the reference's connect_elements /
-                      mesh_boundary_conditions on unit_square_mesh, for the vectorised builder
+(constraints.npz - the rows of the reference's connect_elements / add_system_constraints on unit_square_mesh for the
+vectorised builder - is written by make_golden_constraints.py, hp_refined*.npz by make_golden_hp.py,
+timemarch_advdif.npz by make_golden_timemarch.py)
 """
 from __future__ import annotations
 
