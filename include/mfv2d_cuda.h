@@ -319,6 +319,26 @@ MFV2D_API int mfv2d_cuda_inverse_definite_noalloc(mfv2d_ctx *ctx, int n, const d
                                                   int32_t *status);
 
 /* =========================================================================================
+ * error-estimation helpers (python/mfv2d/refinement.py), one launch per batch
+ * ========================================================================================= */
+/* y[e] = A[e] x[e], n row-major (rows x cols) matrices: the projector products `projector @ dofs` of
+ * refinement.py:880-886, 1158-1168 (sp.block_diag(...) @ element_solution) for every element. */
+MFV2D_API int mfv2d_cuda_batched_gemv(mfv2d_ctx *ctx, size_t n, int rows, int cols, const double *mats,
+                                      const double *x, double *y, int space);
+/* out[e] = [[A[e], L^T], [L, 0]] ((size + pad)^2 doubles each): the local systems of refinement.py:1001-1050 whose
+ * Lagrange rows L (pad x size, COO lrow/lcol/lval[nnz], HOST arrays, the same for every element) force boundary DoFs of
+ * strongly-zeroed forms to zero and pin the sum of constrained forms. */
+MFV2D_API int mfv2d_cuda_border_batch(mfv2d_ctx *ctx, size_t n, int size, int pad, const double *mats, int nnz,
+                                      const int32_t *lrow, const int32_t *lcol, const double *lval, double *out,
+                                      int space);
+/* compute_legendre_error_estimates (refinement.py:88-152, with compute_legendre_coefficients :40-85) for every element:
+ * u, err = values of the solution and of the error field at the quadrature points of elems' rule, [n][q][q] or
+ * [n][q][q][2] for 1-forms (the Euclidean norm is taken); order_1, order_2 = orders of the Legendre spectrum;
+ * out[n][2] = { sum err^2 w det , |h-refinement cost| }.  Weights and Jacobian determinants are recomputed from the corners. */
+MFV2D_API int mfv2d_cuda_legendre_estimates_batch(const mfv2d_elements *elems, int order_1, int order_2, int form,
+                                                  const double *u, const double *err, double *out, int space);
+
+/* =========================================================================================
  * element-block linear system (src/algebra/sparse_system.{h,c}, system_objects.c)
  * ========================================================================================= */
 /* system_new / system_fill_out (system_objects.c:73-199,4-71).

@@ -97,6 +97,9 @@ SIGNATURES = {
     "mfv2d_cuda_element_vector_batch": (i32, [vp, vp, dp, dp, dp, i32]),
     "mfv2d_cuda_inverse_batch": (i32, [vp, i32, sz, dp, dp, vp, i32]),
     "mfv2d_cuda_inverse_definite_noalloc": (i32, [vp, i32, vp, vp, vp]),
+    "mfv2d_cuda_batched_gemv": (i32, [vp, sz, i32, i32, dp, dp, dp, i32]),
+    "mfv2d_cuda_border_batch": (i32, [vp, sz, i32, i32, dp, i32, vp, vp, vp, dp, i32]),
+    "mfv2d_cuda_legendre_estimates_batch": (i32, [vp, i32, i32, i32, dp, dp, dp, i32]),
     "mfv2d_cuda_solve_batch": (i32, [vp, i32, i32, sz, dp, dp, dp, vp, i32]),
     "mfv2d_cuda_system_create": (i32, [vp, sz, vp, dp, i32, sz, sz, vp, vp, dp, C.POINTER(vp)]),
     "mfv2d_cuda_system_destroy": (None, [vp]),

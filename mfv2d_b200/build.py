@@ -19,7 +19,7 @@ LIBDIR = os.path.join(HERE, "lib")
 OBJDIR = os.path.join(HERE, "build")
 LIB = os.path.join(LIBDIR, "libmfv2d_cuda.so")
 SOURCES = ["context.cu", "tables.cu", "plan.cu", "assembly.cu", "apply.cu", "element_api.cu", "dense.cu", "system.cu",
-           "comm.cu", "projector.cu", "schur_cg.cu", "peer.cu", "precond.cu", "micro.cu", "bicgstab.cu", "pcg.cu", "noalloc.cu"]
+           "comm.cu", "projector.cu", "schur_cg.cu", "peer.cu", "precond.cu", "micro.cu", "bicgstab.cu", "pcg.cu", "noalloc.cu", "refine.cu"]
 ARCH_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a"]
 NVCC_FLAGS = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC,-fvisibility=hidden", "--expt-relaxed-constexpr",
               "-Xptxas", "-v"]

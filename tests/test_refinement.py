@@ -1,0 +1,104 @@
+"""The batched error estimators (mfv2d_b200/refinement.py, refine.cu) against the reference's own estimators
+(tests/golden/refinement.npz, written by tests/golden/make_golden_refinement.py from python/mfv2d/refinement.py).
+`-m "not gpu"`: through the host emulation of the kernels; `-m gpu`: through libmfv2d_cuda.so on the B200."""
+import os
+import sys
+import types
+
+import numpy as np
+import pytest
+from conftest import golden
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "emu"))
+
+import parity_cases as P
+
+TOL = 1e-10
+
+
+def forcing(x, y):
+    return -2 * np.pi**2 * np.cos(np.pi * x) * np.cos(np.pi * y)
+
+
+def rel(a, b):
+    """entry-wise relative difference (estimates: every element counts on its own scale)"""
+    return float(np.max(np.abs(np.asarray(a) - np.asarray(b)) / np.maximum(np.abs(np.asarray(b)), 1e-300)))
+
+
+def rel_max(a, b):
+    """difference relative to the largest entry (coefficient tables with modes that vanish to rounding)"""
+    return float(np.max(np.abs(np.asarray(a) - np.asarray(b))) / np.max(np.abs(np.asarray(b))))
+
+
+def run_checks(M):
+    from mfv2d_b200 import refinement as R
+
+    g = golden("refinement.npz")
+    p, k = int(g["order"]), int(g["k"])
+    s = P.SYSTEMS["mixed_poisson_sorted"]
+    specs = P.specs_of(M, s)
+    assert [int(o) for o in specs.orders] == [int(o) for o in g["form_orders"]]
+    batch = M.ElementBatch(P.make_basis(M, p, k), np.ascontiguousarray(g["corners"]))
+    n = batch.n
+    sol = g["solution"].reshape(n, -1)
+    iu, iq = list(specs.orders).index(3), list(specs.orders).index(2)
+    # the two per-element helpers (refinement.py:40-152)
+    rule = M.IntegrationRule1D(p + k)
+    xi = eta = np.asarray(rule.nodes)
+    assert rel_max(R.compute_legendre_coefficients(p, p, xi, eta, g["leg_u"] * g["leg_w"] * g["leg_det"], g["leg_det"]), g["leg_coeffs"]) < TOL
+    assert rel_max(R.compute_legendre_coefficients(3, 2, xi, eta, g["leg_u"] * g["leg_w"] * g["leg_det"], g["leg_det"]), g["leg_coeffs_32"]) < TOL
+    assert rel(R.compute_legendre_error_estimates(p, p, xi, eta, g["leg_w"], g["leg_det"], g["leg_u"], g["leg_err"]), g["leg_estimates"]) < TOL
+    # ... and the batched kernel on the same data (element 0 of the batch)
+    u = np.zeros((n, p + k + 1, p + k + 1))
+    e = np.zeros_like(u)
+    u[0], e[0] = g["leg_u"], g["leg_err"]
+    est = R.legendre_error_estimates(batch, 3, u, e)
+    assert rel(est[0], g["leg_estimates"]) < TOL and np.all(est[1:] == 0)
+    # order reduction (:1095-1203)
+    for name, fi in (("u", iu), ("q", iq)):
+        for red in (1, 2):
+            err, cost = R.error_estimate_with_order_reduction(sol, batch, red, specs, fi)
+            ref = g[f"reduction_{name}_{red}"]
+            assert rel(err, ref[:, 0]) < 1e-9 and rel(cost, ref[:, 1]) < 1e-9, (name, red)
+    err, cost = R.error_estimate_with_order_reduction(sol, batch, 4, specs, iu, "prioritize")
+    assert np.all(np.isinf(err)) and np.all(np.isinf(cost)) and np.all(np.isinf(g["reduction_u_4_prioritize"]))
+    with pytest.raises(ValueError):
+        R.error_estimate_with_order_reduction(sol, batch, 4, specs, iu, "other")
+    # local inversion (:832-1093): plain, with the 2-form pinned, with the 1-form zeroed on the element boundary
+    eqs = [types.SimpleNamespace(weight=types.SimpleNamespace(order=2), right=types.SimpleNamespace(explicit_terms=())),
+           types.SimpleNamespace(weight=types.SimpleNamespace(order=3), right=types.SimpleNamespace(explicit_terms=((1.0, types.SimpleNamespace(func=forcing)),)))]
+    system = types.SimpleNamespace(equations=eqs)
+    for tag, zeroed, constrained, targets in (("plain", (), (), ("u", "q")), ("constrained_u", (), (iu,), ("u", "q")), ("zeroed_q_constrained_u", (iq,), (iu,), ("q",))):
+        for name in targets:
+            fi = iu if name == "u" else iq
+            err, cost = R.error_estimate_with_local_inversion(sol, batch, 1, specs, s["lhs"], s.get("rhs"), system, fi, zeroed, constrained)
+            ref = g[f"local_{tag}_{name}"]
+            assert rel(err, ref[:, 0]) < 1e-8 and rel(cost, ref[:, 1]) < 1e-8, (tag, name, rel(err, ref[:, 0]), rel(cost, ref[:, 1]))
+    with pytest.raises(ValueError):  # the reference raises for a 2-form target with zeroed forms (element_boundary_dofs)
+        R.error_estimate_with_local_inversion(sol, batch, 1, specs, s["lhs"], s.get("rhs"), system, iu, (iq,), ())
+
+
+def test_refinement_host_emulation():
+    from build_emu import build
+
+    import mfv2d_b200._capi as capi
+
+    capi._use_library_for_testing(build())
+    try:
+        from mfv2d_b200 import _mfv2d as M
+
+        run_checks(M)
+    finally:
+        capi._use_library_for_testing(capi.LIB_PATH)
+
+
+@pytest.mark.gpu
+def test_refinement_gpu():
+    import mfv2d_b200._capi as capi
+
+    capi._use_library_for_testing(capi.LIB_PATH)
+    from mfv2d_b200 import _mfv2d as M
+    from mfv2d_b200.runtime import get_context
+
+    assert get_context().handle
+    run_checks(M)
