@@ -433,6 +433,11 @@ MFV2D_API int mfv2d_cuda_system_peer_connect(mfv2d_system *sys, const void *hand
                                              const int64_t *holder_ptr, const int32_t *holder_rank);
 /* non-zero after a peer wait timed out (a rank died): results of that call are invalid */
 MFV2D_API int mfv2d_cuda_system_peer_error(mfv2d_system *sys);
+/* Diagnostics (no counterpart in the reference): with MFV2D_PEER_DEBUG bit 8 set at peer_connect, the kernels of the
+ * distributed CG stamp this rank's timeline; out16 receives the nanoseconds accumulated before each stamp
+ * (0 product + tail, 1 gather + publish, 2 launch gap, 3 wait for the peers, 4 update, 5 chunk sums, 6 aggregate + publish,
+ * 7 gap, 8 wait for the coarse residuals, 9 coarse solve) and the counters are reset. */
+MFV2D_API int mfv2d_cuda_system_peer_stats(mfv2d_system *sys, uint64_t *out16);
 
 /* Aggregate hierarchy of the additive multilevel preconditioner of solve_schur_cg (precondition = 2):
  *   M^-1 = diag(S)^-1 + sum_l P_l diag(P_l^T S P_l)^-1 P_l^T + P_L (P_L^T S P_L)^-1 P_L^T,

@@ -125,6 +125,7 @@ SIGNATURES = {
     "mfv2d_cuda_system_peer_export": (i32, [vp, sz, vp]),
     "mfv2d_cuda_system_peer_connect": (i32, [vp, vp, sz, vp, vp]),
     "mfv2d_cuda_system_peer_error": (i32, [vp]),
+    "mfv2d_cuda_system_peer_stats": (i32, [vp, vp]),
     "mfv2d_cuda_system_set_coarse_space": (i32, [vp, i32, vp, vp, vp, i32]),
 }
 

@@ -236,11 +236,12 @@ int mfv2d_cuda_system_peer_connect(mfv2d_system *s, const void *handles_all, siz
         MFV2D_TRY(sys_upload(s, of, &s->d_shared_of));
     }
     void *p = nullptr;
-    MFV2D_TRY(mfv2d_cuda_malloc(ctx, 64, &p));
+    MFV2D_TRY(mfv2d_cuda_malloc(ctx, 64 + 32 * sizeof(unsigned long long), &p));
     s->allocs.push_back(p);
-    MFV2D_CUDA_CHECK(ctx, cudaMemsetAsync(p, 0, 64, ctx->stream));
+    MFV2D_CUDA_CHECK(ctx, cudaMemsetAsync(p, 0, 64 + 32 * sizeof(unsigned long long), ctx->stream));
     pv.epoch = (unsigned long long *)p;
     pv.error = (int *)((char *)p + 32);
+    pv.stats = (unsigned long long *)((char *)p + 64);
     {
         const char *dbg = getenv("MFV2D_PEER_DEBUG");
         pv.dbg = dbg ? atoi(dbg) : 0;
@@ -259,6 +260,20 @@ int mfv2d_cuda_system_peer_error(mfv2d_system *s)
     cudaMemcpyAsync(&h, s->peer.error, sizeof h, cudaMemcpyDeviceToHost, s->ctx->stream);
     cudaStreamSynchronize(s->ctx->stream);
     return h;
+}
+
+// diagnostics (MFV2D_PEER_DEBUG bit 8): the timeline stamps of this rank's stream, nanoseconds accumulated before each of
+// the 16 stamp ids (schur_cg.cu / precond.cu say where they sit); the counters are reset by the call
+int mfv2d_cuda_system_peer_stats(mfv2d_system *s, uint64_t *out16)
+{
+    memset(out16, 0, 16 * sizeof(uint64_t));
+    if (!s->peers_ready || !s->peer.stats)
+        return MFV2D_SUCCESS;
+    mfv2d_ctx *ctx = s->ctx;
+    MFV2D_CUDA_CHECK(ctx, cudaMemcpyAsync(out16, s->peer.stats, 16 * sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->stream));
+    MFV2D_CUDA_CHECK(ctx, cudaMemsetAsync(s->peer.stats, 0, 17 * sizeof(uint64_t), ctx->stream));
+    MFV2D_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    return MFV2D_SUCCESS;
 }
 
 } // extern "C"

@@ -126,6 +126,8 @@ __global__ void __launch_bounds__(SYS_THREADS) coarse_aggregate_kernel(const Coa
             return;
         e = pv.epoch[1] + 1;
         parity = (int)(e & 1);
+        if (blockIdx.x == 0 && threadIdx.x == 0)
+            peer_stamp(pv, 5); // since the CG update: launch gaps + the chunk sums
     }
     bool wrote = false;
     for (long long J = blockIdx.x * (long long)blockDim.x + threadIdx.x; J < a.n_agg_total; J += (long long)gridDim.x * blockDim.x)
@@ -151,10 +153,13 @@ __global__ void __launch_bounds__(SYS_THREADS) coarse_aggregate_kernel(const Coa
         return;
     if (wrote)
         peer_fence(); // every writer orders its own remote stores before the CTA's ticket
-    __syncthreads();
+    const int cta_wrote = __syncthreads_or(wrote ? 1 : 0);
     if (threadIdx.x == 0)
     {
-        peer_fence();
+        if (cta_wrote)
+            peer_fence();
+        else
+            __threadfence();
         s_last = atomicAdd(a.tickets, 1) == (int)gridDim.x - 1;
         if (s_last)
         {
@@ -164,47 +169,76 @@ __global__ void __launch_bounds__(SYS_THREADS) coarse_aggregate_kernel(const Coa
                 if (r != pv.rank)
                     peer_store_flag(peer_flag(pv, r, 1, pv.rank), e);
             pv.epoch[1] = e;
+            peer_stamp(pv, 6); // aggregate sums + publication of the coarse residual
         }
     }
 }
 
-// yc = A_L^-1 (sum over the ranks of rc), one warp per row; every CTA forms the rank-ordered sum in shared memory.
-// rc and yc may not alias: rc = y[exact_begin ...] (input), yc = separate array
-__global__ void __launch_bounds__(SYS_THREADS) coarse_solve_kernel(long long nc, const double *__restrict__ Ainv, const double *__restrict__ rc,
+// rsum = sum over the ranks (in rank order) of the restricted residuals: this rank's rc + the copies the peers have written
+// into the type-1 area.  The only kernel of the coarse solve that waits for the peers.
+__global__ void __launch_bounds__(SYS_THREADS) coarse_sum_kernel(long long nc, const double *__restrict__ rc, double *__restrict__ rsum,
+                                                                const int *__restrict__ done, PeerView pv)
+{
+    if (done && *done)
+        return;
+    const unsigned long long e = pv.epoch[1];
+    const int parity = (int)(e & 1);
+    if (blockIdx.x == 0 && threadIdx.x == 0)
+        peer_stamp(pv, 7); // launch gap
+    peer_wait_all(pv, 1, e);
+    if (blockIdx.x == 0 && threadIdx.x == 0)
+        peer_stamp(pv, 8); // waiting for the peers' coarse residuals
+    if (*(volatile int *)pv.error)
+        return;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < nc; i += (long long)gridDim.x * blockDim.x)
+    {
+        double tot = 0.0;
+        for (int r = 0; r < pv.n_ranks; ++r)
+            tot += r == pv.rank ? rc[i] : peer_load(peer_region(pv, pv.rank, 1, parity, r) + i);
+        rsum[i] = tot;
+    }
+}
+
+// yc = A_L^-1 rs, one warp per row (16-byte loads); every CTA stages rs in shared memory.  rs and yc may not alias.
+__global__ void __launch_bounds__(SYS_THREADS) coarse_solve_kernel(long long nc, const double *__restrict__ Ainv, const double *__restrict__ rsum,
                                                                   double *__restrict__ yc, const int *__restrict__ done, PeerView pv)
 {
     MFV2D_DYN_SMEM(double, rs);
     if (done && *done)
         return;
-    const bool peers = pv.n_ranks > 1;
-    int parity = 0;
-    if (peers)
-    {
-        const unsigned long long e = pv.epoch[1];
-        parity = (int)(e & 1);
-        peer_wait_all(pv, 1, e);
-        if (*(volatile int *)pv.error)
-            return;
-    }
+    if (pv.n_ranks > 1 && *(volatile int *)pv.error)
+        return;
     for (long long i = threadIdx.x; i < nc; i += blockDim.x)
-    {
-        double tot = 0.0;
-        for (int r = 0; r < pv.n_ranks; ++r)
-            tot += r == pv.rank ? rc[i] : peer_load(peer_region(pv, pv.rank, 1, parity, r) + i);
-        rs[i] = tot;
-    }
+        rs[i] = rsum[i];
     __syncthreads();
     const int warp = threadIdx.x >> 5, nwarps = MFV2D_NWARPS;
+    const long long pairs = nc >> 1;
     for (long long row = (long long)blockIdx.x * nwarps + warp; row < nc; row += (long long)gridDim.x * nwarps)
     {
         const double *a = Ainv + (size_t)row * nc;
-        double acc = 0.0;
-        for (long long c = MFV2D_LANE0; c < nc; c += MFV2D_LANE_STEP)
-            acc = fma(a[c], rs[c], acc);
-        acc = warp_sum(acc);
+        double acc0 = 0.0, acc1 = 0.0;
+        if ((((size_t)row * nc) & 1) == 0)
+        {
+            const double2 *a2 = reinterpret_cast<const double2 *>(a);
+            const double2 *r2 = reinterpret_cast<const double2 *>(rs);
+            for (long long c = MFV2D_LANE0; c < pairs; c += MFV2D_LANE_STEP)
+            {
+                const double2 v = a2[c], w = r2[c];
+                acc0 = fma(v.x, w.x, acc0);
+                acc1 = fma(v.y, w.y, acc1);
+            }
+            if ((nc & 1) && MFV2D_LANE0 == 0)
+                acc0 = fma(a[nc - 1], rs[nc - 1], acc0);
+        }
+        else
+            for (long long c = MFV2D_LANE0; c < nc; c += MFV2D_LANE_STEP)
+                acc0 = fma(a[c], rs[c], acc0);
+        const double acc = warp_sum(acc0 + acc1);
         if (MFV2D_LANE0 == 0)
             yc[row] = acc;
     }
+    if (pv.n_ranks > 1 && blockIdx.x == 0 && threadIdx.x == 0)
+        peer_stamp(pv, 9); // CTA 0's share of the coarse mat-vec
 }
 
 // z[i] += cz[i] * sum over the levels of y_l[agg_l[i]]  (the exact level reads yc)
@@ -254,9 +288,17 @@ int coarse_correction(mfv2d_system *s, const double *r, double *z, const int *do
     {
         if (ctx->n_ranks > 1 && !use_peers)
             MFV2D_TRY(comm_allreduce(ctx, s->d_cy + s->exact_begin, (size_t)s->n_exact));
+        const double *rsum = s->d_cy + s->exact_begin;
+        if (ctx->n_ranks > 1 && use_peers)
+        {
+            MFV2D_LAUNCH(coarse_sum_kernel, grid_for(ctx, s->n_exact, SYS_THREADS), SYS_THREADS, 0, ctx->stream, s->n_exact, rsum, s->d_crs, done,
+                         s->peer);
+            ctx->launches++;
+            rsum = s->d_crs;
+        }
         const unsigned grid = (unsigned)std::min<long long>((s->n_exact + warps - 1) / warps, (long long)ctx->sm_count * 4);
         MFV2D_LAUNCH(coarse_solve_kernel, grid, SYS_THREADS, (size_t)s->n_exact * sizeof(double), ctx->stream, s->n_exact,
-                     (const double *)s->d_Ac_inv, (const double *)(s->d_cy + s->exact_begin), s->d_yc, done, use_peers ? s->peer : one);
+                     (const double *)s->d_Ac_inv, rsum, s->d_yc, done, use_peers ? s->peer : one);
         ctx->launches++;
     }
     MFV2D_LAUNCH(coarse_prolong_kernel, grid_for(ctx, s->n_trace, 256), 256, 0, ctx->stream, (long long)s->n_trace, s->n_clevels,
@@ -368,6 +410,7 @@ int mfv2d_cuda_system_set_coarse_space(mfv2d_system *s, int n_levels, const int6
     MFV2D_TRY(sys_alloc(s, (size_t)total, &s->d_cy));
     MFV2D_TRY(sys_alloc(s, (size_t)exact_begin, &s->d_ldinv));
     MFV2D_TRY(sys_alloc(s, (size_t)n_exact, &s->d_yc));
+    MFV2D_TRY(sys_alloc(s, (size_t)n_exact, &s->d_crs));
     long long grid = (long long)ctx->sm_count * 8;
     if (grid > s->n_elem)
         grid = s->n_elem;

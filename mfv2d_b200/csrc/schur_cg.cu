@@ -71,6 +71,8 @@ __global__ void __launch_bounds__(SYS_THREADS) cg1_gather_kernel(const CgGatherA
             return;
         e = pv.epoch[0] + 1;
         parity = (int)(e & 1);
+        if (blockIdx.x == 0 && threadIdx.x == 0)
+            peer_stamp(pv, 0); // since the previous stamp: the tail of the last iteration + the condensed-block product
     }
     double d = 0.0, g = 0.0, rho = 0.0;
     bool wrote = false;
@@ -108,6 +110,7 @@ __global__ void __launch_bounds__(SYS_THREADS) cg1_gather_kernel(const CgGatherA
     }
     if (wrote && !(pv.dbg & 1))
         peer_fence(); // every writer orders its own remote stores before the CTA's ticket
+    const int cta_wrote = peers ? __syncthreads_or(wrote ? 1 : 0) : 0;
     const int np = gridDim.x;
     block_reduce_store(d, a.partials);
     block_reduce_store(g, a.partials + np);
@@ -115,8 +118,8 @@ __global__ void __launch_bounds__(SYS_THREADS) cg1_gather_kernel(const CgGatherA
     // the last CTA to arrive reduces the partials in a fixed order and publishes
     if (threadIdx.x == 0)
     {
-        if (peers)
-            peer_fence();
+        if (cta_wrote)
+            peer_fence(); // a CTA without remote stores only publishes its partials: device scope is enough
         else
             __threadfence();
         s_last = atomicAdd(&flags[4], 1) == np - 1;
@@ -152,6 +155,7 @@ __global__ void __launch_bounds__(SYS_THREADS) cg1_gather_kernel(const CgGatherA
                     if (r != pv.rank)
                         peer_store_flag(peer_flag(pv, r, 0, pv.rank), e);
                 pv.epoch[0] = e;
+                peer_stamp(pv, 1); // gather + reduction + publication
             }
         }
     }
@@ -185,7 +189,11 @@ __global__ void __launch_bounds__(SYS_THREADS) cg1_update_kernel(const CgUpdateA
     {
         const unsigned long long e = pv.epoch[0];
         parity = (int)(e & 1);
+        if (blockIdx.x == 0 && threadIdx.x == 0)
+            peer_stamp(pv, 2); // launch gap between the two kernels
         peer_wait_all(pv, 0, e);
+        if (blockIdx.x == 0 && threadIdx.x == 0)
+            peer_stamp(pv, 3); // waiting for the peers' flags
         if (*(volatile int *)pv.error)
             return;
     }
@@ -268,6 +276,8 @@ __global__ void __launch_bounds__(SYS_THREADS) cg1_update_kernel(const CgUpdateA
         if (a.dinv)
             a.z[i] = ri * a.dinv[i];
     }
+    if (peers && blockIdx.x == 0 && threadIdx.x == 0)
+        peer_stamp(pv, 4); // CTA 0's share of the update
 }
 
 // d[i] = 1 / d[i] (1 where the diagonal vanishes); z[i] = d[i] r[i]

@@ -22,7 +22,10 @@ struct PeerView
     unsigned char *base[MFV2D_MAX_PEERS] = {};
     unsigned long long *epoch = nullptr; // device counters [2]: exchanges of each type started by this rank
     int *error = nullptr;                // device flag: set when a wait timed out
-    int dbg = 0;                         // MFV2D_PEER_DEBUG bits (timing experiments only): 1 = no per-writer fence
+    int dbg = 0;                         // MFV2D_PEER_DEBUG bits (timing experiments only): 1 = no per-writer fence,
+                                         // 2 = one CTA polls the peers' flags, the others a local flag, 8 = timeline stamps
+    unsigned long long *stats = nullptr; // [32] timeline of one rank's stream (dbg & 8): ns accumulated before each stamp id,
+                                         // [16] = time of the last stamp, [17] = local "peers arrived" epochs (dbg & 2), two types
 };
 #define PEER_FLAG_BYTES 512 // flags live in the first 2 * 16 * 8 = 256 bytes, the data area starts here
 #define PEER_XSCALARS 4     // scalars that ride behind the interface values
@@ -55,6 +58,23 @@ static inline double peer_load(const double *p) { return *(const volatile double
 static inline void peer_backoff() { emu_peer_backoff(); }
 #endif
 
+// timeline stamp (ONE thread): the time since the previous stamp of this rank's stream is added to stats[id]
+__device__ __forceinline__ void peer_stamp(const PeerView &pv, int id)
+{
+#ifndef MFV2D_EMU
+    if ((pv.dbg & 8) && pv.stats)
+    {
+        unsigned long long now;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+        const unsigned long long last = pv.stats[16];
+        if (last && now > last)
+            pv.stats[id] += now - last;
+        pv.stats[16] = now;
+        __threadfence();
+    }
+#endif
+}
+
 __device__ __forceinline__ double *peer_region(const PeerView &pv, int holder, int type, int parity, int sender)
 {
     return reinterpret_cast<double *>(pv.base[holder] + PEER_FLAG_BYTES) + pv.area_off[type] +
@@ -68,6 +88,49 @@ __device__ __forceinline__ unsigned long long *peer_flag(const PeerView &pv, int
 // rank r's flag); a wait that exceeds the budget sets the error flag instead of hanging the GPU.  Ends with a CTA barrier.
 __device__ __forceinline__ void peer_wait_all(const PeerView &pv, int type, unsigned long long e)
 {
+#ifndef MFV2D_EMU
+    if ((pv.dbg & 2) && pv.stats)
+    {
+        // experiment: only CTA 0 polls the peers' (system-scope) flags; the other CTAs wait for its local release
+        unsigned long long *arrived = pv.stats + 17 + type;
+        if (blockIdx.x == 0)
+        {
+            if ((int)threadIdx.x < pv.n_ranks && (int)threadIdx.x != pv.rank && !*(volatile int *)pv.error)
+            {
+                const unsigned long long *f = peer_flag(pv, pv.rank, type, (int)threadIdx.x);
+                unsigned long long spins = 0;
+                while (peer_load_flag(f) < e)
+                {
+                    if (++spins > (1ull << 26))
+                    {
+                        *pv.error = 1;
+                        break;
+                    }
+                    peer_backoff();
+                }
+            }
+            __syncthreads();
+            if (threadIdx.x == 0)
+                asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(arrived), "l"(e) : "memory");
+        }
+        else
+        {
+            if (threadIdx.x == 0)
+            {
+                unsigned long long v = 0, spins = 0;
+                do
+                {
+                    asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(arrived) : "memory");
+                    if (v >= e || *(volatile int *)pv.error)
+                        break;
+                    peer_backoff();
+                } while (++spins < (1ull << 27));
+            }
+            __syncthreads();
+        }
+        return;
+    }
+#endif
     if ((int)threadIdx.x < pv.n_ranks && (int)threadIdx.x != pv.rank && !*(volatile int *)pv.error)
     {
         const unsigned long long *f = peer_flag(pv, pv.rank, type, (int)threadIdx.x);
@@ -144,6 +207,7 @@ struct mfv2d_system
     double *d_ldinv = nullptr;          // [exact_begin] 1 / diag(P_l^T S P_l)
     double *d_cy = nullptr;             // [n_agg_total] scaled restrictions | this rank's part of the exact level's residual
     double *d_yc = nullptr;             // [n_exact] correction of the exact level
+    double *d_crs = nullptr;            // [n_exact] restricted residual summed over the ranks (peer exchange)
     double *d_Ac_inv = nullptr;         // [n_exact^2] inverse of P_L^T S P_L, row-major
     bool coarse_ready = false;
     // work vectors

@@ -254,6 +254,13 @@ class LinearSystem:
     def peer_error(self) -> bool:
         return bool(lib().mfv2d_cuda_system_peer_error(self.handle))
 
+    def peer_stats(self) -> np.ndarray:
+        """Timeline of this rank's distributed CG (``MFV2D_PEER_DEBUG`` bit 8): nanoseconds accumulated before each of the
+        16 stamps since the last call (``mfv2d_cuda_system_peer_stats``)."""
+        out = np.zeros(16, np.uint64)
+        check(lib().mfv2d_cuda_system_peer_stats(self.handle, out.ctypes.data), self.ctx.handle)
+        return out
+
     def set_coarse_space(self, aggregates: np.ndarray, z: np.ndarray, n_agg, exact_last: bool = True) -> None:
         """Aggregate hierarchy of the multilevel preconditioner (``precondition="multilevel"``): ``aggregates[level, multiplier]``
         (aggregate id or -1) and the near-null-space value ``z`` of every multiplier of this rank

@@ -138,6 +138,8 @@ def main():
     for _ in range(args.repeat):  # the first solve pays NCCL's lazy set-up and the graph instantiation
         B.barrier(dist)
         ctx.synchronize()
+        if world > 1:
+            system.peer_stats()  # reset the timeline counters (MFV2D_PEER_DEBUG bit 8)
         t0 = time.perf_counter()
         xs, lam, res, it = SV.solve_schur_iterative(system, rhs, phi, SV.ConvergenceSettings(args.max_iter, 1e300, args.rtol),
                                                     precondition=args.precondition)
@@ -145,6 +147,14 @@ def main():
         ctx.synchronize()
         solve_times.append(B.max_over_ranks(dist, time.perf_counter() - t0))
     solve_s = solve_times[-1]
+    timeline = None
+    if world > 1 and int(os.environ.get("MFV2D_PEER_DEBUG", "0")) & 8:
+        mine = (system.peer_stats()[:10].astype(np.float64) / max(int(it), 1) / 1e3).round(2).tolist()
+        gathered = [None] * world
+        dist.all_gather_object(gathered, mine)
+        timeline = {"us_per_iteration_by_stamp": gathered,
+                    "stamps": "0 product+tail | 1 gather+publish | 2 gap | 3 wait peers | 4 update (CTA 0) | 5 gap+chunk sums | 6 aggregate+publish | "
+                              "7 gap | 8 wait coarse | 9 coarse solve (CTA 0); one row per rank"}
 
     # ---- residual of the saddle-point system [[A, N^T], [N, 0]] (x, lam) = (rhs, 0), summed over the ranks ----
     r1 = system.apply_diagonal(xs).get() + system.apply_trace_transpose(lam).get() - rhs_h.ravel()
@@ -164,7 +174,8 @@ def main():
         "solve": {"method": "CG on the Schur complement N A^-1 N^T" + f", preconditioner {args.precondition}", "rtol": args.rtol, "s": solve_s, "s_all_solves": solve_times,
                   "exchange": os.environ.get("MFV2D_CG_EXCHANGE", "peer" if world > 1 else "-"), "graph": os.environ.get("MFV2D_CG_GRAPH", "default"),
                   "iterations": int(it), "us_per_iteration": solve_s / max(int(it), 1) * 1e6, "cg_residual": float(res),
-                  "saddle_relative_residual": float(np.sqrt(num / den))},
+                  "saddle_relative_residual": float(np.sqrt(num / den)), "peer_debug": os.environ.get("MFV2D_PEER_DEBUG", "0"),
+                  "timeline": timeline},
     }
     if rank == 0:
         B.emit(line)

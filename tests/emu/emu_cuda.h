@@ -60,6 +60,7 @@ static inline double __hiloint2double(int hi, int lo)
     return d;
 }
 static inline void __syncthreads() {}
+static inline int __syncthreads_or(int v) { return v; } // one thread per CTA
 static inline void __syncwarp() {}
 static inline void __threadfence() {}
 static inline void __threadfence_system() {}
