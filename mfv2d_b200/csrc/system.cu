@@ -13,6 +13,7 @@
 //         slots that contribute to it (the reference's trace_offsets/trace_values, sparse_system.h:27-32):
 //         the Schur operator costs sum m_e^2 reads per application instead of sum N_e^2.
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 
 #include "system.cuh"
@@ -807,6 +808,17 @@ int mfv2d_cuda_system_create(mfv2d_ctx *ctx, size_t n_elem, const int64_t *block
         }                                                                                                      \
     } while (0)
 
+    // MFV2D_SYSTEM_TIMING=1: wall-clock milliseconds of the set-up phases on stderr (the device is synchronised at each mark)
+    const bool timing = getenv("MFV2D_SYSTEM_TIMING") != nullptr;
+    auto t_last = std::chrono::steady_clock::now();
+    auto tick = [&](const char *what) {
+        if (!timing)
+            return;
+        cudaStreamSynchronize(ctx->stream);
+        const auto now = std::chrono::steady_clock::now();
+        fprintf(stderr, "[system_create rank %d] %-28s %8.2f ms\n", ctx->rank, what, std::chrono::duration<double, std::milli>(now - t_last).count());
+        t_last = now;
+    };
     std::vector<int64_t> boff(block_offsets, block_offsets + n_elem + 1), moff(n_elem + 1, 0);
     if (n_elem == 0)
         boff.assign(1, 0);
@@ -931,6 +943,7 @@ int mfv2d_cuda_system_create(mfv2d_ctx *ctx, size_t n_elem, const int64_t *block
         for (int64_t k = 0; k < s->n_slots; ++k)
             tr_slot[fill[slot_trace[k]]++] = k;
     }
+    tick("host constraint structure");
     // ---- upload ----
     SYS_TRY(sys_upload(s, boff, &s->d_block_off));
     SYS_TRY(sys_upload(s, moff, &s->d_mat_off));
@@ -963,6 +976,7 @@ int mfv2d_cuda_system_create(mfv2d_ctx *ctx, size_t n_elem, const int64_t *block
             SYS_TRY(sys_upload(s, tr2, &s->d_tr2));
         }
     }
+    tick("uploads");
     const size_t mat_total = (size_t)moff[n_elem];
     if (blocks_space == MFV2D_DEVICE)
     {
@@ -998,6 +1012,7 @@ int mfv2d_cuda_system_create(mfv2d_ctx *ctx, size_t n_elem, const int64_t *block
             s->symmetric = h_flag == 0;
         }
     }
+    tick("symmetry test");
     std::vector<int64_t> s_off(n_elem + 1, 0);
     for (size_t e = 0; e < n_elem; ++e)
     {
@@ -1027,6 +1042,7 @@ int mfv2d_cuda_system_create(mfv2d_ctx *ctx, size_t n_elem, const int64_t *block
     cudaMemsetAsync(s->d_cg, 0, 64 * sizeof(double), ctx->stream);
     s->n_partials = ctx->sm_count * 4;
     SYS_TRY(sys_alloc(s, (size_t)3 * s->n_partials, &s->d_partials));
+    tick("allocations");
     // ---- factorise: explicit inverses of the dense blocks ----
     int32_t *d_status = nullptr;
     SYS_TRY(sys_alloc(s, n_elem, &d_status));
@@ -1043,6 +1059,7 @@ int mfv2d_cuda_system_create(mfv2d_ctx *ctx, size_t n_elem, const int64_t *block
             SYS_TRY(launch_inverse_batch(ctx, (int)n, e2 - e, s->d_A + moff[e], s->d_Ainv + moff[e], d_status + e));
             e = e2;
         }
+    tick("block inverses");
     if (n_elem)
     {
         std::vector<int32_t> status(n_elem);
@@ -1062,6 +1079,7 @@ int mfv2d_cuda_system_create(mfv2d_ctx *ctx, size_t n_elem, const int64_t *block
             SYS_TRY(mfv2d_fail(ctx, MFV2D_CUDA_ERROR, "schur_build kernel launch failed"));
     }
     SYS_TRY(mfv2d_cuda_synchronize(ctx));
+    tick("condensed blocks");
 #undef SYS_TRY
     *out = s;
     return MFV2D_SUCCESS;

@@ -1,0 +1,132 @@
+"""BASELINE.json configs[2] at full size on one B200: unsteady linear advection-diffusion, n x n deformed elements of order p
+(default 512 x 512, p = 5), trapezoidal time march with the device-backed callers (mfv2d_b200/callers.py).
+
+    python profiles/config2_march.py [--n 512] [--order 5] [--steps 3]
+
+The operator is the time-march-updated system of tests/golden/timemarch_advdif.npz (bytecode written by the reference's own
+CompiledSystem after update_system_for_time_march, dt = 0.05: q 1-form, u 2-form, nu = 0.05, the advection field of
+tests/fields.py); constraints = the continuity rows of the structured mesh (natural boundary conditions); right-hand side =
+dual DoFs of a smooth source on the u rows.  Every step: residual by one matrix-free apply over all elements, correction by
+BiCGStab on the (non-symmetric) Schur complement, dual <- primal by the matrix-free mass apply.  Prints one JSON line:
+set-up and per-step times, Krylov iterations, and the relative residual of the saddle-point system of the last step,
+`||[b - A x - N^T l ; -N x]|| / ||b||`.
+"""
+import argparse
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+import fields as F  # noqa: E402
+from mfv2d_b200 import _mfv2d as M  # noqa: E402
+from mfv2d_b200 import callers as CL  # noqa: E402
+from mfv2d_b200 import solving as SV  # noqa: E402
+from mfv2d_b200 import structured as ST  # noqa: E402
+from mfv2d_b200.runtime import get_context  # noqa: E402
+
+
+def source(x, y):
+    return 3.0 * np.cos(np.pi * x) * np.sin(0.7 * np.pi * y)
+
+
+def decode(codes):
+    out = []
+    for rowc in codes:
+        r = []
+        for blk in rowc:
+            if blk is None:
+                r.append(None)
+                continue
+            ops = []
+            for item in blk:
+                item = list(item)
+                if item[0] == 7 and isinstance(item[2], str) and item[2].startswith("fn:"):
+                    item[2] = F.FIELDS[item[2][3:]]
+                ops.append(tuple(item))
+            r.append(tuple(ops))
+        out.append(tuple(r))
+    return tuple(out)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--n", type=int, default=512)
+    ap.add_argument("--order", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--rtol", type=float, default=1e-12)
+    ap.add_argument("--max-iter", type=int, default=40000)
+    ap.add_argument("--nl-rtol", type=float, default=1e-10, help="stop the corrections of a step when max|residual| <= nl_rtol * max|rhs|")
+    ap.add_argument("--nl-max", type=int, default=3)
+    args = ap.parse_args()
+    g = np.load(os.path.join(ROOT, "tests", "golden", "timemarch_advdif.npz"), allow_pickle=True)
+    raw = json.loads(str(g["codes"]))
+    lhs = decode(raw["lhs"])
+    dt, k = float(g["dt"]), int(g["k"])
+    p, n = args.order, args.n
+    specs = M._ElementFormSpecification(*zip(raw["form_names"], raw["form_orders"]))
+    ctx = get_context()
+    t0 = time.perf_counter()
+    corners = ST.unit_square_corners(n, n, F.deform)
+    rule = M.IntegrationRule1D(p + k)
+    batch = M.ElementBatch(M.Basis2D(M.Basis1D(p, rule), M.Basis1D(p, rule)), np.ascontiguousarray(corners), ctx)
+    row, col, val, n_trace = ST.continuity_constraints(n, n, p, raw["form_orders"])
+    ne = specs.total_size(p, p)
+    explicit = np.zeros((batch.n, ne))
+    iu = raw["form_names"].index("u")
+    off_u = specs.form_offset(iu, p, p)
+    explicit[:, off_u:off_u + specs.form_size(iu, p, p)] = batch.dual_dofs(3, source)
+    explicit = explicit.ravel()
+    con_rhs = np.zeros(n_trace)
+    host_s = time.perf_counter() - t0
+
+    # the march (callers.trapezoidal_march builds the LinearSystem: element matrices stay on the device)
+    stats = {"krylov_iterations": [], "krylov_residual": []}
+    orig = SV.solve_schur_bicgstab
+
+    def counting(system, rd, rt, conv, precondition=True):
+        x, lam, res, it = orig(system, rd, rt, conv, precondition)
+        stats["krylov_iterations"].append(int(it))
+        stats["krylov_residual"].append(float(res))
+        stats["last"] = (system, np.array(rd), np.array(rt), np.array(x), np.array(lam))
+        return x, lam, res, it
+
+    SV.solve_schur_bicgstab = counting
+    step_times = []
+    t_all = time.perf_counter()
+    orig_nl = CL.non_linear_solve_run
+
+    def timed(*a, **kw):
+        ctx.synchronize()
+        t = time.perf_counter()
+        out = orig_nl(*a, **kw)
+        ctx.synchronize()
+        step_times.append(time.perf_counter() - t)
+        return out
+
+    CL.non_linear_solve_run = timed
+    sols, iters = CL.trapezoidal_march(specs, lhs, None, batch, (row, col, val), n_trace, con_rhs, explicit, [iu], dt, args.steps, max_iterations=args.nl_max, rtol=args.nl_rtol,
+                                       krylov=SV.ConvergenceSettings(args.max_iter, 1e300, args.rtol))
+    total_s = time.perf_counter() - t_all
+    system, rd, rt, x, lam = stats.pop("last")
+    r1 = rd - system.apply_diagonal(x) - system.apply_trace_transpose(lam)
+    r2 = rt - system.apply_trace(x)
+    rel = float(np.sqrt(r1 @ r1 + r2 @ r2) / np.sqrt(rd @ rd + rt @ rt))
+    print(json.dumps({
+        "config": f"BASELINE.json configs[2]: unsteady advection-diffusion (q1, u2), {n}x{n} deformed elements, order {p}, integration order p+{k}, "
+                  f"trapezoidal march dt = {dt}, {args.steps} steps, 1 GPU",
+        "elements": batch.n, "element_dofs": ne, "dense_dofs": batch.n * ne, "multipliers": int(n_trace),
+        "host_mesh_constraints_rhs_s": host_s, "march_total_s": total_s, "setup_s": total_s - sum(step_times) if step_times else None,
+        "step_s": step_times, "newton_iterations_per_step": [int(i) for i in iters], **stats,
+        "last_correction_saddle_relative_residual": rel, "solution_norms": [float(np.linalg.norm(s)) for s in sols],
+        "method": "BiCGStab on the Schur complement N A^-1 N^T (full condensed blocks, Jacobi right preconditioner), device resident",
+    }))
+
+
+if __name__ == "__main__":
+    main()
