@@ -1335,6 +1335,12 @@ template <int Q> static int launch_fused_q(mfv2d_ctx *ctx, FusedArgs &fa, size_t
     const int want = APPLYT_THREADS / Q; // phase B: one thread per (element, quadrature column), one round
     if (epb > want)
         epb = want;
+    if (const char *env = getenv("MFV2D_APPLY_EPB")) // experiment: elements per CTA pass
+    {
+        const int v = atoi(env);
+        if (v >= 1 && v < epb)
+            epb = v;
+    }
     if (epb < 1)
         epb = 1;
     fa.epb = epb;
