@@ -25,14 +25,17 @@ from . import solving as SV
 def non_linear_solve_run(form_specs, lhs_codes, rhs_codes, batch: M.ElementBatch, system: SV.LinearSystem, explicit_vec: np.ndarray,
                          constraint_rhs: np.ndarray, solution: np.ndarray, lagrange: np.ndarray, *, max_iterations: int, atol: float,
                          rtol: float, relax: float = 1.0, max_mag: float | None = None, time_carry_index: np.ndarray | None = None,
-                         time_carry_term: np.ndarray | None = None, solve: Callable | None = None, field_values=None):
+                         time_carry_term: np.ndarray | None = None, solve: Callable | None = None, field_values=None,
+                         reduce_max: Callable[[float], float] | None = None):
     """``non_linear_solve_run`` (python/mfv2d/solve_system.py:353-485) on one bucket of elements.
 
     ``explicit_vec`` ``(n * N_e,)`` is the dense right-hand side (weak boundary terms included), ``constraint_rhs`` the one of
     the constraint rows; ``solution`` / ``lagrange`` are updated in place and returned with the iteration count and the last
     maximum residual.  ``system`` holds the element matrices of ``lhs_codes`` (the linearised operator of the correction
     solve, ``system_decomp`` of the reference); ``solve(system, r_dense, r_trace) -> (dx, dlambda)`` defaults to the
-    Schur-complement CG, pass ``solving.solve_schur_bicgstab`` based solvers for non-symmetric blocks."""
+    Schur-complement CG, pass ``solving.solve_schur_bicgstab`` based solvers for non-symmetric blocks.  On a partitioned
+    system (one strip of the mesh per rank, ``system`` connected to its peers) every rank passes its local vectors, the
+    GLOBAL ``max_mag`` and ``reduce_max`` = the host's max-all-reduce: the stopping decision is then the same on all ranks."""
     n, ne = batch.n, form_specs.total_size(batch.p, batch.p)
     base = np.array(explicit_vec, np.float64)
     if time_carry_term is not None:
@@ -54,6 +57,8 @@ def non_linear_solve_run(form_specs, lhs_codes, rhs_codes, batch: M.ElementBatch
         r_dense = base - main_value
         r_trace = constraint_rhs - system.apply_trace(solution)
         max_residual = float(max(np.max(np.abs(r_dense), initial=0.0), np.max(np.abs(r_trace), initial=0.0)))
+        if reduce_max is not None:
+            max_residual = float(reduce_max(max_residual))
         if not (max_residual > atol and max_residual > max_mag * rtol):
             break
         dx, dl = solve(system, r_dense, r_trace)
@@ -74,15 +79,19 @@ def time_carry_indices(form_specs, p: int, n: int, march_forms: Sequence[int]) -
 def trapezoidal_march(form_specs, lhs_codes, rhs_codes, batch: M.ElementBatch, constraints, n_trace: int, constraint_rhs: np.ndarray,
                       explicit_vec: np.ndarray, march_forms: Sequence[int], dt: float, nt: int, *, max_iterations: int = 20, atol: float = 1e-13,
                       rtol: float = 0.0, symmetric: bool = False, initial_solution: np.ndarray | None = None,
-                      initial_dual: np.ndarray | None = None, field_values=None, krylov: SV.ConvergenceSettings | None = None):
+                      initial_dual: np.ndarray | None = None, field_values=None, krylov: SV.ConvergenceSettings | None = None,
+                      system: SV.LinearSystem | None = None, reduce_max: Callable[[float], float] | None = None):
     """The trapezoidal time march of ``solve_system_2d`` (python/mfv2d/solve_system_2d.py:289-397).
 
     ``lhs_codes`` are those of the system AFTER ``update_system_for_time_march`` (the ``2 / dt`` mass terms are part of the
     operator).  Returns the list of DoF vectors after every step (the arrays the reference hands to
     ``reconstruct_mesh_from_solution``).  ``symmetric=False`` solves the corrections with BiCGStab on the Schur complement
-    (advection makes the element blocks non-symmetric), ``True`` with CG."""
+    (advection makes the element blocks non-symmetric), ``True`` with CG.  Multi-GPU: pass this rank's strip as ``batch``, its
+    partitioned ``constraints`` / vectors, a ``system`` that is already connected to its peers (``set_interface`` +
+    ``connect_peers``) and ``reduce_max``."""
     n, ne = batch.n, form_specs.total_size(batch.p, batch.p)
-    system = SV.compute_linear_system(form_specs, lhs_codes, batch, constraints, n_trace, field_values=field_values)
+    if system is None:
+        system = SV.compute_linear_system(form_specs, lhs_codes, batch, constraints, n_trace, field_values=field_values)
     krylov = krylov or SV.ConvergenceSettings(20000, 1e300, 1e-13)
     if symmetric:
         def solve(sysm, rd, rt):
@@ -97,12 +106,15 @@ def trapezoidal_march(form_specs, lhs_codes, rhs_codes, batch: M.ElementBatch, c
     old_carry = np.zeros(carry.size) if initial_dual is None else np.asarray(initial_dual, np.float64).ravel()[carry]
     time_carry_term = np.asarray(explicit_vec, np.float64)[carry].copy()
     max_mag = float(np.max(np.abs(np.concatenate([explicit_vec, constraint_rhs]))))
+    if reduce_max is not None:
+        max_mag = float(reduce_max(max_mag))
     out, iters = [], []
     for _ in range(nt):
         current = 2.0 / dt * old_carry + time_carry_term
         solution, lagrange, it, _res = non_linear_solve_run(form_specs, lhs_codes, rhs_codes, batch, system, explicit_vec, constraint_rhs, solution,
                                                            lagrange, max_iterations=max_iterations, atol=atol, rtol=rtol, max_mag=max_mag,
-                                                           time_carry_index=carry, time_carry_term=current, solve=solve, field_values=field_values)
+                                                           time_carry_index=carry, time_carry_term=current, solve=solve, field_values=field_values,
+                                                           reduce_max=reduce_max)
         projected = np.asarray(M.compute_element_dual_from_primal(form_specs, solution.reshape(n, ne), batch)).ravel()
         new_carry = projected[carry]
         time_carry_term = 2.0 / dt * (new_carry - old_carry) - time_carry_term

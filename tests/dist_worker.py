@@ -127,9 +127,11 @@ def main():
 
         it, itj, _, worst = PC.check_partitioned_solve(M, SV, ST, ctx, rank, world, all_gather, fix, nh, nv)
         itj2, it2 = PC.check_multilevel(M, SV, ST, ctx, rank, world, all_gather, nh=32, nv=32, p=3, k=3, mid_sizes=(2,), exact_size=8)
+        itb, errb = PC.check_partitioned_bicgstab(M, SV, ST, ctx, rank, world, all_gather)
         if rank == 0:
             print(f"dist_worker ok: mode {mode}, world {world}, iterations {it} (jacobi {itj}), err {worst:.2e}; "
-                  f"multilevel {it2} vs jacobi {itj2} on 32x32 p3, exchange {os.environ.get('MFV2D_CG_EXCHANGE', 'peer')}", flush=True)
+                  f"multilevel {it2} vs jacobi {itj2} on 32x32 p3; BiCGStab (advection-diffusion) {itb} iterations, err {errb:.1e}; "
+                  f"exchange {os.environ.get('MFV2D_CG_EXCHANGE', 'peer')}", flush=True)
         dist.barrier()
         dist.destroy_process_group()
         return

@@ -589,6 +589,74 @@ def check_partitioned_solve(M, SV, ST, ctx, rank, world, all_gather, fix, nh, nv
     return it, itj, it2, err
 
 
+def _timemarch_system(M):
+    """bytecode + form layout of the time-march-updated advection-diffusion system of tests/golden/timemarch_advdif.npz"""
+    g = golden("timemarch_advdif.npz")
+    raw = json.loads(str(g["codes"]))
+    lhs = []
+    for rowc in raw["lhs"]:
+        r = []
+        for blk in rowc:
+            if blk is None:
+                r.append(None)
+                continue
+            ops = []
+            for item in blk:
+                item = list(item)
+                if item[0] == 7 and isinstance(item[2], str) and item[2].startswith("fn:"):
+                    item[2] = F.FIELDS[item[2][3:]]
+                ops.append(tuple(item))
+            r.append(tuple(ops))
+        lhs.append(tuple(r))
+    return g, raw, tuple(lhs), M._ElementFormSpecification(*zip(raw["form_names"], raw["form_orders"]))
+
+
+def check_partitioned_bicgstab(M, SV, ST, ctx, rank, world, all_gather, nh=8, nv=8):
+    """One rank of a partitioned BiCGStab solve on the Schur complement of a NON-symmetric system (the advection-diffusion
+    operator of the time-march fixture on its 8 x 8 order-4 mesh): the strip solution must agree with a direct sparse solve
+    of the global saddle-point system (SciPy SuperLU on the host, the reference's production path) and every rank must take
+    the same number of iterations."""
+    import scipy.sparse as sp
+    import scipy.sparse.linalg as spl
+
+    g, raw, lhs, specs = _timemarch_system(M)
+    p, k = int(g["order"]), int(g["k"])
+    ne = specs.total_size(p, p)
+    corners = np.ascontiguousarray(g["corners"])
+    n = corners.shape[0]
+    assert n == nh * nv
+    row, col, val, nt = ST.continuity_constraints(nh, nv, p, raw["form_orders"])
+    rhs = np.asarray(g["explicit"], np.float64)
+    phi = np.zeros(nt)
+    # global direct solve (host)
+    mats_all = M.compute_element_matrices(specs, lhs, M.ElementBatch(make_basis(M, p, k), corners, ctx))
+    A = sp.block_diag([sp.csr_matrix(m) for m in mats_all], format="csr")
+    N = sp.coo_matrix((val, (row, col)), shape=(nt, n * ne)).tocsr()
+    sol = spl.spsolve(sp.bmat([[A, N.T], [N, None]], format="csc"), np.concatenate([rhs, phi]))
+    # this rank's strip
+    parts = ST.strip_partition(nh, nv, world)
+    bounds = [parts[r][0] * ne for r in range(world)] + [parts[-1][1] * ne]
+    lo, hi = parts[rank]
+    if world > 1:
+        P = ST.partition_constraints(row, col, val, nt, bounds, rank)
+        prow, pcol, pval, pnt, rows_glob = P.row, P.col, P.val, P.n_trace, P.global_rows
+    else:
+        prow, pcol, pval, pnt, rows_glob = row, col, val, nt, np.arange(nt)
+    sysm = SV.LinearSystem(np.ascontiguousarray(mats_all[lo:hi]), (prow, pcol, pval), pnt, ctx=ctx)
+    if world > 1:
+        sysm.set_interface(P.shared_index, P.slot, P.n_slots, P.owned)
+        sysm.connect_peers(P.holder_ptr, P.holder_rank, all_gather)
+    x, lam, res, it = SV.solve_schur_bicgstab(sysm, np.ascontiguousarray(rhs[bounds[rank]:bounds[rank + 1]]), np.ascontiguousarray(phi[rows_glob]),
+                                              SV.ConvergenceSettings(4000, 1e300, 1e-13))
+    assert not (world > 1 and sysm.peer_error())
+    ex = relerr(x, sol[bounds[rank]:bounds[rank + 1]])
+    el = float(np.max(np.abs(lam - sol[n * ne:][rows_glob])) / max(np.max(np.abs(sol[n * ne:])), 1e-300))
+    assert ex < 1e-9 and el < 1e-9, (rank, ex, el, it)
+    counts = all_gather(int(it))
+    assert all(c == counts[0] for c in counts), counts
+    return int(it), max(ex, el)
+
+
 def check_multilevel(M, SV, ST, ctx, rank, world, all_gather, nh=24, nv=24, p=2, k=2, mid_sizes=(2,), exact_size=6, deform=None):
     """The multilevel preconditioner (precond.cu) on a synthetic deformed mesh, one rank of ``world``: same solution as the
     Jacobi-preconditioned CG, clearly fewer iterations, identical counts on every rank."""

@@ -81,3 +81,10 @@ def test_peer_exchange_schur_cg(emu, world):
 def test_multilevel(emu, world):
     res = run_ranks(emu, world, P.check_multilevel)
     assert all(r == res[0] for r in res)
+
+
+@pytest.mark.parametrize("world", [1, 2, 4])
+def test_peer_exchange_bicgstab(emu, world):
+    """BiCGStab on a non-symmetric (advection-diffusion) system, partitioned into strips, against a direct sparse solve"""
+    res = run_ranks(emu, world, P.check_partitioned_bicgstab)
+    assert all(r[0] == res[0][0] for r in res)
