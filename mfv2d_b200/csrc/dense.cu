@@ -165,6 +165,31 @@ __global__ void __launch_bounds__(DENSE_THREADS) inverse_kernel(int n, unsigned 
 // shared-memory reads for RA x CB fused multiply-adds per thread, where inverse_kernel pays three reads and a write per
 // FMA.  Row swaps are undone as a column permutation when the inverse is written out.  Pivot test of
 // decompose_pivoted_lu (src/algebra/matrix.c:454-457): |pivot| < 1e-12 -> MFV2D_PIVOT_FAILED.
+// CTA-uniform dispatch on a run-time index in [0, N), N <= 8: BODY sees the index as the compile-time constant I, so a row
+// or column of the register tile is addressed directly.  (A predicated loop over all N candidates costs N times the
+// instructions: with it a Gauss-Jordan step was 566 warp instructions for 32 FMAs per thread.)
+#define UNIFORM_CASE(idx, N, C, BODY)                                                                                            \
+    else if ((C) < (N) && (idx) == (C))                                                                                          \
+    {                                                                                                                            \
+        constexpr int I = (C) < (N) ? (C) : 0;                                                                                   \
+        BODY                                                                                                                     \
+    }
+#define UNIFORM_SWITCH(idx, N, BODY)                                                                                             \
+    do                                                                                                                           \
+    {                                                                                                                            \
+        if (false)                                                                                                               \
+        {                                                                                                                        \
+        }                                                                                                                        \
+        UNIFORM_CASE(idx, N, 0, BODY)                                                                                            \
+        UNIFORM_CASE(idx, N, 1, BODY)                                                                                            \
+        UNIFORM_CASE(idx, N, 2, BODY)                                                                                            \
+        UNIFORM_CASE(idx, N, 3, BODY)                                                                                            \
+        UNIFORM_CASE(idx, N, 4, BODY)                                                                                            \
+        UNIFORM_CASE(idx, N, 5, BODY)                                                                                            \
+        UNIFORM_CASE(idx, N, 6, BODY)                                                                                            \
+        UNIFORM_CASE(idx, N, 7, BODY)                                                                                            \
+    } while (0)
+
 template <int TI, int RA, int CB>
 __global__ void __launch_bounds__(TI * 16) inverse_reg_kernel(int n, unsigned long long batch, const double *__restrict__ in,
                                                              double *__restrict__ out, int32_t *__restrict__ status)
@@ -187,9 +212,18 @@ __global__ void __launch_bounds__(TI * 16) inverse_reg_kernel(int n, unsigned lo
                 e[a][b] = (i < n && j < n) ? src[(size_t)i * n + j] : (i == j ? 1.0 : 0.0); // identity padding
             }
         int bad = 0;
-        for (int k = 0; k < n; ++k)
+        // the 16 pivots of one column group share the register column kb (and, TI being 16 or 32, the register row ka): the
+        // outer loop is unrolled so that both are compile-time constants and the pivot column / pivot row of the tile are
+        // addressed directly - only the row of the pivot ELEMENT (ra) is a run-time index
+        static_assert(TI % 16 == 0, "ka must be constant over a column group");
+#pragma unroll
+        for (int kb = 0; kb < CB; ++kb)
+        for (int ktj = 0; ktj < 16; ++ktj)
         {
-            const int kb = k >> 4, ktj = k & 15, ka = k / TI, kti = k - ka * TI;
+            const int k = 16 * kb + ktj;
+            if (k >= n)
+                break;
+            const int ka = (16 * kb) / TI, kti = k - ka * TI;
             // 1. pivot search in column k, rows >= k: the 16-lane column owners propose, everybody picks the winner
             if (tj == ktj)
             {
@@ -199,11 +233,7 @@ __global__ void __launch_bounds__(TI * 16) inverse_reg_kernel(int n, unsigned lo
                 for (int a = 0; a < RA; ++a)
                 {
                     const int i = ti + TI * a;
-                    double v = 0.0;
-#pragma unroll
-                    for (int b = 0; b < CB; ++b)
-                        if (b == kb)
-                            v = fabs(e[a][b]);
+                    const double v = fabs(e[a][kb]);
                     if (i >= k && i < n && v > best)
                     {
                         best = v;
@@ -241,31 +271,22 @@ __global__ void __launch_bounds__(TI * 16) inverse_reg_kernel(int n, unsigned lo
             // 2. rows k and r and the (pre-swap) pivot column through shared memory: row_a = old row r (the new pivot row),
             //    row_b = old row k
             if (ti == rti)
+                UNIFORM_SWITCH(ra, RA, {
+#pragma unroll
+                    for (int b = 0; b < CB; ++b)
+                        row_a[tj + TJ * b] = e[I][b];
+                });
+            if (ti == kti && r != k)
             {
 #pragma unroll
-                for (int a = 0; a < RA; ++a)
-                    if (a == ra)
-#pragma unroll
-                        for (int b = 0; b < CB; ++b)
-                            row_a[tj + TJ * b] = e[a][b];
-            }
-            if (ti == kti)
-            {
-#pragma unroll
-                for (int a = 0; a < RA; ++a)
-                    if (a == ka)
-#pragma unroll
-                        for (int b = 0; b < CB; ++b)
-                            row_b[tj + TJ * b] = e[a][b];
+                for (int b = 0; b < CB; ++b)
+                    row_b[tj + TJ * b] = e[ka][b];
             }
             if (tj == ktj)
             {
 #pragma unroll
                 for (int a = 0; a < RA; ++a)
-#pragma unroll
-                    for (int b = 0; b < CB; ++b)
-                        if (b == kb)
-                            colk[ti + TI * a] = e[a][b];
+                    colk[ti + TI * a] = e[a][kb];
             }
             __syncthreads();
             if (r != k)
@@ -273,25 +294,20 @@ __global__ void __launch_bounds__(TI * 16) inverse_reg_kernel(int n, unsigned lo
                 if (ti == kti)
                 {
 #pragma unroll
-                    for (int a = 0; a < RA; ++a)
-                        if (a == ka)
-#pragma unroll
-                            for (int b = 0; b < CB; ++b)
-                                e[a][b] = row_a[tj + TJ * b];
+                    for (int b = 0; b < CB; ++b)
+                        e[ka][b] = row_a[tj + TJ * b];
                 }
                 if (ti == rti)
-                {
+                    UNIFORM_SWITCH(ra, RA, {
 #pragma unroll
-                    for (int a = 0; a < RA; ++a)
-                        if (a == ra)
-#pragma unroll
-                            for (int b = 0; b < CB; ++b)
-                                e[a][b] = row_b[tj + TJ * b];
-                }
+                        for (int b = 0; b < CB; ++b)
+                            e[I][b] = row_b[tj + TJ * b];
+                    });
             }
-            // 4. Gauss-Jordan update of the whole block in registers
+            // 4. Gauss-Jordan update of the whole block in registers: the plain rank-one update everywhere, then the pivot
+            //    column (f) and the pivot row (row * 1 / pivot, 1 / pivot on the diagonal) are overwritten
             const double ip = 1.0 / row_a[k];
-            double rk[CB];
+            double rk[CB], f[RA];
 #pragma unroll
             for (int b = 0; b < CB; ++b)
                 rk[b] = row_a[tj + TJ * b];
@@ -299,20 +315,22 @@ __global__ void __launch_bounds__(TI * 16) inverse_reg_kernel(int n, unsigned lo
             for (int a = 0; a < RA; ++a)
             {
                 const int i = ti + TI * a;
-                const double f = -colk[i == k ? r : (i == r ? k : i)] * ip; // the column was published before the swap
+                f[a] = -colk[i == k ? r : (i == r ? k : i)] * ip; // the column was published before the swap
 #pragma unroll
                 for (int b = 0; b < CB; ++b)
-                {
-                    const int j = tj + TJ * b;
-                    double v;
-                    if (i == k)
-                        v = (j == k) ? ip : rk[b] * ip;
-                    else if (j == k)
-                        v = f;
-                    else
-                        v = fma(f, rk[b], e[a][b]);
-                    e[a][b] = v;
-                }
+                    e[a][b] = fma(f[a], rk[b], e[a][b]);
+            }
+            if (tj == ktj)
+            {
+#pragma unroll
+                for (int a = 0; a < RA; ++a)
+                    e[a][kb] = f[a];
+            }
+            if (ti == kti)
+            {
+#pragma unroll
+                for (int b = 0; b < CB; ++b)
+                    e[ka][b] = (tj + TJ * b == k) ? ip : rk[b] * ip;
             }
             // colk / row_a / row_b are read here and rewritten after the NEXT step's first barrier; cand_* are rewritten before
             // it, but were last read before this step's second barrier: two barriers per pivot are enough
