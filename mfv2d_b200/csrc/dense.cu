@@ -197,6 +197,7 @@ __global__ void __launch_bounds__(TI * 16) inverse_reg_kernel(int n, unsigned lo
     constexpr int TJ = 16, NT = TI * TJ;
     __shared__ double colk[TI * RA], row_a[TJ * CB], row_b[TJ * CB], cand_v[TI];
     __shared__ int cand_i[TI], piv[TI * RA], cperm[TJ * CB], cinv[TJ * CB];
+    __shared__ double ip_s;
     const int tj = threadIdx.x & 15, ti = threadIdx.x >> 4;
     const size_t nn = (size_t)n * n;
     for (unsigned long long blk = blockIdx.x; blk < batch; blk += gridDim.x)
@@ -244,26 +245,22 @@ __global__ void __launch_bounds__(TI * 16) inverse_reg_kernel(int n, unsigned lo
                 cand_i[ti] = bi;
             }
             __syncthreads();
-            // every warp reduces the TI candidates by itself (no second barrier, no serial scan)
+            // every warp reduces the TI candidates by itself (no second barrier, no serial scan): non-negative doubles order
+            // like their bit patterns, so the arg-max is three hardware warp reductions (REDUX) - largest high word, largest
+            // low word among those, smallest row index among the winners (the tie rule of the shuffle version it replaces)
             int r;
             {
                 const int lane = threadIdx.x & 31;
-                double best = lane < TI ? cand_v[lane] : -2.0;
-                int bi = lane < TI ? cand_i[lane] : 0x7fffffff;
-#pragma unroll
-                for (int o = 16; o > 0; o >>= 1)
-                {
-                    const double ov = __shfl_xor_sync(0xffffffffu, best, o);
-                    const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-                    if (ov > best || (ov == best && oi < bi))
-                    {
-                        best = ov;
-                        bi = oi;
-                    }
-                }
+                const double cv = lane < TI ? cand_v[lane] : -1.0;
+                const unsigned ci = lane < TI ? (unsigned)cand_i[lane] : 0x7fffffffu;
+                const bool valid = cv >= 0.0; // false for the "no row" sentinel and for NaN
+                const unsigned hi = valid ? (unsigned)__double2hiint(cv) : 0u, lo = valid ? (unsigned)__double2loint(cv) : 0u;
+                const unsigned mh = __reduce_max_sync(0xffffffffu, hi);
+                const unsigned ml = __reduce_max_sync(0xffffffffu, hi == mh ? lo : 0u);
+                r = (int)__reduce_min_sync(0xffffffffu, (hi == mh && lo == ml) ? ci : 0x7fffffffu);
+                const double best = __hiloint2double((int)mh, (int)ml);
                 if (!(best >= PIVOT_TOL))
                     bad = 1;
-                r = bi;
                 if (threadIdx.x == 0)
                     piv[k] = r;
             }
@@ -275,6 +272,8 @@ __global__ void __launch_bounds__(TI * 16) inverse_reg_kernel(int n, unsigned lo
 #pragma unroll
                     for (int b = 0; b < CB; ++b)
                         row_a[tj + TJ * b] = e[I][b];
+                    if (tj == ktj)
+                        ip_s = 1.0 / e[I][kb]; // one division per pivot instead of one per thread
                 });
             if (ti == kti && r != k)
             {
@@ -306,7 +305,7 @@ __global__ void __launch_bounds__(TI * 16) inverse_reg_kernel(int n, unsigned lo
             }
             // 4. Gauss-Jordan update of the whole block in registers: the plain rank-one update everywhere, then the pivot
             //    column (f) and the pivot row (row * 1 / pivot, 1 / pivot on the diagonal) are overwritten
-            const double ip = 1.0 / row_a[k];
+            const double ip = ip_s;
             double rk[CB], f[RA];
 #pragma unroll
             for (int b = 0; b < CB; ++b)
