@@ -834,6 +834,30 @@ static int plan_lower_vector_fused(mfv2d_plan *plan)
     fv.off_rowC = put(rowC);
     fv.off_yrow = put(yrow);
     fv.off_contrib = put(contrib);
+    {
+        // fast output stage: when no row has more than two contributions, every row gets a fixed record of two
+        // (coefficient, four 16-bit addresses); unused addresses point at the slot's zero cell, so the kernel needs neither
+        // the loop over the contributions nor the incidence branch
+        bool two = true;
+        for (int k = 0; k < N && two; ++k)
+            two = per_row[k].size() >= 1 && per_row[k].size() <= 2;
+        fv.off_yfast = -1;
+        if (two)
+        {
+            std::vector<int32_t> yfast;
+            auto pack = [](int32_t lo, int32_t hi) { return (int32_t)(((uint32_t)lo & 0xffffu) | ((uint32_t)hi << 16)); };
+            for (int k = 0; k < N; ++k)
+            {
+                const auto &c0 = per_row[k][0];
+                const bool has1 = per_row[k].size() > 1;
+                const auto &c1 = per_row[k][has1 ? 1 : 0];
+                const int32_t z = (int32_t)zero_cell;
+                yfast.insert(yfast.end(), {c0[0], pack(c0[1], c0[2]), pack(c0[3], c0[4]), c1[0], has1 ? pack(c1[1], c1[2]) : pack(z, z),
+                                           has1 ? pack(c1[3], c1[4]) : pack(z, z), 0, 0});
+            }
+            fv.off_yfast = put(yfast);
+        }
+    }
     while (blob.size() & 3)
         blob.push_back(0);
     fv.blob_ints = (int)blob.size();
@@ -856,8 +880,43 @@ struct FusedArgs
     FusedVecInfo fv;
     const int32_t *blob;
     int n_coef, inc_rows;
-    int epb; // elements per pass
+    int epb;  // elements per pass
+    int bulk; // x of a pass arrives by cp.async.bulk (one 1-D bulk copy per element, mbarrier completion) instead of 8-byte cp.async
 };
+
+#ifndef MFV2D_EMU
+// ---- 1-D bulk copies global -> shared with mbarrier completion (TMA engine, SASS UBLKCP) ----------------------------
+__device__ __forceinline__ void mbar_init(unsigned long long *bar, int count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long *bar, unsigned bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void *smem_dst, const void *gmem_src, unsigned bytes, unsigned long long *bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     (unsigned)__cvta_generic_to_shared(smem_dst)),
+                 "l"(gmem_src), "r"(bytes), "r"((unsigned)__cvta_generic_to_shared(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned parity)
+{
+    asm volatile("{\n"
+                 ".reg .pred P1;\n"
+                 "LAB_WAIT:\n"
+                 "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+                 "@P1 bra DONE;\n"
+                 "bra LAB_WAIT;\n"
+                 "DONE:\n"
+                 "}\n" ::"r"((unsigned)__cvta_generic_to_shared(bar)),
+                 "r"(parity)
+                 : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+#endif
+
 
 __device__ __forceinline__ double signed_gather(const int4 m, const double *__restrict__ src)
 {
@@ -1198,6 +1257,14 @@ template <int Q> __global__ void __launch_bounds__(APPLYT_THREADS, 2) element_ve
 
     // x of a pass and its corners are copied global -> shared asynchronously (no registers in flight): issued
     // right after phase A of the previous pass (x is dead from there on; the corners are double buffered)
+#ifndef MFV2D_EMU
+    __shared__ unsigned long long x_bar; // completion of the bulk copies of one pass (phase = pass parity)
+    if (fa.bulk && threadIdx.x == 0)
+    {
+        mbar_init(&x_bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+#endif
     auto prefetch = [&](unsigned long long grp, int parity) {
         if (grp >= n_groups)
             return;
@@ -1205,6 +1272,21 @@ template <int Q> __global__ void __launch_bounds__(APPLYT_THREADS, 2) element_ve
         const int nv = (int)((args.n_elem - elem0) < (unsigned long long)epb ? (args.n_elem - elem0) : epb);
         for (int i = threadIdx.x; i < nv * 8; i += blockDim.x)
             cp_async8(slots + SLOT(i >> 3) + parity * 8 + (i & 7), args.corners + elem0 * 8 + i);
+#ifndef MFV2D_EMU
+        if (fa.bulk)
+        {
+            // one thread arms the barrier with the byte count of the pass and issues one 1-D bulk copy per element (N * 8 bytes,
+            // 16-byte aligned on both sides): 25 instructions instead of 3 000 8-byte cp.async, none of them on the LSU
+            if (threadIdx.x == 0)
+            {
+                fence_proxy_async(); // the slots were last touched through the generic proxy (phase A of this pass)
+                mbar_expect_tx(&x_bar, (unsigned)(nv * N * 8));
+                for (int e = 0; e < nv; ++e)
+                    bulk_g2s(slots + SLOT(e) + off_xs, args.x + (elem0 + e) * N, (unsigned)(N * 8), &x_bar);
+            }
+            return;
+        }
+#endif
         for (int i = threadIdx.x; i < nv * N; i += blockDim.x)
         {
             const int e = (int)(((float)i + 0.5f) * inv_n);
@@ -1244,7 +1326,11 @@ template <int Q> __global__ void __launch_bounds__(APPLYT_THREADS, 2) element_ve
         const unsigned long long elem0 = grp * epb;
         const int nv = (int)((args.n_elem - elem0) < (unsigned long long)epb ? (args.n_elem - elem0) : epb);
         cp_async_wait_all();
-        __syncthreads(); // x / corners of this pass have landed; the previous pass is done with the t rows
+        __syncthreads(); // corners (and x, 8-byte path) of this pass have landed; the previous pass is done with the t rows
+#ifndef MFV2D_EMU
+        if (fa.bulk)
+            mbar_wait(&x_bar, (unsigned)parity); // x of this pass: the bulk copies have completed their bytes
+#endif
         // ---- phase A: t[row][:] = sum_j c[j] B_j[:], rows of the same table two at a time ----
         {
             // lanes = consecutive elements of ONE row pair: descriptors, tables and branches are warp uniform
@@ -1307,6 +1393,20 @@ template <int Q> __global__ void __launch_bounds__(APPLYT_THREADS, 2) element_ve
         }
         __syncthreads();
         // ---- post: y[k] = sum over the terms of coef * (signed sum of up to four outputs), stored to HBM ----
+        if (fv.off_yfast >= 0)
+        {
+            const int4 *yf = reinterpret_cast<const int4 *>(blob + fv.off_yfast);
+            for (int i = threadIdx.x; i < nv * N; i += blockDim.x)
+            {
+                const int e = (int)(((float)i + 0.5f) * inv_n), k = i - e * N;
+                const double *slot = slots + SLOT(e);
+                const int4 d0 = yf[2 * k], d1 = yf[2 * k + 1];
+                const double v0 = (slot[d0.y & 0xffff] + slot[(unsigned)d0.y >> 16]) - (slot[d0.z & 0xffff] + slot[(unsigned)d0.z >> 16]);
+                const double v1 = (slot[d1.x & 0xffff] + slot[(unsigned)d1.x >> 16]) - (slot[d1.y & 0xffff] + slot[(unsigned)d1.y >> 16]);
+                args.y[elem0 * N + i] = fma(coef[d0.w], v1, coef[d0.x] * v0);
+            }
+            continue;
+        }
         for (int i = threadIdx.x; i < nv * N; i += blockDim.x)
         {
             const int e = (int)(((float)i + 0.5f) * inv_n), k = i - e * N;
@@ -1344,6 +1444,12 @@ template <int Q> static int launch_fused_q(mfv2d_ctx *ctx, FusedArgs &fa, size_t
     if (epb < 1)
         epb = 1;
     fa.epb = epb;
+    {
+        // bulk copies need 16-byte alignment of every element's x (N even), of the slot position of x and of the buffer
+        const char *env = getenv("MFV2D_APPLY_BULK");
+        fa.bulk = !(env && env[0] == '0') && (fa.a.n_total % 2 == 0) && (fa.fv.off_vec % 2 == 0) && (fa.fv.slot_doubles % 2 == 0) &&
+                  ((size_t)fa.a.x % 16 == 0) && (fixed_bytes % 16 == 0);
+    }
     const size_t smem = fixed_bytes + (size_t)epb * slot_bytes;
     if (smem > ctx->smem_optin)
         return -1; // the caller falls back to the term-by-term kernel

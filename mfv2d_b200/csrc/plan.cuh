@@ -192,6 +192,7 @@ struct FusedVecInfo
     int off_pre, off_rowA, off_termB, off_rowC, off_yrow, off_contrib; // ints, each a multiple of 4
     int blob_ints;
     int off_vec, off_t, slot_doubles; // slot: corners[8] | in / out vectors (aliased) | t rows
+    int off_yfast;                    // -1, or 8 ints per output row: two branch-free contributions (every row has at most two)
 };
 
 struct mfv2d_plan
