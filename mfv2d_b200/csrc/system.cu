@@ -835,57 +835,54 @@ int mfv2d_cuda_system_create(mfv2d_ctx *ctx, size_t n_elem, const int64_t *block
             s->uniform = false;
     }
     // ---- constraint structure (host) ----
-    // validate ordering and bounds; build CSR of N, CSR of N^T, and the per-element local rows
-    std::vector<int64_t> n_ptr(n_trace + 1, 0), t_ptr(s->n_dense + 1, 0);
-    for (size_t k = 0; k < n_con; ++k)
-    {
-        if (con_row[k] < 0 || (size_t)con_row[k] >= n_trace || con_col[k] < 0 || con_col[k] >= s->n_dense)
-            SYS_TRY(mfv2d_fail(ctx, MFV2D_INDEX_OUT_OF_RANGE, "system_create: constraint entry %zu is out of range", k));
-        if (k && (con_row[k] < con_row[k - 1] || (con_row[k] == con_row[k - 1] && con_col[k] <= con_col[k - 1])))
-            SYS_TRY(mfv2d_fail(ctx, MFV2D_BAD_ARGUMENT, "system_create: constraint entries must be sorted by (row, column) without duplicates"));
-        n_ptr[con_row[k] + 1]++;
-        t_ptr[con_col[k] + 1]++;
-    }
-    for (size_t i = 0; i < n_trace; ++i)
-        n_ptr[i + 1] += n_ptr[i];
-    for (int64_t i = 0; i < s->n_dense; ++i)
-        t_ptr[i + 1] += t_ptr[i];
-    std::vector<int64_t> n_col(con_col, con_col + n_con), t_col(n_con);
-    std::vector<double> n_val(con_val, con_val + n_con), t_val(n_con);
-    {
-        std::vector<int64_t> fill(t_ptr.begin(), t_ptr.end() - 1);
-        for (size_t k = 0; k < n_con; ++k)
-        {
-            const int64_t pos = fill[con_col[k]]++;
-            t_col[pos] = con_row[k];
-            t_val[pos] = con_val[k];
-        }
-    }
-    // element of each entry; slots = (element, multiplier) pairs in (element, multiplier) order
-    std::vector<int64_t> elem_of(n_con);
+    // validate ordering and bounds; build CSR of N, CSR of N^T, and the per-element local rows.  Every pass below is
+    // sequential or works on cache-resident pieces: the entries are first grouped by element (one counting sort), then N^T and
+    // the local rows are built element by element - a histogram over all n_dense columns with random increments costs 5x
+    // the time (15 M columns for 125 k order-6 elements).
+    std::vector<int64_t> n_ptr(n_trace + 1, 0);
+    const int64_t ne0 = n_elem ? boff[1] - boff[0] : 1;
+    std::vector<int32_t> elem_of(n_con);
+    std::vector<int64_t> ecount(n_elem + 1, 0);
     {
         size_t e = 0;
-        // columns are not monotone over k, so search
         for (size_t k = 0; k < n_con; ++k)
         {
             const int64_t c = con_col[k];
-            if (!(e < n_elem && boff[e] <= c && c < boff[e + 1]))
+            if (con_row[k] < 0 || (size_t)con_row[k] >= n_trace || c < 0 || c >= s->n_dense)
+                SYS_TRY(mfv2d_fail(ctx, MFV2D_INDEX_OUT_OF_RANGE, "system_create: constraint entry %zu is out of range", k));
+            if (k && (con_row[k] < con_row[k - 1] || (con_row[k] == con_row[k - 1] && c <= con_col[k - 1])))
+                SYS_TRY(mfv2d_fail(ctx, MFV2D_BAD_ARGUMENT, "system_create: constraint entries must be sorted by (row, column) without duplicates"));
+            n_ptr[con_row[k] + 1]++;
+            if (s->uniform)
+                e = (size_t)(c / ne0);
+            else if (!(e < n_elem && boff[e] <= c && c < boff[e + 1])) // columns are not monotone over k, so search
                 e = (size_t)(std::upper_bound(boff.begin(), boff.end(), c) - boff.begin()) - 1;
-            elem_of[k] = (int64_t)e;
+            elem_of[k] = (int32_t)e;
+            ecount[e + 1]++;
         }
     }
-    // order entries by (element, row, col): stable counting sort by element keeps (row, col) order
-    std::vector<int64_t> ecount(n_elem + 1, 0);
-    for (size_t k = 0; k < n_con; ++k)
-        ecount[elem_of[k] + 1]++;
+    for (size_t i = 0; i < n_trace; ++i)
+        n_ptr[i + 1] += n_ptr[i];
     for (size_t e = 0; e < n_elem; ++e)
         ecount[e + 1] += ecount[e];
-    std::vector<int64_t> order(n_con);
+    std::vector<int64_t> n_col(con_col, con_col + n_con);
+    std::vector<double> n_val(con_val, con_val + n_con);
+    // entries grouped by element in (row, col) order (stable counting sort); the grouped copies make every later pass sequential
+    std::vector<int64_t> g_row(n_con);
+    std::vector<int32_t> g_lcol(n_con);
+    std::vector<double> g_val(n_con);
     {
         std::vector<int64_t> fill(ecount.begin(), ecount.end() - 1);
         for (size_t k = 0; k < n_con; ++k)
-            order[fill[elem_of[k]]++] = (int64_t)k;
+        {
+            const int32_t e = elem_of[k];
+            const int64_t pos = fill[e]++;
+            g_row[pos] = con_row[k];
+            g_lcol[pos] = (int32_t)(con_col[k] - boff[e]);
+            g_val[pos] = con_val[k];
+        }
     }
+    std::vector<int32_t>().swap(elem_of);
     // Row equilibration of the CONDENSED system only: S' = D S D with D = 2^-round(log2 max|row of N|) (exact scaling).  The
     // hanging-side rows of non-conforming meshes carry coefficients up to 1e8 (inverse interpolation matrices,
     // python/mfv2d/continuity.py:256-265), which would put 16 orders of magnitude between the entries of S and make the
@@ -899,38 +896,63 @@ int mfv2d_cuda_system_create(mfv2d_ctx *ctx, size_t n_elem, const int64_t *block
         for (size_t k = 0; k < n_con; ++k)
             mx[con_row[k]] = std::max(mx[con_row[k]], std::fabs(con_val[k]));
         for (size_t i = 0; i < n_trace; ++i)
-            if (mx[i] > 0.0 && std::isfinite(mx[i]))
+            if (mx[i] > 0.0 && std::isfinite(mx[i]) && mx[i] != 1.0)
             {
                 rs[i] = std::ldexp(1.0, -(int)std::lround(std::log2(mx[i])));
                 if (rs[i] != 1.0)
                     s->scaled = true;
             }
     }
+    // element by element: the local rows (slots) and the element's rows of N^T (its dense columns, entries by multiplier)
     std::vector<int64_t> slot_off(n_elem + 1, 0), slot_trace, lrow_ptr(1, 0);
     std::vector<int32_t> lrow_col(n_con);
     std::vector<double> lrow_val(n_con);
-    for (size_t e = 0; e < n_elem; ++e)
+    std::vector<int64_t> t_ptr(s->n_dense + 1), t_col(n_con);
+    std::vector<double> t_val(n_con);
+    slot_trace.reserve(n_con);
+    lrow_ptr.reserve(n_con + 1);
     {
-        int64_t prev_row = -1;
-        for (int64_t a = ecount[e]; a < ecount[e + 1]; ++a)
+        std::vector<int64_t> cnt((size_t)s->max_n + 1);
+        t_ptr[0] = 0;
+        for (size_t e = 0; e < n_elem; ++e)
         {
-            const int64_t k = order[a];
-            if (con_row[k] != prev_row)
+            const int64_t lo = ecount[e], hi = ecount[e + 1];
+            const int ne = (int)(boff[e + 1] - boff[e]);
+            int64_t prev_row = -1;
+            std::fill(cnt.begin(), cnt.begin() + ne + 1, (int64_t)0);
+            for (int64_t a = lo; a < hi; ++a)
             {
-                if (prev_row >= 0)
-                    lrow_ptr.push_back(a);
-                slot_trace.push_back(con_row[k]);
-                prev_row = con_row[k];
+                if (g_row[a] != prev_row)
+                {
+                    if (prev_row >= 0)
+                        lrow_ptr.push_back(a);
+                    slot_trace.push_back(g_row[a]);
+                    prev_row = g_row[a];
+                }
+                lrow_col[a] = g_lcol[a];
+                lrow_val[a] = g_val[a] * rs[g_row[a]];
+                cnt[g_lcol[a] + 1]++;
             }
-            lrow_col[a] = (int32_t)(con_col[k] - boff[e]);
-            lrow_val[a] = con_val[k] * rs[con_row[k]];
+            if (prev_row >= 0)
+                lrow_ptr.push_back(hi);
+            slot_off[e + 1] = (int64_t)slot_trace.size();
+            const int m = (int)(slot_off[e + 1] - slot_off[e]);
+            if (m > s->max_m)
+                s->max_m = m;
+            // N^T rows boff[e] .. boff[e + 1]: entries of one column keep their multiplier order (the grouped order is by row)
+            const int64_t base = t_ptr[boff[e]];
+            for (int c = 0; c < ne; ++c)
+            {
+                cnt[c + 1] += cnt[c];
+                t_ptr[boff[e] + c + 1] = base + cnt[c + 1];
+            }
+            for (int64_t a = lo; a < hi; ++a)
+            {
+                const int64_t pos = base + cnt[g_lcol[a]]++;
+                t_col[pos] = g_row[a];
+                t_val[pos] = g_val[a];
+            }
         }
-        if (prev_row >= 0)
-            lrow_ptr.push_back(ecount[e + 1]);
-        slot_off[e + 1] = (int64_t)slot_trace.size();
-        const int m = (int)(slot_off[e + 1] - slot_off[e]);
-        if (m > s->max_m)
-            s->max_m = m;
     }
     s->n_slots = (int64_t)slot_trace.size();
     std::vector<int64_t> tr_ptr(n_trace + 1, 0), tr_slot(s->n_slots);
