@@ -1062,7 +1062,12 @@ int mfv2d_cuda_system_create(mfv2d_ctx *ctx, size_t n_elem, const int64_t *block
         SYS_TRY(sys_alloc(s, (size_t)s->n_trace, &s->d_work_trace[i]));
     SYS_TRY(sys_alloc(s, (size_t)64, &s->d_cg));
     cudaMemsetAsync(s->d_cg, 0, 64 * sizeof(double), ctx->stream);
-    s->n_partials = ctx->sm_count * 4;
+    {
+        // CTAs of the vector kernels of the Krylov solvers (= partial sums of their dot products) per SM
+        const char *env = getenv("MFV2D_CG_CTAS_PER_SM");
+        const int per_sm = env ? atoi(env) : 4;
+        s->n_partials = ctx->sm_count * (per_sm >= 1 && per_sm <= 16 ? per_sm : 4);
+    }
     SYS_TRY(sys_alloc(s, (size_t)3 * s->n_partials, &s->d_partials));
     tick("allocations");
     // ---- factorise: explicit inverses of the dense blocks ----
