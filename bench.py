@@ -527,15 +527,11 @@ def run_ours(args):
         c6[:, :, 0], c6[:, :, 1], c6[:, :, 2], c6[:, :, 3] = pts[:-1, :-1], pts[:-1, 1:], pts[1:, 1:], pts[1:, :-1]
         c6 = np.ascontiguousarray(c6.reshape(-1, 4, 2))
         n6 = c6.shape[0]
-        row, col, val, nt_glob = ST.continuity_constraints_1form(nh, nv, p6, s_orders)
-        bounds = [parts[r][0] * ne6 for r in range(world)] + [parts[-1][1] * ne6]
-        part = ST.partition_constraints(row, col, val, nt_glob, bounds, rank)
-        del row, col, val
-        strip_rows = [parts[r][0] // nh for r in range(world)] + [nv]
+        # this rank's constraint rows, interface lists and aggregate hierarchy straight from the closed form of the reference's
+        # row order: O(strip) per rank (the global builder + partition_constraints give the same arrays, tests/test_distributed.py)
         mids = tuple(int(v) for v in args.solve_mid.split(",") if v)
-        agg, zc, n_agg = ST.coarse_hierarchy_1form(nh, nv, p6, s_orders, mids, args.solve_agg, strip_rows)
-        hier = ST.localize_hierarchy(agg, zc, n_agg, part)
-        del agg, zc
+        part, hier, nt_glob = ST.strip_system_1form(nh, nv, p6, s_orders, world, rank, mids, args.solve_agg)
+        n_agg = hier[2]
         host_s = time.perf_counter() - t_host
         if world > 1:
             ctx.init_comm(world, rank, None)  # ranks only: every exchange goes through the NVLink peer blocks, NCCL is not loaded
@@ -543,7 +539,10 @@ def run_ours(args):
         solve_batch = M.ElementBatch(basis6, ctx.to_device(c6), ctx)
         mats6 = ctx.empty((n6, ne6, ne6))
         M.compute_element_matrices(s_specs, s_lhs, solve_batch, out=mats6)
+        ctx.synchronize()
+        t_asm = time.perf_counter() - t0
         system = SV.LinearSystem(mats6, (part.row, part.col, part.val), part.n_trace, ctx)
+        t_sys = time.perf_counter() - t0 - t_asm
         if world > 1:
             system.set_interface(part.shared_index, part.slot, part.n_slots, part.owned)
 
@@ -554,7 +553,8 @@ def run_ours(args):
 
             system.connect_peers(part.holder_ptr, part.holder_rank, all_gather, n_coarse=n_agg[-1])
         ctx.synchronize()
-        setup_s = max_over_ranks(dist, time.perf_counter() - t0)
+        setup_rank0 = time.perf_counter() - t0
+        setup_s = max_over_ranks(dist, setup_rank0)
         t0 = time.perf_counter()
         system.set_coarse_space(*hier)
         ctx.synchronize()
@@ -616,7 +616,8 @@ def run_ours(args):
             "s": solve_s, "s_first_solve": times[0], "s_all_solves": times, "iterations": int(it), "us_per_iteration": solve_s / max(int(it), 1) * 1e6,
             "cg_residual": float(res), "saddle_relative_residual": saddle, "gate": 1e-10, "peer_error": bool(peer_bad),
             "elements": int(nh * nv), "dense_dofs": int(nh * nv * ne6), "multipliers": int(nt_glob), "interface_multipliers": int(part.n_slots),
-            "system_setup_s": setup_s, "preconditioner_setup_s": coarse_s, "host_mesh_constraints_partition_s": host_s,
+            "system_setup_s": setup_s, "system_setup_breakdown_rank0_s": {"assembly": t_asm, "system_create": t_sys, "interface_and_peers": max(setup_rank0 - t_asm - t_sys, 0.0)},
+            "preconditioner_setup_s": coarse_s, "host_mesh_constraints_partition_s": host_s,
             "pipeline_s": host_s + setup_s + coarse_s + times[0],
             "roofline": {"bound": "hbm", "achieved": it_bytes / (solve_s / max(int(it), 1)) / 1e9, "peak": peak, "unit": "GB/s",
                          "frac": it_bytes / (solve_s / max(int(it), 1)) / 1e9 / peak, "traffic": None, "kernel": "one CG iteration (schur_local_packed + "

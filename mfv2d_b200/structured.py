@@ -393,3 +393,108 @@ def localize_hierarchy(agg: np.ndarray, z: np.ndarray, n_agg, part: "ConstraintP
         a[keep] = compact
         counts[lvl] = int(used.size)
     return loc, np.ascontiguousarray(z[part.global_rows]), counts
+
+
+def strip_system_1form(nh: int, nv: int, p: int, form_orders, n_ranks: int, rank: int, mid_sizes=(4,), exact_size: int = 16):
+    """One rank's constraint partition AND its view of the aggregate hierarchy in time and memory proportional to the STRIP.
+
+    Equal, field by field, to ``partition_constraints(*continuity_constraints_1form(nh, nv, p, form_orders), bounds, rank)`` and
+    ``localize_hierarchy(*coarse_hierarchy_1form(nh, nv, p, form_orders, mid_sizes, exact_size, strip_rows), part)`` for the
+    strips of :func:`strip_partition` (checked in tests/test_distributed.py), but built from the closed form of the reference's
+    row order (python/mfv2d/continuity.py:610-759 on ``unit_square_mesh``) instead of from the global matrix: on the 10^6-element
+    mesh of BASELINE.json configs[4] every rank otherwise spends seconds generating and sorting 24 M global entries.
+    Systems without 0-forms only (their corner chains have no closed form here); ``exact_size >= 2`` (every aggregate of the exact
+    level then holds a multiplier).  Returns ``(part, (agg, z, n_agg), n_trace_global)``."""
+    orders = [int(o) for o in form_orders]
+    if any(o == FORM_ORDER_0 for o in orders):
+        raise ValueError("strip_system_1form: systems with 0-forms need the global builder")
+    if exact_size and exact_size < 2:
+        raise ValueError("strip_system_1form: exact_size must be at least 2")
+    offs, ne = _form_offsets(form_orders, p)
+    strip_rows = np.array([nv * r // n_ranks for r in range(n_ranks + 1)], np.int64)
+    j0, j1 = int(strip_rows[rank]), int(strip_rows[rank + 1])
+    np1, nh_edges = p + 1, p * (p + 1)
+    k = np.arange(p)[::-1]  # DoFs along a side are traversed in reverse
+    kk = np.arange(p)
+    n_h, n_v = (nv - 1) * nh, nv * (nh - 1)
+    per_form = (n_h + n_v) * p
+    n1 = sum(1 for o in orders if o == FORM_ORDER_1)
+    owner = lambda j: int(np.searchsorted(strip_rows, j, side="right") - 1)  # noqa: E731  rank that holds element row j
+    cuts = [j for j in range(1, nv) if owner(j - 1) != owner(j)]  # horizontal lines on a strip boundary, increasing
+    cut_index = {j: b for b, j in enumerate(cuts)}
+    e_rows, e_cols, e_vals = [], [], []  # entries in this rank's columns
+    m_rows, m_ei, m_ej, m_z = [], [], [], []  # one record per multiplier held here
+    s_rows, s_slot, s_other = [], [], []  # shared multipliers
+    f1 = 0
+    for f, order in enumerate(orders):
+        if order != FORM_ORDER_1:
+            continue
+        o, base = int(offs[f]), f1 * per_form
+        ja, jb = max(j0, 1), min(j1, nv - 1)
+        if jb >= ja and j1 > j0:
+            jj, ii = np.meshgrid(np.arange(ja, jb + 1), np.arange(nh), indexing="ij")
+            jj, ii = jj.ravel(), ii.ravel()
+            grow = base + (nh * (jj - 1) + ii)[:, None] * p + kk[None, :]
+            m_rows.append(grow.ravel()), m_ei.append(np.repeat(ii, p)), m_ej.append(np.repeat(jj - 1, p)), m_z.append(np.ones(grow.size))
+            below = jj - 1 >= j0  # top side of the element below: h(p, c), +1
+            e_rows.append(grow[below].ravel())
+            e_cols.append(((ii[below] + nh * (jj[below] - 1 - j0))[:, None] * ne + o + p * p + k[None, :]).ravel())
+            e_vals.append(np.ones(int(below.sum()) * p))
+            above = jj < j1  # bottom side of the element above: h(0, c), -1
+            e_rows.append(grow[above].ravel())
+            e_cols.append(((ii[above] + nh * (jj[above] - j0))[:, None] * ne + o + k[None, :]).ravel())
+            e_vals.append(-np.ones(int(above.sum()) * p))
+            for j in (j0, j1):
+                if j in cut_index and ja <= j <= jb:
+                    sel = jj == j
+                    s_rows.append(grow[sel].ravel())
+                    s_slot.append(((f1 * len(cuts) + cut_index[j]) * nh * p + ii[sel][:, None] * p + kk[None, :]).ravel())
+                    s_other.append(np.full(int(sel.sum()) * p, owner(j - 1) if j == j0 else owner(j), np.int64))
+        if j1 > j0 and nh > 1:
+            jj, ii = np.meshgrid(np.arange(j0, j1), np.arange(1, nh), indexing="ij")
+            jj, ii = jj.ravel(), ii.ravel()
+            grow = base + n_h * p + (jj * (nh - 1) + ii - 1)[:, None] * p + kk[None, :]
+            m_rows.append(grow.ravel()), m_ei.append(np.repeat(ii - 1, p)), m_ej.append(np.repeat(jj, p)), m_z.append(-np.ones(grow.size))
+            e_rows.append(grow.ravel())  # left side of the right element: v(r, 0), +1
+            e_cols.append(((ii + nh * (jj - j0))[:, None] * ne + o + nh_edges + np1 * k[None, :]).ravel())
+            e_vals.append(np.ones(grow.size))
+            e_rows.append(grow.ravel())  # right side of the left element: v(r, p), -1
+            e_cols.append(((ii - 1 + nh * (jj - j0))[:, None] * ne + o + nh_edges + np1 * k[None, :] + p).ravel())
+            e_vals.append(-np.ones(grow.size))
+        f1 += 1
+    n_trace_global = n1 * per_form
+    cat = lambda parts, dt: np.concatenate(parts).astype(dt) if parts else np.zeros(0, dt)  # noqa: E731
+    g_all = cat(m_rows, np.int64)
+    order_m = np.argsort(g_all, kind="stable")
+    g_rows = g_all[order_m]
+    ei, ej, z = cat(m_ei, np.int64)[order_m], cat(m_ej, np.int64)[order_m], cat(m_z, np.float64)[order_m]
+    rows_g, l_col, l_val = cat(e_rows, np.int64), cat(e_cols, np.int64), cat(e_vals, np.float64)
+    l_row = np.searchsorted(g_rows, rows_g)
+    order_e = np.lexsort((l_col, l_row))
+    sg, ss, so = cat(s_rows, np.int64), cat(s_slot, np.int64), cat(s_other, np.int64)
+    order_s = np.argsort(sg, kind="stable")
+    sg, ss, so = sg[order_s], ss[order_s], so[order_s]
+    sh = np.searchsorted(g_rows, sg).astype(np.int64)
+    owned = np.ones(g_rows.size, np.uint8)
+    owned[sh[so < rank]] = 0
+    part = ConstraintPartition(l_row[order_e], l_col[order_e], l_val[order_e], g_rows.size, g_rows, sh, ss, n1 * len(cuts) * nh * p, owned,
+                               np.arange(sh.size + 1, dtype=np.int64), so.astype(np.int32))
+    # hierarchy: rank-local levels (shared multipliers left out, ids compacted in key order), then the exact level with global ids
+    strip = np.searchsorted(strip_rows, ej, side="right") - 1
+    jl = ej - strip_rows[strip]
+    levels, counts = [], []
+    for H in mid_sizes:
+        key = (strip * (nv + 1) + jl // H) * (nh + 1) + ei // H
+        a = np.full(g_rows.size, -1, np.int32)
+        keep = np.ones(g_rows.size, bool)
+        keep[sh] = False
+        used, compact = np.unique(key[keep], return_inverse=True)
+        a[keep] = compact
+        levels.append(a)
+        counts.append(int(used.size))
+    if exact_size:
+        nbi = -(-nh // exact_size)
+        levels.append(((ej // exact_size) * nbi + ei // exact_size).astype(np.int32))
+        counts.append(nbi * (-(-nv // exact_size)))
+    agg = np.stack(levels) if levels else np.zeros((0, g_rows.size), np.int32)
+    return part, (agg, z, counts), n_trace_global

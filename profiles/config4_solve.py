@@ -90,10 +90,8 @@ def main():
     del x, y
 
     # ---- constraints of the GLOBAL mesh, this rank's part ----
-    row, col, val, nt_glob = ST.continuity_constraints_1form(nh, nv, p, orders)
-    bounds = [parts[r][0] * ne for r in range(world)] + [parts[-1][1] * ne]
-    part = ST.partition_constraints(row, col, val, nt_glob, bounds, rank)
-    del row, col, val
+    mids = tuple(int(v) for v in args.mid.split(",") if v)
+    part, hier, nt_glob = ST.strip_system_1form(nh, nv, p, orders, world, rank, mids, args.agg)  # O(strip): closed form of the reference's row order
     if world > 1:
         ids = [rt.comm_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(ids, src=0)
@@ -103,9 +101,7 @@ def main():
     system = SV.LinearSystem(mats, (part.row, part.col, part.val), part.n_trace, ctx)
     n_coarse = 0
     if args.precondition == "multilevel":
-        mids = tuple(int(v) for v in args.mid.split(",") if v)
-        agg, zc, n_agg = ST.coarse_hierarchy_1form(nh, nv, p, orders, mids, args.agg, [parts[r][0] // nh for r in range(world)] + [nv])
-        n_coarse = n_agg[-1]
+        n_coarse = hier[2][-1]
     if world > 1:
         system.set_interface(part.shared_index, part.slot, part.n_slots, part.owned)
 
@@ -120,7 +116,7 @@ def main():
     coarse_s = 0.0
     if n_coarse:
         t0 = time.perf_counter()
-        system.set_coarse_space(*ST.localize_hierarchy(agg, zc, n_agg, part))
+        system.set_coarse_space(*hier)
         ctx.synchronize()
         coarse_s = B.max_over_ranks(dist, time.perf_counter() - t0)
 

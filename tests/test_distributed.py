@@ -52,6 +52,30 @@ def test_partition_is_consistent():
         assert len(slots) == (world - 1) * nh * p  # p multipliers per edge on every cut (one 1-form)
 
 
+@pytest.mark.parametrize("nh,nv,p,orders,world,mids,exact", [(6, 6, 3, [2, 3], 2, (2,), 3), (7, 9, 2, [2, 3], 3, (2,), 4), (5, 8, 4, [3, 2], 4, (2,), 2),
+                                                             (8, 8, 3, [2, 3], 1, (2,), 4), (4, 12, 2, [2, 2, 3], 3, (2, 3), 4), (10, 5, 3, [2, 3], 8, (2,), 2)])
+def test_strip_local_builder_equals_global(nh, nv, p, orders, world, mids, exact):
+    """structured.strip_system_1form (closed form of the reference's row order, O(strip)) against the global path:
+    partition_constraints of the reference-ordered global matrix + localize_hierarchy, field by field, every rank
+    (including ranks with an empty strip)."""
+    from mfv2d_b200 import structured as ST
+
+    row, col, val, nt = ST.continuity_constraints_1form(nh, nv, p, orders)
+    ne = int(ST.form_sizes(orders, p).sum())
+    parts = ST.strip_partition(nh, nv, world)
+    bounds = [parts[r][0] * ne for r in range(world)] + [parts[-1][1] * ne]
+    strip_rows = [parts[r][0] // nh for r in range(world)] + [nv]
+    agg, zc, n_agg = ST.coarse_hierarchy_1form(nh, nv, p, orders, mids, exact, strip_rows)
+    for rank in range(world):
+        ref = ST.partition_constraints(row, col, val, nt, bounds, rank)
+        rl, rz, rc = ST.localize_hierarchy(agg, zc, n_agg, ref)
+        got, (gl, gz, gc), ntg = ST.strip_system_1form(nh, nv, p, orders, world, rank, mids, exact)
+        assert ntg == nt and ref.n_trace == got.n_trace and ref.n_slots == got.n_slots
+        for name in ("row", "col", "val", "global_rows", "shared_index", "slot", "owned", "holder_ptr", "holder_rank"):
+            assert np.array_equal(np.asarray(getattr(ref, name)), np.asarray(getattr(got, name))), (rank, name)
+        assert np.array_equal(rl, gl) and np.array_equal(rz, gz) and list(rc) == list(gc)
+
+
 @pytest.mark.parametrize("fix,nh,nv", [("solve_3x4_p4", 3, 4), ("solve_6x6_p3_def", 6, 6)])
 def test_gloo_world2_schur_cg(fix, nh, nv):
     _run("numpy", fix, nh, nv, 2, 29611)
