@@ -653,6 +653,56 @@ int sys_apply_trace(const mfv2d_system *s, const double *x, double *t)
     return sys_interface_sum(s, t, 0, nullptr);
 }
 
+// CSR of N^T built on the device from the per-element local rows (set-up): the rows of N^T that belong to element e are its
+// dense columns; their entries, ordered by multiplier, are the element's local-row entries bucketed by local column.  One
+// CTA per element; the histogram lives in shared memory.  (Building these arrays on the host and uploading them - 8 bytes
+// per dense DoF for t_ptr alone - was a quarter of the set-up time.)
+__global__ void __launch_bounds__(128) build_transpose_kernel(unsigned long long n_elem, const int64_t *__restrict__ block_off,
+                                                             const int64_t *__restrict__ slot_off, const int64_t *__restrict__ slot_trace,
+                                                             const int64_t *__restrict__ lrow_ptr, const int32_t *__restrict__ lrow_col,
+                                                             const double *__restrict__ lrow_val, const double *__restrict__ rs,
+                                                             int64_t *__restrict__ t_ptr, int64_t *__restrict__ t_col, double *__restrict__ t_val)
+{
+    MFV2D_DYN_SMEM(int, cnt);
+    for (unsigned long long e = blockIdx.x; e < n_elem; e += gridDim.x)
+    {
+        const int64_t b0 = block_off[e];
+        const int ne = (int)(block_off[e + 1] - b0);
+        const int64_t s0 = slot_off[e], s1 = slot_off[e + 1];
+        const int64_t a0 = lrow_ptr[s0], a1 = lrow_ptr[s1]; // the element's entries are contiguous; a0 = entries of the elements before it
+        for (int c = threadIdx.x; c <= ne; c += blockDim.x)
+            cnt[c] = 0;
+        __syncthreads();
+        for (int64_t a = a0 + threadIdx.x; a < a1; a += blockDim.x)
+            atomicAdd(&cnt[lrow_col[a] + 1], 1);
+        __syncthreads();
+        if (threadIdx.x == 0)
+        {
+            for (int c = 0; c < ne; ++c)
+                cnt[c + 1] += cnt[c];
+            if (e == 0)
+                t_ptr[0] = 0;
+        }
+        __syncthreads();
+        for (int c = threadIdx.x; c < ne; c += blockDim.x)
+            t_ptr[b0 + c + 1] = a0 + cnt[c + 1];
+        __syncthreads();
+        if (threadIdx.x == 0) // in slot (= multiplier) order, so that the entries of one column keep it
+            for (int64_t sl = s0; sl < s1; ++sl)
+            {
+                const int64_t row = slot_trace[sl];
+                const double unscale = rs ? 1.0 / rs[row] : 1.0; // rs is a power of two: exact
+                for (int64_t a = lrow_ptr[sl]; a < lrow_ptr[sl + 1]; ++a)
+                {
+                    const int64_t pos = a0 + cnt[lrow_col[a]]++;
+                    t_col[pos] = row;
+                    t_val[pos] = lrow_val[a] * unscale;
+                }
+            }
+        __syncthreads();
+    }
+}
+
 // per-element products S_e t_e -> slot_val (the big kernel of a Schur application)
 int sys_schur_local(const mfv2d_system *s, const double *t_in, const int *done)
 {
@@ -907,19 +957,13 @@ int mfv2d_cuda_system_create(mfv2d_ctx *ctx, size_t n_elem, const int64_t *block
     std::vector<int64_t> slot_off(n_elem + 1, 0), slot_trace, lrow_ptr(1, 0);
     std::vector<int32_t> lrow_col(n_con);
     std::vector<double> lrow_val(n_con);
-    std::vector<int64_t> t_ptr(s->n_dense + 1), t_col(n_con);
-    std::vector<double> t_val(n_con);
     slot_trace.reserve(n_con);
     lrow_ptr.reserve(n_con + 1);
     {
-        std::vector<int64_t> cnt((size_t)s->max_n + 1);
-        t_ptr[0] = 0;
         for (size_t e = 0; e < n_elem; ++e)
         {
             const int64_t lo = ecount[e], hi = ecount[e + 1];
-            const int ne = (int)(boff[e + 1] - boff[e]);
             int64_t prev_row = -1;
-            std::fill(cnt.begin(), cnt.begin() + ne + 1, (int64_t)0);
             for (int64_t a = lo; a < hi; ++a)
             {
                 if (g_row[a] != prev_row)
@@ -931,7 +975,6 @@ int mfv2d_cuda_system_create(mfv2d_ctx *ctx, size_t n_elem, const int64_t *block
                 }
                 lrow_col[a] = g_lcol[a];
                 lrow_val[a] = g_val[a] * rs[g_row[a]];
-                cnt[g_lcol[a] + 1]++;
             }
             if (prev_row >= 0)
                 lrow_ptr.push_back(hi);
@@ -939,19 +982,6 @@ int mfv2d_cuda_system_create(mfv2d_ctx *ctx, size_t n_elem, const int64_t *block
             const int m = (int)(slot_off[e + 1] - slot_off[e]);
             if (m > s->max_m)
                 s->max_m = m;
-            // N^T rows boff[e] .. boff[e + 1]: entries of one column keep their multiplier order (the grouped order is by row)
-            const int64_t base = t_ptr[boff[e]];
-            for (int c = 0; c < ne; ++c)
-            {
-                cnt[c + 1] += cnt[c];
-                t_ptr[boff[e] + c + 1] = base + cnt[c + 1];
-            }
-            for (int64_t a = lo; a < hi; ++a)
-            {
-                const int64_t pos = base + cnt[g_lcol[a]]++;
-                t_col[pos] = g_row[a];
-                t_val[pos] = g_val[a];
-            }
         }
     }
     s->n_slots = (int64_t)slot_trace.size();
@@ -972,9 +1002,6 @@ int mfv2d_cuda_system_create(mfv2d_ctx *ctx, size_t n_elem, const int64_t *block
     SYS_TRY(sys_upload(s, n_ptr, &s->d_n_ptr));
     SYS_TRY(sys_upload(s, n_col, &s->d_n_col));
     SYS_TRY(sys_upload(s, n_val, &s->d_n_val));
-    SYS_TRY(sys_upload(s, t_ptr, &s->d_t_ptr));
-    SYS_TRY(sys_upload(s, t_col, &s->d_t_col));
-    SYS_TRY(sys_upload(s, t_val, &s->d_t_val));
     SYS_TRY(sys_upload(s, slot_off, &s->d_slot_off));
     SYS_TRY(sys_upload(s, slot_trace, &s->d_slot_trace));
     SYS_TRY(sys_upload(s, lrow_ptr, &s->d_lrow_ptr));
@@ -984,6 +1011,27 @@ int mfv2d_cuda_system_create(mfv2d_ctx *ctx, size_t n_elem, const int64_t *block
     SYS_TRY(sys_upload(s, tr_slot, &s->d_tr_slot));
     if (s->scaled)
         SYS_TRY(sys_upload(s, rs, &s->d_rs));
+    // N^T (CSR over the dense DoFs) on the device, from the local rows
+    SYS_TRY(sys_alloc(s, (size_t)s->n_dense + 1, &s->d_t_ptr));
+    SYS_TRY(sys_alloc(s, n_con ? n_con : 1, &s->d_t_col));
+    SYS_TRY(sys_alloc(s, n_con ? n_con : 1, &s->d_t_val));
+    if (n_elem)
+    {
+        long long grid = (long long)ctx->sm_count * 16;
+        if (grid > (long long)n_elem)
+            grid = (long long)n_elem;
+        const size_t smem = (size_t)(s->max_n + 2) * sizeof(int);
+        if (smem > 48 * 1024)
+            SYS_TRY(mfv2d_fail(ctx, MFV2D_CUDA_UNSUPPORTED, "system_create: blocks of %d rows exceed the shared memory of the transpose kernel", s->max_n));
+        MFV2D_LAUNCH(build_transpose_kernel, (unsigned)grid, 128, smem, ctx->stream, (unsigned long long)n_elem, s->d_block_off, s->d_slot_off,
+                     s->d_slot_trace, s->d_lrow_ptr, s->d_lrow_col, s->d_lrow_val, s->scaled ? (const double *)s->d_rs : (const double *)nullptr,
+                     s->d_t_ptr, s->d_t_col, s->d_t_val);
+        ctx->launches++;
+        if (cudaGetLastError() != cudaSuccess)
+            SYS_TRY(mfv2d_fail(ctx, MFV2D_CUDA_ERROR, "system_create: transpose kernel launch failed"));
+    }
+    else
+        cudaMemsetAsync(s->d_t_ptr, 0, sizeof(int64_t), ctx->stream);
     {
         // conforming meshes: at most two elements per multiplier -> a fixed-width 32-bit table for the CG's gather kernel
         bool two = s->n_slots < (int64_t)1 << 31;

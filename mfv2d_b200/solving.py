@@ -277,20 +277,23 @@ class LinearSystem:
 PRECONDITIONERS = {False: 0, None: 0, "none": 0, True: 1, "jacobi": 1, "multilevel": 2}
 
 
-def solve_schur_iterative(system: LinearSystem, rhs, constraints, convergence: ConvergenceSettings, precondition=False):
+def solve_schur_iterative(system: LinearSystem, rhs, constraints, convergence: ConvergenceSettings, precondition=False, out=None):
     """python/mfv2d/solving.py:439-500: CG on ``N A^-1 N^T`` for the multipliers, then back substitution.
     Returns ``(x, lambda, residual, iterations)`` like the reference.  ``precondition``: ``False`` (the reference's
-    method), ``True`` / ``"jacobi"``, or ``"multilevel"`` (Jacobi + aggregate hierarchy, see ``LinearSystem.set_coarse_space``)."""
+    method), ``True`` / ``"jacobi"``, or ``"multilevel"`` (Jacobi + aggregate hierarchy, see ``LinearSystem.set_coarse_space``).
+    ``out=(x, lambda)``: buffers for the solution (e.g. page-locked arrays of ``Context.pinned`` on the host-buffer path)."""
     if isinstance(rhs, _SystemVector):  # DenseVector / TraceVector in and out, like the reference
         xd, ld, r, i = solve_schur_iterative(system, rhs.data, constraints.data, convergence, precondition)
         return DenseVector.__new__(DenseVector)._init(system, xd), TraceVector.__new__(TraceVector)._init(system, ld), r, i
     dev = isinstance(rhs, DeviceArray)
     if dev:
-        x, lam = system.ctx.empty(system.n_dense), system.ctx.empty(system.n_trace)
+        x, lam = out if out is not None else (system.ctx.empty(system.n_dense), system.ctx.empty(system.n_trace))
     else:
         rhs = np.ascontiguousarray(rhs, np.float64)
         constraints = np.ascontiguousarray(constraints, np.float64)
-        x, lam = np.empty(system.n_dense), np.empty(system.n_trace)
+        x, lam = out if out is not None else (np.empty(system.n_dense), np.empty(system.n_trace))
+        if x.shape != (system.n_dense,) or lam.shape != (system.n_trace,) or x.dtype != np.float64 or lam.dtype != np.float64:
+            raise ValueError("out must be float64 arrays of the dense and trace sizes")
     res, it = C.c_double(), C.c_int()
     check(
         lib().mfv2d_cuda_solve_schur_cg(system.handle, addr(rhs), addr(constraints), int(convergence.maximum_iterations),
