@@ -842,7 +842,29 @@ static int plan_lower_vector_fused(mfv2d_plan *plan)
         for (int k = 0; k < N && two; ++k)
             two = per_row[k].size() >= 1 && per_row[k].size() <= 2;
         fv.off_yfast = -1;
-        if (two)
+        fv.yfast_pairs = 0;
+        bool pairs = two;
+        for (int k = 0; k < N && pairs; ++k)
+            for (const auto &c : per_row[k])
+                pairs = pairs && c[2] == zero_cell && c[4] == zero_cell;
+        if (pairs)
+        {
+            // ... and when every contribution is (one positive) - (one negative) entry (mass terms, E21^T, E10 / E21 on the right
+            // of a mass): one 16-byte record per row, four value reads
+            std::vector<int32_t> yfast;
+            auto pack = [](int32_t lo, int32_t hi) { return (int32_t)(((uint32_t)lo & 0xffffu) | ((uint32_t)hi << 16)); };
+            for (int k = 0; k < N; ++k)
+            {
+                const auto &c0 = per_row[k][0];
+                const bool has1 = per_row[k].size() > 1;
+                const auto &c1 = per_row[k][has1 ? 1 : 0];
+                const int32_t z = (int32_t)zero_cell;
+                yfast.insert(yfast.end(), {c0[0], pack(c0[1], c0[3]), c1[0], has1 ? pack(c1[1], c1[3]) : pack(z, z)});
+            }
+            fv.off_yfast = put(yfast);
+            fv.yfast_pairs = 1;
+        }
+        else if (two)
         {
             std::vector<int32_t> yfast;
             auto pack = [](int32_t lo, int32_t hi) { return (int32_t)(((uint32_t)lo & 0xffffu) | ((uint32_t)hi << 16)); };
@@ -1396,6 +1418,19 @@ template <int Q> __global__ void __launch_bounds__(APPLYT_THREADS, 2) element_ve
         if (fv.off_yfast >= 0)
         {
             const int4 *yf = reinterpret_cast<const int4 *>(blob + fv.off_yfast);
+            if (fv.yfast_pairs)
+            {
+                for (int i = threadIdx.x; i < nv * N; i += blockDim.x)
+                {
+                    const int e = (int)(((float)i + 0.5f) * inv_n), k = i - e * N;
+                    const double *slot = slots + SLOT(e);
+                    const int4 d = yf[k]; // coef0, (p | n) of contribution 0, coef1, (p | n) of contribution 1
+                    const double v0 = slot[d.y & 0xffff] - slot[(unsigned)d.y >> 16];
+                    const double v1 = slot[d.w & 0xffff] - slot[(unsigned)d.w >> 16];
+                    args.y[elem0 * N + i] = fma(coef[d.z], v1, coef[d.x] * v0);
+                }
+                continue;
+            }
             for (int i = threadIdx.x; i < nv * N; i += blockDim.x)
             {
                 const int e = (int)(((float)i + 0.5f) * inv_n), k = i - e * N;
@@ -2001,8 +2036,11 @@ static int launch_apply(const mfv2d_plan *plan, const mfv2d_elements *e, const d
     }
     if (!column_mode && plan->vector_dmma && e->n > 0)
     {
+        // opt-in since round 2: with the bulk-copy prefetch and the fixed-record output stage the DFMA kernel below is faster
+        // on every order measured (Stokes p4: 39.7 vs 38.6 GDoF/s, mixed Poisson p4: 46.4 vs 41.1, Stokes p3: 35.5 vs 24.0;
+        // profiles/apply_dmma_vs_fused.py)
         const char *env = getenv("MFV2D_APPLY_DMMA");
-        if (!(env && env[0] == '0'))
+        if (env && env[0] == '1')
         {
             const int r = launch_dmma(ctx, plan, a, e->n);
             if (r >= 0)

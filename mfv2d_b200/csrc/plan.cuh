@@ -193,6 +193,7 @@ struct FusedVecInfo
     int blob_ints;
     int off_vec, off_t, slot_doubles; // slot: corners[8] | in / out vectors (aliased) | t rows
     int off_yfast;                    // -1, or 8 ints per output row: two branch-free contributions (every row has at most two)
+    int yfast_pairs;                  // 1: every contribution is one positive and one negative address -> 4 ints per output row
 };
 
 struct mfv2d_plan

@@ -114,6 +114,14 @@ def test_apply_warp_kernel(gpu, monkeypatch):
     P.check_matrix_vector_consistency(gpu[0], "direct_poisson", 5, 3)
 
 
+def test_apply_dmma_kernel(gpu, monkeypatch):
+    """the fp64 tensor-core apply kernel (q <= 8; opt-in since the DFMA kernel overtook it) stays parity-green"""
+    monkeypatch.setenv("MFV2D_APPLY_DMMA", "1")
+    P.check_matrix_vector_consistency(gpu[0], "stokes", 4, 3)
+    P.check_matrix_vector_consistency(gpu[0], "mixed_poisson", 4, 3)
+    P.check_matrix_vector_consistency(gpu[0], "stokes", 3, 3)
+
+
 def test_time_march(gpu):
     """BASELINE.json configs[2] (slice): trapezoidal march of unsteady advection-diffusion against the reference's own march"""
     P.check_time_march(*gpu)
