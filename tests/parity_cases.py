@@ -547,6 +547,31 @@ def check_saddle_residual_small_elements(M, SV, ST, nh=12, nv=10, p=4, scale=2e-
     return res_plain, res_refined
 
 
+def check_degenerate_element(M):
+    """A collapsed element inside a batch: every path that inverts a mass matrix must report MFV2D_PIVOT_FAILED with the
+    element's index (matrix_full_invert -> decompose_pivoted_lu, src/algebra/matrix.c:361-460), never return inf / NaN."""
+    quads = np.ascontiguousarray(F.QUADS[:3]).copy()
+    quads[1] = quads[1][0]  # all four corners at one point: det = 0 everywhere
+    batch = M.ElementBatch(make_basis(M, 3, 2), quads)
+    for order in (1, 2, 3):
+        try:
+            batch.mass(order, inverse=True)
+            raise AssertionError("a singular mass matrix must raise")
+        except RuntimeError as e:
+            assert "MFV2D_PIVOT_FAILED" in str(e) and "element 1" in str(e), str(e)
+    assert np.all(np.isfinite(batch.mass(1)))  # the forward 0-form mass of a collapsed element is just zero (1-/2-forms divide by det, as the reference does)
+    specs = M._ElementFormSpecification(("q", 2), ("u", 3))
+    try:
+        M.compute_element_matrices(specs, M._mass_expressions(specs, True), batch)
+        raise AssertionError("an element matrix with a singular inverse mass must raise")
+    except RuntimeError as e:
+        assert "MFV2D_PIVOT_FAILED" in str(e), str(e)
+    good = M.ElementBatch(make_basis(M, 3, 2), np.ascontiguousarray(F.QUADS[:3]))
+    inv = M.compute_element_matrices(specs, M._mass_expressions(specs, True), good)
+    fwd = M.compute_element_matrices(specs, M._mass_expressions(specs, False), good)
+    assert relerr(inv @ fwd, np.broadcast_to(np.eye(inv.shape[1]), inv.shape)) < 1e-10
+
+
 def check_partitioned_solve(M, SV, ST, ctx, rank, world, all_gather, fix, nh, nv):
     """One rank of a partitioned Schur solve of a golden mixed-Poisson system through the NVLink peer exchange
     (peer.cu): strips of elements, interface sums and Krylov scalars written into the other ranks' exchange blocks by

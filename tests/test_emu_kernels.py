@@ -45,6 +45,10 @@ def test_system_golden(emu, name):
     P.check_system_golden(emu[0], name, cases=((1, 2), (3, 3), (4, 2), (5, 0)))
 
 
+def test_degenerate_element(emu):
+    P.check_degenerate_element(emu[0])
+
+
 def test_dual_dofs(emu):
     P.check_dual_dofs(emu[0])
 

@@ -53,6 +53,10 @@ def test_mixed_order_buckets(gpu, name):
     P.check_mixed_order_buckets(gpu[0], orders=(2, 3, 4, 5, 6, 7, 8), per_order=9, name=name)
 
 
+def test_degenerate_element(gpu):
+    P.check_degenerate_element(gpu[0])
+
+
 def test_dual_dofs(gpu):
     P.check_dual_dofs(gpu[0])
 
