@@ -4,7 +4,8 @@
 // python/mfv2d/solving.py:439-500; its production path is SuperLU, solve_system_2d.py:258-282); this is the device
 // counterpart that lets the implicit time march of BASELINE.json configs[2] run without a global factorisation.
 // All scalars (rho, alpha, omega, beta, the residual and the stopping flag) live on the device; the host reads them back
-// once per block of iterations.  Right-preconditioned with the Jacobi diagonal of S when asked.
+// once per block of iterations.  Right-preconditioned with the Jacobi diagonal of S (precondition = 1) or with the additive
+// multilevel preconditioner of precond.cu (2: Jacobi + aggregate levels, after mfv2d_cuda_system_set_coarse_space).
 #include <cmath>
 
 #include "system.cuh"
@@ -121,6 +122,7 @@ __global__ void bicg_direction_kernel(long long n, const double *__restrict__ sc
 }
 
 __global__ void jacobi_setup_kernel(long long n, double *__restrict__ d, const double *__restrict__ r, double *__restrict__ z);
+int coarse_correction(mfv2d_system *s, const double *r, double *z, const int *done, bool use_peers); // precond.cu
 
 extern "C" int mfv2d_cuda_solve_schur_bicgstab(mfv2d_system *s, const double *rhs, const double *phi, int max_iter, double atol, double rtol,
                                                int precondition, double *x, double *lambda, double *residual, int *iterations, int space)
@@ -129,6 +131,11 @@ extern "C" int mfv2d_cuda_solve_schur_bicgstab(mfv2d_system *s, const double *rh
     const long long nt = s->n_trace, nd = s->n_dense;
     if ((nd && (!rhs || !x)) || (nt && (!phi || !lambda)))
         return mfv2d_fail(ctx, MFV2D_BAD_ARGUMENT, "solve_schur_bicgstab: rhs, phi, x and lambda must not be NULL");
+    if (precondition < 0 || precondition > 2)
+        return mfv2d_fail(ctx, MFV2D_BAD_ARGUMENT, "solve_schur_bicgstab: unknown preconditioner %d", precondition);
+    if (precondition == 2 && !s->coarse_ready)
+        return mfv2d_fail(ctx, MFV2D_BAD_ARGUMENT, "solve_schur_bicgstab: the multilevel preconditioner needs mfv2d_cuda_system_set_coarse_space");
+    const bool use_peers = sys_use_peers(s);
     MFV2D_TRY(sys_require_interface(s));
     Staged srhs, sphi, sx, slam;
     int r = stage_in(ctx, rhs, nd * sizeof(double), space, &srhs);
@@ -230,6 +237,8 @@ extern "C" int mfv2d_cuda_solve_schur_bicgstab(mfv2d_system *s, const double *rh
                     MFV2D_LAUNCH(bicg_scalar_kernel, 1, 32, 0, ctx->stream, sc, 0, it == 0 ? 1 : 0);
                     MFV2D_LAUNCH(bicg_direction_kernel, gt, 256, 0, ctx->stream, nt, (const double *)sc, (const double *)res, (const double *)v, p,
                                  dinv, hat, (const int *)flags);
+                    if (precondition >= 2 && (r = coarse_correction(s, p, hat, flags, use_peers))) // p^ = (D^-1 + sum_l P_l .. P_l^T) p
+                        break;
                     if ((r = sys_apply_schur(s, hat, v, flags)))
                         break;
                     if ((r = dot2(r0, v, nullptr, nullptr, sc + B_R0V, nullptr)))
@@ -242,6 +251,8 @@ extern "C" int mfv2d_cuda_solve_schur_bicgstab(mfv2d_system *s, const double *rh
                     MFV2D_LAUNCH(bicg_combine_kernel, gt, 256, 0, ctx->stream, nt, sv, (const double *)res, (const double *)v,
                                  (const double *)nullptr, (const double *)(sc + B_ALPHA), -1.0, (const double *)nullptr, 0.0, dinv, hat,
                                  (const int *)flags);
+                    if (precondition >= 2 && (r = coarse_correction(s, sv, hat, flags, use_peers)))
+                        break;
                     if ((r = sys_apply_schur(s, hat, t, flags)))
                         break;
                     if ((r = dot2(t, sv, t, t, sc + B_TS, sc + B_TT)))

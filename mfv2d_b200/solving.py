@@ -322,7 +322,7 @@ def solve_schur_bicgstab(system: LinearSystem, rhs, constraints, convergence: Co
     check(
         lib().mfv2d_cuda_solve_schur_bicgstab(system.handle, addr(rhs), addr(constraints), int(convergence.maximum_iterations),
                                               float(convergence.absolute_tolerance), float(convergence.relative_tolerance),
-                                              int(bool(precondition)), addr(x), addr(lam), C.byref(res), C.byref(it),
+                                              PRECONDITIONERS[precondition], addr(x), addr(lam), C.byref(res), C.byref(it),
                                               space_of(rhs, constraints, x, lam)),
         system.ctx.handle,
     )

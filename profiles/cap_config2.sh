@@ -3,7 +3,7 @@
 O=gpurun_out; mkdir -p $O; port=29720
 for N in ${1:-"8 4 2"}; do
   port=$((port + 1))
-  timeout 400 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port $port profiles/config2_march.py --gpus $N --steps 3 \
+  timeout 400 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port $port profiles/config2_march.py --gpus $N --steps 3 --precondition ${PC:-multilevel} --agg ${AGG:-8} --mid ${MID:-2,4} \
       > $O/config2_512_${N}gpu_r02.json 2> $O/config2_512_${N}gpu.err; echo "N=$N rc $?"
   python - <<PY
 import json

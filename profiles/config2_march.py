@@ -66,6 +66,9 @@ def main():
     ap.add_argument("--max-iter", type=int, default=40000)
     ap.add_argument("--nl-rtol", type=float, default=1e-10, help="stop the corrections of a step when max|residual| <= nl_rtol * max|rhs|")
     ap.add_argument("--nl-max", type=int, default=3)
+    ap.add_argument("--precondition", default="jacobi", choices=["jacobi", "multilevel"])
+    ap.add_argument("--agg", type=int, default=16)
+    ap.add_argument("--mid", default="4")
     args = ap.parse_args()
     g = np.load(os.path.join(ROOT, "tests", "golden", "timemarch_advdif.npz"), allow_pickle=True)
     raw = json.loads(str(g["codes"]))
@@ -99,6 +102,11 @@ def main():
     con_rhs = np.zeros(n_trace)
     host_s = B.max_over_ranks(dist, time.perf_counter() - t0)
     t0 = time.perf_counter()
+    n_coarse = 0
+    if args.precondition == "multilevel":
+        mids = tuple(int(v) for v in args.mid.split(",") if v)
+        _, hier, _ = ST.strip_system_1form(n, n, p, raw["form_orders"], world, rank, mids, args.agg)
+        n_coarse = hier[2][-1]
     if world > 1:
         ctx.init_comm(world, rank, None)
     system = SV.compute_linear_system(specs, lhs, batch, (row, col, val), n_trace)
@@ -110,7 +118,9 @@ def main():
             dist.all_gather_object(outl, obj)
             return outl
 
-        system.connect_peers(part.holder_ptr, part.holder_rank, all_gather, n_coarse=0)
+        system.connect_peers(part.holder_ptr, part.holder_rank, all_gather, n_coarse=n_coarse)
+    if args.precondition == "multilevel":
+        system.set_coarse_space(*hier)
     ctx.synchronize()
     setup_s = B.max_over_ranks(dist, time.perf_counter() - t0)
     reduce_max = (lambda v: B.max_over_ranks(dist, v)) if world > 1 else None
@@ -119,7 +129,7 @@ def main():
     stats = {"krylov_iterations": [], "krylov_residual": []}
     orig = SV.solve_schur_bicgstab
 
-    def counting(system, rd, rt_, conv, precondition=True):
+    def counting(system, rd, rt_, conv, precondition="jacobi"):
         x, lam, res, it = orig(system, rd, rt_, conv, precondition)
         stats["krylov_iterations"].append(int(it))
         stats["krylov_residual"].append(float(res))
@@ -142,7 +152,7 @@ def main():
     CL.non_linear_solve_run = timed
     sols, iters = CL.trapezoidal_march(specs, lhs, None, batch, (row, col, val), n_trace, con_rhs, explicit, [iu], dt, args.steps,
                                        max_iterations=args.nl_max, rtol=args.nl_rtol, krylov=SV.ConvergenceSettings(args.max_iter, 1e300, args.rtol),
-                                       system=system, reduce_max=reduce_max)
+                                       system=system, reduce_max=reduce_max, precondition=args.precondition)
     total_s = B.max_over_ranks(dist, time.perf_counter() - t_all)
     assert not (world > 1 and system.peer_error())
     _, rd, rtr, x, lam = stats.pop("last")
@@ -161,7 +171,7 @@ def main():
             "host_mesh_constraints_rhs_s": host_s, "system_setup_s": setup_s, "march_total_s": total_s,
             "step_s": step_times, "newton_iterations_per_step": [int(i) for i in iters], **stats,
             "last_correction_saddle_relative_residual": rel, "solution_norms": sol_norms,
-            "method": "BiCGStab on the Schur complement N A^-1 N^T (full condensed blocks, Jacobi right preconditioner), device resident; "
+            "method": f"BiCGStab on the Schur complement N A^-1 N^T (full condensed blocks, {args.precondition} right preconditioner), device resident; "
                       "interface sums and dot products over NVLink peer memory",
         })
     B.barrier(dist)

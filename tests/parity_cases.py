@@ -668,9 +668,10 @@ def check_partitioned_bicgstab(M, SV, ST, ctx, rank, world, all_gather, nh=8, nv
     else:
         prow, pcol, pval, pnt, rows_glob = row, col, val, nt, np.arange(nt)
     sysm = SV.LinearSystem(np.ascontiguousarray(mats_all[lo:hi]), (prow, pcol, pval), pnt, ctx=ctx)
+    _, hier, _ = ST.strip_system_1form(nh, nv, p, raw["form_orders"], world, rank, (2,), 4)
     if world > 1:
         sysm.set_interface(P.shared_index, P.slot, P.n_slots, P.owned)
-        sysm.connect_peers(P.holder_ptr, P.holder_rank, all_gather)
+        sysm.connect_peers(P.holder_ptr, P.holder_rank, all_gather, n_coarse=hier[2][-1])
     x, lam, res, it = SV.solve_schur_bicgstab(sysm, np.ascontiguousarray(rhs[bounds[rank]:bounds[rank + 1]]), np.ascontiguousarray(phi[rows_glob]),
                                               SV.ConvergenceSettings(4000, 1e300, 1e-13))
     assert not (world > 1 and sysm.peer_error())
@@ -679,6 +680,15 @@ def check_partitioned_bicgstab(M, SV, ST, ctx, rank, world, all_gather, nh=8, nv
     assert ex < 1e-9 and el < 1e-9, (rank, ex, el, it)
     counts = all_gather(int(it))
     assert all(c == counts[0] for c in counts), counts
+    # the multilevel preconditioner (aggregates of 2 x 2 elements + exact level of 4 x 4) on the same non-symmetric system
+    sysm.set_coarse_space(*hier)
+    x2, lam2, _, it2 = SV.solve_schur_bicgstab(sysm, np.ascontiguousarray(rhs[bounds[rank]:bounds[rank + 1]]), np.ascontiguousarray(phi[rows_glob]),
+                                               SV.ConvergenceSettings(4000, 1e300, 1e-13), precondition="multilevel")
+    assert not (world > 1 and sysm.peer_error())
+    assert relerr(x2, sol[bounds[rank]:bounds[rank + 1]]) < 1e-9, (rank, it2)
+    counts2 = all_gather(int(it2))
+    assert all(c == counts2[0] for c in counts2), counts2
+    assert it2 <= it + 4, (it2, it)  # 8 x 8 elements with the 2/dt mass term: well conditioned, the coarse levels cannot gain here
     return int(it), max(ex, el)
 
 
