@@ -61,10 +61,13 @@ void host_gll(int n, int max_iter, double tol, double *x, double *w, int *not_co
     }
 }
 
-// l_j(x) = prod_{i != j} (x - r_i) / prod_{i != j} (r_j - r_i), numerators by prefix/suffix products
+// l_j(x) = prod_{i != j} (x - r_i) / prod_{i != j} (r_j - r_i).  Both products run over i in increasing order and the
+// quotient is formed as numerator * (1 / denominator): the operation order of src/polynomials/lagrange.c:9-101, so that the
+// values are the reference's bit for bit (the hanging-side constraint rows invert matrices of these values with condition
+// numbers up to 1e8: a last-bit difference here is a 1e-8 difference there).
 void host_lagrange(int n, const double *roots, int m, const double *pos, double *out)
 {
-    std::vector<double> inv_den(n), pre(n + 1), suf(n + 1);
+    std::vector<double> inv_den(n);
     for (int j = 0; j < n; ++j)
     {
         double d = 1.0;
@@ -74,16 +77,14 @@ void host_lagrange(int n, const double *roots, int m, const double *pos, double 
         inv_den[j] = 1.0 / d;
     }
     for (int k = 0; k < m; ++k)
-    {
-        pre[0] = 1.0;
-        for (int i = 0; i < n; ++i)
-            pre[i + 1] = pre[i] * (pos[k] - roots[i]);
-        suf[n] = 1.0;
-        for (int i = n - 1; i >= 0; --i)
-            suf[i] = suf[i + 1] * (pos[k] - roots[i]);
         for (int j = 0; j < n; ++j)
-            out[(size_t)k * n + j] = pre[j] * suf[j + 1] * inv_den[j];
-    }
+        {
+            double num = 1.0;
+            for (int i = 0; i < n; ++i)
+                if (i != j)
+                    num *= (pos[k] - roots[i]);
+            out[(size_t)k * n + j] = num * inv_den[j];
+        }
 }
 
 // l_j'(x) = (1/den_j) sum_{m != j} prod_{i != j, m} (x - r_i)

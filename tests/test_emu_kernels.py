@@ -45,6 +45,13 @@ def test_system_golden(emu, name):
     P.check_system_golden(emu[0], name, cases=((1, 2), (3, 3), (4, 2), (5, 0)))
 
 
+@pytest.mark.parametrize("mesh,gate,sol_tol", [("b", 1e-10, 1e-7), ("a", 2e-7, 1e-5)])
+def test_hp_forest(emu, mesh, gate, sol_tol):
+    """configs[3] from arrays alone: own quadtree, own hanging-side rows, mixed block sizes, Schur CG.  Mesh a (93 leaves,
+    orders 2..8) has hanging-side coefficients up to 4e8: gates as for the reference-generated twin of it (test_hp_refined)"""
+    print(P.check_hp_forest(*emu, mesh, gate, sol_tol))
+
+
 def test_degenerate_element(emu):
     P.check_degenerate_element(emu[0])
 

@@ -53,6 +53,13 @@ def test_mixed_order_buckets(gpu, name):
     P.check_mixed_order_buckets(gpu[0], orders=(2, 3, 4, 5, 6, 7, 8), per_order=9, name=name)
 
 
+@pytest.mark.parametrize("mesh,gate,sol_tol", [("b", 1e-10, 1e-7), ("a", 2e-7, 1e-5)])
+def test_hp_forest(gpu, mesh, gate, sol_tol):
+    """configs[3] from arrays alone: own quadtree, own hanging-side rows, mixed block sizes, Schur CG.  Mesh a (93 leaves,
+    orders 2..8) has hanging-side coefficients up to 4e8: gates as for the reference-generated twin of it (test_hp_refined)"""
+    print(P.check_hp_forest(*gpu, mesh, gate, sol_tol))
+
+
 def test_degenerate_element(gpu):
     P.check_degenerate_element(gpu[0])
 
