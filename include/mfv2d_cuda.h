@@ -379,6 +379,15 @@ MFV2D_API int mfv2d_cuda_vec_axpby(mfv2d_ctx *ctx, size_t n, double a, const dou
                                    const double *y, double *out, int space);
 MFV2D_API int mfv2d_cuda_vec_dot(mfv2d_ctx *ctx, size_t n, const double *x, const double *y, double *result,
                                  int space);
+/* max_i |x_i| (NaN if any entry is NaN): the residual test of non_linear_solve_run
+ * (python/mfv2d/solve_system.py:430-447: np.max(np.abs(residual))) without bringing the vector to the host. */
+MFV2D_API int mfv2d_cuda_vec_absmax(mfv2d_ctx *ctx, size_t n, const double *x, double *result, int space);
+/* out[e*out_stride + j] = a*x[e*x_stride + j] + b*y[e*y_stride + j], j < len, e < n_blocks, DEVICE pointers (already offset to
+ * the first entry): gathers / scatter-adds the DoFs of one form of every element at once - the time-carry terms of the
+ * trapezoidal march (find_time_carry_indices, python/mfv2d/solve_system.py:604-617, solve_system_2d.py:325-397). */
+MFV2D_API int mfv2d_cuda_strided_axpby(mfv2d_ctx *ctx, size_t n_blocks, size_t len, double a, const double *x,
+                                       size_t x_stride, double b, const double *y, size_t y_stride, double *out,
+                                       size_t out_stride);
 
 /* solve_schur_iterative (python/mfv2d/solving.py:439-500) with cg_general (:350-436) running on
  * the device: lambda from CG on S, then x = A^-1 y - A^-1 N^T lambda.

@@ -112,6 +112,8 @@ SIGNATURES = {
     "mfv2d_cuda_system_apply_schur": (i32, [vp, dp, dp, i32]),
     "mfv2d_cuda_vec_axpby": (i32, [vp, sz, dbl, dp, dbl, dp, dp, i32]),
     "mfv2d_cuda_vec_dot": (i32, [vp, sz, dp, dp, C.POINTER(dbl), i32]),
+    "mfv2d_cuda_vec_absmax": (i32, [vp, sz, dp, C.POINTER(dbl), i32]),
+    "mfv2d_cuda_strided_axpby": (i32, [vp, sz, sz, dbl, dp, sz, dbl, dp, sz, dp, sz]),
     "mfv2d_cuda_solve_schur_cg": (i32, [vp, dp, dp, i32, dbl, dbl, i32, dp, dp, C.POINTER(dbl), C.POINTER(i32), i32]),
     "mfv2d_cuda_solve_schur_bicgstab": (i32, [vp, dp, dp, i32, dbl, dbl, i32, dp, dp, C.POINTER(dbl), C.POINTER(i32), i32]),
     "mfv2d_cuda_solve_pcg": (i32, [vp, dp, dp, i32, dbl, dbl, dp, dp, C.POINTER(dbl), C.POINTER(i32), i32]),

@@ -528,6 +528,62 @@ __global__ void axpby_kernel(long long n, double a, const double *__restrict__ x
         out[i] = a * x[i] + b * y[i];
 }
 
+// out[e * os + j] = a x[e * xs + j] + b y[e * ys + j] (j < len): the DoFs of one form of every element at once
+__global__ void strided_axpby_kernel(unsigned long long n_blocks, unsigned long long len, double a, const double *x, unsigned long long xs,
+                                     double b, const double *y, unsigned long long ys, double *out, unsigned long long os)
+{
+    const unsigned long long total = n_blocks * len;
+    for (unsigned long long g = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; g < total; g += (unsigned long long)gridDim.x * blockDim.x)
+    {
+        const unsigned long long e = g / len, j = g - e * len;
+        out[e * os + j] = a * x[e * xs + j] + b * y[e * ys + j];
+    }
+}
+
+// partials[blockIdx] = max |x_i| over the CTA's strided range; a NaN anywhere is reported as NaN (numpy's max does the same)
+__global__ void __launch_bounds__(SYS_THREADS) absmax_partial_kernel(long long n, const double *__restrict__ x, double *__restrict__ partials)
+{
+    __shared__ double red[32];
+    double m = 0.0;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    {
+        const double v = fabs(x[i]);
+        m = (v > m || v != v) ? v : m; // once NaN, stays NaN (NaN > m and m > NaN are both false, v != v keeps it)
+        if (m != m)
+            break;
+    }
+#ifndef MFV2D_EMU
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+    {
+        const double v = __shfl_xor_sync(0xffffffffu, m, o);
+        m = (v > m || v != v) ? v : m;
+    }
+#endif
+    const int warp = threadIdx.x >> 5, nwarps = MFV2D_NWARPS;
+    if ((threadIdx.x & 31) == 0)
+        red[warp] = m;
+    __syncthreads();
+    if (threadIdx.x == 0)
+    {
+        double r = 0.0;
+        for (int w = 0; w < nwarps; ++w)
+            r = (red[w] > r || red[w] != red[w]) ? red[w] : r;
+        partials[blockIdx.x] = r;
+    }
+}
+
+__global__ void absmax_final_kernel(int np, const double *__restrict__ partials, double *__restrict__ result)
+{
+    if (threadIdx.x == 0 && blockIdx.x == 0)
+    {
+        double r = 0.0;
+        for (int i = 0; i < np; ++i)
+            r = (partials[i] > r || partials[i] != partials[i]) ? partials[i] : r;
+        *result = r;
+    }
+}
+
 // v[i] *= d[i] (inverse = 0) or v[i] /= d[i] (inverse = 1)
 __global__ void scale_by_kernel(long long n, const double *__restrict__ d, double *__restrict__ v, int inverse)
 {
@@ -1245,6 +1301,47 @@ int mfv2d_cuda_vec_axpby(mfv2d_ctx *ctx, size_t n, double a, const double *x, do
     stage_abort(&sx);
     stage_abort(&sy);
     return r;
+}
+
+int mfv2d_cuda_vec_absmax(mfv2d_ctx *ctx, size_t n, const double *x, double *result, int space)
+{
+    *result = 0.0;
+    if (n == 0)
+        return MFV2D_SUCCESS;
+    Staged sx;
+    const int np = ctx->sm_count * 4; // partial maxima live in the context's scalar buffer neighbourhood: allocate per call
+    void *partials = nullptr;
+    int r = stage_in(ctx, x, n * sizeof(double), space, &sx);
+    if (!r)
+        r = mfv2d_cuda_malloc(ctx, (size_t)np * sizeof(double), &partials);
+    if (!r)
+    {
+        MFV2D_LAUNCH(absmax_partial_kernel, (unsigned)np, SYS_THREADS, 0, ctx->stream, (long long)n, (const double *)sx.dev, (double *)partials);
+        MFV2D_LAUNCH(absmax_final_kernel, 1, 32, 0, ctx->stream, np, (const double *)partials, ctx->d_scalars);
+        ctx->launches += 2;
+        if (cudaGetLastError() != cudaSuccess)
+            r = mfv2d_fail(ctx, MFV2D_CUDA_ERROR, "absmax kernel launch failed");
+    }
+    if (!r)
+        r = read_scalars(ctx, ctx->d_scalars, 1, result);
+    stage_abort(&sx);
+    if (partials)
+        mfv2d_cuda_free(ctx, partials);
+    return r;
+}
+
+int mfv2d_cuda_strided_axpby(mfv2d_ctx *ctx, size_t n_blocks, size_t len, double a, const double *x, size_t x_stride, double b, const double *y,
+                             size_t y_stride, double *out, size_t out_stride)
+{
+    if (n_blocks == 0 || len == 0)
+        return MFV2D_SUCCESS;
+    if (!x || !y || !out || x_stride < len || y_stride < len || out_stride < len)
+        return mfv2d_fail(ctx, MFV2D_BAD_ARGUMENT, "strided_axpby: device pointers and strides of at least `len` are required");
+    MFV2D_LAUNCH(strided_axpby_kernel, grid_for(ctx, (long long)(n_blocks * len), 256), 256, 0, ctx->stream, (unsigned long long)n_blocks,
+                 (unsigned long long)len, a, x, (unsigned long long)x_stride, b, y, (unsigned long long)y_stride, out, (unsigned long long)out_stride);
+    ctx->launches++;
+    MFV2D_CUDA_CHECK(ctx, cudaGetLastError());
+    return MFV2D_SUCCESS;
 }
 
 int mfv2d_cuda_vec_dot(mfv2d_ctx *ctx, size_t n, const double *x, const double *y, double *result, int space)

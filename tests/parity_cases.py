@@ -883,6 +883,24 @@ def check_time_march(M, SV, ST):
     assert len(sols) == ref.shape[0] - 1
     for i, s in enumerate(sols):
         assert relerr(s, ref[i + 1]) < 1e-8, (i, relerr(s, ref[i + 1]))
+    # the same march with every vector resident on the device: same iteration counts, same solutions up to the Krylov tolerance;
+    # steps that `keep` drops are not downloaded
+    dsols, diters = CL.trapezoidal_march(specs, lhs, None, batch, (g["con_row"], g["con_col"], g["con_val"]), nt, g["con_rhs"], g["explicit"],
+                                         [raw["form_names"].index("u")], float(g["dt"]), int(g["nt"]), device=True,
+                                         keep=lambda step: step != 1)
+    assert diters == iters and dsols[1] is None
+    for i, s in enumerate(dsols):
+        if s is not None:
+            assert relerr(s, sols[i]) < 1e-10 and relerr(s, ref[i + 1]) < 1e-8, (i, relerr(s, sols[i]))
+    # BLAS-1 helpers of the device march: max |x| (NaN propagates, empty -> 0) on host and device buffers
+    ctx = batch.ctx
+    rng = np.random.default_rng(3)
+    v = rng.standard_normal(100003)
+    v[77777] = -9.5
+    assert CL.vec_absmax(v, ctx) == 9.5 and CL.vec_absmax(ctx.to_device(v), ctx) == 9.5
+    assert CL.vec_absmax(np.zeros(0), ctx) == 0.0
+    v[5] = np.nan
+    assert np.isnan(CL.vec_absmax(ctx.to_device(v), ctx))
     return iters
 
 
