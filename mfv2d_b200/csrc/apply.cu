@@ -1272,7 +1272,13 @@ template <int Q> __global__ void __launch_bounds__(APPLYT_THREADS, 2) element_ve
     const int epb = fa.epb, SD = fv.slot_doubles;
     // slot of element e: stride SD (congruent to Q modulo 16 doubles: phase B, lanes = (e, b), is conflict free) plus a
     // small rotation so that 16-byte accesses of phases A / C, lanes = consecutive elements, fall into distinct bank groups
-#define SLOT(e) ((e) * SD + 2 * (((e) >> 1) & 3))
+    // The rotation depends on s = (SD / 2) mod 8, the slot stride in 16-byte units: the bases of 8 consecutive elements must fall
+    // into 8 distinct 16-byte bank groups.  s odd (Q = 5, 6, 9, 10, 13, 14): already a permutation, no rotation (a rotation
+    // costs a factor 2 there: measured x3.9 / x2.0 / x1.6 wavefronts on the 8-byte, 16-byte and phase-B accesses at Q = 10);
+    // s = 2, 6: one step every 4 elements; s = 0, 4: one step every 2 elements.
+    const int rot_s = (SD >> 1) & 7;
+    const int rot_shift = (rot_s & 1) ? 0 : ((rot_s & 2) ? 2 : 1), rot_mask = (rot_s & 1) ? 0 : ((rot_s & 2) ? 1 : 3);
+#define SLOT(e) ((e) * SD + 2 * (((e) >> rot_shift) & rot_mask))
     const int off_xs = fv.off_vec;
     const unsigned long long n_groups = (args.n_elem + epb - 1) / epb;
     const float inv_n = 1.0f / (float)N;
