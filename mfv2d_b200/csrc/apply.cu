@@ -1031,55 +1031,6 @@ template <int Q, int NT> __device__ __forceinline__ void row_dot_n(const double 
         res[n] = a0[n] + a1[n];
 }
 
-// ---- the 1-D tables as KERNEL PARAMETERS (constant bank 0) ----------------------------------------------------------
-// The fused apply is bound by the shared-memory pipe (ncu: 67 % of its peak against 31 % of the fp64 pipe, 3.2 wavefront
-// cycles per DFMA cycle), and a third of the wavefronts were the broadcast reads of the 1-D basis tables.  With the row
-// loops fully unrolled the table entries become immediate constant-bank operands of the DFMAs (`DFMA R, R, c[0x0][imm], R`):
-// no shared-memory read and no load instruction at all.  The tables travel by value in the launch parameters (2 Q LDQ
-// doubles: 1.6 KB at Q = 10), so concurrent launches with different bases need no shared symbol.  kind 0 = node rows, 1 = edge.
-template <int Q, bool CT> struct FusedTab
-{
-    double t[2][Q][(Q + 1) & ~1];
-};
-template <int Q> struct FusedTab<Q, false>
-{
-    double t[1][1][2];
-};
-
-// acc[n][:] (+)= c[n] * T[K][I][:]  with I a compile-time row index (same operation order per accumulator as row_mul_n / row_axpy_n)
-template <int Q, int NT, int K, bool FIRST>
-__device__ __forceinline__ void ct_row_axpy(double (&acc)[NT][Q], const double (&c)[NT], const FusedTab<Q, true> &ft, const int I)
-{
-#pragma unroll
-    for (int b = 0; b < Q; ++b)
-#pragma unroll
-        for (int n = 0; n < NT; ++n)
-            acc[n][b] = FIRST ? c[n] * ft.t[K][I][b] : fma(c[n], ft.t[K][I][b], acc[n][b]);
-}
-
-// res[n] = T[K][I][:] . g[n][:]  (even points into one accumulator, odd ones into the other, like row_dot_n)
-template <int Q, int NT, int K>
-__device__ __forceinline__ void ct_row_dot(const FusedTab<Q, true> &ft, const int I, const double (&g)[NT][Q], double (&res)[NT])
-{
-    double a0[NT], a1[NT];
-#pragma unroll
-    for (int n = 0; n < NT; ++n)
-        a0[n] = a1[n] = 0.0;
-#pragma unroll
-    for (int b = 0; b < Q; ++b)
-#pragma unroll
-        for (int n = 0; n < NT; ++n)
-        {
-            if (b & 1)
-                a1[n] = fma(ft.t[K][I][b], g[n][b], a1[n]);
-            else
-                a0[n] = fma(ft.t[K][I][b], g[n][b], a0[n]);
-        }
-#pragma unroll
-    for (int n = 0; n < NT; ++n)
-        res[n] = a0[n] + a1[n];
-}
-
 // coefficient j of a phase-A row: read in place, or gathered from x through the right incidence
 __device__ __forceinline__ double fused_coef(const double *__restrict__ slot, int src, int g, int j, const int4 *__restrict__ gtab)
 {
@@ -1095,44 +1046,14 @@ template <int Q> struct FusedUnroll
     static constexpr int value = Q >= 10 ? 2 : 1;
 };
 
-// phase A with the table rows as constant operands: K = table kind, rows unrolled up to the table's maximum
-template <int Q, int NT, int K>
-__device__ __forceinline__ void fused_rows_a_ct(const int4 d0, const int4 d1, double *__restrict__ slot, const int4 *__restrict__ gtab,
-                                                const FusedTab<Q, true> &ft, double (&acc)[NT][Q])
-{
-#pragma unroll
-    for (int j = 0; j < Q - K; ++j)
-    {
-        if (j >= d0.y)
-            break;
-        double c[NT];
-        c[0] = fused_coef(slot, d0.x, d1.z, j, gtab);
-        if (NT > 1)
-            c[NT - 1] = fused_coef(slot, d1.x, d1.w, j, gtab);
-        if (j == 0)
-            ct_row_axpy<Q, NT, K, true>(acc, c, ft, j);
-        else
-            ct_row_axpy<Q, NT, K, false>(acc, c, ft, j);
-    }
-}
-
-template <int Q, int NT, bool CT>
+template <int Q, int NT>
 __device__ __forceinline__ void fused_rows_a(const int4 d0, const int4 d1, double *__restrict__ slot, const double *__restrict__ smem, int edge_off,
-                                             const int4 *__restrict__ gtab, const FusedTab<Q, CT> &ft)
+                                             const int4 *__restrict__ gtab)
 {
     constexpr int UNR = FusedUnroll<Q>::value;
     constexpr int LDQ = (Q + 1) & ~1;
     const double *B = smem + d0.z * edge_off;
     double acc[NT][Q];
-    if constexpr (CT && NT == 2)
-    {
-        if (d0.z == 0)
-            fused_rows_a_ct<Q, NT, 0>(d0, d1, slot, gtab, ft, acc);
-        else
-            fused_rows_a_ct<Q, NT, 1>(d0, d1, slot, gtab, ft, acc);
-    }
-    else
-    {
     {
         // first coefficient: plain products instead of zero + fma
         double c[NT];
@@ -1150,7 +1071,6 @@ __device__ __forceinline__ void fused_rows_a(const int4 d0, const int4 d1, doubl
             c[NT - 1] = fused_coef(slot, d1.x, d1.w, j, gtab);
         row_axpy_n<Q, NT>(acc, c, B + j * LDQ);
     }
-    }
 #pragma unroll
     for (int n = 0; n < NT; ++n)
     {
@@ -1164,26 +1084,8 @@ __device__ __forceinline__ void fused_rows_a(const int4 d0, const int4 d1, doubl
 }
 
 // phase C: the nB results of a row overwrite the head of the row itself (it has been read into registers)
-template <int Q, int NT, int K>
-__device__ __forceinline__ void fused_rows_c_ct(const int nj, double *__restrict__ dst0, double *__restrict__ dst1, const FusedTab<Q, true> &ft,
-                                                const double (&tr)[NT][Q])
-{
-#pragma unroll
-    for (int j = 0; j < Q - K; ++j)
-    {
-        if (j >= nj)
-            break;
-        double res[NT];
-        ct_row_dot<Q, NT, K>(ft, j, tr, res);
-        dst0[j] = res[0];
-        if (NT > 1)
-            dst1[j] = res[NT - 1];
-    }
-}
-
-template <int Q, int NT, bool CT>
-__device__ __forceinline__ void fused_rows_c(const int4 d0, const int4 d1, double *__restrict__ slot, const double *__restrict__ smem, int edge_off,
-                                             const FusedTab<Q, CT> &ft)
+template <int Q, int NT>
+__device__ __forceinline__ void fused_rows_c(const int4 d0, const int4 d1, double *__restrict__ slot, const double *__restrict__ smem, int edge_off)
 {
     constexpr int UNR = FusedUnroll<Q>::value;
     constexpr int LDQ = (Q + 1) & ~1;
@@ -1204,14 +1106,6 @@ __device__ __forceinline__ void fused_rows_c(const int4 d0, const int4 d1, doubl
     }
     const double *B = smem + d0.z * edge_off;
     double *dst0 = slot + d0.x, *dst1 = slot + (NT > 1 ? d1.x : d0.x);
-    if constexpr (CT && NT == 2)
-    {
-        if (d0.z == 0)
-            fused_rows_c_ct<Q, NT, 0>(d0.y, dst0, dst1, ft, tr);
-        else
-            fused_rows_c_ct<Q, NT, 1>(d0.y, dst0, dst1, ft, tr);
-        return;
-    }
 #pragma unroll(UNR)
     for (int j = 0; j < d0.y; ++j)
     {
@@ -1230,45 +1124,10 @@ struct ColumnGeo
 };
 
 // one term (NT = 1) or two terms of the same kind (NT = 2) on the quadrature column b of one element
-// interpolation / projection along eta of phase B with the table rows as constant operands
-template <int Q, int NT, int K>
-__device__ __forceinline__ void fused_b_in_ct(double (&u)[NT][Q], double *const (&tc)[NT], const int first, const int n, const int LDT,
-                                              const FusedTab<Q, true> &ft)
-{
-#pragma unroll
-    for (int i = 0; i < Q - K; ++i)
-    {
-        if (i >= n)
-            break;
-        double c[NT];
-#pragma unroll
-        for (int m = 0; m < NT; ++m)
-            c[m] = tc[m][(first + i) * LDT];
-        ct_row_axpy<Q, NT, K, false>(u, c, ft, i);
-    }
-}
-
-template <int Q, int NT, int K>
-__device__ __forceinline__ void fused_b_out_ct(const double (&u)[NT][Q], double *const (&tc)[NT], const int first, const int n, const int LDT,
-                                               const FusedTab<Q, true> &ft)
-{
-#pragma unroll
-    for (int i = 0; i < Q - K; ++i)
-    {
-        if (i >= n)
-            break;
-        double res[NT];
-        ct_row_dot<Q, NT, K>(ft, i, u, res);
-#pragma unroll
-        for (int m = 0; m < NT; ++m)
-            tc[m][(first + i) * LDT] = res[m];
-    }
-}
-
-template <int Q, int NT, bool CT>
+template <int Q, int NT>
 __device__ __forceinline__ void fused_terms_b(const int *__restrict__ tb, double *__restrict__ slot, int b, const double *__restrict__ smem,
                                               int edge_off, const double *__restrict__ pnts, const double *__restrict__ wgts,
-                                              const ColumnGeo &g, const double *__restrict__ fp, const FusedTab<Q, CT> &ft)
+                                              const ColumnGeo &g, const double *__restrict__ fp)
 {
     constexpr int UNR = FusedUnroll<Q>::value;
     constexpr int LDQ = (Q + 1) & ~1;
@@ -1285,18 +1144,6 @@ __device__ __forceinline__ void fused_terms_b(const int *__restrict__ tb, double
 #pragma unroll
         for (int a = 0; a < Q; ++a)
             u0[n][a] = u1[n][a] = 0.0;
-    if constexpr (CT && NT == 1)
-    {
-        if (tb[4] == 0)
-            fused_b_in_ct<Q, NT, 0>(u0, tc, 0, nA0, LDT, ft);
-        else
-            fused_b_in_ct<Q, NT, 1>(u0, tc, 0, nA0, LDT, ft);
-        if (tb[6] == 0)
-            fused_b_in_ct<Q, NT, 0>(u1, tc, nA0, nA1, LDT, ft);
-        else
-            fused_b_in_ct<Q, NT, 1>(u1, tc, nA0, nA1, LDT, ft);
-    }
-    else
     {
         const double *A = smem + tb[4] * edge_off;
 #pragma unroll(UNR)
@@ -1384,18 +1231,6 @@ __device__ __forceinline__ void fused_terms_b(const int *__restrict__ tb, double
             }
         }
     }
-    if constexpr (CT && NT == 1)
-    {
-        if (tb[8] == 0)
-            fused_b_out_ct<Q, NT, 0>(u0, tc, 0, nO0, LDT, ft);
-        else
-            fused_b_out_ct<Q, NT, 1>(u0, tc, 0, nO0, LDT, ft);
-        if (tb[10] == 0)
-            fused_b_out_ct<Q, NT, 0>(u1, tc, nO0, nO1, LDT, ft);
-        else
-            fused_b_out_ct<Q, NT, 1>(u1, tc, nO0, nO1, LDT, ft);
-    }
-    else
     {
         const double *A = smem + tb[8] * edge_off;
 #pragma unroll(UNR)
@@ -1420,8 +1255,7 @@ __device__ __forceinline__ void fused_terms_b(const int *__restrict__ tb, double
     }
 }
 
-template <int Q, bool CT>
-__global__ void __launch_bounds__(APPLYT_THREADS, 2) element_vector_fused_kernel(const FusedArgs fa, const FusedTab<Q, CT> ft)
+template <int Q> __global__ void __launch_bounds__(APPLYT_THREADS, 2) element_vector_fused_kernel(const FusedArgs fa)
 {
     MFV2D_DYN_SMEM(double, smem);
     constexpr int LDQ = (Q + 1) & ~1;
@@ -1536,9 +1370,9 @@ __global__ void __launch_bounds__(APPLYT_THREADS, 2) element_vector_fused_kernel
                 double *slot = slots + SLOT(e);
                 const int4 d0 = rowA[2 * row], d1 = rowA[2 * row + 1];
                 if (d1.x >= 0)
-                    fused_rows_a<Q, 2, CT>(d0, d1, slot, smem, edge_off, gtab, ft);
+                    fused_rows_a<Q, 2>(d0, d1, slot, smem, edge_off, gtab);
                 else
-                    fused_rows_a<Q, 1, CT>(d0, d1, slot, smem, edge_off, gtab, ft);
+                    fused_rows_a<Q, 1>(d0, d1, slot, smem, edge_off, gtab);
             }
         }
         __syncthreads();
@@ -1564,9 +1398,9 @@ __global__ void __launch_bounds__(APPLYT_THREADS, 2) element_vector_fused_kernel
                 const int *tb = termB + 12 * t;
                 const double *fp = tb[0] >= 3 ? args.fields[tb[1]] + (elem0 + e) * (unsigned long long)(2 * Q * Q) + 2 * b : nullptr;
                 if (tb[11] >= 0)
-                    fused_terms_b<Q, 2, CT>(tb, slot, b, smem, edge_off, pnts, wgts, g, fp, ft);
+                    fused_terms_b<Q, 2>(tb, slot, b, smem, edge_off, pnts, wgts, g, fp);
                 else
-                    fused_terms_b<Q, 1, CT>(tb, slot, b, smem, edge_off, pnts, wgts, g, fp, ft);
+                    fused_terms_b<Q, 1>(tb, slot, b, smem, edge_off, pnts, wgts, g, fp);
             }
         }
         __syncthreads();
@@ -1580,9 +1414,9 @@ __global__ void __launch_bounds__(APPLYT_THREADS, 2) element_vector_fused_kernel
                 double *slot = slots + SLOT(e);
                 const int4 d0 = rowC[2 * row], d1 = rowC[2 * row + 1];
                 if (d1.x >= 0)
-                    fused_rows_c<Q, 2, CT>(d0, d1, slot, smem, edge_off, ft);
+                    fused_rows_c<Q, 2>(d0, d1, slot, smem, edge_off);
                 else
-                    fused_rows_c<Q, 1, CT>(d0, d1, slot, smem, edge_off, ft);
+                    fused_rows_c<Q, 1>(d0, d1, slot, smem, edge_off);
             }
         }
         __syncthreads();
@@ -1634,19 +1468,8 @@ __global__ void __launch_bounds__(APPLYT_THREADS, 2) element_vector_fused_kernel
 }
 #undef SLOT
 
-template <int Q, bool CT> static int launch_fused_q(mfv2d_ctx *ctx, FusedArgs &fa, size_t fixed_bytes, size_t n_elem, const mfv2d_basis *basis)
+template <int Q> static int launch_fused_q(mfv2d_ctx *ctx, FusedArgs &fa, size_t fixed_bytes, size_t n_elem)
 {
-    FusedTab<Q, CT> ft{};
-    if (CT)
-    {
-        const int p = basis->p;
-        for (int i = 0; i <= p && i < Q; ++i)
-            for (int b = 0; b < Q; ++b)
-                ft.t[0][i][b] = basis->node[(size_t)i * Q + b];
-        for (int i = 0; i < p && i < Q; ++i)
-            for (int b = 0; b < Q; ++b)
-                ft.t[CT ? 1 : 0][i][b] = basis->edge[(size_t)i * Q + b];
-    }
     const size_t slot_bytes = (size_t)fa.fv.slot_doubles * 8;
     const size_t budget = ((size_t)228 * 1024 - 2048) / 2; // two CTAs per SM
     int epb = (int)((budget > fixed_bytes ? budget - fixed_bytes : 0) / slot_bytes);
@@ -1671,17 +1494,16 @@ template <int Q, bool CT> static int launch_fused_q(mfv2d_ctx *ctx, FusedArgs &f
     const size_t smem = fixed_bytes + (size_t)epb * slot_bytes;
     if (smem > ctx->smem_optin)
         return -1; // the caller falls back to the term-by-term kernel
-    auto kernel = element_vector_fused_kernel<Q, CT>;
-    MFV2D_CUDA_CHECK(ctx, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    MFV2D_CUDA_CHECK(ctx, cudaFuncSetAttribute(element_vector_fused_kernel<Q>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 1;
-    MFV2D_CUDA_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, APPLYT_THREADS, smem));
+    MFV2D_CUDA_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, element_vector_fused_kernel<Q>, APPLYT_THREADS, smem));
     if (per_sm < 1)
         per_sm = 1;
     unsigned long long grid = (unsigned long long)ctx->sm_count * per_sm;
     const unsigned long long need = (n_elem + epb - 1) / epb;
     if (grid > need)
         grid = need;
-    MFV2D_LAUNCH(kernel, (unsigned)grid, APPLYT_THREADS, smem, ctx->stream, fa, ft);
+    MFV2D_LAUNCH(element_vector_fused_kernel<Q>, (unsigned)grid, APPLYT_THREADS, smem, ctx->stream, fa);
     ctx->launches++;
     MFV2D_CUDA_CHECK(ctx, cudaGetLastError());
     return MFV2D_SUCCESS;
@@ -2244,15 +2066,11 @@ static int launch_apply(const mfv2d_plan *plan, const mfv2d_elements *e, const d
         const size_t fixed_bytes = ((size_t)(2 * p + 1) * ldq + 2 * ldq + (((size_t)fa.n_coef + 1) & ~(size_t)1)) * 8 +
                                    (size_t)fa.fv.blob_ints * 4 + (size_t)fa.inc_rows * 16;
         int r = -1;
-        // 1-D tables as constant-bank operands (launch parameters) for 4 <= q <= 12; MFV2D_APPLY_CTAB=0 keeps them in shared memory
-        const char *ctab_env = getenv("MFV2D_APPLY_CTAB");
-        const bool ctab = !(ctab_env && ctab_env[0] == '0');
         switch (q)
         {
 #define MFV2D_Q_CASE(Q)                                                                                        \
     case Q:                                                                                                    \
-        r = (ctab && Q >= 4 && Q <= 12 && p < Q) ? launch_fused_q<Q, (Q >= 4 && Q <= 12)>(ctx, fa, fixed_bytes, e->n, plan->basis)   \
-                                                 : launch_fused_q<Q, false>(ctx, fa, fixed_bytes, e->n, plan->basis);          \
+        r = launch_fused_q<Q>(ctx, fa, fixed_bytes, e->n);                                                     \
         break;
             MFV2D_Q_CASE(2)
             MFV2D_Q_CASE(3)
