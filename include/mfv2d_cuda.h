@@ -325,6 +325,11 @@ MFV2D_API int mfv2d_cuda_inverse_definite_noalloc(mfv2d_ctx *ctx, int n, const d
  * refinement.py:880-886, 1158-1168 (sp.block_diag(...) @ element_solution) for every element. */
 MFV2D_API int mfv2d_cuda_batched_gemv(mfv2d_ctx *ctx, size_t n, int rows, int cols, const double *mats,
                                       const double *x, double *y, int space);
+/* c[e] = op(a[e]) b[e], n row-major matrices: op(a) is (m x k) - a itself, or (trans_a != 0) the transpose of a stored
+ * (k x m) matrix; b is (k x l), c (m x l).  The element-wise triple products of the VMS operator,
+ * `projector_c2f.T @ fine_matrix @ projector_c2f` (python/mfv2d/solve_system.py:751), for every element at once. */
+MFV2D_API int mfv2d_cuda_batched_gemm(mfv2d_ctx *ctx, size_t n, int m, int k, int l, int trans_a, const double *a,
+                                      const double *b, double *c, int space);
 /* out[e] = [[A[e], L^T], [L, 0]] ((size + pad)^2 doubles each): the local systems of refinement.py:1001-1050 whose
  * Lagrange rows L (pad x size, COO lrow/lcol/lval[nnz], HOST arrays, the same for every element) force boundary DoFs of
  * strongly-zeroed forms to zero and pin the sum of constrained forms. */

@@ -98,6 +98,7 @@ SIGNATURES = {
     "mfv2d_cuda_inverse_batch": (i32, [vp, i32, sz, dp, dp, vp, i32]),
     "mfv2d_cuda_inverse_definite_noalloc": (i32, [vp, i32, vp, vp, vp]),
     "mfv2d_cuda_batched_gemv": (i32, [vp, sz, i32, i32, dp, dp, dp, i32]),
+    "mfv2d_cuda_batched_gemm": (i32, [vp, sz, i32, i32, i32, i32, dp, dp, dp, i32]),
     "mfv2d_cuda_border_batch": (i32, [vp, sz, i32, i32, dp, i32, vp, vp, vp, dp, i32]),
     "mfv2d_cuda_legendre_estimates_batch": (i32, [vp, i32, i32, i32, dp, dp, dp, i32]),
     "mfv2d_cuda_solve_batch": (i32, [vp, i32, i32, sz, dp, dp, dp, vp, i32]),

@@ -32,6 +32,48 @@ __global__ void __launch_bounds__(REFINE_THREADS) batched_gemv_kernel(unsigned l
     }
 }
 
+// ---- C[e] = op(A[e]) B[e] for n row-major matrices: a 4 x 4 register tile per thread, operands through L1 / L2 ---------
+// op(A) is (m x k): A itself, or the transpose of a stored (k x m) matrix.  Set-up work of the VMS operator (coarse blocks
+// P^T A_f P), not a hot kernel: two loads per four FMAs, no shared-memory staging.
+__global__ void __launch_bounds__(REFINE_THREADS) batched_gemm_kernel(unsigned long long n, int m, int k, int l, int trans_a,
+                                                                     const double *__restrict__ A, const double *__restrict__ B,
+                                                                     double *__restrict__ Cm)
+{
+    const int tm = (m + 3) / 4, tl = (l + 3) / 4;
+    const unsigned long long per = (unsigned long long)tm * tl, total = n * per;
+    for (unsigned long long g = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; g < total; g += (unsigned long long)gridDim.x * blockDim.x)
+    {
+        const unsigned long long e = g / per;
+        const int t = (int)(g - e * per);
+        const int i0 = (t / tl) * 4, j0 = (t - (t / tl) * tl) * 4;
+        const double *a = A + e * (unsigned long long)m * k, *b = B + e * (unsigned long long)k * l;
+        double acc[4][4] = {};
+        for (int kk = 0; kk < k; ++kk)
+        {
+            double av[4], bv[4];
+#pragma unroll
+            for (int r = 0; r < 4; ++r)
+            {
+                const int i = i0 + r < m ? i0 + r : m - 1, j = j0 + r < l ? j0 + r : l - 1;
+                av[r] = trans_a ? a[(size_t)kk * m + i] : a[(size_t)i * k + kk];
+                bv[r] = b[(size_t)kk * l + j];
+            }
+#pragma unroll
+            for (int r = 0; r < 4; ++r)
+#pragma unroll
+                for (int c = 0; c < 4; ++c)
+                    acc[r][c] = fma(av[r], bv[c], acc[r][c]);
+        }
+        double *cm = Cm + e * (unsigned long long)m * l;
+#pragma unroll
+        for (int r = 0; r < 4; ++r)
+#pragma unroll
+            for (int c = 0; c < 4; ++c)
+                if (i0 + r < m && j0 + c < l)
+                    cm[(size_t)(i0 + r) * l + j0 + c] = acc[r][c];
+    }
+}
+
 // ---- out[e] = [[A[e], L^T], [L, 0]] : the same `pad` Lagrange rows (COO, entries lval) for every element --------------
 __global__ void border_batch_kernel(unsigned long long n_elem, int N, int pad, const double *__restrict__ A, int nnz,
                                     const int32_t *__restrict__ lrow, const int32_t *__restrict__ lcol, const double *__restrict__ lval,
@@ -207,6 +249,39 @@ int mfv2d_cuda_batched_gemv(mfv2d_ctx *ctx, size_t n, int rows, int cols, const 
         stage_abort(&sy);
     stage_abort(&sa);
     stage_abort(&sx);
+    return r;
+}
+
+int mfv2d_cuda_batched_gemm(mfv2d_ctx *ctx, size_t n, int m, int k, int l, int trans_a, const double *a, const double *b, double *c, int space)
+{
+    if (m < 1 || k < 1 || l < 1)
+        return mfv2d_fail(ctx, MFV2D_BAD_ARGUMENT, "batched_gemm: m, k and l must be positive");
+    if (n == 0)
+        return MFV2D_SUCCESS;
+    Staged sa, sb, sc;
+    int r = stage_in(ctx, a, n * (size_t)m * k * sizeof(double), space, &sa);
+    if (!r)
+        r = stage_in(ctx, b, n * (size_t)k * l * sizeof(double), space, &sb);
+    if (!r)
+        r = stage_out_alloc(ctx, c, n * (size_t)m * l * sizeof(double), space, &sc);
+    if (!r)
+    {
+        const unsigned long long total = (unsigned long long)n * ((m + 3) / 4) * ((l + 3) / 4);
+        unsigned long long grid = (total + REFINE_THREADS - 1) / REFINE_THREADS;
+        if (grid > (unsigned long long)ctx->sm_count * 16)
+            grid = (unsigned long long)ctx->sm_count * 16;
+        MFV2D_LAUNCH(batched_gemm_kernel, (unsigned)grid, REFINE_THREADS, 0, ctx->stream, (unsigned long long)n, m, k, l, trans_a ? 1 : 0,
+                     (const double *)sa.dev, (const double *)sb.dev, (double *)sc.dev);
+        ctx->launches++;
+        if (cudaGetLastError() != cudaSuccess)
+            r = mfv2d_fail(ctx, MFV2D_CUDA_ERROR, "batched_gemm kernel launch failed");
+    }
+    if (!r)
+        r = stage_finish(&sc);
+    else
+        stage_abort(&sc);
+    stage_abort(&sa);
+    stage_abort(&sb);
     return r;
 }
 
