@@ -46,7 +46,8 @@ def non_linear_solve_run(form_specs, lhs_codes, rhs_codes, batch: M.ElementBatch
                          constraint_rhs: np.ndarray, solution: np.ndarray, lagrange: np.ndarray, *, max_iterations: int, atol: float,
                          rtol: float, relax: float = 1.0, max_mag: float | None = None, time_carry_index: np.ndarray | None = None,
                          time_carry_term: np.ndarray | None = None, solve: Callable | None = None, field_values=None,
-                         reduce_max: Callable[[float], float] | None = None, field_cache: dict | None = None):
+                         reduce_max: Callable[[float], float] | None = None, field_cache: dict | None = None, sg_operator=None,
+                         fine_scales: np.ndarray | None = None, residual_history: list | None = None):
     """``non_linear_solve_run`` (python/mfv2d/solve_system.py:353-485) on one bucket of elements.
 
     ``explicit_vec`` ``(n * N_e,)`` is the dense right-hand side (weak boundary terms included), ``constraint_rhs`` the one of
@@ -55,7 +56,13 @@ def non_linear_solve_run(form_specs, lhs_codes, rhs_codes, batch: M.ElementBatch
     solve, ``system_decomp`` of the reference); ``solve(system, r_dense, r_trace) -> (dx, dlambda)`` defaults to the
     Schur-complement CG, pass ``solving.solve_schur_bicgstab`` based solvers for non-symmetric blocks.  On a partitioned
     system (one strip of the mesh per rank, ``system`` connected to its peers) every rank passes its local vectors, the
-    GLOBAL ``max_mag`` and ``reduce_max`` = the host's max-all-reduce: the stopping decision is then the same on all ranks."""
+    GLOBAL ``max_mag`` and ``reduce_max`` = the host's max-all-reduce: the stopping decision is then the same on all ranks.
+
+    ``sg_operator`` (:class:`mfv2d_b200.vms.SuyashGreenOperator`) adds the variational-multiscale closure of
+    solve_system.py:432-440: before the residual is tested the unresolved contributions are recomputed from the current
+    solution (starting from ``fine_scales``) and their coarse image is taken off the residual; the function then returns a
+    fifth value, the unresolved scales it ended with, like the reference.  ``residual_history``: a list that receives the
+    maximum residual of every iteration (``return_all_residuals`` of the reference)."""
     n, ne = batch.n, form_specs.total_size(batch.p, batch.p)
     base = np.array(explicit_vec, np.float64)
     if time_carry_term is not None:
@@ -71,6 +78,7 @@ def non_linear_solve_run(form_specs, lhs_codes, rhs_codes, batch: M.ElementBatch
     if field_cache is None:
         field_cache = {}
     iter_cnt, max_residual = 0, 0.0
+    unresolved = fine_scales
     while iter_cnt < max_iterations:
         lhs = _apply_codes(form_specs, lhs_codes, batch, solution.reshape(n, ne), field_values, field_cache)
         if rhs_codes is not None:
@@ -78,15 +86,25 @@ def non_linear_solve_run(form_specs, lhs_codes, rhs_codes, batch: M.ElementBatch
         main_value = np.asarray(lhs).ravel() + system.apply_trace_transpose(lagrange)
         r_dense = base - main_value
         r_trace = constraint_rhs - system.apply_trace(solution)
+        if sg_operator is not None:
+            sg_operator.update_nonlinear_advection(solution)
+            unresolved = sg_operator.compute_unresolved_contributions(solution, unresolved)
+            image = sg_operator.fine_results_to_coarse_dofs(unresolved, dual=True)
+            r_dense -= image[: r_dense.size]
+            r_trace -= image[r_dense.size:]
         max_residual = float(max(np.max(np.abs(r_dense), initial=0.0), np.max(np.abs(r_trace), initial=0.0)))
         if reduce_max is not None:
             max_residual = float(reduce_max(max_residual))
+        if residual_history is not None:
+            residual_history.append(max_residual)
         if not (max_residual > atol and max_residual > max_mag * rtol):
             break
         dx, dl = solve(system, r_dense, r_trace)
         solution += relax * dx
         lagrange += relax * dl
         iter_cnt += 1
+    if sg_operator is not None:
+        return solution, lagrange, iter_cnt, max_residual, unresolved
     return solution, lagrange, iter_cnt, max_residual
 
 

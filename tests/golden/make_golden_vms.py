@@ -10,7 +10,8 @@ vectors: the bytecode of the systems, the constraint rows ``add_system_constrain
 mesh, the fine forcing, the two projectors (element 0), ``fine_scale_greens_function``, ``compute_unresolved_contributions``
 (with and without an initial guess, relaxation 1 and 0.7), ``recover_unresolved`` and ``fine_results_to_coarse_dofs``; and
 the same operator with the non-linear advection ``0.3 (q * v @ q)`` added: ``update_nonlinear_advection`` at a scaled coarse
-solution, the advection block of element 0 and the unresolved contributions after it.
+solution, the advection block of element 0 and the unresolved contributions after it.  ``solve_*``: the steady solve of the
+full system without and with the closure by the reference's ``solve_system_2d`` (see ``solve_fixture``).
 """
 import json
 import os
@@ -49,6 +50,54 @@ def coo(m):
     m = m.tocoo()
     o = np.lexsort((m.col, m.row))
     return m.row[o].astype(np.int64), m.col[o].astype(np.int64), m.data[o].astype(np.float64), int(m.shape[0])
+
+
+def solve_fixture(mesh, sym, non, full, increase, conv):
+    """The steady solve of the full system with the VMS closure through the reference's own driver (solve_system_2d with
+    vms_settings, python/mfv2d/solve_system_2d.py:303-316, solve_system.py:432-440): right-hand side and constraint rows of
+    compute_linear_system, the residual history of non_linear_solve_run, the solution and the fine scales it ends with."""
+    import mfv2d.solve_system_2d  # noqa: F401
+    from mfv2d.solve_system import SolverSettings, SystemSettings
+
+    S2 = sys.modules["mfv2d.solve_system_2d"]
+    cap = {}
+    orig_recon, orig_nl, orig_lin = S2.reconstruct_mesh_from_solution, S2.non_linear_solve_run, S2.compute_linear_system
+
+    def recon(form_specs, recon_order, spaces, solution, fine_scales):
+        cap["solution"] = np.array(solution, np.float64)
+        cap["fine"] = None if fine_scales is None else np.array(fine_scales, np.float64)
+        return orig_recon(form_specs, 1, spaces, solution, None)
+
+    def nl(*a, **kw):
+        out = orig_nl(*a, **kw)
+        cap["iterations"], cap["residuals"] = int(out[2]), np.array(out[3]).ravel()[: int(out[2]) + 1]
+        return out
+
+    def lin(*a, **kw):
+        out = orig_lin(*a, **kw)
+        cap["explicit"] = np.concatenate([np.array(x) for x in out[0]])
+        cap["lag"], cap["lag_vec"] = out[2], np.array(out[3])
+        return out
+
+    S2.reconstruct_mesh_from_solution, S2.non_linear_solve_run, S2.compute_linear_system = recon, nl, lin
+    out = {}
+    try:
+        for tag, vms in (("plain", None), ("vms", VMSSettings(sym, non, increase, conv, 1.0))):
+            S2.solve_system_2d(mesh, system_settings=SystemSettings(full, over_integration_order=2),
+                               solver_settings=SolverSettings(ConvergenceSettings(maximum_iterations=40, relative_tolerance=0, absolute_tolerance=1e-11)),
+                               vms_settings=vms, recon_order=1)
+            out[f"solve_{tag}_solution"], out[f"solve_{tag}_residuals"] = cap["solution"], cap["residuals"]
+            if vms is not None:
+                out["solve_vms_fine_scales"] = cap["fine"]
+    finally:
+        S2.reconstruct_mesh_from_solution, S2.non_linear_solve_run, S2.compute_linear_system = orig_recon, orig_nl, orig_lin
+    cfull = CompiledSystem(full)
+    assert cfull.rhs_codes is None
+    out["solve_codes"] = json.dumps({"lhs": encode_codes(cfull.lhs_codes)})
+    out["solve_explicit"] = cap["explicit"]
+    r, c, val, rows = coo(cap["lag"])
+    out["solve_con_row"], out["solve_con_col"], out["solve_con_val"], out["solve_con_rhs"] = r, c, val, cap["lag_vec"]
+    return out
 
 
 def main(nh=3, nv=2, order=3, increase=1):
@@ -114,6 +163,7 @@ def main(nh=3, nv=2, order=3, increase=1):
     data["codes_nonlin"] = json.dumps(codes2)
     data["unresolved_nonlin"] = op2.compute_unresolved_contributions(small[: n * nc], None)
     data["advection_nonlin_0"] = op2.fine_advection_operator.toarray()[:nf, :nf]
+    data.update(solve_fixture(mesh, sym, non, full, increase, conv))
     np.savez_compressed(os.path.join(HERE, "vms.npz"), **data)
     for k_, v_ in data.items():
         print(k_, np.asarray(v_).shape, float(np.abs(np.asarray(v_, dtype=float)).max()) if not isinstance(v_, str) else "")

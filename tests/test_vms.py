@@ -95,6 +95,32 @@ def run_checks(M):
     op2.update_nonlinear_advection(small)  # a second update replaces the non-linear part, it does not accumulate
     assert rel_max(op2.fine_advection.get()[0], g["advection_nonlin_0"]) < 1e-12
     assert rel_max(op2.compute_unresolved_contributions(small[: n * nc], None), g["unresolved_nonlin"]) < TOL
+    # the steady solve with the closure (solve_system.py:432-440 inside non_linear_solve_run) against the reference's own
+    # solve_system_2d(vms_settings=...): same residual history, solution and fine scales; corrections by BiCGStab on the
+    # Schur complement of the full (advective) operator instead of SuperLU
+    from mfv2d_b200 import callers as CL
+
+    lhs = decode(json.loads(str(g["solve_codes"]))["lhs"])
+    con = (g["solve_con_row"], g["solve_con_col"], g["solve_con_val"])
+    n_trace = g["solve_con_rhs"].size
+    system = SV.compute_linear_system(specs, lhs, batch, con, n_trace)
+    kry = SV.ConvergenceSettings(5000, 1e300, 1e-14)
+
+    def solve(sysm, rd, rt):
+        return SV.solve_schur_bicgstab(sysm, rd, rt, kry)[:2]
+
+    for tag, sg in (("plain", None), ("vms", make(1.0))):
+        hist = []
+        out = CL.non_linear_solve_run(specs, lhs, None, batch, system, g["solve_explicit"], g["solve_con_rhs"], np.zeros(n * nc), np.zeros(n_trace),
+                                      max_iterations=40, atol=1e-11, rtol=0.0, solve=solve, sg_operator=sg, residual_history=hist)
+        ref_hist = g[f"solve_{tag}_residuals"]
+        assert out[2] == ref_hist.size - 1, (tag, out[2], hist, ref_hist)
+        assert np.allclose(hist[:-1], ref_hist[:-1], rtol=1e-6, atol=1e-11), (tag, hist, ref_hist)
+        assert rel_max(out[0], g[f"solve_{tag}_solution"]) < 1e-9, (tag, rel_max(out[0], g[f"solve_{tag}_solution"]))
+        if sg is not None:
+            assert len(out) == 5 and rel_max(out[4], g["solve_vms_fine_scales"]) < 1e-7
+        else:
+            assert len(out) == 4
     return op.krylov_iterations
 
 
