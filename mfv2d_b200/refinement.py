@@ -16,9 +16,9 @@ reference (python/mfv2d/refinement.py)          here
                                                 batched dense solver, reconstruction, Legendre estimates
 =============================================  =====================================================================
 
-Not covered: the weak-boundary-condition contribution to the residual (:902-958) - it walks the reference's ``Mesh`` /
-dual manifold objects, which are outside this path - and the VMS estimator (:1387-), which needs the global fine-scale
-Green's operator of ``mfv2d.solve_system``.
+The weak-boundary-condition contribution to the residual (:902-958) walks the reference's ``Mesh`` / dual manifold; here
+it is an array argument (``boundary_residual``, built by ``structured.weak_bc_contributions``).  The fine-scale Green's
+operator the VMS estimator (:1387-) needs is ``mfv2d_b200.vms.SuyashGreenOperator``.
 """
 from __future__ import annotations
 
@@ -120,7 +120,8 @@ def error_estimate_with_order_reduction(solution, batch: M.ElementBatch, reducti
 
 
 def error_estimate_with_local_inversion(solution, batch: M.ElementBatch, recon_order: int, form_specs, lhs_codes, rhs_codes, system,
-                                        form_index: int, zeroed_forms: Sequence[int] = (), constrained_forms: Sequence[int] = ()):
+                                        form_index: int, zeroed_forms: Sequence[int] = (), constrained_forms: Sequence[int] = (),
+                                        boundary_residual=None):
     """python/mfv2d/refinement.py:832-1093 for all elements of ``batch`` (without the weak-boundary-condition part of the
     residual, :902-958): the solution is projected to order ``p + recon_order``, the residual of the system is formed
     there with the matrix-free apply, the local system - bordered with Lagrange rows that zero the boundary DoFs of
@@ -128,7 +129,11 @@ def error_estimate_with_local_inversion(solution, batch: M.ElementBatch, recon_o
     target form's part of the local solution is the error field.
 
     ``system`` provides the right-hand-side functions as in :func:`mfv2d_b200._mfv2d.compute_element_rhs`;
-    ``lhs_codes`` / ``rhs_codes`` are the bytecode of ``CompiledSystem`` (``rhs_codes`` may be ``None``)."""
+    ``lhs_codes`` / ``rhs_codes`` are the bytecode of ``CompiledSystem`` (``rhs_codes`` may be ``None``).
+    ``boundary_residual`` ``(n, N_fine)``: the natural-boundary-condition terms of the right-hand side on the space of order
+    ``p + recon_order`` (``structured.weak_bc_contributions`` with the fine order), added to the residual where the
+    reference intends to (:902-958; its own loop runs over a boolean mask instead of line indices and takes the side DoFs
+    with the coarse orders, so it cannot serve as a fixture - the argument is the array-side replacement)."""
     n, p, q = batch.n, batch.p, batch.q
     ctx = batch.ctx
     ph = p + int(recon_order)
@@ -154,6 +159,8 @@ def error_estimate_with_local_inversion(solution, batch: M.ElementBatch, recon_o
     residual -= forcing
     if rhs_codes is not None and any(any(c for c in row) for row in rhs_codes):
         residual += M.compute_element_vectors(form_specs, rhs_codes, fine, d_fine, out=ctx.empty((n, ne_f))).get()
+    if boundary_residual is not None:
+        residual += np.asarray(boundary_residual, np.float64).reshape(n, ne_f)
     # local systems (:989-1053)
     d_lhs = M.compute_element_matrices(form_specs, lhs_codes, fine, d_fine, out=ctx.empty((n, ne_f, ne_f)))
     target_order = int(form_specs[form_index][1])

@@ -206,6 +206,45 @@ def strong_bc_constraints(nh: int, nv: int, p: int, form_orders, form_index: int
     return np.concatenate(cols).astype(np.int64), np.concatenate(vals)
 
 
+def weak_bc_contributions(nh: int, nv: int, p: int, form_orders, form_index: int, terms, corners: np.ndarray, node: np.ndarray, edge: np.ndarray,
+                          rule_nodes: np.ndarray, rule_weights: np.ndarray, skip_lines=(), out: np.ndarray | None = None) -> np.ndarray:
+    """Weak (natural) boundary terms of the equation weighted by form ``form_index`` on the boundary of the structured mesh
+    (``_element_weak_boundary_condition``, python/mfv2d/boundary.py:109-214, called per boundary line by
+    ``mesh_boundary_conditions`` :439-487): for every boundary side the boundary functions of ``terms`` = ``[(k, func), ...]``
+    (the ``KBoundaryProjection`` pairs of the equation's right-hand side) are sampled at the 1-D rule's points on the straight
+    side and integrated against the trace basis - 0-forms: ``-(f . t)`` with the nodal basis, 1-forms: ``-n_dir f`` with the
+    edge basis.  ``node`` / ``edge`` are ``Basis1D(p, rule).node / .edge``; ``skip_lines`` lists the positions in
+    :func:`boundary_lines` that carry a strong condition instead.  Adds into ``out`` ``(n, N_e)`` (created when ``None``):
+    the array that is added to ``compute_element_rhs`` to form the explicit right-hand side of ``compute_linear_system``."""
+    offs, ne = _form_offsets(form_orders, p)
+    order = int(form_orders[form_index])
+    if order not in (FORM_ORDER_0, FORM_ORDER_1):
+        raise ValueError(f"Unknown/Invalid weak form order form_order={order}.")
+    o = int(offs[form_index])
+    if out is None:
+        out = np.zeros((nh * nv, ne))
+    skip = set(int(i) for i in skip_lines)
+    for i_line, (e, side) in enumerate(boundary_lines(nh, nv)):
+        if i_line in skip:
+            continue
+        p0, p1 = corners[e, side - 1], corners[e, side & 3]
+        dx, dy = (p1[0] - p0[0]) / 2, (p1[1] - p0[1]) / 2
+        xv = (p1[0] + p0[0]) / 2 + dx * rule_nodes
+        yv = (p1[1] + p0[1]) / 2 + dy * rule_nodes
+        ndir = 2 * ((side & 2) >> 1) - 1
+        dofs = _side_dofs(side, order, p) + o
+        vals = np.zeros(dofs.size)
+        for k, func in terms:
+            f = np.array(func(xv, yv), np.float64)
+            if order == FORM_ORDER_0:
+                basis, f = node, -(f[..., 0] * dx + f[..., 1] * dy) * rule_weights
+            else:
+                basis, f = edge, f * (-rule_weights * ndir)
+            vals += np.sum(f[None, ...] * basis, axis=1) * k
+        out[e, dofs] += vals
+    return out
+
+
 def system_constraints(nh: int, nv: int, p: int, form_orders, constrained_forms=(), strong_bcs=(), corners=None, roots=None, rule_nodes=None,
                        rule_weights=None):
     """The whole constraint matrix of ``add_system_constraints`` (python/mfv2d/continuity.py:762-872) for a conforming

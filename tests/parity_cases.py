@@ -876,6 +876,18 @@ def check_time_march(M, SV, ST):
     mat0 = M.compute_element_matrices(specs, lhs, batch)[0]
     assert relerr(mat0, g["mat0"]) < TOL_MAT
     assert relerr(mat0, mat0.T) > 1e-3  # the advection term makes the blocks non-symmetric
+    # the explicit right-hand side of the reference's compute_linear_system rebuilt from arrays: dual DoFs of the source on
+    # the u rows (device) + the weak boundary terms `p ^ u_bc` on the q rows (structured.weak_bc_contributions)
+    ne = specs.total_size(p, p)
+    iq, iu = raw["form_names"].index("q"), raw["form_names"].index("u")
+    rhs = np.zeros((batch.n, ne))
+    ou = specs.form_offset(iu, p, p)
+    rhs[:, ou:ou + specs.form_size(iu, p, p)] = batch.dual_dofs(3, lambda x, y: 3.0 * np.cos(np.pi * x) * np.sin(0.7 * np.pi * y))
+    b1 = batch.basis_2d.basis_xi
+    ST.weak_bc_contributions(int(g["nh"]), int(g["nv"]), p, raw["form_orders"], iq,
+                             [(1.0, lambda x, y: np.sin(0.5 * np.pi * x) * np.cos(0.5 * np.pi * y) + 1.0)], g["corners"], np.asarray(b1.node),
+                             np.asarray(b1.edge), np.asarray(b1.rule.nodes), np.asarray(b1.rule.weights), out=rhs)
+    assert np.max(np.abs(rhs.ravel() - g["explicit"])) < 1e-13 * np.max(np.abs(g["explicit"]))
     nt = g["con_rhs"].size
     sols, iters = CL.trapezoidal_march(specs, lhs, None, batch, (g["con_row"], g["con_col"], g["con_val"]), nt, g["con_rhs"], g["explicit"],
                                        [raw["form_names"].index("u")], float(g["dt"]), int(g["nt"]))

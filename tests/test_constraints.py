@@ -65,3 +65,23 @@ def test_solve_fixture_constraints_bit_exact(fix, nh, nv):
     row2, col2, val2, n = ST.continuity_constraints_1form(nh, nv, p, fo)
     assert n == g["con_rhs"].size
     assert np.array_equal(row2, g["con_row"][o].astype(np.int64)) and np.array_equal(col2, col[o]) and np.array_equal(val2, g["con_val"][o])
+
+
+@pytest.mark.parametrize("nh,nv,p", MESHES)
+def test_weak_boundary_terms(nh, nv, p):
+    """weak_bc_contributions against the weak ElementConstraints of the reference's mesh_boundary_conditions
+    (tests/golden/weak_bc.npz): tangential integrals for the 0-form weight, normal integrals for the 1-form weight, lines
+    with a strong condition skipped.  The 1-D tables come from the oracle here; the sums are the reference's, so the
+    agreement is to rounding."""
+    g = golden("weak_bc.npz")
+    fo = [int(o) for o in g["form_orders"]]
+    corners = g[f"corners_{nh}x{nv}"]
+    assert np.array_equal(corners, ST.unit_square_corners(nh, nv, F.deform))
+    b = O.basis(p, p + 3)  # FemCache(2): p + 3 points
+    for tag, skip in (("none", ()), ("half", g[f"half_lines_{nh}x{nv}"])):
+        ref = g[f"weak_{tag}_{nh}x{nv}_p{p}"]
+        out = ST.weak_bc_contributions(nh, nv, p, fo, 0, [(0.5, bc_vec)], corners, b.node, b.edge, b.pnts, b.wgts)
+        ST.weak_bc_contributions(nh, nv, p, fo, 1, [(-2.0, bc_u)], corners, b.node, b.edge, b.pnts, b.wgts, skip_lines=skip, out=out)
+        assert np.max(np.abs(out - ref)) <= 1e-14 * np.max(np.abs(ref)), (tag, np.max(np.abs(out - ref)))
+    with pytest.raises(ValueError):
+        ST.weak_bc_contributions(nh, nv, p, fo, 2, [(1.0, bc_u)], corners, b.node, b.edge, b.pnts, b.wgts)

@@ -74,6 +74,31 @@ def run_checks(M):
             err, cost = R.error_estimate_with_local_inversion(sol, batch, 1, specs, s["lhs"], s.get("rhs"), system, fi, zeroed, constrained)
             ref = g[f"local_{tag}_{name}"]
             assert rel(err, ref[:, 0]) < 1e-8 and rel(cost, ref[:, 1]) < 1e-8, (tag, name, rel(err, ref[:, 0]), rel(cost, ref[:, 1]))
+    # boundary_residual: extra right-hand-side terms on the fine space.  Adding the dual DoFs of a second forcing g as
+    # `boundary_residual` must equal the estimator of the system whose right-hand side is f + g (the residual is linear in it);
+    # with the weak boundary terms of structured.weak_bc_contributions (fine order) the call runs and changes the estimate
+    from mfv2d_b200 import structured as ST
+
+    def extra(x, y):
+        return np.sin(2.0 * x) * (1.0 + y)
+
+    fine_rule = M.IntegrationRule1D(batch.q - 1)
+    fb1 = M.Basis1D(p + 1, fine_rule)
+    fine = M.ElementBatch(M.Basis2D(fb1, fb1), np.ascontiguousarray(g["corners"]))
+    nf = specs.total_size(p + 1, p + 1)
+    b_res = np.zeros((batch.n, nf))
+    ou = specs.form_offset(iu, p + 1, p + 1)
+    b_res[:, ou:ou + specs.form_size(iu, p + 1, p + 1)] = fine.dual_dofs(3, extra)
+    eqs2 = [eqs[0], types.SimpleNamespace(weight=types.SimpleNamespace(order=3), right=types.SimpleNamespace(
+        explicit_terms=((1.0, types.SimpleNamespace(func=forcing)), (1.0, types.SimpleNamespace(func=extra)))))]
+    e1, c1 = R.error_estimate_with_local_inversion(sol, batch, 1, specs, s["lhs"], s.get("rhs"), system, iu, (), (), boundary_residual=b_res)
+    e2, c2 = R.error_estimate_with_local_inversion(sol, batch, 1, specs, s["lhs"], s.get("rhs"), types.SimpleNamespace(equations=eqs2), iu)
+    assert rel(e1, e2) < 1e-9 and rel(c1, c2) < 1e-9
+    weak = ST.weak_bc_contributions(3, 2, p + 1, [int(o) for o in specs.orders], iq, [(1.0, extra)], g["corners"], np.asarray(fb1.node),
+                                    np.asarray(fb1.edge), np.asarray(fine_rule.nodes), np.asarray(fine_rule.weights))
+    e3, _ = R.error_estimate_with_local_inversion(sol, batch, 1, specs, s["lhs"], s.get("rhs"), system, iu, (), (), boundary_residual=weak)
+    e0, _ = R.error_estimate_with_local_inversion(sol, batch, 1, specs, s["lhs"], s.get("rhs"), system, iu)
+    assert np.all(np.isfinite(e3)) and rel(e3, e0) > 1e-6
     with pytest.raises(ValueError):  # the reference raises for a 2-form target with zeroed forms (element_boundary_dofs)
         R.error_estimate_with_local_inversion(sol, batch, 1, specs, s["lhs"], s.get("rhs"), system, iu, (iq,), ())
 
