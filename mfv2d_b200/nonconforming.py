@@ -268,3 +268,131 @@ def continuity_constraints_forest(forest: QuadForest, form_orders):
     if not rows:
         return np.zeros(0, np.int64), np.zeros(0, np.int64), np.zeros(0), 0, offsets
     return np.concatenate(rows), np.concatenate(cols).astype(np.int64), np.concatenate(vals), n_rows, offsets
+
+
+def boundary_terms_forest(forest: QuadForest, form_orders, root_corners, over_integration: int, strong=(), weak=()):
+    """``mesh_boundary_conditions`` (python/mfv2d/boundary.py:382-498) for a :class:`QuadForest`.
+
+    The boundary lines are those of the root grid, in the order of ``structured.boundary_lines`` (= ``mesh.boundary_indices``);
+    along a refined side the leaves are visited first child first (:152-172, :264-289).  Per line the equations are taken in
+    form order: ``strong`` = ``[(form index, func, line positions or None for all lines), ...]`` wins over ``weak`` =
+    ``[(form index, [(k, func), ...]), ...]``.  Strong 0-form rows skip a root-grid node that an earlier line has set (:455-470) -
+    the node between two children of one side is set from both (the reference does the same); 1-form rows are the fluxes
+    through the sub-edges.  ``over_integration`` is the ``FemCache`` order difference (rule of order ``p + over_integration``).
+
+    Returns ``(leaf, dof, value)`` arrays of the strong rows in the reference's order (``dof`` local to the leaf, form offset
+    included) and the weak contributions as one flat vector over the global dense columns."""
+    from .structured import boundary_lines
+
+    orders = [int(o) for o in form_orders]
+    corners = forest.leaf_corners(root_corners)
+    sizes = np.array([int(form_sizes(orders, int(p)).sum()) for p in forest.leaf_orders], np.int64)
+    offsets = np.concatenate([[0], np.cumsum(sizes)])
+    weak_vec = np.zeros(int(offsets[-1]))
+    s_leaf, s_dof, s_val = [], [], []
+    tables: dict[int, tuple] = {}
+
+    def basis(p: int):
+        if p not in tables:
+            rule = M.IntegrationRule1D(p + int(over_integration))
+            b = M.Basis1D(p, rule)
+            tables[p] = (np.asarray(b.roots, np.float64), np.asarray(rule.nodes, np.float64), np.asarray(rule.weights, np.float64),
+                         np.asarray(b.node, np.float64), np.asarray(b.edge, np.float64))
+        return tables[p]
+
+    def leaves_on(e: int, side: int, first: bool, last: bool):
+        """(leaf element, skip_first, skip_last) along the side, first child first"""
+        if not forest.is_split(e):
+            return [(e, first, last)]
+        a, b = forest.pair_on_side(e, side)
+        return leaves_on(a, side, first, False) + leaves_on(b, side, False, last)
+
+    nh, nv = forest.nh, forest.nv
+    set_nodes = np.zeros((nv + 1, nh + 1), bool)
+    strong_of = {int(fi): (func, None if lines is None else set(int(i) for i in lines)) for fi, func, lines in strong}
+    weak_of = {int(fi): terms for fi, terms in weak}
+    for i_line, (root, side) in enumerate(boundary_lines(nh, nv)):
+        ei, ej = root % nh, root // nh
+        node_of = [(ej, ei), (ej, ei + 1), (ej + 1, ei + 1), (ej + 1, ei)]
+        n0, n1 = node_of[side - 1], node_of[side & 3]
+        ndir = 2 * ((side & 2) >> 1) - 1
+        for f, order in enumerate(orders):
+            is_strong = f in strong_of and (strong_of[f][1] is None or i_line in strong_of[f][1])
+            if not is_strong and not weak_of.get(f):
+                continue
+            if order == FORM_ORDER_2:
+                raise ValueError(f"Unknown/Invalid weak form order form_order={order}." if not is_strong else "2-forms have no boundary DoFs.")
+            for e, skip_first, skip_last in leaves_on(root, side, bool(is_strong and set_nodes[n0]), bool(is_strong and set_nodes[n1])):
+                leaf = int(forest.leaf_index[e])
+                p = int(forest.leaf_orders[leaf])
+                roots, rn, rw, node, edge = basis(p)
+                c = corners[leaf]
+                p0, p1 = c[side - 1], c[side & 3]
+                dx, dy = (p1[0] - p0[0]) / 2, (p1[1] - p0[1]) / 2
+                form_off = int(form_sizes(orders[:f], p).sum()) if f else 0
+                dofs = np.asarray(_side_dofs(side, order, p), np.int64) + form_off
+                if is_strong:
+                    func = strong_of[f][0]
+                    xv = (p1[0] + p0[0]) / 2 + dx * roots
+                    yv = (p1[1] + p0[1]) / 2 + dy * roots
+                    if order == FORM_ORDER_0:
+                        v = np.asarray(func(xv, yv), np.float64) * np.ones(p + 1)
+                        lo, hi = (1 if skip_first else 0), (p if skip_last else p + 1)
+                        dofs, v = dofs[lo:hi], v[lo:hi]
+                    else:
+                        v = np.zeros(p)
+                        for i in range(p):
+                            xc = (xv[i + 1] + xv[i]) / 2 + (xv[i + 1] - xv[i]) / 2 * rn
+                            yc = (yv[i + 1] + yv[i]) / 2 + (yv[i + 1] - yv[i]) / 2 * rn
+                            ddx, ddy = (xv[i + 1] - xv[i]) / 2, (yv[i + 1] - yv[i]) / 2
+                            normal = ndir * np.array((ddy, -ddx))
+                            fv = np.asarray(func(xc, yc), np.float64)
+                            v[i] = np.sum((fv[..., 0] * normal[0] + fv[..., 1] * normal[1]) * rw)
+                    s_leaf.append(np.full(dofs.size, leaf, np.int64)), s_dof.append(dofs), s_val.append(v)
+                else:
+                    xv = (p1[0] + p0[0]) / 2 + dx * rn
+                    yv = (p1[1] + p0[1]) / 2 + dy * rn
+                    vals = np.zeros(dofs.size)
+                    for k, func in weak_of[f]:
+                        fv = np.array(func(xv, yv), np.float64)
+                        if order == FORM_ORDER_0:
+                            tab, fv = node, -(fv[..., 0] * dx + fv[..., 1] * dy) * rw
+                        else:
+                            tab, fv = edge, fv * (-rw * ndir)
+                        vals += np.sum(fv[None, ...] * tab, axis=1) * k
+                    weak_vec[offsets[leaf] + dofs] += vals
+            if is_strong:
+                set_nodes[n0] = set_nodes[n1] = True
+    cat = (lambda parts, dt: np.concatenate(parts).astype(dt) if parts else np.zeros(0, dt))
+    return (cat(s_leaf, np.int64), cat(s_dof, np.int64), cat(s_val, np.float64)), weak_vec
+
+
+def system_constraints_forest(forest: QuadForest, form_orders, root_corners, over_integration: int, constrained_forms=(), strong=(), weak=()):
+    """The constraint matrix and right-hand side of ``add_system_constraints`` (python/mfv2d/continuity.py:762-872) for a
+    :class:`QuadForest`: continuity rows (:func:`continuity_constraints_forest`), one row per ``constrained_forms`` entry
+    ``(value, form index)`` (every DoF of the form in every leaf, coefficient 1), one row per strongly set DoF
+    (:func:`boundary_terms_forest`).  Returns ``(row, col, val)`` sorted by row then column with duplicates summed (what
+    ``scipy.sparse.csr_array`` does to the reference's triplets), the right-hand side, the row count, the dense offsets of the
+    leaves and the weak boundary additions to the dense right-hand side."""
+    orders = [int(o) for o in form_orders]
+    row, col, val, n, offsets = continuity_constraints_forest(forest, orders)
+    rows, cols, vals, rhs = [row], [col], [val], [np.zeros(n)]
+    for value, fi in constrained_forms:
+        c = []
+        for leaf, p in enumerate(forest.leaf_orders):
+            fs = form_sizes(orders, int(p))
+            start = int(offsets[leaf] + fs[: int(fi)].sum())
+            c.append(np.arange(start, start + int(fs[int(fi)])))
+        c = np.concatenate(c)
+        rows.append(np.full(c.size, n, np.int64)), cols.append(c), vals.append(np.ones(c.size)), rhs.append(np.array([float(value)]))
+        n += 1
+    (s_leaf, s_dof, s_val), weak_vec = boundary_terms_forest(forest, orders, root_corners, over_integration, strong, weak)
+    rows.append(n + np.arange(s_val.size)), cols.append(offsets[s_leaf] + s_dof), vals.append(np.ones(s_val.size)), rhs.append(s_val)
+    n += int(s_val.size)
+    row, col, val = np.concatenate(rows).astype(np.int64), np.concatenate(cols).astype(np.int64), np.concatenate(vals)
+    # sum duplicates (a hanging-side row can name a DoF twice), sort by (row, column)
+    key = row * int(offsets[-1]) + col
+    uniq, inverse = np.unique(key, return_inverse=True)
+    summed = np.zeros(uniq.size)
+    np.add.at(summed, inverse, val)
+    return uniq // int(offsets[-1]), uniq % int(offsets[-1]), summed, np.concatenate(rhs), n, offsets, weak_vec

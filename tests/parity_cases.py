@@ -784,7 +784,7 @@ def check_hp_refined(M, SV, ST, fixture="hp_refined", gate=1e-10):
     return it, rel
 
 
-def check_hp_forest(M, SV, ST, mesh="b", gate=1e-10, sol_tol=1e-7):
+def check_hp_forest(M, SV, ST, mesh="b", gate=1e-10, sol_tol=1e-7, bc=False):
     """BASELINE.json configs[3] without any reference-generated input at run time: the quadtree of tests/golden/forest.npz as
     arrays -> leaf corners by subdivision, constraint rows from mfv2d_b200.nonconforming (pinned bit for bit to the reference in
     tests/test_nonconforming.py), element matrices per order bucket, ONE LinearSystem with mixed block sizes, the hanging-side row
@@ -817,11 +817,23 @@ def check_hp_forest(M, SV, ST, mesh="b", gate=1e-10, sol_tol=1e-7):
             r = np.zeros(out[j].shape[0])
             r[-int(p) * int(p):] = f[j]
             rhs_parts[e] = r
-    row, col, val, nt, off = NC.continuity_constraints_forest(forest, s["form_orders"])
-    assert np.array_equal(np.diff(off), [m.shape[0] for m in mats])
-    o = np.lexsort((col, row))
-    row, col, val = row[o], col[o], val[o]
-    rhs, phi = np.concatenate(rhs_parts), np.zeros(nt)
+    if bc:
+        # boundary conditions from arrays (nonconforming.system_constraints_forest): the flux q.n prescribed strongly on the first
+        # half of the boundary lines, the value of u weakly (natural condition) on the others
+        root_corners = ST.unit_square_corners(nh, nv, F.deform if mesh != "c" else None)
+        n_lines = 2 * (nh + nv)
+        row, col, val, phi, nt, off, weak_vec = NC.system_constraints_forest(
+            forest, s["form_orders"], root_corners, k, (),
+            [(0, lambda x, y: np.stack((np.pi * np.sin(np.pi * x) * np.cos(np.pi * y), np.pi * np.cos(np.pi * x) * np.sin(np.pi * y)), axis=-1), range(n_lines // 2))],
+            [(0, [(1.0, lambda x, y: np.cos(np.pi * x) * np.cos(np.pi * y))])])
+        assert np.array_equal(np.diff(off), [m.shape[0] for m in mats]) and np.any(weak_vec) and np.any(phi)
+        rhs = np.concatenate(rhs_parts) + weak_vec
+    else:
+        row, col, val, nt, off = NC.continuity_constraints_forest(forest, s["form_orders"])
+        assert np.array_equal(np.diff(off), [m.shape[0] for m in mats])
+        o = np.lexsort((col, row))
+        row, col, val = row[o], col[o], val[o]
+        rhs, phi = np.concatenate(rhs_parts), np.zeros(nt)
     A = sp.block_diag([sp.csr_matrix(m) for m in mats], format="csr")
     N = sp.coo_matrix((val, (row, col)), shape=(nt, int(off[-1]))).tocsr()
     K = sp.bmat([[A, N.T], [N, None]], format="csc")

@@ -52,6 +52,12 @@ def test_hp_forest(emu, mesh, gate, sol_tol):
     print(P.check_hp_forest(*emu, mesh, gate, sol_tol))
 
 
+def test_hp_forest_boundary_conditions(emu):
+    """the same solve with boundary conditions built from arrays: strong flux rows on half of the boundary (single-entry rows
+    next to the hanging-side rows), natural condition on the rest"""
+    print(P.check_hp_forest(*emu, "b", 1e-10, 1e-7, bc=True))
+
+
 def test_degenerate_element(emu):
     P.check_degenerate_element(emu[0])
 

@@ -60,6 +60,12 @@ def test_hp_forest(gpu, mesh, gate, sol_tol):
     print(P.check_hp_forest(*gpu, mesh, gate, sol_tol))
 
 
+def test_hp_forest_boundary_conditions(gpu):
+    """the same solve with boundary conditions built from arrays: strong flux rows on half of the boundary (single-entry rows
+    next to the hanging-side rows), natural condition on the rest"""
+    print(P.check_hp_forest(*gpu, "b", 1e-10, 1e-7, bc=True))
+
+
 def test_degenerate_element(gpu):
     P.check_degenerate_element(gpu[0])
 

@@ -7,7 +7,16 @@ import numpy as np
 import pytest
 from conftest import golden
 
+import fields as F
 from mfv2d_b200 import nonconforming as NC
+
+
+def bc_u(x, y):
+    return np.sin(1.3 * x + 0.2) * np.cos(0.7 * y - 0.1)
+
+
+def bc_vec(x, y):
+    return np.stack((np.cos(0.9 * x) * (1 + y), np.sin(1.1 * y + 0.3) * (2 - x)), axis=-1)
 
 FORMS = {"mixed": [2, 3], "direct": [1, 2], "stokes": [1, 2, 3]}
 
@@ -60,3 +69,41 @@ def test_forest_input_checks():
         NC.QuadForest(1, 1, np.full((1, 4), -1), [0], [2, 3])
     with pytest.raises(ValueError):
         NC.QuadForest(1, 1, np.array([[1, 2, 3, 4], [-1] * 4, [-1] * 4, [-1] * 4, [-1] * 4]), [0, 1, 2, 3], [2, 2, 2, 2])
+
+
+@pytest.mark.parametrize("mesh", ["a", "b", "c"])
+def test_boundary_terms_forest(mesh):
+    """Strong rows and weak right-hand-side terms on the boundary of the hp-refined meshes against the reference's
+    mesh_boundary_conditions (tests/golden/forest_bc.npz): same leaves, same DoFs, in the same order; values to rounding."""
+    from mfv2d_b200 import structured as ST
+
+    g, gb = golden("forest.npz"), golden("forest_bc.npz")
+    nh, nv = (int(v) for v in g[f"{mesh}_dims"])
+    forest = NC.QuadForest(nh, nv, g[f"{mesh}_children"], g[f"{mesh}_leaf"], g[f"{mesh}_orders"])
+    assert [tuple(t) for t in gb[f"{mesh}_lines"]] == ST.boundary_lines(nh, nv)
+    root_corners = ST.unit_square_corners(nh, nv, None if mesh == "c" else F.deform)
+    n_lines = 2 * (nh + nv)
+    cases = {
+        "stokes": ([1, 2, 3], [(1, bc_vec, range(n_lines // 2))], [(0, [(0.5, bc_vec)]), (1, [(-2.0, bc_u)])]),
+        "direct": ([1, 2], [(0, bc_u, None)], [(1, [(1.0, bc_u)])]),
+    }
+    for name, (orders, strong, weak) in cases.items():
+        (leaf, dof, val), weak_vec = NC.boundary_terms_forest(forest, orders, root_corners, 2, strong, weak)
+        tag = f"{mesh}_{name}"
+        assert np.array_equal(leaf, gb[tag + "_strong_leaf"]) and np.array_equal(dof, gb[tag + "_strong_dof"])
+        assert np.max(np.abs(val - gb[tag + "_strong_val"])) <= 1e-14 * max(1.0, np.max(np.abs(val)))
+        sizes = np.array([int(ST.form_sizes(orders, int(p)).sum()) for p in forest.leaf_orders])
+        offsets = np.concatenate([[0], np.cumsum(sizes)])
+        ref = np.zeros(offsets[-1])
+        np.add.at(ref, offsets[gb[tag + "_weak_leaf"]] + gb[tag + "_weak_dof"], gb[tag + "_weak_val"])
+        assert np.max(np.abs(weak_vec - ref)) <= 1e-14 * np.max(np.abs(ref)), np.max(np.abs(weak_vec - ref))
+        # the whole matrix of add_system_constraints (continuity + gauge + strong rows) and its weak additions
+        gauge = [(0.25, 2)] if name == "stokes" else []
+        row, col, val, rhs, n, offsets2, weak2 = NC.system_constraints_forest(forest, orders, root_corners, 2, gauge, strong, weak)
+        assert n == gb[tag + "_full_rhs"].size and np.array_equal(offsets2, offsets)
+        keep = gb[tag + "_full_val"] != 0  # scipy keeps explicit zeros of cancelled duplicates; the builder may or may not produce them
+        keep2 = val != 0
+        assert np.array_equal(row[keep2], gb[tag + "_full_row"][keep]) and np.array_equal(col[keep2], gb[tag + "_full_col"][keep])
+        assert np.max(np.abs(val[keep2] - gb[tag + "_full_val"][keep])) <= 1e-12
+        assert np.max(np.abs(rhs - gb[tag + "_full_rhs"])) <= 1e-14 * max(1.0, np.max(np.abs(rhs)))
+        assert np.max(np.abs(weak2 - gb[tag + "_full_weak"])) <= 1e-14 * np.max(np.abs(ref))
