@@ -300,6 +300,14 @@ MFV2D_API int mfv2d_cuda_element_vector_batch(const mfv2d_plan *plan, const mfv2
 /* out[b] = in[b]^-1 for `batch` n x n matrices (_compute_matrix_inverse). status[batch] or NULL. */
 MFV2D_API int mfv2d_cuda_inverse_batch(mfv2d_ctx *ctx, int n, size_t batch, const double *in, double *out,
                                        int32_t *status, int space);
+/* out = in^-1 for ONE large definite matrix (n x n, row-major, in place allowed: out == in), Gauss-Jordan WITHOUT pivoting,
+ * blocked 32 pivots per pass (a shared-memory block inverse, two panels, one register-tiled rank-32 update): the routine behind
+ * the exact level of the multilevel preconditioner (mfv2d_cuda_system_set_coarse_space).  The reference inverts dense
+ * matrices with pivoted LU (`_compute_matrix_inverse`, src/algebra/matrix.c:546-600) - use mfv2d_cuda_inverse_batch for
+ * matrices that need pivoting.  *status (HOST int, may be NULL) and the return code are MFV2D_PIVOT_FAILED when a pivot
+ * vanishes. */
+MFV2D_API int mfv2d_cuda_inverse_definite(mfv2d_ctx *ctx, int n, const double *in, double *out, int32_t *status,
+                                          int space);
 /* X[b] = A[b]^-1 B[b], B is n x nrhs row-major (_solve_linear_system). */
 MFV2D_API int mfv2d_cuda_solve_batch(mfv2d_ctx *ctx, int n, int nrhs, size_t batch, const double *a,
                                      const double *b, double *x, int32_t *status, int space);

@@ -96,6 +96,7 @@ SIGNATURES = {
     "mfv2d_cuda_element_matrix_batch": (i32, [vp, vp, dp, dp, dp, i32]),
     "mfv2d_cuda_element_vector_batch": (i32, [vp, vp, dp, dp, dp, i32]),
     "mfv2d_cuda_inverse_batch": (i32, [vp, i32, sz, dp, dp, vp, i32]),
+    "mfv2d_cuda_inverse_definite": (i32, [vp, i32, dp, dp, C.POINTER(i32), i32]),
     "mfv2d_cuda_inverse_definite_noalloc": (i32, [vp, i32, vp, vp, vp]),
     "mfv2d_cuda_batched_gemv": (i32, [vp, sz, i32, i32, dp, dp, dp, i32]),
     "mfv2d_cuda_batched_gemm": (i32, [vp, sz, i32, i32, i32, i32, dp, dp, dp, i32]),

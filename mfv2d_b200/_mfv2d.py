@@ -800,6 +800,22 @@ def _compute_matrix_inverse(x, /) -> np.ndarray:
     return out
 
 
+def inverse_definite(x, /) -> np.ndarray:
+    """Inverse of ONE large definite matrix by the blocked, unpivoted Gauss-Jordan elimination that serves the exact level of
+    the multilevel preconditioner (``mfv2d_cuda_inverse_definite``, dense.cu); no counterpart in the reference, whose dense
+    inverse is the pivoted LU of :func:`_compute_matrix_inverse`.  Raises when a pivot vanishes."""
+    import ctypes as C
+
+    ctx = get_context()
+    a = np.ascontiguousarray(x, np.float64)
+    if a.ndim != 2 or a.shape[0] != a.shape[1]:
+        raise ValueError("Input must be a square matrix.")
+    out = np.empty_like(a)
+    status = C.c_int(0)
+    check(lib().mfv2d_cuda_inverse_definite(ctx.handle, a.shape[0], a.ctypes.data, out.ctypes.data, C.byref(status), HOST), ctx.handle)
+    return out
+
+
 def _solve_linear_system(mat, rhs, /) -> np.ndarray:
     """src/algebra/matrix.c:578-660: solve ``mat @ x = rhs`` (rhs vector or matrix)."""
     ctx = get_context()

@@ -255,6 +255,23 @@ def check_dense(M):
         raise AssertionError("singular matrix must raise MFV2D_PIVOT_FAILED")
 
 
+def check_inverse_definite(M, sizes=(5, 64, 100, 333)):
+    """The large-matrix inverse behind the preconditioner's exact level (blocked Gauss-Jordan without pivoting from 64 x 64 on,
+    one pivot per pass below) against numpy on SPD and on non-symmetric diagonally dominant matrices, sizes that are not
+    multiples of the block or of the update tile; a singular matrix must be reported."""
+    rng = np.random.default_rng(21)
+    for n in sizes:
+        g = rng.standard_normal((n, n))
+        for a in (g @ g.T + n * np.eye(n), g + 2.0 * n * np.eye(n)):
+            inv = M.inverse_definite(a)
+            assert np.max(np.abs(inv @ a - np.eye(n))) < 1e-11, (n, np.max(np.abs(inv @ a - np.eye(n))))
+            assert relerr(inv, np.linalg.inv(a)) < 1e-11
+    z = np.zeros((70, 70))
+    with pytest.raises(Exception) as info:
+        M.inverse_definite(z)
+    assert "PIVOT" in str(info.value).upper()
+
+
 def check_fields(M, p=3, k=3):
     """tests/test_compute_fields.py: callable and DoF-based fields at the quadrature points."""
     rng = np.random.default_rng(4)

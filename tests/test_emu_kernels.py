@@ -123,3 +123,7 @@ def test_time_march(emu):
 
 def test_reconstruct_grid(emu):
     P.check_reconstruct_grid(emu[0])
+
+
+def test_inverse_definite(emu):
+    P.check_inverse_definite(emu[0])

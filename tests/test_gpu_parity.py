@@ -188,3 +188,7 @@ def test_full_size_properties(gpu):
     blocks, fs = O.decode_expressions(s["lhs"], s["form_names"])
     for e in range(0, batch.n, 4099):
         assert P.relerr(mats[e], O.element_matrix(ob, corners[e], s["form_orders"], blocks, fs)) < 1e-12
+
+
+def test_inverse_definite(gpu):
+    P.check_inverse_definite(gpu[0])
