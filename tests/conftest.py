@@ -23,6 +23,8 @@ def load_systems():
 
     with open(os.path.join(GOLDEN, "systems.json")) as f:
         raw = json.load(f)
+    with open(os.path.join(GOLDEN, "systems_examples.json")) as f:  # the remaining examples/unsteady systems (make_golden_examples.py)
+        raw.update(json.load(f))
 
     def dec(codes):
         if codes is None:
