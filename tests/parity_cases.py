@@ -945,6 +945,46 @@ def check_time_march(M, SV, ST):
     return iters
 
 
+def check_time_march_heat(M, SV, ST):
+    """A march with a 0-FORM unknown against the reference's own solve_system_2d (tests/golden/timemarch_heat.npz: the unsteady
+    direct heat equation of examples/unsteady/plot_heat_direct.py): 0-form continuity rows with corner chains and strong
+    boundary rows rebuilt from arrays, right-hand-side bytecode (a fixed-point iteration per step), CG on the Schur complement
+    of the symmetric positive definite blocks; host vectors and device-resident vectors."""
+    from mfv2d_b200 import callers as CL
+
+    g = golden("timemarch_heat.npz")
+    raw = json.loads(str(g["codes"]))
+
+    def dec(codes):
+        return tuple(tuple(None if blk is None else tuple(tuple(item) for item in blk) for blk in rowc) for rowc in codes)
+
+    lhs, rhs_codes = dec(raw["lhs"]), dec(raw["rhs"])
+    p, k, nh, nv = int(g["order"]), int(g["k"]), int(g["nh"]), int(g["nv"])
+    specs = M._ElementFormSpecification(*zip(raw["form_names"], raw["form_orders"]))
+    batch = M.ElementBatch(make_basis(M, p, k), np.ascontiguousarray(g["corners"]))
+    assert relerr(M.compute_element_matrices(specs, lhs, batch)[0], g["mat0"]) < TOL_MAT
+
+    def steady_u(x, y):
+        return np.cos(np.pi * x / 2) * np.cos(np.pi * y / 2)
+
+    # constraint matrix and explicit right-hand side from arrays = those of the reference's compute_linear_system
+    b1 = batch.basis_2d.basis_xi
+    row, col, val, con_rhs, n_trace = ST.system_constraints(nh, nv, p, raw["form_orders"], (), [(0, steady_u)], g["corners"], np.asarray(b1.roots),
+                                                            np.asarray(b1.rule.nodes), np.asarray(b1.rule.weights))
+    assert np.array_equal(row, g["con_row"]) and np.array_equal(col, g["con_col"]) and np.array_equal(val, g["con_val"])
+    assert np.max(np.abs(con_rhs - g["con_rhs"])) < 1e-15
+    explicit = 1.0 * np.asarray(batch.dual_dofs(1, steady_u)).ravel()
+    assert np.max(np.abs(explicit - g["explicit"])) < 1e-13 * np.max(np.abs(g["explicit"]))
+    ref = g["solutions"]
+    for device in (False, True):
+        sols, iters = CL.trapezoidal_march(specs, lhs, rhs_codes, batch, (row, col, val), n_trace, con_rhs, explicit, [0], float(g["dt"]), int(g["nt"]),
+                                           max_iterations=40, atol=1e-12, rtol=0.0, symmetric=True, device=device)
+        assert [int(i) for i in iters] == [int(i) for i in g["iterations"]], (device, iters, g["iterations"])
+        for i, sv in enumerate(sols):
+            assert relerr(sv, ref[i + 1]) < 1e-8, (device, i, relerr(sv, ref[i + 1]))
+    return iters
+
+
 def check_reconstruct_grid(M, p=4, k=2):
     """reconstruct (python/mfv2d/mimetic2d.py:1172-1279) on tensor grids of arbitrary reference points, restated here with
     numpy straight from the formulas (Lagrange values for nodal factors, minus the running sum of derivatives for edge

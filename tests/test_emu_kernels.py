@@ -127,3 +127,7 @@ def test_reconstruct_grid(emu):
 
 def test_inverse_definite(emu):
     P.check_inverse_definite(emu[0])
+
+
+def test_time_march_heat(emu):
+    print(P.check_time_march_heat(*emu))

@@ -192,3 +192,7 @@ def test_full_size_properties(gpu):
 
 def test_inverse_definite(gpu):
     P.check_inverse_definite(gpu[0])
+
+
+def test_time_march_heat(gpu):
+    print(P.check_time_march_heat(*gpu))
