@@ -985,6 +985,45 @@ def check_time_march_heat(M, SV, ST):
     return iters
 
 
+def check_time_march_reaction(M, SV, ST, name):
+    """The time-march examples with INITIAL CONDITIONS against the reference's own solve_system_2d (tests/golden/
+    timemarch_reaction.npz: examples/unsteady/plot_reaction.py, plot_reaction_mixed.py, plot_vector_reaction.py): the L2 projection
+    of the initial functions (dual DoFs, then the matrix-free inverse-mass apply) and three trapezoidal steps from it."""
+    from mfv2d_b200 import callers as CL
+
+    g = golden("timemarch_reaction.npz")
+    raw = json.loads(str(g[name + "_codes"]))
+    lhs = tuple(tuple(None if blk is None else tuple(tuple(item) for item in blk) for blk in rowc) for rowc in raw["lhs"])
+    assert raw["rhs"] is None
+    p, k = int(g["order"]), int(g["k"])
+    specs = M._ElementFormSpecification(*zip(raw["form_names"], raw["form_orders"]))
+    batch = M.ElementBatch(make_basis(M, p, k), np.ascontiguousarray(g["corners"]))
+    n, ne = batch.n, specs.total_size(p, p)
+    initial = {
+        "reaction": {"u": lambda x, y: 2 * np.cos(np.pi * x / 2) * np.cos(np.pi * y / 2)},
+        "reaction_mixed": {"u": lambda x, y: (1 - x**2) * (1 - y**2), "q": lambda x, y: np.stack((-2 * x * (1 - y**2), -2 * y * (1 - x**2)), axis=-1)},
+        "vector_reaction": {"u": lambda x, y: np.stack((2 * x * y, x**2 * y), axis=-1)},
+    }[name]
+    # initial conditions: dual DoFs of the given functions (zero for the other forms), primal = M^-1 dual per form
+    dual = np.zeros((n, ne))
+    for fi, (fname, order) in enumerate(zip(raw["form_names"], raw["form_orders"])):
+        if fname in initial:
+            o = specs.form_offset(fi, p, p)
+            dual[:, o:o + specs.form_size(fi, p, p)] = batch.dual_dofs(int(order), initial[fname])
+    assert np.max(np.abs(dual.ravel() - g[name + "_initial_dual"])) < 1e-13 * np.max(np.abs(g[name + "_initial_dual"]))
+    primal = np.asarray(M.compute_element_primal_from_dual(specs, dual, batch)).ravel()
+    ref = g[name + "_solutions"]
+    assert relerr(primal, ref[0]) < 1e-11, relerr(primal, ref[0])
+    con = (g[name + "_con_row"], g[name + "_con_col"], g[name + "_con_val"])
+    for device in (False, True):
+        sols, iters = CL.trapezoidal_march(specs, lhs, None, batch, con, g[name + "_con_rhs"].size, g[name + "_con_rhs"], g[name + "_explicit"],
+                                           raw["march_forms"], float(g["dt"]), int(g["nt"]), max_iterations=20, atol=1e-12, rtol=0.0,
+                                           symmetric=(name == "vector_reaction"), initial_solution=primal, initial_dual=dual.ravel(), device=device)
+        for i, sv in enumerate(sols):
+            assert relerr(sv, ref[i + 1]) < 1e-8, (name, device, i, relerr(sv, ref[i + 1]))
+    return iters
+
+
 def check_reconstruct_grid(M, p=4, k=2):
     """reconstruct (python/mfv2d/mimetic2d.py:1172-1279) on tensor grids of arbitrary reference points, restated here with
     numpy straight from the formulas (Lagrange values for nodal factors, minus the running sum of derivatives for edge

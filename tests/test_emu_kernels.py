@@ -131,3 +131,8 @@ def test_inverse_definite(emu):
 
 def test_time_march_heat(emu):
     print(P.check_time_march_heat(*emu))
+
+
+@pytest.mark.parametrize("name", ["reaction", "reaction_mixed", "vector_reaction"])
+def test_time_march_reaction(emu, name):
+    print(P.check_time_march_reaction(*emu, name))

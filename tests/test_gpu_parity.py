@@ -196,3 +196,8 @@ def test_inverse_definite(gpu):
 
 def test_time_march_heat(gpu):
     print(P.check_time_march_heat(*gpu))
+
+
+@pytest.mark.parametrize("name", ["reaction", "reaction_mixed", "vector_reaction"])
+def test_time_march_reaction(gpu, name):
+    print(P.check_time_march_reaction(*gpu, name))
