@@ -1,5 +1,6 @@
 """Fixtures for the remaining time-march examples with INITIAL CONDITIONS: examples/unsteady/plot_reaction.py (u0, q1),
-plot_reaction_mixed.py (u2, q1, weak boundary term) and plot_vector_reaction.py (u1).
+plot_reaction_mixed.py (u2, q1, weak boundary term) and plot_vector_reaction.py (u1); and plot_heat_mixed.py (u2, q1: no initial
+condition, weak boundary term, right-hand-side bytecode).
 
 Run in the build container (needs /root/reference):  python tests/golden/make_golden_marches.py
 For each, the reference's own `solve_system_2d` marches the example's system (:118-122, :111-114, :86-89) with its initial
@@ -79,7 +80,16 @@ def cases():
     u1 = KFormUnknown("u", O1)
     v1 = u1.weight
     out["vector_reaction"] = (KFormSystem(0.5 * (v1 @ u1) == 0.5 * (v1 @ v_final_u), sorting=lambda f: f.order), {v1: u1}, {u1: v_initial_u})
+    # examples/unsteady/plot_heat_mixed.py:64-68: no initial condition, weak boundary term, the term in u on the right (fixed point)
+    uh, qh = KFormUnknown("u", O2), KFormUnknown("q", O1)
+    vh, ph = uh.weight, qh.weight
+    out["heat_mixed"] = (KFormSystem(ph.derivative @ uh - ph @ qh == ph ^ h_steady_u,
+                                     0.02 * (vh @ qh.derivative) == 1.0 * (vh @ h_steady_u) - (1.0 - 0.02 * np.pi**2 / 2) * (vh @ uh)), {vh: uh}, {})
     return out
+
+
+def h_steady_u(x, y):
+    return np.cos(np.pi * x / 2) * np.cos(np.pi * y / 2)
 
 
 def main(nh=4, nv=3, order=3, dt=0.25, nt=3):
@@ -119,10 +129,10 @@ def main(nh=4, nv=3, order=3, dt=0.25, nt=3):
         specs = marched.unknown_forms
         codes = {"form_names": list(specs.names), "form_orders": [int(x) for x in specs.orders], "lhs": encode_codes(comp.lhs_codes),
                  "rhs": encode_codes(comp.rhs_codes), "march_forms": sorted(list(marched.weight_forms).index(w) for w in relations)}
-        assert len(cap["solutions"]) == nt + 1 and len(cap["duals"]) == len(leaf)
+        assert len(cap["solutions"]) == nt + 1 and len(cap["duals"]) == (len(leaf) if initial else 0)
         data[name + "_codes"] = json.dumps(codes)
         data[name + "_explicit"] = np.concatenate(cap["vectors"])
-        data[name + "_initial_dual"] = np.concatenate(cap["duals"])
+        data[name + "_initial_dual"] = np.concatenate(cap["duals"]) if initial else np.zeros(0)
         data[name + "_solutions"] = np.stack(cap["solutions"])
         if cap["lag"] is not None:
             m = cap["lag"].tocoo()

@@ -133,6 +133,6 @@ def test_time_march_heat(emu):
     print(P.check_time_march_heat(*emu))
 
 
-@pytest.mark.parametrize("name", ["reaction", "reaction_mixed", "vector_reaction"])
+@pytest.mark.parametrize("name", ["reaction", "reaction_mixed", "vector_reaction", "heat_mixed"])
 def test_time_march_reaction(emu, name):
     print(P.check_time_march_reaction(*emu, name))

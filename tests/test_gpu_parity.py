@@ -198,6 +198,6 @@ def test_time_march_heat(gpu):
     print(P.check_time_march_heat(*gpu))
 
 
-@pytest.mark.parametrize("name", ["reaction", "reaction_mixed", "vector_reaction"])
+@pytest.mark.parametrize("name", ["reaction", "reaction_mixed", "vector_reaction", "heat_mixed"])
 def test_time_march_reaction(gpu, name):
     print(P.check_time_march_reaction(*gpu, name))
