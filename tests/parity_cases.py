@@ -713,6 +713,49 @@ def check_partitioned_bicgstab(M, SV, ST, ctx, rank, world, all_gather, nh=8, nv
     return int(it), max(ex, el)
 
 
+def check_partitioned_march(M, SV, ST, ctx, rank, world, all_gather, nh=8, nv=8):
+    """One rank of the PARTITIONED time march (configs[2] on several GPUs, in small): the strips of the 8 x 8 order-4
+    advection-diffusion fixture march together - interface sums and BiCGStab scalars through the peer blocks, the stopping
+    test of every correction through `reduce_max` - with host vectors and with device-resident vectors; every rank's strip of
+    every step must equal the reference's own march (tests/golden/timemarch_advdif.npz)."""
+    from mfv2d_b200 import callers as CL
+
+    g, raw, lhs, specs = _timemarch_system(M)
+    p, k = int(g["order"]), int(g["k"])
+    ne = specs.total_size(p, p)
+    corners = np.ascontiguousarray(g["corners"])
+    row, col, val, nt = g["con_row"], g["con_col"], g["con_val"], g["con_rhs"].size
+    parts = ST.strip_partition(nh, nv, world)
+    bounds = [parts[r][0] * ne for r in range(world)] + [parts[-1][1] * ne]
+    lo, hi = parts[rank]
+    batch = M.ElementBatch(make_basis(M, p, k), np.ascontiguousarray(corners[lo:hi]), ctx)
+    if world > 1:
+        P = ST.partition_constraints(row, col, val, nt, bounds, rank)
+        prow, pcol, pval, pnt, rows_glob = P.row, P.col, P.val, P.n_trace, P.global_rows
+    else:
+        prow, pcol, pval, pnt, rows_glob = row, col, val, nt, np.arange(nt)
+    explicit = np.ascontiguousarray(g["explicit"][bounds[rank]:bounds[rank + 1]])
+    con_rhs = np.ascontiguousarray(g["con_rhs"][rows_glob])
+    reduce_max = (lambda v: max(all_gather(float(v)))) if world > 1 else None
+    ref = g["solutions"]
+    out = []
+    for device in (False, True):
+        system = SV.compute_linear_system(specs, lhs, batch, (prow, pcol, pval), pnt)
+        if world > 1:
+            system.set_interface(P.shared_index, P.slot, P.n_slots, P.owned)
+            system.connect_peers(P.holder_ptr, P.holder_rank, all_gather)
+        sols, iters = CL.trapezoidal_march(specs, lhs, None, batch, (prow, pcol, pval), pnt, con_rhs, explicit, [raw["form_names"].index("u")],
+                                           float(g["dt"]), int(g["nt"]), system=system, reduce_max=reduce_max, device=device)
+        assert not (world > 1 and system.peer_error())
+        for i, sv in enumerate(sols):
+            assert relerr(sv, ref[i + 1][bounds[rank]:bounds[rank + 1]]) < 1e-8, (rank, device, i)
+        counts = all_gather(tuple(int(i) for i in iters))
+        assert all(c == counts[0] for c in counts), counts
+        out.append(tuple(int(i) for i in iters))
+    assert out[0] == out[1]
+    return out[0]
+
+
 def check_multilevel(M, SV, ST, ctx, rank, world, all_gather, nh=24, nv=24, p=2, k=2, mid_sizes=(2,), exact_size=6, deform=None):
     """The multilevel preconditioner (precond.cu) on a synthetic deformed mesh, one rank of ``world``: same solution as the
     Jacobi-preconditioned CG, clearly fewer iterations, identical counts on every rank."""

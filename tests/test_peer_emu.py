@@ -88,3 +88,10 @@ def test_peer_exchange_bicgstab(emu, world):
     """BiCGStab on a non-symmetric (advection-diffusion) system, partitioned into strips, against a direct sparse solve"""
     res = run_ranks(emu, world, P.check_partitioned_bicgstab)
     assert all(r[0] == res[0][0] for r in res)
+
+
+@pytest.mark.parametrize("world", [1, 2, 4])
+def test_partitioned_time_march(emu, world):
+    """the trapezoidal march on strips (host vectors and device-resident vectors), every strip against the reference's march"""
+    res = run_ranks(emu, world, P.check_partitioned_march)
+    assert all(r == res[0] for r in res)
