@@ -255,6 +255,36 @@ def check_dense(M):
         raise AssertionError("singular matrix must raise MFV2D_PIVOT_FAILED")
 
 
+def check_empty_and_unconstrained(M, SV):
+    """Edge cases: a batch without elements, a system without constraint rows (every solver reduces to the block solve), a
+    system without elements, an empty vector."""
+    from mfv2d_b200 import callers as CL
+
+    s = SYSTEMS["mixed_poisson_sorted"]
+    specs = specs_of(M, s)
+    p, k = 3, 2
+    ne = specs.total_size(p, p)
+    b0 = M.ElementBatch(make_basis(M, p, k), np.zeros((0, 4, 2)))
+    assert M.compute_element_matrices(specs, s["lhs"], b0).shape == (0, ne, ne)
+    assert M.compute_element_vectors(specs, s["lhs"], b0, np.zeros((0, ne))).shape == (0, ne)
+    assert b0.mass(2).shape == (0, 2 * p * (p + 1), 2 * p * (p + 1))
+    batch = M.ElementBatch(make_basis(M, p, k), np.ascontiguousarray(F.QUADS[:3]))
+    mats = M.compute_element_matrices(specs, s["lhs"], batch)
+    none = (np.zeros(0, np.int64), np.zeros(0, np.int64), np.zeros(0))
+    sysm = SV.LinearSystem(mats, none, 0)
+    rhs = np.random.default_rng(8).standard_normal(3 * ne)
+    ref = np.concatenate([np.linalg.solve(mats[e], rhs[e * ne:(e + 1) * ne]) for e in range(3)])
+    conv = SV.ConvergenceSettings(10, 1e-12, 1e-12)
+    for solve in (SV.solve_schur_iterative, SV.solve_schur_bicgstab, SV.solve_pcg_iterative):
+        x, lam, _res, it = solve(sysm, rhs, np.zeros(0), conv)
+        assert lam.shape == (0,) and it == 0 and relerr(x, ref) < 1e-11, solve.__name__
+    assert sysm.apply_trace(rhs).shape == (0,) and not np.any(sysm.apply_trace_transpose(np.zeros(0)))
+    empty = SV.LinearSystem(np.zeros((0, ne, ne)), none, 0)
+    assert empty.n_dense == 0 and empty.apply_diagonal(np.zeros(0)).shape == (0,)
+    assert CL.vec_absmax(np.zeros(0), batch.ctx) == 0.0
+    assert relerr(M.inverse_definite(np.array([[4.0]])), np.array([[0.25]])) < 1e-15
+
+
 def check_inverse_definite(M, sizes=(5, 64, 100, 333)):
     """The large-matrix inverse behind the preconditioner's exact level (blocked Gauss-Jordan without pivoting from 64 x 64 on,
     one pivot per pass below) against numpy on SPD and on non-symmetric diagonally dominant matrices, sizes that are not

@@ -136,3 +136,7 @@ def test_time_march_heat(emu):
 @pytest.mark.parametrize("name", ["reaction", "reaction_mixed", "vector_reaction", "heat_mixed"])
 def test_time_march_reaction(emu, name):
     print(P.check_time_march_reaction(*emu, name))
+
+
+def test_empty_and_unconstrained(emu):
+    P.check_empty_and_unconstrained(emu[0], emu[1])

@@ -201,3 +201,7 @@ def test_time_march_heat(gpu):
 @pytest.mark.parametrize("name", ["reaction", "reaction_mixed", "vector_reaction", "heat_mixed"])
 def test_time_march_reaction(gpu, name):
     print(P.check_time_march_reaction(*gpu, name))
+
+
+def test_empty_and_unconstrained(gpu):
+    P.check_empty_and_unconstrained(gpu[0], gpu[1])
