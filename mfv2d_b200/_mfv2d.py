@@ -578,6 +578,16 @@ class ElementBatch:
         return vals
 
 
+def _check_field_values(field_values, plan: "Plan", batch: "ElementBatch"):
+    """caller-evaluated fields: ``(n_fields, n, q, q, 2)`` - the kernels index that layout, a smaller buffer must not reach them"""
+    if field_values is not None and plan.n_fields:
+        want = plan.n_fields * batch.n * batch.q * batch.q * 2
+        if int(field_values.size) != want:
+            raise ValueError(f"field_values must have the shape {(plan.n_fields, batch.n, batch.q, batch.q, 2)} ({want} entries), "
+                             f"got {int(field_values.size)} entries")
+    return field_values
+
+
 def _as_dofs(dofs, n: int, size: int, needed: bool):
     if dofs is None:
         if needed:
@@ -599,6 +609,7 @@ def compute_element_matrices(form_specs, expressions, batch: ElementBatch, degre
     dofs = _as_dofs(degrees_of_freedom, batch.n, plan.size, plan.needs_dofs)
     if field_values is None:
         field_values = batch.evaluate_callable_fields(plan)
+    _check_field_values(field_values, plan, batch)
     out = batch._out(out, (batch.n, plan.size, plan.size))
     space = space_of(out)
     if space == DEVICE:
@@ -617,6 +628,7 @@ def compute_element_vectors(form_specs, expressions, batch: ElementBatch, degree
     dofs = _as_dofs(degrees_of_freedom, batch.n, plan.size, True)
     if field_values is None:
         field_values = batch.evaluate_callable_fields(plan)
+    _check_field_values(field_values, plan, batch)
     out = batch._out(out, (batch.n, plan.size))
     space = space_of(out)
     if space == DEVICE:

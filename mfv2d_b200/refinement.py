@@ -78,6 +78,8 @@ def batched_matvec(ctx, mats, x, out=None):
     n, r, c = mats.shape
     if out is None:
         out = ctx.empty((n, r)) if isinstance(mats, DeviceArray) else np.empty((n, r))
+    if int(x.size) != n * c or int(out.size) != n * r:
+        raise ValueError(f"batched_matvec: {n} matrices of {r} x {c} against vectors of {int(x.size)} and {int(out.size)} entries")
     check(lib().mfv2d_cuda_batched_gemv(ctx.handle, n, r, c, addr(mats), addr(x), addr(out), space_of(mats, x, out)), ctx.handle)
     return out
 

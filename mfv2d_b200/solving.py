@@ -277,6 +277,13 @@ class LinearSystem:
 PRECONDITIONERS = {False: 0, None: 0, "none": 0, True: 1, "jacobi": 1, "multilevel": 2}
 
 
+def _check_solver_vectors(system: "LinearSystem", rhs, constraints) -> None:
+    """The C entry points read ``n_dense`` / ``n_trace`` doubles: a shorter buffer must never reach them."""
+    if int(rhs.size) != system.n_dense or int(constraints.size) != system.n_trace:
+        raise ValueError(f"right-hand sides of {int(rhs.size)} and {int(constraints.size)} entries do not match the system "
+                         f"({system.n_dense} dense unknowns, {system.n_trace} multipliers) (MFV2D_BAD_VECTOR_PARENT)")
+
+
 def solve_schur_iterative(system: LinearSystem, rhs, constraints, convergence: ConvergenceSettings, precondition=False, out=None):
     """python/mfv2d/solving.py:439-500: CG on ``N A^-1 N^T`` for the multipliers, then back substitution.
     Returns ``(x, lambda, residual, iterations)`` like the reference.  ``precondition``: ``False`` (the reference's
@@ -287,10 +294,14 @@ def solve_schur_iterative(system: LinearSystem, rhs, constraints, convergence: C
         return DenseVector.__new__(DenseVector)._init(system, xd), TraceVector.__new__(TraceVector)._init(system, ld), r, i
     dev = isinstance(rhs, DeviceArray)
     if dev:
+        _check_solver_vectors(system, rhs, constraints)
         x, lam = out if out is not None else (system.ctx.empty(system.n_dense), system.ctx.empty(system.n_trace))
+        if int(x.size) != system.n_dense or int(lam.size) != system.n_trace:
+            raise ValueError("out must be device arrays of the dense and trace sizes")
     else:
         rhs = np.ascontiguousarray(rhs, np.float64)
         constraints = np.ascontiguousarray(constraints, np.float64)
+        _check_solver_vectors(system, rhs, constraints)
         x, lam = out if out is not None else (np.empty(system.n_dense), np.empty(system.n_trace))
         if x.shape != (system.n_dense,) or lam.shape != (system.n_trace,) or x.dtype != np.float64 or lam.dtype != np.float64:
             raise ValueError("out must be float64 arrays of the dense and trace sizes")
@@ -313,10 +324,12 @@ def solve_schur_bicgstab(system: LinearSystem, rhs, constraints, convergence: Co
         xd, ld, r, i = solve_schur_bicgstab(system, rhs.data, constraints.data, convergence, precondition)
         return DenseVector.__new__(DenseVector)._init(system, xd), TraceVector.__new__(TraceVector)._init(system, ld), r, i
     if isinstance(rhs, DeviceArray):
+        _check_solver_vectors(system, rhs, constraints)
         x, lam = system.ctx.empty(system.n_dense), system.ctx.empty(system.n_trace)
     else:
         rhs = np.ascontiguousarray(rhs, np.float64)
         constraints = np.ascontiguousarray(constraints, np.float64)
+        _check_solver_vectors(system, rhs, constraints)
         x, lam = np.empty(system.n_dense), np.empty(system.n_trace)
     res, it = C.c_double(), C.c_int()
     check(
@@ -336,10 +349,12 @@ def solve_pcg_iterative(system: LinearSystem, rhs, constraints, convergence: Con
         return DenseVector.__new__(DenseVector)._init(system, xd), TraceVector.__new__(TraceVector)._init(system, ld), r, i
     dev = isinstance(rhs, DeviceArray)
     if dev:
+        _check_solver_vectors(system, rhs, constraints)
         x, lam = system.ctx.empty(system.n_dense), system.ctx.empty(system.n_trace)
     else:
         rhs = np.ascontiguousarray(rhs, np.float64)
         constraints = np.ascontiguousarray(constraints, np.float64)
+        _check_solver_vectors(system, rhs, constraints)
         x, lam = np.empty(system.n_dense), np.empty(system.n_trace)
     res, it = C.c_double(), C.c_int()
     check(
@@ -356,12 +371,16 @@ def vec_axpby(a: float, x, b: float, y, out=None, ctx: Context | None = None):
     ctx = ctx or get_context()
     if out is None:
         out = ctx.empty(x.size) if isinstance(x, DeviceArray) else np.empty(x.size)
+    if int(y.size) != int(x.size) or int(out.size) != int(x.size):
+        raise ValueError(f"vec_axpby: operands of {int(x.size)}, {int(y.size)} and {int(out.size)} entries")
     check(lib().mfv2d_cuda_vec_axpby(ctx.handle, x.size, float(a), addr(x), float(b), addr(y), addr(out), space_of(x, y, out)), ctx.handle)
     return out
 
 
 def vec_dot(x, y, ctx: Context | None = None) -> float:
     ctx = ctx or get_context()
+    if int(y.size) != int(x.size):
+        raise ValueError(f"vec_dot: operands of {int(x.size)} and {int(y.size)} entries")
     r = C.c_double()
     check(lib().mfv2d_cuda_vec_dot(ctx.handle, x.size, addr(x), addr(y), C.byref(r), space_of(x, y)), ctx.handle)
     return r.value

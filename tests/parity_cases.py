@@ -283,6 +283,21 @@ def check_empty_and_unconstrained(M, SV):
     assert empty.n_dense == 0 and empty.apply_diagonal(np.zeros(0)).shape == (0,)
     assert CL.vec_absmax(np.zeros(0), batch.ctx) == 0.0
     assert relerr(M.inverse_definite(np.array([[4.0]])), np.array([[0.25]])) < 1e-15
+    # buffers of the wrong size never reach the library (it reads n_dense / n_trace entries)
+    one = SV.LinearSystem(mats, (np.array([0, 0]), np.array([0, ne]), np.array([1.0, -1.0])), 1)
+    for solve in (SV.solve_schur_iterative, SV.solve_schur_bicgstab, SV.solve_pcg_iterative):
+        for bad in ((np.ones(5), np.zeros(1)), (rhs, np.zeros(3))):
+            with pytest.raises(ValueError):
+                solve(one, bad[0], bad[1], conv)
+    with pytest.raises(ValueError):
+        SV.vec_axpby(1.0, np.ones(4), 1.0, np.ones(3))
+    with pytest.raises(ValueError):
+        SV.vec_dot(np.ones(4), np.ones(3))
+    with pytest.raises(ValueError):
+        one.apply_diagonal(np.ones(3))
+    adv = SYSTEMS["adv_dif"]
+    with pytest.raises(ValueError):  # caller-evaluated fields of the wrong size
+        M.compute_element_matrices(specs_of(M, adv), adv["lhs"], batch, None, np.zeros((1, 3, 2, 2, 2)))
 
 
 def check_inverse_definite(M, sizes=(5, 64, 100, 333)):
