@@ -478,6 +478,19 @@ class ElementBatch:
     def form_size(self, order: int) -> int:
         return _form_size(order, self.p, self.p)
 
+    @staticmethod
+    def _in(a, shape, name: str):
+        """an input buffer of exactly ``shape`` (numpy: made contiguous float64; DeviceArray: size checked): the kernels index
+        that layout, so nothing shorter may reach them"""
+        if isinstance(a, DeviceArray):
+            if a.size != int(np.prod(shape)) or a.dtype != np.float64:
+                raise ValueError(f"{name} must hold {tuple(shape)} float64 values, got {a.shape} {a.dtype}")
+            return a
+        a = np.ascontiguousarray(a, np.float64)
+        if a.size != int(np.prod(shape)):
+            raise ValueError(f"{name} must have the shape {tuple(shape)}, got {a.shape}")
+        return a
+
     def mass(self, order: int, inverse: bool = False, out=None):
         """Mass matrices of 0-/1-/2-forms ``(n, n_k, n_k)`` (src/fem_space/fem_space.c:235-411)."""
         order = int(order)
@@ -518,6 +531,7 @@ class ElementBatch:
         if transpose:
             shape = shape[::-1]
         out = self._out(out, (self.n,) + shape)
+        field = self._in(field, (self.n, self.q, self.q, 2), "field")
         check(lib().mfv2d_cuda_interprod_batch(self.handle, int(start_order), int(bool(transpose)), addr(field), addr(out),
                                                space_of(field, out)), self.ctx.handle)
         return out
@@ -526,6 +540,7 @@ class ElementBatch:
         """Field values at the quadrature points from DoFs ``(n, n_k)`` (integrating_fields.c:238-352)."""
         shape = (self.n, self.q, self.q, 2) if int(order) == FORM_ORDER_1 else (self.n, self.q, self.q)
         out = self._out(out, shape)
+        dofs = self._in(dofs, (self.n, self.form_size(int(order))), "dofs")
         check(lib().mfv2d_cuda_reconstruct_batch(self.handle, int(order), addr(dofs), addr(out), space_of(dofs, out)), self.ctx.handle)
         return out
 
@@ -537,6 +552,7 @@ class ElementBatch:
         eta = np.ascontiguousarray(eta, np.float64).ravel()
         shape = (self.n, eta.size, xi.size, 2) if int(order) == FORM_ORDER_1 else (self.n, eta.size, xi.size)
         out = self._out(out, shape)
+        dofs = self._in(dofs, (self.n, self.form_size(int(order))), "dofs")
         check(lib().mfv2d_cuda_reconstruct_grid_batch(self.handle, int(order), addr(dofs), xi.size, xi.ctypes.data, eta.size, eta.ctypes.data,
                                                       addr(out), space_of(dofs, out)), self.ctx.handle)
         return out

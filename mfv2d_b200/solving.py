@@ -147,6 +147,8 @@ class LinearSystem:
             row, col, val = constraints_to_coo(constraints, self.offsets)
             n_trace = len(constraints)
             self.constraint_rhs = np.array([c.rhs for c in constraints], np.float64)
+        if not (row.size == col.size == val.size):
+            raise ValueError(f"constraint triplets of different lengths: {row.size} rows, {col.size} columns, {val.size} values")
         self.con = (row, col, val)
         self.n_trace = int(n_trace)
         self.n_dense = int(self.offsets[-1])
@@ -230,7 +232,9 @@ class LinearSystem:
         si = np.ascontiguousarray(shared_index, np.int64)
         sl = np.ascontiguousarray(slot, np.int64)
         ow = np.ascontiguousarray(owned, np.uint8)
-        assert ow.size == self.n_trace
+        if ow.size != self.n_trace or si.size != sl.size:
+            raise ValueError(f"set_interface: owned must have {self.n_trace} entries (got {ow.size}), shared_index and slot the same length "
+                             f"({si.size}, {sl.size})")
         check(lib().mfv2d_cuda_system_set_interface(self.handle, si.size, si.ctypes.data, sl.ctypes.data, int(n_slots), ow.ctypes.data),
               self.ctx.handle)
 
@@ -247,6 +251,8 @@ class LinearSystem:
         blob = b"".join(handles)
         hp = np.ascontiguousarray(holder_ptr, np.int64)
         hr = np.ascontiguousarray(holder_rank, np.int32)
+        if hp.size < 1 or int(hp[-1]) != hr.size or len(blob) != n * len(handles):
+            raise ValueError("connect_peers: holder_ptr must be a CSR pointer over holder_rank and every rank must contribute one handle")
         hbuf = (C.c_char * len(blob)).from_buffer_copy(blob)
         check(lib().mfv2d_cuda_system_peer_connect(self.handle, hbuf, hp.size - 1, hp.ctypes.data, hr.ctypes.data if hr.size else None),
               self.ctx.handle)
