@@ -59,6 +59,7 @@ class QuadForest:
         if np.any(is_leaf != (self.leaf_index >= 0)):
             raise ValueError("leaf_elements must list exactly the elements without children")
         self._gll: dict[int, np.ndarray] = {}
+        self._side_matrix: dict = {}
 
     # ---- small queries ----------------------------------------------------------------------------------------------
     def is_split(self, e: int) -> bool:
@@ -78,6 +79,13 @@ class QuadForest:
             return self.order(e)
         a, b = self.pair_on_side(e, side)
         return self.side_order(a, side) + self.side_order(b, side)
+
+    def _side_shape(self, e: int, side: int):
+        """nested tuple of the leaf orders along ``side``: the key of the side's interpolation matrix"""
+        if not self.is_split(e):
+            return self.order(e)
+        a, b = self.pair_on_side(e, side)
+        return (self._side_shape(a, side), self._side_shape(b, side))
 
     def nodes(self, order: int) -> np.ndarray:
         if order not in self._gll:
@@ -142,17 +150,20 @@ class QuadForest:
             leaf = int(self.leaf_index[e])
             return [[(leaf, np.array([d], np.int64), np.ones(1))] for d in _side_dofs(side, form, self.order(e))]
         pieces = self.side_pieces(e, side, form)
-        own_nodes = self.nodes(own)
-        nodal = M.lagrange1d(own_nodes, np.concatenate([s.pos for s in pieces]))
-        if form == FORM_ORDER_0:
-            m = np.linalg.inv(nodal)
-        elif form == FORM_ORDER_1:
-            m = np.linalg.inv(self._edge_basis(nodal))
-        else:
+        if form not in (FORM_ORDER_0, FORM_ORDER_1):
             raise ValueError("2-forms have no boundary DoFs.")
-        if out_order != own:
-            to_out = M.lagrange1d(own_nodes, self.nodes(out_order))
-            m = (to_out if form == FORM_ORDER_0 else self._edge_basis(to_out)) @ m
+        # the interpolation matrix depends on the SHAPE of the side only (how it is split and the orders of its leaves), not
+        # on which elements they are: computed once per shape (same arithmetic, so the coefficients stay bit-identical)
+        key = (form, out_order, self._side_shape(e, side))
+        m = self._side_matrix.get(key)
+        if m is None:
+            own_nodes = self.nodes(own)
+            nodal = M.lagrange1d(own_nodes, np.concatenate([s.pos for s in pieces]))
+            m = np.linalg.inv(nodal) if form == FORM_ORDER_0 else np.linalg.inv(self._edge_basis(nodal))
+            if out_order != own:
+                to_out = M.lagrange1d(own_nodes, self.nodes(out_order))
+                m = (to_out if form == FORM_ORDER_0 else self._edge_basis(to_out)) @ m
+            self._side_matrix[key] = m
         rows = []
         for coeffs in m:
             at, row = 0, []
